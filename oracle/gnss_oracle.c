@@ -1,0 +1,843 @@
+/* TEST INFRASTRUCTURE ONLY -- see gnss_oracle.h for scope and parity status.
+ * Build: oracle/Makefile (gcc -O3 -ffp-contract=off: no FMA contraction).
+ * All reference citations are relative to /root/reference/. "volk:" abbreviates
+ * src/algorithms/libs/volk_gnsssdr_module/volk_gnsssdr/kernels/volk_gnsssdr/.
+ */
+#include "gnss_oracle.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct { float re, im; } cf;
+typedef struct { double re, im; } cd;
+
+/* C99 complex-float product as GCC evaluates `a * b` without -ffast-math / FMA */
+static inline cf cmulf_(cf a, cf b)
+{
+    cf r;
+    r.re = a.re * b.re - a.im * b.im;
+    r.im = a.re * b.im + a.im * b.re;
+    return r;
+}
+
+/* ======================= tracking ======================= */
+
+/* volk: volk_gnsssdr_32f_xn_resampler_32f_xn.h:77-95 (_generic) */
+static inline int chip_index_(float v, int code_len)
+{
+    int idx = (int)floor((double)v);
+    if (idx < 0) idx += code_len * (int)((unsigned)abs(idx) / (unsigned)code_len + 1u);
+    idx = (int)((unsigned)idx % (unsigned)code_len);
+    return idx;
+}
+
+void go_resampler_real(float* out, const float* code, float rem_chips, float step_chips,
+    const float* shifts, int code_len, int n_taps, int n)
+{
+    for (int t = 0; t < n_taps; t++)
+        {
+            float* o = out + (size_t)t * n;
+            for (unsigned k = 0; k < (unsigned)n; k++)
+                {
+                    float v = step_chips * (float)k + shifts[t] - rem_chips; /* left to right, float32 */
+                    o[k] = code[chip_index_(v, code_len)];
+                }
+        }
+}
+
+/* volk: volk_gnsssdr_32f_xn_high_dynamics_resampler_32f_xn.h:81-106 (_generic).
+ * tap 0 gets the rate*(float)(n*n) term with n*n in unsigned arithmetic (wraps at n>=65536);
+ * taps >=1 are circular SAMPLE shifts of tap 0. */
+void go_resampler_real_hd(float* out, const float* code, float rem_chips, float step_chips,
+    float rate_chips, const float* shifts, int code_len, int n_taps, int n)
+{
+    for (unsigned k = 0; k < (unsigned)n; k++)
+        {
+            float v = step_chips * (float)k + rate_chips * (float)(k * k) + shifts[0] - rem_chips;
+            out[k] = code[chip_index_(v, code_len)];
+        }
+    unsigned shift_samples = 0;
+    for (int t = 1; t < n_taps; t++)
+        {
+            shift_samples += (unsigned)(int)round((double)((shifts[t] - shifts[t - 1]) / step_chips));
+            float* o = out + (size_t)t * n;
+            memcpy(o, out + shift_samples, ((size_t)n - shift_samples) * sizeof(float));
+            memcpy(o + ((size_t)n - shift_samples), out, (size_t)shift_samples * sizeof(float));
+        }
+}
+
+/* volk: volk_gnsssdr_32fc_xn_resampler_32fc_xn.h _generic (same index maths, complex code) */
+void go_resampler_cplx(float* out_iq, const float* code_iq, float rem_chips, float step_chips,
+    const float* shifts, int code_len, int n_taps, int n)
+{
+    for (int t = 0; t < n_taps; t++)
+        {
+            float* o = out_iq + (size_t)t * n * 2;
+            for (unsigned k = 0; k < (unsigned)n; k++)
+                {
+                    float v = step_chips * (float)k + shifts[t] - rem_chips;
+                    int idx = chip_index_(v, code_len);
+                    o[2 * k] = code_iq[2 * idx];
+                    o[2 * k + 1] = code_iq[2 * idx + 1];
+                }
+        }
+}
+
+/* volk: volk_gnsssdr_32fc_32f_rotator_dot_prod_32fc_xn.h:81-113 (_generic) */
+void go_rotator_dot_prod_real(float* result_iq, const float* in_iq, float inc_re, float inc_im,
+    float* phase_iq, const float* codes, int n_taps, int n)
+{
+    cf phase = {phase_iq[0], phase_iq[1]};
+    const cf inc = {inc_re, inc_im};
+    for (int t = 0; t < n_taps; t++) result_iq[2 * t] = result_iq[2 * t + 1] = 0.0f;
+    for (unsigned k = 0; k < (unsigned)n; k++)
+        {
+            cf x = {in_iq[2 * k], in_iq[2 * k + 1]};
+            cf w = cmulf_(x, phase);
+            if (k % 256 == 0)
+                {
+                    float a = hypotf(phase.re, phase.im);
+                    phase.re /= a;
+                    phase.im /= a;
+                }
+            phase = cmulf_(phase, inc);
+            for (int t = 0; t < n_taps; t++)
+                {
+                    float c = codes[(size_t)t * n + k];
+                    result_iq[2 * t] += w.re * c;
+                    result_iq[2 * t + 1] += w.im * c;
+                }
+        }
+    phase_iq[0] = phase.re;
+    phase_iq[1] = phase.im;
+}
+
+/* volk: volk_gnsssdr_32fc_32f_high_dynamic_rotator_dot_prod_32fc_xn.h:120-150 (_generic_arg
+ * formulation: rate phasor = (cos,sin)((float)(n*n)*arg(rate)); the cpowf form at :82-116 is the
+ * same number up to libm rounding).  Sample n is rotated by phase0*inc^n*rate^((n-1)^2): the rate
+ * factor is applied after the sample is used.  The n%256 renormalisation is a no-op on the result
+ * because *phase is overwritten (it only changes *phase transiently). */
+void go_rotator_dot_prod_real_hd(float* result_iq, const float* in_iq, float inc_re, float inc_im,
+    float rate_re, float rate_im, float* phase_iq, const float* codes, int n_taps, int n)
+{
+    cf phase = {phase_iq[0], phase_iq[1]};
+    cf phase_doppler = phase;
+    const cf inc = {inc_re, inc_im};
+    const float arga = atan2f(rate_im, rate_re);
+    for (int t = 0; t < n_taps; t++) result_iq[2 * t] = result_iq[2 * t + 1] = 0.0f;
+    for (unsigned k = 0; k < (unsigned)n; k++)
+        {
+            if (k % 256 == 0)
+                {
+                    float a = hypotf(phase.re, phase.im);
+                    phase.re /= a;
+                    phase.im /= a;
+                }
+            cf x = {in_iq[2 * k], in_iq[2 * k + 1]};
+            cf w = cmulf_(x, phase);
+            phase_doppler = cmulf_(phase_doppler, inc);
+            float theta = (float)(k * k) * arga;
+            cf pr = {cosf(theta), sinf(theta)};
+            phase = cmulf_(phase_doppler, pr);
+            for (int t = 0; t < n_taps; t++)
+                {
+                    float c = codes[(size_t)t * n + k];
+                    result_iq[2 * t] += w.re * c;
+                    result_iq[2 * t + 1] += w.im * c;
+                }
+        }
+    phase_iq[0] = phase.re;
+    phase_iq[1] = phase.im;
+}
+
+/* volk: volk_gnsssdr_32fc_x2_rotator_dot_prod_32fc_xn.h:81-120 (_generic) */
+void go_rotator_dot_prod_cplx(float* result_iq, const float* in_iq, float inc_re, float inc_im,
+    float* phase_iq, const float* codes_iq, int n_taps, int n)
+{
+    cf phase = {phase_iq[0], phase_iq[1]};
+    const cf inc = {inc_re, inc_im};
+    for (int t = 0; t < n_taps; t++) result_iq[2 * t] = result_iq[2 * t + 1] = 0.0f;
+    for (unsigned k = 0; k < (unsigned)n; k++)
+        {
+            cf x = {in_iq[2 * k], in_iq[2 * k + 1]};
+            cf w = cmulf_(x, phase);
+            if (k % 256 == 0)
+                {
+                    float a = hypotf(phase.re, phase.im);
+                    phase.re /= a;
+                    phase.im /= a;
+                }
+            phase = cmulf_(phase, inc);
+            for (int t = 0; t < n_taps; t++)
+                {
+                    const float* cc = codes_iq + ((size_t)t * n + k) * 2;
+                    cf c = {cc[0], cc[1]};
+                    cf p = cmulf_(w, c);
+                    result_iq[2 * t] += p.re;
+                    result_iq[2 * t + 1] += p.im;
+                }
+        }
+    phase_iq[0] = phase.re;
+    phase_iq[1] = phase.im;
+}
+
+/* src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:101-152 */
+void go_multicorrelator_real(const float* in_iq, int n, const float* code, int code_len, const float* shifts,
+    int n_taps, float rem_carr_phase_rad, float phase_step_rad, float phase_rate_step_rad,
+    float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips,
+    int high_dyn, float* corr_out_iq)
+{
+    float* codes = (float*)malloc(sizeof(float) * (size_t)n_taps * (size_t)n);
+    float phase[2] = {cosf(rem_carr_phase_rad), -sinf(rem_carr_phase_rad)}; /* :140-141 */
+    /* std::exp(lv_32fc_t(0.0, -step)) == std::polar(expf(0), -step) == (cosf(-step), sinf(-step)) */
+    if (high_dyn)
+        {
+            go_resampler_real_hd(codes, code, rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips, shifts, code_len, n_taps, n);
+            go_rotator_dot_prod_real_hd(corr_out_iq, in_iq, cosf(-phase_step_rad), sinf(-phase_step_rad),
+                cosf(-phase_rate_step_rad), sinf(-phase_rate_step_rad), phase, codes, n_taps, n);
+        }
+    else
+        {
+            go_resampler_real(codes, code, rem_code_phase_chips, code_phase_step_chips, shifts, code_len, n_taps, n);
+            go_rotator_dot_prod_real(corr_out_iq, in_iq, cosf(-phase_step_rad), sinf(-phase_step_rad), phase, codes, n_taps, n);
+        }
+    free(codes);
+}
+
+/* src/algorithms/tracking/libs/cpu_multicorrelator.cc:99-126 */
+void go_multicorrelator_cplx(const float* in_iq, int n, const float* code_iq, int code_len, const float* shifts,
+    int n_taps, float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips,
+    float code_phase_step_chips, float* corr_out_iq)
+{
+    float* codes = (float*)malloc(sizeof(float) * 2 * (size_t)n_taps * (size_t)n);
+    float phase[2] = {cosf(rem_carr_phase_rad), -sinf(rem_carr_phase_rad)};
+    go_resampler_cplx(codes, code_iq, rem_code_phase_chips, code_phase_step_chips, shifts, code_len, n_taps, n);
+    go_rotator_dot_prod_cplx(corr_out_iq, in_iq, cosf(-phase_step_rad), sinf(-phase_step_rad), phase, codes, n_taps, n);
+    free(codes);
+}
+
+/* Arbiter (not a reference function): same float32 chip indices as the reference resampler, but the
+ * carrier phase and the accumulation are evaluated in float64 with the exact phase
+ * -(rem + n*step) of the float32 arguments. */
+void go_multicorrelator_real_f64(const float* in_iq, int n, const float* code, int code_len, const float* shifts,
+    int n_taps, float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips,
+    float code_phase_step_chips, double* corr_out_iq)
+{
+    for (int t = 0; t < n_taps; t++) corr_out_iq[2 * t] = corr_out_iq[2 * t + 1] = 0.0;
+    for (unsigned k = 0; k < (unsigned)n; k++)
+        {
+            double ph = -((double)rem_carr_phase_rad + (double)k * (double)phase_step_rad);
+            double c = cos(ph), s = sin(ph);
+            double xr = in_iq[2 * k], xi = in_iq[2 * k + 1];
+            double wr = xr * c - xi * s, wi = xr * s + xi * c;
+            for (int t = 0; t < n_taps; t++)
+                {
+                    float v = code_phase_step_chips * (float)k + shifts[t] - rem_code_phase_chips;
+                    double cc = code[chip_index_(v, code_len)];
+                    corr_out_iq[2 * t] += wr * cc;
+                    corr_out_iq[2 * t + 1] += wi * cc;
+                }
+        }
+}
+
+/* ======================= acquisition helpers ======================= */
+
+/* volk: volk_gnsssdr_s32f_sincos_32fc.h:405-416 (_generic): phase accumulated in float32 */
+void go_sincos(float* out_iq, float phase_inc, float phase0, int n)
+{
+    float ph = phase0;
+    for (int i = 0; i < n; i++)
+        {
+            out_iq[2 * i] = cosf(ph);
+            out_iq[2 * i + 1] = sinf(ph);
+            ph += phase_inc;
+        }
+}
+
+/* volk: volk_gnsssdr_32f_index_max_32u.h:460-483 (_generic): strict '>', first maximum wins */
+uint32_t go_index_max(const float* src, uint32_t n)
+{
+    uint32_t index = 0;
+    if (n > 0)
+        {
+            float max = src[0];
+            for (uint32_t i = 1; i < n; ++i)
+                {
+                    if (src[i] > max)
+                        {
+                            index = i;
+                            max = src[i];
+                        }
+                }
+        }
+    return index;
+}
+
+/* volk: volk_gnsssdr_16ic_convert_32fc.h:63-72 */
+void go_16ic_convert_32fc(float* out_iq, const int16_t* in_iq, uint32_t n)
+{
+    for (uint32_t i = 0; i < 2 * n; i++) out_iq[i] = (float)in_iq[i];
+}
+
+/* ---- un-normalised DFT of any length: X[k] = sum_n x[n] exp(sign*j*2*pi*k*n/N).
+ * The reference calls FFTW3f through gr::fft::fft_complex (pcps_acquisition.cc:125-128); FFTW is an
+ * un-vendored system dependency, so this is the published DFT definition evaluated by a recursive
+ * decimation-in-time mixed-radix algorithm (radix = smallest prime factor, naive DFT inside each
+ * butterfly), twiddles from double-precision sin/cos.  Same mathematical transform and sign/scale
+ * convention as FFTW_FORWARD / FFTW_BACKWARD; results differ from FFTW by float rounding only. */
+#define GO_FFT_IMPL(NAME, T, CT)                                                                          \
+    static void NAME##_rec(const CT* in, CT* out, int n, int stride, const CT* tw, int tw_stride, CT* scratch) \
+    {                                                                                                     \
+        if (n == 1)                                                                                       \
+            {                                                                                             \
+                out[0] = in[0];                                                                           \
+                return;                                                                                   \
+            }                                                                                             \
+        int p = 2;                                                                                        \
+        while (n % p) p++;                                                                                \
+        int m = n / p;                                                                                    \
+        for (int r = 0; r < p; r++) NAME##_rec(in + (size_t)r * stride, out + (size_t)r * m, m, stride * p, tw, tw_stride * p, scratch); \
+        /* out[r*m + k] = DFT_m of the r-th decimated sequence; combine */                               \
+        for (int k = 0; k < m; k++)                                                                       \
+            {                                                                                             \
+                for (int r = 0; r < p; r++)                                                               \
+                    {                                                                                     \
+                        CT w = tw[(size_t)((long long)r * k % ((long long)n)) * tw_stride];               \
+                        CT v = out[(size_t)r * m + k];                                                    \
+                        scratch[r].re = v.re * w.re - v.im * w.im;                                        \
+                        scratch[r].im = v.re * w.im + v.im * w.re;                                        \
+                    }                                                                                     \
+                for (int q = 0; q < p; q++)                                                               \
+                    {                                                                                     \
+                        T sr = scratch[0].re, si = scratch[0].im;                                         \
+                        for (int r = 1; r < p; r++)                                                       \
+                            {                                                                             \
+                                CT w = tw[(size_t)(((long long)r * q % p) * m) * tw_stride];              \
+                                sr += scratch[r].re * w.re - scratch[r].im * w.im;                        \
+                                si += scratch[r].re * w.im + scratch[r].im * w.re;                        \
+                            }                                                                             \
+                        scratch[p + q].re = sr;                                                           \
+                        scratch[p + q].im = si;                                                           \
+                    }                                                                                     \
+                for (int q = 0; q < p; q++) out[(size_t)q * m + k] = scratch[p + q];                      \
+            }                                                                                             \
+    }                                                                                                     \
+    void NAME(T* data_iq, int n, int sign)                                                                \
+    {                                                                                                     \
+        CT* tw = (CT*)malloc(sizeof(CT) * (size_t)n);                                                     \
+        CT* tmp = (CT*)malloc(sizeof(CT) * (size_t)n);                                                    \
+        int maxp = 2;                                                                                     \
+        for (int r = n, p = 2; r > 1;)                                                                    \
+            {                                                                                             \
+                if (r % p == 0) { if (p > maxp) maxp = p; r /= p; }                                       \
+                else p++;                                                                                 \
+            }                                                                                             \
+        CT* scratch = (CT*)malloc(sizeof(CT) * 2 * (size_t)maxp);                                         \
+        for (int i = 0; i < n; i++)                                                                       \
+            {                                                                                             \
+                double a = (double)sign * 6.283185307179586476925286766559 * (double)i / (double)n;       \
+                tw[i].re = (T)cos(a);                                                                     \
+                tw[i].im = (T)sin(a);                                                                     \
+            }                                                                                             \
+        memcpy(tmp, data_iq, sizeof(CT) * (size_t)n);                                                     \
+        NAME##_rec(tmp, (CT*)data_iq, n, 1, tw, 1, scratch);                                              \
+        free(scratch);                                                                                    \
+        free(tmp);                                                                                        \
+        free(tw);                                                                                         \
+    }
+
+GO_FFT_IMPL(go_fft_f32, float, cf)
+GO_FFT_IMPL(go_fft_f64, double, cd)
+
+/* ======================= PRN codes ======================= */
+
+/* src/algorithms/libs/gps_sdr_signal_processing.cc:37-117: G1/G2 LFSRs of IS-GPS-200 with the
+ * reference's G2 delay table (PRN 1-32, then SBAS 120-138 at table index 32..50). */
+void go_gps_l1_ca_code_int(int32_t* dest, int32_t prn, uint32_t chip_shift)
+{
+    enum { L = 1023 };
+    static const int32_t delays[51] = {5, 6, 7, 8, 17, 18, 139, 140, 141, 251, 252, 254, 255, 256, 257, 258, 469, 470, 471, 472,
+        473, 474, 509, 512, 513, 514, 515, 516, 859, 860, 861, 862,
+        145, 175, 52, 21, 237, 235, 886, 657, 634, 762, 355, 1012, 176, 603, 130, 359, 595, 68, 386};
+    unsigned char g1[L], g2[L], r1[10], r2[10];
+    int32_t prn_idx = (120 <= prn && prn <= 138) ? prn - 88 : prn - 1;
+    if (prn_idx < 0 || prn_idx > 50) return;
+    for (int i = 0; i < 10; i++) r1[i] = r2[i] = 1;
+    for (int i = 0; i < L; i++)
+        {
+            g1[i] = r1[0];
+            g2[i] = r2[0];
+            unsigned char f1 = r1[7] ^ r1[0];
+            unsigned char f2 = (unsigned char)((r2[8] + r2[7] + r2[4] + r2[2] + r2[1] + r2[0]) & 1);
+            for (int j = 0; j < 9; j++)
+                {
+                    r1[j] = r1[j + 1];
+                    r2[j] = r2[j + 1];
+                }
+            r1[9] = f1;
+            r2[9] = f2;
+        }
+    uint32_t delay = (uint32_t)(L - delays[prn_idx]);
+    delay += chip_shift;
+    delay %= L;
+    for (uint32_t i = 0; i < L; i++)
+        {
+            dest[i] = (g1[(i + chip_shift) % L] ^ g2[delay]) ? 1 : -1;
+            delay = (delay + 1) % L;
+        }
+}
+
+void go_gps_l1_ca_code_float(float* dest, int32_t prn, uint32_t chip_shift)
+{
+    int32_t c[1023];
+    memset(c, 0, sizeof(c));
+    go_gps_l1_ca_code_int(c, prn, chip_shift);
+    for (int i = 0; i < 1023; i++) dest[i] = (float)c[i];
+}
+
+/* auxCeil lambda, gps_sdr_signal_processing.cc:35 */
+static inline int32_t aux_ceil_(float x) { return (int32_t)(int64_t)(x + 1); }
+
+/* gps_sdr_signal_processing.cc:151-196: float32 index maths, last sample forced to the last chip */
+void go_gps_l1_ca_code_sampled(float* dest_iq, uint32_t prn, int32_t fs, uint32_t chip_shift)
+{
+    float code[1023];
+    const int32_t code_freq_basis = 1023000, code_length = 1023;
+    int32_t samples_per_code = (int32_t)((double)fs / (double)(code_freq_basis / code_length));
+    float ts = (float)(1.0 / (double)(float)fs);
+    float tc = (float)(1.0 / (double)(float)code_freq_basis);
+    go_gps_l1_ca_code_float(code, (int32_t)prn, chip_shift);
+    for (int32_t i = 0; i < samples_per_code; i++)
+        {
+            float aux = (ts * (float)(i + 1)) / tc;
+            int32_t idx = aux_ceil_(aux) - 1;
+            dest_iq[2 * i] = (i == samples_per_code - 1) ? code[code_length - 1] : code[idx];
+            dest_iq[2 * i + 1] = 0.0f;
+        }
+}
+
+/* src/algorithms/libs/gnss_signal_processing.cc:161-183 */
+void go_code_resampler_f32(const float* from, float* dest, float fs_in, float fs_out, uint32_t len_in, uint32_t len_out)
+{
+    const float t_in = 1 / fs_in;
+    const float t_out = 1 / fs_out;
+    for (uint32_t i = 0; i < len_out - 1; i++)
+        {
+            float aux = (t_out * (float)(i + 1)) / t_in;
+            uint32_t idx = (uint32_t)(aux_ceil_(aux) - 1);
+            dest[i] = from[idx];
+        }
+    dest[len_out - 1] = from[len_in - 1];
+}
+
+/* ======================= pcps_acquisition block ======================= */
+/* State and arithmetic of src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.cc.
+ * The GNU Radio plumbing (general_work states 0/1, :976-1034) is replaced by the caller handing
+ * d_consumed_samples items; everything from acquisition_core (:668) on is restated line by line,
+ * including the quirks listed in SURVEY.md 7.3 (stale d_tmp_buffer, one-sided exclusion wrap,
+ * N^4 normalisation, input power over the zero padding, step-two Doppler truncation). */
+struct go_acq
+{
+    go_acq_conf c;
+    uint32_t consumed, fft_size, num_bins;
+    int use_cfar;
+    float* tmp_buffer;   /* d_tmp_buffer, persists between calls (quirk 1) */
+    float* fft_codes;    /* d_fft_codes, IQ */
+    float** wipeoffs;    /* d_grid_doppler_wipeoffs[bin], IQ */
+    float** wipeoffs2;   /* step two */
+    float** grid;        /* d_magnitude_grid[bin][fft_size] */
+    float** grid_snap;   /* tests only */
+    float* work;         /* fft in/out, IQ */
+    double* work64;
+    float* input_signal; /* d_input_signal IQ */
+    uint32_t dwell_counter; /* d_num_noncoherent_integrations_counter */
+    int step_two, positive_acq;
+    float doppler_center_step_two;
+};
+
+static const double GO_GPS_TWO_PI = 6.283185307179586; /* GPS_L1_CA.h:46 */
+
+/* pcps_acquisition.cc:296-310 (+ analytic arbiter) */
+static void go_acq_local_carrier_(const go_acq* a, float* carrier_iq, uint32_t n, float freq)
+{
+    float phase_step_rad = (float)(GO_GPS_TWO_PI * freq / (float)a->c.fs_in);
+    if (a->c.analytic_wipeoff)
+        {
+            for (uint32_t i = 0; i < n; i++)
+                {
+                    double ph = -(double)phase_step_rad * (double)i;
+                    carrier_iq[2 * i] = (float)cos(ph);
+                    carrier_iq[2 * i + 1] = (float)sin(ph);
+                }
+        }
+    else
+        go_sincos(carrier_iq, -phase_step_rad, 0.0f, (int)n);
+}
+
+static void go_acq_update_grid_(go_acq* a)
+{
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            int32_t doppler = -(int32_t)a->c.doppler_max + (int32_t)(a->c.doppler_step * i);
+            go_acq_local_carrier_(a, a->wipeoffs[i], a->fft_size, (float)(a->c.freq_offset_hz + doppler));
+        }
+}
+
+go_acq* go_acq_create(const go_acq_conf* conf)
+{
+    go_acq* a = (go_acq*)calloc(1, sizeof(go_acq));
+    a->c = *conf;
+    /* ctor :75-117 */
+    a->consumed = (uint32_t)((float)conf->sampled_ms * conf->samples_per_ms * (float)(conf->bit_transition_flag ? 2 : 1));
+    a->fft_size = (conf->sampled_ms == conf->ms_per_code) ? a->consumed : a->consumed * 2;
+    if (conf->bit_transition_flag)
+        {
+            a->fft_size = a->consumed * 2;
+            a->c.max_dwells = 1;
+        }
+    a->use_cfar = (a->c.max_dwells == 1) ? conf->use_CFAR_algorithm_flag : 0; /* :152-159 */
+    /* init() :326 */
+    a->num_bins = (uint32_t)ceil((double)((int32_t)conf->doppler_max - (int32_t)(-(int32_t)conf->doppler_max)) / (double)conf->doppler_step);
+    size_t n = a->fft_size;
+    a->tmp_buffer = (float*)calloc(n, sizeof(float));
+    a->fft_codes = (float*)calloc(2 * n, sizeof(float));
+    a->work = (float*)calloc(2 * n, sizeof(float));
+    a->work64 = (double*)calloc(2 * n, sizeof(double));
+    a->input_signal = (float*)calloc(2 * n, sizeof(float));
+    a->wipeoffs = (float**)calloc(a->num_bins, sizeof(float*));
+    a->grid = (float**)calloc(a->num_bins, sizeof(float*));
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            a->wipeoffs[i] = (float*)calloc(2 * n, sizeof(float));
+            a->grid[i] = (float*)calloc(n, sizeof(float));
+        }
+    if (conf->keep_grid)
+        {
+            a->grid_snap = (float**)calloc(a->num_bins, sizeof(float*));
+            for (uint32_t i = 0; i < a->num_bins; i++) a->grid_snap[i] = (float*)calloc(n, sizeof(float));
+        }
+    if (conf->make_2_steps)
+        {
+            a->wipeoffs2 = (float**)calloc(conf->num_doppler_bins_step2, sizeof(float*));
+            for (uint32_t i = 0; i < conf->num_doppler_bins_step2; i++) a->wipeoffs2[i] = (float*)calloc(2 * n, sizeof(float));
+        }
+    go_acq_update_grid_(a);
+    return a;
+}
+
+void go_acq_destroy(go_acq* a)
+{
+    if (!a) return;
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            free(a->wipeoffs[i]);
+            free(a->grid[i]);
+            if (a->grid_snap) free(a->grid_snap[i]);
+        }
+    free(a->grid_snap);
+    if (a->wipeoffs2)
+        {
+            for (uint32_t i = 0; i < a->c.num_doppler_bins_step2; i++) free(a->wipeoffs2[i]);
+            free(a->wipeoffs2);
+        }
+    free(a->wipeoffs);
+    free(a->grid);
+    free(a->tmp_buffer);
+    free(a->fft_codes);
+    free(a->work);
+    free(a->work64);
+    free(a->input_signal);
+    free(a);
+}
+
+uint32_t go_acq_fft_size(const go_acq* a) { return a->fft_size; }
+uint32_t go_acq_consumed_samples(const go_acq* a) { return a->consumed; }
+uint32_t go_acq_num_doppler_bins(const go_acq* a) { return a->num_bins; }
+const float* go_acq_grid(const go_acq* a, int bin) { return a->grid_snap ? a->grid_snap[bin] : a->grid[bin]; }
+
+static void go_acq_fft_(go_acq* a, float* buf_iq, int sign)
+{
+    uint32_t n = a->fft_size;
+    if (a->c.fft_f64)
+        {
+            for (uint32_t i = 0; i < 2 * n; i++) a->work64[i] = buf_iq[i];
+            go_fft_f64(a->work64, (int)n, sign);
+            for (uint32_t i = 0; i < 2 * n; i++) buf_iq[i] = (float)a->work64[i];
+        }
+    else
+        go_fft_f32(buf_iq, (int)n, sign);
+}
+
+/* pcps_acquisition.cc:239-274.  `code_iq` holds what the adapter passes: d_consumed_samples items
+ * (fft_size/2 with bit_transition_flag, :253-258). */
+void go_acq_set_local_code(go_acq* a, const float* code_iq)
+{
+    uint32_t n = a->fft_size;
+    memset(a->work, 0, sizeof(float) * 2 * n);
+    if (a->c.bit_transition_flag)
+        {
+            uint32_t offset = n / 2;
+            memcpy(a->work + 2 * offset, code_iq, sizeof(float) * 2 * offset);
+        }
+    else if (a->c.sampled_ms == a->c.ms_per_code)
+        memcpy(a->work, code_iq, sizeof(float) * 2 * a->consumed);
+    else
+        memcpy(a->work + 2 * (size_t)a->consumed, code_iq, sizeof(float) * 2 * a->consumed);
+    go_acq_fft_(a, a->work, -1);
+    for (uint32_t i = 0; i < n; i++) /* volk_32fc_conjugate_32fc */
+        {
+            a->fft_codes[2 * i] = a->work[2 * i];
+            a->fft_codes[2 * i + 1] = -a->work[2 * i + 1];
+        }
+}
+
+/* pcps_acquisition.cc:565-596 */
+static float go_acq_stat_cfar_(go_acq* a, uint32_t* indext, int32_t* doppler, uint32_t* bin_out, float* peak, float input_power,
+    uint32_t num_bins, int32_t doppler_max, int32_t doppler_step)
+{
+    float grid_maximum = 0.0f;
+    uint32_t index_doppler = 0, index_time = 0;
+    float nf = (float)a->fft_size * (float)a->fft_size;
+    for (uint32_t i = 0; i < num_bins; i++)
+        {
+            uint32_t t = go_index_max(a->grid[i], a->fft_size);
+            if (a->grid[i][t] > grid_maximum)
+                {
+                    grid_maximum = a->grid[i][t];
+                    index_doppler = i;
+                    index_time = t;
+                }
+        }
+    *indext = index_time;
+    *bin_out = index_doppler;
+    *peak = grid_maximum;
+    if (!a->step_two)
+        *doppler = -doppler_max + doppler_step * (int32_t)index_doppler;
+    else
+        *doppler = (int32_t)(a->doppler_center_step_two + ((float)index_doppler - (float)floor(a->c.num_doppler_bins_step2 / 2.0)) * a->c.doppler_step2);
+    float magt = grid_maximum / (nf * nf);
+    return magt / input_power;
+}
+
+/* pcps_acquisition.cc:599-665 */
+static float go_acq_stat_peaks_(go_acq* a, uint32_t* indext, int32_t* doppler, uint32_t* bin_out, float* peak,
+    uint32_t num_bins, int32_t doppler_max, int32_t doppler_step)
+{
+    float first_peak = 0.0f;
+    uint32_t index_doppler = 0, index_time = 0;
+    for (uint32_t i = 0; i < num_bins; i++)
+        {
+            uint32_t t = go_index_max(a->grid[i], a->fft_size);
+            if (a->grid[i][t] > first_peak)
+                {
+                    first_peak = a->grid[i][t];
+                    index_doppler = i;
+                    index_time = t;
+                }
+        }
+    *indext = index_time;
+    *bin_out = index_doppler;
+    *peak = first_peak;
+    if (!a->step_two)
+        *doppler = -doppler_max + doppler_step * (int32_t)index_doppler;
+    else
+        *doppler = (int32_t)(a->doppler_center_step_two + ((float)index_doppler - (float)floor(a->c.num_doppler_bins_step2 / 2.0)) * a->c.doppler_step2);
+
+    int32_t ex1 = (int32_t)index_time - (int32_t)a->c.samples_per_chip;
+    int32_t ex2 = (int32_t)index_time + (int32_t)a->c.samples_per_chip;
+    if (ex1 < 0)
+        ex1 = (int32_t)a->fft_size + ex1;
+    else if (ex2 >= (int32_t)a->fft_size)
+        ex2 = ex2 - (int32_t)a->fft_size;
+    int32_t idx = ex1;
+    memcpy(a->tmp_buffer, a->grid[index_doppler], a->fft_size); /* d_fft_size BYTES, :647 (quirk 1) */
+    do
+        {
+            a->tmp_buffer[idx] = 0.0f;
+            idx++;
+            if (idx == (int32_t)a->fft_size) idx = 0;
+        }
+    while (idx != ex2);
+    uint32_t t2 = go_index_max(a->tmp_buffer, a->fft_size);
+    float second_peak = a->tmp_buffer[t2];
+    return first_peak / second_peak;
+}
+
+/* pcps_acquisition.cc:668-930 */
+int go_acq_run(go_acq* a, const void* samples, uint64_t samp_count, go_acq_result* out)
+{
+    const uint32_t n = a->fft_size;
+    const uint32_t eff = a->c.bit_transition_flag ? n / 2 : n;
+    int32_t doppler = 0;
+    uint32_t indext = 0, bin = 0;
+    float peak = 0.0f;
+    memset(out, 0, sizeof(*out));
+    if (a->c.cshort)
+        go_16ic_convert_32fc(a->input_signal, (const int16_t*)samples, a->consumed);
+    else
+        memcpy(a->input_signal, samples, sizeof(float) * 2 * a->consumed);
+    for (uint32_t i = 2 * a->consumed; i < 2 * n; i++) a->input_signal[i] = 0.0f;
+    const float* in = a->input_signal;
+
+    float input_power = 0.0f;
+    a->dwell_counter++;
+    if (a->use_cfar || a->c.bit_transition_flag) /* :703-709 */
+        {
+            for (uint32_t i = 0; i < n; i++) a->tmp_buffer[i] = in[2 * i] * in[2 * i] + in[2 * i + 1] * in[2 * i + 1];
+            for (uint32_t i = 0; i < n; i++) input_power += a->tmp_buffer[i];
+            input_power /= (float)n;
+        }
+
+    uint32_t nb = a->step_two ? a->c.num_doppler_bins_step2 : a->num_bins;
+    float** wip = a->step_two ? a->wipeoffs2 : a->wipeoffs;
+    for (uint32_t d = 0; d < nb; d++) /* :714-745 / :773-803 */
+        {
+            const float* w = wip[d];
+            for (uint32_t i = 0; i < n; i++)
+                {
+                    a->work[2 * i] = in[2 * i] * w[2 * i] - in[2 * i + 1] * w[2 * i + 1];
+                    a->work[2 * i + 1] = in[2 * i] * w[2 * i + 1] + in[2 * i + 1] * w[2 * i];
+                }
+            go_acq_fft_(a, a->work, -1);
+            for (uint32_t i = 0; i < n; i++)
+                {
+                    float xr = a->work[2 * i], xi = a->work[2 * i + 1];
+                    float cr = a->fft_codes[2 * i], ci = a->fft_codes[2 * i + 1];
+                    a->work[2 * i] = xr * cr - xi * ci;
+                    a->work[2 * i + 1] = xr * ci + xi * cr;
+                }
+            go_acq_fft_(a, a->work, +1);
+            const float* y = a->work + 2 * (size_t)(a->c.bit_transition_flag ? eff : 0);
+            if (a->dwell_counter == 1)
+                for (uint32_t i = 0; i < eff; i++) a->grid[d][i] = y[2 * i] * y[2 * i] + y[2 * i + 1] * y[2 * i + 1];
+            else
+                {
+                    for (uint32_t i = 0; i < eff; i++) a->tmp_buffer[i] = y[2 * i] * y[2 * i] + y[2 * i + 1] * y[2 * i + 1];
+                    for (uint32_t i = 0; i < eff; i++) a->grid[d][i] = a->grid[d][i] + a->tmp_buffer[i];
+                }
+        }
+
+    float stat;
+    if (!a->step_two)
+        {
+            if (a->use_cfar)
+                stat = go_acq_stat_cfar_(a, &indext, &doppler, &bin, &peak, input_power, a->num_bins, (int32_t)a->c.doppler_max, (int32_t)a->c.doppler_step);
+            else
+                stat = go_acq_stat_peaks_(a, &indext, &doppler, &bin, &peak, a->num_bins, (int32_t)a->c.doppler_max, (int32_t)a->c.doppler_step);
+        }
+    else
+        {
+            int32_t dmax2 = (int32_t)(a->doppler_center_step_two - ((float)a->c.num_doppler_bins_step2 / 2.0) * a->c.doppler_step2);
+            if (a->use_cfar)
+                stat = go_acq_stat_cfar_(a, &indext, &doppler, &bin, &peak, input_power, a->c.num_doppler_bins_step2, dmax2, (int32_t)a->c.doppler_step2);
+            else
+                stat = go_acq_stat_peaks_(a, &indext, &doppler, &bin, &peak, a->c.num_doppler_bins_step2, dmax2, (int32_t)a->c.doppler_step2);
+        }
+    out->code_phase_index = indext;
+    out->doppler_hz = doppler;
+    out->doppler_bin = bin;
+    out->peak_mag = peak;
+    out->input_power = input_power;
+    out->test_statistic = stat;
+    out->acq_delay_samples = (double)fmodf((float)indext, a->c.samples_per_code); /* :766 */
+    out->acq_doppler_hz = (double)doppler;
+    out->acq_samplestamp = samp_count;
+
+    /* decision logic :832-909 */
+    int state = 1; /* d_state while in acquisition_core is 2; we track only what it becomes */
+    int decision;
+    int positive_sent = 0, negative_sent = 0;
+    if (!a->c.bit_transition_flag)
+        {
+            if (stat > a->c.threshold)
+                {
+                    if (a->c.make_2_steps)
+                        {
+                            if (a->step_two)
+                                {
+                                    positive_sent = 1;
+                                    a->step_two = 0;
+                                    state = 0;
+                                }
+                            else
+                                {
+                                    a->step_two = 1;
+                                    a->dwell_counter = 0;
+                                    a->positive_acq = 0;
+                                    state = 0;
+                                }
+                        }
+                    else
+                        {
+                            positive_sent = 1;
+                            state = 0;
+                        }
+                }
+            else
+                state = 1;
+            if (a->dwell_counter == a->c.max_dwells)
+                {
+                    if (state != 0) negative_sent = 1;
+                    state = 0;
+                    a->step_two = 0;
+                }
+        }
+    else
+        {
+            if (stat > a->c.threshold)
+                {
+                    if (a->c.make_2_steps)
+                        {
+                            if (a->step_two)
+                                {
+                                    positive_sent = 1;
+                                    a->step_two = 0;
+                                }
+                            else
+                                {
+                                    a->step_two = 1;
+                                    a->dwell_counter = 0;
+                                }
+                        }
+                    else
+                        positive_sent = 1;
+                }
+            else
+                {
+                    a->step_two = 0;
+                    negative_sent = 1;
+                }
+            state = 0;
+        }
+    if (positive_sent) a->positive_acq = 1;
+    if (negative_sent) a->positive_acq = 0;
+    if (positive_sent)
+        decision = 1;
+    else if (negative_sent)
+        decision = 0;
+    else if (a->step_two)
+        decision = 3;
+    else
+        decision = 2;
+    out->decision = decision;
+    if (a->step_two) /* general_work :964-970 re-centres the fine grid before the next dwell */
+        {
+            a->doppler_center_step_two = (float)out->acq_doppler_hz;
+            for (uint32_t i = 0; i < a->c.num_doppler_bins_step2; i++)
+                {
+                    float dd = ((float)i - (float)floor(a->c.num_doppler_bins_step2 / 2.0)) * a->c.doppler_step2;
+                    go_acq_local_carrier_(a, a->wipeoffs2[i], n, a->doppler_center_step_two + dd);
+                }
+        }
+    if (a->grid_snap)
+        for (uint32_t i = 0; i < a->num_bins; i++) memcpy(a->grid_snap[i], a->grid[i], sizeof(float) * n);
+    /* :912-929 */
+    if (a->dwell_counter == a->c.max_dwells || a->positive_acq == 1)
+        {
+            a->dwell_counter = 0;
+            a->positive_acq = 0;
+            for (uint32_t i = 0; i < a->num_bins; i++) memset(a->grid[i], 0, sizeof(float) * n);
+        }
+    (void)state;
+    return 0;
+}

@@ -1,0 +1,121 @@
+/* TEST INFRASTRUCTURE ONLY -- CPU oracle for the B200 correlator engine.
+ *
+ * Plain-C restatement of the reference's (zhufengGNSS/gnss-sdr-1) PCPS acquisition and
+ * multicorrelator arithmetic.  Only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs may load this; the product library
+ * (libgnss_b200.so) never links or calls it.
+ *
+ * Parity status: PINNED.  Tracking functions are checked bit-for-bit against the
+ * reference's own _generic protokernels compiled from /root/reference (oracle/_ref,
+ * tests/test_oracle_vs_ref.py, tests/golden/trk_*.npz); acquisition is checked against
+ * the reference's two in-tree acquisition fixtures and their expected answers
+ * (gps_l1_ca_pcps_acquisition_test.cc:285-286, galileo_e1_pcps_ambiguous_acquisition_test.cc:293-294).
+ * The FFT behind acquisition is FFTW3f in the reference (un-vendored system dependency,
+ * version not pinned in-tree); here it is a mixed-radix DFT written from the published
+ * definition, so acquisition magnitudes agree with the reference to float32 rounding only.
+ */
+#ifndef GNSS_ORACLE_H
+#define GNSS_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------- tracking: volk_gnsssdr _generic restatements ---------------- */
+void go_resampler_real(float* out /*T x n*/, const float* code, float rem_chips, float step_chips,
+    const float* shifts, int code_len, int n_taps, int n);
+void go_resampler_real_hd(float* out /*T x n*/, const float* code, float rem_chips, float step_chips,
+    float rate_chips, const float* shifts, int code_len, int n_taps, int n);
+void go_resampler_cplx(float* out_iq /*T x n x 2*/, const float* code_iq, float rem_chips, float step_chips,
+    const float* shifts, int code_len, int n_taps, int n);
+void go_rotator_dot_prod_real(float* result_iq, const float* in_iq, float inc_re, float inc_im,
+    float* phase_iq, const float* codes /*T x n*/, int n_taps, int n);
+void go_rotator_dot_prod_real_hd(float* result_iq, const float* in_iq, float inc_re, float inc_im,
+    float rate_re, float rate_im, float* phase_iq, const float* codes, int n_taps, int n);
+void go_rotator_dot_prod_cplx(float* result_iq, const float* in_iq, float inc_re, float inc_im,
+    float* phase_iq, const float* codes_iq /*T x n x 2*/, int n_taps, int n);
+/* Cpu_Multicorrelator_Real_Codes::Carrier_wipeoff_multicorrelator_resampler */
+void go_multicorrelator_real(const float* in_iq, int n, const float* code, int code_len, const float* shifts,
+    int n_taps, float rem_carr_phase_rad, float phase_step_rad, float phase_rate_step_rad,
+    float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips,
+    int high_dyn, float* corr_out_iq);
+/* Cpu_Multicorrelator::Carrier_wipeoff_multicorrelator_resampler (complex codes) */
+void go_multicorrelator_cplx(const float* in_iq, int n, const float* code_iq, int code_len, const float* shifts,
+    int n_taps, float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips,
+    float code_phase_step_chips, float* corr_out_iq);
+/* float64 arbiter on the oracle's own chip indices */
+void go_multicorrelator_real_f64(const float* in_iq, int n, const float* code, int code_len, const float* shifts,
+    int n_taps, float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips,
+    float code_phase_step_chips, double* corr_out_iq);
+
+/* ---------------- acquisition helpers ---------------- */
+void go_sincos(float* out_iq, float phase_inc, float phase0, int n);
+uint32_t go_index_max(const float* src, uint32_t n);
+void go_16ic_convert_32fc(float* out_iq, const int16_t* in_iq, uint32_t n);
+/* un-normalised DFT, sign=-1 forward / +1 backward, any n (radix 2,3,4,5 + generic prime) */
+void go_fft_f32(float* data_iq, int n, int sign);
+void go_fft_f64(double* data_iq, int n, int sign);
+
+/* ---------------- PRN codes ---------------- */
+void go_gps_l1_ca_code_int(int32_t* dest, int32_t prn, uint32_t chip_shift);
+void go_gps_l1_ca_code_float(float* dest, int32_t prn, uint32_t chip_shift);
+void go_gps_l1_ca_code_sampled(float* dest_iq, uint32_t prn, int32_t fs, uint32_t chip_shift);
+/* gnss_signal_processing.cc resampler(): nearest-neighbour code resampling used by E1/E5a/L5 set_local_code */
+void go_code_resampler_f32(const float* from, float* dest, float fs_in, float fs_out, uint32_t len_in, uint32_t len_out);
+
+/* ---------------- pcps_acquisition block ---------------- */
+typedef struct go_acq_conf
+{
+    /* Acq_Conf (acq_conf.h:39-68) fields used by the arithmetic */
+    uint32_t sampled_ms;
+    uint32_t ms_per_code;
+    uint32_t samples_per_chip;
+    uint32_t max_dwells;
+    uint32_t doppler_max;
+    uint32_t doppler_step;
+    uint32_t num_doppler_bins_step2;
+    float doppler_step2;
+    int64_t fs_in;
+    float samples_per_ms;
+    float samples_per_code;
+    int bit_transition_flag;
+    int use_CFAR_algorithm_flag;
+    int make_2_steps;
+    int cshort; /* it_size == sizeof(lv_16sc_t) */
+    float threshold;
+    int64_t freq_offset_hz; /* d_old_freq (GLONASS FDMA), pcps_acquisition.cc:277-293 */
+    int fft_f64;            /* arbiter: run the DFTs in float64 */
+    int analytic_wipeoff;   /* arbiter: exact phase instead of float32-accumulated table */
+    int keep_grid;          /* tests: snapshot the magnitude grid before the end-of-attempt reset (:919-928) */
+} go_acq_conf;
+
+typedef struct go_acq_result
+{
+    uint32_t code_phase_index; /* indext */
+    int32_t doppler_hz;
+    uint32_t doppler_bin;
+    float peak_mag;
+    float input_power;
+    float test_statistic;
+    int decision; /* 1 positive, 0 negative, 2 need more dwells, 3 step two armed */
+    double acq_delay_samples;
+    double acq_doppler_hz;
+    uint64_t acq_samplestamp;
+} go_acq_result;
+
+typedef struct go_acq go_acq;
+go_acq* go_acq_create(const go_acq_conf* conf);
+void go_acq_destroy(go_acq* a);
+uint32_t go_acq_fft_size(const go_acq* a);
+uint32_t go_acq_consumed_samples(const go_acq* a);
+uint32_t go_acq_num_doppler_bins(const go_acq* a);
+void go_acq_set_local_code(go_acq* a, const float* code_iq);
+/* samples: d_consumed_samples items (float IQ pairs, or int16 IQ pairs when conf.cshort) */
+int go_acq_run(go_acq* a, const void* samples, uint64_t samp_count, go_acq_result* out);
+/* kept magnitude grid, bins x effective_fft_size */
+const float* go_acq_grid(const go_acq* a, int bin);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

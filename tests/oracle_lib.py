@@ -1,0 +1,222 @@
+"""ctypes doors into the CPU oracle (TEST INFRASTRUCTURE ONLY).
+
+`oracle()`  -> oracle/libgnss_oracle.so  : plain-C restatement (oracle/gnss_oracle.c)
+`ref()`     -> oracle/_ref/libgnss_ref.so: the reference's own sources compiled from /root/reference
+               (prebuilt file on the GPU box; None when it was never built)
+
+Nothing in the product package imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+i16p = np.ctypeslib.ndpointer(np.int16, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+
+
+class GoAcqConf(C.Structure):
+    _fields_ = [
+        ("sampled_ms", C.c_uint32), ("ms_per_code", C.c_uint32), ("samples_per_chip", C.c_uint32),
+        ("max_dwells", C.c_uint32), ("doppler_max", C.c_uint32), ("doppler_step", C.c_uint32),
+        ("num_doppler_bins_step2", C.c_uint32), ("doppler_step2", C.c_float), ("fs_in", C.c_int64),
+        ("samples_per_ms", C.c_float), ("samples_per_code", C.c_float), ("bit_transition_flag", C.c_int),
+        ("use_CFAR_algorithm_flag", C.c_int), ("make_2_steps", C.c_int), ("cshort", C.c_int),
+        ("threshold", C.c_float), ("freq_offset_hz", C.c_int64), ("fft_f64", C.c_int),
+        ("analytic_wipeoff", C.c_int), ("keep_grid", C.c_int),
+    ]
+
+
+class GoAcqResult(C.Structure):
+    _fields_ = [
+        ("code_phase_index", C.c_uint32), ("doppler_hz", C.c_int32), ("doppler_bin", C.c_uint32),
+        ("peak_mag", C.c_float), ("input_power", C.c_float), ("test_statistic", C.c_float),
+        ("decision", C.c_int), ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double),
+        ("acq_samplestamp", C.c_uint64),
+    ]
+
+
+_oracle = None
+_ref = None
+
+
+def build_oracle():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "all"])
+
+
+def oracle():
+    global _oracle
+    if _oracle is not None:
+        return _oracle
+    path = os.path.join(ORACLE_DIR, "libgnss_oracle.so")
+    if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(os.path.join(ORACLE_DIR, "gnss_oracle.c")):
+        build_oracle()
+    L = C.CDLL(path)
+    L.go_resampler_real.argtypes = [f32p, f32p, C.c_float, C.c_float, f32p, C.c_int, C.c_int, C.c_int]
+    L.go_resampler_real_hd.argtypes = [f32p, f32p, C.c_float, C.c_float, C.c_float, f32p, C.c_int, C.c_int, C.c_int]
+    L.go_rotator_dot_prod_real.argtypes = [f32p, f32p, C.c_float, C.c_float, f32p, f32p, C.c_int, C.c_int]
+    L.go_multicorrelator_real.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int] + [C.c_float] * 6 + [C.c_int, f32p]
+    L.go_multicorrelator_cplx.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int] + [C.c_float] * 4 + [f32p]
+    L.go_multicorrelator_real_f64.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int] + [C.c_float] * 4 + [f64p]
+    L.go_sincos.argtypes = [f32p, C.c_float, C.c_float, C.c_int]
+    L.go_index_max.argtypes = [f32p, C.c_uint32]
+    L.go_index_max.restype = C.c_uint32
+    L.go_16ic_convert_32fc.argtypes = [f32p, i16p, C.c_uint32]
+    L.go_fft_f32.argtypes = [f32p, C.c_int, C.c_int]
+    L.go_fft_f64.argtypes = [f64p, C.c_int, C.c_int]
+    L.go_gps_l1_ca_code_int.argtypes = [i32p, C.c_int32, C.c_uint32]
+    L.go_gps_l1_ca_code_float.argtypes = [f32p, C.c_int32, C.c_uint32]
+    L.go_gps_l1_ca_code_sampled.argtypes = [f32p, C.c_uint32, C.c_int32, C.c_uint32]
+    L.go_code_resampler_f32.argtypes = [f32p, f32p, C.c_float, C.c_float, C.c_uint32, C.c_uint32]
+    L.go_acq_create.argtypes = [C.POINTER(GoAcqConf)]
+    L.go_acq_create.restype = C.c_void_p
+    L.go_acq_destroy.argtypes = [C.c_void_p]
+    for fn in (L.go_acq_fft_size, L.go_acq_consumed_samples, L.go_acq_num_doppler_bins):
+        fn.argtypes = [C.c_void_p]
+        fn.restype = C.c_uint32
+    L.go_acq_set_local_code.argtypes = [C.c_void_p, f32p]
+    L.go_acq_run.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(GoAcqResult)]
+    L.go_acq_grid.argtypes = [C.c_void_p, C.c_int]
+    L.go_acq_grid.restype = C.POINTER(C.c_float)
+    _oracle = L
+    return L
+
+
+def ref():
+    """The reference compiled from its own sources, or None if oracle/_ref was never built."""
+    global _ref
+    if _ref is not None:
+        return _ref
+    path = os.path.join(ORACLE_DIR, "_ref", "libgnss_ref.so")
+    if not os.path.exists(path):
+        if os.path.isdir("/root/reference/src"):
+            subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "ref"])
+        else:
+            return None
+    L = C.CDLL(path)
+    L.gbref_set_arch.argtypes = [C.c_int]
+    L.gbref_multicorrelator_real.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int] + [C.c_float] * 6 + [C.c_int, f32p]
+    L.gbref_multicorrelator_cplx.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int] + [C.c_float] * 4 + [f32p]
+    L.gbref_multicorrelator_16sc.argtypes = [i16p, C.c_int, i16p, C.c_int, f32p, C.c_int] + [C.c_float] * 4 + [i16p]
+    L.gbref_resampler_real.argtypes = [f32p, f32p, C.c_float, C.c_float, f32p, C.c_int, C.c_int, C.c_int, C.c_int]
+    L.gbref_rotator_dot_prod_real.argtypes = [f32p, f32p, C.c_float, C.c_float, f32p, f32p, C.c_int, C.c_int, C.c_int]
+    L.gbref_sincos.argtypes = [f32p, C.c_float, C.c_float, C.c_int, C.c_int]
+    L.gbref_index_max.argtypes = [f32p, C.c_uint]
+    L.gbref_index_max.restype = C.c_uint
+    L.gbref_16ic_convert_32fc.argtypes = [f32p, i16p, C.c_uint]
+    L.gbref_gps_l1_ca_code_float.argtypes = [f32p, C.c_int, C.c_uint]
+    L.gbref_gps_l1_ca_code_sampled.argtypes = [f32p, C.c_uint, C.c_int, C.c_uint]
+    L.gbref_galileo_e1_code_sinboc11_float.argtypes = [f32p, C.c_char_p, C.c_uint]
+    L.gbref_galileo_e1_code_sampled.argtypes = [f32p, C.c_char_p, C.c_int, C.c_uint, C.c_int, C.c_uint, C.c_int]
+    L.gbref_gps_l5i_code_float.argtypes = [f32p, C.c_uint]
+    L.gbref_gps_l5q_code_float.argtypes = [f32p, C.c_uint]
+    L.gbref_gps_l5i_code_sampled.argtypes = [f32p, C.c_uint, C.c_int]
+    L.gbref_gps_l2c_m_code_float.argtypes = [f32p, C.c_uint]
+    L.gbref_galileo_e5a_code_primary.argtypes = [f32p, C.c_int, C.c_char_p]
+    L.gbref_galileo_e5a_code_sampled.argtypes = [f32p, C.c_char_p, C.c_uint, C.c_int, C.c_uint]
+    L.gbref_beidou_b1i_code_float.argtypes = [f32p, C.c_int, C.c_uint]
+    L.gbref_beidou_b1i_code_sampled.argtypes = [f32p, C.c_uint, C.c_int, C.c_uint]
+    L.gbref_glonass_l1_ca_code.argtypes = [f32p, C.c_uint]
+    L.gbref_glonass_l1_ca_code_sampled.argtypes = [f32p, C.c_int, C.c_uint]
+    L.gbref_fll_four_quadrant_atan.argtypes = [C.c_float] * 4 + [C.c_double] * 2
+    L.gbref_fll_four_quadrant_atan.restype = C.c_double
+    for fn in (L.gbref_pll_four_quadrant_atan, L.gbref_pll_cloop_two_quadrant_atan):
+        fn.argtypes = [C.c_float] * 2
+        fn.restype = C.c_double
+    L.gbref_dll_nc_e_minus_l_normalized.argtypes = [C.c_float] * 4
+    L.gbref_dll_nc_e_minus_l_normalized.restype = C.c_double
+    L.gbref_dll_nc_vemlp_normalized.argtypes = [f32p] * 4
+    L.gbref_dll_nc_vemlp_normalized.restype = C.c_double
+    L.gbref_cn0_svn_estimator.argtypes = [f32p, C.c_int, C.c_double]
+    L.gbref_cn0_svn_estimator.restype = C.c_float
+    L.gbref_carrier_lock_detector.argtypes = [f32p, C.c_int]
+    L.gbref_carrier_lock_detector.restype = C.c_float
+    L.gbref_tracking_loop_filter_run.argtypes = [C.c_float, C.c_float, C.c_int, C.c_int, C.c_float, f32p, f32p, C.c_int]
+    L.gbref_fll_pll_filter_run.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, f32p, f32p, C.c_float, f32p, C.c_int]
+    L.gbref_bench_multicorrelator_real.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int, C.c_int, C.c_int, C.c_int]
+    L.gbref_bench_multicorrelator_real.restype = C.c_double
+    _ref = L
+    return L
+
+
+# ---------------------------------------------------------------- convenience wrappers
+def multicorrelator_real(lib_kind, x, code, shifts, rem_carr, phase_step, rem_code, code_step,
+                         phase_rate=0.0, code_rate=0.0, high_dyn=False):
+    """x: complex64 array; returns complex64[T].  lib_kind: 'oracle' | 'ref_generic' | 'ref_avx'."""
+    x = np.ascontiguousarray(x, np.complex64).view(np.float32)
+    code = np.ascontiguousarray(code, np.float32)
+    shifts = np.ascontiguousarray(shifts, np.float32)
+    out = np.zeros(2 * len(shifts), np.float32)
+    args = (x, len(x) // 2, code, len(code), shifts, len(shifts), rem_carr, phase_step, phase_rate,
+            rem_code, code_step, code_rate, int(high_dyn), out)
+    if lib_kind == "oracle":
+        oracle().go_multicorrelator_real(*args)
+    else:
+        r = ref()
+        r.gbref_set_arch(1 if lib_kind == "ref_avx" else 0)
+        r.gbref_multicorrelator_real(*args)
+        r.gbref_set_arch(0)
+    return out.view(np.complex64)
+
+
+def acq_conf(**kw):
+    c = GoAcqConf()
+    d = dict(sampled_ms=1, ms_per_code=1, samples_per_chip=4, max_dwells=1, doppler_max=5000, doppler_step=250,
+             num_doppler_bins_step2=4, doppler_step2=125.0, fs_in=4000000, samples_per_ms=4000.0,
+             samples_per_code=4000.0, bit_transition_flag=0, use_CFAR_algorithm_flag=1, make_2_steps=0,
+             cshort=0, threshold=0.0, freq_offset_hz=0, fft_f64=0, analytic_wipeoff=0, keep_grid=0)
+    d.update(kw)
+    for k, v in d.items():
+        setattr(c, k, v)
+    return c
+
+
+class OracleAcq:
+    """pcps_acquisition restatement as an object (oracle/gnss_oracle.c go_acq_*)."""
+
+    def __init__(self, **kw):
+        self.L = oracle()
+        self.conf = acq_conf(**kw)
+        self.h = self.L.go_acq_create(C.byref(self.conf))
+        self.fft_size = self.L.go_acq_fft_size(self.h)
+        self.consumed = self.L.go_acq_consumed_samples(self.h)
+        self.num_bins = self.L.go_acq_num_doppler_bins(self.h)
+
+    def set_local_code(self, code_c64):
+        code = np.ascontiguousarray(code_c64, np.complex64).view(np.float32)
+        need = self.fft_size // 2 if self.conf.bit_transition_flag else self.consumed
+        assert len(code) // 2 >= need, (len(code) // 2, need)
+        self.L.go_acq_set_local_code(self.h, code)
+
+    def run(self, samples, samp_count=0):
+        if self.conf.cshort:
+            s = np.ascontiguousarray(samples, np.int16)
+            assert s.size >= 2 * self.consumed
+        else:
+            s = np.ascontiguousarray(samples, np.complex64).view(np.float32)
+            assert s.size >= 2 * self.consumed
+        r = GoAcqResult()
+        self.L.go_acq_run(self.h, s.ctypes.data_as(C.c_void_p), samp_count, C.byref(r))
+        return r
+
+    def grid(self):
+        eff = self.fft_size // 2 if self.conf.bit_transition_flag else self.fft_size
+        return np.stack([np.ctypeslib.as_array(self.L.go_acq_grid(self.h, b), shape=(self.fft_size,))[:eff].copy()
+                         for b in range(self.num_bins)])
+
+    def close(self):
+        if self.h:
+            self.L.go_acq_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
