@@ -1,0 +1,166 @@
+// Internal declarations shared by the CUDA translation units of libgnss_b200.so (sm_100a only).
+#pragma once
+#include "../../include/gnss_b200.h"
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GB200_TRK_THREADS 256
+#define GB200_TRK_WMAX 4224  // code-window floats staged per CTA (covers 4096 samples at <= 1 table-sample/sample)
+#define GB200_OUT_STRIDE (GB200_MAX_TAPS + 1)  // complex floats per request in the output array
+
+// One multicorrelator request as the kernels see it (device memory, one per (channel, epoch)).
+struct GbTrkWork
+{
+    const void* samples;     // first sample of the correlation window (contiguous: ring mirror)
+    const float* code;       // local code table (float, or float2 when complex)
+    const float* data_code;  // pilot tracking: data-component table correlated at tap `prompt_tap`, or nullptr
+    int code_len;
+    int n;                   // signal_length_samples
+    int n_taps;
+    int prompt_tap;
+    float shifts[GB200_MAX_TAPS];
+    float rem_carr, phase_step, phase_rate;
+    float rem_code, code_step, code_rate;
+    int out_index;           // request slot in the output / partial arrays
+    float nco_mag_delta;     // |inc| - 1 of the reference's float32 phase increment (see nco_* below)
+    // Reference-matched carrier NCO.  The reference rotates by phase_{n+1} = phase_n * inc in float32 with
+    // phase_0 = (cosf(rem), -sinf(rem)) and inc = (cosf(-step), sinf(-step)) (cpu_multicorrelator_real_codes.cc:140-149),
+    // renormalising every 256 samples.  The float32 ROUNDING OF inc shifts the NCO frequency by up to ~3e-8*step rad per
+    // sample, which over 10^4..10^5 samples is visible at the 1e-4 parity budget.  The host therefore derives, in float64,
+    // the angle of the rounded phase_0 and of the rounded inc; the kernel evaluates phase_0 * inc^n from those.
+    double nco_a0_turns;     // arg(phase_0) / 2pi
+    double nco_theta_turns;  // arg(inc) / 2pi
+    double nco_log_mag;      // log|inc| (high-dynamics path: the reference never renormalises phase_doppler there)
+};
+
+// acquisition grid-reduction record: ordering key = (mag desc, bin asc, idx asc)
+struct GbPeak
+{
+    float mag;
+    uint32_t idx;
+    uint32_t bin;
+    uint32_t pad_;
+};
+
+// ---- sample loads: int8 / int16 are widened exactly as volk_gnsssdr_16ic_convert_32fc does ((float)int) ----
+template <int ITEM>
+__device__ __forceinline__ float2 gb_load_item(const void* base, size_t i);
+
+template <>
+__device__ __forceinline__ float2 gb_load_item<GB200_ITEM_32FC>(const void* base, size_t i)
+{
+    return __ldg(reinterpret_cast<const float2*>(base) + i);
+}
+template <>
+__device__ __forceinline__ float2 gb_load_item<GB200_ITEM_16IC>(const void* base, size_t i)
+{
+    short2 v = __ldg(reinterpret_cast<const short2*>(base) + i);
+    return make_float2((float)v.x, (float)v.y);
+}
+template <>
+__device__ __forceinline__ float2 gb_load_item<GB200_ITEM_8IC>(const void* base, size_t i)
+{
+    char2 v = __ldg(reinterpret_cast<const char2*>(base) + i);
+    return make_float2((float)v.x, (float)v.y);
+}
+
+__host__ __device__ inline size_t gb_item_bytes(int item_type)
+{
+    return item_type == GB200_ITEM_32FC ? 8 : (item_type == GB200_ITEM_16IC ? 4 : 2);
+}
+
+// exp(j * 2*pi * (a + n*b)) with a, b in turns (float64), result float32
+__device__ __forceinline__ float2 gb_phasor_turns(double a, double b, double n)
+{
+    double t = fma(n, b, a);
+    t -= rint(t);
+    float s, c;
+    sincospif(2.0f * (float)t, &s, &c);
+    return make_float2(c, s);
+}
+
+__device__ __forceinline__ float2 gb_cmul(float2 a, float2 b)
+{
+    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+
+// kernel launchers (defined in the .cu files, called from service.cu)
+cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_taps, bool has_data, int item_type,
+    int code_kind, bool high_dyn, float2* d_partials, unsigned* d_counters, float2* d_out, int chunk, cudaStream_t st,
+    int* launches);
+
+// ------------------------------------------------------------------ acquisition FFT plan
+#define GB200_ACQ_THREADS 256
+#define GB200_MAX_RADIX_PASSES 16
+#define GB200_MAX_GENERIC_RADIX 64
+
+// Two-level ("four-step") decomposition N = N1 * N2 of the un-normalised DFT:
+//   n = N2*n1 + n2,  k = k1 + N1*k2
+//   forward : A[k1][n2] = W_N^(n2 k1) * sum_n1 x[N2 n1 + n2] W_N1^(n1 k1);   X[k1 + N1 k2] = sum_n2 A[k1][n2] W_N2^(n2 k2)
+//   backward: B[k1][n2] = W_N^-(n2 k1) * sum_k2 Y[k1 + N1 k2] W_N2^-(n2 k2); y[N2 n1 + n2] = sum_k1 B[k1][n2] W_N1^-(n1 k1)
+// Spectra live in the "[k1][k2]" layout (k1-major) everywhere, so both directions only ever touch
+// whole rows (row kernels) or tiles of adjacent columns (column kernels).
+struct GbFftPlan
+{
+    int N, N1, N2;
+    int nrad1, nrad2;
+    int rad1[GB200_MAX_RADIX_PASSES];
+    int rad2[GB200_MAX_RADIX_PASSES];
+    int tile1;  // columns (n2) per CTA in the column kernels (sub-FFT length N1)
+    int tile2;  // rows (k1) per CTA in the row kernels (sub-FFT length N2)
+    const float2* tw1;  // device: W_N1^i, i < N1 (forward sign)
+    const float2* tw2;  // device: W_N2^i, i < N2
+};
+
+// Reference-matched Doppler wipe-off.  The reference builds each bin's table with
+// volk_gnsssdr_s32f_sincos_32fc: out[n] = (cosf(ph_n), sinf(ph_n)), ph_{n+1} = fl32(ph_n + inc) (float32
+// running sum, ...s32f_sincos_32fc.h:405-416).  Inside one float32 binade that running sum is exactly
+// linear in n with an increment rounded to the binade's ulp, so the host simulates the sum once per bin
+// and hands the kernel the piecewise-linear description; ph_n is then reproduced EXACTLY without a table.
+struct GbWipeSeg
+{
+    int n_start;     // first sample of the segment
+    float ph_start;  // ph at n_start
+    float inc_eff;   // exact ph_{n+1} - ph_n inside the segment
+};
+
+struct GbAcqFwdParams
+{
+    const void* samples;   // consumed items
+    int consumed;
+    int item_type;
+    const GbWipeSeg* segs;        // all bins' segments, concatenated
+    const int* seg_offsets;       // [bins + 1] offsets into segs
+    float2* colbuf;        // [bins][N1][N2] scratch after the column stage
+    float2* spectra;       // [bins][N1][N2] forward spectra, [k1][k2] layout
+};
+
+struct GbAcqInvParams
+{
+    const float2* spectra;          // [bins][N1][N2]
+    const float2* const* code_fft;  // per handle: conj(FFT(code)) in [k1][k2] layout
+    float2* rowbuf;                 // [transforms in chunk][N1][N2]
+    int n_bins;
+    int first_transform;            // chunk offset; transform t = handle * n_bins + bin
+    int n_transforms;               // in this chunk
+    int keep_offset;                // first kept output index (N/2 with bit_transition, else 0)
+    int keep_len;                   // effective_fft_size
+    float* const* grid;             // per handle: [bins][keep_len] magnitude grid or nullptr
+    int accumulate;                 // dwell > 1: grid += mag
+    GbPeak* partial;                // [transform][tiles] per-CTA maxima (only when grid == nullptr)
+    float* const* tmpbuf;           // per handle d_tmp_buffer image or nullptr: receives the last bin's magnitudes when accumulating (:737)
+};
+
+cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches);
+cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches);
+cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches);
+cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type, int N, float* d_power, float* d_mag2_tmp, cudaStream_t st, int* launches);
+// grid-free path: reduce per-CTA maxima -> per handle peak
+cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins, int tiles, GbPeak* out, cudaStream_t st, int* launches);
+// grid path: scan stored grids -> per handle peak
+cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches);
+// first_vs_second_peak_statistic's second peak with the d_tmp_buffer quirk (pcps_acquisition.cc:633-660)
+cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches);
+cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st, int* launches);
+size_t gb_acq_col_smem(const GbFftPlan& plan);
+size_t gb_acq_row_smem(const GbFftPlan& plan);

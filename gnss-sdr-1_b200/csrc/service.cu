@@ -1,0 +1,1456 @@
+// libgnss_b200.so: host side of the C ABI declared in include/gnss_b200.h.
+// One gb200_service owns the CUDA stream, the per-stream device sample rings, the FFT plans and the
+// scratch pools; acquisition and tracking handles borrow them.  No CPU compute path exists here: if no
+// sm_100 device is present, gb200_service_create fails and nothing else can be called.
+#include "gb200_internal.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#define GB_CUDA(s, call)                                                                                  \
+    do                                                                                                    \
+        {                                                                                                 \
+            cudaError_t e__ = (call);                                                                     \
+            if (e__ != cudaSuccess)                                                                       \
+                {                                                                                         \
+                    (s)->set_error(std::string(#call) + ": " + cudaGetErrorString(e__));                  \
+                    return GB200_E_CUDA;                                                                  \
+                }                                                                                         \
+        }                                                                                                 \
+    while (0)
+
+namespace
+{
+std::string g_global_error = "no error";
+}
+
+struct GbRing
+{
+    void* d_buf = nullptr;
+    int item_type = -1;
+    uint64_t cap = 0, slack = 0;
+    uint64_t end = 0;    // one past the newest item index held
+    uint64_t begin = 0;  // oldest item index still held
+    bool any = false;
+};
+
+struct GbPlanEntry
+{
+    GbFftPlan plan;
+    float2* d_tw1 = nullptr;
+    float2* d_tw2 = nullptr;
+};
+
+struct gb200_service
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<GbRing> rings;
+    uint64_t ring_capacity = 0, ring_slack = 0;
+    std::map<int, GbPlanEntry> plans;
+    uint64_t launches = 0;
+    std::string error = "no error";
+    std::recursive_mutex mu;
+    // scratch pools (grown on demand, reused)
+    void* d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    void* h_pinned = nullptr;
+    size_t h_pinned_bytes = 0;
+    int sm_count = 148;
+
+    void set_error(const std::string& e) { error = e; g_global_error = e; }
+    int scratch(int slot, size_t bytes, void** out)
+    {
+        if (bytes > scratch_bytes[slot])
+            {
+                if (d_scratch[slot]) cudaFree(d_scratch[slot]);
+                d_scratch[slot] = nullptr;
+                scratch_bytes[slot] = 0;
+                size_t want = bytes + bytes / 4;
+                cudaError_t e = cudaMalloc(&d_scratch[slot], want);
+                if (e != cudaSuccess)
+                    {
+                        set_error(std::string("cudaMalloc scratch: ") + cudaGetErrorString(e));
+                        return GB200_E_CUDA;
+                    }
+                scratch_bytes[slot] = want;
+            }
+        *out = d_scratch[slot];
+        return GB200_OK;
+    }
+    int pinned(size_t bytes, void** out)
+    {
+        if (bytes > h_pinned_bytes)
+            {
+                if (h_pinned) cudaFreeHost(h_pinned);
+                h_pinned = nullptr;
+                h_pinned_bytes = 0;
+                cudaError_t e = cudaMallocHost(&h_pinned, bytes * 2);
+                if (e != cudaSuccess)
+                    {
+                        set_error(std::string("cudaMallocHost: ") + cudaGetErrorString(e));
+                        return GB200_E_CUDA;
+                    }
+                h_pinned_bytes = bytes * 2;
+            }
+        *out = h_pinned;
+        return GB200_OK;
+    }
+};
+
+extern "C" const char* gb200_version(void) { return "gnss_b200 0.1 (sm_100a)"; }
+
+extern "C" const char* gb200_last_error(const gb200_service* s) { return s ? s->error.c_str() : g_global_error.c_str(); }
+
+extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service** out)
+{
+    if (!out) return GB200_E_INVALID;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        {
+            g_global_error = "no CUDA device: libgnss_b200 has no CPU fallback";
+            return GB200_E_NO_DEVICE;
+        }
+    int dev = (cfg && cfg->device >= 0) ? cfg->device : 0;
+    if (cfg && cfg->device < 0) cudaGetDevice(&dev);
+    if (dev >= count)
+        {
+            g_global_error = "device ordinal out of range";
+            return GB200_E_INVALID;
+        }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10)
+        {
+            g_global_error = "device is not sm_100 (Blackwell B200): the kernels are built for sm_100a only";
+            return GB200_E_NO_DEVICE;
+        }
+    if (cudaSetDevice(dev) != cudaSuccess)
+        {
+            g_global_error = "cudaSetDevice failed";
+            return GB200_E_CUDA;
+        }
+    gb200_service* s = new gb200_service();
+    s->device = dev;
+    s->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess)
+        {
+            g_global_error = "cudaStreamCreate failed";
+            delete s;
+            return GB200_E_CUDA;
+        }
+    s->rings.resize((cfg && cfg->max_streams > 0) ? cfg->max_streams : 4);
+    s->ring_capacity = (cfg && cfg->ring_capacity) ? cfg->ring_capacity : (1ull << 24);
+    s->ring_slack = (cfg && cfg->ring_slack) ? cfg->ring_slack : (1ull << 21);
+    if (s->ring_slack > s->ring_capacity) s->ring_slack = s->ring_capacity;
+    *out = s;
+    return GB200_OK;
+}
+
+extern "C" int gb200_service_destroy(gb200_service* s)
+{
+    if (!s) return GB200_E_INVALID;
+    cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->stream);
+    for (auto& r : s->rings)
+        if (r.d_buf) cudaFree(r.d_buf);
+    for (auto& kv : s->plans)
+        {
+            if (kv.second.d_tw1) cudaFree(kv.second.d_tw1);
+            if (kv.second.d_tw2) cudaFree(kv.second.d_tw2);
+        }
+    for (int i = 0; i < 8; i++)
+        if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    cudaStreamDestroy(s->stream);
+    delete s;
+    return GB200_OK;
+}
+
+extern "C" void* gb200_service_cuda_stream(gb200_service* s) { return s ? (void*)s->stream : nullptr; }
+
+extern "C" int gb200_service_synchronize(gb200_service* s)
+{
+    if (!s) return GB200_E_INVALID;
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    return GB200_OK;
+}
+
+extern "C" uint64_t gb200_service_launch_count(const gb200_service* s) { return s ? s->launches : 0; }
+
+// ------------------------------------------------------------------ sample ring
+static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_items, int item_type, uint64_t first, cudaMemcpyKind kind)
+{
+    if (!s || !src || stream_id < 0 || stream_id >= (int)s->rings.size() || item_type < 0 || item_type > 2) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    GbRing& r = s->rings[stream_id];
+    const size_t isz = gb_item_bytes(item_type);
+    if (!r.d_buf)
+        {
+            r.cap = s->ring_capacity;
+            r.slack = s->ring_slack;
+            r.item_type = item_type;
+            GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack) * isz));
+        }
+    if (r.item_type != item_type)
+        {
+            // the front-end was reconfigured: drop what is held and re-type the ring
+            GB_CUDA(s, cudaStreamSynchronize(s->stream));
+            GB_CUDA(s, cudaFree(r.d_buf));
+            r.d_buf = nullptr;
+            GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack) * isz));
+            r.item_type = item_type;
+            r.any = false;
+            r.begin = r.end = 0;
+        }
+    if (n_items == 0) return GB200_OK;
+    if (n_items > r.cap)
+        {
+            s->set_error("push larger than ring capacity");
+            return GB200_E_RANGE;
+        }
+    if (r.any && first != r.end)
+        {
+            // discontinuity: everything held so far is dropped
+            r.begin = first;
+        }
+    else if (!r.any)
+        r.begin = first;
+    const char* p = (const char*)src;
+    uint64_t idx = first;
+    size_t left = n_items;
+    while (left)
+        {
+            const uint64_t pos = idx % r.cap;
+            const size_t run = (size_t)std::min<uint64_t>(left, r.cap - pos);
+            GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + pos * isz, p, run * isz, kind, s->stream));
+            if (pos < r.slack)  // keep the mirror [cap, cap+slack) == [0, slack) so every window is contiguous
+                {
+                    const size_t mrun = (size_t)std::min<uint64_t>(run, r.slack - pos);
+                    GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + (r.cap + pos) * isz, p, mrun * isz, kind, s->stream));
+                }
+            p += run * isz;
+            idx += run;
+            left -= run;
+        }
+    r.end = first + n_items;
+    r.any = true;
+    if (r.end - r.begin > r.cap) r.begin = r.end - r.cap;
+    return GB200_OK;
+}
+
+extern "C" int gb200_stream_push(gb200_service* s, int stream_id, const void* samples, size_t n_items, int item_type, uint64_t first_sample_index)
+{
+    return ring_push(s, stream_id, samples, n_items, item_type, first_sample_index, cudaMemcpyHostToDevice);
+}
+
+extern "C" int gb200_stream_push_device(gb200_service* s, int stream_id, const void* d_samples, size_t n_items, int item_type, uint64_t first_sample_index)
+{
+    return ring_push(s, stream_id, d_samples, n_items, item_type, first_sample_index, cudaMemcpyDeviceToDevice);
+}
+
+// device pointer to `len` contiguous items starting at absolute index `first`, or GB200_E_RANGE
+static int ring_window(gb200_service* s, int stream_id, uint64_t first, uint64_t len, int item_type, const void** out)
+{
+    if (stream_id < 0 || stream_id >= (int)s->rings.size()) return GB200_E_INVALID;
+    GbRing& r = s->rings[stream_id];
+    if (!r.any || first < r.begin || first + len > r.end || len > r.slack)
+        {
+            char msg[200];
+            snprintf(msg, sizeof msg, "samples [%llu, %llu) not in ring [%llu, %llu) (slack %llu)", (unsigned long long)first,
+                (unsigned long long)(first + len), (unsigned long long)r.begin, (unsigned long long)r.end, (unsigned long long)r.slack);
+            s->set_error(msg);
+            return GB200_E_RANGE;
+        }
+    if (r.item_type != item_type)
+        {
+            s->set_error("handle item_type differs from the stream's");
+            return GB200_E_INVALID;
+        }
+    *out = (const char*)r.d_buf + (first % r.cap) * gb_item_bytes(item_type);
+    return GB200_OK;
+}
+
+// ------------------------------------------------------------------ FFT plans
+static bool factor_radices(int M, int* rad, int* nrad)
+{
+    int n = 0, m = M;
+    const int pref[] = {8, 4, 5, 3, 2};
+    for (int p : pref)
+        while (m % p == 0 && m > 1)
+            {
+                if (n >= GB200_MAX_RADIX_PASSES) return false;
+                rad[n++] = p;
+                m /= p;
+            }
+    for (int p = 7; m > 1; p += 2)
+        {
+            while (m % p == 0)
+                {
+                    if (p > GB200_MAX_GENERIC_RADIX || n >= GB200_MAX_RADIX_PASSES) return false;
+                    rad[n++] = p;
+                    m /= p;
+                }
+            if (p > GB200_MAX_GENERIC_RADIX && m > 1) return false;
+        }
+    if (M == 1) n = 0;
+    *nrad = n;
+    return true;
+}
+
+static int pick_tile(int M)
+{
+    // shared memory per CTA = (2*M*(tile+1) + M) * 8 B; keep <= ~72 KB when possible (3 CTAs/SM), hard cap 200 KB
+    const int tiles[] = {16, 8, 4, 2, 1};
+    for (int t : tiles)
+        if (((size_t)2 * M * (t + 1) + M) * 8 <= 72 * 1024) return t;
+    for (int t : tiles)
+        if (((size_t)2 * M * (t + 1) + M) * 8 <= 200 * 1024) return t;
+    return 0;
+}
+
+static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
+{
+    auto it = s->plans.find(N);
+    if (it != s->plans.end())
+        {
+            *out = &it->second.plan;
+            return GB200_OK;
+        }
+    if (N < 1) return GB200_E_INVALID;
+    // N1 <= N2, as close to sqrt(N) as the factorisation allows, both sub-lengths supported
+    int best1 = 0;
+    for (int n1 = 1; (long long)n1 * n1 <= N; n1++)
+        {
+            if (N % n1) continue;
+            int n2 = N / n1, r[GB200_MAX_RADIX_PASSES], nr;
+            if (!factor_radices(n1, r, &nr) || !factor_radices(n2, r, &nr)) continue;
+            if (!pick_tile(n1) || !pick_tile(n2)) continue;
+            best1 = n1;
+        }
+    if (!best1)
+        {
+            s->set_error("FFT length " + std::to_string(N) + " unsupported (prime factor > 64 or sub-transform too long)");
+            return GB200_E_UNSUPPORTED;
+        }
+    GbPlanEntry e;
+    memset(&e.plan, 0, sizeof(e.plan));
+    e.plan.N = N;
+    e.plan.N1 = best1;
+    e.plan.N2 = N / best1;
+    factor_radices(e.plan.N1, e.plan.rad1, &e.plan.nrad1);
+    factor_radices(e.plan.N2, e.plan.rad2, &e.plan.nrad2);
+    e.plan.tile1 = pick_tile(e.plan.N1);
+    e.plan.tile2 = pick_tile(e.plan.N2);
+    for (int which = 0; which < 2; which++)
+        {
+            const int M = which ? e.plan.N2 : e.plan.N1;
+            std::vector<float2> tw(M);
+            for (int i = 0; i < M; i++)
+                {
+                    const double a = -6.283185307179586476925286766559 * (double)i / (double)M;
+                    tw[i] = make_float2((float)cos(a), (float)sin(a));
+                }
+            float2* d = nullptr;
+            GB_CUDA(s, cudaMalloc(&d, sizeof(float2) * M));
+            GB_CUDA(s, cudaMemcpyAsync(d, tw.data(), sizeof(float2) * M, cudaMemcpyHostToDevice, s->stream));
+            GB_CUDA(s, cudaStreamSynchronize(s->stream));
+            if (which)
+                e.d_tw2 = d;
+            else
+                e.d_tw1 = d;
+        }
+    e.plan.tw1 = e.d_tw1;
+    e.plan.tw2 = e.d_tw2;
+    auto ins = s->plans.emplace(N, e);
+    *out = &ins.first->second.plan;
+    return GB200_OK;
+}
+
+// ------------------------------------------------------------------ acquisition
+struct gb200_acq
+{
+    gb200_service* s = nullptr;
+    gb200_acq_cfg c;
+    uint32_t consumed = 0, fft_size = 0, num_bins = 0, eff = 0;
+    bool use_cfar = false;
+    bool keep_grid = false;
+    const GbFftPlan* plan = nullptr;
+    float2* d_code_fft = nullptr;
+    bool code_set = false;
+    float* d_grid = nullptr;  // [max(num_bins, bins_step2)][eff]
+    size_t grid_rows = 0;
+    float* d_tmp = nullptr;   // d_tmp_buffer image, fft_size floats (non-CFAR statistic only)
+    // block state (pcps_acquisition members)
+    uint32_t dwell_counter = 0;  // d_num_noncoherent_integrations_counter
+    bool step_two = false;
+    int positive_acq = 0;
+    float doppler_center_step_two = 0.f;
+    // wipe-off description cache (recomputed when the Doppler grid changes)
+    std::vector<float> seg_steps;
+    std::vector<GbWipeSeg> segs;
+    std::vector<int> seg_offs;
+    // launch -> collect hand-over
+    uint64_t pending_first = 0;
+    int pending_group = -1, pending_slot = -1;
+    bool pending = false;
+
+    bool need_grid() const { return keep_grid || !use_cfar || c.max_dwells > 1; }
+};
+
+static const double kGpsTwoPi = 6.283185307179586;  // GPS_L1_CA.h:46
+
+// pcps_acquisition.cc:296-305: phase_step_rad as float32
+static float acq_phase_step(const gb200_acq* a, float freq) { return (float)(kGpsTwoPi * freq / (float)a->c.fs_in); }
+
+static void acq_bin_steps(const gb200_acq* a, std::vector<float>& steps)
+{
+    steps.clear();
+    if (!a->step_two)
+        {
+            for (uint32_t i = 0; i < a->num_bins; i++)
+                {
+                    const int32_t doppler = -(int32_t)a->c.doppler_max + (int32_t)(a->c.doppler_step * i);  // :357-358
+                    steps.push_back(acq_phase_step(a, (float)(a->c.freq_offset_hz + doppler)));
+                }
+        }
+    else
+        {
+            for (uint32_t i = 0; i < a->c.num_doppler_bins_step2; i++)  // :383-390
+                {
+                    const float doppler = ((float)i - (float)floor(a->c.num_doppler_bins_step2 / 2.0)) * a->c.doppler_step2;
+                    steps.push_back(acq_phase_step(a, a->doppler_center_step_two + doppler));
+                }
+        }
+}
+
+// Simulate volk_gnsssdr_s32f_sincos_32fc_generic's float32 phase accumulation (phase starts at 0, increment
+// -phase_step_rad, pcps_acquisition.cc:307-309) and compress it into exact piecewise-linear segments.
+static void acq_wipe_segments(float phase_step_rad, uint32_t n, std::vector<GbWipeSeg>& out)
+{
+    const float inc = -phase_step_rad;
+    volatile float ph = 0.0f;  // volatile: keep every partial sum rounded to float32
+    GbWipeSeg cur;
+    cur.n_start = 0;
+    cur.ph_start = 0.0f;
+    cur.inc_eff = 0.0f;
+    bool have_inc = false;
+    for (uint32_t i = 0; i + 1 < n; i++)
+        {
+            const float prev = ph;
+            ph = prev + inc;
+            const float next = ph;
+            const float d = (float)((double)next - (double)prev);
+            if (!have_inc)
+                {
+                    cur.inc_eff = d;
+                    have_inc = true;
+                }
+            else if (d != cur.inc_eff)
+                {
+                    out.push_back(cur);
+                    cur.n_start = (int)i;
+                    cur.ph_start = prev;
+                    cur.inc_eff = d;
+                }
+        }
+    out.push_back(cur);
+}
+
+static void acq_all_segments(const std::vector<float>& steps, uint32_t n, std::vector<GbWipeSeg>& segs, std::vector<int>& offs)
+{
+    segs.clear();
+    offs.clear();
+    for (float st : steps)
+        {
+            offs.push_back((int)segs.size());
+            acq_wipe_segments(st, n, segs);
+        }
+    offs.push_back((int)segs.size());
+}
+
+static void acq_derive(gb200_acq* a)
+{
+    const gb200_acq_cfg& c = a->c;
+    a->consumed = (uint32_t)((float)c.sampled_ms * c.samples_per_ms * (float)(c.bit_transition_flag ? 2 : 1));  // :75
+    a->fft_size = (c.sampled_ms == c.ms_per_code) ? a->consumed : a->consumed * 2;                               // :76-84
+    if (c.bit_transition_flag)
+        {
+            a->fft_size = a->consumed * 2;  // :113-117
+            a->c.max_dwells = 1;
+        }
+    a->eff = c.bit_transition_flag ? a->fft_size / 2 : a->fft_size;
+    a->use_cfar = (a->c.max_dwells == 1) ? (c.use_CFAR_algorithm_flag != 0) : false;  // :152-159
+    a->num_bins = c.doppler_step ? (uint32_t)std::ceil((double)((int32_t)c.doppler_max - (int32_t)(-(int32_t)c.doppler_max)) / (double)c.doppler_step) : 0;  // :326
+}
+
+static int acq_alloc_grid(gb200_acq* a)
+{
+    gb200_service* s = a->s;
+    const size_t rows = std::max<size_t>(a->num_bins, a->c.make_2_steps ? a->c.num_doppler_bins_step2 : 0);
+    if (a->need_grid() && (a->d_grid == nullptr || rows > a->grid_rows))
+        {
+            if (a->d_grid) cudaFree(a->d_grid);
+            a->d_grid = nullptr;
+            GB_CUDA(s, cudaMalloc(&a->d_grid, sizeof(float) * rows * a->eff));
+            GB_CUDA(s, cudaMemsetAsync(a->d_grid, 0, sizeof(float) * rows * a->eff, s->stream));
+            a->grid_rows = rows;
+        }
+    if (!a->use_cfar && !a->d_tmp)
+        {
+            GB_CUDA(s, cudaMalloc(&a->d_tmp, sizeof(float) * a->fft_size));
+            GB_CUDA(s, cudaMemsetAsync(a->d_tmp, 0, sizeof(float) * a->fft_size, s->stream));
+        }
+    return GB200_OK;
+}
+
+extern "C" int gb200_acq_create(gb200_service* s, const gb200_acq_cfg* cfg, gb200_acq** out)
+{
+    if (!s || !cfg || !out) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    *out = nullptr;
+    if (cfg->item_type < 0 || cfg->item_type > 2 || cfg->doppler_step == 0 || cfg->fs_in <= 0 || cfg->max_dwells == 0)
+        {
+            s->set_error("gb200_acq_create: bad configuration");
+            return GB200_E_INVALID;
+        }
+    gb200_acq* a = new gb200_acq();
+    a->s = s;
+    a->c = *cfg;
+    acq_derive(a);
+    if (a->consumed == 0 || a->num_bins == 0 || (uint64_t)a->consumed > s->ring_slack)
+        {
+            s->set_error("gb200_acq_create: consumed samples is 0 or exceeds the ring slack");
+            delete a;
+            return GB200_E_INVALID;
+        }
+    int rc = get_plan(s, (int)a->fft_size, &a->plan);
+    if (rc != GB200_OK)
+        {
+            delete a;
+            return rc;
+        }
+    cudaError_t e = cudaMalloc(&a->d_code_fft, sizeof(float2) * a->fft_size);
+    if (e != cudaSuccess)
+        {
+            s->set_error(std::string("cudaMalloc code fft: ") + cudaGetErrorString(e));
+            delete a;
+            return GB200_E_CUDA;
+        }
+    rc = acq_alloc_grid(a);
+    if (rc != GB200_OK)
+        {
+            gb200_acq_destroy(a);
+            return rc;
+        }
+    *out = a;
+    return GB200_OK;
+}
+
+extern "C" int gb200_acq_destroy(gb200_acq* a)
+{
+    if (!a) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(a->s->mu);
+    cudaSetDevice(a->s->device);
+    cudaStreamSynchronize(a->s->stream);
+    if (a->d_code_fft) cudaFree(a->d_code_fft);
+    if (a->d_grid) cudaFree(a->d_grid);
+    if (a->d_tmp) cudaFree(a->d_tmp);
+    delete a;
+    return GB200_OK;
+}
+
+extern "C" uint32_t gb200_acq_fft_size(const gb200_acq* a) { return a ? a->fft_size : 0; }
+extern "C" uint32_t gb200_acq_consumed_samples(const gb200_acq* a) { return a ? a->consumed : 0; }
+extern "C" uint32_t gb200_acq_num_doppler_bins(const gb200_acq* a) { return a ? a->num_bins : 0; }
+
+extern "C" int gb200_acq_set_local_code(gb200_acq* a, const float* code_iq, size_t n_items)
+{
+    if (!a || !code_iq) return GB200_E_INVALID;
+    gb200_service* s = a->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    const uint32_t N = a->fft_size;
+    // zero-pad layout of pcps_acquisition.cc:253-270
+    size_t offset, count;
+    if (a->c.bit_transition_flag)
+        {
+            offset = N / 2;
+            count = N / 2;
+        }
+    else if (a->c.sampled_ms == a->c.ms_per_code)
+        {
+            offset = 0;
+            count = a->consumed;
+        }
+    else
+        {
+            offset = N - a->consumed;
+            count = a->consumed;
+        }
+    if (n_items < count)
+        {
+            s->set_error("gb200_acq_set_local_code: code shorter than the block's copy length");
+            return GB200_E_INVALID;
+        }
+    void* hp;
+    int rc = s->pinned(sizeof(float2) * N, &hp);
+    if (rc) return rc;
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));  // the pinned staging buffer may still be in flight
+    memset(hp, 0, sizeof(float2) * N);
+    memcpy((float2*)hp + offset, code_iq, sizeof(float2) * count);
+    void *d_in, *d_col;
+    if ((rc = s->scratch(2, sizeof(float2) * N, &d_in))) return rc;
+    if ((rc = s->scratch(3, sizeof(float2) * N, &d_col))) return rc;
+    GB_CUDA(s, cudaMemcpyAsync(d_in, hp, sizeof(float2) * N, cudaMemcpyHostToDevice, s->stream));
+    GbAcqFwdParams p;
+    p.samples = d_in;
+    p.consumed = (int)N;
+    p.item_type = GB200_ITEM_32FC;
+    p.segs = nullptr;
+    p.seg_offsets = nullptr;
+    p.colbuf = (float2*)d_col;
+    p.spectra = a->d_code_fft;
+    int l = 0;
+    GB_CUDA(s, gb_acq_forward(*a->plan, p, 1, false, s->stream, &l));
+    GB_CUDA(s, gb_acq_conj(a->d_code_fft, N, s->stream, &l));  // volk_32fc_conjugate_32fc, :273
+    s->launches += l;
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    a->code_set = true;
+    return GB200_OK;
+}
+
+extern "C" int gb200_acq_set_doppler(gb200_acq* a, uint32_t doppler_max, uint32_t doppler_step, int64_t freq_offset_hz)
+{
+    if (!a || doppler_step == 0) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(a->s->mu);
+    cudaSetDevice(a->s->device);
+    a->c.doppler_max = doppler_max;
+    a->c.doppler_step = doppler_step;
+    a->c.freq_offset_hz = freq_offset_hz;
+    acq_derive(a);
+    return acq_alloc_grid(a);
+}
+
+extern "C" int gb200_acq_set_threshold(gb200_acq* a, float threshold)
+{
+    if (!a) return GB200_E_INVALID;
+    a->c.threshold = threshold;
+    return GB200_OK;
+}
+
+extern "C" int gb200_acq_keep_grid(gb200_acq* a, int keep)
+{
+    if (!a) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(a->s->mu);
+    cudaSetDevice(a->s->device);
+    a->keep_grid = keep != 0;
+    return acq_alloc_grid(a);
+}
+
+extern "C" int gb200_acq_reset(gb200_acq* a)
+{
+    if (!a) return GB200_E_INVALID;
+    gb200_service* s = a->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    a->dwell_counter = 0;
+    a->step_two = false;
+    a->positive_acq = 0;
+    if (a->d_grid) GB_CUDA(s, cudaMemsetAsync(a->d_grid, 0, sizeof(float) * a->grid_rows * a->eff, s->stream));
+    return GB200_OK;
+}
+
+extern "C" int gb200_acq_read_grid(gb200_acq* a, float* dst)
+{
+    if (!a || !dst) return GB200_E_INVALID;
+    gb200_service* s = a->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (!a->d_grid)
+        {
+            s->set_error("gb200_acq_read_grid: handle keeps no grid (see gb200_acq_keep_grid)");
+            return GB200_E_STATE;
+        }
+    GB_CUDA(s, cudaMemcpyAsync(dst, a->d_grid, sizeof(float) * a->num_bins * a->eff, cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    return GB200_OK;
+}
+
+// ---- batched acquisition: launch (asynchronous) / collect ----
+namespace
+{
+struct AcqGroup
+{
+    std::vector<int> members;  // indices into the caller's list
+    std::vector<float> steps;
+    bool grid = false;
+    size_t off_segs = 0, off_segoff = 0, off_code = 0, off_grid = 0, off_tmp = 0;  // byte offsets in the upload arena
+    size_t off_power = 0, off_peaks = 0;                            // byte offsets in the result arena
+};
+struct AcqBatchCtx
+{
+    std::vector<AcqGroup> groups;
+    std::vector<char> h_results;
+    bool active = false;
+};
+AcqBatchCtx g_unused_ctx;
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+}  // namespace
+
+static std::map<gb200_service*, AcqBatchCtx>& acq_ctx_map()
+{
+    static std::map<gb200_service*, AcqBatchCtx> m;
+    return m;
+}
+
+extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index)
+{
+    if (!list || n <= 0 || !list[0]) return GB200_E_INVALID;
+    gb200_service* s = list[0]->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    AcqBatchCtx& ctx = acq_ctx_map()[s];
+    if (ctx.active)
+        {
+            s->set_error("gb200_acq_launch_batch: previous batch not collected");
+            return GB200_E_STATE;
+        }
+    for (int i = 0; i < n; i++)
+        {
+            if (!list[i] || list[i]->s != s) return GB200_E_INVALID;
+            if (!list[i]->code_set)
+                {
+                    s->set_error("gb200_acq_run: set_local_code has not been called");
+                    return GB200_E_STATE;
+                }
+            for (int j = 0; j < i; j++)
+                if (list[j] == list[i]) return GB200_E_INVALID;
+        }
+    // group handles that can share the wiped-off forward spectra
+    ctx.groups.clear();
+    std::vector<float> steps;
+    for (int i = 0; i < n; i++)
+        {
+            gb200_acq* a = list[i];
+            acq_bin_steps(a, steps);
+            bool placed = false;
+            if (!a->need_grid())
+                for (auto& g : ctx.groups)
+                    {
+                        gb200_acq* b = list[g.members[0]];
+                        if (!g.grid && b->fft_size == a->fft_size && b->consumed == a->consumed && b->c.item_type == a->c.item_type &&
+                            b->c.bit_transition_flag == a->c.bit_transition_flag && g.steps == steps)
+                            {
+                                g.members.push_back(i);
+                                placed = true;
+                                break;
+                            }
+                    }
+            if (!placed)
+                {
+                    AcqGroup g;
+                    g.members.push_back(i);
+                    g.steps = steps;
+                    g.grid = a->need_grid();
+                    ctx.groups.push_back(g);
+                }
+        }
+    // arenas
+    size_t up = 0, res = 0;
+    for (auto& g : ctx.groups)
+        {
+            gb200_acq* a0 = list[g.members[0]];
+            if (a0->seg_steps != g.steps || a0->seg_offs.empty())
+                {
+                    acq_all_segments(g.steps, a0->fft_size, a0->segs, a0->seg_offs);
+                    a0->seg_steps = g.steps;
+                }
+            g.off_segs = up;
+            up = align_up(up + a0->segs.size() * sizeof(GbWipeSeg), 16);
+            g.off_segoff = up;
+            up = align_up(up + a0->seg_offs.size() * sizeof(int), 16);
+            g.off_code = up;
+            up = align_up(up + g.members.size() * sizeof(void*), 16);
+            g.off_grid = up;
+            up = align_up(up + g.members.size() * sizeof(void*), 16);
+            g.off_tmp = up;
+            up = align_up(up + g.members.size() * sizeof(void*), 16);
+            g.off_power = res;
+            res = align_up(res + sizeof(float), 16);
+            g.off_peaks = res;
+            res = align_up(res + g.members.size() * sizeof(GbPeak), 16);
+        }
+    void *h_up, *d_up, *d_res;
+    int rc;
+    if ((rc = s->pinned(up + res, &h_up))) return rc;
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    if ((rc = s->scratch(4, up, &d_up))) return rc;
+    if ((rc = s->scratch(5, res, &d_res))) return rc;
+    for (auto& g : ctx.groups)
+        {
+            {
+                gb200_acq* a0 = list[g.members[0]];
+                memcpy((char*)h_up + g.off_segs, a0->segs.data(), a0->segs.size() * sizeof(GbWipeSeg));
+                memcpy((char*)h_up + g.off_segoff, a0->seg_offs.data(), a0->seg_offs.size() * sizeof(int));
+            }
+            for (size_t k = 0; k < g.members.size(); k++)
+                {
+                    gb200_acq* a = list[g.members[k]];
+                    ((const float2**)((char*)h_up + g.off_code))[k] = a->d_code_fft;
+                    ((float**)((char*)h_up + g.off_grid))[k] = g.grid ? a->d_grid : nullptr;
+                    ((float**)((char*)h_up + g.off_tmp))[k] = a->d_tmp;
+                }
+        }
+    GB_CUDA(s, cudaMemcpyAsync(d_up, h_up, up, cudaMemcpyHostToDevice, s->stream));
+
+    int l = 0;
+    for (auto& g : ctx.groups)
+        {
+            gb200_acq* a0 = list[g.members[0]];
+            const GbFftPlan& plan = *a0->plan;
+            const int N = (int)a0->fft_size;
+            const int bins = (int)g.steps.size();
+            const void* win;
+            if ((rc = ring_window(s, stream_id, first_sample_index, a0->consumed, a0->c.item_type, &win))) return rc;
+            void *d_col, *d_spec;
+            if ((rc = s->scratch(0, sizeof(float2) * (size_t)N * bins, &d_col))) return rc;
+            if ((rc = s->scratch(1, sizeof(float2) * (size_t)N * bins, &d_spec))) return rc;
+            GbAcqFwdParams fp;
+            fp.samples = win;
+            fp.consumed = (int)a0->consumed;
+            fp.item_type = a0->c.item_type;
+            fp.segs = (const GbWipeSeg*)((char*)d_up + g.off_segs);
+            fp.seg_offsets = (const int*)((char*)d_up + g.off_segoff);
+            fp.colbuf = (float2*)d_col;
+            fp.spectra = (float2*)d_spec;
+            GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l));
+            // input power (CFAR or bit transition, pcps_acquisition.cc:703-709)
+            bool want_power = false;
+            for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag;
+            float* d_power = (float*)((char*)d_res + g.off_power);
+            if (want_power)
+                GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, N, d_power, (g.grid && !a0->use_cfar) ? a0->d_tmp : nullptr, s->stream, &l));
+            // inverse side in L2-sized chunks of transforms
+            const int T = bins * (int)g.members.size();
+            const size_t l2_budget = 48ull << 20;
+            int chunkT = (int)std::max<size_t>(1, l2_budget / (sizeof(float2) * (size_t)N));
+            chunkT = std::min(chunkT, T);
+            const int tiles = (plan.N2 + plan.tile1 - 1) / plan.tile1;
+            void *d_row, *d_part;
+            if ((rc = s->scratch(2, sizeof(float2) * (size_t)N * chunkT, &d_row))) return rc;
+            if ((rc = s->scratch(3, sizeof(GbPeak) * (size_t)T * tiles, &d_part))) return rc;
+            for (int t0 = 0; t0 < T; t0 += chunkT)
+                {
+                    GbAcqInvParams ip;
+                    ip.spectra = (const float2*)d_spec;
+                    ip.code_fft = (const float2* const*)((char*)d_up + g.off_code);
+                    ip.rowbuf = (float2*)d_row;
+                    ip.n_bins = bins;
+                    ip.first_transform = t0;
+                    ip.n_transforms = std::min(chunkT, T - t0);
+                    ip.keep_offset = a0->c.bit_transition_flag ? N / 2 : 0;
+                    ip.keep_len = (int)a0->eff;
+                    ip.grid = g.grid ? (float* const*)((char*)d_up + g.off_grid) : nullptr;
+                    ip.accumulate = (g.grid && a0->dwell_counter >= 1) ? 1 : 0;  // this is dwell number dwell_counter+1
+                    ip.partial = (GbPeak*)d_part;
+                    ip.tmpbuf = (g.grid && !a0->use_cfar) ? (float* const*)((char*)d_up + g.off_tmp) : nullptr;
+                    GB_CUDA(s, gb_acq_inverse(plan, ip, s->stream, &l));
+                }
+            GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
+            if (g.grid)
+                GB_CUDA(s, gb_acq_grid_peaks((float* const*)((char*)d_up + g.off_grid), (int)g.members.size(), bins, (int)a0->eff, d_peaks, s->stream, &l));
+            else
+                GB_CUDA(s, gb_acq_reduce_peaks((const GbPeak*)d_part, (int)g.members.size(), bins, tiles, d_peaks, s->stream, &l));
+        }
+    s->launches += l;
+    ctx.h_results.resize(res);
+    GB_CUDA(s, cudaMemcpyAsync((char*)h_up + up, d_res, res, cudaMemcpyDeviceToHost, s->stream));
+    for (int i = 0; i < n; i++)
+        {
+            list[i]->pending = true;
+            list[i]->pending_first = first_sample_index;
+        }
+    for (size_t gi = 0; gi < ctx.groups.size(); gi++)
+        for (size_t k = 0; k < ctx.groups[gi].members.size(); k++)
+            {
+                list[ctx.groups[gi].members[k]]->pending_group = (int)gi;
+                list[ctx.groups[gi].members[k]]->pending_slot = (int)k;
+            }
+    ctx.active = true;
+    // remember where the results will land
+    ctx.h_results.assign(sizeof(void*) + sizeof(size_t), 0);
+    *(void**)ctx.h_results.data() = (char*)h_up + up;
+    return GB200_OK;
+}
+
+// decision logic of acquisition_core, pcps_acquisition.cc:832-929 (events -> `decision`)
+static void acq_decide(gb200_acq* a, float stat, gb200_acq_result* out)
+{
+    bool positive = false, negative = false;
+    int state = 1;
+    if (!a->c.bit_transition_flag)
+        {
+            if (stat > a->c.threshold)
+                {
+                    if (a->c.make_2_steps)
+                        {
+                            if (a->step_two)
+                                {
+                                    positive = true;
+                                    a->step_two = false;
+                                    state = 0;
+                                }
+                            else
+                                {
+                                    a->step_two = true;
+                                    a->dwell_counter = 0;
+                                    a->positive_acq = 0;
+                                    state = 0;
+                                }
+                        }
+                    else
+                        {
+                            positive = true;
+                            state = 0;
+                        }
+                }
+            else
+                state = 1;
+            if (a->dwell_counter == a->c.max_dwells)
+                {
+                    if (state != 0) negative = true;
+                    state = 0;
+                    a->step_two = false;
+                }
+        }
+    else
+        {
+            if (stat > a->c.threshold)
+                {
+                    if (a->c.make_2_steps)
+                        {
+                            if (a->step_two)
+                                {
+                                    positive = true;
+                                    a->step_two = false;
+                                }
+                            else
+                                {
+                                    a->step_two = true;
+                                    a->dwell_counter = 0;
+                                }
+                        }
+                    else
+                        positive = true;
+                }
+            else
+                {
+                    a->step_two = false;
+                    negative = true;
+                }
+        }
+    if (positive) a->positive_acq = 1;
+    if (negative) a->positive_acq = 0;
+    out->decision = positive ? 1 : (negative ? 0 : (a->step_two ? 3 : 2));
+    if (a->step_two) a->doppler_center_step_two = (float)out->acq_doppler_hz;  // general_work :964-970
+}
+
+extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_result* out)
+{
+    if (!list || n <= 0 || !list[0] || !out) return GB200_E_INVALID;
+    gb200_service* s = list[0]->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    AcqBatchCtx& ctx = acq_ctx_map()[s];
+    if (!ctx.active)
+        {
+            s->set_error("gb200_acq_collect_batch: nothing launched");
+            return GB200_E_STATE;
+        }
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    const char* h_res = *(char**)ctx.h_results.data();
+    int rc = GB200_OK;
+    for (int i = 0; i < n; i++)
+        {
+            gb200_acq* a = list[i];
+            if (!a->pending || a->pending_group < 0 || a->pending_group >= (int)ctx.groups.size())
+                {
+                    s->set_error("gb200_acq_collect_batch: handle was not part of the launched batch");
+                    ctx.active = false;
+                    return GB200_E_STATE;
+                }
+            const AcqGroup& g = ctx.groups[a->pending_group];
+            const float power = *(const float*)(h_res + g.off_power);
+            const GbPeak pk = ((const GbPeak*)(h_res + g.off_peaks))[a->pending_slot];
+            gb200_acq_result r;
+            memset(&r, 0, sizeof r);
+            a->dwell_counter++;
+            const bool was_step_two = a->step_two;
+            r.code_phase_index = pk.idx;
+            r.doppler_bin = pk.bin;
+            r.peak_mag = pk.mag;
+            if (!was_step_two)
+                r.doppler_hz = -(int32_t)a->c.doppler_max + (int32_t)a->c.doppler_step * (int32_t)pk.bin;  // :585-588
+            else
+                r.doppler_hz = (int32_t)(a->doppler_center_step_two + ((float)pk.bin - (float)floor(a->c.num_doppler_bins_step2 / 2.0)) * a->c.doppler_step2);  // :591
+            float stat;
+            if (a->use_cfar)
+                {
+                    r.input_power = power;
+                    const float nf = (float)a->fft_size * (float)a->fft_size;  // :571
+                    const float magt = pk.mag / (nf * nf);
+                    stat = magt / power;
+                }
+            else
+                {
+                    r.input_power = a->c.bit_transition_flag ? power : 0.0f;
+                    // second peak on the winning row (:633-660); one more tiny launch + 4-byte read
+                    float* d_second;
+                    void* scratch;
+                    if ((rc = s->scratch(6, 16, &scratch))) break;
+                    d_second = (float*)scratch;
+                    int l = 0;
+                    cudaError_t e = gb_acq_second_peak(a->d_grid + (size_t)pk.bin * a->eff, a->d_tmp, (int)a->fft_size, (int)pk.idx, (int)a->c.samples_per_chip, d_second, s->stream, &l);
+                    s->launches += l;
+                    float second = 0.f;
+                    if (e == cudaSuccess) e = cudaMemcpyAsync(&second, d_second, sizeof(float), cudaMemcpyDeviceToHost, s->stream);
+                    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+                    if (e != cudaSuccess)
+                        {
+                            s->set_error(std::string("second peak: ") + cudaGetErrorString(e));
+                            rc = GB200_E_CUDA;
+                            break;
+                        }
+                    stat = pk.mag / second;
+                }
+            r.test_statistic = stat;
+            r.acq_delay_samples = (double)fmodf((float)pk.idx, a->c.samples_per_code);  // :766 (float32 fmod)
+            r.acq_doppler_hz = (double)r.doppler_hz;
+            r.acq_samplestamp = a->pending_first + a->consumed;  // d_sample_counter after buffering, SURVEY 3.2
+            acq_decide(a, stat, &r);
+            // end-of-attempt reset, :912-929
+            if (a->dwell_counter == a->c.max_dwells || a->positive_acq == 1)
+                {
+                    a->dwell_counter = 0;
+                    a->positive_acq = 0;
+                    if (a->d_grid && !a->keep_grid)
+                        {
+                            cudaError_t e = cudaMemsetAsync(a->d_grid, 0, sizeof(float) * a->grid_rows * a->eff, s->stream);
+                            if (e != cudaSuccess) rc = GB200_E_CUDA;
+                        }
+                }
+            a->pending = false;
+            out[i] = r;
+        }
+    ctx.active = false;
+    return rc;
+}
+
+extern "C" int gb200_acq_run_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index, gb200_acq_result* out)
+{
+    int rc = gb200_acq_launch_batch(list, n, stream_id, first_sample_index);
+    if (rc) return rc;
+    return gb200_acq_collect_batch(list, n, out);
+}
+
+extern "C" int gb200_acq_run(gb200_acq* a, int stream_id, uint64_t first_sample_index, gb200_acq_result* out)
+{
+    gb200_acq* l[1] = {a};
+    return gb200_acq_run_batch(l, 1, stream_id, first_sample_index, out);
+}
+
+// ------------------------------------------------------------------ tracking
+struct gb200_trk
+{
+    gb200_service* s = nullptr;
+    gb200_trk_cfg c;
+    float* d_code = nullptr;       // float[code_len] or float2[code_len]
+    float* d_data_code = nullptr;  // float[code_len] or nullptr
+    int code_len = 0;
+    int n_taps = 0;
+    int prompt_tap = 0;
+    bool has_data = false;
+    float shifts[GB200_MAX_TAPS];
+    // resources of the single-request path (gb200_trk_correlate)
+    gb200_trk_batch* single = nullptr;
+};
+
+struct TrkGroup
+{
+    int first = 0, count = 0;  // range in the (sorted) work array
+    int n_taps = 0, item_type = 0, code_kind = 0, max_n = 0;
+    bool has_data = false, high_dyn = false;
+};
+
+struct gb200_trk_batch
+{
+    gb200_service* s = nullptr;
+    int n = 0;
+    std::vector<GbTrkWork> h_work;
+    std::vector<int> order;  // work slot -> request index
+    std::vector<TrkGroup> groups;
+    GbTrkWork* d_work = nullptr;
+    float2* d_out = nullptr;
+    float2* d_partials = nullptr;
+    unsigned* d_counters = nullptr;
+    float2* h_out = nullptr;  // pinned
+    int chunk = 4096;
+    int max_chunks = 1;
+};
+
+extern "C" int gb200_trk_create(gb200_service* s, const gb200_trk_cfg* cfg, gb200_trk** out)
+{
+    if (!s || !cfg || !out) return GB200_E_INVALID;
+    *out = nullptr;
+    if (cfg->n_taps < 1 || cfg->n_taps > GB200_MAX_TAPS || cfg->max_code_len < 1 || cfg->item_type < 0 || cfg->item_type > 2 ||
+        (cfg->code_kind != GB200_CODE_REAL && cfg->code_kind != GB200_CODE_CPLX) || (cfg->high_dyn && cfg->code_kind == GB200_CODE_CPLX))
+        {
+            s->set_error("gb200_trk_create: bad configuration");
+            return GB200_E_INVALID;
+        }
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    gb200_trk* t = new gb200_trk();
+    t->s = s;
+    t->c = *cfg;
+    const size_t w = cfg->code_kind == GB200_CODE_CPLX ? 2 : 1;
+    cudaError_t e = cudaMalloc(&t->d_code, sizeof(float) * w * cfg->max_code_len);
+    if (e == cudaSuccess && cfg->code_kind == GB200_CODE_REAL) e = cudaMalloc(&t->d_data_code, sizeof(float) * cfg->max_code_len);
+    if (e != cudaSuccess)
+        {
+            s->set_error(std::string("cudaMalloc code: ") + cudaGetErrorString(e));
+            if (t->d_code) cudaFree(t->d_code);
+            delete t;
+            return GB200_E_CUDA;
+        }
+    *out = t;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_destroy(gb200_trk* t)
+{
+    if (!t) return GB200_E_INVALID;
+    gb200_service* s = t->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->stream);
+    if (t->single) gb200_trk_batch_destroy(t->single);
+    if (t->d_code) cudaFree(t->d_code);
+    if (t->d_data_code) cudaFree(t->d_data_code);
+    delete t;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_set_local_code_and_taps(gb200_trk* t, const void* code, int code_len, const float* shifts, int n_taps)
+{
+    if (!t || !code || !shifts) return GB200_E_INVALID;
+    gb200_service* s = t->s;
+    if (code_len < 1 || code_len > t->c.max_code_len || n_taps < 1 || n_taps > t->c.n_taps)
+        {
+            s->set_error("gb200_trk_set_local_code_and_taps: code_len / n_taps exceed what the handle was created for");
+            return GB200_E_INVALID;
+        }
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    const size_t w = t->c.code_kind == GB200_CODE_CPLX ? 2 : 1;
+    GB_CUDA(s, cudaMemcpyAsync(t->d_code, code, sizeof(float) * w * code_len, cudaMemcpyHostToDevice, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));  // `code` is caller memory: do not keep reading it
+    t->code_len = code_len;
+    t->n_taps = n_taps;
+    for (int i = 0; i < GB200_MAX_TAPS; i++) t->shifts[i] = i < n_taps ? shifts[i] : 0.f;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_set_data_code(gb200_trk* t, const float* code, int code_len, int prompt_tap)
+{
+    if (!t) return GB200_E_INVALID;
+    gb200_service* s = t->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    if (!code)
+        {
+            t->has_data = false;
+            return GB200_OK;
+        }
+    if (t->c.code_kind != GB200_CODE_REAL || code_len != t->code_len || prompt_tap < 0 || prompt_tap >= t->n_taps)
+        {
+            s->set_error("gb200_trk_set_data_code: needs a real-code handle, the tracking code's length and a valid prompt tap");
+            return GB200_E_INVALID;
+        }
+    cudaSetDevice(s->device);
+    GB_CUDA(s, cudaMemcpyAsync(t->d_data_code, code, sizeof(float) * code_len, cudaMemcpyHostToDevice, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    t->has_data = true;
+    t->prompt_tap = prompt_tap;
+    return GB200_OK;
+}
+
+static int trk_fill_work(gb200_service* s, const gb200_trk_req& r, int out_index, GbTrkWork* w)
+{
+    gb200_trk* t = r.trk;
+    if (!t || t->s != s || t->code_len == 0 || r.n_samples < 1)
+        {
+            s->set_error("tracking request: handle not initialised (set_local_code_and_taps) or n_samples < 1");
+            return GB200_E_STATE;
+        }
+    if ((uint64_t)r.n_samples >= (1u << 24))
+        {
+            s->set_error("tracking request: n_samples must be < 2^24");
+            return GB200_E_INVALID;
+        }
+    const void* win;
+    int rc = ring_window(s, r.stream_id, r.first_sample_index, (uint64_t)r.n_samples, t->c.item_type, &win);
+    if (rc) return rc;
+    memset(w, 0, sizeof(*w));
+    w->samples = win;
+    w->code = t->d_code;
+    w->data_code = t->has_data ? t->d_data_code : nullptr;
+    w->code_len = t->code_len;
+    w->n = r.n_samples;
+    w->n_taps = t->n_taps;
+    w->prompt_tap = t->prompt_tap;
+    memcpy(w->shifts, t->shifts, sizeof(w->shifts));
+    w->rem_carr = r.rem_carr_phase_rad;
+    w->phase_step = r.phase_step_rad;
+    w->phase_rate = r.phase_rate_step_rad;
+    w->rem_code = r.rem_code_phase_chips;
+    w->code_step = r.code_phase_step_chips;
+    w->code_rate = r.code_phase_rate_step_chips;
+    w->out_index = out_index;
+    {
+        // the reference's float32 NCO constants (cpu_multicorrelator_real_codes.cc:140-149), host libm like the reference
+        const float p0r = cosf(r.rem_carr_phase_rad), p0i = -sinf(r.rem_carr_phase_rad);
+        const float incr = cosf(-r.phase_step_rad), inci = sinf(-r.phase_step_rad);
+        const double inv2pi = 0.15915494309189533576888376337251;
+        w->nco_a0_turns = atan2((double)p0i, (double)p0r) * inv2pi;
+        w->nco_theta_turns = atan2((double)inci, (double)incr) * inv2pi;
+        const double mag = hypot((double)incr, (double)inci);
+        w->nco_mag_delta = (float)(mag - 1.0);
+        w->nco_log_mag = log(mag);
+    }
+    return GB200_OK;
+}
+
+static void trk_group_key(const gb200_trk* t, TrkGroup* g)
+{
+    g->n_taps = t->n_taps;
+    g->item_type = t->c.item_type;
+    g->code_kind = t->c.code_kind;
+    g->has_data = t->has_data;
+    g->high_dyn = t->c.high_dyn != 0;
+}
+
+static bool trk_same_group(const TrkGroup& a, const TrkGroup& b)
+{
+    return a.n_taps == b.n_taps && a.item_type == b.item_type && a.code_kind == b.code_kind && a.has_data == b.has_data && a.high_dyn == b.high_dyn;
+}
+
+// (re)build the work array of a batch from requests; buffers must already be sized for b->n requests
+static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
+{
+    gb200_service* s = b->s;
+    const int n = b->n;
+    // bucket requests by kernel variant, keeping request order inside a bucket
+    b->groups.clear();
+    std::vector<int> gid(n);
+    for (int i = 0; i < n; i++)
+        {
+            if (!reqs[i].trk) return GB200_E_INVALID;
+            TrkGroup k;
+            trk_group_key(reqs[i].trk, &k);
+            int found = -1;
+            for (size_t g = 0; g < b->groups.size(); g++)
+                if (trk_same_group(b->groups[g], k)) found = (int)g;
+            if (found < 0)
+                {
+                    b->groups.push_back(k);
+                    found = (int)b->groups.size() - 1;
+                }
+            gid[i] = found;
+            b->groups[found].count++;
+            b->groups[found].max_n = std::max(b->groups[found].max_n, reqs[i].n_samples);
+        }
+    int off = 0;
+    for (auto& g : b->groups)
+        {
+            g.first = off;
+            off += g.count;
+            g.count = 0;
+        }
+    b->h_work.resize(n);
+    b->order.resize(n);
+    int max_n = 1;
+    for (int i = 0; i < n; i++)
+        {
+            TrkGroup& g = b->groups[gid[i]];
+            const int slot = g.first + g.count++;
+            int rc = trk_fill_work(s, reqs[i], i, &b->h_work[slot]);
+            if (rc) return rc;
+            b->order[slot] = i;
+            max_n = std::max(max_n, reqs[i].n_samples);
+        }
+    // chunk size: 4096 samples per CTA unless that leaves the GPU under two waves
+    long long ctas = 0;
+    b->chunk = 4096;
+    for (int c : {4096, 2048, 1024})
+        {
+            ctas = 0;
+            for (int i = 0; i < n; i++) ctas += (reqs[i].n_samples + c - 1) / c;
+            b->chunk = c;
+            if (ctas >= 4LL * s->sm_count) break;
+        }
+    b->max_chunks = (max_n + b->chunk - 1) / b->chunk;
+    return GB200_OK;
+}
+
+static int trk_batch_alloc(gb200_service* s, int n, int max_chunks_cap, gb200_trk_batch** out)
+{
+    gb200_trk_batch* b = new gb200_trk_batch();
+    b->s = s;
+    b->n = n;
+    cudaError_t e = cudaMalloc(&b->d_work, sizeof(GbTrkWork) * n);
+    if (e == cudaSuccess) e = cudaMalloc(&b->d_out, sizeof(float2) * GB200_OUT_STRIDE * n);
+    if (e == cudaSuccess) e = cudaMalloc(&b->d_partials, sizeof(float2) * GB200_OUT_STRIDE * (size_t)n * max_chunks_cap);
+    if (e == cudaSuccess) e = cudaMalloc(&b->d_counters, sizeof(unsigned) * n);
+    if (e == cudaSuccess) e = cudaMemsetAsync(b->d_counters, 0, sizeof(unsigned) * n, s->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(b->d_out, 0, sizeof(float2) * GB200_OUT_STRIDE * n, s->stream);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&b->h_out, sizeof(float2) * GB200_OUT_STRIDE * n);
+    if (e != cudaSuccess)
+        {
+            s->set_error(std::string("tracking batch allocation: ") + cudaGetErrorString(e));
+            gb200_trk_batch_destroy(b);
+            return GB200_E_CUDA;
+        }
+    *out = b;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_batch_create(gb200_service* s, int n, const gb200_trk_req* reqs, gb200_trk_batch** out)
+{
+    if (!s || n <= 0 || !reqs || !out) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    *out = nullptr;
+    int max_n = 1;
+    for (int i = 0; i < n; i++) max_n = std::max(max_n, reqs[i].n_samples);
+    gb200_trk_batch* b;
+    int rc = trk_batch_alloc(s, n, (max_n + 1023) / 1024, &b);
+    if (rc) return rc;
+    rc = trk_batch_stage(b, reqs);
+    if (rc)
+        {
+            gb200_trk_batch_destroy(b);
+            return rc;
+        }
+    cudaError_t e = cudaMemcpyAsync(b->d_work, b->h_work.data(), sizeof(GbTrkWork) * n, cudaMemcpyHostToDevice, s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    if (e != cudaSuccess)
+        {
+            s->set_error(std::string("tracking batch upload: ") + cudaGetErrorString(e));
+            gb200_trk_batch_destroy(b);
+            return GB200_E_CUDA;
+        }
+    *out = b;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
+{
+    if (!b) return GB200_E_INVALID;
+    gb200_service* s = b->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    int l = 0;
+    for (const auto& g : b->groups)
+        {
+            // every group shares max_chunks (the partial-sum pitch) so request slots stay independent
+            GB_CUDA(s, gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.item_type, g.code_kind,
+                           g.high_dyn, b->d_partials, b->d_counters, b->d_out, b->chunk, s->stream, &l));
+        }
+    s->launches += l;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_batch_fetch(gb200_trk_batch* b, float* outs_iq)
+{
+    if (!b || !outs_iq) return GB200_E_INVALID;
+    gb200_service* s = b->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    GB_CUDA(s, cudaMemcpyAsync(b->h_out, b->d_out, sizeof(float2) * GB200_OUT_STRIDE * b->n, cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    memcpy(outs_iq, b->h_out, sizeof(float2) * GB200_OUT_STRIDE * b->n);
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_batch_destroy(gb200_trk_batch* b)
+{
+    if (!b) return GB200_E_INVALID;
+    gb200_service* s = b->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->stream);
+    if (b->d_work) cudaFree(b->d_work);
+    if (b->d_out) cudaFree(b->d_out);
+    if (b->d_partials) cudaFree(b->d_partials);
+    if (b->d_counters) cudaFree(b->d_counters);
+    if (b->h_out) cudaFreeHost(b->h_out);
+    delete b;
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_trk_req* reqs, float* outs_iq)
+{
+    gb200_trk_batch* b;
+    int rc = gb200_trk_batch_create(s, n, reqs, &b);
+    if (rc) return rc;
+    rc = gb200_trk_batch_launch(b);
+    if (!rc) rc = gb200_trk_batch_fetch(b, outs_iq);
+    gb200_trk_batch_destroy(b);
+    return rc;
+}
+
+extern "C" int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_sample_index, float rem_carr_phase_rad,
+    float phase_step_rad, float phase_rate_step_rad, float rem_code_phase_chips, float code_phase_step_chips,
+    float code_phase_rate_step_chips, int n_samples, float* corr_out_iq)
+{
+    if (!t || !corr_out_iq) return GB200_E_INVALID;
+    gb200_service* s = t->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    gb200_trk_req r;
+    r.trk = t;
+    r.stream_id = stream_id;
+    r.first_sample_index = first_sample_index;
+    r.rem_carr_phase_rad = rem_carr_phase_rad;
+    r.phase_step_rad = phase_step_rad;
+    r.phase_rate_step_rad = phase_rate_step_rad;
+    r.rem_code_phase_chips = rem_code_phase_chips;
+    r.code_phase_step_chips = code_phase_step_chips;
+    r.code_phase_rate_step_chips = code_phase_rate_step_chips;
+    r.n_samples = n_samples;
+    int rc;
+    if (!t->single)
+        {
+            // per-handle resident resources: one request, up to ring_slack samples in 1024-sample chunks
+            rc = trk_batch_alloc(s, 1, (int)((s->ring_slack + 1023) / 1024), &t->single);
+            if (rc) return rc;
+        }
+    gb200_trk_batch* b = t->single;
+    rc = trk_batch_stage(b, &r);
+    if (rc) return rc;
+    GB_CUDA(s, cudaMemcpyAsync(b->d_work, b->h_work.data(), sizeof(GbTrkWork), cudaMemcpyHostToDevice, s->stream));
+    rc = gb200_trk_batch_launch(b);
+    if (rc) return rc;
+    GB_CUDA(s, cudaMemcpyAsync(b->h_out, b->d_out, sizeof(float2) * GB200_OUT_STRIDE, cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    memcpy(corr_out_iq, b->h_out, sizeof(float2) * (t->n_taps + (t->has_data ? 1 : 0)));
+    return GB200_OK;
+}

@@ -1,0 +1,188 @@
+/* libgnss_b200.so -- C ABI of the B200-native GNSS correlator engine.
+ *
+ * This is the drop-in boundary for GNSS-SDR's PCPS acquisition and DLL/PLL(-VEML) tracking
+ * multicorrelator.  Plain C, opaque handles, int status returns (0 = ok, <0 = GB200_E_*; the
+ * library never calls exit() and never throws across this boundary), caller-owned host buffers.
+ * Every entry point cites the reference interface it replaces (paths relative to the
+ * zhufengGNSS/gnss-sdr-1 tree).  There is NO CPU fallback: every compute entry point fails with
+ * GB200_E_NO_DEVICE when no sm_100 device is present.
+ */
+#ifndef GNSS_B200_H
+#define GNSS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GB200_OK 0
+#define GB200_E_INVALID (-1)   /* bad argument / handle */
+#define GB200_E_NO_DEVICE (-2) /* no CUDA device, or not sm_100 */
+#define GB200_E_CUDA (-3)      /* CUDA runtime error, see gb200_last_error() */
+#define GB200_E_RANGE (-4)     /* requested samples are not (or no longer) in the device ring */
+#define GB200_E_STATE (-5)     /* call order violated (e.g. run before set_local_code) */
+#define GB200_E_UNSUPPORTED (-6)
+
+/* sample item types: gr_complex, lv_16sc_t (interleaved int16 I,Q), lv_8sc_t (interleaved int8 I,Q) */
+#define GB200_ITEM_32FC 0
+#define GB200_ITEM_16IC 1
+#define GB200_ITEM_8IC 2
+
+typedef struct gb200_service gb200_service;
+typedef struct gb200_acq gb200_acq;
+typedef struct gb200_trk gb200_trk;
+typedef struct gb200_trk_batch gb200_trk_batch;
+
+/* ------------------------------------------------------------------ service ------------- */
+/* One per process and GPU.  Replaces the per-channel device setup of
+ * cuda_multicorrelator::init_cuda_integrated_resampler (src/algorithms/tracking/libs/cuda_multicorrelator.cu:137-241). */
+typedef struct gb200_service_cfg
+{
+    int device;                 /* CUDA ordinal; -1 = current device */
+    int max_streams;            /* number of sample streams (front-end bands); 0 -> 4 */
+    uint64_t ring_capacity;     /* items kept per stream on the device; 0 -> 1<<24 */
+    uint64_t ring_slack;        /* longest window a single acquisition / correlation may read; 0 -> 1<<21 */
+} gb200_service_cfg;
+
+int gb200_service_create(const gb200_service_cfg* cfg, gb200_service** out);
+int gb200_service_destroy(gb200_service* s);
+const char* gb200_last_error(const gb200_service* s); /* NULL-safe; never NULL */
+const char* gb200_version(void);
+/* the cudaStream_t every launch of this service is issued on (for CUDA-event timing by the caller) */
+void* gb200_service_cuda_stream(gb200_service* s);
+int gb200_service_synchronize(gb200_service* s);
+/* number of kernels launched by this library since creation (bench "gpu_launches") */
+uint64_t gb200_service_launch_count(const gb200_service* s);
+
+/* Hand a block of the conditioned sample stream to the device ONCE for all channels.  Replaces each
+ * block's own read of input_items[0] (pcps_acquisition.cc:995-1034 state 1 buffering;
+ * dll_pll_veml_tracking.cc:1544 general_work input).  `samples` is host memory (pinned or pageable).
+ * Items stay packed in their wire type on the device (int8/int16 are converted in-register by the
+ * kernels exactly as volk_gnsssdr_16ic_convert_32fc.h:63-72 does). */
+int gb200_stream_push(gb200_service* s, int stream_id, const void* samples, size_t n_items, int item_type,
+    uint64_t first_sample_index);
+/* same, `samples` already in device memory (device-to-device copy on the service stream) */
+int gb200_stream_push_device(gb200_service* s, int stream_id, const void* d_samples, size_t n_items, int item_type,
+    uint64_t first_sample_index);
+
+/* ------------------------------------------------------------------ acquisition --------- */
+/* = Acq_Conf (src/algorithms/acquisition/libs/acq_conf.h:39-68) + the setters' values */
+typedef struct gb200_acq_cfg
+{
+    uint32_t sampled_ms;
+    uint32_t ms_per_code;
+    uint32_t samples_per_chip;
+    uint32_t max_dwells;
+    uint32_t doppler_max;
+    uint32_t doppler_step;
+    uint32_t num_doppler_bins_step2;
+    float doppler_step2;
+    int64_t fs_in;
+    float samples_per_ms;
+    float samples_per_code;
+    int bit_transition_flag;
+    int use_CFAR_algorithm_flag;
+    int make_2_steps;
+    int item_type; /* GB200_ITEM_* of the stream it will read */
+    float threshold;
+    int64_t freq_offset_hz; /* GLONASS FDMA d_old_freq, pcps_acquisition.cc:277-293 */
+} gb200_acq_cfg;
+
+typedef struct gb200_acq_result
+{
+    uint32_t code_phase_index; /* indext: arg-max index in the kept row */
+    int32_t doppler_hz;
+    uint32_t doppler_bin;
+    float peak_mag;       /* |.|^2 grid maximum (un-normalised, as d_magnitude_grid) */
+    float input_power;    /* d_input_power */
+    float test_statistic; /* d_test_statistics */
+    int decision;         /* 1 positive (event 1), 0 negative (event 2), 2 need more dwells, 3 step two armed */
+    double acq_delay_samples;  /* Gnss_Synchro::Acq_delay_samples */
+    double acq_doppler_hz;     /* Gnss_Synchro::Acq_doppler_hz */
+    uint64_t acq_samplestamp;  /* Gnss_Synchro::Acq_samplestamp_samples = first_sample_index + consumed */
+} gb200_acq_result;
+
+/* = pcps_acquisition ctor + init() (pcps_acquisition.cc:63-195, 313-370) */
+int gb200_acq_create(gb200_service* s, const gb200_acq_cfg* cfg, gb200_acq** out);
+int gb200_acq_destroy(gb200_acq* a);
+uint32_t gb200_acq_fft_size(const gb200_acq* a);         /* d_fft_size */
+uint32_t gb200_acq_consumed_samples(const gb200_acq* a); /* d_consumed_samples */
+uint32_t gb200_acq_num_doppler_bins(const gb200_acq* a); /* d_num_doppler_bins */
+/* = pcps_acquisition::set_local_code (pcps_acquisition.cc:239-274): zero-pad layout, FFT, conj; cached on device.
+ * `code_iq`: n_items complex floats as the adapter passes them (d_consumed_samples, or d_fft_size/2 with bit_transition). */
+int gb200_acq_set_local_code(gb200_acq* a, const float* code_iq, size_t n_items);
+/* = set_doppler_max / set_doppler_step (pcps_acquisition.h:226-250) + FDMA offset; re-derives the bin grid */
+int gb200_acq_set_doppler(gb200_acq* a, uint32_t doppler_max, uint32_t doppler_step, int64_t freq_offset_hz);
+int gb200_acq_set_threshold(gb200_acq* a, float threshold);
+/* = reset()/set_state(1): clears dwell counter, step-two state and the magnitude grid */
+int gb200_acq_reset(gb200_acq* a);
+/* = acquisition_core (pcps_acquisition.cc:668-930) for one dwell over d_consumed_samples items of
+ * `stream_id` starting at `first_sample_index`. */
+int gb200_acq_run(gb200_acq* a, int stream_id, uint64_t first_sample_index, gb200_acq_result* out);
+/* Many acquisitions (channels / PRNs) over the SAME sample block in one launch sequence: the
+ * Doppler-wiped forward FFTs are computed once and shared by every handle with the same geometry. */
+int gb200_acq_run_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index, gb200_acq_result* out);
+/* split form of run_batch: launch is asynchronous on the service stream, collect blocks */
+int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index);
+int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_result* out);
+/* magnitude grid of the last dwell, num_bins x effective_fft_size floats (dump=true, pcps_acquisition.cc:741-744).
+ * Only valid when the handle keeps a grid: max_dwells > 1, use_CFAR_algorithm_flag == 0, or after gb200_acq_keep_grid(a, 1). */
+int gb200_acq_keep_grid(gb200_acq* a, int keep);
+int gb200_acq_read_grid(gb200_acq* a, float* dst);
+
+/* ------------------------------------------------------------------ tracking ------------ */
+#define GB200_MAX_TAPS 8
+#define GB200_CODE_REAL 0 /* Cpu_Multicorrelator_Real_Codes (float codes)        */
+#define GB200_CODE_CPLX 1 /* Cpu_Multicorrelator (complex-float codes, GLONASS)  */
+
+typedef struct gb200_trk_cfg
+{
+    int n_taps;          /* correlators (3 = E,P,L; 5 = VE,E,P,L,VL) */
+    int max_code_len;    /* longest local code table in samples (1023 ... 20460) */
+    int code_kind;       /* GB200_CODE_* */
+    int high_dyn;        /* set_high_dynamics_resampler(): quadratic NCO terms honoured */
+    int item_type;       /* GB200_ITEM_* of the stream */
+} gb200_trk_cfg;
+
+/* = Cpu_Multicorrelator_Real_Codes::init (src/algorithms/tracking/libs/cpu_multicorrelator_real_codes.cc:62-76) */
+int gb200_trk_create(gb200_service* s, const gb200_trk_cfg* cfg, gb200_trk** out);
+int gb200_trk_destroy(gb200_trk* t);
+/* = set_local_code_and_taps (cpu_multicorrelator_real_codes.cc:79-89).  `code`: code_len floats (REAL) or
+ * code_len complex floats (CPLX); `shifts`: n_taps tap offsets in code-table samples. */
+int gb200_trk_set_local_code_and_taps(gb200_trk* t, const void* code, int code_len, const float* shifts, int n_taps);
+/* pilot tracking: the data-component code correlated at the tap `prompt_tap` with identical NCO
+ * parameters (dll_pll_veml_tracking.cc:900-910, correlator_data_cpu); adds one output after the n_taps. */
+int gb200_trk_set_data_code(gb200_trk* t, const float* code, int code_len, int prompt_tap);
+/* = Carrier_wipeoff_multicorrelator_resampler (cpu_multicorrelator_real_codes.h:55; same argument list).
+ * corr_out_iq: n_taps (+1 with a data code) complex floats. */
+int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_sample_index,
+    float rem_carr_phase_rad, float phase_step_rad, float phase_rate_step_rad,
+    float rem_code_phase_chips, float code_phase_step_chips, float code_phase_rate_step_chips,
+    int n_samples, float* corr_out_iq);
+
+/* One epoch request of one channel, for the batched forms. */
+typedef struct gb200_trk_req
+{
+    gb200_trk* trk;
+    int stream_id;
+    uint64_t first_sample_index;
+    float rem_carr_phase_rad, phase_step_rad, phase_rate_step_rad;
+    float rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips;
+    int n_samples;
+} gb200_trk_req;
+
+/* All requests in ONE launch.  outs: for request i, (n_taps_i + has_data_i) complex floats, packed
+ * in request order at stride GB200_MAX_TAPS+1 complex floats. */
+int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_trk_req* reqs, float* outs_iq);
+/* split form: stage -> launch (asynchronous, repeatable) -> fetch */
+int gb200_trk_batch_create(gb200_service* s, int n, const gb200_trk_req* reqs, gb200_trk_batch** out);
+int gb200_trk_batch_launch(gb200_trk_batch* b);
+int gb200_trk_batch_fetch(gb200_trk_batch* b, float* outs_iq);
+int gb200_trk_batch_destroy(gb200_trk_batch* b);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNSS_B200_H */

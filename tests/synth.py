@@ -1,0 +1,85 @@
+"""Deterministic synthetic GNSS IQ and code-table access for tests and bench.
+
+x[n] = sum_s A_s * c_s((t - tau_s) * Rc * (1 + f_s / f_carrier)) * exp(j (2 pi f_s t + phi_s)) + w[n]
+with w complex white Gaussian (sigma^2 = 1 per component) from numpy PCG64(seed) and
+A_s = sqrt(2 * 10^(CN0/10) / fs).  Code tables come from tests/golden/codes.npz, which was produced by
+the reference's own generators (tests/golden/make_golden.py).
+"""
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+_codes = None
+
+CODE_SHAPES = {
+    "gps_l1_ca": (32, 1023), "gal_e1b_sinboc": (36, 8184), "gal_e1c_sinboc": (36, 8184),
+    "gps_l5i": (32, 10230), "gps_l5q": (32, 10230), "bds_b1i": (33, 2046), "glo_l1_ca": (1, 511),
+}
+# chips per second of the TABLE (E1 tables hold 2 samples per chip: sinBOC(1,1))
+TABLE_RATE = {
+    "gps_l1_ca": 1.023e6, "gal_e1b_sinboc": 2 * 1.023e6, "gal_e1c_sinboc": 2 * 1.023e6,
+    "gps_l5i": 10.23e6, "gps_l5q": 10.23e6, "bds_b1i": 2.046e6, "glo_l1_ca": 0.511e6,
+}
+CARRIER_HZ = {
+    "gps_l1_ca": 1575.42e6, "gal_e1b_sinboc": 1575.42e6, "gal_e1c_sinboc": 1575.42e6,
+    "gps_l5i": 1176.45e6, "gps_l5q": 1176.45e6, "bds_b1i": 1561.098e6, "glo_l1_ca": 1602e6,
+}
+
+
+def code_table(kind, prn):
+    """float32 +-1 table exactly as the reference generator returns it (1 sample/chip; 2/chip for E1 sinBOC)."""
+    global _codes
+    if _codes is None:
+        _codes = np.load(os.path.join(GOLDEN, "codes.npz"))
+    rows, length = CODE_SHAPES[kind]
+    bits = np.unpackbits(_codes[kind])[: rows * length].reshape(rows, length)
+    return (bits[prn - 1].astype(np.float32) * 2.0 - 1.0)
+
+
+def golden_array(name):
+    global _codes
+    if _codes is None:
+        _codes = np.load(os.path.join(GOLDEN, "codes.npz"))
+    return _codes[name]
+
+
+def sampled_code(table, table_rate, fs, n):
+    """set_local_code-style nearest-neighbour sampling used for the local acquisition replica:
+    sample i takes table[floor(i * table_rate / fs) mod L] (double arithmetic; test-side helper)."""
+    idx = np.floor(np.arange(n, dtype=np.float64) * (table_rate / fs)).astype(np.int64) % len(table)
+    return table[idx].astype(np.complex64)
+
+
+def make_iq(fs, n, sats, seed, noise=True):
+    """sats: list of dict(kind, prn, cn0_dbhz, doppler_hz, delay_samples, phase=0.0[, data_kind]).
+    Returns complex64[n]."""
+    rng = np.random.default_rng(seed)
+    if noise:
+        x = rng.standard_normal(n) + 1j * rng.standard_normal(n)
+    else:
+        x = np.zeros(n, np.complex128)
+    t = np.arange(n, dtype=np.float64) / fs
+    for s in sats:
+        tab = code_table(s["kind"], s["prn"]).astype(np.float64)
+        rate = TABLE_RATE[s["kind"]] * (1.0 + s["doppler_hz"] / CARRIER_HZ[s["kind"]])
+        tau = s["delay_samples"] / fs
+        idx = np.floor((t - tau) * rate).astype(np.int64) % len(tab)
+        amp = np.sqrt(2.0 * 10.0 ** (s["cn0_dbhz"] / 10.0) / fs)
+        sig = tab[idx]
+        if "pilot_kind" in s:  # data + pilot on the same carrier (E1B + E1C: e1b - e1c, both BPSK-on-real here)
+            ptab = code_table(s["pilot_kind"], s["prn"]).astype(np.float64)
+            sig = (sig - ptab[idx]) / np.sqrt(2.0)
+        x += amp * sig * np.exp(1j * (2 * np.pi * s["doppler_hz"] * t + s.get("phase", 0.0)))
+    return x.astype(np.complex64)
+
+
+def quantize(x, item):
+    """gr_complex -> interleaved int16 (x * 2^10) or int8 (x * 2^4), saturated."""
+    if item == "16ic":
+        q = np.clip(np.rint(np.stack([x.real, x.imag], -1) * 1024.0), -32768, 32767).astype(np.int16)
+    elif item == "8ic":
+        q = np.clip(np.rint(np.stack([x.real, x.imag], -1) * 16.0), -128, 127).astype(np.int8)
+    else:
+        raise ValueError(item)
+    return np.ascontiguousarray(q.reshape(-1))

@@ -1,0 +1,164 @@
+"""GPU parity: batched multicorrelator (libgnss_b200.so via the C ABI) against the oracle.
+
+Parity metric: per request max_v |gpu_v - oracle_v| <= 1e-4 * max_v |oracle_v|, oracle =
+the reference's _generic protokernels (oracle/gnss_oracle.c is bit-identical to them, see
+test_oracle_cpu.py).  Chip indices must be identical, which the float64 arbiter on the oracle's own
+indices (go_multicorrelator_real_f64) checks far below the 1e-4 budget.
+"""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import synth
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def rel_err(got, want):
+    return float(np.abs(got - want).max() / np.abs(want).max())
+
+
+def test_golden_cases(service, golden_dir):
+    """Known answers produced by the reference's own Cpu_Multicorrelator_Real_Codes (tests/golden/trk_golden.npz)."""
+    import gnss_b200 as gb
+
+    g = np.load(golden_dir + "/trk_golden.npz")
+    codes = [g["gps_code"], g["e1_code"]]
+    for i in range(int(g["n_cases"])):
+        c = {k: g["c%d_%s" % (i, k)] for k in ("code_id", "shifts", "x", "hd", "out_generic", "out_avx", "rem_carr", "phase_step",
+                                                "rem_code", "code_step", "phase_rate", "code_rate")}
+        code = codes[int(c["code_id"])]
+        x = c["x"]
+        service.push(0, x, gb.ITEM_32FC, 0)
+        mc = gb.Multicorrelator(service, len(c["shifts"]), len(code), high_dyn=bool(c["hd"]))
+        mc.set_local_code_and_taps(code, c["shifts"])
+        got = mc.correlate(0, 0, float(c["rem_carr"]), float(c["phase_step"]), float(c["rem_code"]), float(c["code_step"]), len(x),
+                           float(c["phase_rate"]), float(c["code_rate"]))
+        mc.close()
+        e = rel_err(got, c["out_generic"])
+        assert e < TOL, (i, e, got, c["out_generic"])
+        if not bool(c["hd"]):
+            f64 = np.zeros(2 * len(c["shifts"]))
+            ol.oracle().go_multicorrelator_real_f64(np.ascontiguousarray(x).view(np.float32), len(x), code, len(code), c["shifts"], len(c["shifts"]),
+                                                    float(c["rem_carr"]), float(c["phase_step"]), float(c["rem_code"]), float(c["code_step"]), f64)
+            f64 = f64.view(np.complex128)
+            assert np.abs(got - f64).max() / np.abs(f64).max() < 5e-6, (i, got, f64)  # identical chip indices, accurate NCO
+
+
+@pytest.mark.parametrize("item", ["32fc", "16ic", "8ic"])
+def test_batch_random_vs_oracle(service, item):
+    """Many (channel, epoch) requests in one launch: ragged lengths, 1/3/5 taps, data tap, all item types."""
+    import gnss_b200 as gb
+
+    rng = np.random.default_rng(11)
+    n_total = 120000
+    x = (rng.standard_normal(n_total) + 1j * rng.standard_normal(n_total)).astype(np.complex64) * 3.0
+    it = {"32fc": gb.ITEM_32FC, "16ic": gb.ITEM_16IC, "8ic": gb.ITEM_8IC}[item]
+    if item == "32fc":
+        service.push(0, x, it, 1000)
+        xf = x
+    else:
+        q = synth.quantize(x, item)
+        service.push(0, q, it, 1000)
+        xf = (q[0::2].astype(np.float32) + 1j * q[1::2].astype(np.float32)).astype(np.complex64)
+    gps = synth.code_table("gps_l1_ca", 3)
+    e1c = synth.code_table("gal_e1c_sinboc", 4)
+    e1b = synth.code_table("gal_e1b_sinboc", 4)
+    chans = []
+    m = gb.Multicorrelator(service, 3, 1023, item_type=it)
+    m.set_local_code_and_taps(gps, [-0.5, 0.0, 0.5])
+    chans.append((m, gps, None, [-0.5, 0.0, 0.5], 1023 / 4000))
+    m = gb.Multicorrelator(service, 5, 8184, item_type=it)
+    m.set_local_code_and_taps(e1c, [-1.2, -0.3, 0.0, 0.3, 1.2])
+    m.set_data_code(e1b, 2)
+    chans.append((m, e1c, e1b, [-1.2, -0.3, 0.0, 0.3, 1.2], 8184 / 32000))
+    m = gb.Multicorrelator(service, 1, 1023, item_type=it)
+    m.set_local_code_and_taps(gps, [0.0])
+    chans.append((m, gps, None, [0.0], 0.4))
+    m = gb.Multicorrelator(service, 2, 1023, item_type=it)  # generic-tap-count kernel
+    m.set_local_code_and_taps(gps, [-0.25, 0.25])
+    chans.append((m, gps, None, [-0.25, 0.25], 0.7))
+    items, meta = [], []
+    for k in range(60):
+        ci = k % len(chans)
+        m, code, dcode, sh, step = chans[ci]
+        n = int(rng.choice([1, 31, 255, 256, 257, 1000, 4000, 4096, 4097, 9000, 32000, 40001]))
+        first = 1000 + int(rng.integers(0, n_total - n))
+        p = (float(rng.uniform(-3.1, 3.1)), float(rng.uniform(-0.2, 0.2)), float(rng.uniform(-2.0, 2.0)), float(step * (1 + rng.uniform(-1e-5, 1e-5))))
+        items.append((m, 0, first, p[0], p[1], 0.0, p[2], p[3], 0.0, n))
+        meta.append((ci, first, n, p))
+    out = gb.correlate_batch(service, gb.make_reqs(items))
+    worst = 0.0
+    for k, (ci, first, n, p) in enumerate(meta):
+        m, code, dcode, sh, step = chans[ci]
+        seg = xf[first - 1000: first - 1000 + n]
+        want = ol.multicorrelator_real("oracle", seg, code, np.asarray(sh, np.float32), p[0], p[1], p[2], p[3])
+        got = out[k, : len(sh)]
+        scale = np.abs(want).max()
+        if dcode is not None:
+            wd = ol.multicorrelator_real("oracle", seg, dcode, np.asarray([sh[2]], np.float32), p[0], p[1], p[2], p[3])
+            want = np.concatenate([want, wd])
+            got = out[k, : len(sh) + 1]
+            scale = max(scale, np.abs(wd).max())
+        e = float(np.abs(got - want).max() / scale)
+        worst = max(worst, e)
+        assert e < TOL, (k, ci, n, e, got, want)
+    for c in chans:
+        c[0].close()
+    print("worst relative error", worst)
+
+
+def test_complex_codes_and_general_path(service):
+    """GLONASS-style complex code tables (Cpu_Multicorrelator) and the no-window fall-back (step > 1 table sample/sample)."""
+    import gnss_b200 as gb
+
+    rng = np.random.default_rng(5)
+    n = 6000
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    service.push(1, x, gb.ITEM_32FC, 0)
+    code = (rng.choice([-1.0, 1.0], 511) + 1j * rng.choice([-1.0, 1.0], 511)).astype(np.complex64)
+    sh = np.array([-0.5, 0.0, 0.5], np.float32)
+    m = gb.Multicorrelator(service, 3, 511, code_kind=gb.CODE_CPLX)
+    m.set_local_code_and_taps(code, sh)
+    got = m.correlate(1, 0, 0.4, -0.03, 0.6, 511 / 6000.0, n)
+    want = np.zeros(6, np.float32)
+    ol.oracle().go_multicorrelator_cplx(x.view(np.float32), n, code.view(np.float32), 511, sh, 3, 0.4, -0.03, 0.6, np.float32(511 / 6000.0), want)
+    assert rel_err(got, want.view(np.complex64)) < TOL
+    m.close()
+    gps = synth.code_table("gps_l1_ca", 9)
+    m = gb.Multicorrelator(service, 3, 1023)
+    m.set_local_code_and_taps(gps, sh)
+    for step, rem in ((2.5, 0.3), (0.256, -5000.7), (0.256, 123456.5)):  # window too wide / far-away remnants
+        got = m.correlate(1, 0, 0.1, 0.02, rem, step, n)
+        want = ol.multicorrelator_real("oracle", x, gps, sh, 0.1, 0.02, rem, step)
+        assert rel_err(got, want) < TOL, (step, rem)
+    m.close()
+
+
+def test_ring_wraparound_and_errors(service):
+    """Windows that straddle the ring's wrap point are contiguous through the mirror; stale or future samples are refused."""
+    import gnss_b200 as gb
+
+    s = gb.Service(device=0, ring_capacity=10000, ring_slack=5000)
+    try:
+        rng = np.random.default_rng(2)
+        x = (rng.standard_normal(26000) + 1j * rng.standard_normal(26000)).astype(np.complex64)
+        gps = synth.code_table("gps_l1_ca", 1)
+        sh = np.array([-0.5, 0.0, 0.5], np.float32)
+        m = gb.Multicorrelator(s, 3, 1023)
+        m.set_local_code_and_taps(gps, sh)
+        for blk in range(0, 26000, 2000):
+            s.push(0, x[blk: blk + 2000], gb.ITEM_32FC, blk)
+        first = 18500  # positions 8500..12500 -> wraps at 10000
+        got = m.correlate(0, first, 0.0, 0.01, 0.0, 0.25575, 4000)
+        want = ol.multicorrelator_real("oracle", x[first: first + 4000], gps, sh, 0.0, 0.01, 0.0, 0.25575)
+        assert rel_err(got, want) < TOL
+        with pytest.raises(gb.Gb200Error) as ei:
+            m.correlate(0, 100, 0.0, 0.01, 0.0, 0.25575, 4000)  # overwritten long ago
+        assert ei.value.code == -4
+        with pytest.raises(gb.Gb200Error):
+            m.correlate(0, 25000, 0.0, 0.01, 0.0, 0.25575, 4000)  # not pushed yet
+        m.close()
+    finally:
+        s.close()
