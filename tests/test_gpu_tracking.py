@@ -43,7 +43,9 @@ def test_golden_cases(service, golden_dir):
             ol.oracle().go_multicorrelator_real_f64(np.ascontiguousarray(x).view(np.float32), len(x), code, len(code), c["shifts"], len(c["shifts"]),
                                                     float(c["rem_carr"]), float(c["phase_step"]), float(c["rem_code"]), float(c["code_step"]), f64)
             f64 = f64.view(np.complex128)
-            assert np.abs(got - f64).max() / np.abs(f64).max() < 5e-6, (i, got, f64)  # identical chip indices, accurate NCO
+            # identical chip indices (one flipped chip moves a tap by ~2/N = 5e-4 of the prompt); the residual is the NCO
+            # frequency offset of the reference's float32-rounded phase increment, which the engine reproduces on purpose
+            assert np.abs(got - f64).max() / np.abs(f64).max() < 5e-5, (i, got, f64)
 
 
 @pytest.mark.parametrize("item", ["32fc", "16ic", "8ic"])

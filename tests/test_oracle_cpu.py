@@ -36,8 +36,12 @@ def test_multicorrelator_oracle_vs_reference_golden(golden_dir):
             assert np.abs(got - c["out_generic"]).max() <= 2e-6 * np.abs(c["out_generic"]).max(), i
         else:
             assert np.array_equal(got.view(np.float32), c["out_generic"].view(np.float32)), (i, got, c["out_generic"])
-            # the reference's own two protokernels agree only to ~1e-4 of the largest tap
-            assert np.abs(c["out_avx"] - c["out_generic"]).max() <= 1.5e-4 * np.abs(c["out_generic"]).max()
+            # Informational: the reference's own _u_avx protokernels agree with _generic to ~2e-5 of the largest tap on
+            # the GPS cases (NCO rounding), but pick neighbouring chips on the 8184-sample E1 table with +-1.2 shifts
+            # (cases 12-19: up to 2.4e-2 on noise-only input).  _generic is the reference QA's own oracle
+            # (lib/qa_utils.cc) and is what the engine follows.
+            if i < 12:
+                assert np.abs(c["out_avx"] - c["out_generic"]).max() <= 1e-4 * np.abs(c["out_generic"]).max()
         n += 1
     assert n == 24
 
@@ -157,11 +161,15 @@ def test_acquisition_block_logic():
 
 # ------------------------------------------------------------------ loop maths golden (reference scalar libs)
 def test_loop_golden_is_consistent(golden_dir):
-    """tracking_loop_filter_test.cc:117-118: 2nd order, BW 5 Hz, T = 1 ms impulse response {0,0,13.37778,0.0889,...}."""
+    """The reference's own known answers (tracking_loop_filter_test.cc:85,116,147,178, EXPECT_NEAR 1e-4; there the impulse
+    is at index 2, here at index 1) are reproduced by the scalar libs that generated loop_golden.npz."""
     g = np.load(golden_dir + "/loop_golden.npz")
-    assert np.allclose(g["tlf_o2_l0"][:6], [0.0, 0.0, 13.37778, 0.0889, 0.0889, 0.0889], atol=1e-4)
+    assert np.allclose(g["tlf_o1_l1"][:5], [0.0, 0.01, 0.02, 0.02, 0.02], atol=1e-4)
+    assert np.allclose(g["tlf_o2_l0"][:5], [0.0, 13.37778, 0.0889, 0.0889, 0.0889], atol=1e-4)
+    assert np.allclose(g["tlf_o2_l1"][:5], [0.0, 0.006689, 0.013422, 0.013511, 0.013600], atol=1e-4)
     p = g["pts"]
-    assert np.allclose(g["pll_two_quadrant"], np.arctan(p[:, 1].astype(np.float64) / p[:, 0]) / (2 * np.pi), atol=1e-7)
+    assert np.allclose(g["pll_two_quadrant"], np.arctan(p[:, 1] / p[:, 0]).astype(np.float64), atol=1e-6)
+    assert np.allclose(g["pll_four_quadrant"], np.arctan2(p[:, 1], p[:, 0]).astype(np.float64), atol=1e-6)
 
 
 # ------------------------------------------------------------------ the C-ABI library
@@ -199,5 +207,6 @@ def test_product_does_not_touch_oracle():
             if f.endswith((".cu", ".cuh", ".py", ".h", ".cc", ".cpp", "Makefile")):
                 txt = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in txt.replace("no oracle", ""), os.path.join(dirpath, f)
-    out = os.popen("ldd %s 2>/dev/null; nm -D %s | grep -i ' U ' " % (os.path.join(pkg, "libgnss_b200.so"),) * 2).read()
+    so = os.path.join(pkg, "libgnss_b200.so")
+    out = os.popen("ldd %s 2>/dev/null; nm -D %s | grep -i ' U ' " % (so, so)).read()
     assert "gnss_oracle" not in out and "gnss_ref" not in out
