@@ -665,13 +665,14 @@ cudaError_t set_smem(K kernel, size_t bytes)
 size_t gb_acq_col_smem(const GbFftPlan& plan) { return smem_for(plan.N1, plan.tile1); }
 size_t gb_acq_row_smem(const GbFftPlan& plan) { return smem_for(plan.N2, plan.tile2); }
 
-cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches)
+cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt)
 {
     cudaError_t e;
     {
         PlanDev pd = make_plan_dev(plan, true);
         const size_t sm = gb_acq_col_smem(plan);
         dim3 grid((plan.N2 + plan.tile1 - 1) / plan.tile1, n_bins);
+        if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_FWD_COL);
         switch (p.item_type)
             {
             case GB200_ITEM_32FC:
@@ -688,6 +689,7 @@ cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n
                 break;
             default: return cudaErrorInvalidValue;
             }
+        if (kt) gb_kt_end(kt);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }
@@ -696,14 +698,16 @@ cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n
         const size_t sm = gb_acq_row_smem(plan);
         dim3 grid((plan.N1 + plan.tile2 - 1) / plan.tile2, n_bins);
         if ((e = set_smem(gb_acq_fwd_row, sm)) != cudaSuccess) return e;
+        if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_FWD_ROW);
         gb_acq_fwd_row<<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p);
+        if (kt) gb_kt_end(kt);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }
     return cudaSuccess;
 }
 
-cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches)
+cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt)
 {
     cudaError_t e;
     {
@@ -711,7 +715,9 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
         const size_t sm = gb_acq_row_smem(plan);
         dim3 grid((plan.N1 + plan.tile2 - 1) / plan.tile2, p.n_transforms);
         if ((e = set_smem(gb_acq_inv_row, sm)) != cudaSuccess) return e;
+        if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_ROW);
         gb_acq_inv_row<<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p);
+        if (kt) gb_kt_end(kt);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }
@@ -720,7 +726,9 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
         const size_t sm = gb_acq_col_smem(plan);
         dim3 grid((plan.N2 + plan.tile1 - 1) / plan.tile1, p.n_transforms);
         if ((e = set_smem(gb_acq_inv_col, sm)) != cudaSuccess) return e;
+        if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_COL);
         gb_acq_inv_col<<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p);
+        if (kt) gb_kt_end(kt);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }

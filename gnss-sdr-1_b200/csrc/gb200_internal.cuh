@@ -151,8 +151,11 @@ struct GbAcqInvParams
     float* const* tmpbuf;           // per handle d_tmp_buffer image or nullptr: receives the last bin's magnitudes when accumulating (:737)
 };
 
-cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches);
-cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches);
+// per-kernel-class CUDA-event timing hooks (service.cu); `ctx` may be nullptr
+void gb_kt_begin(void* ctx, int kernel_class);
+void gb_kt_end(void* ctx);
+cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt);
+cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt);
 cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches);
 cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type, int N, float* d_power, float* d_mag2_tmp, cudaStream_t st, int* launches);
 // grid-free path: reduce per-CTA maxima -> per handle peak

@@ -46,6 +46,17 @@ struct GbPlanEntry
     float2* d_tw2 = nullptr;
 };
 
+// optional per-kernel-class CUDA-event timing (bench roofline); off by default
+struct GbKernelTiming
+{
+    bool enabled = false;
+    struct Pending { int cls; cudaEvent_t a, b; };
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> pool;
+    double ms[GB200_KCLASS_COUNT] = {0};
+    uint64_t count[GB200_KCLASS_COUNT] = {0};
+};
+
 struct gb200_service
 {
     int device = 0;
@@ -62,6 +73,10 @@ struct gb200_service
     void* h_pinned = nullptr;
     size_t h_pinned_bytes = 0;
     int sm_count = 148;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    GbKernelTiming kt;
+    void* d_flush = nullptr;
+    size_t flush_bytes = 0;
 
     void set_error(const std::string& e) { error = e; g_global_error = e; }
     int scratch(int slot, size_t bytes, void** out)
@@ -167,6 +182,9 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     for (int i = 0; i < 8; i++)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    if (s->d_flush) cudaFree(s->d_flush);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
     cudaStreamDestroy(s->stream);
     delete s;
     return GB200_OK;
@@ -182,6 +200,156 @@ extern "C" int gb200_service_synchronize(gb200_service* s)
 }
 
 extern "C" uint64_t gb200_service_launch_count(const gb200_service* s) { return s ? s->launches : 0; }
+
+extern "C" int gb200_service_timer_start(gb200_service* s)
+{
+    if (!s) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (!s->ev0)
+        {
+            GB_CUDA(s, cudaEventCreate(&s->ev0));
+            GB_CUDA(s, cudaEventCreate(&s->ev1));
+        }
+    GB_CUDA(s, cudaEventRecord(s->ev0, s->stream));
+    return GB200_OK;
+}
+
+extern "C" int gb200_service_timer_stop(gb200_service* s, float* elapsed_ms)
+{
+    if (!s || !elapsed_ms || !s->ev0) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    GB_CUDA(s, cudaEventRecord(s->ev1, s->stream));
+    GB_CUDA(s, cudaEventSynchronize(s->ev1));
+    GB_CUDA(s, cudaEventElapsedTime(elapsed_ms, s->ev0, s->ev1));
+    return GB200_OK;
+}
+
+// ---- per-kernel-class timing ----
+static cudaEvent_t kt_event(gb200_service* s)
+{
+    if (!s->kt.pool.empty())
+        {
+            cudaEvent_t e = s->kt.pool.back();
+            s->kt.pool.pop_back();
+            return e;
+        }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+void gb_kt_begin(void* ctx, int cls)
+{
+    gb200_service* s = (gb200_service*)ctx;
+    if (!s || !s->kt.enabled) return;
+    GbKernelTiming::Pending p;
+    p.cls = cls;
+    p.a = kt_event(s);
+    p.b = kt_event(s);
+    cudaEventRecord(p.a, s->stream);
+    s->kt.pending.push_back(p);
+}
+
+void gb_kt_end(void* ctx)
+{
+    gb200_service* s = (gb200_service*)ctx;
+    if (!s || !s->kt.enabled || s->kt.pending.empty()) return;
+    cudaEventRecord(s->kt.pending.back().b, s->stream);
+}
+
+static void kt_drain(gb200_service* s)
+{
+    for (auto& p : s->kt.pending)
+        {
+            float ms = 0.f;
+            if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess)
+                {
+                    s->kt.ms[p.cls] += ms;
+                    s->kt.count[p.cls]++;
+                }
+            s->kt.pool.push_back(p.a);
+            s->kt.pool.push_back(p.b);
+        }
+    s->kt.pending.clear();
+}
+
+extern "C" int gb200_service_kernel_timing(gb200_service* s, int enable)
+{
+    if (!s) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    kt_drain(s);
+    s->kt.enabled = enable != 0;
+    for (int i = 0; i < GB200_KCLASS_COUNT; i++)
+        {
+            s->kt.ms[i] = 0;
+            s->kt.count[i] = 0;
+        }
+    return GB200_OK;
+}
+
+extern "C" int gb200_service_kernel_stats(gb200_service* s, int kernel_class, double* total_ms, uint64_t* launches)
+{
+    if (!s || kernel_class < 0 || kernel_class >= GB200_KCLASS_COUNT || !total_ms || !launches) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    kt_drain(s);
+    *total_ms = s->kt.ms[kernel_class];
+    *launches = s->kt.count[kernel_class];
+    return GB200_OK;
+}
+
+double gb_fma_peak_launch(float* d_out, int blocks, int iters, cudaStream_t st);
+
+// measured FP32 FMA throughput of this device in TFLOP/s (best of 5 launches, CUDA events)
+extern "C" int gb200_service_measure_fp32(gb200_service* s, double* tflops)
+{
+    if (!s || !tflops) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    const int blocks = s->sm_count * 4;
+    void* d;
+    int rc = s->scratch(7, sizeof(float) * 512 * (size_t)blocks, &d);
+    if (rc) return rc;
+    cudaEvent_t a, b;
+    GB_CUDA(s, cudaEventCreate(&a));
+    GB_CUDA(s, cudaEventCreate(&b));
+    double best = 0;
+    for (int rep = 0; rep < 6; rep++)
+        {
+            GB_CUDA(s, cudaEventRecord(a, s->stream));
+            const double flops = gb_fma_peak_launch((float*)d, blocks, 4096, s->stream);
+            GB_CUDA(s, cudaEventRecord(b, s->stream));
+            GB_CUDA(s, cudaEventSynchronize(b));
+            float ms = 0;
+            GB_CUDA(s, cudaEventElapsedTime(&ms, a, b));
+            if (rep > 0 && ms > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+        }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    s->launches += 6;
+    *tflops = best;
+    return GB200_OK;
+}
+
+extern "C" int gb200_service_flush_l2(gb200_service* s, size_t bytes)
+{
+    if (!s || !bytes) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (bytes > s->flush_bytes)
+        {
+            if (s->d_flush) cudaFree(s->d_flush);
+            s->d_flush = nullptr;
+            s->flush_bytes = 0;
+            GB_CUDA(s, cudaMalloc(&s->d_flush, bytes));
+            s->flush_bytes = bytes;
+        }
+    GB_CUDA(s, cudaMemsetAsync(s->d_flush, 0x5a, bytes, s->stream));
+    return GB200_OK;
+}
 
 // ------------------------------------------------------------------ sample ring
 static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_items, int item_type, uint64_t first, cudaMemcpyKind kind)
@@ -619,7 +787,7 @@ extern "C" int gb200_acq_set_local_code(gb200_acq* a, const float* code_iq, size
     p.colbuf = (float2*)d_col;
     p.spectra = a->d_code_fft;
     int l = 0;
-    GB_CUDA(s, gb_acq_forward(*a->plan, p, 1, false, s->stream, &l));
+    GB_CUDA(s, gb_acq_forward(*a->plan, p, 1, false, s->stream, &l, nullptr));
     GB_CUDA(s, gb_acq_conj(a->d_code_fft, N, s->stream, &l));  // volk_32fc_conjugate_32fc, :273
     s->launches += l;
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
@@ -831,7 +999,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             fp.seg_offsets = (const int*)((char*)d_up + g.off_segoff);
             fp.colbuf = (float2*)d_col;
             fp.spectra = (float2*)d_spec;
-            GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l));
+            GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l, s));
             // input power (CFAR or bit transition, pcps_acquisition.cc:703-709)
             bool want_power = false;
             for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag;
@@ -862,7 +1030,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     ip.accumulate = (g.grid && a0->dwell_counter >= 1) ? 1 : 0;  // this is dwell number dwell_counter+1
                     ip.partial = (GbPeak*)d_part;
                     ip.tmpbuf = (g.grid && !a0->use_cfar) ? (float* const*)((char*)d_up + g.off_tmp) : nullptr;
-                    GB_CUDA(s, gb_acq_inverse(plan, ip, s->stream, &l));
+                    GB_CUDA(s, gb_acq_inverse(plan, ip, s->stream, &l, s));
                 }
             GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
             if (g.grid)
@@ -1371,8 +1539,11 @@ extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
     for (const auto& g : b->groups)
         {
             // every group shares max_chunks (the partial-sum pitch) so request slots stay independent
-            GB_CUDA(s, gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.item_type, g.code_kind,
-                           g.high_dyn, b->d_partials, b->d_counters, b->d_out, b->chunk, s->stream, &l));
+            gb_kt_begin(s, GB200_KCLASS_TRK);
+            cudaError_t e = gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.item_type, g.code_kind,
+                g.high_dyn, b->d_partials, b->d_counters, b->d_out, b->chunk, s->stream, &l);
+            gb_kt_end(s);
+            GB_CUDA(s, e);
         }
     s->launches += l;
     return GB200_OK;

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(HERE, "libgnss_b200.so")
 
 ITEM_32FC, ITEM_16IC, ITEM_8IC = 0, 1, 2
 CODE_REAL, CODE_CPLX = 0, 1
+KCLASS = {"trk": 0, "acq_fwd_col": 1, "acq_fwd_row": 2, "acq_inv_row": 3, "acq_inv_col": 4}
 MAX_TAPS = 8
 OUT_STRIDE = MAX_TAPS + 1
 ITEM_DTYPES = {ITEM_32FC: np.complex64, ITEM_16IC: np.int16, ITEM_8IC: np.int8}
@@ -66,7 +67,9 @@ class TrkReq(C.Structure):
 
 EXPORTS = [
     "gb200_service_create", "gb200_service_destroy", "gb200_last_error", "gb200_version", "gb200_service_cuda_stream",
-    "gb200_service_synchronize", "gb200_service_launch_count", "gb200_stream_push", "gb200_stream_push_device",
+    "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
+    "gb200_service_flush_l2", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
+    "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid",
@@ -97,6 +100,12 @@ def lib():
     L.gb200_service_synchronize.argtypes = [vp]
     L.gb200_service_launch_count.argtypes = [vp]
     L.gb200_service_launch_count.restype = u64
+    L.gb200_service_timer_start.argtypes = [vp]
+    L.gb200_service_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
+    L.gb200_service_flush_l2.argtypes = [vp, C.c_size_t]
+    L.gb200_service_measure_fp32.argtypes = [vp, C.POINTER(C.c_double)]
+    L.gb200_service_kernel_timing.argtypes = [vp, i]
+    L.gb200_service_kernel_stats.argtypes = [vp, i, C.POINTER(C.c_double), C.POINTER(u64)]
     L.gb200_stream_push.argtypes = [vp, i, vp, C.c_size_t, i, u64]
     L.gb200_stream_push_device.argtypes = [vp, i, vp, C.c_size_t, i, u64]
     L.gb200_acq_create.argtypes = [vp, C.POINTER(AcqCfg), C.POINTER(vp)]
@@ -161,6 +170,30 @@ class Service:
 
     def launch_count(self):
         return int(self.L.gb200_service_launch_count(self.h))
+
+    def timer_start(self):
+        self.check(self.L.gb200_service_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self.check(self.L.gb200_service_timer_stop(self.h, C.byref(ms)))
+        return float(ms.value)
+
+    def measure_fp32_tflops(self):
+        v = C.c_double()
+        self.check(self.L.gb200_service_measure_fp32(self.h, C.byref(v)))
+        return float(v.value)
+
+    def kernel_timing(self, enable=True):
+        self.check(self.L.gb200_service_kernel_timing(self.h, int(enable)))
+
+    def kernel_stats(self, kernel_class):
+        ms, n = C.c_double(), C.c_uint64()
+        self.check(self.L.gb200_service_kernel_stats(self.h, kernel_class, C.byref(ms), C.byref(n)))
+        return float(ms.value), int(n.value)
+
+    def flush_l2(self, nbytes=256 << 20):
+        self.check(self.L.gb200_service_flush_l2(self.h, nbytes))
 
     def push(self, stream_id, samples, item_type, first_sample_index):
         """samples: numpy complex64 (32FC) or interleaved int16 / int8 (I,Q,I,Q...)."""

@@ -55,6 +55,25 @@ void* gb200_service_cuda_stream(gb200_service* s);
 int gb200_service_synchronize(gb200_service* s);
 /* number of kernels launched by this library since creation (bench "gpu_launches") */
 uint64_t gb200_service_launch_count(const gb200_service* s);
+/* CUDA-event stopwatch on the service stream: start records an event, stop records another, waits for it
+ * and returns the device time between the two in milliseconds (what a profiler-free bench must use). */
+int gb200_service_timer_start(gb200_service* s);
+int gb200_service_timer_stop(gb200_service* s, float* elapsed_ms);
+/* Optional per-kernel-class device timing (CUDA events around each launch of that class), for roofline reports.
+ * kernel_timing(s, 1) zeroes and enables the accumulators; kernel_stats returns total ms and launch count. */
+#define GB200_KCLASS_TRK 0         /* batched multicorrelator */
+#define GB200_KCLASS_ACQ_FWD_COL 1 /* wipe-off + column DFT + twiddle */
+#define GB200_KCLASS_ACQ_FWD_ROW 2 /* row DFT -> spectra */
+#define GB200_KCLASS_ACQ_INV_ROW 3 /* x conj(code DFT) + row inverse DFT + twiddle */
+#define GB200_KCLASS_ACQ_INV_COL 4 /* column inverse DFT + |.|^2 + arg-max */
+#define GB200_KCLASS_COUNT 5
+int gb200_service_kernel_timing(gb200_service* s, int enable);
+int gb200_service_kernel_stats(gb200_service* s, int kernel_class, double* total_ms, uint64_t* launches);
+/* FP32 FMA throughput of this device measured with a register-resident FMA kernel (TFLOP/s, 2 flops per FMA):
+ * the roofline denominator of the multicorrelator, which is FP32-bound, not HBM- or tensor-bound */
+int gb200_service_measure_fp32(gb200_service* s, double* tflops);
+/* write `bytes` of device memory on the service stream (L2 flush between timed iterations) */
+int gb200_service_flush_l2(gb200_service* s, size_t bytes);
 
 /* Hand a block of the conditioned sample stream to the device ONCE for all channels.  Replaces each
  * block's own read of input_items[0] (pcps_acquisition.cc:995-1034 state 1 buffering;

@@ -165,7 +165,7 @@ void gbref_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float acq_d
 // ---- timed CPU baseline: the shape of cpu_multicorrelator_real_codes_test.cc:133-163, but with the
 //      block's default kernel pair (standard resampler + standard rotator, dll_pll_veml_tracking.cc:419) ----
 double gbref_bench_multicorrelator_real(const float* sig_in_iq, int n_samples, const float* code, int code_len,
-    const float* shifts, int n_taps, int n_threads, int iters_per_thread, int avx)
+    const float* shifts, int n_taps, int n_threads, int iters_per_thread, int avx, const float* data_code)
 {
     gb_ref_volk_arch = avx;
     std::vector<std::thread> th;
@@ -180,13 +180,31 @@ double gbref_bench_multicorrelator_real(const float* sig_in_iq, int n_samples, c
             mc.set_high_dynamics_resampler(false);
             mc.set_local_code_and_taps(code_len, code, sh.data());
             mc.set_input_output_vectors(out.data(), reinterpret_cast<const std::complex<float>*>(sig_in_iq));
+            // pilot tracking: second 1-tap instance on the data code with identical NCO parameters
+            // (correlator_data_cpu, dll_pll_veml_tracking.cc:900-910)
+            Cpu_Multicorrelator_Real_Codes md;
+            float dshift[1] = {shifts[n_taps / 2]};
+            std::complex<float> dout[1];
+            if (data_code)
+                {
+                    md.init(2 * n_samples, 1);
+                    md.set_high_dynamics_resampler(false);
+                    md.set_local_code_and_taps(code_len, data_code, dshift);
+                    md.set_input_output_vectors(dout, reinterpret_cast<const std::complex<float>*>(sig_in_iq));
+                }
             float step = float(code_len) / float(n_samples);
             for (int i = 0; i < iters_per_thread; i++)
                 {
                     mc.Carrier_wipeoff_multicorrelator_resampler(0.1f * float(i % 7), 0.0123f + 1e-4f * float(t), 0.0f, 0.25f * float(i % 3), step, 0.0f, n_samples);
                     sink[t] += out[n_taps / 2].real();
+                    if (data_code)
+                        {
+                            md.Carrier_wipeoff_multicorrelator_resampler(0.1f * float(i % 7), 0.0123f + 1e-4f * float(t), 0.0f, 0.25f * float(i % 3), step, 0.0f, n_samples);
+                            sink[t] += dout[0].real();
+                        }
                 }
             mc.free();
+            if (data_code) md.free();
         });
     for (auto& x : th) x.join();
     auto t1 = std::chrono::steady_clock::now();
