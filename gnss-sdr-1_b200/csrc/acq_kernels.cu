@@ -128,52 +128,59 @@ __device__ __forceinline__ void bfly(float2* v)
     if (R == 8) bfly8<SIGN>(v);
 }
 
-// One Stockham pass of radix R over a batch of `nb` sub-transforms of length M.
+// One Stockham pass of radix R over a tile of TILE = 2^LOGT sub-transforms of length M (all TILE columns are
+// always computed; ragged tiles are zero-filled on load and masked on store).
 // tw[i] = W_M^i (forward sign); the pass twiddle for input r of butterfly position k is W_M^(r*k*M/(Ns*R)).
-template <int SIGN, int R>
-__device__ __forceinline__ void radix_pass(const float2* __restrict__ x, float2* __restrict__ y, int M, int nb, int pitch,
-    int Ns, const float2* __restrict__ tw)
+// k = j mod Ns through a multiply-high by magic = ceil(2^32 / Ns) (exact for j, Ns < 65536).
+template <int SIGN, int R, int LOGT>
+__device__ __forceinline__ void radix_pass(const float2* __restrict__ x, float2* __restrict__ y, int M, int Ns, unsigned magic,
+    const float2* __restrict__ tw)
 {
+    constexpr int TILE = 1 << LOGT;
+    constexpr int PITCH = TILE + 1;
     const int nbf = M / R;
     const int tstride = M / (Ns * R);
-    const int total = nbf * nb;
+    const int total = nbf << LOGT;
     for (int idx = threadIdx.x; idx < total; idx += blockDim.x)
         {
-            const int j = idx / nb;
-            const int b = idx - j * nb;
-            const int k = j % Ns;
+            const int j = idx >> LOGT;
+            const int b = idx & (TILE - 1);
             float2 v[R];
 #pragma unroll
-            for (int r = 0; r < R; r++) v[r] = x[(j + r * nbf) * pitch + b];
+            for (int r = 0; r < R; r++) v[r] = x[(j + r * nbf) * PITCH + b];
+            int k = 0;
             if (Ns > 1)
                 {
+                    k = j - (int)__umulhi((unsigned)j, magic) * Ns;
+                    const int kt = k * tstride;
 #pragma unroll
                     for (int r = 1; r < R; r++)
                         {
-                            const float2 w = tw[r * k * tstride];
+                            const float2 w = tw[r * kt];
                             v[r] = SIGN > 0 ? cmul_conj(v[r], w) : cmul(v[r], w);
                         }
                 }
             bfly<SIGN, R>(v);
             const int j0 = (j - k) * R + k;
 #pragma unroll
-            for (int r = 0; r < R; r++) y[(j0 + r * Ns) * pitch + b] = v[r];
+            for (int r = 0; r < R; r++) y[(j0 + r * Ns) * PITCH + b] = v[r];
         }
 }
 
 // generic odd-prime radix (naive O(R^2) butterfly); R <= GB200_MAX_GENERIC_RADIX
-template <int SIGN>
-__device__ void radix_pass_generic(const float2* __restrict__ x, float2* __restrict__ y, int M, int nb, int pitch, int Ns,
-    int R, const float2* __restrict__ tw)
+template <int SIGN, int LOGT>
+__device__ void radix_pass_generic(const float2* __restrict__ x, float2* __restrict__ y, int M, int Ns, int R, const float2* __restrict__ tw)
 {
+    constexpr int TILE = 1 << LOGT;
+    constexpr int PITCH = TILE + 1;
     const int nbf = M / R;
     const int tstride = M / (Ns * R);
     const int rstride = M / R;
-    const int total = nbf * nb;
+    const int total = nbf << LOGT;
     for (int idx = threadIdx.x; idx < total; idx += blockDim.x)
         {
-            const int j = idx / nb;
-            const int b = idx - j * nb;
+            const int j = idx >> LOGT;
+            const int b = idx & (TILE - 1);
             const int k = j % Ns;
             const int j0 = (j - k) * R + k;
             for (int q = 0; q < R; q++)
@@ -184,32 +191,44 @@ __device__ void radix_pass_generic(const float2* __restrict__ x, float2* __restr
                             // combined twiddle exponent: pass twiddle r*k*tstride + butterfly r*q*(M/R), mod M
                             const int e = (int)(((long long)r * k * tstride + (long long)((r * q) % R) * rstride) % M);
                             const float2 w = tw[e];
-                            const float2 xv = x[(j + r * nbf) * pitch + b];
+                            const float2 xv = x[(j + r * nbf) * PITCH + b];
                             const float2 p = SIGN > 0 ? cmul_conj(xv, w) : cmul(xv, w);
                             acc.x += p.x;
                             acc.y += p.y;
                         }
-                    y[(j0 + q * Ns) * pitch + b] = acc;
+                    y[(j0 + q * Ns) * PITCH + b] = acc;
                 }
         }
 }
 
+struct PlanDev  // by-value kernel argument
+{
+    int N, N1, N2, nrad, M;
+    int rad[GB200_MAX_RADIX_PASSES];
+    unsigned magic[GB200_MAX_RADIX_PASSES];  // ceil(2^32 / Ns) of each pass
+    const float2* tw;    // W_M^i, i < M
+    const float2* twN;   // W_N^i, i < max(N1, N2) * 16 (forward sign)
+    float two_over_N;
+};
+
 // Full sub-transform: runs all radix passes; returns the buffer holding the result.
-template <int SIGN>
-__device__ float2* block_fft(float2* a, float2* b, int M, int nb, int pitch, const int* rad, int nrad, const float2* tw)
+template <int SIGN, int LOGT>
+__device__ float2* block_fft(float2* a, float2* b, const PlanDev& pl, const float2* tw)
 {
     int Ns = 1;
-    for (int p = 0; p < nrad; p++)
+    const int M = pl.M;
+    for (int p = 0; p < pl.nrad; p++)
         {
-            const int R = rad[p];
+            const int R = pl.rad[p];
+            const unsigned mg = pl.magic[p];
             switch (R)
                 {
-                case 2: radix_pass<SIGN, 2>(a, b, M, nb, pitch, Ns, tw); break;
-                case 3: radix_pass<SIGN, 3>(a, b, M, nb, pitch, Ns, tw); break;
-                case 4: radix_pass<SIGN, 4>(a, b, M, nb, pitch, Ns, tw); break;
-                case 5: radix_pass<SIGN, 5>(a, b, M, nb, pitch, Ns, tw); break;
-                case 8: radix_pass<SIGN, 8>(a, b, M, nb, pitch, Ns, tw); break;
-                default: radix_pass_generic<SIGN>(a, b, M, nb, pitch, Ns, R, tw); break;
+                case 2: radix_pass<SIGN, 2, LOGT>(a, b, M, Ns, mg, tw); break;
+                case 3: radix_pass<SIGN, 3, LOGT>(a, b, M, Ns, mg, tw); break;
+                case 4: radix_pass<SIGN, 4, LOGT>(a, b, M, Ns, mg, tw); break;
+                case 5: radix_pass<SIGN, 5, LOGT>(a, b, M, Ns, mg, tw); break;
+                case 8: radix_pass<SIGN, 8, LOGT>(a, b, M, Ns, mg, tw); break;
+                default: radix_pass_generic<SIGN, LOGT>(a, b, M, Ns, R, tw); break;
                 }
             __syncthreads();
             float2* t = a;
@@ -220,36 +239,48 @@ __device__ float2* block_fft(float2* a, float2* b, int M, int nb, int pitch, con
     return a;
 }
 
+// shared-memory carve-up common to the four kernels: two [M][TILE+1] buffers, W_M table, per-CTA W_N^(m*base) table
+template <int LOGT>
+__device__ __forceinline__ void carve(float2* smem, int M, float2*& bufA, float2*& bufB, float2*& tw, float2*& twA)
+{
+    constexpr int PITCH = (1 << LOGT) + 1;
+    bufA = smem;
+    bufB = bufA + (size_t)M * PITCH;
+    tw = bufB + (size_t)M * PITCH;
+    twA = tw + M;
+}
+
+// twA[m] = W_N^(m * base) (forward sign), m < M: the part of the four-step twiddle W_N^(n2 k1) that is common to the tile
+__device__ __forceinline__ void fill_twA(float2* twA, int M, int base, const PlanDev& pl)
+{
+    for (int m = threadIdx.x; m < M; m += blockDim.x)
+        {
+            const unsigned e = (unsigned)(((unsigned long long)(unsigned)m * (unsigned)base) % (unsigned)pl.N);
+            twA[m] = twiddle_big<-1>(e, pl.N, pl.two_over_N);
+        }
+}
+
 }  // namespace
 
 namespace
 {
 
-struct PlanDev  // by-value kernel argument
-{
-    int N, N1, N2, nrad, M, tile;
-    int rad[GB200_MAX_RADIX_PASSES];
-    const float2* tw;
-    float two_over_N;
-};
-
 // ---------------------------------------------------------------------------------------------
 // Column kernel, forward: x[N2*n1 + n2] * wipeoff -> DFT over n1 (length N1) -> * W_N^(n2 k1) -> colbuf[k1][n2]
-// grid = (ceil(N2 / tile), bins)
-template <int ITEM>
+// grid = (ceil(N2 / TILE), bins)
+template <int ITEM, int LOGT>
 __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     gb_acq_fwd_col(PlanDev pl, GbAcqFwdParams p, int wipeoff)
 {
+    constexpr int TILE = 1 << LOGT;
+    constexpr int PITCH = TILE + 1;
     extern __shared__ __align__(16) float2 smem[];
     const int M = pl.N1, N2 = pl.N2;
-    const int pitch = pl.tile + 1;
-    float2* bufA = smem;
-    float2* bufB = smem + (size_t)M * pitch;
-    float2* tw = bufB + (size_t)M * pitch;
+    float2 *bufA, *bufB, *tw, *twA;
+    carve<LOGT>(smem, M, bufA, bufB, tw, twA);
     for (int i = threadIdx.x; i < M; i += blockDim.x) tw[i] = __ldg(pl.tw + i);
-
-    const int c0 = blockIdx.x * pl.tile;
-    const int nb = min(pl.tile, N2 - c0);
+    const int c0 = blockIdx.x * TILE;
+    fill_twA(twA, M, c0, pl);
     const int bin = blockIdx.y;
     const GbWipeSeg* segs = nullptr;
     int nseg = 0;
@@ -259,13 +290,14 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
             nseg = __ldg(p.seg_offsets + bin + 1) - o0;
             segs = p.segs + o0;
         }
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
+    for (int idx = threadIdx.x; idx < (M << LOGT); idx += blockDim.x)
         {
-            const int n1 = idx / nb;
-            const int b = idx - n1 * nb;
-            const int n = N2 * n1 + c0 + b;
+            const int n1 = idx >> LOGT;
+            const int b = idx & (TILE - 1);
+            const int n2 = c0 + b;
+            const int n = N2 * n1 + n2;
             float2 x = make_float2(0.f, 0.f);
-            if (n < p.consumed)
+            if (n2 < N2 && n < p.consumed)
                 {
                     x = gb_load_item<ITEM>(p.samples, (size_t)n);
                     if (wipeoff)
@@ -287,87 +319,127 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
                             x = cmul(x, make_float2(c, s));
                         }
                 }
-            bufA[n1 * pitch + b] = x;
+            bufA[n1 * PITCH + b] = x;
         }
     __syncthreads();
-    float2* res = block_fft<-1>(bufA, bufB, M, nb, pitch, pl.rad, pl.nrad, tw);
+    float2* res = block_fft<-1, LOGT>(bufA, bufB, pl, tw);
     float2* dst = p.colbuf + (size_t)bin * pl.N;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
+    for (int idx = threadIdx.x; idx < (M << LOGT); idx += blockDim.x)
         {
-            const int k1 = idx / nb;
-            const int b = idx - k1 * nb;
+            const int k1 = idx >> LOGT;
+            const int b = idx & (TILE - 1);
             const int n2 = c0 + b;
-            const unsigned e = (unsigned)(((unsigned long long)n2 * (unsigned)k1) % (unsigned)pl.N);
-            dst[(size_t)k1 * N2 + n2] = cmul(res[k1 * pitch + b], twiddle_big<-1>(e, pl.N, pl.two_over_N));
+            if (n2 < N2)
+                {
+                    const float2 w = cmul(twA[k1], __ldg(pl.twN + k1 * b));  // W_N^(k1 c0) * W_N^(k1 b)
+                    dst[(size_t)k1 * N2 + n2] = cmul(res[k1 * PITCH + b], w);
+                }
         }
 }
 
 // Row kernel, forward: colbuf[k1][n2] -> DFT over n2 (length N2) -> spectra[k1][k2]
-// grid = (ceil(N1 / tile), bins)
+// grid = (ceil(N1 / TILE), bins)
+template <int LOGT>
 __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     gb_acq_fwd_row(PlanDev pl, GbAcqFwdParams p)
 {
+    constexpr int TILE = 1 << LOGT;
+    constexpr int PITCH = TILE + 1;
     extern __shared__ __align__(16) float2 smem[];
     const int M = pl.N2, N1 = pl.N1;
-    const int pitch = pl.tile + 1;
-    float2* bufA = smem;
-    float2* bufB = smem + (size_t)M * pitch;
-    float2* tw = bufB + (size_t)M * pitch;
+    float2 *bufA, *bufB, *tw, *twA;
+    carve<LOGT>(smem, M, bufA, bufB, tw, twA);
     for (int i = threadIdx.x; i < M; i += blockDim.x) tw[i] = __ldg(pl.tw + i);
-    const int r0 = blockIdx.x * pl.tile;
-    const int nb = min(pl.tile, N1 - r0);
+    const int r0 = blockIdx.x * TILE;
+    const int nb = min(TILE, N1 - r0);
     const float2* src = p.colbuf + (size_t)blockIdx.y * pl.N + (size_t)r0 * M;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
-        {
-            const int b = idx / M;
-            const int m = idx - b * M;
-            bufA[m * pitch + b] = src[idx];
-        }
+    const int db = (int)blockDim.x / M, dm = (int)blockDim.x % M;
+    {
+        int b = threadIdx.x / M, m = threadIdx.x - b * M;
+        for (int idx = threadIdx.x; idx < M * TILE; idx += blockDim.x)
+            {
+                bufA[m * PITCH + b] = b < nb ? src[idx] : make_float2(0.f, 0.f);
+                m += dm;
+                b += db;
+                if (m >= M)
+                    {
+                        m -= M;
+                        b++;
+                    }
+            }
+    }
     __syncthreads();
-    float2* res = block_fft<-1>(bufA, bufB, M, nb, pitch, pl.rad, pl.nrad, tw);
+    float2* res = block_fft<-1, LOGT>(bufA, bufB, pl, tw);
     float2* dst = p.spectra + (size_t)blockIdx.y * pl.N + (size_t)r0 * M;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
-        {
-            const int b = idx / M;
-            const int m = idx - b * M;
-            dst[idx] = res[m * pitch + b];
-        }
+    {
+        int b = threadIdx.x / M, m = threadIdx.x - b * M;
+        for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
+            {
+                dst[idx] = res[m * PITCH + b];
+                m += dm;
+                b += db;
+                if (m >= M)
+                    {
+                        m -= M;
+                        b++;
+                    }
+            }
+    }
 }
 
 // Row kernel, inverse: spectra[bin][k1][k2] * codefft[handle][k1][k2] -> inverse DFT over k2 (length N2)
-// -> * W_N^-(n2 k1) -> rowbuf[t][k1][n2].      grid = (ceil(N1 / tile), transforms in chunk)
+// -> * W_N^-(n2 k1) -> rowbuf[t][k1][n2].      grid = (ceil(N1 / TILE), transforms in chunk)
+template <int LOGT>
 __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     gb_acq_inv_row(PlanDev pl, GbAcqInvParams p)
 {
+    constexpr int TILE = 1 << LOGT;
+    constexpr int PITCH = TILE + 1;
     extern __shared__ __align__(16) float2 smem[];
     const int M = pl.N2, N1 = pl.N1;
-    const int pitch = pl.tile + 1;
-    float2* bufA = smem;
-    float2* bufB = smem + (size_t)M * pitch;
-    float2* tw = bufB + (size_t)M * pitch;
+    float2 *bufA, *bufB, *tw, *twA;
+    carve<LOGT>(smem, M, bufA, bufB, tw, twA);
     for (int i = threadIdx.x; i < M; i += blockDim.x) tw[i] = __ldg(pl.tw + i);
-    const int r0 = blockIdx.x * pl.tile;
-    const int nb = min(pl.tile, N1 - r0);
+    const int r0 = blockIdx.x * TILE;
+    const int nb = min(TILE, N1 - r0);
+    fill_twA(twA, M, r0, pl);
     const int t = p.first_transform + blockIdx.y;
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
     const float2* xs = p.spectra + (size_t)bin * pl.N + (size_t)r0 * M;
     const float2* cs = p.code_fft[handle] + (size_t)r0 * M;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
-        {
-            const int b = idx / M;
-            const int m = idx - b * M;
-            bufA[m * pitch + b] = cmul(__ldg(xs + idx), __ldg(cs + idx));
-        }
+    const int db = (int)blockDim.x / M, dm = (int)blockDim.x % M;
+    {
+        int b = threadIdx.x / M, m = threadIdx.x - b * M;
+        for (int idx = threadIdx.x; idx < M * TILE; idx += blockDim.x)
+            {
+                bufA[m * PITCH + b] = b < nb ? cmul(__ldg(xs + idx), __ldg(cs + idx)) : make_float2(0.f, 0.f);
+                m += dm;
+                b += db;
+                if (m >= M)
+                    {
+                        m -= M;
+                        b++;
+                    }
+            }
+    }
     __syncthreads();
-    float2* res = block_fft<+1>(bufA, bufB, M, nb, pitch, pl.rad, pl.nrad, tw);
+    float2* res = block_fft<+1, LOGT>(bufA, bufB, pl, tw);
     float2* dst = p.rowbuf + (size_t)blockIdx.y * pl.N + (size_t)r0 * M;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
-        {
-            const int b = idx / M;
-            const int n2 = idx - b * M;
-            const unsigned e = (unsigned)(((unsigned long long)n2 * (unsigned)(r0 + b)) % (unsigned)pl.N);
-            dst[idx] = cmul(res[n2 * pitch + b], twiddle_big<+1>(e, pl.N, pl.two_over_N));
-        }
+    {
+        int b = threadIdx.x / M, m = threadIdx.x - b * M;
+        for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
+            {
+                const float2 w = cmul(twA[m], __ldg(pl.twN + m * b));  // W_N^(n2 r0) * W_N^(n2 b); the inverse needs its conjugate
+                dst[idx] = cmul_conj(res[m * PITCH + b], w);
+                m += dm;
+                b += db;
+                if (m >= M)
+                    {
+                        m -= M;
+                        b++;
+                    }
+            }
+    }
 }
 
 __device__ __forceinline__ bool peak_better(float m, unsigned i, float bm, unsigned bi)
@@ -376,43 +448,43 @@ __device__ __forceinline__ bool peak_better(float m, unsigned i, float bm, unsig
 }
 
 // Column kernel, inverse: rowbuf[t][k1][n2] -> inverse DFT over k1 (length N1) -> y[N2*n1 + n2] -> |y|^2
-// -> either per-CTA (max, first index) or the magnitude grid.   grid = (ceil(N2 / tile), transforms in chunk)
+// -> either per-CTA (max, first index) or the magnitude grid.   grid = (ceil(N2 / TILE), transforms in chunk)
+template <int LOGT>
 __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     gb_acq_inv_col(PlanDev pl, GbAcqInvParams p)
 {
+    constexpr int TILE = 1 << LOGT;
+    constexpr int PITCH = TILE + 1;
     extern __shared__ __align__(16) float2 smem[];
     __shared__ float s_mag[GB200_ACQ_THREADS / 32];
     __shared__ unsigned s_idx[GB200_ACQ_THREADS / 32];
     const int M = pl.N1, N2 = pl.N2;
-    const int pitch = pl.tile + 1;
-    float2* bufA = smem;
-    float2* bufB = smem + (size_t)M * pitch;
-    float2* tw = bufB + (size_t)M * pitch;
+    float2 *bufA, *bufB, *tw, *twA;
+    carve<LOGT>(smem, M, bufA, bufB, tw, twA);
     for (int i = threadIdx.x; i < M; i += blockDim.x) tw[i] = __ldg(pl.tw + i);
-    const int c0 = blockIdx.x * pl.tile;
-    const int nb = min(pl.tile, N2 - c0);
+    const int c0 = blockIdx.x * TILE;
     const float2* src = p.rowbuf + (size_t)blockIdx.y * pl.N;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
+    for (int idx = threadIdx.x; idx < (M << LOGT); idx += blockDim.x)
         {
-            const int k1 = idx / nb;
-            const int b = idx - k1 * nb;
-            bufA[k1 * pitch + b] = src[(size_t)k1 * N2 + c0 + b];
+            const int k1 = idx >> LOGT;
+            const int b = idx & (TILE - 1);
+            bufA[k1 * PITCH + b] = (c0 + b < N2) ? src[(size_t)k1 * N2 + c0 + b] : make_float2(0.f, 0.f);
         }
     __syncthreads();
-    float2* res = block_fft<+1>(bufA, bufB, M, nb, pitch, pl.rad, pl.nrad, tw);
+    float2* res = block_fft<+1, LOGT>(bufA, bufB, pl, tw);
 
     const int t = p.first_transform + blockIdx.y;
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
     float* grid = p.grid ? p.grid[handle] : nullptr;
     float best = -1.0f;
     unsigned best_i = 0xffffffffu;
-    for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
+    for (int idx = threadIdx.x; idx < (M << LOGT); idx += blockDim.x)
         {
-            const int n1 = idx / nb;
-            const int b = idx - n1 * nb;
+            const int n1 = idx >> LOGT;
+            const int b = idx & (TILE - 1);
             const int n = N2 * n1 + c0 + b - p.keep_offset;
-            if (n < 0 || n >= p.keep_len) continue;
-            const float2 y = res[n1 * pitch + b];
+            if (c0 + b >= N2 || n < 0 || n >= p.keep_len) continue;
+            const float2 y = res[n1 * PITCH + b];
             const float mag = __fadd_rn(__fmul_rn(y.x, y.x), __fmul_rn(y.y, y.y));  // volk_32fc_magnitude_squared_32f
             if (grid)
                 {
@@ -644,20 +716,53 @@ PlanDev make_plan_dev(const GbFftPlan& plan, bool columns)
     d.N2 = plan.N2;
     d.M = columns ? plan.N1 : plan.N2;
     d.nrad = columns ? plan.nrad1 : plan.nrad2;
-    d.tile = columns ? plan.tile1 : plan.tile2;
-    for (int i = 0; i < GB200_MAX_RADIX_PASSES; i++) d.rad[i] = columns ? plan.rad1[i] : plan.rad2[i];
+    int Ns = 1;
+    for (int i = 0; i < GB200_MAX_RADIX_PASSES; i++)
+        {
+            d.rad[i] = columns ? plan.rad1[i] : plan.rad2[i];
+            d.magic[i] = Ns > 1 ? (unsigned)((0x100000000ull + (unsigned)Ns - 1) / (unsigned)Ns) : 0u;
+            if (i < d.nrad) Ns *= d.rad[i];
+        }
     d.tw = columns ? plan.tw1 : plan.tw2;
+    d.twN = plan.twN;
     d.two_over_N = (float)(2.0 / (double)plan.N);
     return d;
 }
 
-size_t smem_for(int M, int tile) { return ((size_t)2 * M * (tile + 1) + M) * sizeof(float2); }
+// two [M][tile+1] buffers + W_M table + per-CTA W_N^(m*base) table
+size_t smem_for(int M, int tile) { return ((size_t)2 * M * (tile + 1) + 2 * (size_t)M) * sizeof(float2); }
+
+int log2_tile(int tile)
+{
+    int l = 0;
+    while ((1 << l) < tile) l++;
+    return l;
+}
 
 template <typename K>
 cudaError_t set_smem(K kernel, size_t bytes)
 {
     if (bytes > 48 * 1024) return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     return cudaSuccess;
+}
+
+// launch KERNEL<..., LOGT> for the run-time tile size
+#define GB_TILE_DISPATCH(LOGT_VALUE, ...)      \
+    switch (LOGT_VALUE)                        \
+        {                                      \
+        case 4: { constexpr int LT = 4; __VA_ARGS__; } break; \
+        case 3: { constexpr int LT = 3; __VA_ARGS__; } break; \
+        case 2: { constexpr int LT = 2; __VA_ARGS__; } break; \
+        case 1: { constexpr int LT = 1; __VA_ARGS__; } break; \
+        default: { constexpr int LT = 0; __VA_ARGS__; } break; \
+        }
+
+template <int ITEM>
+cudaError_t launch_fwd_col(int logt, dim3 grid, size_t sm, cudaStream_t st, const PlanDev& pd, const GbAcqFwdParams& p, int wipeoff)
+{
+    cudaError_t e = cudaSuccess;
+    GB_TILE_DISPATCH(logt, e = set_smem(gb_acq_fwd_col<ITEM, LT>, sm); if (e == cudaSuccess) gb_acq_fwd_col<ITEM, LT><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p, wipeoff))
+    return e;
 }
 
 }  // namespace
@@ -671,36 +776,30 @@ cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n
     {
         PlanDev pd = make_plan_dev(plan, true);
         const size_t sm = gb_acq_col_smem(plan);
+        const int logt = log2_tile(plan.tile1);
         dim3 grid((plan.N2 + plan.tile1 - 1) / plan.tile1, n_bins);
         if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_FWD_COL);
         switch (p.item_type)
             {
-            case GB200_ITEM_32FC:
-                if ((e = set_smem(gb_acq_fwd_col<GB200_ITEM_32FC>, sm)) != cudaSuccess) return e;
-                gb_acq_fwd_col<GB200_ITEM_32FC><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p, wipeoff ? 1 : 0);
-                break;
-            case GB200_ITEM_16IC:
-                if ((e = set_smem(gb_acq_fwd_col<GB200_ITEM_16IC>, sm)) != cudaSuccess) return e;
-                gb_acq_fwd_col<GB200_ITEM_16IC><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p, wipeoff ? 1 : 0);
-                break;
-            case GB200_ITEM_8IC:
-                if ((e = set_smem(gb_acq_fwd_col<GB200_ITEM_8IC>, sm)) != cudaSuccess) return e;
-                gb_acq_fwd_col<GB200_ITEM_8IC><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p, wipeoff ? 1 : 0);
-                break;
+            case GB200_ITEM_32FC: e = launch_fwd_col<GB200_ITEM_32FC>(logt, grid, sm, st, pd, p, wipeoff ? 1 : 0); break;
+            case GB200_ITEM_16IC: e = launch_fwd_col<GB200_ITEM_16IC>(logt, grid, sm, st, pd, p, wipeoff ? 1 : 0); break;
+            case GB200_ITEM_8IC: e = launch_fwd_col<GB200_ITEM_8IC>(logt, grid, sm, st, pd, p, wipeoff ? 1 : 0); break;
             default: return cudaErrorInvalidValue;
             }
         if (kt) gb_kt_end(kt);
+        if (e != cudaSuccess) return e;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }
     {
         PlanDev pd = make_plan_dev(plan, false);
         const size_t sm = gb_acq_row_smem(plan);
+        const int logt = log2_tile(plan.tile2);
         dim3 grid((plan.N1 + plan.tile2 - 1) / plan.tile2, n_bins);
-        if ((e = set_smem(gb_acq_fwd_row, sm)) != cudaSuccess) return e;
         if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_FWD_ROW);
-        gb_acq_fwd_row<<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p);
+        GB_TILE_DISPATCH(logt, e = set_smem(gb_acq_fwd_row<LT>, sm); if (e == cudaSuccess) gb_acq_fwd_row<LT><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p))
         if (kt) gb_kt_end(kt);
+        if (e != cudaSuccess) return e;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }
@@ -713,22 +812,24 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
     {
         PlanDev pd = make_plan_dev(plan, false);
         const size_t sm = gb_acq_row_smem(plan);
+        const int logt = log2_tile(plan.tile2);
         dim3 grid((plan.N1 + plan.tile2 - 1) / plan.tile2, p.n_transforms);
-        if ((e = set_smem(gb_acq_inv_row, sm)) != cudaSuccess) return e;
         if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_ROW);
-        gb_acq_inv_row<<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p);
+        GB_TILE_DISPATCH(logt, e = set_smem(gb_acq_inv_row<LT>, sm); if (e == cudaSuccess) gb_acq_inv_row<LT><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p))
         if (kt) gb_kt_end(kt);
+        if (e != cudaSuccess) return e;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }
     {
         PlanDev pd = make_plan_dev(plan, true);
         const size_t sm = gb_acq_col_smem(plan);
+        const int logt = log2_tile(plan.tile1);
         dim3 grid((plan.N2 + plan.tile1 - 1) / plan.tile1, p.n_transforms);
-        if ((e = set_smem(gb_acq_inv_col, sm)) != cudaSuccess) return e;
         if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_COL);
-        gb_acq_inv_col<<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p);
+        GB_TILE_DISPATCH(logt, e = set_smem(gb_acq_inv_col<LT>, sm); if (e == cudaSuccess) gb_acq_inv_col<LT><<<grid, GB200_ACQ_THREADS, sm, st>>>(pd, p))
         if (kt) gb_kt_end(kt);
+        if (e != cudaSuccess) return e;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (launches) (*launches)++;
     }

@@ -44,6 +44,7 @@ struct GbPlanEntry
     GbFftPlan plan;
     float2* d_tw1 = nullptr;
     float2* d_tw2 = nullptr;
+    float2* d_twN = nullptr;
 };
 
 // optional per-kernel-class CUDA-event timing (bench roofline); off by default
@@ -178,6 +179,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
         {
             if (kv.second.d_tw1) cudaFree(kv.second.d_tw1);
             if (kv.second.d_tw2) cudaFree(kv.second.d_tw2);
+            if (kv.second.d_twN) cudaFree(kv.second.d_twN);
         }
     for (int i = 0; i < 8; i++)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
@@ -474,12 +476,12 @@ static bool factor_radices(int M, int* rad, int* nrad)
 
 static int pick_tile(int M)
 {
-    // shared memory per CTA = (2*M*(tile+1) + M) * 8 B; keep <= ~72 KB when possible (3 CTAs/SM), hard cap 200 KB
+    // shared memory per CTA = (2*M*(tile+1) + 2*M) * 8 B; keep <= ~72 KB when possible (3 CTAs/SM), hard cap 200 KB
     const int tiles[] = {16, 8, 4, 2, 1};
     for (int t : tiles)
-        if (((size_t)2 * M * (t + 1) + M) * 8 <= 72 * 1024) return t;
+        if (((size_t)2 * M * (t + 1) + 2 * (size_t)M) * 8 <= 72 * 1024) return t;
     for (int t : tiles)
-        if (((size_t)2 * M * (t + 1) + M) * 8 <= 200 * 1024) return t;
+        if (((size_t)2 * M * (t + 1) + 2 * (size_t)M) * 8 <= 200 * 1024) return t;
     return 0;
 }
 
@@ -516,26 +518,31 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
     factor_radices(e.plan.N2, e.plan.rad2, &e.plan.nrad2);
     e.plan.tile1 = pick_tile(e.plan.N1);
     e.plan.tile2 = pick_tile(e.plan.N2);
-    for (int which = 0; which < 2; which++)
+    for (int which = 0; which < 3; which++)
         {
-            const int M = which ? e.plan.N2 : e.plan.N1;
+            // which 0/1: W_N1^i / W_N2^i (sub-transform twiddles); which 2: W_N^i for i < 16*max(N1,N2)
+            const int M = which == 2 ? 16 * std::max(e.plan.N1, e.plan.N2) : (which ? e.plan.N2 : e.plan.N1);
+            const int D = which == 2 ? N : M;
             std::vector<float2> tw(M);
             for (int i = 0; i < M; i++)
                 {
-                    const double a = -6.283185307179586476925286766559 * (double)i / (double)M;
+                    const double a = -6.283185307179586476925286766559 * (double)(i % D) / (double)D;
                     tw[i] = make_float2((float)cos(a), (float)sin(a));
                 }
             float2* d = nullptr;
             GB_CUDA(s, cudaMalloc(&d, sizeof(float2) * M));
             GB_CUDA(s, cudaMemcpyAsync(d, tw.data(), sizeof(float2) * M, cudaMemcpyHostToDevice, s->stream));
             GB_CUDA(s, cudaStreamSynchronize(s->stream));
-            if (which)
+            if (which == 2)
+                e.d_twN = d;
+            else if (which)
                 e.d_tw2 = d;
             else
                 e.d_tw1 = d;
         }
     e.plan.tw1 = e.d_tw1;
     e.plan.tw2 = e.d_tw2;
+    e.plan.twN = e.d_twN;
     auto ins = s->plans.emplace(N, e);
     *out = &ins.first->second.plan;
     return GB200_OK;
