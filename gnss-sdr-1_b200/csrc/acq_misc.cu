@@ -1,0 +1,232 @@
+// Small acquisition kernels: conjugate, input power, peak reductions, second-peak statistic.
+#include "acq_fft.cuh"
+
+namespace
+{
+
+__global__ void gb_conj_kernel(float2* d, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) d[i].y = -d[i].y;
+}
+
+// d_input_power = sum_{n<N} |x[n]|^2 / N with x zero-padded beyond `consumed` (pcps_acquisition.cc:703-709);
+// optionally leaves |x|^2 in the block's d_tmp_buffer image (needed only to reproduce quirk 1 of SURVEY 7.3).
+// Single CTA, fixed summation tree -> deterministic.
+template <int ITEM>
+__global__ void __launch_bounds__(1024) gb_input_power_kernel(const void* samples, int consumed, int N, float* power, float* tmp)
+{
+    __shared__ float s[32];
+    float acc = 0.f;
+    for (int n = threadIdx.x; n < N; n += blockDim.x)
+        {
+            float m = 0.f;
+            if (n < consumed)
+                {
+                    const float2 x = gb_load_item<ITEM>(samples, (size_t)n);
+                    m = __fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y));
+                }
+            if (tmp) tmp[n] = m;
+            acc += m;
+        }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32)
+        {
+            acc = threadIdx.x < (blockDim.x >> 5) ? s[threadIdx.x] : 0.f;
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+            if (threadIdx.x == 0) *power = acc / (float)N;
+        }
+}
+
+// ordering of the reference's two nested strict-'>' scans (bins ascending, index ascending):
+// larger magnitude wins; on equal magnitude the lower bin, then the lower index
+__device__ __forceinline__ bool peak_before(const GbPeak& a, const GbPeak& b)
+{
+    if (a.mag != b.mag) return a.mag > b.mag;
+    if (a.bin != b.bin) return a.bin < b.bin;
+    return a.idx < b.idx;
+}
+
+__device__ __forceinline__ GbPeak peak_block_reduce(GbPeak best)
+{
+    __shared__ GbPeak s[32];
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            GbPeak other;
+            other.mag = __shfl_down_sync(0xffffffffu, best.mag, o);
+            other.idx = __shfl_down_sync(0xffffffffu, best.idx, o);
+            other.bin = __shfl_down_sync(0xffffffffu, best.bin, o);
+            other.pad_ = 0;
+            if (peak_before(other, best)) best = other;
+        }
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int k = 1; k < (int)(blockDim.x >> 5); k++)
+            if (peak_before(s[k], best)) best = s[k];
+    return best;  // valid in thread 0
+}
+
+// one CTA per handle: reduce [bins][tiles] per-CTA maxima
+__global__ void __launch_bounds__(256) gb_reduce_peaks_kernel(const GbPeak* partial, int n_bins, int tiles, GbPeak* out)
+{
+    const GbPeak* p = partial + (size_t)blockIdx.x * n_bins * tiles;
+    GbPeak best;
+    best.mag = -1.f;
+    best.idx = 0xffffffffu;
+    best.bin = 0xffffffffu;
+    best.pad_ = 0;
+    for (int i = threadIdx.x; i < n_bins * tiles; i += blockDim.x)
+        {
+            GbPeak c = p[i];
+            if (peak_before(c, best)) best = c;
+        }
+    best = peak_block_reduce(best);
+    if (threadIdx.x == 0)
+        {
+            // the reference starts from grid_maximum = 0 with strict '>': an all-zero grid reports bin 0, index 0
+            if (!(best.mag > 0.f))
+                {
+                    best.mag = 0.f;
+                    best.idx = 0;
+                    best.bin = 0;
+                }
+            out[blockIdx.x] = best;
+        }
+}
+
+// one CTA per handle: scan its stored magnitude grid [bins][row_len]
+__global__ void __launch_bounds__(1024) gb_grid_peaks_kernel(float* const* grids, int n_bins, int row_len, GbPeak* out)
+{
+    const float* g = grids[blockIdx.x];
+    GbPeak best;
+    best.mag = -1.f;
+    best.idx = 0xffffffffu;
+    best.bin = 0xffffffffu;
+    best.pad_ = 0;
+    const size_t total = (size_t)n_bins * row_len;
+    for (size_t i = threadIdx.x; i < total; i += blockDim.x)
+        {
+            GbPeak c;
+            c.mag = g[i];
+            c.bin = (unsigned)(i / row_len);
+            c.idx = (unsigned)(i - (size_t)c.bin * row_len);
+            c.pad_ = 0;
+            if (peak_before(c, best)) best = c;
+        }
+    best = peak_block_reduce(best);
+    if (threadIdx.x == 0)
+        {
+            if (!(best.mag > 0.f))
+                {
+                    best.mag = 0.f;
+                    best.idx = 0;
+                    best.bin = 0;
+                }
+            out[blockIdx.x] = best;
+        }
+}
+
+// first_vs_second_peak_statistic tail (pcps_acquisition.cc:633-660), single CTA:
+//   memcpy(d_tmp_buffer, row, d_fft_size BYTES)  -> only the first N/4 floats are refreshed (quirk 1)
+//   zero [idx - spc, idx + spc) with the one-sided wrap of :637-644 (quirk 2), do-while semantics
+//   second peak = first maximum of d_tmp_buffer[0..N)
+__global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, int row_len, float* tmp, int N, int idx, int spc, float* second)
+{
+    const int ncopy = min(N / 4, row_len);
+    for (int i = threadIdx.x; i < ncopy; i += blockDim.x) tmp[i] = row[i];
+    __syncthreads();
+    int ex1 = idx - spc, ex2 = idx + spc;
+    if (ex1 < 0)
+        ex1 = N + ex1;
+    else if (ex2 >= N)
+        ex2 = ex2 - N;
+    // do { tmp[i] = 0; i++; if (i == N) i = 0; } while (i != ex2): at least one element, wraps the whole buffer when ex1 == ex2
+    int count = ex2 - ex1;
+    if (count <= 0) count += N;
+    for (int k = threadIdx.x; k < count; k += blockDim.x)
+        {
+            int i = ex1 + k;
+            if (i >= N) i -= N;
+            if (i >= 0 && i < N) tmp[i] = 0.f;
+        }
+    __syncthreads();
+    GbPeak best;
+    best.mag = -INFINITY;
+    best.idx = 0xffffffffu;
+    best.bin = 0;
+    best.pad_ = 0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x)
+        {
+            GbPeak c;
+            c.mag = tmp[i];
+            c.idx = (unsigned)i;
+            c.bin = 0;
+            c.pad_ = 0;
+            if (peak_before(c, best)) best = c;
+        }
+    best = peak_block_reduce(best);
+    if (threadIdx.x == 0) *second = best.mag;
+}
+
+// last dwell's magnitudes of the LAST Doppler bin into d_tmp_buffer (pcps_acquisition.cc:737, dwell > 1)
+__global__ void gb_copy_kernel(float* dst, const float* src, int n)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+}
+}  // namespace
+
+size_t gb_acq_col_smem(const GbFftPlan& plan) { return smem_for(plan.N1, plan.tile1); }
+size_t gb_acq_row_smem(const GbFftPlan& plan) { return smem_for(plan.N2, plan.tile2); }
+
+cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches)
+{
+    gb_conj_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(data, n);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type, int N, float* d_power, float* d_mag2_tmp, cudaStream_t st, int* launches)
+{
+    switch (item_type)
+        {
+        case GB200_ITEM_32FC: gb_input_power_kernel<GB200_ITEM_32FC><<<1, 1024, 0, st>>>(samples, consumed, N, d_power, d_mag2_tmp); break;
+        case GB200_ITEM_16IC: gb_input_power_kernel<GB200_ITEM_16IC><<<1, 1024, 0, st>>>(samples, consumed, N, d_power, d_mag2_tmp); break;
+        case GB200_ITEM_8IC: gb_input_power_kernel<GB200_ITEM_8IC><<<1, 1024, 0, st>>>(samples, consumed, N, d_power, d_mag2_tmp); break;
+        default: return cudaErrorInvalidValue;
+        }
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins, int tiles, GbPeak* out, cudaStream_t st, int* launches)
+{
+    gb_reduce_peaks_kernel<<<n_handles, 256, 0, st>>>(partial, n_bins, tiles, out);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches)
+{
+    gb_grid_peaks_kernel<<<n_handles, 1024, 0, st>>>(grids, n_bins, row_len, out);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches)
+{
+    gb_second_peak_kernel<<<1, 1024, 0, st>>>(grid_row, N, tmp_buffer, N, idx, samples_per_chip, d_second);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st, int* launches)
+{
+    gb_copy_kernel<<<(n + 255) / 256, 256, 0, st>>>(dst, src, n);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+

@@ -110,7 +110,8 @@ struct GbFftPlan
     int tile2;  // rows (k1) per CTA in the row kernels (sub-FFT length N2)
     const float2* tw1;  // device: W_N1^i, i < N1 (forward sign)
     const float2* tw2;  // device: W_N2^i, i < N2
-    const float2* twN;  // device: W_N^i, i < 16 * max(N1, N2): the per-column part of the four-step twiddle
+    const float2* twN;  // device: W_N^i, i < max(256, 16 * max(N1, N2)): the per-column part of the four-step twiddle
+    const float2* twNhi;  // device: W_N^(256 i), i < ceil(N / 256)
 };
 
 // Reference-matched Doppler wipe-off.  The reference builds each bin's table with

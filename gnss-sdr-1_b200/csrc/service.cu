@@ -45,6 +45,7 @@ struct GbPlanEntry
     float2* d_tw1 = nullptr;
     float2* d_tw2 = nullptr;
     float2* d_twN = nullptr;
+    float2* d_twNhi = nullptr;
 };
 
 // optional per-kernel-class CUDA-event timing (bench roofline); off by default
@@ -180,6 +181,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
             if (kv.second.d_tw1) cudaFree(kv.second.d_tw1);
             if (kv.second.d_tw2) cudaFree(kv.second.d_tw2);
             if (kv.second.d_twN) cudaFree(kv.second.d_twN);
+            if (kv.second.d_twNhi) cudaFree(kv.second.d_twNhi);
         }
     for (int i = 0; i < 8; i++)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
@@ -518,22 +520,25 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
     factor_radices(e.plan.N2, e.plan.rad2, &e.plan.nrad2);
     e.plan.tile1 = pick_tile(e.plan.N1);
     e.plan.tile2 = pick_tile(e.plan.N2);
-    for (int which = 0; which < 3; which++)
+    for (int which = 0; which < 4; which++)
         {
-            // which 0/1: W_N1^i / W_N2^i (sub-transform twiddles); which 2: W_N^i for i < 16*max(N1,N2)
-            const int M = which == 2 ? 16 * std::max(e.plan.N1, e.plan.N2) : (which ? e.plan.N2 : e.plan.N1);
-            const int D = which == 2 ? N : M;
+            // which 0/1: W_N1^i / W_N2^i (sub-transform twiddles); 2: W_N^i, i < max(256, 16*max(N1,N2)); 3: W_N^(256 i)
+            const int M = which == 3 ? (N + 255) / 256 : (which == 2 ? std::max(256, 16 * std::max(e.plan.N1, e.plan.N2)) : (which ? e.plan.N2 : e.plan.N1));
+            const int D = which >= 2 ? N : M;
+            const long long mul = which == 3 ? 256 : 1;
             std::vector<float2> tw(M);
             for (int i = 0; i < M; i++)
                 {
-                    const double a = -6.283185307179586476925286766559 * (double)(i % D) / (double)D;
+                    const double a = -6.283185307179586476925286766559 * (double)((i * mul) % D) / (double)D;
                     tw[i] = make_float2((float)cos(a), (float)sin(a));
                 }
             float2* d = nullptr;
             GB_CUDA(s, cudaMalloc(&d, sizeof(float2) * M));
             GB_CUDA(s, cudaMemcpyAsync(d, tw.data(), sizeof(float2) * M, cudaMemcpyHostToDevice, s->stream));
             GB_CUDA(s, cudaStreamSynchronize(s->stream));
-            if (which == 2)
+            if (which == 3)
+                e.d_twNhi = d;
+            else if (which == 2)
                 e.d_twN = d;
             else if (which)
                 e.d_tw2 = d;
@@ -543,6 +548,7 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
     e.plan.tw1 = e.d_tw1;
     e.plan.tw2 = e.d_tw2;
     e.plan.twN = e.d_twN;
+    e.plan.twNhi = e.d_twNhi;
     auto ins = s->plans.emplace(N, e);
     *out = &ins.first->second.plan;
     return GB200_OK;
