@@ -31,6 +31,7 @@ struct GbTrkWork
     double nco_a0_turns;     // arg(phase_0) / 2pi
     double nco_theta_turns;  // arg(inc) / 2pi
     double nco_log_mag;      // log|inc| (high-dynamics path: the reference never renormalises phase_doppler there)
+    float2 nco_adv;          // unit phasor of GB200_TRK_THREADS * arg(inc): the per-iteration NCO advance of one thread
 };
 
 // acquisition grid-reduction record: ordering key = (mag desc, bin asc, idx asc)

@@ -1415,6 +1415,10 @@ static int trk_fill_work(gb200_service* s, const gb200_trk_req& r, int out_index
         const double mag = hypot((double)incr, (double)inci);
         w->nco_mag_delta = (float)(mag - 1.0);
         w->nco_log_mag = log(mag);
+        {
+            const double a = 6.283185307179586476925 * w->nco_theta_turns * (double)GB200_TRK_THREADS;
+            w->nco_adv = make_float2((float)cos(a), (float)sin(a));
+        }
     }
     return GB200_OK;
 }
@@ -1477,14 +1481,30 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
             b->order[slot] = i;
             max_n = std::max(max_n, reqs[i].n_samples);
         }
-    // chunk size: 4096 samples per CTA unless that leaves the GPU under two waves
-    long long ctas = 0;
-    b->chunk = 4096;
-    for (int c : {4096, 2048, 1024})
+    // chunk size (samples per CTA): the largest that still gives >= 4 CTAs per SM and whose code window (the chips one
+    // CTA can touch: chunk*step + tap spread) fits the shared-memory staging area; per-CTA set-up (NCO seed, window
+    // fill, 6-accumulator reduction) is ~700 instructions per thread, so long chunks matter.
+    double chips_per_sample = 0.0, spread = 0.0;
+    for (int i = 0; i < n; i++)
         {
+            const GbTrkWork& w = b->h_work[i];
+            float lo = w.shifts[0], hi = w.shifts[0];
+            for (int t = 1; t < w.n_taps; t++)
+                {
+                    lo = std::min(lo, w.shifts[t]);
+                    hi = std::max(hi, w.shifts[t]);
+                }
+            spread = std::max(spread, (double)hi - (double)lo);
+            chips_per_sample = std::max(chips_per_sample, std::fabs((double)w.code_step));
+        }
+    long long ctas = 0;
+    b->chunk = 1024;
+    for (int c : {32768, 16384, 8192, 4096, 2048, 1024})
+        {
+            b->chunk = c;
+            if (c > 1024 && (double)std::min(c, max_n) * chips_per_sample + spread + 8.0 > (double)GB200_TRK_WMAX) continue;
             ctas = 0;
             for (int i = 0; i < n; i++) ctas += (reqs[i].n_samples + c - 1) / c;
-            b->chunk = c;
             if (ctas >= 4LL * s->sm_count) break;
         }
     b->max_chunks = (max_n + b->chunk - 1) / b->chunk;

@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(GB200_TRK_THREADS)
     // ---- carrier NCO: seed per thread, then advance by 256 samples per iteration ----
     int n = n0 + threadIdx.x;
     float2 ph = gb_phasor_turns(w.nco_a0_turns, w.nco_theta_turns, (double)n);
-    const float2 adv256 = gb_phasor_turns(0.0, w.nco_theta_turns, (double)GB200_TRK_THREADS);
+    const float2 adv256 = w.nco_adv;
     {
         // |inc| != 1 in float32: between two renormalisations (every 256 samples, chunk starts are multiples of 256)
         // the reference's phasor magnitude is |inc|^e, e = ((n-1) mod 256) + 1 -- constant per thread here
