@@ -1,5 +1,5 @@
 // Inverse side of the PCPS acquisition search (x conj(code DFT), inverse DFT, |.|^2, arg-max), once per (PRN, Doppler bin).
-#include "acq_fft.cuh"
+#include "acq_dif.cuh"
 
 namespace
 {
@@ -149,11 +149,218 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
             p.partial[(size_t)t * gridDim.x + blockIdx.x] = pk;
         }
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fast path: both sub-lengths compile-time (GbDif), in-place DIF tiles, first/last pass fused with global I/O.
+
+// rows: spectra x code spectrum -> inverse DFT over k2 -> x W_N^+(k1 n2) -> rowbuf[t][k1][n2]
+template <int LOGT, class DROW, int N1>
+__global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
+    gb_acq_inv_row_dif(PlanDev pl, GbAcqInvParams p)
+{
+    constexpr int M = DROW::kM, TILE = 1 << LOGT, N = N1 * M;
+    constexpr int RL = DROW::kLastR, NIL = DROW::kLastNI;
+    using L = GbRowTile<LOGT, M>;
+    extern __shared__ __align__(16) float2 smem[];
+    float2* buf = smem;
+    float2* tw = buf + L::size(M);
+    float2* step = tw + M;
+    const int r0 = blockIdx.x * TILE;
+    const int nb = min(TILE, N1 - r0);
+    for (int i = threadIdx.x; i < M; i += GB200_ACQ_THREADS) tw[i] = __ldg(pl.tw + i);
+    if (threadIdx.x < TILE)
+        {
+            const unsigned e = (unsigned)(r0 + threadIdx.x) * (unsigned)NIL % (unsigned)N;
+            step[threadIdx.x] = cmul(__ldg(pl.twN + (e & 255u)), __ldg(pl.twNhi + (e >> 8)));
+        }
+    const int t = p.first_transform + blockIdx.y;
+    const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
+    const float2* xs = p.spectra + (size_t)bin * N + (size_t)r0 * M;
+    const float2* cs = p.code_fft[handle] + (size_t)r0 * M;
+    dif_first<+1, L, M, DROW::kFirstR>(buf, pl.tw, [&](int b, int m) {
+        return b < nb ? cmul(__ldg(xs + b * M + m), __ldg(cs + b * M + m)) : make_float2(0.f, 0.f);
+    });
+    __syncthreads();
+    float2* dst = p.rowbuf + (size_t)blockIdx.y * N + (size_t)r0 * M;
+    DROW::template run_rest<+1, L>(buf, tw, [&](int b, int i, const float2* v) {
+        if (b >= nb) return;
+        const unsigned e0 = (unsigned)(r0 + b) * (unsigned)i;  // < N
+        float2 w = cmul(__ldg(pl.twN + (e0 & 255u)), __ldg(pl.twNhi + (e0 >> 8)));
+        const float2 ws = step[b];
+        float2* d = dst + b * M + i;
+#pragma unroll
+        for (int r = 0; r < RL; r++)
+            {
+                d[r * NIL] = cmul_conj(v[r], w);  // tables hold the forward sign; the inverse needs the conjugate
+                if (r + 1 < RL) w = cmul(w, ws);
+            }
+    });
+}
+
+// columns: rowbuf[t][k1][n2] -> inverse DFT over k1 -> |y[N2 n1 + n2]|^2 -> per-CTA (max, first index) or grid
+template <int LOGT, class DCOL, int N2>
+__global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
+    gb_acq_inv_col_dif(PlanDev pl, GbAcqInvParams p)
+{
+    constexpr int M = DCOL::kM, TILE = 1 << LOGT, N = N2 * M;
+    constexpr int RL = DCOL::kLastR, NIL = DCOL::kLastNI;
+    using L = GbColTile<LOGT>;
+    extern __shared__ __align__(16) float2 smem[];
+    __shared__ float s_mag[GB200_ACQ_THREADS / 32];
+    __shared__ unsigned s_idx[GB200_ACQ_THREADS / 32];
+    float2* buf = smem;
+    float2* tw = buf + L::size(M);
+    const int c0 = blockIdx.x * TILE;
+    for (int i = threadIdx.x; i < M; i += GB200_ACQ_THREADS) tw[i] = __ldg(pl.tw + i);
+    const float2* src = p.rowbuf + (size_t)blockIdx.y * N + c0;
+    dif_first<+1, L, M, DCOL::kFirstR>(buf, pl.tw, [&](int b, int m) {
+        return ((N2 % TILE) == 0 || c0 + b < N2) ? __ldg(src + m * N2 + b) : make_float2(0.f, 0.f);
+    });
+    __syncthreads();
+    const int t = p.first_transform + blockIdx.y;
+    const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
+    float* grid = p.grid ? p.grid[handle] : nullptr;
+    float best = -1.0f;
+    unsigned best_i = 0xffffffffu;
+    DCOL::template run_rest<+1, L>(buf, tw, [&](int b, int i, const float2* v) {
+        if ((N2 % TILE) != 0 && c0 + b >= N2) return;
+        const int nbase = N2 * i + c0 + b - p.keep_offset;
+#pragma unroll
+        for (int r = 0; r < RL; r++)
+            {
+                const int n = nbase + r * (NIL * N2);
+                if (n < 0 || n >= p.keep_len) continue;
+                const float mag = __fadd_rn(__fmul_rn(v[r].x, v[r].x), __fmul_rn(v[r].y, v[r].y));  // volk_32fc_magnitude_squared_32f
+                if (grid)
+                    {
+                        float* g = grid + (size_t)bin * p.keep_len + n;
+                        *g = p.accumulate ? __fadd_rn(*g, mag) : mag;
+                        if (p.accumulate && p.tmpbuf && p.tmpbuf[handle] && bin == p.n_bins - 1) p.tmpbuf[handle][n] = mag;
+                    }
+                else if (peak_better(mag, (unsigned)n, best, best_i))
+                    {
+                        best = mag;
+                        best_i = (unsigned)n;
+                    }
+            }
+    });
+    if (grid) return;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        {
+            const float om = __shfl_down_sync(0xffffffffu, best, o);
+            const unsigned oi = __shfl_down_sync(0xffffffffu, best_i, o);
+            if (peak_better(om, oi, best, best_i))
+                {
+                    best = om;
+                    best_i = oi;
+                }
+        }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0)
+        {
+            s_mag[warp] = best;
+            s_idx[warp] = best_i;
+        }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        {
+            for (int k = 1; k < GB200_ACQ_THREADS / 32; k++)
+                if (peak_better(s_mag[k], s_idx[k], best, best_i))
+                    {
+                        best = s_mag[k];
+                        best_i = s_idx[k];
+                    }
+            GbPeak pk;
+            pk.mag = best;
+            pk.idx = best_i;
+            pk.bin = (unsigned)bin;
+            pk.pad_ = 0;
+            p.partial[(size_t)t * gridDim.x + blockIdx.x] = pk;
+        }
+}
+
+// The (N1, N2) pairs with a fast path; tiles are fixed per pair.  f(GbDif<N1...>{}, GbDif<N2...>{}, GbInt<LOGT1>{}, GbInt<LOGT2>{})
+template <class F>
+bool gb_with_dif_pair(int N1, int N2, F&& f)
+{
+#define GB_DIF_PAIR(n1, n2, D1, D2, LT1, LT2) \
+    if (N1 == n1 && N2 == n2)                 \
+        {                                     \
+            f(D1{}, D2{}, GbInt<LT1>{}, GbInt<LT2>{}); \
+            return true;                      \
+        }
+    using D50 = GbDif<50, 10, 5>;
+    using D80 = GbDif<80, 16, 5>;
+    using D100 = GbDif<100, 10, 10>;
+    using D125 = GbDif<125, 5, 5, 5>;
+    using D128 = GbDif<128, 16, 8>;
+    using D160 = GbDif<160, 16, 10>;
+    using D200 = GbDif<200, 8, 5, 5>;
+    using D250 = GbDif<250, 10, 5, 5>;
+    using D320 = GbDif<320, 8, 8, 5>;
+    using D400 = GbDif<400, 16, 5, 5>;
+    using D500 = GbDif<500, 10, 10, 5>;
+    GB_DIF_PAIR(50, 80, D50, D80, 4, 4)      // 4000   GPS L1 C/A 1 ms @ 4 Msps
+    GB_DIF_PAIR(80, 100, D80, D100, 4, 4)    // 8000
+    GB_DIF_PAIR(125, 128, D125, D128, 4, 4)  // 16000
+    GB_DIF_PAIR(125, 160, D125, D160, 4, 4)  // 20000
+    GB_DIF_PAIR(125, 200, D125, D200, 3, 4)  // 25000  GPS L5 / Galileo E5a 1 ms @ 25 Msps
+    GB_DIF_PAIR(160, 200, D160, D200, 3, 4)  // 32000  Galileo E1 4 ms @ 8 Msps
+    GB_DIF_PAIR(200, 200, D200, D200, 3, 4)  // 40000
+    GB_DIF_PAIR(200, 250, D200, D250, 3, 3)  // 50000
+    GB_DIF_PAIR(250, 320, D250, D320, 3, 3)  // 80000
+    GB_DIF_PAIR(400, 500, D400, D500, 3, 3)  // 200000
+#undef GB_DIF_PAIR
+    return false;
+}
 }  // namespace
+
+bool gb_acq_inverse_tiles(int N1, int N2, int* tile1, int* tile2)
+{
+    return gb_with_dif_pair(N1, N2, [&](auto, auto, auto lt1, auto lt2) {
+        *tile1 = 1 << decltype(lt1)::value;
+        *tile2 = 1 << decltype(lt2)::value;
+    });
+}
 
 cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt)
 {
     cudaError_t e;
+    if (plan.inv_fast)
+        {
+            e = cudaErrorInvalidValue;
+            const PlanDev pdr = make_plan_dev(plan, false), pdc = make_plan_dev(plan, true);
+            gb_with_dif_pair(plan.N1, plan.N2, [&](auto d1, auto d2, auto lt1, auto lt2) {
+                using D1 = decltype(d1);
+                using D2 = decltype(d2);
+                constexpr int LT1 = decltype(lt1)::value, LT2 = decltype(lt2)::value;
+                constexpr int T1 = 1 << LT1, T2 = 1 << LT2;
+                {
+                    auto k = gb_acq_inv_row_dif<LT2, D2, D1::kM>;
+                    const size_t sm = (GbRowTile<LT2, D2::kM>::size(D2::kM) + D2::kM + T2) * sizeof(float2);
+                    if ((e = set_smem(k, sm)) != cudaSuccess) return;
+                    const dim3 grid((D1::kM + T2 - 1) / T2, p.n_transforms);
+                    if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_ROW);
+                    k<<<grid, GB200_ACQ_THREADS, sm, st>>>(pdr, p);
+                    if (kt) gb_kt_end(kt);
+                    if ((e = cudaGetLastError()) != cudaSuccess) return;
+                    if (launches) (*launches)++;
+                }
+                {
+                    auto k = gb_acq_inv_col_dif<LT1, D1, D2::kM>;
+                    const size_t sm = (GbColTile<LT1>::size(D1::kM) + D1::kM) * sizeof(float2);
+                    if ((e = set_smem(k, sm)) != cudaSuccess) return;
+                    const dim3 grid((D2::kM + T1 - 1) / T1, p.n_transforms);
+                    if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_COL);
+                    k<<<grid, GB200_ACQ_THREADS, sm, st>>>(pdc, p);
+                    if (kt) gb_kt_end(kt);
+                    if ((e = cudaGetLastError()) != cudaSuccess) return;
+                    if (launches) (*launches)++;
+                }
+            });
+            return e;
+        }
     {
         const PlanDev pd = make_plan_dev(plan, false);
         const size_t sm = gb_acq_row_smem(plan);

@@ -520,6 +520,17 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
     factor_radices(e.plan.N2, e.plan.rad2, &e.plan.nrad2);
     e.plan.tile1 = pick_tile(e.plan.N1);
     e.plan.tile2 = pick_tile(e.plan.N2);
+    e.plan.inv_tile1 = e.plan.tile1;
+    {
+        // compile-time specialised inverse kernels for the common (N1, N2) pairs; GB200_ACQ_GENERIC=1 forces the general path
+        int t1 = 0, t2 = 0;
+        const char* force = getenv("GB200_ACQ_GENERIC");
+        if (!(force && force[0] == '1') && gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, &t1, &t2))
+            {
+                e.plan.inv_fast = 1;
+                e.plan.inv_tile1 = t1;
+            }
+    }
     for (int which = 0; which < 4; which++)
         {
             // which 0/1: W_N1^i / W_N2^i (sub-transform twiddles); 2: W_N^i, i < max(256, 16*max(N1,N2)); 3: W_N^(256 i)
@@ -1024,7 +1035,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             const size_t l2_budget = 48ull << 20;
             int chunkT = (int)std::max<size_t>(1, l2_budget / (sizeof(float2) * (size_t)N));
             chunkT = std::min(chunkT, T);
-            const int tiles = (plan.N2 + plan.tile1 - 1) / plan.tile1;
+            const int tiles = (plan.N2 + plan.inv_tile1 - 1) / plan.inv_tile1;
             void *d_row, *d_part;
             if ((rc = s->scratch(2, sizeof(float2) * (size_t)N * chunkT, &d_row))) return rc;
             if ((rc = s->scratch(3, sizeof(GbPeak) * (size_t)T * tiles, &d_part))) return rc;

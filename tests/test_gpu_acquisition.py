@@ -200,3 +200,26 @@ def test_odd_lengths_random_code(service, n_ms, fs):
     (pairs, _) = run_pair(service, cfg, code, x.astype(np.complex64))
     check_against_oracle(*pairs[0], "n=%d" % n)
     assert pairs[0][0].code_phase_index == delay and pairs[0][0].doppler_hz == 750 and pairs[0][0].decision == 1
+
+
+@pytest.mark.parametrize("fs", [4000000, 8000000, 16000000, 20000000, 32000000, 40000000, 50000000, 80000000, 200000000])
+@pytest.mark.parametrize("keep_grid", [False, True])
+def test_fast_inverse_lengths(service, fs, keep_grid):
+    """Every (N1, N2) pair with compile-time in-place DIF inverse kernels (csrc/acq_dif.cuh): the fused arg-max path and the
+    grid path against the oracle (25000 is covered by test_odd_lengths_random_code)."""
+    n = fs // 1000
+    rng = np.random.default_rng(fs + 1)
+    code = rng.choice([-1.0, 1.0], n).astype(np.complex64)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    delay, dop = (2 * n) // 7, -500.0
+    t = np.arange(n) / fs
+    x += 0.5 * np.roll(code, delay) * np.exp(2j * np.pi * dop * t).astype(np.complex64)
+    cfg = dict(doppler_max=1000, doppler_step=250, threshold=0.0005, samples_per_chip=2, fs_in=fs, samples_per_ms=float(n),
+               samples_per_code=float(n))
+    (pairs, grids) = run_pair(service, cfg, code, x.astype(np.complex64), keep_grid=keep_grid)
+    check_against_oracle(*pairs[0], "n=%d" % n)
+    assert pairs[0][0].code_phase_index == delay and pairs[0][0].doppler_hz == -500 and pairs[0][0].decision == 1
+    if keep_grid:
+        g, go = grids
+        assert g.shape == go.shape
+        assert np.max(np.abs(g - go)) <= 2e-5 * np.max(go)
