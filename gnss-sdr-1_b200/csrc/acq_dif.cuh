@@ -96,57 +96,60 @@ __device__ __forceinline__ void bflyx(float2* v)
         bfly<SIGN, R>(v);
 }
 
-// ---- tile layouts: where element m of the tile's sub-transform b lives in shared memory ----
-template <int LOGT>
-struct GbColTile  // [m][b], b fastest: column kernels (global rows of TILE consecutive columns)
+// ---- tile layout: element m of the tile's sub-transform b lives at m * MS + b, MS = TILE + 1 (odd) ----
+// With an odd element stride both access directions are bank-conflict free for 8-byte words: lanes along b (stride 1)
+// and lanes along m (stride MS = 1 mod 16).  Work items (i, b) are mapped to threads either b-fastest (column kernels: a
+// global row of TILE consecutive columns per instruction) or i-fastest (row kernels' first and last pass: consecutive
+// elements of one contiguous sub-transform per instruction; i is padded to a multiple of 16 so a half-warp never
+// straddles two sub-transforms).
+template <int LOGT, int NT_>
+struct GbTile
 {
     static constexpr int TILE = 1 << LOGT;
-    static constexpr int MS = TILE + 1;  // element stride in float2
-    template <int NI>
-    static __device__ __forceinline__ void split(int idx, int& i, int& b)
-    {
-        b = idx & (TILE - 1);
-        i = idx >> LOGT;
-    }
-    static __device__ __forceinline__ int lane_base(int b) { return b; }
+    static constexpr int NT = NT_;  // threads per CTA
+    static constexpr int MS = TILE + 1;
     static __host__ __device__ constexpr int size(int M) { return M * MS; }
-};
-template <int LOGT, int M>
-struct GbRowTile  // [b][m], m fastest: row kernels (each sub-transform contiguous in global memory)
-{
-    static constexpr int TILE = 1 << LOGT;
-    static constexpr int MS = 1;
-    static constexpr int PM = M + 1;
-    template <int NI>
-    static __device__ __forceinline__ void split(int idx, int& i, int& b)
+    template <int NI, bool IFAST>
+    struct Map
     {
-        b = (int)((unsigned)idx / (unsigned)NI);
-        i = idx - b * NI;
-    }
-    static __device__ __forceinline__ int lane_base(int b) { return b * PM; }
-    static __host__ __device__ constexpr int size(int) { return TILE * PM; }
+        static constexpr int NIP = IFAST ? ((NI + 15) & ~15) : NI;
+        static constexpr int TOTAL = NIP * TILE;
+        static constexpr bool kExact = (NIP == NI) && (TOTAL % NT_) == 0;
+        static __device__ __forceinline__ bool split(int idx, int& i, int& b)
+        {
+            if (IFAST)
+                {
+                    b = (int)((unsigned)idx / (unsigned)NIP);
+                    i = idx - b * NIP;
+                    return (kExact || idx < TOTAL) && (NIP == NI || i < NI);
+                }
+            b = idx & (TILE - 1);
+            i = idx >> LOGT;
+            return kExact || idx < TOTAL;
+        }
+    };
 };
 
 // ---- passes ----
 // first pass: legs come from `load(b, m)` (global memory), outputs go to the tile; twiddles read through L1 (`twg`)
-template <int SIGN, class L, int M, int R, class LoadF>
+template <int SIGN, class L, bool IFAST, int M, int R, class LoadF>
 __device__ __forceinline__ void dif_first(float2* __restrict__ buf, const float2* __restrict__ twg, LoadF&& load)
 {
-    constexpr int S = M / R, NI = S, TOTAL = NI * L::TILE;
-    constexpr int ITERS = (TOTAL + GB200_ACQ_THREADS - 1) / GB200_ACQ_THREADS;
+    constexpr int S = M / R, NI = S;
+    using MAP = typename L::template Map<NI, IFAST>;
+    constexpr int ITERS = (MAP::TOTAL + L::NT - 1) / L::NT;
 #pragma unroll
     for (int it = 0; it < ITERS; it++)
         {
-            const int idx = it * GB200_ACQ_THREADS + (int)threadIdx.x;
-            if ((TOTAL % GB200_ACQ_THREADS) == 0 || idx < TOTAL)
+            const int idx = it * L::NT + (int)threadIdx.x;
+            int i, b;
+            if (MAP::split(idx, i, b))
                 {
-                    int i, b;
-                    L::template split<NI>(idx, i, b);
                     float2 v[R];
 #pragma unroll
                     for (int r = 0; r < R; r++) v[r] = load(b, i + r * S);
                     bflyx<SIGN, R>(v);
-                    float2* p = buf + L::lane_base(b) + i * L::MS;
+                    float2* p = buf + b + i * L::MS;
                     p[0] = v[0];
 #pragma unroll
                     for (int r = 1; r < R; r++)
@@ -162,19 +165,19 @@ __device__ __forceinline__ void dif_first(float2* __restrict__ buf, const float2
 template <int SIGN, class L, int M, int BP, int R>
 __device__ __forceinline__ void dif_mid(float2* __restrict__ buf, const float2* __restrict__ tw)
 {
-    constexpr int S = BP / R, NI = M / R, TOTAL = NI * L::TILE, TW = M / BP;
-    constexpr int ITERS = (TOTAL + GB200_ACQ_THREADS - 1) / GB200_ACQ_THREADS;
+    constexpr int S = BP / R, NI = M / R, TW = M / BP;
+    using MAP = typename L::template Map<NI, false>;
+    constexpr int ITERS = (MAP::TOTAL + L::NT - 1) / L::NT;
 #pragma unroll
     for (int it = 0; it < ITERS; it++)
         {
-            const int idx = it * GB200_ACQ_THREADS + (int)threadIdx.x;
-            if ((TOTAL % GB200_ACQ_THREADS) == 0 || idx < TOTAL)
+            const int idx = it * L::NT + (int)threadIdx.x;
+            int i, b;
+            if (MAP::split(idx, i, b))
                 {
-                    int i, b;
-                    L::template split<NI>(idx, i, b);
                     const int q = (int)((unsigned)i / (unsigned)S);
                     const int j = i - q * S;
-                    float2* p = buf + L::lane_base(b) + (q * BP + j) * L::MS;
+                    float2* p = buf + b + (q * BP + j) * L::MS;
                     float2 v[R];
 #pragma unroll
                     for (int r = 0; r < R; r++) v[r] = p[r * S * L::MS];
@@ -220,20 +223,20 @@ struct GbLastOf<R0>
 };
 
 // last pass: outputs stay in registers; `store(b, i, v)` receives frequencies k = i + r * (M / R), r < R
-template <int SIGN, class L, int M, int R, class REV, class StoreF>
+template <int SIGN, class L, bool IFAST, int M, int R, class REV, class StoreF>
 __device__ __forceinline__ void dif_last(const float2* __restrict__ buf, StoreF&& store)
 {
-    constexpr int NI = M / R, TOTAL = NI * L::TILE;
-    constexpr int ITERS = (TOTAL + GB200_ACQ_THREADS - 1) / GB200_ACQ_THREADS;
+    constexpr int NI = M / R;
+    using MAP = typename L::template Map<NI, IFAST>;
+    constexpr int ITERS = (MAP::TOTAL + L::NT - 1) / L::NT;
 #pragma unroll
     for (int it = 0; it < ITERS; it++)
         {
-            const int idx = it * GB200_ACQ_THREADS + (int)threadIdx.x;
-            if ((TOTAL % GB200_ACQ_THREADS) == 0 || idx < TOTAL)
+            const int idx = it * L::NT + (int)threadIdx.x;
+            int i, b;
+            if (MAP::split(idx, i, b))
                 {
-                    int i, b;
-                    L::template split<NI>(idx, i, b);
-                    const float2* p = buf + L::lane_base(b) + REV::get((unsigned)i) * L::MS;
+                    const float2* p = buf + b + REV::get((unsigned)i) * L::MS;
                     float2 v[R];
 #pragma unroll
                     for (int r = 0; r < R; r++) v[r] = p[r * L::MS];
@@ -243,27 +246,27 @@ __device__ __forceinline__ void dif_last(const float2* __restrict__ buf, StoreF&
         }
 }
 
-template <int SIGN, class L, int M, int BP, class REV, int... RS>
+template <int SIGN, class L, bool IFAST, int M, int BP, class REV, int... RS>
 struct GbDifRest;
-template <int SIGN, class L, int M, int BP, class REV, int R>
-struct GbDifRest<SIGN, L, M, BP, REV, R>
+template <int SIGN, class L, bool IFAST, int M, int BP, class REV, int R>
+struct GbDifRest<SIGN, L, IFAST, M, BP, REV, R>
 {
     static_assert(BP == R, "radix list must multiply to M");
     template <class StoreF>
     static __device__ __forceinline__ void run(float2* buf, const float2*, StoreF&& store)
     {
-        dif_last<SIGN, L, M, R, REV>(buf, store);
+        dif_last<SIGN, L, IFAST, M, R, REV>(buf, store);
     }
 };
-template <int SIGN, class L, int M, int BP, class REV, int R, int R2, int... REST>
-struct GbDifRest<SIGN, L, M, BP, REV, R, R2, REST...>
+template <int SIGN, class L, bool IFAST, int M, int BP, class REV, int R, int R2, int... REST>
+struct GbDifRest<SIGN, L, IFAST, M, BP, REV, R, R2, REST...>
 {
     template <class StoreF>
     static __device__ __forceinline__ void run(float2* buf, const float2* tw, StoreF&& store)
     {
         dif_mid<SIGN, L, M, BP, R>(buf, tw);
         __syncthreads();
-        GbDifRest<SIGN, L, M, BP / R, REV, R2, REST...>::run(buf, tw, store);
+        GbDifRest<SIGN, L, IFAST, M, BP / R, REV, R2, REST...>::run(buf, tw, store);
     }
 };
 
@@ -278,10 +281,10 @@ struct GbDif
     static constexpr int kLastNI = M_ / kLastR;
     using Rev = GbRevBase<M_, R0, REST...>;
     // after dif_first + barrier: the remaining passes
-    template <int SIGN, class L, class StoreF>
+    template <int SIGN, class L, bool IFAST, class StoreF>
     static __device__ __forceinline__ void run_rest(float2* buf, const float2* tw, StoreF&& store)
     {
-        GbDifRest<SIGN, L, M_, M_ / R0, Rev, REST...>::run(buf, tw, store);
+        GbDifRest<SIGN, L, IFAST, M_, M_ / R0, Rev, REST...>::run(buf, tw, store);
     }
 };
 

@@ -154,20 +154,20 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
 // Fast path: both sub-lengths compile-time (GbDif), in-place DIF tiles, first/last pass fused with global I/O.
 
 // rows: spectra x code spectrum -> inverse DFT over k2 -> x W_N^+(k1 n2) -> rowbuf[t][k1][n2]
-template <int LOGT, class DROW, int N1>
-__global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
+template <int LOGT, int NT, class DROW, int N1>
+__global__ void __launch_bounds__(NT, 1024 / NT)
     gb_acq_inv_row_dif(PlanDev pl, GbAcqInvParams p)
 {
     constexpr int M = DROW::kM, TILE = 1 << LOGT, N = N1 * M;
     constexpr int RL = DROW::kLastR, NIL = DROW::kLastNI;
-    using L = GbRowTile<LOGT, M>;
+    using L = GbTile<LOGT, NT>;
     extern __shared__ __align__(16) float2 smem[];
     float2* buf = smem;
     float2* tw = buf + L::size(M);
     float2* step = tw + M;
     const int r0 = blockIdx.x * TILE;
     const int nb = min(TILE, N1 - r0);
-    for (int i = threadIdx.x; i < M; i += GB200_ACQ_THREADS) tw[i] = __ldg(pl.tw + i);
+    for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
     if (threadIdx.x < TILE)
         {
             const unsigned e = (unsigned)(r0 + threadIdx.x) * (unsigned)NIL % (unsigned)N;
@@ -177,12 +177,12 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
     const float2* xs = p.spectra + (size_t)bin * N + (size_t)r0 * M;
     const float2* cs = p.code_fft[handle] + (size_t)r0 * M;
-    dif_first<+1, L, M, DROW::kFirstR>(buf, pl.tw, [&](int b, int m) {
+    dif_first<+1, L, true, M, DROW::kFirstR>(buf, pl.tw, [&](int b, int m) {
         return b < nb ? cmul(__ldg(xs + b * M + m), __ldg(cs + b * M + m)) : make_float2(0.f, 0.f);
     });
     __syncthreads();
     float2* dst = p.rowbuf + (size_t)blockIdx.y * N + (size_t)r0 * M;
-    DROW::template run_rest<+1, L>(buf, tw, [&](int b, int i, const float2* v) {
+    DROW::template run_rest<+1, L, true>(buf, tw, [&](int b, int i, const float2* v) {
         if (b >= nb) return;
         const unsigned e0 = (unsigned)(r0 + b) * (unsigned)i;  // < N
         float2 w = cmul(__ldg(pl.twN + (e0 & 255u)), __ldg(pl.twNhi + (e0 >> 8)));
@@ -198,22 +198,22 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
 }
 
 // columns: rowbuf[t][k1][n2] -> inverse DFT over k1 -> |y[N2 n1 + n2]|^2 -> per-CTA (max, first index) or grid
-template <int LOGT, class DCOL, int N2>
-__global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
+template <int LOGT, int NT, class DCOL, int N2>
+__global__ void __launch_bounds__(NT, 1024 / NT)
     gb_acq_inv_col_dif(PlanDev pl, GbAcqInvParams p)
 {
     constexpr int M = DCOL::kM, TILE = 1 << LOGT, N = N2 * M;
     constexpr int RL = DCOL::kLastR, NIL = DCOL::kLastNI;
-    using L = GbColTile<LOGT>;
+    using L = GbTile<LOGT, NT>;
     extern __shared__ __align__(16) float2 smem[];
-    __shared__ float s_mag[GB200_ACQ_THREADS / 32];
-    __shared__ unsigned s_idx[GB200_ACQ_THREADS / 32];
+    __shared__ float s_mag[NT / 32];
+    __shared__ unsigned s_idx[NT / 32];
     float2* buf = smem;
     float2* tw = buf + L::size(M);
     const int c0 = blockIdx.x * TILE;
-    for (int i = threadIdx.x; i < M; i += GB200_ACQ_THREADS) tw[i] = __ldg(pl.tw + i);
+    for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
     const float2* src = p.rowbuf + (size_t)blockIdx.y * N + c0;
-    dif_first<+1, L, M, DCOL::kFirstR>(buf, pl.tw, [&](int b, int m) {
+    dif_first<+1, L, false, M, DCOL::kFirstR>(buf, pl.tw, [&](int b, int m) {
         return ((N2 % TILE) == 0 || c0 + b < N2) ? __ldg(src + m * N2 + b) : make_float2(0.f, 0.f);
     });
     __syncthreads();
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
     float* grid = p.grid ? p.grid[handle] : nullptr;
     float best = -1.0f;
     unsigned best_i = 0xffffffffu;
-    DCOL::template run_rest<+1, L>(buf, tw, [&](int b, int i, const float2* v) {
+    DCOL::template run_rest<+1, L, false>(buf, tw, [&](int b, int i, const float2* v) {
         if ((N2 % TILE) != 0 && c0 + b >= N2) return;
         const int nbase = N2 * i + c0 + b - p.keep_offset;
 #pragma unroll
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
     __syncthreads();
     if (threadIdx.x == 0)
         {
-            for (int k = 1; k < GB200_ACQ_THREADS / 32; k++)
+            for (int k = 1; k < NT / 32; k++)
                 if (peak_better(s_mag[k], s_idx[k], best, best_i))
                     {
                         best = s_mag[k];
@@ -280,15 +280,17 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS, 4)
         }
 }
 
-// The (N1, N2) pairs with a fast path; tiles are fixed per pair.  f(GbDif<N1...>{}, GbDif<N2...>{}, GbInt<LOGT1>{}, GbInt<LOGT2>{})
+// The (N1, N2) pairs with a fast path.  f(GbDif<N1...>{}, GbDif<N2...>{}, GbInt<LOGT1>{}, GbInt<NT1>{}, GbInt<LOGT2>{}, GbInt<NT2>{});
+// LOGT1 / NT1: columns per CTA and threads of the column kernel, LOGT2 / NT2: rows per CTA and threads of the row kernel.
+// `variant` selects among alternative instantiations of one pair (tuning; 0 = default).
 template <class F>
-bool gb_with_dif_pair(int N1, int N2, F&& f)
+bool gb_with_dif_pair(int N1, int N2, int variant, F&& f)
 {
-#define GB_DIF_PAIR(n1, n2, D1, D2, LT1, LT2) \
-    if (N1 == n1 && N2 == n2)                 \
-        {                                     \
-            f(D1{}, D2{}, GbInt<LT1>{}, GbInt<LT2>{}); \
-            return true;                      \
+#define GB_DIF_PAIR(n1, n2, var, D1, D2, LT1, NT1, LT2, NT2)                                          \
+    if (N1 == n1 && N2 == n2 && variant == var)                                                       \
+        {                                                                                             \
+            f(D1{}, D2{}, GbInt<LT1>{}, GbInt<NT1>{}, GbInt<LT2>{}, GbInt<NT2>{});                    \
+            return true;                                                                              \
         }
     using D50 = GbDif<50, 10, 5>;
     using D80 = GbDif<80, 16, 5>;
@@ -296,29 +298,36 @@ bool gb_with_dif_pair(int N1, int N2, F&& f)
     using D125 = GbDif<125, 5, 5, 5>;
     using D128 = GbDif<128, 16, 8>;
     using D160 = GbDif<160, 16, 10>;
+    using D160b = GbDif<160, 8, 5, 4>;
     using D200 = GbDif<200, 8, 5, 5>;
+    using D200b = GbDif<200, 10, 5, 4>;
     using D250 = GbDif<250, 10, 5, 5>;
     using D320 = GbDif<320, 8, 8, 5>;
     using D400 = GbDif<400, 16, 5, 5>;
     using D500 = GbDif<500, 10, 10, 5>;
-    GB_DIF_PAIR(50, 80, D50, D80, 4, 4)      // 4000   GPS L1 C/A 1 ms @ 4 Msps
-    GB_DIF_PAIR(80, 100, D80, D100, 4, 4)    // 8000
-    GB_DIF_PAIR(125, 128, D125, D128, 4, 4)  // 16000
-    GB_DIF_PAIR(125, 160, D125, D160, 4, 4)  // 20000
-    GB_DIF_PAIR(125, 200, D125, D200, 3, 4)  // 25000  GPS L5 / Galileo E5a 1 ms @ 25 Msps
-    GB_DIF_PAIR(160, 200, D160, D200, 3, 4)  // 32000  Galileo E1 4 ms @ 8 Msps
-    GB_DIF_PAIR(200, 200, D200, D200, 3, 4)  // 40000
-    GB_DIF_PAIR(200, 250, D200, D250, 3, 3)  // 50000
-    GB_DIF_PAIR(250, 320, D250, D320, 3, 3)  // 80000
-    GB_DIF_PAIR(400, 500, D400, D500, 3, 3)  // 200000
+    GB_DIF_PAIR(50, 80, 0, D50, D80, 4, 128, 4, 128)       // 4000   GPS L1 C/A 1 ms @ 4 Msps
+    GB_DIF_PAIR(80, 100, 0, D80, D100, 4, 128, 4, 128)     // 8000
+    GB_DIF_PAIR(125, 128, 0, D125, D128, 4, 256, 4, 256)   // 16000
+    GB_DIF_PAIR(125, 160, 0, D125, D160, 4, 256, 4, 256)   // 20000
+    GB_DIF_PAIR(125, 200, 0, D125, D200, 3, 256, 4, 256)   // 25000  GPS L5 / Galileo E5a 1 ms @ 25 Msps
+    GB_DIF_PAIR(160, 200, 0, D160, D200, 4, 256, 4, 256)   // 32000  Galileo E1 4 ms @ 8 Msps
+    GB_DIF_PAIR(160, 200, 1, D160, D200, 3, 128, 4, 256)
+    GB_DIF_PAIR(160, 200, 2, D160b, D200, 3, 256, 4, 256)
+    GB_DIF_PAIR(160, 200, 3, D160, D200, 4, 256, 3, 128)
+    GB_DIF_PAIR(160, 200, 4, D160, D200b, 4, 256, 4, 256)
+    GB_DIF_PAIR(160, 200, 5, D160b, D200b, 3, 256, 3, 256)
+    GB_DIF_PAIR(200, 200, 0, D200, D200, 3, 256, 4, 256)   // 40000
+    GB_DIF_PAIR(200, 250, 0, D200, D250, 3, 256, 3, 256)   // 50000
+    GB_DIF_PAIR(250, 320, 0, D250, D320, 3, 256, 3, 256)   // 80000
+    GB_DIF_PAIR(400, 500, 0, D400, D500, 3, 256, 3, 256)   // 200000
 #undef GB_DIF_PAIR
     return false;
 }
 }  // namespace
 
-bool gb_acq_inverse_tiles(int N1, int N2, int* tile1, int* tile2)
+bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2)
 {
-    return gb_with_dif_pair(N1, N2, [&](auto, auto, auto lt1, auto lt2) {
+    return gb_with_dif_pair(N1, N2, variant, [&](auto, auto, auto lt1, auto, auto lt2, auto) {
         *tile1 = 1 << decltype(lt1)::value;
         *tile2 = 1 << decltype(lt2)::value;
     });
@@ -331,29 +340,30 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
         {
             e = cudaErrorInvalidValue;
             const PlanDev pdr = make_plan_dev(plan, false), pdc = make_plan_dev(plan, true);
-            gb_with_dif_pair(plan.N1, plan.N2, [&](auto d1, auto d2, auto lt1, auto lt2) {
+            gb_with_dif_pair(plan.N1, plan.N2, plan.inv_variant, [&](auto d1, auto d2, auto lt1, auto nt1, auto lt2, auto nt2) {
                 using D1 = decltype(d1);
                 using D2 = decltype(d2);
                 constexpr int LT1 = decltype(lt1)::value, LT2 = decltype(lt2)::value;
+                constexpr int NT1 = decltype(nt1)::value, NT2 = decltype(nt2)::value;
                 constexpr int T1 = 1 << LT1, T2 = 1 << LT2;
                 {
-                    auto k = gb_acq_inv_row_dif<LT2, D2, D1::kM>;
-                    const size_t sm = (GbRowTile<LT2, D2::kM>::size(D2::kM) + D2::kM + T2) * sizeof(float2);
+                    auto k = gb_acq_inv_row_dif<LT2, NT2, D2, D1::kM>;
+                    const size_t sm = (GbTile<LT2, NT2>::size(D2::kM) + D2::kM + T2) * sizeof(float2);
                     if ((e = set_smem(k, sm)) != cudaSuccess) return;
                     const dim3 grid((D1::kM + T2 - 1) / T2, p.n_transforms);
                     if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_ROW);
-                    k<<<grid, GB200_ACQ_THREADS, sm, st>>>(pdr, p);
+                    k<<<grid, NT2, sm, st>>>(pdr, p);
                     if (kt) gb_kt_end(kt);
                     if ((e = cudaGetLastError()) != cudaSuccess) return;
                     if (launches) (*launches)++;
                 }
                 {
-                    auto k = gb_acq_inv_col_dif<LT1, D1, D2::kM>;
-                    const size_t sm = (GbColTile<LT1>::size(D1::kM) + D1::kM) * sizeof(float2);
+                    auto k = gb_acq_inv_col_dif<LT1, NT1, D1, D2::kM>;
+                    const size_t sm = (GbTile<LT1, NT1>::size(D1::kM) + D1::kM) * sizeof(float2);
                     if ((e = set_smem(k, sm)) != cudaSuccess) return;
                     const dim3 grid((D2::kM + T1 - 1) / T1, p.n_transforms);
                     if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_COL);
-                    k<<<grid, GB200_ACQ_THREADS, sm, st>>>(pdc, p);
+                    k<<<grid, NT1, sm, st>>>(pdc, p);
                     if (kt) gb_kt_end(kt);
                     if ((e = cudaGetLastError()) != cudaSuccess) return;
                     if (launches) (*launches)++;

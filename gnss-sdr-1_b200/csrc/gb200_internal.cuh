@@ -110,6 +110,7 @@ struct GbFftPlan
     int tile1;  // columns (n2) per CTA in the column kernels (sub-FFT length N1)
     int tile2;  // rows (k1) per CTA in the row kernels (sub-FFT length N2)
     int inv_fast;   // 1: (N1, N2) has the compile-time in-place DIF inverse kernels (acq_dif.cuh)
+    int inv_variant;  // which instantiation of the pair (GB200_ACQ_VARIANT, tuning only)
     int inv_tile1;  // columns per CTA of the inverse column kernel actually launched (sizes the per-CTA peak array)
     const float2* tw1;  // device: W_N1^i, i < N1 (forward sign)
     const float2* tw2;  // device: W_N2^i, i < N2
@@ -161,7 +162,7 @@ void gb_kt_begin(void* ctx, int kernel_class);
 void gb_kt_end(void* ctx);
 cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt);
 cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt);
-bool gb_acq_inverse_tiles(int N1, int N2, int* tile1, int* tile2);  // true when the pair has the fast inverse kernels
+bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2);  // true when the pair has the fast inverse kernels
 cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches);
 cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type, int N, float* d_power, float* d_mag2_tmp, cudaStream_t st, int* launches);
 // grid-free path: reduce per-CTA maxima -> per handle peak

@@ -525,9 +525,13 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
         // compile-time specialised inverse kernels for the common (N1, N2) pairs; GB200_ACQ_GENERIC=1 forces the general path
         int t1 = 0, t2 = 0;
         const char* force = getenv("GB200_ACQ_GENERIC");
-        if (!(force && force[0] == '1') && gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, &t1, &t2))
+        const char* var = getenv("GB200_ACQ_VARIANT");
+        int variant = var ? atoi(var) : 0;
+        if (!gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, variant, &t1, &t2)) variant = 0;
+        if (!(force && force[0] == '1') && gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, variant, &t1, &t2))
             {
                 e.plan.inv_fast = 1;
+                e.plan.inv_variant = variant;
                 e.plan.inv_tile1 = t1;
             }
     }
