@@ -67,6 +67,8 @@ struct gb200_service
     uint64_t ring_capacity = 0, ring_slack = 0;
     std::map<int, GbPlanEntry> plans;
     uint64_t launches = 0;
+    gb200_trk_batch* cb = nullptr;  // arena of gb200_trk_correlate_batch (grow-only)
+    int cb_n = 0, cb_chunks = 0;
     std::string error = "no error";
     std::recursive_mutex mu;
     // scratch pools (grown on demand, reused)
@@ -174,6 +176,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     if (!s) return GB200_E_INVALID;
     cudaSetDevice(s->device);
     cudaStreamSynchronize(s->stream);
+    if (s->cb) gb200_trk_batch_destroy(s->cb);
     for (auto& r : s->rings)
         if (r.d_buf) cudaFree(r.d_buf);
     for (auto& kv : s->plans)
@@ -1627,12 +1630,33 @@ extern "C" int gb200_trk_batch_destroy(gb200_trk_batch* b)
 
 extern "C" int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_trk_req* reqs, float* outs_iq)
 {
-    gb200_trk_batch* b;
-    int rc = gb200_trk_batch_create(s, n, reqs, &b);
+    if (!s || n <= 0 || !reqs || !outs_iq) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    // grow-only arena owned by the service: repeated calls (one per block of epochs) do no allocation
+    int max_n = 1;
+    for (int i = 0; i < n; i++) max_n = std::max(max_n, reqs[i].n_samples);
+    const int chunks_cap = (max_n + 1023) / 1024;
+    if (!s->cb || s->cb_n < n || s->cb_chunks < chunks_cap)
+        {
+            if (s->cb) gb200_trk_batch_destroy(s->cb);
+            s->cb = nullptr;
+            s->cb_n = std::max(n, s->cb_n);
+            s->cb_chunks = std::max(chunks_cap, s->cb_chunks);
+            int rc = trk_batch_alloc(s, s->cb_n, s->cb_chunks, &s->cb);
+            if (rc)
+                {
+                    s->cb_n = s->cb_chunks = 0;
+                    return rc;
+                }
+        }
+    gb200_trk_batch* b = s->cb;
+    b->n = n;
+    int rc = trk_batch_stage(b, reqs);
     if (rc) return rc;
+    GB_CUDA(s, cudaMemcpyAsync(b->d_work, b->h_work.data(), sizeof(GbTrkWork) * n, cudaMemcpyHostToDevice, s->stream));
     rc = gb200_trk_batch_launch(b);
     if (!rc) rc = gb200_trk_batch_fetch(b, outs_iq);
-    gb200_trk_batch_destroy(b);
     return rc;
 }
 
