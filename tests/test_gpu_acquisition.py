@@ -223,3 +223,33 @@ def test_fast_inverse_lengths(service, fs, keep_grid):
         g, go = grids
         assert g.shape == go.shape
         assert np.max(np.abs(g - go)) <= 2e-5 * np.max(go)
+
+
+def test_bin_range_units_equal_full_grid(service):
+    """shard.py's Doppler-bin-range units (sub-grid + freq_offset_hz through the unchanged C ABI) merged with the reference's
+    tie-break reproduce the unsharded search exactly (C1 on 8 GPUs shards one PRN's grid by bin)."""
+    import gnss_b200 as gb
+    import shard
+
+    n = 4000
+    x = c1_signal(2 * n, seed=99)[:n]
+    code = gps_local_code(6)
+    service.push(2, x, gb.ITEM_32FC, 0)
+    full = gb.Acquisition(service, doppler_max=5000, doppler_step=250, threshold=0.008)
+    full.set_local_code(code)
+    rf = full.run(2, 0)
+    full.close()
+    for world in (2, 3, 8):
+        units = shard.acquisition_units(1, 5000, 250, world)
+        recs = []
+        for u, unit in enumerate(units):
+            a = gb.Acquisition(service, doppler_max=unit.doppler_max, doppler_step=unit.doppler_step, freq_offset_hz=unit.freq_offset_hz,
+                               threshold=0.008)
+            assert a.num_bins == unit.bin_hi - unit.bin_lo
+            a.set_local_code(code)
+            r = a.run(2, 0)
+            recs.append(shard.acq_record(u, unit, r.code_phase_index, r.doppler_bin, r.doppler_hz, r.peak_mag, r.input_power))
+            a.close()
+        m = shard.merge_acq_records(recs, 1, n, threshold=0.008)[0]
+        assert (m["code_phase_index"], m["doppler_bin"], m["doppler_hz"], m["decision"]) == (rf.code_phase_index, rf.doppler_bin, rf.doppler_hz, rf.decision)
+        assert m["peak_mag"] == rf.peak_mag and abs(m["test_statistic"] - rf.test_statistic) <= 1e-6 * rf.test_statistic
