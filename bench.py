@@ -235,7 +235,7 @@ def run_b200(args, rank, local_rank, world):
     host_stream = torch.empty(2 * STREAM_ITEMS, dtype=torch.int16).pin_memory()
     if world > 1:
         d_stream = torch.from_numpy(stream_np).to("cuda:%d" % dev) if rank == 0 else torch.empty(2 * STREAM_ITEMS, dtype=torch.int16, device="cuda:%d" % dev)
-        dist.broadcast(d_stream, src=0)
+        dist.broadcast(d_stream.view(torch.uint8), src=0)  # NCCL has no int16: ship the packed items as bytes
         host_stream.copy_(d_stream.cpu())
         del d_stream
     else:
