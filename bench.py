@@ -375,7 +375,7 @@ def run_b200(args, rank, local_rank, world):
         "config": {"workload": "C2: Galileo E1 4 ms PCPS acquisition (32 PRN x 80 bins x 32000 points, CFAR) + 5-tap VEML tracking with data-prompt tap "
                                "(32 ch x 248 epochs x 32000 samples), 8 Msps interleaved int16, per GPU",
                    "l2": "flushed (256 MB write) before every timed region",
-                   "kernel_events": "per-launch CUDA events on the library stream during the last timed step only", "acq_ms_per_step": tot_acq_ms / steps, "trk_ms_per_step": tot_trk_ms / steps},
+                   "kernel_events": "per-launch CUDA events on the library stream during the last timed step only", "acq_ms_per_step": tot_acq_ms / steps, "acq_ms_steps": [round(v, 4) for v in acq_ms], "trk_ms_per_step": tot_trk_ms / steps},
         "e2e": {"value": e2e_acq, "unit": "grid cells/s", "h2d_bytes_per_step": N_FFT * 4, "d2h_bytes_per_step": N_PRN * 56,
                 "ms_per_step": tot_e2e_acq_ms / steps},
         "gpu_launches": launches,

@@ -424,7 +424,7 @@ inline bool gb_fft_is_static(int M)
 {
     switch (M)
         {
-        case 50: case 80: case 125: case 128: case 160: case 200: case 250: case 320: case 400: case 500: case 800: case 1000: return true;
+        case 50: case 80: case 125: case 128: case 160: case 200: case 250: case 256: case 320: case 400: case 500: case 800: case 1000: return true;
         default: return false;
         }
 }
@@ -442,6 +442,7 @@ cudaError_t gb_with_fft(int M, int logt, F&& f)
             case 160: return gb_with_tile<GbFftStatic<160, 8, 5, 4>>(logt, true, f);
             case 200: return gb_with_tile<GbFftStatic<200, 8, 5, 5>>(logt, true, f);
             case 250: return gb_with_tile<GbFftStatic<250, 5, 5, 5, 2>>(logt, true, f);
+            case 256: return gb_with_tile<GbFftStatic<256, 8, 8, 4>>(logt, true, f);
             case 320: return gb_with_tile<GbFftStatic<320, 8, 8, 5>>(logt, true, f);
             case 400: return gb_with_tile<GbFftStatic<400, 8, 5, 5, 2>>(logt, true, f);
             case 500: return gb_with_tile<GbFftStatic<500, 5, 5, 5, 4>>(logt, true, f);

@@ -154,8 +154,8 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
 // Fast path: both sub-lengths compile-time (GbDif), in-place DIF tiles, first/last pass fused with global I/O.
 
 // rows: spectra x code spectrum -> inverse DFT over k2 -> x W_N^+(k1 n2) -> rowbuf[t][k1][n2]
-template <int LOGT, int NT, class DROW, int N1>
-__global__ void __launch_bounds__(NT, 1024 / NT)
+template <int LOGT, int NT, int OCC, class DROW, int N1>
+__global__ void __launch_bounds__(NT, OCC)
     gb_acq_inv_row_dif(PlanDev pl, GbAcqInvParams p)
 {
     constexpr int M = DROW::kM, TILE = 1 << LOGT, N = N1 * M;
@@ -198,8 +198,8 @@ __global__ void __launch_bounds__(NT, 1024 / NT)
 }
 
 // columns: rowbuf[t][k1][n2] -> inverse DFT over k1 -> |y[N2 n1 + n2]|^2 -> per-CTA (max, first index) or grid
-template <int LOGT, int NT, class DCOL, int N2>
-__global__ void __launch_bounds__(NT, 1024 / NT)
+template <int LOGT, int NT, int OCC, class DCOL, int N2>
+__global__ void __launch_bounds__(NT, OCC)
     gb_acq_inv_col_dif(PlanDev pl, GbAcqInvParams p)
 {
     constexpr int M = DCOL::kM, TILE = 1 << LOGT, N = N2 * M;
@@ -280,17 +280,23 @@ __global__ void __launch_bounds__(NT, 1024 / NT)
         }
 }
 
-// The (N1, N2) pairs with a fast path.  f(GbDif<N1...>{}, GbDif<N2...>{}, GbInt<LOGT1>{}, GbInt<NT1>{}, GbInt<LOGT2>{}, GbInt<NT2>{});
-// LOGT1 / NT1: columns per CTA and threads of the column kernel, LOGT2 / NT2: rows per CTA and threads of the row kernel.
-// `variant` selects among alternative instantiations of one pair (tuning; 0 = default).
+// The (N1, N2) pairs with a fast path.  f(GbDif<N1...>{}, GbDif<N2...>{}, column-kernel config, row-kernel config);
+// a config is GbCfg<LOGT, NT, OCC>: tile (columns / rows per CTA) = 2^LOGT, threads per CTA, CTAs per SM the register
+// allocation is bounded for.  `variant` selects among alternative instantiations of one pair (tuning; 0 = default).
+template <int LOGT_, int NT_, int OCC_>
+struct GbCfg
+{
+    static constexpr int LOGT = LOGT_, NT = NT_, OCC = OCC_;
+};
+
 template <class F>
 bool gb_with_dif_pair(int N1, int N2, int variant, F&& f)
 {
-#define GB_DIF_PAIR(n1, n2, var, D1, D2, LT1, NT1, LT2, NT2)                                          \
-    if (N1 == n1 && N2 == n2 && variant == var)                                                       \
-        {                                                                                             \
-            f(D1{}, D2{}, GbInt<LT1>{}, GbInt<NT1>{}, GbInt<LT2>{}, GbInt<NT2>{});                    \
-            return true;                                                                              \
+#define GB_DIF_PAIR(n1, n2, var, D1, D2, C1, C2)      \
+    if (N1 == n1 && N2 == n2 && variant == var)       \
+        {                                             \
+            f(D1{}, D2{}, C1{}, C2{});                \
+            return true;                              \
         }
     using D50 = GbDif<50, 10, 5>;
     using D80 = GbDif<80, 16, 5>;
@@ -299,37 +305,67 @@ bool gb_with_dif_pair(int N1, int N2, int variant, F&& f)
     using D128 = GbDif<128, 16, 8>;
     using D160 = GbDif<160, 16, 10>;
     using D160b = GbDif<160, 8, 5, 4>;
+    using D160c = GbDif<160, 10, 16>;
     using D200 = GbDif<200, 8, 5, 5>;
-    using D200b = GbDif<200, 10, 5, 4>;
+    using D200c = GbDif<200, 5, 8, 5>;
     using D250 = GbDif<250, 10, 5, 5>;
+    using D256 = GbDif<256, 16, 16>;
+    using D125b = GbDif<125, 25, 5>;
     using D320 = GbDif<320, 8, 8, 5>;
     using D400 = GbDif<400, 16, 5, 5>;
     using D500 = GbDif<500, 10, 10, 5>;
-    GB_DIF_PAIR(50, 80, 0, D50, D80, 4, 128, 4, 128)       // 4000   GPS L1 C/A 1 ms @ 4 Msps
-    GB_DIF_PAIR(80, 100, 0, D80, D100, 4, 128, 4, 128)     // 8000
-    GB_DIF_PAIR(125, 128, 0, D125, D128, 4, 256, 4, 256)   // 16000
-    GB_DIF_PAIR(125, 160, 0, D125, D160, 4, 256, 4, 256)   // 20000
-    GB_DIF_PAIR(125, 200, 0, D125, D200, 3, 256, 4, 256)   // 25000  GPS L5 / Galileo E5a 1 ms @ 25 Msps
-    GB_DIF_PAIR(160, 200, 0, D160, D200, 4, 256, 4, 256)   // 32000  Galileo E1 4 ms @ 8 Msps
-    GB_DIF_PAIR(160, 200, 1, D160, D200, 3, 128, 4, 256)
-    GB_DIF_PAIR(160, 200, 2, D160b, D200, 3, 256, 4, 256)
-    GB_DIF_PAIR(160, 200, 3, D160, D200, 4, 256, 3, 128)
-    GB_DIF_PAIR(160, 200, 4, D160, D200b, 4, 256, 4, 256)
-    GB_DIF_PAIR(160, 200, 5, D160b, D200b, 3, 256, 3, 256)
-    GB_DIF_PAIR(200, 200, 0, D200, D200, 3, 256, 4, 256)   // 40000
-    GB_DIF_PAIR(200, 250, 0, D200, D250, 3, 256, 3, 256)   // 50000
-    GB_DIF_PAIR(250, 320, 0, D250, D320, 3, 256, 3, 256)   // 80000
-    GB_DIF_PAIR(400, 500, 0, D400, D500, 3, 256, 3, 256)   // 200000
+    using S128 = GbCfg<4, 128, 8>;
+    using S256 = GbCfg<4, 256, 4>;
+    using E256 = GbCfg<3, 256, 4>;
+    using S256o5 = GbCfg<4, 256, 5>;
+    using S256o6 = GbCfg<4, 256, 6>;
+    using S256o3 = GbCfg<4, 256, 3>;
+    using E128 = GbCfg<3, 128, 8>;
+    GB_DIF_PAIR(50, 80, 0, D50, D80, S128, S128)       // 4000   GPS L1 C/A 1 ms @ 4 Msps
+    GB_DIF_PAIR(80, 100, 0, D80, D100, S128, S128)     // 8000
+    GB_DIF_PAIR(125, 128, 0, D125, D128, S256, S256)   // 16000
+    GB_DIF_PAIR(125, 160, 0, D125, D160, S256, S256)   // 20000
+    GB_DIF_PAIR(125, 200, 0, D125, D200, E256, S256)   // 25000  GPS L5 / Galileo E5a 1 ms @ 25 Msps
+    GB_DIF_PAIR(125, 256, 0, D125, D256, S256, S256)   // 32000, alternative split (GB200_ACQ_SPLIT=125): 2 KB rows, 128 B aligned, but the 16x16 row passes conflict in shared memory
+    GB_DIF_PAIR(125, 256, 1, D125, D256, S256o5, S256)
+    GB_DIF_PAIR(125, 256, 2, D125, D256, S256o6, S256o5)
+    GB_DIF_PAIR(125, 256, 3, D125, D256, S128, S128)
+    GB_DIF_PAIR(160, 200, 0, D160, D200, S256, S256)   // 32000  Galileo E1 4 ms @ 8 Msps
+    GB_DIF_PAIR(160, 200, 1, D160, D200, S256, S256o5)
+    GB_DIF_PAIR(160, 200, 2, D160, D200, S256, S256o6)
+    GB_DIF_PAIR(160, 200, 3, D160b, D200, S256o5, S256)
+    GB_DIF_PAIR(160, 200, 4, D160b, D200, S256o6, S256)
+    GB_DIF_PAIR(160, 200, 5, D160c, D200c, S256, S256)
+    GB_DIF_PAIR(160, 200, 6, D160, D200, S256o3, S256o3)
+    GB_DIF_PAIR(160, 200, 7, D160, D200, E128, E128)
+    GB_DIF_PAIR(200, 200, 0, D200, D200, E256, S256)   // 40000
+    GB_DIF_PAIR(200, 250, 0, D200, D250, E256, E256)   // 50000
+    GB_DIF_PAIR(250, 320, 0, D250, D320, E256, E256)   // 80000
+    GB_DIF_PAIR(400, 500, 0, D400, D500, E256, E256)   // 200000
 #undef GB_DIF_PAIR
     return false;
 }
 }  // namespace
 
+// (N1, N2) splits with a fast path, in order of preference for a given N = N1 * N2
+bool gb_acq_preferred_split(int N, int avoid_n1, int* n1, int* n2)
+{
+    static const int pairs[][2] = {{50, 80}, {80, 100}, {125, 128}, {125, 160}, {125, 200}, {160, 200}, {125, 256}, {200, 200}, {200, 250}, {250, 320}, {400, 500}};
+    for (const auto& p : pairs)
+        if ((long long)p[0] * p[1] == N && p[0] != avoid_n1)
+            {
+                *n1 = p[0];
+                *n2 = p[1];
+                return true;
+            }
+    return false;
+}
+
 bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2)
 {
-    return gb_with_dif_pair(N1, N2, variant, [&](auto, auto, auto lt1, auto, auto lt2, auto) {
-        *tile1 = 1 << decltype(lt1)::value;
-        *tile2 = 1 << decltype(lt2)::value;
+    return gb_with_dif_pair(N1, N2, variant, [&](auto, auto, auto c1, auto c2) {
+        *tile1 = 1 << decltype(c1)::LOGT;
+        *tile2 = 1 << decltype(c2)::LOGT;
     });
 }
 
@@ -340,14 +376,15 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
         {
             e = cudaErrorInvalidValue;
             const PlanDev pdr = make_plan_dev(plan, false), pdc = make_plan_dev(plan, true);
-            gb_with_dif_pair(plan.N1, plan.N2, plan.inv_variant, [&](auto d1, auto d2, auto lt1, auto nt1, auto lt2, auto nt2) {
+            gb_with_dif_pair(plan.N1, plan.N2, plan.inv_variant, [&](auto d1, auto d2, auto c1, auto c2) {
                 using D1 = decltype(d1);
                 using D2 = decltype(d2);
-                constexpr int LT1 = decltype(lt1)::value, LT2 = decltype(lt2)::value;
-                constexpr int NT1 = decltype(nt1)::value, NT2 = decltype(nt2)::value;
+                using C1 = decltype(c1);
+                using C2 = decltype(c2);
+                constexpr int LT1 = C1::LOGT, LT2 = C2::LOGT, NT1 = C1::NT, NT2 = C2::NT;
                 constexpr int T1 = 1 << LT1, T2 = 1 << LT2;
                 {
-                    auto k = gb_acq_inv_row_dif<LT2, NT2, D2, D1::kM>;
+                    auto k = gb_acq_inv_row_dif<LT2, NT2, C2::OCC, D2, D1::kM>;
                     const size_t sm = (GbTile<LT2, NT2>::size(D2::kM) + D2::kM + T2) * sizeof(float2);
                     if ((e = set_smem(k, sm)) != cudaSuccess) return;
                     const dim3 grid((D1::kM + T2 - 1) / T2, p.n_transforms);
@@ -358,7 +395,7 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
                     if (launches) (*launches)++;
                 }
                 {
-                    auto k = gb_acq_inv_col_dif<LT1, NT1, D1, D2::kM>;
+                    auto k = gb_acq_inv_col_dif<LT1, NT1, C1::OCC, D1, D2::kM>;
                     const size_t sm = (GbTile<LT1, NT1>::size(D1::kM) + D1::kM) * sizeof(float2);
                     if ((e = set_smem(k, sm)) != cudaSuccess) return;
                     const dim3 grid((D2::kM + T1 - 1) / T1, p.n_transforms);

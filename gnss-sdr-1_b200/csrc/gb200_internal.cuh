@@ -162,7 +162,8 @@ void gb_kt_begin(void* ctx, int kernel_class);
 void gb_kt_end(void* ctx);
 cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt);
 cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt);
-bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2);  // true when the pair has the fast inverse kernels
+bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2);
+bool gb_acq_preferred_split(int N, int avoid_n1, int* n1, int* n2);  // a split of N that has the fast inverse kernels  // true when the pair has the fast inverse kernels
 cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches);
 cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type, int N, float* d_power, float* d_mag2_tmp, cudaStream_t st, int* launches);
 // grid-free path: reduce per-CTA maxima -> per handle peak

@@ -63,6 +63,8 @@ struct gb200_service
 {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // second lane for the inverse chunks (fills the tail of the other lane's kernels)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::vector<GbRing> rings;
     uint64_t ring_capacity = 0, ring_slack = 0;
     std::map<int, GbPlanEntry> plans;
@@ -72,8 +74,8 @@ struct gb200_service
     std::string error = "no error";
     std::recursive_mutex mu;
     // scratch pools (grown on demand, reused)
-    void* d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    void* d_scratch[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratch_bytes[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     void* h_pinned = nullptr;
     size_t h_pinned_bytes = 0;
     int sm_count = 148;
@@ -157,7 +159,10 @@ extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service*
     gb200_service* s = new gb200_service();
     s->device = dev;
     s->sm_count = prop.multiProcessorCount;
-    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess)
+    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming) != cudaSuccess)
         {
             g_global_error = "cudaStreamCreate failed";
             delete s;
@@ -186,12 +191,15 @@ extern "C" int gb200_service_destroy(gb200_service* s)
             if (kv.second.d_twN) cudaFree(kv.second.d_twN);
             if (kv.second.d_twNhi) cudaFree(kv.second.d_twNhi);
         }
-    for (int i = 0; i < 8; i++)
+    for (int i = 0; i < 10; i++)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->d_flush) cudaFree(s->d_flush);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+    if (s->ev_join) cudaEventDestroy(s->ev_join);
+    if (s->stream2) cudaStreamDestroy(s->stream2);
     cudaStreamDestroy(s->stream);
     delete s;
     return GB200_OK;
@@ -509,6 +517,25 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
             if (!pick_tile(n1) || !pick_tile(n2)) continue;
             best1 = n1;
         }
+    {
+        // prefer a split with compile-time inverse kernels (GB200_ACQ_SPLIT=<n1> steers away from it, tuning only)
+        const char* force = getenv("GB200_ACQ_GENERIC");
+        const char* split = getenv("GB200_ACQ_SPLIT");
+        int p1 = 0, p2 = 0, r[GB200_MAX_RADIX_PASSES], nr;
+        if (!(force && force[0] == '1'))
+            {
+                bool ok = false;
+                if (split && atoi(split) > 0 && N % atoi(split) == 0)
+                    {
+                        p1 = atoi(split);
+                        p2 = N / p1;
+                        ok = true;
+                    }
+                else
+                    ok = gb_acq_preferred_split(N, 0, &p1, &p2);
+                if (ok && factor_radices(p1, r, &nr) && factor_radices(p2, r, &nr) && pick_tile(p1) && pick_tile(p2)) best1 = p1;
+            }
+    }
     if (!best1)
         {
             s->set_error("FFT length " + std::to_string(N) + " unsupported (prime factor > 64 or sub-transform too long)");
@@ -1039,19 +1066,33 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                 GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, N, d_power, (g.grid && !a0->use_cfar) ? a0->d_tmp : nullptr, s->stream, &l));
             // inverse side in L2-sized chunks of transforms
             const int T = bins * (int)g.members.size();
-            const size_t l2_budget = 48ull << 20;
+            // Two lanes: chunk c runs on stream (c & 1) with its own row buffer, so one lane's column kernel overlaps the
+            // other lane's row kernel and each kernel's ragged last wave is filled by the other lane.  Both row buffers
+            // together stay within the L2 budget.  With per-launch event timing on, everything stays on one stream.
+            const bool two_lanes = !s->kt.enabled && !getenv("GB200_ACQ_ONE_LANE");
+            const size_t l2_budget = two_lanes ? (24ull << 20) : (48ull << 20);
             int chunkT = (int)std::max<size_t>(1, l2_budget / (sizeof(float2) * (size_t)N));
             chunkT = std::min(chunkT, T);
             const int tiles = (plan.N2 + plan.inv_tile1 - 1) / plan.inv_tile1;
-            void *d_row, *d_part;
-            if ((rc = s->scratch(2, sizeof(float2) * (size_t)N * chunkT, &d_row))) return rc;
+            void *d_row, *d_row2 = nullptr, *d_part;
+            // lane 0's buffer is sized for the one-lane chunk so that toggling event timing never reallocates
+            if ((rc = s->scratch(2, sizeof(float2) * (size_t)N * std::min<size_t>(T, std::max<size_t>(1, (48ull << 20) / (sizeof(float2) * (size_t)N))), &d_row))) return rc;
+            if (two_lanes && (rc = s->scratch(8, sizeof(float2) * (size_t)N * chunkT, &d_row2))) return rc;
             if ((rc = s->scratch(3, sizeof(GbPeak) * (size_t)T * tiles, &d_part))) return rc;
-            for (int t0 = 0; t0 < T; t0 += chunkT)
+            const bool fork = two_lanes && T > chunkT;
+            if (fork)
                 {
+                    GB_CUDA(s, cudaEventRecord(s->ev_fork, s->stream));
+                    GB_CUDA(s, cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
+                }
+            int lane = 0;
+            for (int t0 = 0; t0 < T; t0 += chunkT, lane ^= 1)
+                {
+                    const bool second = fork && lane;
                     GbAcqInvParams ip;
                     ip.spectra = (const float2*)d_spec;
                     ip.code_fft = (const float2* const*)((char*)d_up + g.off_code);
-                    ip.rowbuf = (float2*)d_row;
+                    ip.rowbuf = (float2*)(second ? d_row2 : d_row);
                     ip.n_bins = bins;
                     ip.first_transform = t0;
                     ip.n_transforms = std::min(chunkT, T - t0);
@@ -1061,7 +1102,12 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     ip.accumulate = (g.grid && a0->dwell_counter >= 1) ? 1 : 0;  // this is dwell number dwell_counter+1
                     ip.partial = (GbPeak*)d_part;
                     ip.tmpbuf = (g.grid && !a0->use_cfar) ? (float* const*)((char*)d_up + g.off_tmp) : nullptr;
-                    GB_CUDA(s, gb_acq_inverse(plan, ip, s->stream, &l, s));
+                    GB_CUDA(s, gb_acq_inverse(plan, ip, second ? s->stream2 : s->stream, &l, s));
+                }
+            if (fork)
+                {
+                    GB_CUDA(s, cudaEventRecord(s->ev_join, s->stream2));
+                    GB_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_join, 0));
                 }
             GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
             if (g.grid)

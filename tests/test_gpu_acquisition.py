@@ -232,7 +232,7 @@ def test_bin_range_units_equal_full_grid(service):
     import shard
 
     n = 4000
-    x = c1_signal(2 * n, seed=99)[:n]
+    x = c1_signal(2 * n, seed=99)[1][:n]
     code = gps_local_code(6)
     service.push(2, x, gb.ITEM_32FC, 0)
     full = gb.Acquisition(service, doppler_max=5000, doppler_step=250, threshold=0.008)
