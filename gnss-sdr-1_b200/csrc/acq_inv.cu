@@ -198,7 +198,9 @@ __global__ void __launch_bounds__(NT, OCC)
 }
 
 // columns: rowbuf[t][k1][n2] -> inverse DFT over k1 -> |y[N2 n1 + n2]|^2 -> per-CTA (max, first index) or grid
-template <int LOGT, int NT, int OCC, class DCOL, int N2>
+// MODE 0: arg-max over the whole row (keep_offset == 0, keep_len == N: the common single-dwell CFAR search);
+// MODE 1: arg-max over a kept window (bit transition); MODE 2: magnitude grid written / accumulated.
+template <int LOGT, int NT, int OCC, class DCOL, int N2, int MODE>
 __global__ void __launch_bounds__(NT, OCC)
     gb_acq_inv_col_dif(PlanDev pl, GbAcqInvParams p)
 {
@@ -219,52 +221,61 @@ __global__ void __launch_bounds__(NT, OCC)
     __syncthreads();
     const int t = p.first_transform + blockIdx.y;
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
-    float* grid = p.grid ? p.grid[handle] : nullptr;
+    float* grid = MODE == 2 ? p.grid[handle] + (size_t)bin * p.keep_len : nullptr;
+    float* tmp = (MODE == 2 && p.accumulate && p.tmpbuf && p.tmpbuf[handle] && bin == p.n_bins - 1) ? p.tmpbuf[handle] : nullptr;
+    // Within one work item the outputs come in increasing n, so "first maximum wins" (volk_gnsssdr_32f_index_max_32u) is
+    // a strict '>' there; items, lanes and warps are then merged with the full (magnitude, index) ordering.
     float best = -1.0f;
     unsigned best_i = 0xffffffffu;
     DCOL::template run_rest<+1, L, false>(buf, tw, [&](int b, int i, const float2* v) {
         if ((N2 % TILE) != 0 && c0 + b >= N2) return;
-        const int nbase = N2 * i + c0 + b - p.keep_offset;
+        const int nbase = N2 * i + c0 + b - (MODE == 0 ? 0 : p.keep_offset);
+        float ibest = -1.0f;
+        unsigned ibest_i = 0xffffffffu;
 #pragma unroll
         for (int r = 0; r < RL; r++)
             {
                 const int n = nbase + r * (NIL * N2);
-                if (n < 0 || n >= p.keep_len) continue;
+                if (MODE != 0 && (n < 0 || n >= p.keep_len)) continue;
                 const float mag = __fadd_rn(__fmul_rn(v[r].x, v[r].x), __fmul_rn(v[r].y, v[r].y));  // volk_32fc_magnitude_squared_32f
-                if (grid)
+                if (MODE == 2)
                     {
-                        float* g = grid + (size_t)bin * p.keep_len + n;
-                        *g = p.accumulate ? __fadd_rn(*g, mag) : mag;
-                        if (p.accumulate && p.tmpbuf && p.tmpbuf[handle] && bin == p.n_bins - 1) p.tmpbuf[handle][n] = mag;
+                        grid[n] = p.accumulate ? __fadd_rn(grid[n], mag) : mag;
+                        if (tmp) tmp[n] = mag;
                     }
-                else if (peak_better(mag, (unsigned)n, best, best_i))
+                else if (mag > ibest)
                     {
-                        best = mag;
-                        best_i = (unsigned)n;
+                        ibest = mag;
+                        ibest_i = (unsigned)n;
                     }
             }
+        if (MODE != 2 && peak_better(ibest, ibest_i, best, best_i))
+            {
+                best = ibest;
+                best_i = ibest_i;
+            }
     });
-    if (grid) return;
+    if constexpr (MODE != 2)
+        {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-        {
-            const float om = __shfl_down_sync(0xffffffffu, best, o);
-            const unsigned oi = __shfl_down_sync(0xffffffffu, best_i, o);
-            if (peak_better(om, oi, best, best_i))
+            for (int o = 16; o > 0; o >>= 1)
                 {
-                    best = om;
-                    best_i = oi;
+                    const float om = __shfl_down_sync(0xffffffffu, best, o);
+                    const unsigned oi = __shfl_down_sync(0xffffffffu, best_i, o);
+                    if (peak_better(om, oi, best, best_i))
+                        {
+                            best = om;
+                            best_i = oi;
+                        }
                 }
-        }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0)
-        {
-            s_mag[warp] = best;
-            s_idx[warp] = best_i;
-        }
-    __syncthreads();
-    if (threadIdx.x == 0)
-        {
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            if (lane == 0)
+                {
+                    s_mag[warp] = best;
+                    s_idx[warp] = best_i;
+                }
+            __syncthreads();
+            if (threadIdx.x != 0) return;
             for (int k = 1; k < NT / 32; k++)
                 if (peak_better(s_mag[k], s_idx[k], best, best_i))
                     {
@@ -395,7 +406,9 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
                     if (launches) (*launches)++;
                 }
                 {
-                    auto k = gb_acq_inv_col_dif<LT1, NT1, C1::OCC, D1, D2::kM>;
+                    const int mode = p.grid ? 2 : ((p.keep_offset == 0 && p.keep_len == plan.N) ? 0 : 1);
+                    auto k = mode == 2 ? gb_acq_inv_col_dif<LT1, NT1, C1::OCC, D1, D2::kM, 2>
+                                       : (mode == 1 ? gb_acq_inv_col_dif<LT1, NT1, C1::OCC, D1, D2::kM, 1> : gb_acq_inv_col_dif<LT1, NT1, C1::OCC, D1, D2::kM, 0>);
                     const size_t sm = (GbTile<LT1, NT1>::size(D1::kM) + D1::kM) * sizeof(float2);
                     if ((e = set_smem(k, sm)) != cudaSuccess) return;
                     const dim3 grid((D2::kM + T1 - 1) / T1, p.n_transforms);

@@ -253,3 +253,18 @@ def test_bin_range_units_equal_full_grid(service):
         m = shard.merge_acq_records(recs, 1, n, threshold=0.008)[0]
         assert (m["code_phase_index"], m["doppler_bin"], m["doppler_hz"], m["decision"]) == (rf.code_phase_index, rf.doppler_bin, rf.doppler_hz, rf.decision)
         assert m["peak_mag"] == rf.peak_mag and abs(m["test_statistic"] - rf.test_statistic) <= 1e-6 * rf.test_statistic
+
+
+@pytest.mark.parametrize("n", [4000, 32000, 6625])
+def test_exact_ties_first_maximum_wins(service, n):
+    """All-equal magnitudes (zero input): the reference's scan keeps the FIRST maximum (volk_gnsssdr_32f_index_max_32u, strict '>'
+    over bins in ascending order), i.e. code phase 0 of Doppler bin 0 -- on the fast (4000, 32000) and general (6625) inverse paths."""
+    import gnss_b200 as gb
+
+    fs = n * 1000
+    cfg = dict(doppler_max=1000, doppler_step=250, threshold=0.5, samples_per_chip=2, fs_in=fs, samples_per_ms=float(n), samples_per_code=float(n))
+    code = np.zeros(n, np.complex64)
+    code[0] = 1.0
+    (pairs, _) = run_pair(service, cfg, code, np.zeros(n, np.complex64))
+    r, ro = pairs[0]
+    assert (r.code_phase_index, r.doppler_bin) == (ro.code_phase_index, ro.doppler_bin) == (0, 0)
