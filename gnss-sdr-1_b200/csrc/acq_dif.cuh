@@ -151,11 +151,26 @@ __device__ __forceinline__ void dif_first(float2* __restrict__ buf, const float2
                     bflyx<SIGN, R>(v);
                     float2* p = buf + b + i * L::MS;
                     p[0] = v[0];
-#pragma unroll
-                    for (int r = 1; r < R; r++)
+                    if (IFAST)
                         {
-                            const float2 w = __ldg(twg + r * i);  // r*i < M
-                            p[r * S * L::MS] = SIGN > 0 ? cmul_conj(v[r], w) : cmul(v[r], w);
+                            // lanes run along i: the table reads W^(r i) would scatter over r times more cache lines per leg,
+                            // and this kernel is bound by the L1 data pipe -- build the powers from W^i in registers instead
+                            // (products of two earlier powers: depth log2 R)
+                            float2 w[R];
+                            w[1] = __ldg(twg + i);
+#pragma unroll
+                            for (int r = 2; r < R; r++) w[r] = cmul(w[r / 2], w[r - r / 2]);
+#pragma unroll
+                            for (int r = 1; r < R; r++) p[r * S * L::MS] = SIGN > 0 ? cmul_conj(v[r], w[r]) : cmul(v[r], w[r]);
+                        }
+                    else
+                        {
+#pragma unroll
+                            for (int r = 1; r < R; r++)
+                                {
+                                    const float2 w = __ldg(twg + r * i);  // r*i < M; lanes run along b: a broadcast
+                                    p[r * S * L::MS] = SIGN > 0 ? cmul_conj(v[r], w) : cmul(v[r], w);
+                                }
                         }
                 }
         }

@@ -162,16 +162,27 @@ __global__ void __launch_bounds__(NT, OCC)
     constexpr int RL = DROW::kLastR, NIL = DROW::kLastNI;
     using L = GbTile<LOGT, NT>;
     extern __shared__ __align__(16) float2 smem[];
+    constexpr int IL = 8, IH = (NIL + IL - 1) / IL;  // last-pass item i = IL * ih + il
     float2* buf = smem;
     float2* tw = buf + L::size(M);
-    float2* step = tw + M;
+    float2* step = tw + M;          // [TILE]      W_N^(k1 NIL): ratio between consecutive outputs of one item
+    float2* tlo = step + TILE;      // [TILE][IL]  W_N^(k1 il)
+    float2* thi = tlo + TILE * IL;  // [TILE][IH]  W_N^(k1 IL ih)      (all forward sign; k1 = r0 + b)
     const int r0 = blockIdx.x * TILE;
     const int nb = min(TILE, N1 - r0);
     for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
-    if (threadIdx.x < TILE)
+    for (int q = threadIdx.x; q < TILE * (1 + IL + IH); q += NT)
         {
-            const unsigned e = (unsigned)(r0 + threadIdx.x) * (unsigned)NIL % (unsigned)N;
-            step[threadIdx.x] = cmul(__ldg(pl.twN + (e & 255u)), __ldg(pl.twNhi + (e >> 8)));
+            const int b = q / (1 + IL + IH), c = q - b * (1 + IL + IH);
+            const unsigned k1 = (unsigned)(r0 + b);
+            const unsigned e = (c == 0 ? k1 * (unsigned)NIL : (c <= IL ? k1 * (unsigned)(c - 1) : k1 * (unsigned)(IL * (c - 1 - IL)))) % (unsigned)N;
+            const float2 w = cmul(__ldg(pl.twN + (e & 255u)), __ldg(pl.twNhi + (e >> 8)));
+            if (c == 0)
+                step[b] = w;
+            else if (c <= IL)
+                tlo[b * IL + c - 1] = w;
+            else
+                thi[b * IH + c - 1 - IL] = w;
         }
     const int t = p.first_transform + blockIdx.y;
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
@@ -184,8 +195,7 @@ __global__ void __launch_bounds__(NT, OCC)
     float2* dst = p.rowbuf + (size_t)blockIdx.y * N + (size_t)r0 * M;
     DROW::template run_rest<+1, L, true>(buf, tw, [&](int b, int i, const float2* v) {
         if (b >= nb) return;
-        const unsigned e0 = (unsigned)(r0 + b) * (unsigned)i;  // < N
-        float2 w = cmul(__ldg(pl.twN + (e0 & 255u)), __ldg(pl.twNhi + (e0 >> 8)));
+        float2 w = cmul(tlo[b * IL + (i & (IL - 1))], thi[b * IH + (i / IL)]);  // W_N^(k1 i)
         const float2 ws = step[b];
         float2* d = dst + b * M + i;
 #pragma unroll
@@ -197,7 +207,6 @@ __global__ void __launch_bounds__(NT, OCC)
     });
 }
 
-// columns: rowbuf[t][k1][n2] -> inverse DFT over k1 -> |y[N2 n1 + n2]|^2 -> per-CTA (max, first index) or grid
 // MODE 0: arg-max over the whole row (keep_offset == 0, keep_len == N: the common single-dwell CFAR search);
 // MODE 1: arg-max over a kept window (bit transition); MODE 2: magnitude grid written / accumulated.
 template <int LOGT, int NT, int OCC, class DCOL, int N2, int MODE>
@@ -396,7 +405,7 @@ cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaS
                 constexpr int T1 = 1 << LT1, T2 = 1 << LT2;
                 {
                     auto k = gb_acq_inv_row_dif<LT2, NT2, C2::OCC, D2, D1::kM>;
-                    const size_t sm = (GbTile<LT2, NT2>::size(D2::kM) + D2::kM + T2) * sizeof(float2);
+                    const size_t sm = (GbTile<LT2, NT2>::size(D2::kM) + D2::kM + T2 * (1 + 8 + (D2::kLastNI + 7) / 8)) * sizeof(float2);
                     if ((e = set_smem(k, sm)) != cudaSuccess) return;
                     const dim3 grid((D1::kM + T2 - 1) / T2, p.n_transforms);
                     if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_ROW);
