@@ -1,0 +1,112 @@
+// B200_Pcps_Acquisition: host mirror of the pcps_acquisition block's control surface
+// (src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition.h:93-250 and the AcquisitionInterface calls the Channel
+// makes on its adapter, src/core/interfaces/acquisition_interface.h:56-72) on top of the C ABI.  GNU Radio's scheduler is
+// replaced by an explicit run(samp_count): the block's own buffering state machine (general_work, :941-1054) only decides
+// WHICH d_consumed_samples items to search, and here those are named by their absolute sample index in the device ring.
+#pragma once
+#include <complex>
+#include <cstdint>
+#include <string>
+
+#include "../../include/gnss_b200.h"
+
+namespace gb200
+{
+// the Gnss_Synchro fields acquisition writes (gnss_synchro.h:54-58)
+struct AcqSynchro
+{
+    double Acq_delay_samples = 0.0;
+    double Acq_doppler_hz = 0.0;
+    uint64_t Acq_samplestamp_samples = 0;
+    uint32_t Acq_doppler_step = 0;
+    bool Flag_valid_acquisition = false;
+};
+
+class B200_Pcps_Acquisition
+{
+public:
+    // conf = the Acq_Conf the adapter fills (acq_conf.h:39-68); item_type = GB200_ITEM_* of the stream searched
+    B200_Pcps_Acquisition(gb200_service* service, const gb200_acq_cfg& conf, int stream_id) : s_(service), conf_(conf), stream_(stream_id)
+    {
+        ok_ = gb200_acq_create(s_, &conf_, &h_) == GB200_OK;
+    }
+    ~B200_Pcps_Acquisition()
+    {
+        if (h_) gb200_acq_destroy(h_);
+    }
+    B200_Pcps_Acquisition(const B200_Pcps_Acquisition&) = delete;
+    B200_Pcps_Acquisition& operator=(const B200_Pcps_Acquisition&) = delete;
+    bool ok() const { return ok_; }
+
+    // ---- AcquisitionInterface, in the order Channel calls it (channel.cc:60-104) ----
+    void set_channel(unsigned channel) { channel_ = channel; }
+    void set_gnss_synchro(AcqSynchro* synchro) { synchro_ = synchro; }          // borrowed, like Gnss_Synchro* (pcps_acquisition.h:133)
+    void set_doppler_max(unsigned doppler_max)
+    {
+        conf_.doppler_max = doppler_max;
+        gb200_acq_set_doppler(h_, conf_.doppler_max, conf_.doppler_step, conf_.freq_offset_hz);
+    }
+    void set_doppler_step(unsigned doppler_step)
+    {
+        conf_.doppler_step = doppler_step;
+        gb200_acq_set_doppler(h_, conf_.doppler_max, conf_.doppler_step, conf_.freq_offset_hz);
+    }
+    void set_threshold(float threshold) { gb200_acq_set_threshold(h_, threshold); }
+    void init() { gb200_acq_set_doppler(h_, conf_.doppler_max, conf_.doppler_step, conf_.freq_offset_hz); }  // (:313-370): grid rebuilt, nothing stored
+    // = pcps_acquisition::set_local_code (:239-274): `code` has d_consumed_samples (or one code period, zero-padded inside) items
+    bool set_local_code(const std::complex<float>* code, size_t n_items)
+    {
+        return gb200_acq_set_local_code(h_, reinterpret_cast<const float*>(code), n_items) == GB200_OK;
+    }
+    void set_state(int state)  // (:393-415): entering state 1 re-arms the search
+    {
+        state_ = state;
+        if (state == 1) gb200_acq_reset(h_);
+    }
+    void reset() { set_state(1); }  // ChannelFsm::start_acquisition -> adapter reset() -> set_active(true) (:226-229)
+    void stop_acquisition() { state_ = 0; }
+    signed int mag() const { return static_cast<signed int>(mag_); }
+    unsigned fft_size() const { return gb200_acq_fft_size(h_); }
+    unsigned consumed_samples() const { return gb200_acq_consumed_samples(h_); }
+
+    // = acquisition_core(samp_count) (:668-929) on the items [samp_count, samp_count + d_consumed_samples) of the stream.
+    // Returns the event the block would send: 1 positive, 2 negative (pcps_acquisition.cc:418-459), 0 none yet
+    // (more dwells wanted, or step two armed: call run() again with the next / the same block).
+    int run(uint64_t samp_count, gb200_acq_result* detail = nullptr)
+    {
+        if (state_ == 0) return 0;
+        gb200_acq_result r;
+        if (gb200_acq_run(h_, stream_, samp_count, &r) != GB200_OK) return -1;
+        if (detail) *detail = r;
+        mag_ = r.peak_mag;
+        test_statistics_ = r.test_statistic;
+        if (synchro_)
+            {
+                synchro_->Acq_delay_samples = r.acq_delay_samples;
+                synchro_->Acq_doppler_hz = r.acq_doppler_hz;
+                synchro_->Acq_samplestamp_samples = r.acq_samplestamp;
+                synchro_->Acq_doppler_step = conf_.doppler_step;
+            }
+        if (r.decision == 1 || r.decision == 0)
+            {
+                state_ = 0;  // d_state = 0; d_active = false
+                if (synchro_) synchro_->Flag_valid_acquisition = (r.decision == 1);
+                return r.decision == 1 ? 1 : 2;
+            }
+        return 0;
+    }
+    float test_statistics() const { return test_statistics_; }
+    std::string last_error() const { return gb200_last_error(s_); }
+
+private:
+    gb200_service* s_;
+    gb200_acq_cfg conf_;
+    gb200_acq* h_ = nullptr;
+    AcqSynchro* synchro_ = nullptr;
+    int stream_;
+    unsigned channel_ = 0;
+    int state_ = 0;
+    bool ok_ = false;
+    float mag_ = 0.0f, test_statistics_ = 0.0f;
+};
+}  // namespace gb200

@@ -1,0 +1,185 @@
+// extern "C" doors of the host-side mirror (libgnss_b200_host.so, plain g++): lets the tests drive the C++ adapter
+// classes -- loop maths, the DLL/PLL epoch loop on the B200 multicorrelator, the acquisition block mirror -- from Python.
+#include <cstring>
+#include <memory>
+
+#include "gb200_acquisition.hpp"
+#include "gb200_multicorrelator.hpp"
+#include "gb200_tracking.hpp"
+
+using namespace gb200;
+
+extern "C" {
+// ---- loop maths (arguments: complex values as re, im floats) ----
+double gbh_pll_cloop_two_quadrant_atan(float re, float im) { return pll_cloop_two_quadrant_atan(cfloat(re, im)); }
+double gbh_pll_four_quadrant_atan(float re, float im) { return pll_four_quadrant_atan(cfloat(re, im)); }
+double gbh_fll_four_quadrant_atan(float re1, float im1, float re2, float im2, double t1, double t2)
+{
+    return fll_four_quadrant_atan(cfloat(re1, im1), cfloat(re2, im2), t1, t2);
+}
+double gbh_dll_nc_e_minus_l_normalized(float ere, float eim, float lre, float lim) { return dll_nc_e_minus_l_normalized(cfloat(ere, eim), cfloat(lre, lim)); }
+double gbh_dll_nc_vemlp_normalized(const float* ve, const float* e, const float* l, const float* vl)
+{
+    return dll_nc_vemlp_normalized(cfloat(ve[0], ve[1]), cfloat(e[0], e[1]), cfloat(l[0], l[1]), cfloat(vl[0], vl[1]));
+}
+float gbh_cn0_svn_estimator(const float* prompt_iq, int n, double t) { return cn0_svn_estimator(reinterpret_cast<const cfloat*>(prompt_iq), n, t); }
+float gbh_carrier_lock_detector(const float* prompt_iq, int n) { return carrier_lock_detector(reinterpret_cast<const cfloat*>(prompt_iq), n); }
+void gbh_loop_filter_run(float update_interval, float bw, int order, int last_integrator, float init_out, const float* in, float* out, int n)
+{
+    LoopFilter f(update_interval, bw, order, last_integrator != 0);
+    f.initialize(init_out);
+    for (int i = 0; i < n; i++) out[i] = f.apply(in[i]);
+}
+void gbh_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float acq_doppler_hz, const float* fll, const float* pll, float t, float* out, int n)
+{
+    FllPllFilter f;
+    f.set_params(fll_bw, pll_bw, order);
+    f.initialize(acq_doppler_hz);
+    for (int i = 0; i < n; i++) out[i] = f.get_carrier_error(fll[i], pll[i], t);
+}
+
+// ---- DLL/PLL tracking channel on the B200 multicorrelator ----
+struct gbh_trk
+{
+    B200_Multicorrelator_Real_Codes corr;
+    std::unique_ptr<DllPllVemlTracking<B200_Multicorrelator_Real_Codes>> loop;
+};
+
+// flat POD image of DllPllConf for ctypes
+struct gbh_trk_conf
+{
+    double fs_in;
+    int vector_length;
+    float pll_bw_hz, dll_bw_hz, fll_bw_hz;
+    int pll_filter_order, dll_filter_order;
+    int enable_fll_pull_in, enable_fll_steady_state;
+    float pull_in_time_s, early_late_space_chips, very_early_late_space_chips;
+    int cn0_samples;
+    float cn0_min;
+    int max_lock_fail;
+    float carrier_lock_th;
+    int track_pilot, veml;
+    double signal_carrier_freq, code_chip_rate;
+    int code_length_chips, code_samples_per_chip;
+    double code_period;
+};
+
+// one epoch, flat
+struct gbh_epoch
+{
+    int valid, loss_of_lock, state, current_prn_length_samples;
+    uint64_t tracking_sample_counter;
+    double prompt_i, prompt_q, code_phase_samples, carrier_phase_rads, carrier_doppler_hz, cn0_db_hz, code_error_chips, carr_phase_error_hz, code_freq_chips;
+    float taps_iq[12];
+};
+
+DllPllConf gbh_to_conf(const gbh_trk_conf* c)
+{
+    DllPllConf d;
+    d.fs_in = c->fs_in;
+    d.vector_length = c->vector_length;
+    d.pll_bw_hz = c->pll_bw_hz;
+    d.dll_bw_hz = c->dll_bw_hz;
+    d.fll_bw_hz = c->fll_bw_hz;
+    d.pll_filter_order = c->pll_filter_order;
+    d.dll_filter_order = c->dll_filter_order;
+    d.enable_fll_pull_in = c->enable_fll_pull_in != 0;
+    d.enable_fll_steady_state = c->enable_fll_steady_state != 0;
+    d.pull_in_time_s = c->pull_in_time_s;
+    d.early_late_space_chips = c->early_late_space_chips;
+    d.very_early_late_space_chips = c->very_early_late_space_chips;
+    d.cn0_samples = c->cn0_samples;
+    d.cn0_min = c->cn0_min;
+    d.max_lock_fail = c->max_lock_fail;
+    d.carrier_lock_th = c->carrier_lock_th;
+    d.track_pilot = c->track_pilot != 0;
+    d.veml = c->veml != 0;
+    d.signal_carrier_freq = c->signal_carrier_freq;
+    d.code_chip_rate = c->code_chip_rate;
+    d.code_length_chips = c->code_length_chips;
+    d.code_samples_per_chip = c->code_samples_per_chip;
+    d.code_period = c->code_period;
+    return d;
+}
+
+void gbh_fill_epoch(const TrackingEpoch& e, int state, gbh_epoch* out)
+{
+    out->valid = e.flag_valid_symbol_output;
+    out->loss_of_lock = e.loss_of_lock;
+    out->state = state;
+    out->current_prn_length_samples = e.current_prn_length_samples;
+    out->tracking_sample_counter = e.tracking_sample_counter;
+    out->prompt_i = e.prompt_i;
+    out->prompt_q = e.prompt_q;
+    out->code_phase_samples = e.code_phase_samples;
+    out->carrier_phase_rads = e.carrier_phase_rads;
+    out->carrier_doppler_hz = e.carrier_doppler_hz;
+    out->cn0_db_hz = e.cn0_db_hz;
+    out->code_error_chips = e.code_error_chips;
+    out->carr_phase_error_hz = e.carr_phase_error_hz;
+    out->code_freq_chips = e.code_freq_chips;
+    for (int t = 0; t < 6; t++)
+        {
+            out->taps_iq[2 * t] = e.taps[t].real();
+            out->taps_iq[2 * t + 1] = e.taps[t].imag();
+        }
+}
+
+gbh_trk* gbh_trk_open(gb200_service* service, int stream_id, int item_type, const gbh_trk_conf* conf)
+{
+    if (!service || !conf) return nullptr;
+    auto* h = new gbh_trk();
+    const DllPllConf d = gbh_to_conf(conf);
+    if (!h->corr.init(service, stream_id, item_type, 2 * d.vector_length, d.veml ? 5 : 3))
+        {
+            delete h;
+            return nullptr;
+        }
+    h->loop.reset(new DllPllVemlTracking<B200_Multicorrelator_Real_Codes>(d, &h->corr));
+    return h;
+}
+int gbh_trk_start(gbh_trk* h, const float* code, const float* data_code, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp,
+    uint64_t sample_counter_now)
+{
+    return (h && h->loop->start_tracking(code, data_code, acq_delay_samples, acq_doppler_hz, acq_samplestamp, sample_counter_now)) ? 0 : -1;
+}
+int gbh_trk_step(gbh_trk* h, gbh_epoch* out)
+{
+    if (!h || !out) return -1;
+    TrackingEpoch e;
+    const bool ok = h->loop->step(&e);
+    gbh_fill_epoch(e, h->loop->state(), out);
+    return ok ? 0 : -2;
+}
+void gbh_trk_close(gbh_trk* h) { delete h; }
+
+// ---- acquisition block mirror: set_state(1) + run(samp_count); returns the event (1 positive, 2 negative, 0 none, <0 error) ----
+int gbh_acq_search(gb200_service* service, const gb200_acq_cfg* conf, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,
+    int max_runs, double* delay_samples, double* doppler_hz, uint64_t* samplestamp, float* test_statistic, int* mag)
+{
+    B200_Pcps_Acquisition acq(service, *conf, stream_id);
+    if (!acq.ok()) return -1;
+    AcqSynchro syn;
+    acq.set_channel(0);
+    acq.set_gnss_synchro(&syn);
+    acq.set_doppler_step(conf->doppler_step);
+    acq.set_threshold(conf->threshold);
+    acq.init();
+    if (!acq.set_local_code(reinterpret_cast<const std::complex<float>*>(code_iq), code_items)) return -1;
+    acq.reset();
+    int ev = 0;
+    uint64_t at = samp_count;
+    for (int k = 0; k < max_runs && ev == 0; k++)
+        {
+            gb200_acq_result r{};
+            ev = acq.run(at, &r);
+            if (ev == 0 && r.decision == 2) at += acq.consumed_samples();  // next dwell consumes the next block; step two re-runs the same one
+        }
+    *delay_samples = syn.Acq_delay_samples;
+    *doppler_hz = syn.Acq_doppler_hz;
+    *samplestamp = syn.Acq_samplestamp_samples;
+    *test_statistic = acq.test_statistics();
+    *mag = acq.mag();
+    return ev;
+}
+}

@@ -1,0 +1,124 @@
+"""ctypes access to the host-side C++ mirror (gnss-sdr-1_b200/libgnss_b200_host.so) and to the test-only build of the same
+epoch loop on the oracle correlator (tests/native/libhost_oracle_loop.so)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+
+
+class TrkConf(C.Structure):
+    _fields_ = [("fs_in", C.c_double), ("vector_length", C.c_int), ("pll_bw_hz", C.c_float), ("dll_bw_hz", C.c_float), ("fll_bw_hz", C.c_float),
+                ("pll_filter_order", C.c_int), ("dll_filter_order", C.c_int), ("enable_fll_pull_in", C.c_int), ("enable_fll_steady_state", C.c_int),
+                ("pull_in_time_s", C.c_float), ("early_late_space_chips", C.c_float), ("very_early_late_space_chips", C.c_float),
+                ("cn0_samples", C.c_int), ("cn0_min", C.c_float), ("max_lock_fail", C.c_int), ("carrier_lock_th", C.c_float),
+                ("track_pilot", C.c_int), ("veml", C.c_int), ("signal_carrier_freq", C.c_double), ("code_chip_rate", C.c_double),
+                ("code_length_chips", C.c_int), ("code_samples_per_chip", C.c_int), ("code_period", C.c_double)]
+
+
+class Epoch(C.Structure):
+    _fields_ = [("valid", C.c_int), ("loss_of_lock", C.c_int), ("state", C.c_int), ("current_prn_length_samples", C.c_int),
+                ("tracking_sample_counter", C.c_uint64), ("prompt_i", C.c_double), ("prompt_q", C.c_double), ("code_phase_samples", C.c_double),
+                ("carrier_phase_rads", C.c_double), ("carrier_doppler_hz", C.c_double), ("cn0_db_hz", C.c_double), ("code_error_chips", C.c_double),
+                ("carr_phase_error_hz", C.c_double), ("code_freq_chips", C.c_double), ("taps_iq", C.c_float * 12)]
+
+
+def gps_l1_conf(**kw):
+    """The GPS L1 C/A adapter's defaults (gps_l1_ca_dll_pll_tracking.cc:76-186): PLL 50 Hz, DLL 2 Hz, 3rd / 2nd order, E-L 0.5 chip."""
+    d = dict(fs_in=4e6, vector_length=4000, pll_bw_hz=50.0, dll_bw_hz=2.0, fll_bw_hz=35.0, pll_filter_order=3, dll_filter_order=2,
+             enable_fll_pull_in=0, enable_fll_steady_state=0, pull_in_time_s=2.0, early_late_space_chips=0.5, very_early_late_space_chips=0.5,
+             cn0_samples=20, cn0_min=30.0, max_lock_fail=50, carrier_lock_th=0.80, track_pilot=0, veml=0, signal_carrier_freq=1575.42e6,
+             code_chip_rate=1.023e6, code_length_chips=1023, code_samples_per_chip=1, code_period=0.001)
+    d.update(kw)
+    return TrkConf(**d)
+
+
+_host = None
+_hol = None
+
+
+def host():
+    global _host
+    if _host is None:
+        L = C.CDLL(os.path.join(ROOT, "gnss-sdr-1_b200", "libgnss_b200_host.so"))
+        for n in ("gbh_pll_cloop_two_quadrant_atan", "gbh_pll_four_quadrant_atan"):
+            getattr(L, n).restype = C.c_double
+            getattr(L, n).argtypes = [C.c_float, C.c_float]
+        L.gbh_fll_four_quadrant_atan.restype = C.c_double
+        L.gbh_fll_four_quadrant_atan.argtypes = [C.c_float] * 4 + [C.c_double] * 2
+        L.gbh_dll_nc_e_minus_l_normalized.restype = C.c_double
+        L.gbh_dll_nc_e_minus_l_normalized.argtypes = [C.c_float] * 4
+        L.gbh_dll_nc_vemlp_normalized.restype = C.c_double
+        L.gbh_dll_nc_vemlp_normalized.argtypes = [f32p] * 4
+        L.gbh_cn0_svn_estimator.restype = C.c_float
+        L.gbh_cn0_svn_estimator.argtypes = [f32p, C.c_int, C.c_double]
+        L.gbh_carrier_lock_detector.restype = C.c_float
+        L.gbh_carrier_lock_detector.argtypes = [f32p, C.c_int]
+        L.gbh_loop_filter_run.argtypes = [C.c_float, C.c_float, C.c_int, C.c_int, C.c_float, f32p, f32p, C.c_int]
+        L.gbh_fll_pll_filter_run.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, f32p, f32p, C.c_float, f32p, C.c_int]
+        L.gbh_trk_open.restype = C.c_void_p
+        L.gbh_trk_open.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(TrkConf)]
+        L.gbh_trk_start.argtypes = [C.c_void_p, f32p, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        L.gbh_trk_step.argtypes = [C.c_void_p, C.POINTER(Epoch)]
+        L.gbh_trk_close.argtypes = [C.c_void_p]
+        L.gbh_acq_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        _host = L
+    return _host
+
+
+def oracle_loop():
+    global _hol
+    if _hol is None:
+        L = C.CDLL(os.path.join(ROOT, "tests", "native", "libhost_oracle_loop.so"))
+        L.hol_open.restype = C.c_void_p
+        L.hol_open.argtypes = [f32p, C.c_uint64, C.c_uint64, C.POINTER(TrkConf)]
+        L.hol_start.argtypes = [C.c_void_p, f32p, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        L.hol_step.argtypes = [C.c_void_p, C.POINTER(Epoch)]
+        L.hol_close.argtypes = [C.c_void_p]
+        _hol = L
+    return _hol
+
+
+FIELDS = ("valid", "loss_of_lock", "state", "current_prn_length_samples", "tracking_sample_counter", "prompt_i", "prompt_q", "code_phase_samples",
+          "carrier_phase_rads", "carrier_doppler_hz", "cn0_db_hz", "code_error_chips", "carr_phase_error_hz", "code_freq_chips")
+
+
+def _record(e):
+    d = {k: getattr(e, k) for k in FIELDS}
+    d["taps"] = np.array(e.taps_iq[:], np.float32).view(np.complex64).copy()
+    return d
+
+
+def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None):
+    L = oracle_loop()
+    x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
+    h = L.hol_open(x, len(x) // 2, first_index, C.byref(conf))
+    code = np.ascontiguousarray(code, np.float32)
+    dc = np.ascontiguousarray(data_code, np.float32) if data_code is not None else None
+    assert L.hol_start(h, code, dc.ctypes.data_as(C.c_void_p) if dc is not None else None, acq_delay, acq_doppler, acq_stamp, first_index) == 0
+    out, e = [], Epoch()
+    for _ in range(n_steps):
+        if L.hol_step(h, C.byref(e)) != 0:
+            break
+        out.append(_record(e))
+    L.hol_close(h)
+    return out
+
+
+def run_b200_channel(service, stream_id, item_type, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None):
+    L = host()
+    h = L.gbh_trk_open(service.h, stream_id, item_type, C.byref(conf))
+    assert h, "gbh_trk_open failed"
+    code = np.ascontiguousarray(code, np.float32)
+    dc = np.ascontiguousarray(data_code, np.float32) if data_code is not None else None
+    assert L.gbh_trk_start(h, code, dc.ctypes.data_as(C.c_void_p) if dc is not None else None, acq_delay, acq_doppler, acq_stamp, first_index) == 0
+    out, e = [], Epoch()
+    for _ in range(n_steps):
+        if L.gbh_trk_step(h, C.byref(e)) != 0:
+            break
+        out.append(_record(e))
+    L.gbh_trk_close(h)
+    return out
