@@ -39,6 +39,10 @@ TAPS = np.array([-1.2, -0.3, 0.0, 0.3, 1.2], np.float32)  # +-0.6 / +-0.15 chip 
 METRIC = "acq grid cells/s (tracking channel*Msamples/s in 'tracking')"
 
 
+# one-lane launch pair under ncu (profiles/r01_ncu_acq_inv_dif_*.txt, capture prof_r01f): 21.28 + 2.31 MB (row) + 50.20 + 0.03 MB (col)
+NCU_PAIR_DRAM_BYTES = 73.8e6
+
+
 def build_stream(seed):
     """Synthetic C2 stream: 10 E1 satellites (B - C), CN0 44..35 dB-Hz, int16 at 2^10 LSB per sigma."""
     import synth
@@ -379,8 +383,9 @@ def run_b200(args, rank, local_rank, world):
         "e2e": {"value": e2e_acq, "unit": "grid cells/s", "h2d_bytes_per_step": N_FFT * 4, "d2h_bytes_per_step": N_PRN * 56,
                 "ms_per_step": tot_e2e_acq_ms / steps},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": acq_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": acq_gbs / hbm_peak, "traffic": None,
-                     "kernel": "gb_acq_inv_row + gb_acq_inv_col (one pass of the inverse side; 16 algorithmic B per cell)",
+        "roofline": {"bound": "hbm", "achieved": acq_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": acq_gbs / hbm_peak, "traffic": NCU_PAIR_DRAM_BYTES,
+                     "traffic_note": "dram__bytes_read+write of one inv_row + one inv_col launch (183 transforms) from ncu --set full, profiles/r01_ncu_acq_inv_dif_{row,col}.txt; ncu flushes caches between kernels, so the column kernel's 50 MB read of the row buffer is DRAM there and an L2 hit in the pipeline; algorithmic bytes of the pair: 93.6e6",
+                     "kernel": "gb_acq_inv_row_dif + gb_acq_inv_col_dif (one pass of the inverse side; 16 algorithmic B per cell)",
                      "peak_source": peak_src, "per_launch_ms": pair_ms, "cells_per_launch": cells_per_launch,
                      "kernel_ms": {k: {"total_ms": v[0], "launches": v[1]} for k, v in kstats.items()}},
         "cpu_baseline": cpu_acq,
