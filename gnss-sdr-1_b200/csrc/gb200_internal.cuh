@@ -34,6 +34,18 @@ struct GbTrkWork
     float2 nco_adv;          // unit phasor of GB200_TRK_THREADS * arg(inc): the per-iteration NCO advance of one thread
 };
 
+// one request of the int16 (Cpu_Multicorrelator_16sc) correlator
+struct GbTrk16Work
+{
+    const void* samples;  // lv_16sc_t window start (contiguous)
+    const void* code;     // lv_16sc_t[code_len] local code
+    int code_len, n, n_taps, out_index;
+    float shifts[GB200_MAX_TAPS];
+    float rem_code, code_step;
+    float2 phase0;  // (cosf(rem_carr), -sinf(rem_carr)), host libm like the reference (cpu_multicorrelator_16sc.cc:99)
+    float2 inc;     // std::exp(lv_32fc_t(0, -phase_step)) = (cosf(-step), sinf(-step))
+};
+
 // acquisition grid-reduction record: ordering key = (mag desc, bin asc, idx asc)
 struct GbPeak
 {
@@ -89,6 +101,9 @@ __device__ __forceinline__ float2 gb_cmul(float2 a, float2 b)
 cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_taps, bool has_data, int item_type,
     int code_kind, bool high_dyn, float2* d_partials, unsigned* d_counters, float2* d_out, int chunk, cudaStream_t st,
     int* launches);
+
+cudaError_t gb_trk16_launch(const GbTrk16Work* d_work, int n_work, int max_n, int n_taps, float2* d_ckpt, int4* d_triples, short* d_out,
+    cudaStream_t st, int* launches);
 
 // ------------------------------------------------------------------ acquisition FFT plan
 #define GB200_ACQ_THREADS 256

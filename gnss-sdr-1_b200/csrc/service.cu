@@ -74,8 +74,10 @@ struct gb200_service
     std::string error = "no error";
     std::recursive_mutex mu;
     // scratch pools (grown on demand, reused)
-    void* d_scratch[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratch_bytes[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    void* d_scratch[16] = {};
+    size_t scratch_bytes[16] = {};
+    void* h16 = nullptr;  // pinned staging of the int16 correlator (work items in, results out)
+    size_t h16_bytes = 0;
     void* h_pinned = nullptr;
     size_t h_pinned_bytes = 0;
     int sm_count = 148;
@@ -191,8 +193,9 @@ extern "C" int gb200_service_destroy(gb200_service* s)
             if (kv.second.d_twN) cudaFree(kv.second.d_twN);
             if (kv.second.d_twNhi) cudaFree(kv.second.d_twNhi);
         }
-    for (int i = 0; i < 10; i++)
+    for (int i = 0; i < 16; i++)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
+    if (s->h16) cudaFreeHost(s->h16);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->d_flush) cudaFree(s->d_flush);
     if (s->ev0) cudaEventDestroy(s->ev0);
@@ -1356,7 +1359,8 @@ extern "C" int gb200_trk_create(gb200_service* s, const gb200_trk_cfg* cfg, gb20
     if (!s || !cfg || !out) return GB200_E_INVALID;
     *out = nullptr;
     if (cfg->n_taps < 1 || cfg->n_taps > GB200_MAX_TAPS || cfg->max_code_len < 1 || cfg->item_type < 0 || cfg->item_type > 2 ||
-        (cfg->code_kind != GB200_CODE_REAL && cfg->code_kind != GB200_CODE_CPLX) || (cfg->high_dyn && cfg->code_kind == GB200_CODE_CPLX))
+        (cfg->code_kind != GB200_CODE_REAL && cfg->code_kind != GB200_CODE_CPLX && cfg->code_kind != GB200_CODE_16SC) ||
+        (cfg->high_dyn && cfg->code_kind != GB200_CODE_REAL) || (cfg->code_kind == GB200_CODE_16SC && cfg->item_type != GB200_ITEM_16IC))
         {
             s->set_error("gb200_trk_create: bad configuration");
             return GB200_E_INVALID;
@@ -1444,6 +1448,11 @@ static int trk_fill_work(gb200_service* s, const gb200_trk_req& r, int out_index
         {
             s->set_error("tracking request: handle not initialised (set_local_code_and_taps) or n_samples < 1");
             return GB200_E_STATE;
+        }
+    if (t->c.code_kind == GB200_CODE_16SC)
+        {
+            s->set_error("tracking request: GB200_CODE_16SC handles are served by gb200_trk_correlate_16sc[_batch]");
+            return GB200_E_INVALID;
         }
     if ((uint64_t)r.n_samples >= (1u << 24))
         {
@@ -1704,6 +1713,93 @@ extern "C" int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_tr
     rc = gb200_trk_batch_launch(b);
     if (!rc) rc = gb200_trk_batch_fetch(b, outs_iq);
     return rc;
+}
+
+
+// ------------------------------------------------------------------ int16 correlator (Cpu_Multicorrelator_16sc)
+extern "C" int gb200_trk_correlate_16sc_batch(gb200_service* s, int n, const gb200_trk_req* reqs, int16_t* outs_iq)
+{
+    if (!s || n <= 0 || !reqs || !outs_iq) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    const size_t work_bytes = sizeof(GbTrk16Work) * (size_t)n, out_bytes = sizeof(int16_t) * 2 * GB200_MAX_TAPS * (size_t)n;
+    if (s->h16_bytes < work_bytes + out_bytes)
+        {
+            if (s->h16) cudaFreeHost(s->h16);
+            s->h16 = nullptr;
+            s->h16_bytes = 0;
+            GB_CUDA(s, cudaMallocHost(&s->h16, 2 * (work_bytes + out_bytes)));
+            s->h16_bytes = 2 * (work_bytes + out_bytes);
+        }
+    GbTrk16Work* hw = (GbTrk16Work*)s->h16;
+    int16_t* hout = (int16_t*)((char*)s->h16 + work_bytes);
+    int max_n = 1, max_taps = 1;
+    bool same_taps = true;
+    for (int i = 0; i < n; i++)
+        {
+            const gb200_trk_req& r = reqs[i];
+            gb200_trk* t = r.trk;
+            if (!t || t->s != s || t->c.code_kind != GB200_CODE_16SC || t->code_len < 1 || r.n_samples < 1)
+                {
+                    s->set_error("gb200_trk_correlate_16sc: request " + std::to_string(i) + " needs a GB200_CODE_16SC handle with a local code and n_samples >= 1");
+                    return GB200_E_INVALID;
+                }
+            const void* win = nullptr;
+            int rc = ring_window(s, r.stream_id, r.first_sample_index, (uint64_t)r.n_samples, GB200_ITEM_16IC, &win);
+            if (rc) return rc;
+            GbTrk16Work& w = hw[i];
+            w.samples = win;
+            w.code = t->d_code;
+            w.code_len = t->code_len;
+            w.n = r.n_samples;
+            w.n_taps = t->n_taps;
+            w.out_index = i;
+            memcpy(w.shifts, t->shifts, sizeof(w.shifts));
+            w.rem_code = r.rem_code_phase_chips;
+            w.code_step = r.code_phase_step_chips;
+            w.phase0 = make_float2(cosf(r.rem_carr_phase_rad), -sinf(r.rem_carr_phase_rad));
+            w.inc = make_float2(cosf(-r.phase_step_rad), sinf(-r.phase_step_rad));
+            max_n = std::max(max_n, r.n_samples);
+            max_taps = std::max(max_taps, t->n_taps);
+            same_taps = same_taps && t->n_taps == reqs[0].trk->n_taps;
+        }
+    const int max_blocks = (max_n + 255) / 256;
+    void *d_work, *d_ckpt, *d_triples, *d_out;
+    int rc;
+    if ((rc = s->scratch(10, work_bytes, &d_work))) return rc;
+    if ((rc = s->scratch(11, sizeof(float2) * (size_t)n * max_blocks, &d_ckpt))) return rc;
+    if ((rc = s->scratch(12, sizeof(int4) * 2 * GB200_MAX_TAPS * (size_t)n * max_blocks, &d_triples))) return rc;
+    if ((rc = s->scratch(13, out_bytes, &d_out))) return rc;
+    GB_CUDA(s, cudaMemcpyAsync(d_work, hw, work_bytes, cudaMemcpyHostToDevice, s->stream));
+    int l = 0;
+    GB_CUDA(s, gb_trk16_launch((const GbTrk16Work*)d_work, n, max_n, same_taps ? max_taps : GB200_MAX_TAPS, (float2*)d_ckpt, (int4*)d_triples, (short*)d_out,
+                   s->stream, &l));
+    s->launches += l;
+    GB_CUDA(s, cudaMemcpyAsync(hout, d_out, out_bytes, cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    memcpy(outs_iq, hout, out_bytes);
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_correlate_16sc(gb200_trk* t, int stream_id, uint64_t first_sample_index, float rem_carr_phase_rad, float phase_step_rad,
+    float rem_code_phase_chips, float code_phase_step_chips, int n_samples, int16_t* corr_out_iq)
+{
+    if (!t || !corr_out_iq) return GB200_E_INVALID;
+    gb200_trk_req r;
+    memset(&r, 0, sizeof(r));
+    r.trk = t;
+    r.stream_id = stream_id;
+    r.first_sample_index = first_sample_index;
+    r.rem_carr_phase_rad = rem_carr_phase_rad;
+    r.phase_step_rad = phase_step_rad;
+    r.rem_code_phase_chips = rem_code_phase_chips;
+    r.code_phase_step_chips = code_phase_step_chips;
+    r.n_samples = n_samples;
+    int16_t out[2 * GB200_MAX_TAPS];
+    int rc = gb200_trk_correlate_16sc_batch(t->s, 1, &r, out);
+    if (rc) return rc;
+    memcpy(corr_out_iq, out, sizeof(int16_t) * 2 * t->n_taps);
+    return GB200_OK;
 }
 
 extern "C" int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_sample_index, float rem_carr_phase_rad,

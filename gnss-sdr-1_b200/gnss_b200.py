@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgnss_b200.so")
 
 ITEM_32FC, ITEM_16IC, ITEM_8IC = 0, 1, 2
-CODE_REAL, CODE_CPLX = 0, 1
+CODE_REAL, CODE_CPLX, CODE_16SC = 0, 1, 2
 KCLASS = {"trk": 0, "acq_fwd_col": 1, "acq_fwd_row": 2, "acq_inv_row": 3, "acq_inv_col": 4}
 MAX_TAPS = 8
 OUT_STRIDE = MAX_TAPS + 1
@@ -74,7 +74,7 @@ EXPORTS = [
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid",
     "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_correlate",
-    "gb200_trk_correlate_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
+    "gb200_trk_correlate_batch", "gb200_trk_correlate_16sc", "gb200_trk_correlate_16sc_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
 ]
 
 _lib = None
@@ -129,6 +129,8 @@ def lib():
     L.gb200_trk_set_data_code.argtypes = [vp, vp, i, i]
     L.gb200_trk_correlate.argtypes = [vp, i, u64, f, f, f, f, f, f, i, vp]
     L.gb200_trk_correlate_batch.argtypes = [vp, i, C.POINTER(TrkReq), vp]
+    L.gb200_trk_correlate_16sc.argtypes = [vp, i, u64, f, f, f, f, i, vp]
+    L.gb200_trk_correlate_16sc_batch.argtypes = [vp, i, C.POINTER(TrkReq), vp]
     L.gb200_trk_batch_create.argtypes = [vp, i, C.POINTER(TrkReq), C.POINTER(vp)]
     L.gb200_trk_batch_launch.argtypes = [vp]
     L.gb200_trk_batch_fetch.argtypes = [vp, vp]
@@ -294,12 +296,16 @@ class Multicorrelator:
         self.n_out = n_taps
 
     def set_local_code_and_taps(self, code, shifts):
+        n_items = None
         if self.cfg.code_kind == CODE_CPLX:
             c = np.ascontiguousarray(code, np.complex64)
+        elif self.cfg.code_kind == CODE_16SC:
+            c = np.ascontiguousarray(code, np.int16)  # interleaved I, Q
+            n_items = c.size // 2
         else:
             c = np.ascontiguousarray(code, np.float32)
         sh = np.ascontiguousarray(shifts, np.float32)
-        self.s.check(self.s.L.gb200_trk_set_local_code_and_taps(self.h, _ptr(c), c.size, _ptr(sh), sh.size))
+        self.s.check(self.s.L.gb200_trk_set_local_code_and_taps(self.h, _ptr(c), c.size if n_items is None else n_items, _ptr(sh), sh.size))
         self.n_taps = sh.size
         self.n_out = sh.size
 
@@ -315,10 +321,23 @@ class Multicorrelator:
                                                   rem_code, code_step, code_rate, n_samples, _ptr(out)))
         return out
 
+    def correlate_16sc(self, stream_id, first_sample_index, rem_carr, phase_step, rem_code, code_step, n_samples):
+        """Cpu_Multicorrelator_16sc semantics; returns int16[n_taps, 2] (I, Q)."""
+        out = np.zeros(2 * self.n_taps, np.int16)
+        self.s.check(self.s.L.gb200_trk_correlate_16sc(self.h, stream_id, first_sample_index, rem_carr, phase_step, rem_code, code_step,
+                                                       n_samples, _ptr(out)))
+        return out.reshape(-1, 2)
+
     def close(self):
         if self.h:
             self.s.L.gb200_trk_destroy(self.h)
             self.h = C.c_void_p()
+
+
+def correlate_16sc_batch(service, reqs):
+    out = np.zeros((len(reqs), 2 * MAX_TAPS), np.int16)
+    service.check(service.L.gb200_trk_correlate_16sc_batch(service.h, len(reqs), reqs, _ptr(out)))
+    return out.reshape(len(reqs), MAX_TAPS, 2)
 
 
 def make_reqs(items):

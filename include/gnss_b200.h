@@ -155,6 +155,7 @@ int gb200_acq_read_grid(gb200_acq* a, float* dst);
 #define GB200_MAX_TAPS 8
 #define GB200_CODE_REAL 0 /* Cpu_Multicorrelator_Real_Codes (float codes)        */
 #define GB200_CODE_CPLX 1 /* Cpu_Multicorrelator (complex-float codes, GLONASS)  */
+#define GB200_CODE_16SC 2 /* Cpu_Multicorrelator_16sc (lv_16sc_t samples and codes, saturating int16 outputs; item_type must be GB200_ITEM_16IC) */
 
 typedef struct gb200_trk_cfg
 {
@@ -195,6 +196,15 @@ typedef struct gb200_trk_req
 /* All requests in ONE launch.  outs: for request i, (n_taps_i + has_data_i) complex floats, packed
  * in request order at stride GB200_MAX_TAPS+1 complex floats. */
 int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_trk_req* reqs, float* outs_iq);
+/* = Cpu_Multicorrelator_16sc::Carrier_wipeoff_multicorrelator_resampler (src/algorithms/tracking/libs/cpu_multicorrelator_16sc.cc:86-105;
+ * same argument list) with the exact semantics of its _generic kernels: float32 rotation, rintf to int16, complex int16
+ * products narrowed to 16 bits, accumulation saturating at every sample (volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn.h:73-108).
+ * The handle must have been created with GB200_CODE_16SC; `code` in gb200_trk_set_local_code_and_taps is then code_len
+ * lv_16sc_t items.  corr_out_iq: n_taps complex int16 (I, Q interleaved).  Bit-exact against the reference. */
+int gb200_trk_correlate_16sc(gb200_trk* t, int stream_id, uint64_t first_sample_index, float rem_carr_phase_rad, float phase_step_rad,
+    float rem_code_phase_chips, float code_phase_step_chips, int n_samples, int16_t* corr_out_iq);
+/* all requests in one launch sequence; the rate fields of gb200_trk_req are ignored.  outs: request i at outs + 2 * GB200_MAX_TAPS * i */
+int gb200_trk_correlate_16sc_batch(gb200_service* s, int n, const gb200_trk_req* reqs, int16_t* outs_iq);
 /* split form: stage -> launch (asynchronous, repeatable) -> fetch */
 int gb200_trk_batch_create(gb200_service* s, int n, const gb200_trk_req* reqs, gb200_trk_batch** out);
 int gb200_trk_batch_launch(gb200_trk_batch* b);

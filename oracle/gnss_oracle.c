@@ -216,6 +216,47 @@ void go_multicorrelator_cplx(const float* in_iq, int n, const float* code_iq, in
     free(codes);
 }
 
+/* Cpu_Multicorrelator_16sc::Carrier_wipeoff_multicorrelator_resampler (src/algorithms/tracking/libs/cpu_multicorrelator_16sc.cc:78-105)
+ * = volk_gnsssdr_16ic_xn_resampler_16ic_xn_generic (..._16ic_xn_resampler_16ic_xn.h:75-94: the float32 index rule of the
+ * float resampler) + volk_gnsssdr_16ic_x2_rotator_dot_prod_16ic_xn_generic (..._16ic_x2_rotator_dot_prod_16ic_xn.h:73-108):
+ * rotate in float32, rintf to int16, THEN (for n % 256 == 0) renormalise the phasor by hypotf, advance it, complex int16
+ * product truncated to 16 bits, saturating int16 accumulation in sample order. */
+static int16_t sat16_(int32_t v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); }
+void go_multicorrelator_16sc(const int16_t* in_iq, int n, const int16_t* code_iq, int code_len, const float* shifts, int n_taps,
+    float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips, float code_phase_step_chips, int16_t* corr_out_iq)
+{
+    float pr = cosf(rem_carr_phase_rad), pi = -sinf(rem_carr_phase_rad);
+    const float ir = cosf(-phase_step_rad), ii = sinf(-phase_step_rad); /* std::exp(lv_32fc_t(0, -step)) */
+    for (int t = 0; t < 2 * n_taps; t++) corr_out_iq[t] = 0;
+    for (unsigned k = 0; k < (unsigned)n; k++)
+        {
+            const float xr = (float)in_iq[2 * k], xi = (float)in_iq[2 * k + 1];
+            const float wr = xr * pr - xi * pi, wi = xr * pi + xi * pr;
+            const int16_t sr = (int16_t)rintf(wr), si = (int16_t)rintf(wi);
+            if (k % 256 == 0)
+                {
+                    const float h = hypotf(pr, pi);
+                    pr /= h;
+                    pi /= h;
+                }
+            {
+                const float nr = pr * ir - pi * ii, ni = pr * ii + pi * ir;
+                pr = nr;
+                pi = ni;
+            }
+            for (int t = 0; t < n_taps; t++)
+                {
+                    const float v = code_phase_step_chips * (float)k + shifts[t] - rem_code_phase_chips;
+                    const int idx = chip_index_(v, code_len);
+                    const int32_t cr = code_iq[2 * idx], ci = code_iq[2 * idx + 1];
+                    const int16_t tr = (int16_t)((int32_t)sr * cr - (int32_t)si * ci); /* product narrowed to 16 bits (wraps) */
+                    const int16_t ti = (int16_t)((int32_t)sr * ci + (int32_t)si * cr);
+                    corr_out_iq[2 * t] = sat16_((int32_t)corr_out_iq[2 * t] + tr);
+                    corr_out_iq[2 * t + 1] = sat16_((int32_t)corr_out_iq[2 * t + 1] + ti);
+                }
+        }
+}
+
 /* Arbiter (not a reference function): same float32 chip indices as the reference resampler, but the
  * carrier phase and the accumulation are evaluated in float64 with the exact phase
  * -(rem + n*step) of the float32 arguments. */

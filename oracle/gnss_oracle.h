@@ -43,6 +43,9 @@ void go_multicorrelator_real(const float* in_iq, int n, const float* code, int c
 void go_multicorrelator_cplx(const float* in_iq, int n, const float* code_iq, int code_len, const float* shifts,
     int n_taps, float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips,
     float code_phase_step_chips, float* corr_out_iq);
+/* Cpu_Multicorrelator_16sc::Carrier_wipeoff_multicorrelator_resampler (int16 samples, complex int16 codes, saturating) */
+void go_multicorrelator_16sc(const int16_t* in_iq, int n, const int16_t* code_iq, int code_len, const float* shifts, int n_taps,
+    float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips, float code_phase_step_chips, int16_t* corr_out_iq);
 /* float64 arbiter on the oracle's own chip indices */
 void go_multicorrelator_real_f64(const float* in_iq, int n, const float* code, int code_len, const float* shifts,
     int n_taps, float rem_carr_phase_rad, float phase_step_rad, float rem_code_phase_chips,

@@ -7,6 +7,7 @@ Outputs (tests/golden/):
   trk_golden.npz   multicorrelator known answers: seeded inputs + outputs of the reference's
                    Cpu_Multicorrelator_Real_Codes / Cpu_Multicorrelator with _generic and _u_avx protokernels
   loop_golden.npz  discriminator / loop-filter / lock-detector outputs of the reference's scalar libs
+  trk16_golden.npz Cpu_Multicorrelator_16sc known answers (int16 samples and codes, saturating outputs), seeds only + outputs
   *.dat            the reference's own acquisition fixtures (src/tests/signal_samples), copied verbatim
 """
 import os
@@ -137,6 +138,17 @@ def make_loop():
     np.savez_compressed(os.path.join(HERE, "loop_golden.npz"), **out)
 
 
+def make_trk16():
+    out = {}
+    import synth
+
+    for k, c in enumerate(synth.trk16_cases()):
+        y = np.zeros(2 * len(c["shifts"]), np.int16)
+        R.gbref_multicorrelator_16sc(c["x"], len(c["x"]) // 2, c["code"], len(c["code"]) // 2, c["shifts"], len(c["shifts"]), *c["args"], y)
+        out["out_%d" % k] = y
+    np.savez_compressed(os.path.join(HERE, "trk16_golden.npz"), **out)
+
+
 if __name__ == "__main__":
     for f in ("GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat", "Galileo_E1_ID_1_Fs_4Msps_8ms.dat"):
         src = os.path.join("/root/reference/src/tests/signal_samples", f)
@@ -145,4 +157,5 @@ if __name__ == "__main__":
     make_codes()
     make_trk()
     make_loop()
+    make_trk16()
     print("golden fixtures written to", HERE)

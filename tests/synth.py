@@ -83,3 +83,28 @@ def quantize(x, item):
     else:
         raise ValueError(item)
     return np.ascontiguousarray(q.reshape(-1))
+
+
+def trk16_cases():
+    """Deterministic case list shared by the generator and the tests (inputs are re-created from the seed, not stored)."""
+    rng = np.random.default_rng(20260016)
+    cases = []
+    for k in range(16):
+        amp = [3.0, 40.0, 400.0, -1.0][k % 4]
+        n = int(rng.integers(200, 12000))
+        code_len = int(rng.choice([511, 1023, 2046]))
+        n_taps = int(rng.choice([1, 3, 5]))
+        if amp < 0:
+            x = np.clip(np.round(rng.standard_normal(2 * n) * 5.0 + 60.0), -32768, 32767).astype(np.int16)
+        else:
+            x = np.clip(np.round(rng.standard_normal(2 * n) * amp), -32768, 32767).astype(np.int16)
+        code = rng.choice([-1, 1], 2 * code_len).astype(np.int16)
+        code[1::2] = rng.choice([-1, 0, 1], code_len)
+        shifts = np.sort(rng.uniform(-1.5, 1.5, n_taps)).astype(np.float32)
+        args = [float(rng.uniform(0, 6.2)), float(rng.uniform(-0.03, 0.03)), float(rng.uniform(0, 1)), float(code_len / 4000.0 * rng.uniform(0.9, 1.1))]
+        if amp < 0:
+            code[0::2] = 1
+            code[1::2] = 0
+            args[1] = 0.0
+        cases.append(dict(x=x, code=code, shifts=shifts, args=[np.float32(a).item() for a in args]))
+    return cases

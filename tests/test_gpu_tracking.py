@@ -164,3 +164,59 @@ def test_ring_wraparound_and_errors(service):
         m.close()
     finally:
         s.close()
+
+
+def test_int16_correlator_bit_exact(service):
+    """Cpu_Multicorrelator_16sc semantics (rintf to int16, 16-bit products, per-sample saturating accumulation) reproduced
+    BIT-exactly by the parallel clamp-add formulation, including runs that saturate, through single and batched calls."""
+    import ctypes as C
+
+    import gnss_b200 as gb
+
+    i16p = np.ctypeslib.ndpointer(np.int16, flags="C_CONTIGUOUS")
+    f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+    L = ol.oracle()
+    L.go_multicorrelator_16sc.argtypes = [i16p, C.c_int, i16p, C.c_int, f32p, C.c_int] + [C.c_float] * 4 + [i16p]
+    rng = np.random.default_rng(16)
+    n_total = 60000
+    saturated = 0
+    for amp in (3.0, 40.0, 400.0, -1.0):
+        if amp < 0:  # a DC stream: with an all-ones code and a frozen NCO the accumulators march into the rails
+            x = np.clip(np.round(rng.standard_normal(2 * n_total) * 5.0 + 60.0), -32768, 32767).astype(np.int16)
+        else:
+            x = np.clip(np.round(rng.standard_normal(2 * n_total) * amp), -32768, 32767).astype(np.int16)
+        first = int(rng.integers(0, 1 << 20))
+        service.push(3, x, gb.ITEM_16IC, first)
+        reqs_items, wants, mcs = [], [], []
+        for trial in range(12):
+            n_taps = int(rng.choice([1, 3, 5, 7]))
+            code_len = int(rng.choice([511, 1023, 2046]))
+            n = int(rng.integers(100, 20000))
+            off = int(rng.integers(0, n_total - n))
+            code = rng.choice([-1, 1], 2 * code_len).astype(np.int16)
+            code[1::2] = rng.choice([-1, 0, 1], code_len)
+            shifts = np.sort(rng.uniform(-1.5, 1.5, n_taps)).astype(np.float32)
+            args = (float(rng.uniform(0, 6.2)), float(rng.uniform(-0.03, 0.03)), float(rng.uniform(0, 1)), float(code_len / 4000.0 * rng.uniform(0.9, 1.1)))
+            if amp < 0:
+                code[0::2] = 1 if trial % 2 else -1
+                code[1::2] = 0
+                args = (float(rng.uniform(0, 6.2)), 0.0 if trial % 4 else 1e-5, args[2], args[3])
+            want = np.zeros(2 * n_taps, np.int16)
+            L.go_multicorrelator_16sc(np.ascontiguousarray(x[2 * off: 2 * (off + n)]), n, code, code_len, shifts, n_taps, *args, want)
+            mc = gb.Multicorrelator(service, n_taps, 2046, code_kind=gb.CODE_16SC, item_type=gb.ITEM_16IC)
+            mc.set_local_code_and_taps(code, shifts)
+            got = mc.correlate_16sc(3, first + off, args[0], args[1], args[2], args[3], n)
+            assert np.array_equal(got.reshape(-1), want), (amp, trial, n, got.reshape(-1), want)
+            saturated += int(np.any(np.abs(want.astype(np.int32)) >= 32767))
+            reqs_items.append((mc, 3, first + off, args[0], args[1], 0.0, args[2], args[3], 0.0, n))
+            wants.append(want)
+            mcs.append(mc)
+        outs = gb.correlate_16sc_batch(service, gb.make_reqs(reqs_items))
+        for k, want in enumerate(wants):
+            assert np.array_equal(outs[k].reshape(-1)[: want.size], want), (amp, k)
+        # the float entry points refuse an int16 handle instead of misreading its code table
+        with pytest.raises(gb.Gb200Error):
+            mcs[0].correlate(3, first, 0.0, 0.0, 0.0, 0.25, 1000)
+        for mc in mcs:
+            mc.close()
+    assert saturated >= 6
