@@ -8,6 +8,8 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <chrono>
+#include <condition_variable>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -69,6 +71,23 @@ struct gb200_service
     uint64_t ring_capacity = 0, ring_slack = 0;
     std::map<int, GbPlanEntry> plans;
     uint64_t launches = 0;
+    // coalescing of concurrent single-request callers ("the service coalesces concurrent callers into one launch")
+    struct TrkPending
+    {
+        gb200_trk_req req;
+        float* out;
+        int rc;
+        bool done;
+    };
+    uint32_t batch_window_us = 0;
+    std::mutex qmu;
+    std::condition_variable qcv;
+    std::vector<TrkPending*> queue;
+    bool collecting = false;
+    bool running = false;   // a coalesced batch is executing: the next collector keeps collecting meanwhile (it could not launch anyway)
+    int live_trk = 0;       // float-correlator handles alive
+    int prev_batch_n = 1;   // callers served by the previous coalesced launch: the collector waits for that many (adaptive)
+    uint64_t coalesced_batches = 0, coalesced_requests = 0;
     gb200_trk_batch* cb = nullptr;  // arena of gb200_trk_correlate_batch (grow-only)
     int cb_n = 0, cb_chunks = 0;
     std::string error = "no error";
@@ -173,6 +192,7 @@ extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service*
     s->rings.resize((cfg && cfg->max_streams > 0) ? cfg->max_streams : 4);
     s->ring_capacity = (cfg && cfg->ring_capacity) ? cfg->ring_capacity : (1ull << 24);
     s->ring_slack = (cfg && cfg->ring_slack) ? cfg->ring_slack : (1ull << 21);
+    s->batch_window_us = cfg ? cfg->batch_window_us : 0;
     if (s->ring_slack > s->ring_capacity) s->ring_slack = s->ring_capacity;
     *out = s;
     return GB200_OK;
@@ -1380,6 +1400,11 @@ extern "C" int gb200_trk_create(gb200_service* s, const gb200_trk_cfg* cfg, gb20
             delete t;
             return GB200_E_CUDA;
         }
+    if (cfg->code_kind != GB200_CODE_16SC)
+        {
+            std::lock_guard<std::mutex> ql(s->qmu);
+            s->live_trk++;
+        }
     *out = t;
     return GB200_OK;
 }
@@ -1391,6 +1416,11 @@ extern "C" int gb200_trk_destroy(gb200_trk* t)
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
     cudaStreamSynchronize(s->stream);
+    if (t->c.code_kind != GB200_CODE_16SC)
+        {
+            std::lock_guard<std::mutex> ql(s->qmu);
+            s->live_trk--;
+        }
     if (t->single) gb200_trk_batch_destroy(t->single);
     if (t->d_code) cudaFree(t->d_code);
     if (t->d_data_code) cudaFree(t->d_data_code);
@@ -1802,25 +1832,12 @@ extern "C" int gb200_trk_correlate_16sc(gb200_trk* t, int stream_id, uint64_t fi
     return GB200_OK;
 }
 
-extern "C" int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_sample_index, float rem_carr_phase_rad,
-    float phase_step_rad, float phase_rate_step_rad, float rem_code_phase_chips, float code_phase_step_chips,
-    float code_phase_rate_step_chips, int n_samples, float* corr_out_iq)
+// one request, its own launch (the path of batch_window_us == 0, and the fall-back that isolates a failing request of a batch)
+static int trk_correlate_direct(gb200_trk* t, const gb200_trk_req& r, float* corr_out_iq)
 {
-    if (!t || !corr_out_iq) return GB200_E_INVALID;
     gb200_service* s = t->s;
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
-    gb200_trk_req r;
-    r.trk = t;
-    r.stream_id = stream_id;
-    r.first_sample_index = first_sample_index;
-    r.rem_carr_phase_rad = rem_carr_phase_rad;
-    r.phase_step_rad = phase_step_rad;
-    r.phase_rate_step_rad = phase_rate_step_rad;
-    r.rem_code_phase_chips = rem_code_phase_chips;
-    r.code_phase_step_chips = code_phase_step_chips;
-    r.code_phase_rate_step_chips = code_phase_rate_step_chips;
-    r.n_samples = n_samples;
     int rc;
     if (!t->single)
         {
@@ -1837,5 +1854,86 @@ extern "C" int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_s
     GB_CUDA(s, cudaMemcpyAsync(b->h_out, b->d_out, sizeof(float2) * GB200_OUT_STRIDE, cudaMemcpyDeviceToHost, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
     memcpy(corr_out_iq, b->h_out, sizeof(float2) * (t->n_taps + (t->has_data ? 1 : 0)));
+    return GB200_OK;
+}
+
+extern "C" int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_sample_index, float rem_carr_phase_rad,
+    float phase_step_rad, float phase_rate_step_rad, float rem_code_phase_chips, float code_phase_step_chips,
+    float code_phase_rate_step_chips, int n_samples, float* corr_out_iq)
+{
+    if (!t || !corr_out_iq) return GB200_E_INVALID;
+    gb200_service* s = t->s;
+    gb200_trk_req r;
+    r.trk = t;
+    r.stream_id = stream_id;
+    r.first_sample_index = first_sample_index;
+    r.rem_carr_phase_rad = rem_carr_phase_rad;
+    r.phase_step_rad = phase_step_rad;
+    r.phase_rate_step_rad = phase_rate_step_rad;
+    r.rem_code_phase_chips = rem_code_phase_chips;
+    r.code_phase_step_chips = code_phase_step_chips;
+    r.code_phase_rate_step_chips = code_phase_rate_step_chips;
+    r.n_samples = n_samples;
+    if (s->batch_window_us == 0 || t->c.code_kind == GB200_CODE_16SC) return trk_correlate_direct(t, r, corr_out_iq);
+
+    // ---- coalescing: every channel's thread queues its epoch; the first one in collects for at most batch_window_us (or until
+    // every live channel has arrived), launches ONE batch for all of them and hands the results back ----
+    gb200_service::TrkPending me{r, corr_out_iq, GB200_OK, false};
+    std::unique_lock<std::mutex> lk(s->qmu);
+    s->queue.push_back(&me);
+    if (s->collecting)
+        {
+            s->qcv.notify_all();  // the collector re-checks "everyone here?"
+            s->qcv.wait(lk, [&] { return me.done; });
+            return me.rc;
+        }
+    s->collecting = true;
+    const auto deadline = std::chrono::steady_clock::now() + std::chrono::microseconds(s->batch_window_us);
+    s->qcv.wait_until(lk, deadline, [&] {
+        const int have = (int)s->queue.size();
+        return have >= s->live_trk || (!s->running && have >= std::max(1, std::min(s->prev_batch_n, s->live_trk)));
+    });
+    // the GPU lane is still busy with the previous batch: nothing is lost by collecting until it is done
+    s->qcv.wait(lk, [&] { return !s->running; });
+    std::vector<gb200_service::TrkPending*> batch;
+    batch.swap(s->queue);
+    s->prev_batch_n = (int)batch.size();
+    s->running = true;
+    s->collecting = false;  // the next arrival starts collecting the next batch while this one runs
+    lk.unlock();
+    const int n = (int)batch.size();
+    std::vector<gb200_trk_req> reqs(n);
+    for (int i = 0; i < n; i++) reqs[i] = batch[i]->req;
+    std::vector<float> outs((size_t)n * 2 * GB200_OUT_STRIDE);
+    int rc = gb200_trk_correlate_batch(s, n, reqs.data(), outs.data());
+    if (rc != GB200_OK && n > 1)
+        {
+            // one bad request (e.g. samples already overwritten in the ring) must not fail the others: redo one by one
+            for (int i = 0; i < n; i++) batch[i]->rc = trk_correlate_direct(batch[i]->req.trk, batch[i]->req, batch[i]->out);
+        }
+    else
+        for (int i = 0; i < n; i++)
+            {
+                batch[i]->rc = rc;
+                const gb200_trk* ti = batch[i]->req.trk;
+                if (rc == GB200_OK) memcpy(batch[i]->out, &outs[(size_t)i * 2 * GB200_OUT_STRIDE], sizeof(float2) * (ti->n_taps + (ti->has_data ? 1 : 0)));
+            }
+    lk.lock();
+    s->coalesced_batches++;
+    s->coalesced_requests += (uint64_t)n;
+    for (int i = 0; i < n; i++) batch[i]->done = true;
+    s->running = false;
+    const int my_rc = me.rc;
+    lk.unlock();
+    s->qcv.notify_all();
+    return my_rc;
+}
+
+extern "C" int gb200_service_coalescing_stats(gb200_service* s, uint64_t* batches, uint64_t* requests)
+{
+    if (!s) return GB200_E_INVALID;
+    std::lock_guard<std::mutex> lk(s->qmu);
+    if (batches) *batches = s->coalesced_batches;
+    if (requests) *requests = s->coalesced_requests;
     return GB200_OK;
 }

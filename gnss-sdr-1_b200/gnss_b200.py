@@ -29,7 +29,8 @@ class Gb200Error(RuntimeError):
 
 
 class ServiceCfg(C.Structure):
-    _fields_ = [("device", C.c_int), ("max_streams", C.c_int), ("ring_capacity", C.c_uint64), ("ring_slack", C.c_uint64)]
+    _fields_ = [("device", C.c_int), ("max_streams", C.c_int), ("ring_capacity", C.c_uint64), ("ring_slack", C.c_uint64),
+                ("batch_window_us", C.c_uint32), ("reserved_", C.c_uint32)]
 
 
 class AcqCfg(C.Structure):
@@ -68,7 +69,7 @@ class TrkReq(C.Structure):
 EXPORTS = [
     "gb200_service_create", "gb200_service_destroy", "gb200_last_error", "gb200_version", "gb200_service_cuda_stream",
     "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
-    "gb200_service_flush_l2", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
+    "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
     "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
@@ -103,6 +104,7 @@ def lib():
     L.gb200_service_timer_start.argtypes = [vp]
     L.gb200_service_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.gb200_service_flush_l2.argtypes = [vp, C.c_size_t]
+    L.gb200_service_coalescing_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.gb200_service_measure_fp32.argtypes = [vp, C.POINTER(C.c_double)]
     L.gb200_service_kernel_timing.argtypes = [vp, i]
     L.gb200_service_kernel_stats.argtypes = [vp, i, C.POINTER(C.c_double), C.POINTER(u64)]
@@ -146,10 +148,10 @@ def _ptr(a):
 class Service:
     """gb200_service: one per process and GPU."""
 
-    def __init__(self, device=-1, max_streams=4, ring_capacity=1 << 24, ring_slack=1 << 21):
+    def __init__(self, device=-1, max_streams=4, ring_capacity=1 << 24, ring_slack=1 << 21, batch_window_us=0):
         self.L = lib()
         self.h = C.c_void_p()
-        cfg = ServiceCfg(device, max_streams, ring_capacity, ring_slack)
+        cfg = ServiceCfg(device, max_streams, ring_capacity, ring_slack, batch_window_us, 0)
         rc = self.L.gb200_service_create(C.byref(cfg), C.byref(self.h))
         if rc:
             raise Gb200Error(rc, self.L.gb200_last_error(None).decode())
@@ -157,6 +159,11 @@ class Service:
     def check(self, rc):
         if rc:
             raise Gb200Error(rc, self.L.gb200_last_error(self.h).decode())
+
+    def coalescing_stats(self):
+        b, r = C.c_uint64(), C.c_uint64()
+        self.check(self.L.gb200_service_coalescing_stats(self.h, C.byref(b), C.byref(r)))
+        return b.value, r.value
 
     def close(self):
         if self.h:

@@ -44,6 +44,9 @@ typedef struct gb200_service_cfg
     int max_streams;            /* number of sample streams (front-end bands); 0 -> 4 */
     uint64_t ring_capacity;     /* items kept per stream on the device; 0 -> 1<<24 */
     uint64_t ring_slack;        /* longest window a single acquisition / correlation may read; 0 -> 1<<21 */
+    uint32_t batch_window_us;   /* > 0: concurrent gb200_trk_correlate callers (one GNU Radio thread per channel) are coalesced into ONE
+                                 * launch; the first caller waits at most this long for the other live channels.  0: every call launches alone */
+    uint32_t reserved_;
 } gb200_service_cfg;
 
 int gb200_service_create(const gb200_service_cfg* cfg, gb200_service** out);
@@ -74,6 +77,8 @@ int gb200_service_kernel_stats(gb200_service* s, int kernel_class, double* total
 int gb200_service_measure_fp32(gb200_service* s, double* tflops);
 /* write `bytes` of device memory on the service stream (L2 flush between timed iterations) */
 int gb200_service_flush_l2(gb200_service* s, size_t bytes);
+/* how many coalesced launches served how many gb200_trk_correlate calls so far (batch_window_us > 0) */
+int gb200_service_coalescing_stats(gb200_service* s, uint64_t* batches, uint64_t* requests);
 
 /* Hand a block of the conditioned sample stream to the device ONCE for all channels.  Replaces each
  * block's own read of input_items[0] (pcps_acquisition.cc:995-1034 state 1 buffering;

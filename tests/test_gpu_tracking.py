@@ -220,3 +220,54 @@ def test_int16_correlator_bit_exact(service):
         for mc in mcs:
             mc.close()
     assert saturated >= 6
+
+
+def test_service_coalesces_concurrent_channel_threads():
+    """One thread per channel (the GNU Radio model) calling the blocking gb200_trk_correlate: with batch_window_us > 0 the service
+    serves them with far fewer launches than calls, and every caller gets exactly the result of a lone call."""
+    import threading
+
+    import gnss_b200 as gb
+
+    n_ch, epochs, n = 16, 40, 4000
+    rng = np.random.default_rng(8)
+    x = (rng.standard_normal(n * (epochs + 2)) + 1j * rng.standard_normal(n * (epochs + 2))).astype(np.complex64)
+    params = [(0.1 * c, 0.002 * (c + 1), 0.05 * c, 1023.0 / 4000.0 * (1 + 1e-6 * c)) for c in range(n_ch)]
+    shifts = np.array([-0.5, 0.0, 0.5], np.float32)
+
+    def run(window):
+        svc = gb.Service(ring_capacity=1 << 20, ring_slack=1 << 16, batch_window_us=window)
+        try:
+            svc.push(0, x, gb.ITEM_32FC, 0)
+            chans = []
+            for c in range(n_ch):
+                m = gb.Multicorrelator(svc, 3, 1023)
+                m.set_local_code_and_taps(synth.code_table("gps_l1_ca", 1 + c), shifts)
+                chans.append(m)
+            out = np.zeros((n_ch, epochs, 3), np.complex64)
+            l0 = svc.launch_count()
+
+            def worker(c):
+                rc, ps, rcode, cs = params[c]
+                for e in range(epochs):
+                    out[c, e] = chans[c].correlate(0, e * n, rc + 0.01 * e, ps, rcode, cs, n)
+
+            th = [threading.Thread(target=worker, args=(c,)) for c in range(n_ch)]
+            for t in th:
+                t.start()
+            for t in th:
+                t.join()
+            launches = svc.launch_count() - l0
+            stats = svc.coalescing_stats()
+            for m in chans:
+                m.close()
+            return out, launches, stats
+        finally:
+            svc.close()
+
+    alone, launches_alone, _ = run(0)
+    together, launches_together, (batches, requests) = run(2000)
+    assert launches_alone == n_ch * epochs
+    assert requests == n_ch * epochs and batches == launches_together
+    assert launches_together <= launches_alone // 3, (launches_together, launches_alone)
+    assert np.array_equal(alone, together)
