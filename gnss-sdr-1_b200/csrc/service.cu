@@ -1354,7 +1354,7 @@ struct gb200_trk
 struct TrkGroup
 {
     int first = 0, count = 0;  // range in the (sorted) work array
-    int n_taps = 0, item_type = 0, code_kind = 0, max_n = 0;
+    int n_taps = 0, item_type = 0, code_kind = 0, max_n = 0, prompt_tap = 0;
     bool has_data = false, high_dyn = false;
 };
 
@@ -1533,11 +1533,13 @@ static void trk_group_key(const gb200_trk* t, TrkGroup* g)
     g->code_kind = t->c.code_kind;
     g->has_data = t->has_data;
     g->high_dyn = t->c.high_dyn != 0;
+    g->prompt_tap = t->prompt_tap;
 }
 
 static bool trk_same_group(const TrkGroup& a, const TrkGroup& b)
 {
-    return a.n_taps == b.n_taps && a.item_type == b.item_type && a.code_kind == b.code_kind && a.has_data == b.has_data && a.high_dyn == b.high_dyn;
+    return a.n_taps == b.n_taps && a.item_type == b.item_type && a.code_kind == b.code_kind && a.has_data == b.has_data && a.high_dyn == b.high_dyn &&
+           (!a.has_data || a.prompt_tap == b.prompt_tap);
 }
 
 // (re)build the work array of a batch from requests; buffers must already be sized for b->n requests
@@ -1676,7 +1678,7 @@ extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
         {
             // every group shares max_chunks (the partial-sum pitch) so request slots stay independent
             gb_kt_begin(s, GB200_KCLASS_TRK);
-            cudaError_t e = gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.item_type, g.code_kind,
+            cudaError_t e = gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.prompt_tap, g.item_type, g.code_kind,
                 g.high_dyn, b->d_partials, b->d_counters, b->d_out, b->chunk, s->stream, &l);
             gb_kt_end(s);
             GB_CUDA(s, e);

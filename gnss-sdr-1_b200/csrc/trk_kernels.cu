@@ -39,7 +39,23 @@ __device__ __forceinline__ int wrap_index(int idx, int len)
     return r < 0 ? r + len : r;
 }
 
-template <int ITEM, int NT, bool HAS_DATA, bool CPLX>
+// shared-memory loads by 32-bit shared address: the window index is folded into ONE address computation
+// (bits * 4 + (window base - 4 * wbase)) instead of a subtract plus a scaled add per tap
+__device__ __forceinline__ float lds_f32(unsigned addr)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float2 lds_f32x2(unsigned addr)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+
+// PROMPT: compile-time index of the tap the data-component code rides on (-1: read GbTrkWork::prompt_tap at run time)
+template <int ITEM, int NT, bool HAS_DATA, bool CPLX, int PROMPT>
 __global__ void __launch_bounds__(GB200_TRK_THREADS)
     gb_trk_kernel(const GbTrkWork* __restrict__ work, int chunk, int max_chunks, float2* __restrict__ partials,
         unsigned* __restrict__ counters, float2* __restrict__ out, int nt_runtime)
@@ -120,6 +136,9 @@ __global__ void __launch_bounds__(GB200_TRK_THREADS)
     float nf = (float)n;  // exact: n < 2^24
     if (window_ok)
         {
+            // shared address of window entry 0 minus the float-magic bias: entry(bits) = swin + bits * stride
+            const unsigned swin = (unsigned)__cvta_generic_to_shared(s_win) - (unsigned)wbase * (CPLX ? 8u : 4u);
+            const int prompt = PROMPT >= 0 ? PROMPT : w.prompt_tap;
 #pragma unroll 4
             for (; n < n1; n += GB200_TRK_THREADS)
                 {
@@ -127,33 +146,36 @@ __global__ void __launch_bounds__(GB200_TRK_THREADS)
                     const float wr = fmaf(x.x, ph.x, -x.y * ph.y);
                     const float wi = fmaf(x.x, ph.y, x.y * ph.x);
                     const float sn = __fmul_rn(step, nf);
+                    unsigned ap = 0;  // shared address of the prompt tap's table entry
 #pragma unroll
                     for (int t = 0; t < NT; t++)
                         {
                             if (t < nt)
                                 {
                                     const float v = __fsub_rn(__fadd_rn(sn, shifts[t]), rem);
-                                    const int j = __float_as_int(__fadd_rd(v, kFloorMagic)) - wbase;
+                                    const unsigned bits = (unsigned)__float_as_int(__fadd_rd(v, kFloorMagic));
                                     if (CPLX)
                                         {
-                                            const float2 c = *reinterpret_cast<const float2*>(&s_win[2 * j]);
+                                            const float2 c = lds_f32x2(swin + bits * 8u);
                                             // (wr + j wi) * (c.x + j c.y), reference order: w * code
                                             acc[t].x += fmaf(wr, c.x, -wi * c.y);
                                             acc[t].y += fmaf(wr, c.y, wi * c.x);
                                         }
                                     else
                                         {
-                                            const float c = s_win[j];
+                                            const unsigned a = swin + bits * 4u;
+                                            const float c = lds_f32(a);
                                             acc[t].x = fmaf(wr, c, acc[t].x);
                                             acc[t].y = fmaf(wi, c, acc[t].y);
-                                            if (HAS_DATA && t == w.prompt_tap)
-                                                {
-                                                    const float cd = s_win[GB200_TRK_WMAX + j];
-                                                    acc[NT].x = fmaf(wr, cd, acc[NT].x);
-                                                    acc[NT].y = fmaf(wi, cd, acc[NT].y);
-                                                }
+                                            if (HAS_DATA && (PROMPT >= 0 ? t == PROMPT : t == prompt)) ap = a;
                                         }
                                 }
+                        }
+                    if (HAS_DATA && !CPLX)
+                        {
+                            const float cd = lds_f32(ap + 4u * GB200_TRK_WMAX);  // the data table sits WMAX floats after the pilot's
+                            acc[NT].x = fmaf(wr, cd, acc[NT].x);
+                            acc[NT].y = fmaf(wi, cd, acc[NT].y);
                         }
                     ph = gb_cmul(ph, adv256);
                     nf += (float)GB200_TRK_THREADS;
@@ -369,11 +391,12 @@ __global__ void __launch_bounds__(GB200_TRK_THREADS)
 }
 
 template <int ITEM>
-cudaError_t launch_item(const GbTrkWork* d_work, dim3 grid, int n_taps, bool has_data, int code_kind, bool high_dyn,
+cudaError_t launch_item(const GbTrkWork* d_work, dim3 grid, int n_taps, bool has_data, int prompt_tap, int code_kind, bool high_dyn,
     int chunk, int max_chunks, float2* d_partials, unsigned* d_counters, float2* d_out, cudaStream_t st)
 {
     dim3 block(GB200_TRK_THREADS);
-#define GB_LAUNCH(NT, HD, CP) gb_trk_kernel<ITEM, NT, HD, CP><<<grid, block, 0, st>>>(d_work, chunk, max_chunks, d_partials, d_counters, d_out, n_taps)
+#define GB_LAUNCH(NT, HD, CP) gb_trk_kernel<ITEM, NT, HD, CP, -1><<<grid, block, 0, st>>>(d_work, chunk, max_chunks, d_partials, d_counters, d_out, n_taps)
+#define GB_LAUNCH_P(NT, P) gb_trk_kernel<ITEM, NT, true, false, P><<<grid, block, 0, st>>>(d_work, chunk, max_chunks, d_partials, d_counters, d_out, n_taps)
     if (high_dyn)
         gb_trk_hd_kernel<ITEM><<<grid, block, 0, st>>>(d_work, chunk, max_chunks, d_partials, d_counters, d_out);
     else if (code_kind == GB200_CODE_CPLX)
@@ -382,10 +405,14 @@ cudaError_t launch_item(const GbTrkWork* d_work, dim3 grid, int n_taps, bool has
         GB_LAUNCH(1, false, false);
     else if (n_taps == 3 && !has_data)
         GB_LAUNCH(3, false, false);
+    else if (n_taps == 3 && has_data && prompt_tap == 1)
+        GB_LAUNCH_P(3, 1);
     else if (n_taps == 3 && has_data)
         GB_LAUNCH(3, true, false);
     else if (n_taps == 5 && !has_data)
         GB_LAUNCH(5, false, false);
+    else if (n_taps == 5 && has_data && prompt_tap == 2)
+        GB_LAUNCH_P(5, 2);
     else if (n_taps == 5 && has_data)
         GB_LAUNCH(5, true, false);
     else if (has_data)
@@ -393,12 +420,13 @@ cudaError_t launch_item(const GbTrkWork* d_work, dim3 grid, int n_taps, bool has
     else
         GB_LAUNCH(GB200_MAX_TAPS, false, false);
 #undef GB_LAUNCH
+#undef GB_LAUNCH_P
     return cudaGetLastError();
 }
 
 }  // namespace
 
-cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_taps, bool has_data, int item_type,
+cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_taps, bool has_data, int prompt_tap, int item_type,
     int code_kind, bool high_dyn, float2* d_partials, unsigned* d_counters, float2* d_out, int chunk, cudaStream_t st,
     int* launches)
 {
@@ -409,13 +437,13 @@ cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_
     switch (item_type)
         {
         case GB200_ITEM_32FC:
-            e = launch_item<GB200_ITEM_32FC>(d_work, grid, n_taps, has_data, code_kind, high_dyn, chunk, max_chunks, d_partials, d_counters, d_out, st);
+            e = launch_item<GB200_ITEM_32FC>(d_work, grid, n_taps, has_data, prompt_tap, code_kind, high_dyn, chunk, max_chunks, d_partials, d_counters, d_out, st);
             break;
         case GB200_ITEM_16IC:
-            e = launch_item<GB200_ITEM_16IC>(d_work, grid, n_taps, has_data, code_kind, high_dyn, chunk, max_chunks, d_partials, d_counters, d_out, st);
+            e = launch_item<GB200_ITEM_16IC>(d_work, grid, n_taps, has_data, prompt_tap, code_kind, high_dyn, chunk, max_chunks, d_partials, d_counters, d_out, st);
             break;
         case GB200_ITEM_8IC:
-            e = launch_item<GB200_ITEM_8IC>(d_work, grid, n_taps, has_data, code_kind, high_dyn, chunk, max_chunks, d_partials, d_counters, d_out, st);
+            e = launch_item<GB200_ITEM_8IC>(d_work, grid, n_taps, has_data, prompt_tap, code_kind, high_dyn, chunk, max_chunks, d_partials, d_counters, d_out, st);
             break;
         default:
             return cudaErrorInvalidValue;
