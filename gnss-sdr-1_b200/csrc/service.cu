@@ -1448,6 +1448,20 @@ extern "C" int gb200_trk_set_local_code_and_taps(gb200_trk* t, const void* code,
     return GB200_OK;
 }
 
+extern "C" int gb200_trk_set_taps(gb200_trk* t, const float* shifts, int n_taps)
+{
+    if (!t || !shifts) return GB200_E_INVALID;
+    gb200_service* s = t->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    if (n_taps != t->n_taps)
+        {
+            s->set_error("gb200_trk_set_taps: n_taps differs from the handle's current tap count");
+            return GB200_E_INVALID;
+        }
+    for (int i = 0; i < n_taps; i++) t->shifts[i] = shifts[i];
+    return GB200_OK;
+}
+
 extern "C" int gb200_trk_set_data_code(gb200_trk* t, const float* code, int code_len, int prompt_tap)
 {
     if (!t) return GB200_E_INVALID;

@@ -74,7 +74,7 @@ EXPORTS = [
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid",
-    "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_correlate",
+    "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_set_taps", "gb200_trk_correlate",
     "gb200_trk_correlate_batch", "gb200_trk_correlate_16sc", "gb200_trk_correlate_16sc_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
 ]
 
@@ -315,6 +315,11 @@ class Multicorrelator:
         self.s.check(self.s.L.gb200_trk_set_local_code_and_taps(self.h, _ptr(c), c.size if n_items is None else n_items, _ptr(sh), sh.size))
         self.n_taps = sh.size
         self.n_out = sh.size
+
+    def set_taps(self, shifts):
+        """Tap offsets only (narrow-spacing switch, dll_pll_veml_tracking.cc:1753-1764)."""
+        sh = np.ascontiguousarray(shifts, np.float32)
+        self.s.check(self.s.L.gb200_trk_set_taps(self.h, _ptr(sh), sh.size))
 
     def set_data_code(self, code, prompt_tap):
         c = np.ascontiguousarray(code, np.float32)

@@ -4,6 +4,7 @@
 // replaced by an explicit run(samp_count): the block's own buffering state machine (general_work, :941-1054) only decides
 // WHICH d_consumed_samples items to search, and here those are named by their absolute sample index in the device ring.
 #pragma once
+#include <cmath>
 #include <complex>
 #include <cstdint>
 #include <string>
@@ -21,6 +22,22 @@ struct AcqSynchro
     uint32_t Acq_doppler_step = 0;
     bool Flag_valid_acquisition = false;
 };
+
+// = the adapters' calculate_threshold(pfa) (gps_l1_ca_pcps_acquisition.cc:262-279, galileo_e1_pcps_ambiguous_acquisition.cc:299-317):
+// the (1 - pfa)^(1 / ncells) quantile of an exponential distribution with rate lambda = vector_length, which is
+// -log1p(-p) / lambda (what boost::math::quantile evaluates).  The bin count loop is inclusive (<= doppler_max), unlike the
+// block's own grid (pcps_acquisition.cc:326), and ncells is an unsigned 32-bit product, both as written there.
+inline float pcps_threshold_from_pfa(float pfa, unsigned doppler_max, unsigned doppler_step, unsigned vector_length)
+{
+    unsigned frequency_bins = 0;
+    if (doppler_step == 0) return 0.0f;
+    for (int doppler = -static_cast<int>(doppler_max); doppler <= static_cast<int>(doppler_max); doppler += static_cast<int>(doppler_step)) frequency_bins++;
+    const unsigned ncells = vector_length * frequency_bins;
+    const double exponent = 1 / static_cast<double>(ncells);
+    const double val = std::pow(1.0 - pfa, exponent);
+    const double lambda = static_cast<double>(vector_length);
+    return static_cast<float>(-std::log1p(-val) / lambda);
+}
 
 class B200_Pcps_Acquisition
 {

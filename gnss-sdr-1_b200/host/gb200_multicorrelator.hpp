@@ -41,6 +41,13 @@ public:
         if (!h_ || n_taps != n_) return false;
         return gb200_trk_set_local_code_and_taps(h_, local_code_in, code_length_chips, shifts_chips, n_taps) == GB200_OK;
     }
+    // the reference keeps a POINTER to the caller's shift array and the tracking block edits it in place when it switches to the
+    // narrow spacings (dll_pll_veml_tracking.cc:1753-1764); here the new values are handed over explicitly
+    bool set_taps(const float* shifts_chips, int n_taps)
+    {
+        if (!h_ || n_taps != n_) return false;
+        return gb200_trk_set_taps(h_, shifts_chips, n_taps) == GB200_OK;
+    }
     // pilot tracking: what correlator_data_cpu does with identical NCO arguments (dll_pll_veml_tracking.cc:899-909)
     bool set_data_code(const float* code, int code_length_chips, int prompt_tap)
     {

@@ -4,6 +4,7 @@
 #include <memory>
 
 #include "gb200_acquisition.hpp"
+#include "gb200_host_flat.h"
 #include "gb200_multicorrelator.hpp"
 #include "gb200_tracking.hpp"
 
@@ -45,91 +46,12 @@ struct gbh_trk
     std::unique_ptr<DllPllVemlTracking<B200_Multicorrelator_Real_Codes>> loop;
 };
 
-// flat POD image of DllPllConf for ctypes
-struct gbh_trk_conf
-{
-    double fs_in;
-    int vector_length;
-    float pll_bw_hz, dll_bw_hz, fll_bw_hz;
-    int pll_filter_order, dll_filter_order;
-    int enable_fll_pull_in, enable_fll_steady_state;
-    float pull_in_time_s, early_late_space_chips, very_early_late_space_chips;
-    int cn0_samples;
-    float cn0_min;
-    int max_lock_fail;
-    float carrier_lock_th;
-    int track_pilot, veml;
-    double signal_carrier_freq, code_chip_rate;
-    int code_length_chips, code_samples_per_chip;
-    double code_period;
-};
-
-// one epoch, flat
-struct gbh_epoch
-{
-    int valid, loss_of_lock, state, current_prn_length_samples;
-    uint64_t tracking_sample_counter;
-    double prompt_i, prompt_q, code_phase_samples, carrier_phase_rads, carrier_doppler_hz, cn0_db_hz, code_error_chips, carr_phase_error_hz, code_freq_chips;
-    float taps_iq[12];
-};
-
-DllPllConf gbh_to_conf(const gbh_trk_conf* c)
-{
-    DllPllConf d;
-    d.fs_in = c->fs_in;
-    d.vector_length = c->vector_length;
-    d.pll_bw_hz = c->pll_bw_hz;
-    d.dll_bw_hz = c->dll_bw_hz;
-    d.fll_bw_hz = c->fll_bw_hz;
-    d.pll_filter_order = c->pll_filter_order;
-    d.dll_filter_order = c->dll_filter_order;
-    d.enable_fll_pull_in = c->enable_fll_pull_in != 0;
-    d.enable_fll_steady_state = c->enable_fll_steady_state != 0;
-    d.pull_in_time_s = c->pull_in_time_s;
-    d.early_late_space_chips = c->early_late_space_chips;
-    d.very_early_late_space_chips = c->very_early_late_space_chips;
-    d.cn0_samples = c->cn0_samples;
-    d.cn0_min = c->cn0_min;
-    d.max_lock_fail = c->max_lock_fail;
-    d.carrier_lock_th = c->carrier_lock_th;
-    d.track_pilot = c->track_pilot != 0;
-    d.veml = c->veml != 0;
-    d.signal_carrier_freq = c->signal_carrier_freq;
-    d.code_chip_rate = c->code_chip_rate;
-    d.code_length_chips = c->code_length_chips;
-    d.code_samples_per_chip = c->code_samples_per_chip;
-    d.code_period = c->code_period;
-    return d;
-}
-
-void gbh_fill_epoch(const TrackingEpoch& e, int state, gbh_epoch* out)
-{
-    out->valid = e.flag_valid_symbol_output;
-    out->loss_of_lock = e.loss_of_lock;
-    out->state = state;
-    out->current_prn_length_samples = e.current_prn_length_samples;
-    out->tracking_sample_counter = e.tracking_sample_counter;
-    out->prompt_i = e.prompt_i;
-    out->prompt_q = e.prompt_q;
-    out->code_phase_samples = e.code_phase_samples;
-    out->carrier_phase_rads = e.carrier_phase_rads;
-    out->carrier_doppler_hz = e.carrier_doppler_hz;
-    out->cn0_db_hz = e.cn0_db_hz;
-    out->code_error_chips = e.code_error_chips;
-    out->carr_phase_error_hz = e.carr_phase_error_hz;
-    out->code_freq_chips = e.code_freq_chips;
-    for (int t = 0; t < 6; t++)
-        {
-            out->taps_iq[2 * t] = e.taps[t].real();
-            out->taps_iq[2 * t + 1] = e.taps[t].imag();
-        }
-}
-
 gbh_trk* gbh_trk_open(gb200_service* service, int stream_id, int item_type, const gbh_trk_conf* conf)
 {
     if (!service || !conf) return nullptr;
     auto* h = new gbh_trk();
     const DllPllConf d = gbh_to_conf(conf);
+    h->corr.set_high_dynamics_resampler(d.high_dyn);  // dll_pll_veml_tracking.cc:413
     if (!h->corr.init(service, stream_id, item_type, 2 * d.vector_length, d.veml ? 5 : 3))
         {
             delete h;
@@ -137,6 +59,10 @@ gbh_trk* gbh_trk_open(gb200_service* service, int stream_id, int item_type, cons
         }
     h->loop.reset(new DllPllVemlTracking<B200_Multicorrelator_Real_Codes>(d, &h->corr));
     return h;
+}
+void gbh_trk_set_channel(gbh_trk* h, unsigned channel)
+{
+    if (h) h->loop->set_channel(channel);
 }
 int gbh_trk_start(gbh_trk* h, const float* code, const float* data_code, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp,
     uint64_t sample_counter_now)
@@ -152,6 +78,11 @@ int gbh_trk_step(gbh_trk* h, gbh_epoch* out)
     return ok ? 0 : -2;
 }
 void gbh_trk_close(gbh_trk* h) { delete h; }
+
+float gbh_pcps_threshold_from_pfa(float pfa, unsigned doppler_max, unsigned doppler_step, unsigned vector_length)
+{
+    return pcps_threshold_from_pfa(pfa, doppler_max, doppler_step, vector_length);
+}
 
 // ---- acquisition block mirror: set_state(1) + run(samp_count); returns the event (1 positive, 2 negative, 0 none, <0 error) ----
 int gbh_acq_search(gb200_service* service, const gb200_acq_cfg* conf, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,

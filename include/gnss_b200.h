@@ -180,6 +180,10 @@ int gb200_trk_set_local_code_and_taps(gb200_trk* t, const void* code, int code_l
 /* pilot tracking: the data-component code correlated at the tap `prompt_tap` with identical NCO
  * parameters (dll_pll_veml_tracking.cc:900-910, correlator_data_cpu); adds one output after the n_taps. */
 int gb200_trk_set_data_code(gb200_trk* t, const float* code, int code_len, int prompt_tap);
+/* Tap offsets only, the code tables stay: the reference's tracking block rewrites d_local_code_shift_chips in place when it
+ * switches from the wide to the narrow correlator spacing (dll_pll_veml_tracking.cc:1753-1764; the multicorrelator holds the
+ * pointer, cpu_multicorrelator_real_codes.cc:79-89). */
+int gb200_trk_set_taps(gb200_trk* t, const float* shifts, int n_taps);
 /* = Carrier_wipeoff_multicorrelator_resampler (cpu_multicorrelator_real_codes.h:55; same argument list).
  * corr_out_iq: n_taps (+1 with a data code) complex floats. */
 int gb200_trk_correlate(gb200_trk* t, int stream_id, uint64_t first_sample_index,

@@ -15,14 +15,24 @@ class TrkConf(C.Structure):
                 ("pull_in_time_s", C.c_float), ("early_late_space_chips", C.c_float), ("very_early_late_space_chips", C.c_float),
                 ("cn0_samples", C.c_int), ("cn0_min", C.c_float), ("max_lock_fail", C.c_int), ("carrier_lock_th", C.c_float),
                 ("track_pilot", C.c_int), ("veml", C.c_int), ("signal_carrier_freq", C.c_double), ("code_chip_rate", C.c_double),
-                ("code_length_chips", C.c_int), ("code_samples_per_chip", C.c_int), ("code_period", C.c_double)]
+                ("code_length_chips", C.c_int), ("code_samples_per_chip", C.c_int), ("code_period", C.c_double),
+                ("pll_bw_narrow_hz", C.c_float), ("dll_bw_narrow_hz", C.c_float), ("early_late_space_narrow_chips", C.c_float),
+                ("very_early_late_space_narrow_chips", C.c_float), ("extend_correlation_symbols", C.c_int), ("high_dyn", C.c_int),
+                ("smoother_length", C.c_int), ("secondary", C.c_int), ("symbols_per_bit", C.c_int), ("interchange_iq", C.c_int),
+                ("correlation_length_ms", C.c_int), ("prn", C.c_uint32), ("n_preamble_symbols", C.c_int), ("preamble_symbols", C.c_int32 * 200),
+                ("secondary_code", C.c_char * 128), ("dump_filename", C.c_char * 256)]
 
 
 class Epoch(C.Structure):
     _fields_ = [("valid", C.c_int), ("loss_of_lock", C.c_int), ("state", C.c_int), ("current_prn_length_samples", C.c_int),
                 ("tracking_sample_counter", C.c_uint64), ("prompt_i", C.c_double), ("prompt_q", C.c_double), ("code_phase_samples", C.c_double),
                 ("carrier_phase_rads", C.c_double), ("carrier_doppler_hz", C.c_double), ("cn0_db_hz", C.c_double), ("code_error_chips", C.c_double),
-                ("carr_phase_error_hz", C.c_double), ("code_freq_chips", C.c_double), ("taps_iq", C.c_float * 12)]
+                ("carr_phase_error_hz", C.c_double), ("code_freq_chips", C.c_double), ("taps_iq", C.c_float * 12),
+                ("correlation_length_ms", C.c_int), ("reserved_", C.c_int)]
+
+
+GALILEO_E1_C_SECONDARY_CODE = "0011100000001010110110010"  # Galileo_E1.h:410
+GPS_PREAMBLE_BITS = (1, 0, 0, 0, 1, 0, 1, 1)                # GPS_L1_CA.h:82-85
 
 
 def gps_l1_conf(**kw):
@@ -30,9 +40,41 @@ def gps_l1_conf(**kw):
     d = dict(fs_in=4e6, vector_length=4000, pll_bw_hz=50.0, dll_bw_hz=2.0, fll_bw_hz=35.0, pll_filter_order=3, dll_filter_order=2,
              enable_fll_pull_in=0, enable_fll_steady_state=0, pull_in_time_s=2.0, early_late_space_chips=0.5, very_early_late_space_chips=0.5,
              cn0_samples=20, cn0_min=30.0, max_lock_fail=50, carrier_lock_th=0.80, track_pilot=0, veml=0, signal_carrier_freq=1575.42e6,
-             code_chip_rate=1.023e6, code_length_chips=1023, code_samples_per_chip=1, code_period=0.001)
+             code_chip_rate=1.023e6, code_length_chips=1023, code_samples_per_chip=1, code_period=0.001,
+             pll_bw_narrow_hz=20.0, dll_bw_narrow_hz=2.0, early_late_space_narrow_chips=0.5, very_early_late_space_narrow_chips=0.5,
+             extend_correlation_symbols=1, high_dyn=0, smoother_length=10, secondary=0, symbols_per_bit=20, interchange_iq=0,
+             correlation_length_ms=1, prn=1, n_preamble_symbols=0, secondary_code=b"", dump_filename=b"",
+             preamble_symbols=[1 if b else -1 for b in GPS_PREAMBLE_BITS for _ in range(20)])
     d.update(kw)
-    return TrkConf(**d)
+    return _conf(d)
+
+
+def _conf(d):
+    d = dict(d)
+    pre = d.pop("preamble_symbols", None)
+    for k in ("secondary_code", "dump_filename"):
+        if isinstance(d.get(k), str):
+            d[k] = d[k].encode()
+    c = TrkConf(**d)
+    if pre is not None:
+        c.n_preamble_symbols = len(pre)
+        for i, v in enumerate(pre):
+            c.preamble_symbols[i] = int(v)
+    return c
+
+
+def galileo_e1_conf(**kw):
+    """The Galileo E1 adapter's defaults (galileo_e1_dll_pll_veml_tracking.cc): PLL 5 Hz, DLL 0.5 Hz, E-L 0.15, VE-VL 0.6 chip, 4 ms
+    code, two table samples per chip; tracking the pilot (E1C) makes the 25-chip secondary code the synchronisation pattern."""
+    d = dict(fs_in=8e6, vector_length=32000, pll_bw_hz=5.0, dll_bw_hz=0.5, fll_bw_hz=35.0, pll_filter_order=3, dll_filter_order=2,
+             enable_fll_pull_in=0, enable_fll_steady_state=0, pull_in_time_s=2.0, early_late_space_chips=0.15, very_early_late_space_chips=0.6,
+             cn0_samples=20, cn0_min=25.0, max_lock_fail=50, carrier_lock_th=0.85, track_pilot=1, veml=1, signal_carrier_freq=1575.42e6,
+             code_chip_rate=1.023e6, code_length_chips=4092, code_samples_per_chip=2, code_period=0.004,
+             pll_bw_narrow_hz=2.0, dll_bw_narrow_hz=0.25, early_late_space_narrow_chips=0.15, very_early_late_space_narrow_chips=0.6,
+             extend_correlation_symbols=1, high_dyn=0, smoother_length=10, secondary=1, symbols_per_bit=1, interchange_iq=0,
+             correlation_length_ms=4, prn=1, n_preamble_symbols=0, secondary_code=GALILEO_E1_C_SECONDARY_CODE, dump_filename=b"")
+    d.update(kw)
+    return _conf(d)
 
 
 _host = None
@@ -63,6 +105,9 @@ def host():
         L.gbh_trk_start.argtypes = [C.c_void_p, f32p, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
         L.gbh_trk_step.argtypes = [C.c_void_p, C.POINTER(Epoch)]
         L.gbh_trk_close.argtypes = [C.c_void_p]
+        L.gbh_trk_set_channel.argtypes = [C.c_void_p, C.c_uint]
+        L.gbh_pcps_threshold_from_pfa.restype = C.c_float
+        L.gbh_pcps_threshold_from_pfa.argtypes = [C.c_float, C.c_uint, C.c_uint, C.c_uint]
         L.gbh_acq_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_int)]
         _host = L
@@ -78,12 +123,13 @@ def oracle_loop():
         L.hol_start.argtypes = [C.c_void_p, f32p, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
         L.hol_step.argtypes = [C.c_void_p, C.POINTER(Epoch)]
         L.hol_close.argtypes = [C.c_void_p]
+        L.hol_set_channel.argtypes = [C.c_void_p, C.c_uint]
         _hol = L
     return _hol
 
 
 FIELDS = ("valid", "loss_of_lock", "state", "current_prn_length_samples", "tracking_sample_counter", "prompt_i", "prompt_q", "code_phase_samples",
-          "carrier_phase_rads", "carrier_doppler_hz", "cn0_db_hz", "code_error_chips", "carr_phase_error_hz", "code_freq_chips")
+          "carrier_phase_rads", "carrier_doppler_hz", "cn0_db_hz", "code_error_chips", "carr_phase_error_hz", "code_freq_chips", "correlation_length_ms")
 
 
 def _record(e):
@@ -92,10 +138,12 @@ def _record(e):
     return d
 
 
-def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None):
+def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None, channel=None):
     L = oracle_loop()
     x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
     h = L.hol_open(x, len(x) // 2, first_index, C.byref(conf))
+    if channel is not None:
+        L.hol_set_channel(h, channel)
     code = np.ascontiguousarray(code, np.float32)
     dc = np.ascontiguousarray(data_code, np.float32) if data_code is not None else None
     assert L.hol_start(h, code, dc.ctypes.data_as(C.c_void_p) if dc is not None else None, acq_delay, acq_doppler, acq_stamp, first_index) == 0
@@ -108,10 +156,12 @@ def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_dopp
     return out
 
 
-def run_b200_channel(service, stream_id, item_type, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None):
+def run_b200_channel(service, stream_id, item_type, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None, channel=None):
     L = host()
     h = L.gbh_trk_open(service.h, stream_id, item_type, C.byref(conf))
     assert h, "gbh_trk_open failed"
+    if channel is not None:
+        L.gbh_trk_set_channel(h, channel)
     code = np.ascontiguousarray(code, np.float32)
     dc = np.ascontiguousarray(data_code, np.float32) if data_code is not None else None
     assert L.gbh_trk_start(h, code, dc.ctypes.data_as(C.c_void_p) if dc is not None else None, acq_delay, acq_doppler, acq_stamp, first_index) == 0

@@ -52,7 +52,11 @@ def sampled_code(table, table_rate, fs, n):
 
 
 def make_iq(fs, n, sats, seed, noise=True):
-    """sats: list of dict(kind, prn, cn0_dbhz, doppler_hz, delay_samples, phase=0.0[, data_kind]).
+    """sats: list of dict(kind, prn, cn0_dbhz, doppler_hz, delay_samples, phase=0.0[, pilot_kind][, symbols][, symbol_periods]
+    [, secondary][, doppler_rate_hz_s]).
+    symbols: +-1 array multiplying the data component, one entry per `symbol_periods` code periods (cyclic);
+    secondary: '0'/'1' string multiplying the pilot (or, without pilot_kind, the only) component per code period, '0' -> +1;
+    doppler_rate_hz_s: linear Doppler drift (carrier phase gets the quadratic term; the code rate follows the mean Doppler).
     Returns complex64[n]."""
     rng = np.random.default_rng(seed)
     if noise:
@@ -64,13 +68,27 @@ def make_iq(fs, n, sats, seed, noise=True):
         tab = code_table(s["kind"], s["prn"]).astype(np.float64)
         rate = TABLE_RATE[s["kind"]] * (1.0 + s["doppler_hz"] / CARRIER_HZ[s["kind"]])
         tau = s["delay_samples"] / fs
-        idx = np.floor((t - tau) * rate).astype(np.int64) % len(tab)
+        pos = np.floor((t - tau) * rate).astype(np.int64)
+        idx = pos % len(tab)
         amp = np.sqrt(2.0 * 10.0 ** (s["cn0_dbhz"] / 10.0) / fs)
         sig = tab[idx]
+        period = pos // len(tab)
+        if "symbols" in s:
+            sym = np.asarray(s["symbols"], np.float64)
+            sig = sig * sym[(period // int(s.get("symbol_periods", 1))) % len(sym)]
+        sec = None
+        if "secondary" in s:
+            sec = np.array([1.0 if ch == "0" else -1.0 for ch in s["secondary"]])[period % len(s["secondary"])]
         if "pilot_kind" in s:  # data + pilot on the same carrier (E1B + E1C: e1b - e1c, both BPSK-on-real here)
             ptab = code_table(s["pilot_kind"], s["prn"]).astype(np.float64)
-            sig = (sig - ptab[idx]) / np.sqrt(2.0)
-        x += amp * sig * np.exp(1j * (2 * np.pi * s["doppler_hz"] * t + s.get("phase", 0.0)))
+            pil = ptab[idx] if sec is None else ptab[idx] * sec
+            sig = (sig - pil) / np.sqrt(2.0)
+        elif sec is not None:
+            sig = sig * sec
+        ph = 2 * np.pi * s["doppler_hz"] * t + s.get("phase", 0.0)
+        if "doppler_rate_hz_s" in s:
+            ph = ph + np.pi * s["doppler_rate_hz_s"] * t * t
+        x += amp * sig * np.exp(1j * ph)
     return x.astype(np.complex64)
 
 

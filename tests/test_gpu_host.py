@@ -81,6 +81,52 @@ def test_c1_closed_loop_matches_oracle_loop(service, item):
         assert abs(dop_g[-200:].mean() - s["doppler_hz"]) < 3.0
 
 
+def test_e1_pilot_extended_integration_matches_oracle_loop(service, tmp_path):
+    """C2 / C5 shape: Galileo E1 pilot channel, VEML taps + data-prompt tap, 16-bit samples at 8 Msps; secondary-code lock, then
+    4-symbol coherent integration with the narrow tap spacings (gb200_trk_set_taps).  Same state sequence as the loop on the oracle
+    correlator, trajectories together, identical dump record stream layout."""
+    import gnss_b200 as gb
+    import test_host_cpu as thc
+
+    fs, doppler, delay = 8e6, 2210.0, 9123
+    x, pilot, data, symbols = thc.e1_scene(255, doppler, delay, cn0=47.0, fs=fs, seed=20260005, prn=11)  # fits the session ring (2^23 items)
+    q = synth.quantize(x, "16ic")
+    service.push(2, q, gb.ITEM_16IC, 0)
+    x = (q[0::2].astype(np.float32) + 1j * q[1::2].astype(np.float32)).astype(np.complex64)
+    kw = dict(fs_in=fs, vector_length=32000, extend_correlation_symbols=4, pll_bw_hz=15.0, dll_bw_hz=2.0, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=0.5,
+              early_late_space_narrow_chips=0.06, very_early_late_space_narrow_chips=0.25, prn=11, pll_filter_order=2)
+    args = dict(code=pilot, acq_delay=float(delay) + 0.4, acq_doppler=doppler - 12.0, acq_stamp=0, n_steps=245, data_code=data)
+    ref = hl.run_oracle_channel(x, 0, hl.galileo_e1_conf(dump_filename=str(tmp_path / "ref_.dat"), **kw), channel=3, **args)
+    got = hl.run_b200_channel(service, 2, gb.ITEM_16IC, 0, hl.galileo_e1_conf(dump_filename=str(tmp_path / "b200_.dat"), **kw), channel=3, **args)
+    assert len(got) == len(ref) == 245 and not any(e["loss_of_lock"] for e in got)
+    st_g, st_r = [e["state"] for e in got], [e["state"] for e in ref]
+    assert st_g == st_r and 3 in st_g and 4 in st_g
+    first3 = st_g.index(3)
+    for g, r in list(zip(got, ref))[1:30]:
+        scale = np.abs(r["taps"]).max()
+        assert g["tracking_sample_counter"] == r["tracking_sample_counter"]
+        assert np.abs(g["taps"] - r["taps"]).max() <= 2e-4 * scale
+    gv, rv = [e for e in got if e["valid"]], [e for e in ref if e["valid"]]
+    dop_g, dop_r = np.array([e["carrier_doppler_hz"] for e in gv]), np.array([e["carrier_doppler_hz"] for e in rv])
+    pos_g = np.array([e["tracking_sample_counter"] + e["code_phase_samples"] for e in gv])
+    pos_r = np.array([e["tracking_sample_counter"] + e["code_phase_samples"] for e in rv])
+    print("E1 closed loop: first state 3 at epoch %d, doppler diff max %.3g Hz, position diff max %.3g samples" % (
+        first3, np.abs(dop_g - dop_r).max(), np.abs(pos_g - pos_r).max()))
+    assert np.abs(dop_g - dop_r).max() < 1.0 and np.abs(pos_g - pos_r).max() < 0.05
+    assert abs(dop_g[-60:].mean() - doppler) < 1.0
+    # narrow taps took effect on the device: E and L move up the correlation peak
+    wide = np.array([np.abs(e["taps"][:5]) for e in got[first3 - 10:first3]])
+    narrow = np.array([np.abs(e["taps"][:5]) for e in got[-40:]])
+    assert (narrow[:, 1] + narrow[:, 3]).mean() / narrow[:, 2].mean() > (wide[:, 1] + wide[:, 3]).mean() / wide[:, 2].mean() + 0.3
+    # dump streams: same record count, integer fields identical, float fields together
+    d_g = np.fromfile(str(tmp_path / "b200_3.dat"), dtype=thc.DUMP_RECORD)
+    d_r = np.fromfile(str(tmp_path / "ref_3.dat"), dtype=thc.DUMP_RECORD)
+    assert len(d_g) == len(d_r) == len(gv)
+    np.testing.assert_array_equal(d_g["PRN_start_sample_count"], d_r["PRN_start_sample_count"])
+    np.testing.assert_array_equal(d_g["PRN"], d_r["PRN"])
+    np.testing.assert_allclose(d_g["abs_P"], d_r["abs_P"], rtol=2e-3)
+
+
 def test_acquisition_block_mirror(service):
     """B200_Pcps_Acquisition driven like Channel drives its adapter: set_channel, set_gnss_synchro, set_doppler_step, set_threshold,
     init, set_local_code, reset, then blocks until an event; positive for a present PRN, negative for an absent one."""

@@ -76,3 +76,137 @@ def test_closed_loop_locks_on_oracle_correlator():
     taps = np.array([e["taps"][:3] for e in tail])
     assert np.abs(taps[:, 1]).mean() > 1.6 * np.abs(taps[:, 0]).mean()
     assert abs(np.abs(taps[:, 0]).mean() - np.abs(taps[:, 2]).mean()) < 0.1 * np.abs(taps[:, 1]).mean()
+
+
+# ---- states 3 / 4, secondary code, preamble, dump (8f N2) --------------------------------------------------
+
+# log_data's record (dll_pll_veml_tracking.cc:1195-1243), the layout tracking_dump_reader.cc:38-60 reads back
+DUMP_RECORD = np.dtype([("abs_VE", "<f4"), ("abs_E", "<f4"), ("abs_P", "<f4"), ("abs_L", "<f4"), ("abs_VL", "<f4"), ("prompt_I", "<f4"), ("prompt_Q", "<f4"),
+                        ("PRN_start_sample_count", "<u8"), ("acc_carrier_phase_rad", "<f4"), ("carrier_doppler_hz", "<f4"),
+                        ("carrier_doppler_rate_hz_s", "<f4"), ("code_freq_chips", "<f4"), ("code_freq_rate_chips", "<f4"), ("carr_error_hz", "<f4"),
+                        ("carr_error_filt_hz", "<f4"), ("code_error_chips", "<f4"), ("code_error_filt_chips", "<f4"), ("CN0_SNV_dB_Hz", "<f4"),
+                        ("carrier_lock_test", "<f4"), ("aux1", "<f4"), ("aux2", "<f8"), ("PRN", "<u4")])
+
+
+def e1_scene(n_epochs, doppler, delay, cn0=46.0, fs=4e6, seed=20260002, prn=3):
+    rng = np.random.default_rng(seed + 1)
+    symbols = rng.integers(0, 2, 4096) * 2.0 - 1.0
+    n = int(n_epochs * 0.004 * fs)
+    x = synth.make_iq(fs, n, [dict(kind="gal_e1b_sinboc", pilot_kind="gal_e1c_sinboc", prn=prn, cn0_dbhz=cn0, doppler_hz=doppler, delay_samples=delay,
+                                   symbols=symbols, secondary=hl.GALILEO_E1_C_SECONDARY_CODE)], seed)
+    return x, synth.code_table("gal_e1c_sinboc", prn), synth.code_table("gal_e1b_sinboc", prn), symbols
+
+
+def test_e1_pilot_secondary_lock_extended_integration_and_dump(tmp_path):
+    """Galileo E1 pilot tracking: wide tracking until the 25-chip secondary code is found in the prompt signs, then the 3 x (integrate)
+    + 1 x (narrow DLL/PLL update) cycle with the narrow tap spacings; the data-prompt tap carries the E1B symbols; every DLL/PLL or
+    integration cycle appends one 96-byte record to <dump_filename><channel>.dat."""
+    doppler, delay, fs = -1270.0, 5333, 4e6
+    x, pilot, data, symbols = e1_scene(430, doppler, delay)
+    dump = str(tmp_path / "trk_dump_.dat")
+    # 2nd-order PLL: the reference's 3rd-order carrier filter (tracking_FLL_PLL_filter.cc:105-118, mirrored bit-exactly) has a lightly damped
+    # pole pair at (-0.1 +- 0.32j) w0 -- seconds of settling at these bandwidths, too long for a CPU test
+    conf = hl.galileo_e1_conf(fs_in=fs, vector_length=16000, extend_correlation_symbols=4, pll_bw_hz=15.0, dll_bw_hz=2.0, pll_bw_narrow_hz=5.0,
+                              dll_bw_narrow_hz=0.5, early_late_space_narrow_chips=0.1, very_early_late_space_narrow_chips=0.3, prn=3,
+                              dump_filename=dump, cn0_min=25.0, pll_filter_order=2)
+    ep = hl.run_oracle_channel(x, 0, conf, pilot, acq_delay=float(delay) + 0.3, acq_doppler=doppler + 20.0, acq_stamp=0, n_steps=420, data_code=data, channel=7)
+    assert not any(e["loss_of_lock"] for e in ep)
+    states = [e["state"] for e in ep]  # state AFTER the step
+    first3 = states.index(3)
+    # the window of 25 prompts has to fill (pull-in step + 25 epochs) and then align with the secondary code's start
+    assert 25 <= first3 <= 130  # plus the PLL pull-in from the 20 Hz acquisition error
+    assert set(states[:first3]) == {2}
+    cyc = states[first3:]
+    assert cyc[:9] == [3, 3, 3, 4, 3, 3, 3, 4, 3]  # (state after each step) 3 integrations in state 3, then the loop update in state 4
+    assert all(e["correlation_length_ms"] == 4 for e in ep if e["valid"])
+    # narrow spacing: the early/late taps sit closer to the prompt -> their magnitude ratio to the prompt rises from (1 - 3*0.15) to (1 - 3*0.1)
+    # for a sinBOC(1,1) main peak (slope 3 per chip)
+    wide = np.array([np.abs(e["taps"][:5]) for e in ep[first3 - 12:first3]])
+    narrow = np.array([np.abs(e["taps"][:5]) for e in ep[-40:]])
+    rw, rn = (wide[:, 1] + wide[:, 3]).mean() / (2 * wide[:, 2].mean()), (narrow[:, 1] + narrow[:, 3]).mean() / (2 * narrow[:, 2].mean())
+    assert 0.45 < rw < 0.65 and rw + 0.1 < rn < 0.90  # (3.9 samples per chip: the sampled correlation function is a staircase)
+    tail = [e for e in ep[-120:] if e["valid"]]
+    dop = np.array([e["carrier_doppler_hz"] for e in tail])
+    assert abs(dop.mean() - doppler) < 1.0 and dop.std() < 2.0
+    # the estimate is refreshed every cn0_samples + 1 loop updates (84 epochs here); the last one is from narrow-tracking prompts only
+    assert abs(tail[-1]["cn0_db_hz"] - 43.0) < 3.0  # the pilot carries half of the 46 dB-Hz
+    # data-prompt tap: E1B symbols, up to the common sign of the carrier lock
+    sc = np.array([e["tracking_sample_counter"] - e["current_prn_length_samples"] for e in tail], np.float64)
+    period = np.round((sc - delay) / 16000.0).astype(int)
+    got = np.sign([e["prompt_i"] for e in tail])
+    want = symbols[period % len(symbols)]
+    assert abs(np.mean(got * want)) > 0.98
+    # dump: one record per valid epoch (state 2 cycles, integrations and narrow updates), 96 bytes each
+    raw = np.fromfile(dump[:-4] + "7.dat", dtype=DUMP_RECORD)
+    valid = [e for e in ep if e["valid"]]
+    assert DUMP_RECORD.itemsize == 96 and len(raw) == len(valid)
+    assert np.all(raw["PRN"] == 3)
+    np.testing.assert_array_equal(raw["PRN_start_sample_count"], [e["tracking_sample_counter"] for e in valid])
+    np.testing.assert_allclose(raw["carrier_doppler_hz"], [e["carrier_doppler_hz"] for e in valid], rtol=1e-6)
+    np.testing.assert_allclose(raw["prompt_I"], [e["prompt_i"] for e in valid], rtol=1e-6)
+    assert np.all(raw["aux2"] == raw["PRN_start_sample_count"].astype(np.float64))
+    # narrow-update records hold the 4-epoch coherent sums: about 4x the single-epoch prompt magnitude
+    st = np.array([e["state"] for e in valid])
+    upd = raw["abs_P"][(st == 3) & (np.arange(len(st)) > first3 + 8)]
+    single = np.abs([e["taps"][2] for e in valid[-40:]]).mean()
+    assert 3.4 < np.median(upd) / single < 4.4
+
+
+def test_gps_preamble_gates_extended_integration():
+    """No secondary code (GPS L1 C/A): the loop stays in state 2 for 10 s, then waits for the telemetry preamble in the prompt signs
+    (160 symbols) and only then starts the 20-symbol coherent integration, aligned with the bit edges."""
+    fs, doppler, delay = 1.023e6, 740.0, 311
+    bits = np.random.default_rng(5).integers(0, 2, 600) * 2 - 1
+    for k in range(0, 600, 30):  # a preamble every 30 bits (0.6 s)
+        bits[k:k + 8] = [1 if b else -1 for b in hl.GPS_PREAMBLE_BITS]
+    n = int(11.9 * fs)
+    x = synth.make_iq(fs, n, [dict(kind="gps_l1_ca", prn=9, cn0_dbhz=50.0, doppler_hz=doppler, delay_samples=delay, symbols=bits.astype(float),
+                                   symbol_periods=20)], 99)
+    conf = hl.gps_l1_conf(fs_in=fs, vector_length=1023, extend_correlation_symbols=20, pll_bw_hz=35.0, pll_bw_narrow_hz=10.0, dll_bw_narrow_hz=1.0,
+                          early_late_space_narrow_chips=0.5, prn=9)
+    ep = hl.run_oracle_channel(x, 0, conf, synth.code_table("gps_l1_ca", 9), acq_delay=float(delay), acq_doppler=doppler - 15.0, acq_stamp=0, n_steps=11800)
+    assert not any(e["loss_of_lock"] for e in ep)
+    states = np.array([e["state"] for e in ep])
+    first3 = int(np.argmax(states == 3))
+    t_switch = ep[first3]["tracking_sample_counter"] / fs
+    assert 10.0 < t_switch < 10.0 + 0.6 + 0.17 and set(states[:first3]) == {2}
+    # the preamble's last symbol is the last code period of a bit: the 20-symbol sums that follow never straddle a bit edge
+    period = int(round((ep[first3]["tracking_sample_counter"] - ep[first3]["current_prn_length_samples"] - delay) / 1023.0))
+    assert (period + 1) % 20 == 0
+    upd = [i for i in range(first3 + 1, len(ep)) if states[i - 1] == 4 or (states[i] == 3 and states[i - 1] == 4)]
+    four = [i for i in range(first3 + 1, len(ep)) if ep[i]["valid"] and states[i - 1] == 3 and states[i] == 4]
+    assert len(four) > 50 and len(upd) > 0
+    assert np.all(np.diff(four) == 20)
+    dop = np.array([ep[i]["carrier_doppler_hz"] for i in four[-30:]])
+    assert abs(dop.mean() - doppler) < 1.0
+
+
+def test_high_dynamics_rate_smoothing_tracks_a_chirp():
+    """high_dyn: the carrier phase-rate handed to the correlator comes from the two-window average of the NCO steps (:1018-1036);
+    on a 400 Hz/s chirp it converges to 2 pi rate / fs^2 and the loop keeps lock."""
+    fs, doppler, rate, delay = 4e6, 500.0, 400.0, 777
+    n = int(1.2 * fs)
+    x = synth.make_iq(fs, n, [dict(kind="gps_l1_ca", prn=4, cn0_dbhz=50.0, doppler_hz=doppler, delay_samples=delay, doppler_rate_hz_s=rate)], 41)
+    conf = hl.gps_l1_conf(high_dyn=1, smoother_length=10, prn=4)
+    ep = hl.run_oracle_channel(x, 0, conf, synth.code_table("gps_l1_ca", 4), acq_delay=float(delay), acq_doppler=doppler, acq_stamp=0, n_steps=1150)
+    assert not any(e["loss_of_lock"] for e in ep)
+    tail = [e for e in ep if e["valid"]][-300:]
+    t = np.array([e["tracking_sample_counter"] for e in tail]) / fs
+    dop = np.array([e["carrier_doppler_hz"] for e in tail])
+    slope = np.polyfit(t, dop, 1)[0]
+    assert abs(slope - rate) < 40.0
+    assert np.abs(dop - (doppler + rate * t)).max() < 25.0
+
+
+def test_threshold_from_pfa_is_the_exponential_quantile():
+    """calculate_threshold (gps_l1_ca_pcps_acquisition.cc:262-279): inclusive bin count, ncells = vector_length * bins,
+    threshold = quantile(Exp(lambda = vector_length), (1 - pfa)^(1 / ncells))."""
+    from scipy.stats import expon
+
+    L = hl.host()
+    for pfa, dmax, step, n in [(0.001, 5000, 250, 4000), (0.01, 5000, 125, 32000), (1e-6, 10000, 500, 8000), (0.1, 5000, 250, 25000)]:
+        bins = len(range(-dmax, dmax + 1, step))
+        val = (1.0 - float(np.float32(pfa))) ** (1.0 / (n * bins))
+        want = expon.ppf(val, scale=1.0 / n)
+        got = L.gbh_pcps_threshold_from_pfa(pfa, dmax, step, n)
+        assert got == pytest.approx(want, rel=1e-6)
