@@ -8,8 +8,10 @@
 #include <complex>
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "../../include/gnss_b200.h"
+#include "gb200_matfile.hpp"
 
 namespace gb200
 {
@@ -21,6 +23,10 @@ struct AcqSynchro
     uint64_t Acq_samplestamp_samples = 0;
     uint32_t Acq_doppler_step = 0;
     bool Flag_valid_acquisition = false;
+    // identity of the satellite searched (gnss_synchro.h:44-48); only the dump file name and its PRN variable read them here
+    char System = 'G';
+    char Signal[3] = {'1', 'C', 0};
+    uint32_t PRN = 0;
 };
 
 // = the adapters' calculate_threshold(pfa) (gps_l1_ca_pcps_acquisition.cc:262-279, galileo_e1_pcps_ambiguous_acquisition.cc:299-317):
@@ -68,7 +74,20 @@ public:
         conf_.doppler_step = doppler_step;
         gb200_acq_set_doppler(h_, conf_.doppler_max, conf_.doppler_step, conf_.freq_offset_hz);
     }
-    void set_threshold(float threshold) { gb200_acq_set_threshold(h_, threshold); }
+    void set_threshold(float threshold)
+    {
+        conf_.threshold = threshold;
+        gb200_acq_set_threshold(h_, threshold);
+    }
+    // dump / dump_filename / dump_channel of Acq_Conf (pcps_acquisition.cc:160-194): one .mat per finished search of `dump_channel`
+    void set_dump(const std::string& dump_filename, unsigned dump_channel)
+    {
+        dump_filename_ = dump_filename;
+        dump_channel_ = dump_channel;
+        dump_ = !dump_filename.empty();
+        gb200_acq_keep_grid(h_, dump_ ? 1 : 0);
+    }
+    const std::string& last_dump_file() const { return last_dump_file_; }
     void init() { gb200_acq_set_doppler(h_, conf_.doppler_max, conf_.doppler_step, conf_.freq_offset_hz); }  // (:313-370): grid rebuilt, nothing stored
     // = pcps_acquisition::set_local_code (:239-274): `code` has d_consumed_samples (or one code period, zero-padded inside) items
     bool set_local_code(const std::complex<float>* code, size_t n_items)
@@ -104,8 +123,11 @@ public:
                 synchro_->Acq_samplestamp_samples = r.acq_samplestamp;
                 synchro_->Acq_doppler_step = conf_.doppler_step;
             }
+        if (r.decision != 3) num_dwells_++;  // d_num_noncoherent_integrations_counter (:711); the step-two pass does not count
         if (r.decision == 1 || r.decision == 0)
             {
+                if (dump_ && channel_ == dump_channel_) dump_results(r);  // (:913-918)
+                num_dwells_ = 0;
                 state_ = 0;  // d_state = 0; d_active = false
                 if (synchro_) synchro_->Flag_valid_acquisition = (r.decision == 1);
                 return r.decision == 1 ? 1 : 2;
@@ -116,6 +138,43 @@ public:
     std::string last_error() const { return gb200_last_error(s_); }
 
 private:
+    // = dump_results (pcps_acquisition.cc:462-562): same file name pattern, variable names, classes and dimensions; written as a
+    // Level-5 MAT-file (see gb200_matfile.hpp).  The step-two narrow grid is not kept on the device and is not dumped.
+    void dump_results(const gb200_acq_result& r)
+    {
+        dump_number_++;
+        const AcqSynchro blank;
+        const AcqSynchro& syn = synchro_ ? *synchro_ : blank;
+        std::string filename = dump_filename_;
+        filename += "_";
+        filename += syn.System;
+        filename += "_";
+        filename += syn.Signal[0];
+        filename += syn.Signal[1];
+        filename += "_ch_" + std::to_string(channel_) + "_" + std::to_string(dump_number_) + "_sat_" + std::to_string(syn.PRN) + ".mat";
+        const uint32_t bins = gb200_acq_num_doppler_bins(h_);
+        const uint32_t eff = conf_.bit_transition_flag ? gb200_acq_fft_size(h_) / 2 : gb200_acq_fft_size(h_);
+        std::vector<float> grid(static_cast<size_t>(bins) * eff);
+        if (gb200_acq_read_grid(h_, grid.data()) != GB200_OK) return;
+        MatFileWriter m(filename);
+        if (!m.ok()) return;
+        // the device grid is [bin][index] row-major, i.e. exactly the column-major (index, bin) matrix grid_ is (:743)
+        m.write("acq_grid", MatFileWriter::kSingle, grid.data(), eff, bins);
+        m.write_scalar<uint32_t>("doppler_max", MatFileWriter::kUint32, conf_.doppler_max);
+        m.write_scalar<uint32_t>("doppler_step", MatFileWriter::kUint32, conf_.doppler_step);
+        m.write_scalar<int32_t>("d_positive_acq", MatFileWriter::kInt32, r.decision == 1 ? 1 : 0);
+        m.write_scalar<float>("acq_doppler_hz", MatFileWriter::kSingle, static_cast<float>(r.acq_doppler_hz));
+        m.write_scalar<float>("acq_delay_samples", MatFileWriter::kSingle, static_cast<float>(r.acq_delay_samples));
+        m.write_scalar<float>("test_statistic", MatFileWriter::kSingle, r.test_statistic);
+        m.write_scalar<float>("threshold", MatFileWriter::kSingle, conf_.threshold);
+        m.write_scalar<float>("input_power", MatFileWriter::kSingle, r.input_power);
+        m.write_scalar<uint64_t>("sample_counter", MatFileWriter::kUint64, r.acq_samplestamp);
+        m.write_scalar<uint32_t>("PRN", MatFileWriter::kUint32, syn.PRN);
+        m.write_scalar<uint32_t>("num_dwells", MatFileWriter::kUint32, num_dwells_);
+        m.close();
+        last_dump_file_ = filename;
+    }
+
     gb200_service* s_;
     gb200_acq_cfg conf_;
     gb200_acq* h_ = nullptr;
@@ -125,5 +184,10 @@ private:
     int state_ = 0;
     bool ok_ = false;
     float mag_ = 0.0f, test_statistics_ = 0.0f;
+    bool dump_ = false;
+    unsigned dump_channel_ = 0;
+    uint32_t num_dwells_ = 0;
+    long long dump_number_ = 0;
+    std::string dump_filename_, last_dump_file_;
 };
 }  // namespace gb200

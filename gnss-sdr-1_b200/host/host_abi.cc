@@ -79,19 +79,49 @@ int gbh_trk_step(gbh_trk* h, gbh_epoch* out)
 }
 void gbh_trk_close(gbh_trk* h) { delete h; }
 
+// the MAT-file writer on its own (the CPU tests read the file back with scipy.io.loadmat)
+int gbh_matfile_write_grid(const char* filename, const float* grid, size_t rows, size_t cols, uint32_t prn, uint64_t sample_counter, int32_t positive)
+{
+    MatFileWriter m(filename);
+    if (!m.ok()) return -1;
+    bool ok = m.write("acq_grid", MatFileWriter::kSingle, grid, rows, cols);
+    ok = ok && m.write_scalar<uint32_t>("PRN", MatFileWriter::kUint32, prn);
+    ok = ok && m.write_scalar<uint64_t>("sample_counter", MatFileWriter::kUint64, sample_counter);
+    ok = ok && m.write_scalar<int32_t>("d_positive_acq", MatFileWriter::kInt32, positive);
+    return ok ? 0 : -2;
+}
+
 float gbh_pcps_threshold_from_pfa(float pfa, unsigned doppler_max, unsigned doppler_step, unsigned vector_length)
 {
     return pcps_threshold_from_pfa(pfa, doppler_max, doppler_step, vector_length);
 }
 
 // ---- acquisition block mirror: set_state(1) + run(samp_count); returns the event (1 positive, 2 negative, 0 none, <0 error) ----
+int gbh_acq_search_dump(gb200_service* service, const gb200_acq_cfg* conf, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,
+    int max_runs, double* delay_samples, double* doppler_hz, uint64_t* samplestamp, float* test_statistic, int* mag, const char* dump_filename,
+    unsigned channel, char system, const char* signal, unsigned prn, char* dump_file_out, size_t dump_file_cap);
+
 int gbh_acq_search(gb200_service* service, const gb200_acq_cfg* conf, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,
     int max_runs, double* delay_samples, double* doppler_hz, uint64_t* samplestamp, float* test_statistic, int* mag)
+{
+    return gbh_acq_search_dump(service, conf, stream_id, code_iq, code_items, samp_count, max_runs, delay_samples, doppler_hz, samplestamp, test_statistic,
+        mag, nullptr, 0, 'G', "1C", 0, nullptr, 0);
+}
+
+// the same search with dump=true on `channel` (pcps_acquisition.cc:160-194, 462-562); the written file's name comes back in dump_file_out
+int gbh_acq_search_dump(gb200_service* service, const gb200_acq_cfg* conf, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,
+    int max_runs, double* delay_samples, double* doppler_hz, uint64_t* samplestamp, float* test_statistic, int* mag, const char* dump_filename,
+    unsigned channel, char system, const char* signal, unsigned prn, char* dump_file_out, size_t dump_file_cap)
 {
     B200_Pcps_Acquisition acq(service, *conf, stream_id);
     if (!acq.ok()) return -1;
     AcqSynchro syn;
-    acq.set_channel(0);
+    syn.System = system;
+    syn.Signal[0] = signal ? signal[0] : '1';
+    syn.Signal[1] = signal ? signal[1] : 'C';
+    syn.PRN = prn;
+    acq.set_channel(channel);
+    if (dump_filename && dump_filename[0]) acq.set_dump(dump_filename, channel);
     acq.set_gnss_synchro(&syn);
     acq.set_doppler_step(conf->doppler_step);
     acq.set_threshold(conf->threshold);
@@ -111,6 +141,11 @@ int gbh_acq_search(gb200_service* service, const gb200_acq_cfg* conf, int stream
     *samplestamp = syn.Acq_samplestamp_samples;
     *test_statistic = acq.test_statistics();
     *mag = acq.mag();
+    if (dump_file_out && dump_file_cap > 0)
+        {
+            std::strncpy(dump_file_out, acq.last_dump_file().c_str(), dump_file_cap - 1);
+            dump_file_out[dump_file_cap - 1] = 0;
+        }
     return ev;
 }
 }

@@ -106,6 +106,10 @@ def host():
         L.gbh_trk_step.argtypes = [C.c_void_p, C.POINTER(Epoch)]
         L.gbh_trk_close.argtypes = [C.c_void_p]
         L.gbh_trk_set_channel.argtypes = [C.c_void_p, C.c_uint]
+        L.gbh_matfile_write_grid.argtypes = [C.c_char_p, f32p, C.c_size_t, C.c_size_t, C.c_uint32, C.c_uint64, C.c_int32]
+        L.gbh_acq_search_dump.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                          C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_char_p, C.c_uint, C.c_char, C.c_char_p, C.c_uint,
+                                          C.c_char_p, C.c_size_t]
         L.gbh_pcps_threshold_from_pfa.restype = C.c_float
         L.gbh_pcps_threshold_from_pfa.argtypes = [C.c_float, C.c_uint, C.c_uint, C.c_uint]
         L.gbh_acq_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),

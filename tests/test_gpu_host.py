@@ -160,3 +160,46 @@ def test_acquisition_block_mirror(service):
     # then reports negative
     ev, _, _, stamp, stat = search(31, 5.0, max_dwells=2)
     assert ev == 2 and 1.0 < stat < 5.0 and stamp == 1000000 + 8000
+
+
+def test_acquisition_dump_matfile(service, tmp_path):
+    """dump=true on the searched channel: one .mat per finished search named like dump_results does (pcps_acquisition.cc:462-477), holding
+    the magnitude grid (effective_fft_size x num_doppler_bins, one column per bin) and the scalars acquisition_dump_reader.cc reads;
+    the grid equals the oracle's grid."""
+    from scipy.io import loadmat
+
+    import gnss_b200 as gb
+    import oracle_lib as ol
+
+    sats, x = c1_scene(8, cn0=58.0)
+    service.push(2, x, gb.ITEM_32FC, 2000000)
+    L = hl.host()
+    prn = sats[2]["prn"]
+    cfg = gb.AcqCfg(sampled_ms=1, ms_per_code=1, samples_per_chip=4, max_dwells=1, doppler_max=5000, doppler_step=250, num_doppler_bins_step2=4,
+                    doppler_step2=125.0, fs_in=4000000, samples_per_ms=4000.0, samples_per_code=4000.0, bit_transition_flag=0,
+                    use_CFAR_algorithm_flag=1, make_2_steps=0, item_type=gb.ITEM_32FC, threshold=0.001, freq_offset_hz=0)
+    code = np.zeros(8000, np.float32)
+    ol.oracle().go_gps_l1_ca_code_sampled(code, prn, 4000000, 0)
+    delay, dop, stamp, stat, mag = C.c_double(), C.c_double(), C.c_uint64(), C.c_float(), C.c_int()
+    name = C.create_string_buffer(512)
+    ev = L.gbh_acq_search_dump(service.h, C.byref(cfg), 2, code, 4000, 2000000, 4, C.byref(delay), C.byref(dop), C.byref(stamp), C.byref(stat),
+                               C.byref(mag), str(tmp_path / "acq_dump").encode(), 5, b"G", b"1C", prn, name, 512)
+    assert ev == 1
+    fn = name.value.decode()
+    assert fn == str(tmp_path / "acq_dump") + "_G_1C_ch_5_1_sat_%d.mat" % prn
+    m = loadmat(fn)
+    assert m["acq_grid"].shape == (4000, 40) and m["acq_grid"].dtype == np.float32
+    assert int(m["doppler_max"][0, 0]) == 5000 and int(m["doppler_step"][0, 0]) == 250 and int(m["PRN"][0, 0]) == prn
+    assert int(m["d_positive_acq"][0, 0]) == 1 and int(m["num_dwells"][0, 0]) == 1 and int(m["sample_counter"][0, 0]) == 2004000
+    assert float(m["acq_doppler_hz"][0, 0]) == dop.value and float(m["acq_delay_samples"][0, 0]) == np.float32(delay.value)
+    assert float(m["test_statistic"][0, 0]) == stat.value and float(m["threshold"][0, 0]) == np.float32(0.001)
+    # peak where the result says, grid equal to the oracle's
+    col, row = np.unravel_index(np.argmax(m["acq_grid"].T), (40, 4000))
+    assert -5000 + 250 * col == int(dop.value) and row == int(delay.value)
+    o = ol.OracleAcq(doppler_max=5000, doppler_step=250, threshold=0.001, keep_grid=1)
+    o.set_local_code(code.view(np.complex64)[:4000].copy())
+    r = o.run(x[:4000], 2004000)
+    want = o.grid()
+    o.close()
+    np.testing.assert_allclose(m["acq_grid"].T, want, rtol=2e-4, atol=1e-6 * want.max())
+    assert float(m["input_power"][0, 0]) == pytest.approx(r.input_power, rel=1e-5)

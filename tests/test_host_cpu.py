@@ -210,3 +210,20 @@ def test_threshold_from_pfa_is_the_exponential_quantile():
         want = expon.ppf(val, scale=1.0 / n)
         got = L.gbh_pcps_threshold_from_pfa(pfa, dmax, step, n)
         assert got == pytest.approx(want, rel=1e-6)
+
+
+def test_matfile_writer_is_read_back_by_scipy(tmp_path):
+    """Level-5 MAT-file with the variable names / classes / dimensions of dump_results (pcps_acquisition.cc:486-535)."""
+    from scipy.io import loadmat
+
+    rng = np.random.default_rng(3)
+    rows, cols = 1000, 7  # (effective_fft_size, num_doppler_bins): one COLUMN per Doppler bin
+    grid = rng.random((cols, rows), dtype=np.float32)  # device layout [bin][index]
+    fn = str(tmp_path / "acq_G_1C_ch_0_1_sat_9.mat")
+    assert hl.host().gbh_matfile_write_grid(fn.encode(), grid.reshape(-1), rows, cols, 9, (1 << 40) + 5, 1) == 0
+    m = loadmat(fn)
+    assert m["acq_grid"].dtype == np.float32 and m["acq_grid"].shape == (rows, cols)
+    np.testing.assert_array_equal(m["acq_grid"], grid.T)
+    assert m["PRN"].dtype == np.uint32 and m["PRN"].shape == (1, 1) and int(m["PRN"][0, 0]) == 9
+    assert m["sample_counter"].dtype == np.uint64 and int(m["sample_counter"][0, 0]) == (1 << 40) + 5
+    assert m["d_positive_acq"].dtype == np.int32 and int(m["d_positive_acq"][0, 0]) == 1
