@@ -230,3 +230,35 @@ cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st
     return cudaGetLastError();
 }
 
+
+
+// ---- ingest: conjugate the pushed items in place (inverted_spectrum option of the data-type adapters) ----
+// Replaces conjugate_cc / conjugate_sc / conjugate_ic (src/algorithms/libs/conjugate_{cc,sc,ic}.cc -> volk_32fc_conjugate_32fc,
+// volk_gnsssdr_16ic_conjugate_16ic, volk_gnsssdr_8ic_conjugate_8ic): the imaginary part is negated in the item's own type, so
+// the most negative integer stays what two's-complement negation makes of it, like the reference's generic kernels.
+namespace
+{
+template <class T>
+__global__ void gb_conj_kernel(T* __restrict__ iq, size_t n_items)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_items; i += (size_t)gridDim.x * blockDim.x)
+        {
+            T v = iq[2 * i + 1];
+            iq[2 * i + 1] = (T)(-v);
+        }
+}
+}  // namespace
+
+cudaError_t gb_conj_items(void* d_items, size_t n_items, int item_type, cudaStream_t st)
+{
+    if (n_items == 0) return cudaSuccess;
+    const int threads = 256;
+    const int blocks = (int)std::min<size_t>((n_items + threads - 1) / threads, 148 * 8);
+    if (item_type == GB200_ITEM_32FC)
+        gb_conj_kernel<float><<<blocks, threads, 0, st>>>((float*)d_items, n_items);
+    else if (item_type == GB200_ITEM_16IC)
+        gb_conj_kernel<short><<<blocks, threads, 0, st>>>((short*)d_items, n_items);
+    else
+        gb_conj_kernel<signed char><<<blocks, threads, 0, st>>>((signed char*)d_items, n_items);
+    return cudaGetLastError();
+}

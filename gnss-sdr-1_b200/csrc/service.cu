@@ -39,6 +39,7 @@ struct GbRing
     uint64_t end = 0;    // one past the newest item index held
     uint64_t begin = 0;  // oldest item index still held
     bool any = false;
+    bool conj = false;   // inverted_spectrum: items are conjugated as they are pushed
 };
 
 struct GbPlanEntry
@@ -436,10 +437,15 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
             const uint64_t pos = idx % r.cap;
             const size_t run = (size_t)std::min<uint64_t>(left, r.cap - pos);
             GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + pos * isz, p, run * isz, kind, s->stream));
+            if (r.conj)
+                {
+                    GB_CUDA(s, gb_conj_items((char*)r.d_buf + pos * isz, run, item_type, s->stream));
+                    s->launches++;
+                }
             if (pos < r.slack)  // keep the mirror [cap, cap+slack) == [0, slack) so every window is contiguous
                 {
                     const size_t mrun = (size_t)std::min<uint64_t>(run, r.slack - pos);
-                    GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + (r.cap + pos) * isz, p, mrun * isz, kind, s->stream));
+                    GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + (r.cap + pos) * isz, (const char*)r.d_buf + pos * isz, mrun * isz, cudaMemcpyDeviceToDevice, s->stream));
                 }
             p += run * isz;
             idx += run;
@@ -448,6 +454,14 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
     r.end = first + n_items;
     r.any = true;
     if (r.end - r.begin > r.cap) r.begin = r.end - r.cap;
+    return GB200_OK;
+}
+
+extern "C" int gb200_stream_set_inverted_spectrum(gb200_service* s, int stream_id, int inverted)
+{
+    if (!s || stream_id < 0 || stream_id >= (int)s->rings.size()) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    s->rings[stream_id].conj = inverted != 0;
     return GB200_OK;
 }
 

@@ -70,7 +70,7 @@ EXPORTS = [
     "gb200_service_create", "gb200_service_destroy", "gb200_last_error", "gb200_version", "gb200_service_cuda_stream",
     "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
     "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
-    "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device",
+    "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid",
@@ -209,6 +209,10 @@ class Service:
         a = np.ascontiguousarray(samples, ITEM_DTYPES[item_type])
         n_items = a.size if item_type == ITEM_32FC else a.size // 2
         self.check(self.L.gb200_stream_push(self.h, stream_id, _ptr(a), n_items, item_type, first_sample_index))
+
+    def set_inverted_spectrum(self, stream_id, inverted):
+        """inverted_spectrum of the data-type adapters: later pushes to this stream are conjugated on the device."""
+        self.check(self.L.gb200_stream_set_inverted_spectrum(self.h, stream_id, int(inverted)))
 
     def push_ptr(self, stream_id, host_ptr, n_items, item_type, first_sample_index):
         self.check(self.L.gb200_stream_push(self.h, stream_id, C.c_void_p(host_ptr), n_items, item_type, first_sample_index))

@@ -87,6 +87,10 @@ int gb200_service_coalescing_stats(gb200_service* s, uint64_t* batches, uint64_t
  * kernels exactly as volk_gnsssdr_16ic_convert_32fc.h:63-72 does). */
 int gb200_stream_push(gb200_service* s, int stream_id, const void* samples, size_t n_items, int item_type,
     uint64_t first_sample_index);
+/* `inverted_spectrum` of the data-type adapters (ishort_to_complex.cc:49-59, ibyte_to_complex.cc:49-59: a conjugate_cc /
+ * conjugate_sc / conjugate_ic block after the conversion): items pushed to this stream from now on are conjugated on the device
+ * in their wire type as part of the push. */
+int gb200_stream_set_inverted_spectrum(gb200_service* s, int stream_id, int inverted);
 /* same, `samples` already in device memory (device-to-device copy on the service stream) */
 int gb200_stream_push_device(gb200_service* s, int stream_id, const void* d_samples, size_t n_items, int item_type,
     uint64_t first_sample_index);

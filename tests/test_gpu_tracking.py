@@ -166,6 +166,46 @@ def test_ring_wraparound_and_errors(service):
         s.close()
 
 
+@pytest.mark.parametrize("item", ["32fc", "16ic", "8ic"])
+def test_inverted_spectrum_ingest(item):
+    """inverted_spectrum of the data-type adapters (ishort_to_complex.cc:49-59 ...): items are conjugated in their wire type as part
+    of the push, wrap-around mirror included; the most negative integer keeps its two's-complement negation (-32768 / -128)."""
+    import gnss_b200 as gb
+
+    s = gb.Service(device=0, ring_capacity=10000, ring_slack=5000)
+    try:
+        rng = np.random.default_rng(7)
+        x = (rng.standard_normal(16000) + 1j * rng.standard_normal(16000)).astype(np.complex64) * 40.0
+        it = {"32fc": gb.ITEM_32FC, "16ic": gb.ITEM_16IC, "8ic": gb.ITEM_8IC}[item]
+        if item == "32fc":
+            host, conj = x, np.conj(x)
+        else:
+            dt, lo = (np.int16, -32768) if item == "16ic" else (np.int8, -128)
+            q = np.clip(np.rint(np.stack([x.real, x.imag], -1)), lo, -lo - 1).astype(dt)
+            q[5::97, 1] = lo  # -lo does not exist in the type: the negation wraps back to lo
+            host = q.reshape(-1)
+            qc = q.copy()
+            qc[:, 1] = (-q[:, 1].astype(np.int32)).astype(dt)
+            conj = (qc[:, 0].astype(np.float32) + 1j * qc[:, 1].astype(np.float32)).astype(np.complex64)
+        s.set_inverted_spectrum(0, True)
+        step = 2000 * (1 if item == "32fc" else 2)
+        for k, blk in enumerate(range(0, 16000, 2000)):
+            s.push(0, host[k * step: (k + 1) * step], it, blk)
+        gps = synth.code_table("gps_l1_ca", 3)
+        sh = np.array([-0.5, 0.0, 0.5], np.float32)
+        m = gb.Multicorrelator(s, 3, 1023, item_type=it)
+        m.set_local_code_and_taps(gps, sh)
+        first = 8500  # wraps at 10000: the second half is read through the mirror
+        got = m.correlate(0, first, 0.3, -0.02, 0.1, 0.25575, 4000)
+        want = ol.multicorrelator_real("oracle", conj[first: first + 4000], gps, sh, 0.3, -0.02, 0.1, 0.25575)
+        assert rel_err(got, want) < TOL
+        s.set_inverted_spectrum(0, False)
+        s.push(0, host[: step], it, 16000)
+        m.close()
+    finally:
+        s.close()
+
+
 def test_int16_correlator_bit_exact(service):
     """Cpu_Multicorrelator_16sc semantics (rintf to int16, 16-bit products, per-sample saturating accumulation) reproduced
     BIT-exactly by the parallel clamp-add formulation, including runs that saturate, through single and batched calls."""
