@@ -5,7 +5,9 @@
 #include <stdint.h>
 
 #define GB200_TRK_THREADS 256
-#define GB200_TRK_WMAX 4224  // code-window floats staged per CTA (covers 4096 samples at <= 1 table-sample/sample)
+#define GB200_RING_TAIL_ITEMS 1024         // spare items allocated behind the ring: the tracking kernel reads whole groups of 4 x 256 samples
+#define GB200_TRK_SMEM_MAX (96 * 1024)   // dynamic shared memory a tracking CTA may use (code window + carrier table)
+#define GB200_TRK_SMEM_PREF (72 * 1024)  // preferred ceiling when choosing the chunk: 3 CTAs per SM
 #define GB200_OUT_STRIDE (GB200_MAX_TAPS + 1)  // complex floats per request in the output array
 
 // One multicorrelator request as the kernels see it (device memory, one per (channel, epoch)).
@@ -14,6 +16,8 @@ struct GbTrkWork
     const void* samples;     // first sample of the correlation window (contiguous: ring mirror)
     const float* code;       // local code table (float, or float2 when complex)
     const float* data_code;  // pilot tracking: data-component table correlated at tap `prompt_tap`, or nullptr
+    const float* ext;        // the code repeated over ext_entries window entries (float, (pilot, data) or (re, im)) for bulk staging
+    int ext_entries;
     int code_len;
     int n;                   // signal_length_samples
     int n_taps;
@@ -31,8 +35,15 @@ struct GbTrkWork
     double nco_a0_turns;     // arg(phase_0) / 2pi
     double nco_theta_turns;  // arg(inc) / 2pi
     double nco_log_mag;      // log|inc| (high-dynamics path: the reference never renormalises phase_doppler there)
-    float2 nco_adv;          // unit phasor of GB200_TRK_THREADS * arg(inc): the per-iteration NCO advance of one thread
+    unsigned long long nco_a0_fix;     // frac(nco_a0_turns) * 2^64: the kernels carry the turn count in 64-bit fixed point
+    unsigned long long nco_theta_fix;  // frac(nco_theta_turns) * 2^64 (two's complement for negative increments)
 };
+
+// dynamic shared memory of gb_trk_kernel: window entries (4 or 8 bytes each) + one float4 per loop iteration of the chunk
+__host__ __device__ inline size_t gb_trk_smem_bytes(int win_entries, bool wide_entries, int chunk)
+{
+    return (((size_t)win_entries * (wide_entries ? 8 : 4) + 15) & ~(size_t)15) + (size_t)(chunk / GB200_TRK_THREADS + 4) * 16;
+}
 
 // one request of the int16 (Cpu_Multicorrelator_16sc) correlator
 struct GbTrk16Work
@@ -100,7 +111,7 @@ __device__ __forceinline__ float2 gb_cmul(float2 a, float2 b)
 // kernel launchers (defined in the .cu files, called from service.cu)
 cudaError_t gb_conj_items(void* d_items, size_t n_items, int item_type, cudaStream_t st);
 cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_taps, bool has_data, int prompt_tap, int item_type,
-    int code_kind, bool high_dyn, float2* d_partials, unsigned* d_counters, float2* d_out, int chunk, cudaStream_t st,
+    int code_kind, bool high_dyn, float2* d_partials, unsigned* d_counters, float2* d_out, int chunk, int win_entries, cudaStream_t st,
     int* launches);
 
 cudaError_t gb_trk16_launch(const GbTrk16Work* d_work, int n_work, int max_n, int n_taps, float2* d_ckpt, int4* d_triples, short* d_out,

@@ -403,7 +403,8 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
             r.cap = s->ring_capacity;
             r.slack = s->ring_slack;
             r.item_type = item_type;
-            GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack) * isz));
+            GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack + GB200_RING_TAIL_ITEMS) * isz));
+            GB_CUDA(s, cudaMemsetAsync((char*)r.d_buf + (r.cap + r.slack) * isz, 0, GB200_RING_TAIL_ITEMS * isz, s->stream));
         }
     if (r.item_type != item_type)
         {
@@ -411,7 +412,8 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
             GB_CUDA(s, cudaStreamSynchronize(s->stream));
             GB_CUDA(s, cudaFree(r.d_buf));
             r.d_buf = nullptr;
-            GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack) * isz));
+            GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack + GB200_RING_TAIL_ITEMS) * isz));
+            GB_CUDA(s, cudaMemsetAsync((char*)r.d_buf + (r.cap + r.slack) * isz, 0, GB200_RING_TAIL_ITEMS * isz, s->stream));
             r.item_type = item_type;
             r.any = false;
             r.begin = r.end = 0;
@@ -1356,6 +1358,11 @@ struct gb200_trk
     gb200_trk_cfg c;
     float* d_code = nullptr;       // float[code_len] or float2[code_len]
     float* d_data_code = nullptr;  // float[code_len] or nullptr
+    // "extended table": the code repeated over ext_entries window entries in the layout the kernel stages (float, or
+    // float2 = (pilot, data) / (re, im)), so that a CTA's whole code window is one contiguous 16-byte-aligned range
+    float* d_ext = nullptr;
+    int ext_entries = 0;
+    std::vector<float> h_code, h_data;  // host copies the extended table is rebuilt from
     int code_len = 0;
     int n_taps = 0;
     int prompt_tap = 0;
@@ -1385,6 +1392,7 @@ struct gb200_trk_batch
     unsigned* d_counters = nullptr;
     float2* h_out = nullptr;  // pinned
     int chunk = 4096;
+    int win_entries = 1032;  // code-window entries per CTA (sizes the dynamic shared memory)
     int max_chunks = 1;
 };
 
@@ -1407,6 +1415,7 @@ extern "C" int gb200_trk_create(gb200_service* s, const gb200_trk_cfg* cfg, gb20
     const size_t w = cfg->code_kind == GB200_CODE_CPLX ? 2 : 1;
     cudaError_t e = cudaMalloc(&t->d_code, sizeof(float) * w * cfg->max_code_len);
     if (e == cudaSuccess && cfg->code_kind == GB200_CODE_REAL) e = cudaMalloc(&t->d_data_code, sizeof(float) * cfg->max_code_len);
+    if (e == cudaSuccess && cfg->code_kind != GB200_CODE_16SC) e = cudaMalloc(&t->d_ext, sizeof(float) * 2 * (2 * (size_t)cfg->max_code_len + 2048));
     if (e != cudaSuccess)
         {
             s->set_error(std::string("cudaMalloc code: ") + cudaGetErrorString(e));
@@ -1438,7 +1447,41 @@ extern "C" int gb200_trk_destroy(gb200_trk* t)
     if (t->single) gb200_trk_batch_destroy(t->single);
     if (t->d_code) cudaFree(t->d_code);
     if (t->d_data_code) cudaFree(t->d_data_code);
+    if (t->d_ext) cudaFree(t->d_ext);
     delete t;
+    return GB200_OK;
+}
+
+// (re)build the extended table from the host copies of the code(s); caller holds s->mu
+static int trk_rebuild_ext(gb200_trk* t)
+{
+    gb200_service* s = t->s;
+    if (!t->d_ext || t->code_len < 1) return GB200_OK;
+    const int L = t->code_len;
+    const bool cplx = t->c.code_kind == GB200_CODE_CPLX;
+    const int ew = (cplx || t->has_data) ? 2 : 1;
+    const int entries = (2 * L + 2048) & ~3;
+    std::vector<float> ext((size_t)entries * ew);
+    for (int j = 0; j < entries; j++)
+        {
+            const int k = j % L;
+            if (cplx)
+                {
+                    ext[2 * (size_t)j] = t->h_code[2 * (size_t)k];
+                    ext[2 * (size_t)j + 1] = t->h_code[2 * (size_t)k + 1];
+                }
+            else if (t->has_data)
+                {
+                    ext[2 * (size_t)j] = t->h_code[k];
+                    ext[2 * (size_t)j + 1] = t->h_data[k];
+                }
+            else
+                ext[j] = t->h_code[k];
+        }
+    t->ext_entries = 0;
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));  // launches in flight may still read the old table
+    GB_CUDA(s, cudaMemcpy(t->d_ext, ext.data(), sizeof(float) * ext.size(), cudaMemcpyHostToDevice));
+    t->ext_entries = entries;
     return GB200_OK;
 }
 
@@ -1456,9 +1499,15 @@ extern "C" int gb200_trk_set_local_code_and_taps(gb200_trk* t, const void* code,
     const size_t w = t->c.code_kind == GB200_CODE_CPLX ? 2 : 1;
     GB_CUDA(s, cudaMemcpyAsync(t->d_code, code, sizeof(float) * w * code_len, cudaMemcpyHostToDevice, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));  // `code` is caller memory: do not keep reading it
+    if (t->has_data && code_len != t->code_len) t->has_data = false;  // a data table of another length cannot ride along
     t->code_len = code_len;
     t->n_taps = n_taps;
     for (int i = 0; i < GB200_MAX_TAPS; i++) t->shifts[i] = i < n_taps ? shifts[i] : 0.f;
+    if (t->c.code_kind != GB200_CODE_16SC)
+        {
+            t->h_code.assign((const float*)code, (const float*)code + w * code_len);
+            return trk_rebuild_ext(t);
+        }
     return GB200_OK;
 }
 
@@ -1484,7 +1533,8 @@ extern "C" int gb200_trk_set_data_code(gb200_trk* t, const float* code, int code
     if (!code)
         {
             t->has_data = false;
-            return GB200_OK;
+            cudaSetDevice(s->device);
+            return trk_rebuild_ext(t);
         }
     if (t->c.code_kind != GB200_CODE_REAL || code_len != t->code_len || prompt_tap < 0 || prompt_tap >= t->n_taps)
         {
@@ -1496,7 +1546,8 @@ extern "C" int gb200_trk_set_data_code(gb200_trk* t, const float* code, int code
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
     t->has_data = true;
     t->prompt_tap = prompt_tap;
-    return GB200_OK;
+    t->h_data.assign(code, code + code_len);
+    return trk_rebuild_ext(t);
 }
 
 static int trk_fill_work(gb200_service* s, const gb200_trk_req& r, int out_index, GbTrkWork* w)
@@ -1524,6 +1575,8 @@ static int trk_fill_work(gb200_service* s, const gb200_trk_req& r, int out_index
     w->samples = win;
     w->code = t->d_code;
     w->data_code = t->has_data ? t->d_data_code : nullptr;
+    w->ext = t->ext_entries > 0 ? t->d_ext : nullptr;
+    w->ext_entries = t->ext_entries;
     w->code_len = t->code_len;
     w->n = r.n_samples;
     w->n_taps = t->n_taps;
@@ -1547,8 +1600,16 @@ static int trk_fill_work(gb200_service* s, const gb200_trk_req& r, int out_index
         w->nco_mag_delta = (float)(mag - 1.0);
         w->nco_log_mag = log(mag);
         {
-            const double a = 6.283185307179586476925 * w->nco_theta_turns * (double)GB200_TRK_THREADS;
-            w->nco_adv = make_float2((float)cos(a), (float)sin(a));
+            // 64-bit fixed-point turn counts for the kernels (wrap mod 1 turn in integer arithmetic)
+            auto to_fix = [](double turns) -> unsigned long long {
+                double f = turns - floor(turns);  // [0, 1)
+                if (f >= 1.0) f = 0.0;
+                const double hi = floor(f * 4294967296.0);
+                const double lo = floor((f * 4294967296.0 - hi) * 4294967296.0);
+                return ((unsigned long long)hi << 32) | (unsigned long long)std::min(lo, 4294967295.0);
+            };
+            w->nco_a0_fix = to_fix(w->nco_a0_turns);
+            w->nco_theta_fix = to_fix(w->nco_theta_turns);
         }
     }
     return GB200_OK;
@@ -1630,16 +1691,27 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
             spread = std::max(spread, (double)hi - (double)lo);
             chips_per_sample = std::max(chips_per_sample, std::fabs((double)w.code_step));
         }
+    // window entries are 8 bytes when they carry (pilot, data) chips or complex chips, else 4
+    bool wide = false;
+    for (const auto& g : b->groups) wide = wide || g.has_data || g.code_kind == GB200_CODE_CPLX;
+    // + 1023 samples: the kernel pads every thread's work to whole groups of four (4 x 256 samples)
+    auto win_for = [&](int c) { return ((int)ceil((double)(std::min(c, max_n) + 1023) * chips_per_sample + spread) + 8 + 1) & ~1; };
     long long ctas = 0;
     b->chunk = 1024;
+    static const int chunk_cap = getenv("GB200_TRK_CHUNK_MAX") ? atoi(getenv("GB200_TRK_CHUNK_MAX")) : 32768;  // tuning only
     for (int c : {32768, 16384, 8192, 4096, 2048, 1024})
         {
+            if (c > chunk_cap && c > 1024) continue;
             b->chunk = c;
-            if (c > 1024 && (double)std::min(c, max_n) * chips_per_sample + spread + 8.0 > (double)GB200_TRK_WMAX) continue;
+            // prefer windows that leave room for 3 CTAs per SM; the smallest chunk is always accepted (a window that does
+            // not fit even then makes the kernel take its table-in-L2 path)
+            if (c > 1024 && gb_trk_smem_bytes(win_for(c), wide, c) > (size_t)GB200_TRK_SMEM_PREF) continue;
             ctas = 0;
             for (int i = 0; i < n; i++) ctas += (reqs[i].n_samples + c - 1) / c;
             if (ctas >= 4LL * s->sm_count) break;
         }
+    b->win_entries = win_for(b->chunk);
+    while (b->win_entries > 2 && gb_trk_smem_bytes(b->win_entries, wide, b->chunk) > (size_t)GB200_TRK_SMEM_MAX) b->win_entries -= 2;
     b->max_chunks = (max_n + b->chunk - 1) / b->chunk;
     return GB200_OK;
 }
@@ -1707,7 +1779,7 @@ extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
             // every group shares max_chunks (the partial-sum pitch) so request slots stay independent
             gb_kt_begin(s, GB200_KCLASS_TRK);
             cudaError_t e = gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.prompt_tap, g.item_type, g.code_kind,
-                g.high_dyn, b->d_partials, b->d_counters, b->d_out, b->chunk, s->stream, &l);
+                g.high_dyn, b->d_partials, b->d_counters, b->d_out, b->chunk, b->win_entries, s->stream, &l);
             gb_kt_end(s);
             GB_CUDA(s, e);
         }
