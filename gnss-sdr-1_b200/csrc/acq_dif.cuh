@@ -21,7 +21,8 @@ namespace
 template <int SIGN>
 __device__ __forceinline__ float2 cmul_const(float2 a, float c, float s)  // a * (c + j*SIGN*s)
 {
-    return SIGN > 0 ? make_float2(fmaf(a.x, c, -a.y * s), fmaf(a.x, s, a.y * c)) : make_float2(fmaf(a.x, c, a.y * s), fmaf(a.y, c, -a.x * s));
+    // (a.x c - SIGN a.y s, SIGN a.x s + a.y c) = a.x (c, SIGN s) + a.y (-SIGN s, c)
+    return upk2(fma2x(pk2(a.x, a.x), pk2(c, SIGN > 0 ? s : -s), mul2x(pk2(a.y, a.y), pk2(SIGN > 0 ? -s : s, c))));
 }
 
 // radix 16 = 4 x 4: x[4a+b] -> X[k1 + 4 k2]

@@ -19,21 +19,68 @@
 namespace
 {
 
+// ---- complex arithmetic on packed FP32 pairs (sm_100a FADD2 / FMUL2 / FFMA2): one issue slot per complex add and two per
+// complex multiply.  Every lane is the IEEE round-to-nearest operation of the scalar instruction it replaces; ptxas turns
+// pk2(a, a) operands into scalar broadcasts and swapped / half-negated operands into source modifiers.
+typedef unsigned long long gb_f32x2;
+__device__ __forceinline__ gb_f32x2 pk2(float lo, float hi)
+{
+    gb_f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ gb_f32x2 pk2(float2 a) { return pk2(a.x, a.y); }
+__device__ __forceinline__ float2 upk2(gb_f32x2 v)
+{
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+__device__ __forceinline__ gb_f32x2 fma2x(gb_f32x2 a, gb_f32x2 b, gb_f32x2 c)
+{
+    gb_f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ gb_f32x2 mul2x(gb_f32x2 a, gb_f32x2 b)
+{
+    gb_f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ gb_f32x2 add2x(gb_f32x2 a, gb_f32x2 b)
+{
+    gb_f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ gb_f32x2 sub2x(gb_f32x2 a, gb_f32x2 b)
+{
+    gb_f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ float gb_fneg(float v) { return __int_as_float(__float_as_int(v) ^ (int)0x80000000); }
+
 __device__ __forceinline__ float2 cmul(float2 a, float2 b)
 {
-    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+    // (a.x b.x - a.y b.y, a.x b.y + a.y b.x) = a.x (b.x, b.y) + a.y (-b.y, b.x)
+    return upk2(fma2x(pk2(a.x, a.x), pk2(b), mul2x(pk2(a.y, a.y), pk2(gb_fneg(b.y), b.x))));
 }
 __device__ __forceinline__ float2 cmul_conj(float2 a, float2 b)  // a * conj(b)
 {
-    return make_float2(fmaf(a.x, b.x, a.y * b.y), fmaf(a.y, b.x, -a.x * b.y));
+    // (a.x b.x + a.y b.y, a.y b.x - a.x b.y) = a.y (b.y, b.x) + a.x (b.x, -b.y)
+    return upk2(fma2x(pk2(a.x, a.x), pk2(b.x, gb_fneg(b.y)), mul2x(pk2(a.y, a.y), pk2(b.y, b.x))));
 }
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return upk2(add2x(pk2(a), pk2(b))); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return upk2(sub2x(pk2(a), pk2(b))); }
+__device__ __forceinline__ float2 cscale(float2 a, float s) { return upk2(mul2x(pk2(a), pk2(s, s))); }            // s a
+__device__ __forceinline__ float2 caxpy(float s, float2 a, float2 y) { return upk2(fma2x(pk2(a), pk2(s, s), pk2(y))); }  // s a + y
 // multiply by -j*SIGN... rot(a) = a * (SIGN>0 ? +j : -j)
 template <int SIGN>
 __device__ __forceinline__ float2 rotj(float2 a)
 {
-    return SIGN > 0 ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
+    return SIGN > 0 ? make_float2(gb_fneg(a.y), a.x) : make_float2(a.y, gb_fneg(a.x));
 }
 
 // W_N^(SIGN*e) for 0 <= e < N, e reduced exactly in integers, angle evaluated with sincospif
@@ -61,8 +108,8 @@ __device__ __forceinline__ void bfly3(float2* v)
     const float s60 = 0.86602540378443864676f;
     float2 t1 = cadd(v[1], v[2]);
     float2 t2 = csub(v[1], v[2]);
-    float2 m = make_float2(fmaf(-0.5f, t1.x, v[0].x), fmaf(-0.5f, t1.y, v[0].y));
-    float2 r = rotj<SIGN>(make_float2(s60 * t2.x, s60 * t2.y));
+    float2 m = caxpy(-0.5f, t1, v[0]);
+    float2 r = rotj<SIGN>(cscale(t2, s60));
     v[0] = cadd(v[0], t1);
     v[1] = cadd(m, r);
     v[2] = csub(m, r);
@@ -86,11 +133,11 @@ __device__ __forceinline__ void bfly5(float2* v)
     const float s2 = 0.58778525229247312917f;   // sin(4pi/5)
     float2 a1 = cadd(v[1], v[4]), b1 = csub(v[1], v[4]);
     float2 a2 = cadd(v[2], v[3]), b2 = csub(v[2], v[3]);
-    float2 m1 = make_float2(v[0].x + c1 * a1.x + c2 * a2.x, v[0].y + c1 * a1.y + c2 * a2.y);
-    float2 m2 = make_float2(v[0].x + c2 * a1.x + c1 * a2.x, v[0].y + c2 * a1.y + c1 * a2.y);
-    float2 r1 = rotj<SIGN>(make_float2(s1 * b1.x + s2 * b2.x, s1 * b1.y + s2 * b2.y));
-    float2 r2 = rotj<SIGN>(make_float2(s2 * b1.x - s1 * b2.x, s2 * b1.y - s1 * b2.y));
-    v[0] = make_float2(v[0].x + a1.x + a2.x, v[0].y + a1.y + a2.y);
+    float2 m1 = caxpy(c2, a2, caxpy(c1, a1, v[0]));
+    float2 m2 = caxpy(c1, a2, caxpy(c2, a1, v[0]));
+    float2 r1 = rotj<SIGN>(caxpy(s2, b2, cscale(b1, s1)));
+    float2 r2 = rotj<SIGN>(caxpy(-s1, b2, cscale(b1, s2)));
+    v[0] = cadd(cadd(v[0], a1), a2);
     v[1] = cadd(m1, r1);
     v[4] = csub(m1, r1);
     v[2] = cadd(m2, r2);
@@ -106,9 +153,10 @@ __device__ __forceinline__ void bfly8(float2* v)
     bfly4<SIGN>(e);
     bfly4<SIGN>(o);
     // twiddles W_8^q, q = 1,2,3
-    float2 w1 = SIGN > 0 ? make_float2(h * (o[1].x - o[1].y), h * (o[1].x + o[1].y)) : make_float2(h * (o[1].x + o[1].y), h * (o[1].y - o[1].x));
+    // o1 * h (1 + j SIGN), o3 * h (-1 + j SIGN): one packed add of the (half-negated, swapped) pair, one packed scale
+    float2 w1 = cscale(cadd(o[1], rotj<SIGN>(o[1])), h);
     float2 w2 = rotj<SIGN>(o[2]);
-    float2 w3 = SIGN > 0 ? make_float2(-h * (o[3].x + o[3].y), h * (o[3].x - o[3].y)) : make_float2(h * (o[3].y - o[3].x), -h * (o[3].x + o[3].y));
+    float2 w3 = cscale(csub(rotj<SIGN>(o[3]), o[3]), h);
     v[0] = cadd(e[0], o[0]);
     v[4] = csub(e[0], o[0]);
     v[1] = cadd(e[1], w1);

@@ -40,6 +40,8 @@ struct GbRing
     uint64_t begin = 0;  // oldest item index still held
     bool any = false;
     bool conj = false;   // inverted_spectrum: items are conjugated as they are pushed
+    cudaEvent_t ev_pushed = nullptr;  // recorded on the copy stream behind the newest push
+    bool pushed_unseen = false;       // the compute stream has not been ordered behind ev_pushed yet
 };
 
 struct GbPlanEntry
@@ -68,6 +70,12 @@ struct gb200_service
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;  // second lane for the inverse chunks (fills the tail of the other lane's kernels)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // Ingest runs on its own stream so that the H2D copy of block k+1 overlaps the kernels working on block k.  Ordering:
+    // a consumer launch waits for the newest push of every ring (ev_pushed); a push waits for the newest consumer launch
+    // (ev_consumed) before it may overwrite ring memory.
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_consumed = nullptr;
+    bool any_consumed = false;
     std::vector<GbRing> rings;
     uint64_t ring_capacity = 0, ring_slack = 0;
     std::map<int, GbPlanEntry> plans;
@@ -183,6 +191,8 @@ extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service*
     s->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_consumed, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming) != cudaSuccess)
         {
@@ -203,6 +213,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
 {
     if (!s) return GB200_E_INVALID;
     cudaSetDevice(s->device);
+    if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
     cudaStreamSynchronize(s->stream);
     if (s->cb) gb200_trk_batch_destroy(s->cb);
     for (auto& r : s->rings)
@@ -224,6 +235,10 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->ev_join) cudaEventDestroy(s->ev_join);
     if (s->stream2) cudaStreamDestroy(s->stream2);
+    if (s->ev_consumed) cudaEventDestroy(s->ev_consumed);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    for (auto& r : s->rings)
+        if (r.ev_pushed) cudaEventDestroy(r.ev_pushed);
     cudaStreamDestroy(s->stream);
     delete s;
     return GB200_OK;
@@ -234,7 +249,28 @@ extern "C" void* gb200_service_cuda_stream(gb200_service* s) { return s ? (void*
 extern "C" int gb200_service_synchronize(gb200_service* s)
 {
     if (!s) return GB200_E_INVALID;
+    GB_CUDA(s, cudaStreamSynchronize(s->copy_stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    return GB200_OK;
+}
+
+// order the compute stream behind every push issued so far (call before launching anything that reads a ring)
+static int rings_acquire(gb200_service* s)
+{
+    for (auto& r : s->rings)
+        if (r.pushed_unseen)
+            {
+                GB_CUDA(s, cudaStreamWaitEvent(s->stream, r.ev_pushed, 0));
+                r.pushed_unseen = false;
+            }
+    return GB200_OK;
+}
+
+// mark the kernels launched so far as readers of ring memory (call after launching them)
+static int rings_release(gb200_service* s)
+{
+    GB_CUDA(s, cudaEventRecord(s->ev_consumed, s->stream));
+    s->any_consumed = true;
     return GB200_OK;
 }
 
@@ -251,6 +287,7 @@ extern "C" int gb200_service_timer_start(gb200_service* s)
             GB_CUDA(s, cudaEventCreate(&s->ev1));
         }
     GB_CUDA(s, cudaEventRecord(s->ev0, s->stream));
+    GB_CUDA(s, cudaStreamWaitEvent(s->copy_stream, s->ev0, 0));  // pushes issued after the start mark begin after it
     return GB200_OK;
 }
 
@@ -259,6 +296,7 @@ extern "C" int gb200_service_timer_stop(gb200_service* s, float* elapsed_ms)
     if (!s || !elapsed_ms || !s->ev0) return GB200_E_INVALID;
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
+    { int rc = rings_acquire(s); if (rc) return rc; }  // a push with no consumer behind it still ends inside the timed region
     GB_CUDA(s, cudaEventRecord(s->ev1, s->stream));
     GB_CUDA(s, cudaEventSynchronize(s->ev1));
     GB_CUDA(s, cudaEventElapsedTime(elapsed_ms, s->ev0, s->ev1));
@@ -404,16 +442,18 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
             r.slack = s->ring_slack;
             r.item_type = item_type;
             GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack + GB200_RING_TAIL_ITEMS) * isz));
-            GB_CUDA(s, cudaMemsetAsync((char*)r.d_buf + (r.cap + r.slack) * isz, 0, GB200_RING_TAIL_ITEMS * isz, s->stream));
+            GB_CUDA(s, cudaMemsetAsync((char*)r.d_buf + (r.cap + r.slack) * isz, 0, GB200_RING_TAIL_ITEMS * isz, s->copy_stream));
         }
+    if (!r.ev_pushed) GB_CUDA(s, cudaEventCreateWithFlags(&r.ev_pushed, cudaEventDisableTiming));
     if (r.item_type != item_type)
         {
             // the front-end was reconfigured: drop what is held and re-type the ring
+            GB_CUDA(s, cudaStreamSynchronize(s->copy_stream));
             GB_CUDA(s, cudaStreamSynchronize(s->stream));
             GB_CUDA(s, cudaFree(r.d_buf));
             r.d_buf = nullptr;
             GB_CUDA(s, cudaMalloc(&r.d_buf, (r.cap + r.slack + GB200_RING_TAIL_ITEMS) * isz));
-            GB_CUDA(s, cudaMemsetAsync((char*)r.d_buf + (r.cap + r.slack) * isz, 0, GB200_RING_TAIL_ITEMS * isz, s->stream));
+            GB_CUDA(s, cudaMemsetAsync((char*)r.d_buf + (r.cap + r.slack) * isz, 0, GB200_RING_TAIL_ITEMS * isz, s->copy_stream));
             r.item_type = item_type;
             r.any = false;
             r.begin = r.end = 0;
@@ -431,6 +471,8 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
         }
     else if (!r.any)
         r.begin = first;
+    // kernels already launched may still read the items this push overwrites
+    if (s->any_consumed) GB_CUDA(s, cudaStreamWaitEvent(s->copy_stream, s->ev_consumed, 0));
     const char* p = (const char*)src;
     uint64_t idx = first;
     size_t left = n_items;
@@ -438,21 +480,23 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
         {
             const uint64_t pos = idx % r.cap;
             const size_t run = (size_t)std::min<uint64_t>(left, r.cap - pos);
-            GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + pos * isz, p, run * isz, kind, s->stream));
+            GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + pos * isz, p, run * isz, kind, s->copy_stream));
             if (r.conj)
                 {
-                    GB_CUDA(s, gb_conj_items((char*)r.d_buf + pos * isz, run, item_type, s->stream));
+                    GB_CUDA(s, gb_conj_items((char*)r.d_buf + pos * isz, run, item_type, s->copy_stream));
                     s->launches++;
                 }
             if (pos < r.slack)  // keep the mirror [cap, cap+slack) == [0, slack) so every window is contiguous
                 {
                     const size_t mrun = (size_t)std::min<uint64_t>(run, r.slack - pos);
-                    GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + (r.cap + pos) * isz, (const char*)r.d_buf + pos * isz, mrun * isz, cudaMemcpyDeviceToDevice, s->stream));
+                    GB_CUDA(s, cudaMemcpyAsync((char*)r.d_buf + (r.cap + pos) * isz, (const char*)r.d_buf + pos * isz, mrun * isz, cudaMemcpyDeviceToDevice, s->copy_stream));
                 }
             p += run * isz;
             idx += run;
             left -= run;
         }
+    GB_CUDA(s, cudaEventRecord(r.ev_pushed, s->copy_stream));
+    r.pushed_unseen = true;
     r.end = first + n_items;
     r.any = true;
     if (r.end - r.begin > r.cap) r.begin = r.end - r.cap;
@@ -999,6 +1043,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             for (int j = 0; j < i; j++)
                 if (list[j] == list[i]) return GB200_E_INVALID;
         }
+    { int rc0 = rings_acquire(s); if (rc0) return rc0; }
     // group handles that can share the wiped-off forward spectra
     ctx.groups.clear();
     std::vector<float> steps;
@@ -1155,6 +1200,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                 GB_CUDA(s, gb_acq_reduce_peaks((const GbPeak*)d_part, (int)g.members.size(), bins, tiles, d_peaks, s->stream, &l));
         }
     s->launches += l;
+    { int rc0 = rings_release(s); if (rc0) return rc0; }
     ctx.h_results.resize(res);
     GB_CUDA(s, cudaMemcpyAsync((char*)h_up + up, d_res, res, cudaMemcpyDeviceToHost, s->stream));
     for (int i = 0; i < n; i++)
@@ -1774,6 +1820,7 @@ extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
     int l = 0;
+    { int rc = rings_acquire(s); if (rc) return rc; }
     for (const auto& g : b->groups)
         {
             // every group shares max_chunks (the partial-sum pitch) so request slots stay independent
@@ -1784,7 +1831,7 @@ extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
             GB_CUDA(s, e);
         }
     s->launches += l;
-    return GB200_OK;
+    return rings_release(s);
 }
 
 extern "C" int gb200_trk_batch_fetch(gb200_trk_batch* b, float* outs_iq)
@@ -1904,8 +1951,10 @@ extern "C" int gb200_trk_correlate_16sc_batch(gb200_service* s, int n, const gb2
     if ((rc = s->scratch(13, out_bytes, &d_out))) return rc;
     GB_CUDA(s, cudaMemcpyAsync(d_work, hw, work_bytes, cudaMemcpyHostToDevice, s->stream));
     int l = 0;
+    if ((rc = rings_acquire(s))) return rc;
     GB_CUDA(s, gb_trk16_launch((const GbTrk16Work*)d_work, n, max_n, same_taps ? max_taps : GB200_MAX_TAPS, (float2*)d_ckpt, (int4*)d_triples, (short*)d_out,
                    s->stream, &l));
+    if ((rc = rings_release(s))) return rc;
     s->launches += l;
     GB_CUDA(s, cudaMemcpyAsync(hout, d_out, out_bytes, cudaMemcpyDeviceToHost, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));

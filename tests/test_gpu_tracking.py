@@ -306,8 +306,11 @@ def test_service_coalesces_concurrent_channel_threads():
             svc.close()
 
     alone, launches_alone, _ = run(0)
-    together, launches_together, (batches, requests) = run(2000)
     assert launches_alone == n_ch * epochs
-    assert requests == n_ch * epochs and batches == launches_together
+    for attempt in range(3):  # how many callers meet in one window depends on host thread scheduling: allow a re-run on a loaded box
+        together, launches_together, (batches, requests) = run(2000)
+        assert requests == n_ch * epochs and batches == launches_together
+        if launches_together <= launches_alone // 3:
+            break
     assert launches_together <= launches_alone // 3, (launches_together, launches_alone)
     assert np.array_equal(alone, together)
