@@ -109,6 +109,8 @@ __device__ __forceinline__ float2 gb_cmul(float2 a, float2 b)
 }
 
 // kernel launchers (defined in the .cu files, called from service.cu)
+// device-side copy of `bytes` (multiple of 8) from device-mapped host memory (or anywhere) to device memory
+cudaError_t gb_copy_words(void* dst, const void* src, size_t bytes, cudaStream_t st);
 cudaError_t gb_conj_items(void* d_items, size_t n_items, int item_type, cudaStream_t st);
 cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_taps, bool has_data, int prompt_tap, int item_type,
     int code_kind, bool high_dyn, float2* d_partials, unsigned* d_counters, float2* d_out, int chunk, int win_entries, cudaStream_t st,

@@ -42,6 +42,25 @@ struct GbRing
     bool conj = false;   // inverted_spectrum: items are conjugated as they are pushed
     cudaEvent_t ev_pushed = nullptr;  // recorded on the copy stream behind the newest push
     bool pushed_unseen = false;       // the compute stream has not been ordered behind ev_pushed yet
+    // the last GB_RING_MARKS pushes, each with its own event: a tracking request waits only for the push that delivered its
+    // last sample, so one call over several pushed blocks starts on the early blocks while the later ones still land
+    struct Mark
+    {
+        uint64_t end = 0;   // one past the newest item of that push (0: slot unused)
+        uint64_t seq = 0;   // push order
+        cudaEvent_t ev = nullptr;
+    };
+    static const int kMarks = 16;
+    Mark marks[kMarks];
+    uint64_t push_seq = 0;
+    // event of the oldest recorded push that already covers item index `need_end - 1` (nullptr: none recorded)
+    const Mark* mark_for(uint64_t need_end) const
+    {
+        const Mark* best = nullptr;
+        for (int i = 0; i < kMarks; i++)
+            if (marks[i].end >= need_end && marks[i].end != 0 && (!best || marks[i].seq < best->seq)) best = &marks[i];
+        return best;
+    }
 };
 
 struct GbPlanEntry
@@ -114,7 +133,13 @@ struct gb200_service
     void* d_flush = nullptr;
     size_t flush_bytes = 0;
 
-    void set_error(const std::string& e) { error = e; g_global_error = e; }
+    void set_error(const std::string& e)
+    {
+        static std::mutex emu;
+        std::lock_guard<std::mutex> lk(emu);
+        error = e;
+        g_global_error = e;
+    }
     int scratch(int slot, size_t bytes, void** out)
     {
         if (bytes > scratch_bytes[slot])
@@ -238,7 +263,11 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     if (s->ev_consumed) cudaEventDestroy(s->ev_consumed);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     for (auto& r : s->rings)
-        if (r.ev_pushed) cudaEventDestroy(r.ev_pushed);
+        {
+            if (r.ev_pushed) cudaEventDestroy(r.ev_pushed);
+            for (auto& m : r.marks)
+                if (m.ev) cudaEventDestroy(m.ev);
+        }
     cudaStreamDestroy(s->stream);
     delete s;
     return GB200_OK;
@@ -468,6 +497,7 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
         {
             // discontinuity: everything held so far is dropped
             r.begin = first;
+            for (auto& m : r.marks) m.end = 0;
         }
     else if (!r.any)
         r.begin = first;
@@ -497,6 +527,13 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
         }
     GB_CUDA(s, cudaEventRecord(r.ev_pushed, s->copy_stream));
     r.pushed_unseen = true;
+    {
+        GbRing::Mark& m = r.marks[r.push_seq % GbRing::kMarks];
+        if (!m.ev) GB_CUDA(s, cudaEventCreateWithFlags(&m.ev, cudaEventDisableTiming));
+        GB_CUDA(s, cudaEventRecord(m.ev, s->copy_stream));
+        m.end = first + n_items;
+        m.seq = ++r.push_seq;
+    }
     r.end = first + n_items;
     r.any = true;
     if (r.end - r.begin > r.cap) r.begin = r.end - r.cap;
@@ -1423,13 +1460,44 @@ struct TrkGroup
     int first = 0, count = 0;  // range in the (sorted) work array
     int n_taps = 0, item_type = 0, code_kind = 0, max_n = 0, prompt_tap = 0;
     bool has_data = false, high_dyn = false;
+    cudaEvent_t ready = nullptr;  // push event the group's requests wait for (the push that delivered their newest sample)
+    uint64_t ready_seq = 0;
 };
 
 struct gb200_trk_batch
 {
     gb200_service* s = nullptr;
     int n = 0;
-    std::vector<GbTrkWork> h_work;
+    // Request records are staged in pinned, device-mapped host memory and pulled to the device by a small kernel: a
+    // cudaMemcpyAsync would queue on the host-to-device copy engine BEHIND the sample pushes still in flight and hold the
+    // first block's launch back until the last block has landed.
+    struct PinnedWork
+    {
+        GbTrkWork* p = nullptr;
+        GbTrkWork* dev = nullptr;  // device alias of p
+        size_t cap = 0, n = 0;
+        GbTrkWork& operator[](size_t i) { return p[i]; }
+        GbTrkWork* data() { return p; }
+        bool resize(size_t m)
+        {
+            if (m > cap)
+                {
+                    if (p) cudaFreeHost(p);
+                    p = nullptr;
+                    cap = 0;
+                    const size_t want = std::max<size_t>(m, 64);
+                    if (cudaHostAlloc((void**)&p, sizeof(GbTrkWork) * want, cudaHostAllocMapped) != cudaSuccess) return false;
+                    if (cudaHostGetDevicePointer((void**)&dev, p, 0) != cudaSuccess) return false;
+                    cap = want;
+                }
+            n = m;
+            return true;
+        }
+        ~PinnedWork()
+        {
+            if (p) cudaFreeHost(p);
+        }
+    } h_work;
     std::vector<int> order;  // work slot -> request index
     std::vector<TrkGroup> groups;
     GbTrkWork* d_work = nullptr;
@@ -1674,25 +1742,54 @@ static void trk_group_key(const gb200_trk* t, TrkGroup* g)
 static bool trk_same_group(const TrkGroup& a, const TrkGroup& b)
 {
     return a.n_taps == b.n_taps && a.item_type == b.item_type && a.code_kind == b.code_kind && a.has_data == b.has_data && a.high_dyn == b.high_dyn &&
-           (!a.has_data || a.prompt_tap == b.prompt_tap);
+           (!a.has_data || a.prompt_tap == b.prompt_tap) && a.ready == b.ready;
 }
 
 // (re)build the work array of a batch from requests; buffers must already be sized for b->n requests
+// host threads that fill a long batch of request records (GB200_HOST_THREADS, default 8)
+[[maybe_unused]] static int gb_host_threads()
+{
+    static const int n = [] {
+        const char* e = getenv("GB200_HOST_THREADS");
+        const int v = e ? atoi(e) : 8;
+        return v < 1 ? 1 : (v > 64 ? 64 : v);
+    }();
+    return n;
+}
+
 static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
 {
     gb200_service* s = b->s;
     const int n = b->n;
     // bucket requests by kernel variant, keeping request order inside a bucket
     b->groups.clear();
+    static const bool trace = getenv("GB200_TRACE") != nullptr;
+    const auto ts0 = std::chrono::steady_clock::now();
     std::vector<int> gid(n);
+    std::vector<TrkGroup> keys(n);
+    for (int i = 0; i < n; i++)
+        if (!reqs[i].trk) return GB200_E_INVALID;
+#pragma omp parallel for schedule(static) num_threads(gb_host_threads()) if (n >= 1024)
     for (int i = 0; i < n; i++)
         {
-            if (!reqs[i].trk) return GB200_E_INVALID;
-            TrkGroup k;
+            TrkGroup& k = keys[i];
             trk_group_key(reqs[i].trk, &k);
+            if (reqs[i].stream_id >= 0 && reqs[i].stream_id < (int)s->rings.size())
+                if (const GbRing::Mark* m = s->rings[reqs[i].stream_id].mark_for(reqs[i].first_sample_index + (uint64_t)std::max(reqs[i].n_samples, 0)))
+                    {
+                        k.ready = m->ev;
+                        k.ready_seq = m->seq;
+                    }
+        }
+    for (int i = 0; i < n; i++)
+        {
+            const TrkGroup& k = keys[i];
             int found = -1;
-            for (size_t g = 0; g < b->groups.size(); g++)
-                if (trk_same_group(b->groups[g], k)) found = (int)g;
+            if (i > 0 && trk_same_group(b->groups[gid[i - 1]], k))
+                found = gid[i - 1];  // the common case: consecutive requests of one channel
+            else
+                for (size_t g = 0; g < b->groups.size(); g++)
+                    if (trk_same_group(b->groups[g], k)) found = (int)g;
             if (found < 0)
                 {
                     b->groups.push_back(k);
@@ -1702,6 +1799,20 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
             b->groups[found].count++;
             b->groups[found].max_n = std::max(b->groups[found].max_n, reqs[i].n_samples);
         }
+    {
+        // launch order = push order, so an early block's kernel never queues behind a wait for a later block
+        std::vector<int> perm(b->groups.size()), inv(b->groups.size());
+        for (size_t g = 0; g < perm.size(); g++) perm[g] = (int)g;
+        std::stable_sort(perm.begin(), perm.end(), [&](int x, int y) { return b->groups[x].ready_seq < b->groups[y].ready_seq; });
+        std::vector<TrkGroup> sorted;
+        for (size_t g = 0; g < perm.size(); g++)
+            {
+                sorted.push_back(b->groups[perm[g]]);
+                inv[perm[g]] = (int)g;
+            }
+        b->groups.swap(sorted);
+        for (int i = 0; i < n; i++) gid[i] = inv[gid[i]];
+    }
     int off = 0;
     for (auto& g : b->groups)
         {
@@ -1709,17 +1820,43 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
             off += g.count;
             g.count = 0;
         }
-    b->h_work.resize(n);
+    if (!b->h_work.resize(n))
+        {
+            s->set_error("tracking batch: pinned staging allocation failed");
+            return GB200_E_CUDA;
+        }
     b->order.resize(n);
+    const auto ts1 = std::chrono::steady_clock::now();
     int max_n = 1;
+    std::vector<int> slot_of(n);
     for (int i = 0; i < n; i++)
         {
             TrkGroup& g = b->groups[gid[i]];
-            const int slot = g.first + g.count++;
-            int rc = trk_fill_work(s, reqs[i], i, &b->h_work[slot]);
-            if (rc) return rc;
-            b->order[slot] = i;
+            slot_of[i] = g.first + g.count++;
+            b->order[slot_of[i]] = i;
             max_n = std::max(max_n, reqs[i].n_samples);
+        }
+    {
+        // the per-request NCO constants go through host libm in float32 and float64 (~0.1 us each): a long batch is filled
+        // by a few host threads
+        int first_rc = GB200_OK;
+#pragma omp parallel for schedule(static) num_threads(gb_host_threads()) if (n >= 1024)
+        for (int i = 0; i < n; i++)
+            {
+                const int rc = trk_fill_work(s, reqs[i], i, &b->h_work[slot_of[i]]);
+                if (rc)
+                    {
+#pragma omp critical(gb200_fill_rc)
+                        if (!first_rc) first_rc = rc;
+                    }
+            }
+        if (first_rc) return first_rc;
+    }
+    if (trace)
+        {
+            const auto ts2 = std::chrono::steady_clock::now();
+            auto us = [](auto a, auto z) { return (double)std::chrono::duration_cast<std::chrono::nanoseconds>(z - a).count() * 1e-3; };
+            fprintf(stderr, "  stage: keys+groups %.1f us, fill %.1f us\n", us(ts0, ts1), us(ts1, ts2));
         }
     // chunk size (samples per CTA): the largest that still gives >= 4 CTAs per SM and whose code window (the chips one
     // CTA can touch: chunk*step + tap spread) fits the shared-memory staging area; per-CTA set-up (NCO seed, window
@@ -1801,7 +1938,7 @@ extern "C" int gb200_trk_batch_create(gb200_service* s, int n, const gb200_trk_r
             gb200_trk_batch_destroy(b);
             return rc;
         }
-    cudaError_t e = cudaMemcpyAsync(b->d_work, b->h_work.data(), sizeof(GbTrkWork) * n, cudaMemcpyHostToDevice, s->stream);
+    cudaError_t e = gb_copy_words(b->d_work, b->h_work.dev, sizeof(GbTrkWork) * (size_t)n, s->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
     if (e != cudaSuccess)
         {
@@ -1820,9 +1957,9 @@ extern "C" int gb200_trk_batch_launch(gb200_trk_batch* b)
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
     int l = 0;
-    { int rc = rings_acquire(s); if (rc) return rc; }
     for (const auto& g : b->groups)
         {
+            if (g.ready) GB_CUDA(s, cudaStreamWaitEvent(s->stream, g.ready, 0));
             // every group shares max_chunks (the partial-sum pitch) so request slots stay independent
             gb_kt_begin(s, GB200_KCLASS_TRK);
             cudaError_t e = gb_trk_launch(b->d_work + g.first, g.count, b->max_chunks * b->chunk, g.n_taps, g.has_data, g.prompt_tap, g.item_type, g.code_kind,
@@ -1886,11 +2023,23 @@ extern "C" int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_tr
         }
     gb200_trk_batch* b = s->cb;
     b->n = n;
+    static const bool trace = getenv("GB200_TRACE") != nullptr;  // host wall-clock phases of one call, to stderr
+    const auto t0 = std::chrono::steady_clock::now();
     int rc = trk_batch_stage(b, reqs);
     if (rc) return rc;
-    GB_CUDA(s, cudaMemcpyAsync(b->d_work, b->h_work.data(), sizeof(GbTrkWork) * n, cudaMemcpyHostToDevice, s->stream));
+    const auto t1 = std::chrono::steady_clock::now();
+    GB_CUDA(s, gb_copy_words(b->d_work, b->h_work.dev, sizeof(GbTrkWork) * (size_t)n, s->stream));
+    s->launches++;
     rc = gb200_trk_batch_launch(b);
+    const auto t2 = std::chrono::steady_clock::now();
     if (!rc) rc = gb200_trk_batch_fetch(b, outs_iq);
+    if (trace)
+        {
+            const auto t3 = std::chrono::steady_clock::now();
+            auto us = [](auto a, auto z) { return (double)std::chrono::duration_cast<std::chrono::nanoseconds>(z - a).count() * 1e-3; };
+            fprintf(stderr, "gb200_trk_correlate_batch n=%d: stage %.1f us, launch %.1f us (%zu groups), wait+fetch %.1f us\n", n, us(t0, t1), us(t1, t2),
+                b->groups.size(), us(t2, t3));
+        }
     return rc;
 }
 
@@ -1999,7 +2148,8 @@ static int trk_correlate_direct(gb200_trk* t, const gb200_trk_req& r, float* cor
     gb200_trk_batch* b = t->single;
     rc = trk_batch_stage(b, &r);
     if (rc) return rc;
-    GB_CUDA(s, cudaMemcpyAsync(b->d_work, b->h_work.data(), sizeof(GbTrkWork), cudaMemcpyHostToDevice, s->stream));
+    GB_CUDA(s, gb_copy_words(b->d_work, b->h_work.dev, sizeof(GbTrkWork), s->stream));
+    s->launches++;
     rc = gb200_trk_batch_launch(b);
     if (rc) return rc;
     GB_CUDA(s, cudaMemcpyAsync(b->h_out, b->d_out, sizeof(float2) * GB200_OUT_STRIDE, cudaMemcpyDeviceToHost, s->stream));

@@ -20,6 +20,7 @@
 // of the code table those samples can touch is staged once into shared memory already wrapped
 // ("window"), so the hot loop does no modulo: index = float-magic floor - window base.
 #include "gb200_internal.cuh"
+#include <algorithm>
 
 namespace
 {
@@ -700,4 +701,24 @@ cudaError_t gb_trk_launch(const GbTrkWork* d_work, int n_work, int max_n, int n_
         }
     if (launches) (*launches)++;
     return e;
+}
+
+namespace
+{
+__global__ void gb_copy_words_kernel(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, size_t n)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+}  // namespace
+
+// Pulls request records out of device-mapped pinned host memory with SM loads.  (A cudaMemcpyAsync would sit in the
+// host-to-device copy engine's queue behind every sample push still in flight.)
+cudaError_t gb_copy_words(void* dst, const void* src, size_t bytes, cudaStream_t st)
+{
+    const size_t n = bytes / 8;
+    if (n == 0) return cudaSuccess;
+    const int threads = 256;
+    const int blocks = (int)std::min<size_t>((n + threads - 1) / threads, 296);
+    gb_copy_words_kernel<<<blocks, threads, 0, st>>>((unsigned long long*)dst, (const unsigned long long*)src, n);
+    return cudaGetLastError();
 }
