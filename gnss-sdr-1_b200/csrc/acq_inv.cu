@@ -101,9 +101,10 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
             const int n = N2 * n1 + c0 + b - p.keep_offset;
             if (c0 + b >= N2 || n < 0 || n >= p.keep_len) continue;
             const float2 y = res[n1 * PITCH + b];
-            const float mag = __fadd_rn(__fmul_rn(y.x, y.x), __fmul_rn(y.y, y.y));  // volk_32fc_magnitude_squared_32f
+            float mag = __fadd_rn(__fmul_rn(y.x, y.x), __fmul_rn(y.y, y.y));  // volk_32fc_magnitude_squared_32f
             if (grid)
                 {
+                    if (p.scale) mag = __fmul_rn(mag, __ldg(p.scale));  // volk_32f_s32f_multiply_32f
                     float* g = grid + (size_t)bin * p.keep_len + n;
                     *g = p.accumulate ? __fadd_rn(*g, mag) : mag;
                     if (p.accumulate && p.tmpbuf && p.tmpbuf[handle] && bin == p.n_bins - 1) p.tmpbuf[handle][n] = mag;
@@ -246,9 +247,10 @@ __global__ void __launch_bounds__(NT, OCC)
             {
                 const int n = nbase + r * (NIL * N2);
                 if (MODE != 0 && (n < 0 || n >= p.keep_len)) continue;
-                const float mag = __fadd_rn(__fmul_rn(v[r].x, v[r].x), __fmul_rn(v[r].y, v[r].y));  // volk_32fc_magnitude_squared_32f
+                float mag = __fadd_rn(__fmul_rn(v[r].x, v[r].x), __fmul_rn(v[r].y, v[r].y));  // volk_32fc_magnitude_squared_32f
                 if (MODE == 2)
                     {
+                        if (p.scale) mag = __fmul_rn(mag, __ldg(p.scale));  // volk_32f_s32f_multiply_32f
                         grid[n] = p.accumulate ? __fadd_rn(grid[n], mag) : mag;
                         if (tmp) tmp[n] = mag;
                     }

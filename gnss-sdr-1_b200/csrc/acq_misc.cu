@@ -36,7 +36,14 @@ __global__ void __launch_bounds__(1024) gb_input_power_kernel(const void* sample
         {
             acc = threadIdx.x < (blockDim.x >> 5) ? s[threadIdx.x] : 0.f;
             for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
-            if (threadIdx.x == 0) *power = acc / (float)N;
+            if (threadIdx.x == 0)
+                {
+                    const float p = acc / (float)N;
+                    power[0] = p;
+                    // Tong detector (pcps_tong_acquisition_cc.cc:333-335): per-dwell scale 1 / (N^2 * N^2 * input_power), float32
+                    const float fnf = __fmul_rn((float)N, (float)N);
+                    power[1] = __fdiv_rn(1.0f, __fmul_rn(__fmul_rn(fnf, fnf), p));
+                }
         }
 }
 

@@ -184,6 +184,7 @@ struct GbAcqInvParams
     int accumulate;                 // dwell > 1: grid += mag
     GbPeak* partial;                // [transform][tiles] per-CTA maxima (only when grid == nullptr)
     float* const* tmpbuf;           // per handle d_tmp_buffer image or nullptr: receives the last bin's magnitudes when accumulating (:737)
+    const float* scale;             // device scalar or nullptr: magnitudes are multiplied by it before they enter the grid (Tong detector)
 };
 
 // per-kernel-class CUDA-event timing hooks (service.cu); `ctx` may be nullptr

@@ -88,6 +88,8 @@ struct gb200_service
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;  // second lane for the inverse chunks (fills the tail of the other lane's kernels)
+    cudaStream_t stream34[2] = {nullptr, nullptr};  // optional third / fourth lane (GB200_ACQ_LANES)
+    cudaEvent_t ev_join34[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // Ingest runs on its own stream so that the H2D copy of block k+1 overlaps the kernels working on block k.  Ordering:
     // a consumer launch waits for the newest push of every ring (ev_pushed); a push waits for the newest consumer launch
@@ -217,6 +219,10 @@ extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service*
     if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&s->stream34[0], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&s->stream34[1], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_join34[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_join34[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_consumed, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming) != cudaSuccess)
@@ -260,6 +266,11 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->ev_join) cudaEventDestroy(s->ev_join);
     if (s->stream2) cudaStreamDestroy(s->stream2);
+    for (int k = 0; k < 2; k++)
+        {
+            if (s->ev_join34[k]) cudaEventDestroy(s->ev_join34[k]);
+            if (s->stream34[k]) cudaStreamDestroy(s->stream34[k]);
+        }
     if (s->ev_consumed) cudaEventDestroy(s->ev_consumed);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     for (auto& r : s->rings)
@@ -747,7 +758,11 @@ struct gb200_acq
     int pending_group = -1, pending_slot = -1;
     bool pending = false;
 
-    bool need_grid() const { return keep_grid || !use_cfar || c.max_dwells > 1; }
+    // sibling blocks served through the same Doppler loop
+    std::vector<float> custom_steps;  // gb200_acq_set_doppler_grid: phase step per bin replaces the doppler_max/doppler_step rule
+    bool scaled_accum = false;        // gb200_acq_set_scaled_accumulation: Tong detector, grid += mag / (N^4 input_power) every dwell
+
+    bool need_grid() const { return keep_grid || !use_cfar || c.max_dwells > 1 || scaled_accum; }
 };
 
 static const double kGpsTwoPi = 6.283185307179586;  // GPS_L1_CA.h:46
@@ -758,7 +773,9 @@ static float acq_phase_step(const gb200_acq* a, float freq) { return (float)(kGp
 static void acq_bin_steps(const gb200_acq* a, std::vector<float>& steps)
 {
     steps.clear();
-    if (!a->step_two)
+    if (!a->step_two && !a->custom_steps.empty())
+        steps = a->custom_steps;
+    else if (!a->step_two)
         {
             for (uint32_t i = 0; i < a->num_bins; i++)
                 {
@@ -834,6 +851,7 @@ static void acq_derive(gb200_acq* a)
     a->eff = c.bit_transition_flag ? a->fft_size / 2 : a->fft_size;
     a->use_cfar = (a->c.max_dwells == 1) ? (c.use_CFAR_algorithm_flag != 0) : false;  // :152-159
     a->num_bins = c.doppler_step ? (uint32_t)std::ceil((double)((int32_t)c.doppler_max - (int32_t)(-(int32_t)c.doppler_max)) / (double)c.doppler_step) : 0;  // :326
+    a->custom_steps.clear();
 }
 
 static int acq_alloc_grid(gb200_acq* a)
@@ -985,6 +1003,35 @@ extern "C" int gb200_acq_set_doppler(gb200_acq* a, uint32_t doppler_max, uint32_
     return acq_alloc_grid(a);
 }
 
+extern "C" int gb200_acq_set_doppler_grid(gb200_acq* a, uint32_t n_bins, const float* phase_step_rad)
+{
+    if (!a || !phase_step_rad || n_bins == 0 || n_bins > 65535) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(a->s->mu);
+    cudaSetDevice(a->s->device);
+    if (a->c.make_2_steps)
+        {
+            a->s->set_error("gb200_acq_set_doppler_grid: not combined with make_2_steps");
+            return GB200_E_INVALID;
+        }
+    a->custom_steps.assign(phase_step_rad, phase_step_rad + n_bins);
+    a->num_bins = n_bins;
+    return acq_alloc_grid(a);
+}
+
+extern "C" int gb200_acq_set_scaled_accumulation(gb200_acq* a, int enable)
+{
+    if (!a) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(a->s->mu);
+    cudaSetDevice(a->s->device);
+    if (a->c.bit_transition_flag || a->c.make_2_steps)
+        {
+            a->s->set_error("gb200_acq_set_scaled_accumulation: not combined with bit_transition_flag / make_2_steps");
+            return GB200_E_INVALID;
+        }
+    a->scaled_accum = enable != 0;
+    return acq_alloc_grid(a);
+}
+
 extern "C" int gb200_acq_set_threshold(gb200_acq* a, float threshold)
 {
     if (!a) return GB200_E_INVALID;
@@ -1131,7 +1178,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             g.off_tmp = up;
             up = align_up(up + g.members.size() * sizeof(void*), 16);
             g.off_power = res;
-            res = align_up(res + sizeof(float), 16);
+            res = align_up(res + 2 * sizeof(float), 16);  // input power, Tong scale
             g.off_peaks = res;
             res = align_up(res + g.members.size() * sizeof(GbPeak), 16);
         }
@@ -1181,7 +1228,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l, s));
             // input power (CFAR or bit transition, pcps_acquisition.cc:703-709)
             bool want_power = false;
-            for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag;
+            for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag || list[m]->scaled_accum;
             float* d_power = (float*)((char*)d_res + g.off_power);
             if (want_power)
                 GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, N, d_power, (g.grid && !a0->use_cfar) ? a0->d_tmp : nullptr, s->stream, &l));
@@ -1190,30 +1237,37 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             // Two lanes: chunk c runs on stream (c & 1) with its own row buffer, so one lane's column kernel overlaps the
             // other lane's row kernel and each kernel's ragged last wave is filled by the other lane.  Both row buffers
             // together stay within the L2 budget.  With per-launch event timing on, everything stays on one stream.
-            const bool two_lanes = !s->kt.enabled && !getenv("GB200_ACQ_ONE_LANE");
-            const size_t l2_budget = two_lanes ? (24ull << 20) : (48ull << 20);
+            static const int lanes_cfg = getenv("GB200_ACQ_ONE_LANE") ? 1 : (getenv("GB200_ACQ_LANES") ? std::max(1, std::min(4, atoi(getenv("GB200_ACQ_LANES")))) : 2);
+            static const size_t l2_total = (size_t)(getenv("GB200_ACQ_L2_MB") ? std::max(4, atoi(getenv("GB200_ACQ_L2_MB"))) : 48) << 20;
+            const int lanes = s->kt.enabled ? 1 : lanes_cfg;
+            const size_t l2_budget = l2_total / (size_t)lanes;
             int chunkT = (int)std::max<size_t>(1, l2_budget / (sizeof(float2) * (size_t)N));
             chunkT = std::min(chunkT, T);
             const int tiles = (plan.N2 + plan.inv_tile1 - 1) / plan.inv_tile1;
-            void *d_row, *d_row2 = nullptr, *d_part;
+            void* d_rows[4] = {nullptr, nullptr, nullptr, nullptr};
+            void* d_part;
+            static const int row_slots[4] = {2, 8, 14, 15};
             // lane 0's buffer is sized for the one-lane chunk so that toggling event timing never reallocates
-            if ((rc = s->scratch(2, sizeof(float2) * (size_t)N * std::min<size_t>(T, std::max<size_t>(1, (48ull << 20) / (sizeof(float2) * (size_t)N))), &d_row))) return rc;
-            if (two_lanes && (rc = s->scratch(8, sizeof(float2) * (size_t)N * chunkT, &d_row2))) return rc;
+            if ((rc = s->scratch(2, sizeof(float2) * (size_t)N * std::min<size_t>(T, std::max<size_t>(1, l2_total / (sizeof(float2) * (size_t)N))), &d_rows[0]))) return rc;
+            for (int k = 1; k < lanes; k++)
+                if ((rc = s->scratch(row_slots[k], sizeof(float2) * (size_t)N * chunkT, &d_rows[k]))) return rc;
             if ((rc = s->scratch(3, sizeof(GbPeak) * (size_t)T * tiles, &d_part))) return rc;
-            const bool fork = two_lanes && T > chunkT;
+            const bool fork = lanes > 1 && T > chunkT;
+            cudaStream_t lane_stream[4] = {s->stream, s->stream2, s->stream34[0], s->stream34[1]};
+            cudaEvent_t lane_join[4] = {nullptr, s->ev_join, s->ev_join34[0], s->ev_join34[1]};
             if (fork)
                 {
                     GB_CUDA(s, cudaEventRecord(s->ev_fork, s->stream));
-                    GB_CUDA(s, cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
+                    for (int k = 1; k < lanes; k++) GB_CUDA(s, cudaStreamWaitEvent(lane_stream[k], s->ev_fork, 0));
                 }
             int lane = 0;
-            for (int t0 = 0; t0 < T; t0 += chunkT, lane ^= 1)
+            for (int t0 = 0; t0 < T; t0 += chunkT, lane = (lane + 1) % lanes)
                 {
-                    const bool second = fork && lane;
+                    const int ln = fork ? lane : 0;
                     GbAcqInvParams ip;
                     ip.spectra = (const float2*)d_spec;
                     ip.code_fft = (const float2* const*)((char*)d_up + g.off_code);
-                    ip.rowbuf = (float2*)(second ? d_row2 : d_row);
+                    ip.rowbuf = (float2*)d_rows[ln];
                     ip.n_bins = bins;
                     ip.first_transform = t0;
                     ip.n_transforms = std::min(chunkT, T - t0);
@@ -1222,14 +1276,16 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     ip.grid = g.grid ? (float* const*)((char*)d_up + g.off_grid) : nullptr;
                     ip.accumulate = (g.grid && a0->dwell_counter >= 1) ? 1 : 0;  // this is dwell number dwell_counter+1
                     ip.partial = (GbPeak*)d_part;
-                    ip.tmpbuf = (g.grid && !a0->use_cfar) ? (float* const*)((char*)d_up + g.off_tmp) : nullptr;
-                    GB_CUDA(s, gb_acq_inverse(plan, ip, second ? s->stream2 : s->stream, &l, s));
+                    ip.tmpbuf = (g.grid && !a0->use_cfar && !a0->scaled_accum) ? (float* const*)((char*)d_up + g.off_tmp) : nullptr;
+                    ip.scale = (g.grid && a0->scaled_accum) ? d_power + 1 : nullptr;
+                    GB_CUDA(s, gb_acq_inverse(plan, ip, lane_stream[ln], &l, s));
                 }
             if (fork)
-                {
-                    GB_CUDA(s, cudaEventRecord(s->ev_join, s->stream2));
-                    GB_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_join, 0));
-                }
+                for (int k = 1; k < lanes; k++)
+                    {
+                        GB_CUDA(s, cudaEventRecord(lane_join[k], lane_stream[k]));
+                        GB_CUDA(s, cudaStreamWaitEvent(s->stream, lane_join[k], 0));
+                    }
             GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
             if (g.grid)
                 GB_CUDA(s, gb_acq_grid_peaks((float* const*)((char*)d_up + g.off_grid), (int)g.members.size(), bins, (int)a0->eff, d_peaks, s->stream, &l));
@@ -1369,6 +1425,20 @@ extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_
             else
                 r.doppler_hz = (int32_t)(a->doppler_center_step_two + ((float)pk.bin - (float)floor(a->c.num_doppler_bins_step2 / 2.0)) * a->c.doppler_step2);  // :591
             float stat;
+            if (a->scaled_accum)
+                {
+                    // Tong detector: the kept grid already holds the accumulated test statistic; the caller owns the
+                    // counter logic and ends the attempt with gb200_acq_reset
+                    r.input_power = power;
+                    r.test_statistic = pk.mag;
+                    r.acq_delay_samples = (double)fmodf((float)pk.idx, a->c.samples_per_code);
+                    r.acq_doppler_hz = (double)r.doppler_hz;
+                    r.acq_samplestamp = a->pending_first + a->consumed;
+                    r.decision = 2;
+                    a->pending = false;
+                    out[i] = r;
+                    continue;
+                }
             if (a->use_cfar)
                 {
                     r.input_power = power;

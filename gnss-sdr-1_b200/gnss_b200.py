@@ -72,7 +72,7 @@ EXPORTS = [
     "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
     "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
-    "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
+    "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid",
     "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_set_taps", "gb200_trk_correlate",
     "gb200_trk_correlate_batch", "gb200_trk_correlate_16sc", "gb200_trk_correlate_16sc_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
@@ -119,6 +119,8 @@ def lib():
     L.gb200_acq_set_doppler.argtypes = [vp, u32, u32, C.c_int64]
     L.gb200_acq_set_threshold.argtypes = [vp, f]
     L.gb200_acq_reset.argtypes = [vp]
+    L.gb200_acq_set_doppler_grid.argtypes = [vp, u32, vp]
+    L.gb200_acq_set_scaled_accumulation.argtypes = [vp, i]
     L.gb200_acq_run.argtypes = [vp, i, u64, C.POINTER(AcqResult)]
     L.gb200_acq_run_batch.argtypes = [C.POINTER(vp), i, i, u64, C.POINTER(AcqResult)]
     L.gb200_acq_launch_batch.argtypes = [C.POINTER(vp), i, i, u64]
@@ -245,6 +247,15 @@ class Acquisition:
 
     def set_doppler(self, doppler_max, doppler_step, freq_offset_hz=0):
         self.s.check(self.s.L.gb200_acq_set_doppler(self.h, doppler_max, doppler_step, freq_offset_hz))
+
+    def set_doppler_grid(self, phase_steps_rad):
+        """explicit per-bin phase steps (sibling PCPS blocks with their own grid rule)"""
+        st = np.ascontiguousarray(phase_steps_rad, np.float32)
+        self.s.check(self.s.L.gb200_acq_set_doppler_grid(self.h, len(st), _ptr(st)))
+
+    def set_scaled_accumulation(self, enable=True):
+        """Tong detector arithmetic: grid += |y|^2 / (N^4 input_power) every dwell"""
+        self.s.check(self.s.L.gb200_acq_set_scaled_accumulation(self.h, 1 if enable else 0))
         self.num_bins = self.s.L.gb200_acq_num_doppler_bins(self.h)
 
     def set_threshold(self, th):

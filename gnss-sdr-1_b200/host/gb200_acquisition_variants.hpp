@@ -1,0 +1,282 @@
+// Host mirrors of two sibling PCPS blocks that run the same Doppler loop as pcps_acquisition, on top of
+// the C ABI:
+//   B200_Pcps_Tong_Acquisition        pcps_tong_acquisition_cc         (src/algorithms/acquisition/gnuradio_blocks/pcps_tong_acquisition_cc.cc)
+//   B200_Galileo_Pcps_8ms_Acquisition galileo_pcps_8ms_acquisition_cc  (.../galileo_pcps_8ms_acquisition_cc.cc)
+// Both blocks use fft_size = sampled_ms * samples_per_ms with NO zero padding, count their Doppler bins inclusively
+// ("doppler <= doppler_max") and build the wipe-off tables with their own phase-step expression, so the bins are handed to
+// the engine as an explicit list (gb200_acq_set_doppler_grid).  The device does the per-bin arithmetic; the counters,
+// thresholds and Gnss_Synchro fields stay here.
+#pragma once
+#include <cmath>
+#include <complex>
+#include <cstdint>
+#include <vector>
+
+#include "../../include/gnss_b200.h"
+#include "gb200_acquisition.hpp"
+
+namespace gb200
+{
+struct AcqVariantConf
+{
+    uint32_t sampled_ms = 1;
+    uint32_t doppler_max = 5000;
+    uint32_t doppler_step = 250;
+    int64_t fs_in = 4000000;
+    int samples_per_ms = 4000;
+    int samples_per_code = 4000;
+    float threshold = 0.0f;
+    uint32_t max_dwells = 1;                                          // 8 ms block
+    uint32_t tong_init_val = 1, tong_max_val = 2, tong_max_dwells = 20;  // Tong block
+    int item_type = GB200_ITEM_32FC;
+};
+
+namespace detail
+{
+inline gb200_acq_cfg variant_cfg(const AcqVariantConf& c, bool keep_grid_dwells)
+{
+    gb200_acq_cfg g{};
+    g.sampled_ms = c.sampled_ms;
+    g.ms_per_code = c.sampled_ms;  // fft_size == consumed samples: no zero padding in these blocks
+    g.samples_per_chip = 1;
+    g.max_dwells = keep_grid_dwells ? 0x7fffffffu : 1u;  // Tong: the engine never ends the attempt by itself
+    g.doppler_max = c.doppler_max;
+    g.doppler_step = c.doppler_step;
+    g.fs_in = c.fs_in;
+    g.samples_per_ms = static_cast<float>(c.samples_per_ms);
+    g.samples_per_code = static_cast<float>(c.samples_per_code);
+    g.use_CFAR_algorithm_flag = 1;
+    g.item_type = c.item_type;
+    g.threshold = c.threshold;
+    return g;
+}
+inline uint32_t inclusive_bins(uint32_t doppler_max, uint32_t doppler_step)
+{
+    uint32_t n = 0;
+    for (auto d = -static_cast<int32_t>(doppler_max); d <= static_cast<int32_t>(doppler_max); d += static_cast<int32_t>(doppler_step)) n++;
+    return n;
+}
+}  // namespace detail
+
+// ------------------------------------------------------------------------------------------------ Tong detector
+class B200_Pcps_Tong_Acquisition
+{
+public:
+    B200_Pcps_Tong_Acquisition(gb200_service* s, const AcqVariantConf& c, int stream_id) : s_(s), c_(c), stream_(stream_id)
+    {
+        const gb200_acq_cfg g = detail::variant_cfg(c, true);
+        ok_ = gb200_acq_create(s_, &g, &h_) == GB200_OK;
+        if (ok_) init();
+    }
+    ~B200_Pcps_Tong_Acquisition()
+    {
+        if (h_) gb200_acq_destroy(h_);
+    }
+    B200_Pcps_Tong_Acquisition(const B200_Pcps_Tong_Acquisition&) = delete;
+    B200_Pcps_Tong_Acquisition& operator=(const B200_Pcps_Tong_Acquisition&) = delete;
+    bool ok() const { return ok_; }
+    void set_gnss_synchro(AcqSynchro* p) { synchro_ = p; }
+    void set_threshold(float t) { c_.threshold = t; }
+    void set_doppler_max(uint32_t v)
+    {
+        c_.doppler_max = v;
+        init();
+    }
+    void set_doppler_step(uint32_t v)
+    {
+        c_.doppler_step = v;
+        init();
+    }
+    // = init() (pcps_tong_acquisition_cc.cc:183-215): phase_step_rad = GPS_TWO_PI * doppler / float(fs) evaluated in double, stored as float
+    void init()
+    {
+        const double GPS_TWO_PI = 6.283185307179586;
+        bins_ = detail::inclusive_bins(c_.doppler_max, c_.doppler_step);
+        std::vector<float> steps(bins_);
+        for (uint32_t i = 0; i < bins_; i++)
+            {
+                const int32_t doppler = -static_cast<int32_t>(c_.doppler_max) + static_cast<int32_t>(c_.doppler_step * i);
+                const float phase_step_rad = GPS_TWO_PI * doppler / static_cast<float>(c_.fs_in);
+                steps[i] = phase_step_rad;
+            }
+        ok_ = ok_ && gb200_acq_set_doppler_grid(h_, bins_, steps.data()) == GB200_OK && gb200_acq_set_scaled_accumulation(h_, 1) == GB200_OK;
+    }
+    bool set_local_code(const std::complex<float>* code, size_t n_items)
+    {
+        return gb200_acq_set_local_code(h_, reinterpret_cast<const float*>(code), n_items) == GB200_OK;
+    }
+    // = set_state(1) (:226-252): counters and grid cleared
+    void set_state(int state)
+    {
+        state_ = state;
+        if (state == 1)
+            {
+                dwell_count_ = 0;
+                tong_count_ = static_cast<int32_t>(c_.tong_init_val);
+                mag_ = 0.0f;
+                gb200_acq_reset(h_);
+            }
+    }
+    void reset() { set_state(1); }
+    uint32_t fft_size() const { return gb200_acq_fft_size(h_); }
+    uint32_t num_doppler_bins() const { return bins_; }
+    int32_t tong_count() const { return tong_count_; }
+    uint32_t dwell_count() const { return dwell_count_; }
+    float test_statistics() const { return test_statistics_; }
+    float input_power() const { return input_power_; }
+    uint32_t code_phase_index() const { return indext_; }
+
+    // one pass through general_work state 1 (:290-395) on the fft_size items starting at samp_count.
+    // Returns the event: 1 positive, 2 negative, 0 keep dwelling (call again with the next block), -1 error.
+    int run(uint64_t samp_count)
+    {
+        if (state_ != 1) return 0;
+        gb200_acq_result r;
+        if (gb200_acq_run(h_, stream_, samp_count, &r) != GB200_OK) return -1;
+        dwell_count_++;
+        mag_ = r.peak_mag;  // d_mag: maximum of the accumulated, normalised grid
+        input_power_ = r.input_power;
+        indext_ = r.code_phase_index;
+        if (synchro_)
+            {
+                synchro_->Acq_delay_samples = static_cast<double>(r.code_phase_index % static_cast<uint32_t>(c_.samples_per_code));
+                synchro_->Acq_doppler_hz = static_cast<double>(-static_cast<int32_t>(c_.doppler_max) + static_cast<int32_t>(c_.doppler_step * r.doppler_bin));
+                synchro_->Acq_samplestamp_samples = r.acq_samplestamp;
+                synchro_->Acq_doppler_step = c_.doppler_step;
+            }
+        test_statistics_ = mag_;
+        int state = 1;
+        if (test_statistics_ > c_.threshold * dwell_count_)
+            {
+                tong_count_++;
+                if (tong_count_ == static_cast<int32_t>(c_.tong_max_val)) state = 2;
+            }
+        else
+            {
+                tong_count_--;
+                if (tong_count_ == 0) state = 3;
+            }
+        if (dwell_count_ >= c_.tong_max_dwells) state = 3;
+        if (state == 1) return 0;
+        state_ = 0;  // d_active = false; d_state = 0
+        if (synchro_) synchro_->Flag_valid_acquisition = (state == 2);
+        return state == 2 ? 1 : 2;
+    }
+
+private:
+    gb200_service* s_;
+    AcqVariantConf c_;
+    gb200_acq* h_ = nullptr;
+    AcqSynchro* synchro_ = nullptr;
+    int stream_;
+    bool ok_ = false;
+    int state_ = 0;
+    uint32_t bins_ = 0, dwell_count_ = 0, indext_ = 0;
+    int32_t tong_count_ = 0;
+    float mag_ = 0.0f, input_power_ = 0.0f, test_statistics_ = 0.0f;
+};
+
+// ------------------------------------------------------------------------------------------------ Galileo E1 8 ms (codes A / B)
+class B200_Galileo_Pcps_8ms_Acquisition
+{
+public:
+    B200_Galileo_Pcps_8ms_Acquisition(gb200_service* s, const AcqVariantConf& c, int stream_id) : s_(s), c_(c), stream_(stream_id)
+    {
+        const gb200_acq_cfg g = detail::variant_cfg(c, false);
+        ok_ = gb200_acq_create(s_, &g, &h_[0]) == GB200_OK && gb200_acq_create(s_, &g, &h_[1]) == GB200_OK;
+        if (ok_) init();
+    }
+    ~B200_Galileo_Pcps_8ms_Acquisition()
+    {
+        for (auto* h : h_)
+            if (h) gb200_acq_destroy(h);
+    }
+    B200_Galileo_Pcps_8ms_Acquisition(const B200_Galileo_Pcps_8ms_Acquisition&) = delete;
+    B200_Galileo_Pcps_8ms_Acquisition& operator=(const B200_Galileo_Pcps_8ms_Acquisition&) = delete;
+    bool ok() const { return ok_; }
+    void set_gnss_synchro(AcqSynchro* p) { synchro_ = p; }
+    void set_threshold(float t) { c_.threshold = t; }
+    // = init() (galileo_pcps_8ms_acquisition_cc.cc:140-172): float(GALILEO_TWO_PI) * doppler / float(fs), all in float32
+    void init()
+    {
+        const double GALILEO_TWO_PI = 6.283185307179600;
+        bins_ = detail::inclusive_bins(c_.doppler_max, c_.doppler_step);
+        std::vector<float> steps(bins_);
+        for (uint32_t i = 0; i < bins_; i++)
+            {
+                const int32_t doppler = -static_cast<int32_t>(c_.doppler_max) + static_cast<int32_t>(c_.doppler_step * i);
+                const float phase_step_rad = static_cast<float>(GALILEO_TWO_PI) * doppler / static_cast<float>(c_.fs_in);
+                steps[i] = phase_step_rad;
+            }
+        for (auto* h : h_) ok_ = ok_ && gb200_acq_set_doppler_grid(h, bins_, steps.data()) == GB200_OK;
+    }
+    // = set_local_code (:117-138): code A as given; code B = the same with its second code period multiplied by (-1, 0)
+    bool set_local_code(const std::complex<float>* code, size_t n_items)
+    {
+        std::vector<std::complex<float>> b(code, code + n_items);
+        const size_t spc = static_cast<size_t>(c_.samples_per_code);
+        for (size_t i = spc; i < 2 * spc && i < n_items; i++) b[i] = code[i] * std::complex<float>(-1.0f, 0.0f);
+        return gb200_acq_set_local_code(h_[0], reinterpret_cast<const float*>(code), n_items) == GB200_OK &&
+               gb200_acq_set_local_code(h_[1], reinterpret_cast<const float*>(b.data()), n_items) == GB200_OK;
+    }
+    void set_state(int state)
+    {
+        state_ = state;
+        if (state == 1) well_count_ = 0;
+    }
+    void reset() { set_state(1); }
+    uint32_t fft_size() const { return gb200_acq_fft_size(h_[0]); }
+    uint32_t num_doppler_bins() const { return bins_; }
+    float test_statistics() const { return test_statistics_; }
+    float mag() const { return mag_; }
+    float input_power() const { return input_power_; }
+    uint32_t code_phase_index() const { return indext_; }
+    uint32_t doppler_bin() const { return bin_; }
+
+    // one pass through general_work state 1 (:225-375); both codes share the wiped-off forward spectra in ONE batch.
+    // Per bin the block keeps the larger of (A, B), A on ties, and over the bins the first strictly larger value; on the
+    // two per-code winners that is: A unless B is larger, or equal in an earlier bin.
+    int run(uint64_t samp_count)
+    {
+        if (state_ != 1) return 0;
+        gb200_acq_result r[2];
+        if (gb200_acq_run_batch(h_, 2, stream_, samp_count, r) != GB200_OK) return -1;
+        well_count_++;
+        const float fnf = static_cast<float>(fft_size()) * static_cast<float>(fft_size());
+        const float m[2] = {r[0].peak_mag / (fnf * fnf), r[1].peak_mag / (fnf * fnf)};
+        const int w = (m[1] > m[0] || (m[1] == m[0] && r[1].doppler_bin < r[0].doppler_bin)) ? 1 : 0;
+        mag_ = m[w];
+        indext_ = r[w].code_phase_index;
+        bin_ = r[w].doppler_bin;
+        input_power_ = r[0].input_power;
+        if (synchro_)
+            {
+                synchro_->Acq_delay_samples = static_cast<double>(indext_ % static_cast<uint32_t>(c_.samples_per_code));
+                synchro_->Acq_doppler_hz = static_cast<double>(-static_cast<int32_t>(c_.doppler_max) + static_cast<int32_t>(c_.doppler_step * bin_));
+                synchro_->Acq_samplestamp_samples = r[w].acq_samplestamp;
+                synchro_->Acq_doppler_step = c_.doppler_step;
+            }
+        test_statistics_ = mag_ / input_power_;
+        int state = 1;
+        if (test_statistics_ > c_.threshold)
+            state = 2;
+        else if (well_count_ == c_.max_dwells)
+            state = 3;
+        if (state == 1) return 0;
+        state_ = 0;
+        if (synchro_) synchro_->Flag_valid_acquisition = (state == 2);
+        return state == 2 ? 1 : 2;
+    }
+
+private:
+    gb200_service* s_;
+    AcqVariantConf c_;
+    gb200_acq* h_[2] = {nullptr, nullptr};
+    AcqSynchro* synchro_ = nullptr;
+    int stream_;
+    bool ok_ = false;
+    int state_ = 0;
+    uint32_t bins_ = 0, well_count_ = 0, indext_ = 0, bin_ = 0;
+    float mag_ = 0.0f, input_power_ = 0.0f, test_statistics_ = 0.0f;
+};
+}  // namespace gb200

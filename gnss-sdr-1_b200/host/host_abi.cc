@@ -4,6 +4,7 @@
 #include <memory>
 
 #include "gb200_acquisition.hpp"
+#include "gb200_acquisition_variants.hpp"
 #include "gb200_host_flat.h"
 #include "gb200_multicorrelator.hpp"
 #include "gb200_tracking.hpp"
@@ -146,6 +147,69 @@ int gbh_acq_search_dump(gb200_service* service, const gb200_acq_cfg* conf, int s
             std::strncpy(dump_file_out, acq.last_dump_file().c_str(), dump_file_cap - 1);
             dump_file_out[dump_file_cap - 1] = 0;
         }
+    return ev;
+}
+
+// ---- sibling PCPS blocks (gb200_acquisition_variants.hpp): a whole attempt, one record of 8 doubles per dwell ----
+// cfg = {sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells, tong_init_val,
+//        tong_max_val, tong_max_dwells, item_type}; variant 0 = Tong, 1 = Galileo E1 8 ms.
+// record = {event, code_phase_index, Acq_doppler_hz, test_statistic, input_power, tong_count, dwell_count, Acq_delay_samples}
+int gbh_acqv_attempt(gb200_service* service, int variant, const double* cfg, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,
+    int max_runs, double* records, int* n_records)
+{
+    AcqVariantConf c;
+    c.sampled_ms = (uint32_t)cfg[0];
+    c.doppler_max = (uint32_t)cfg[1];
+    c.doppler_step = (uint32_t)cfg[2];
+    c.fs_in = (int64_t)cfg[3];
+    c.samples_per_ms = (int)cfg[4];
+    c.samples_per_code = (int)cfg[5];
+    c.threshold = (float)cfg[6];
+    c.max_dwells = (uint32_t)cfg[7];
+    c.tong_init_val = (uint32_t)cfg[8];
+    c.tong_max_val = (uint32_t)cfg[9];
+    c.tong_max_dwells = (uint32_t)cfg[10];
+    c.item_type = (int)cfg[11];
+    AcqSynchro syn;
+    int ev = 0, n = 0;
+    uint64_t at = samp_count;
+    auto drive = [&](auto& acq) -> int {
+        if (!acq.ok()) return -1;
+        acq.set_gnss_synchro(&syn);
+        if (!acq.set_local_code(reinterpret_cast<const std::complex<float>*>(code_iq), code_items)) return -1;
+        acq.reset();
+        for (int k = 0; k < max_runs && ev == 0; k++)
+            {
+                ev = acq.run(at);
+                if (ev < 0) return ev;
+                double* r = records + 8 * n++;
+                r[0] = ev;
+                r[1] = acq.code_phase_index();
+                r[2] = syn.Acq_doppler_hz;
+                r[3] = acq.test_statistics();
+                r[4] = acq.input_power();
+                r[7] = syn.Acq_delay_samples;
+                at += acq.fft_size();
+            }
+        return ev;
+    };
+    if (variant == 0)
+        {
+            B200_Pcps_Tong_Acquisition acq(service, c, stream_id);
+            ev = drive(acq);
+            // the counters of the last dwell (the per-dwell values are implied by the event sequence)
+            if (n > 0)
+                {
+                    records[8 * (n - 1) + 5] = acq.tong_count();
+                    records[8 * (n - 1) + 6] = acq.dwell_count();
+                }
+        }
+    else
+        {
+            B200_Galileo_Pcps_8ms_Acquisition acq(service, c, stream_id);
+            ev = drive(acq);
+        }
+    *n_records = n;
     return ev;
 }
 }

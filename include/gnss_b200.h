@@ -144,6 +144,16 @@ int gb200_acq_set_local_code(gb200_acq* a, const float* code_iq, size_t n_items)
 /* = set_doppler_max / set_doppler_step (pcps_acquisition.h:226-250) + FDMA offset; re-derives the bin grid */
 int gb200_acq_set_doppler(gb200_acq* a, uint32_t doppler_max, uint32_t doppler_step, int64_t freq_offset_hz);
 int gb200_acq_set_threshold(gb200_acq* a, float threshold);
+/* Sibling PCPS blocks that run the same Doppler loop with their own grid rule:
+ * explicit phase step per bin [rad/sample], replacing the doppler_max / doppler_step rule until the next gb200_acq_set_doppler.
+ *   pcps_tong_acquisition_cc::init            pcps_tong_acquisition_cc.cc:183-205 (inclusive bin count, double-precision step)
+ *   galileo_pcps_8ms_acquisition_cc::init     galileo_pcps_8ms_acquisition_cc.cc:148-170 (float32 step, GALILEO_TWO_PI)
+ * gb200_acq_result::doppler_bin indexes this list; doppler_hz is then the caller's to derive. */
+int gb200_acq_set_doppler_grid(gb200_acq* a, uint32_t n_bins, const float* phase_step_rad);
+/* Tong detector arithmetic (pcps_tong_acquisition_cc.cc:330-350): every dwell adds |y|^2 / (N^4 * input_power_of_that_dwell) to
+ * the kept grid; gb200_acq_result::peak_mag / test_statistic are the accumulated maximum, decision is always 2 (the
+ * caller owns the Tong counter) and gb200_acq_reset starts a new attempt (= set_state(1), :226-252). */
+int gb200_acq_set_scaled_accumulation(gb200_acq* a, int enable);
 /* = reset()/set_state(1): clears dwell counter, step-two state and the magnitude grid */
 int gb200_acq_reset(gb200_acq* a);
 /* = acquisition_core (pcps_acquisition.cc:668-930) for one dwell over d_consumed_samples items of

@@ -882,3 +882,229 @@ int go_acq_run(go_acq* a, const void* samples, uint64_t samp_count, go_acq_resul
     (void)state;
     return 0;
 }
+
+/* ======================= sibling PCPS blocks that share the Doppler-loop arithmetic ======================= */
+/* Both follow the older block layout: fft_size = sampled_ms * samples_per_ms, inclusive Doppler-bin count
+ * ("doppler <= doppler_max"), wipe-off tables from volk_gnsssdr_s32f_sincos_32fc with the phase starting at 0. */
+struct go_acqv
+{
+    go_acqv_conf c;
+    uint32_t num_bins;
+    float** wipeoffs;   /* [bin] IQ */
+    float** grid;       /* Tong: d_grid_data[bin][fft_size] */
+    float* fft_code_a;  /* conj(FFT(code)), IQ */
+    float* fft_code_b;  /* 8 ms: second replica inverted */
+    float* work;
+    float* mag;
+    uint32_t dwell_count;
+    int32_t tong_count;
+};
+
+go_acqv* go_acqv_create(const go_acqv_conf* conf)
+{
+    go_acqv* a = (go_acqv*)calloc(1, sizeof(go_acqv));
+    a->c = *conf;
+    const uint32_t n = conf->fft_size;
+    /* pcps_tong_acquisition_cc.cc:183-189, galileo_pcps_8ms_acquisition_cc.cc:150-158: inclusive count */
+    a->num_bins = 0;
+    for (int32_t d = -(int32_t)conf->doppler_max; d <= (int32_t)conf->doppler_max; d += (int32_t)conf->doppler_step) a->num_bins++;
+    a->wipeoffs = (float**)calloc(a->num_bins, sizeof(float*));
+    a->grid = (float**)calloc(a->num_bins, sizeof(float*));
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            a->wipeoffs[i] = (float*)calloc(2 * (size_t)n, sizeof(float));
+            a->grid[i] = (float*)calloc(n, sizeof(float));
+            const int32_t doppler = -(int32_t)conf->doppler_max + (int32_t)(conf->doppler_step * i);
+            float phase_step_rad;
+            if (conf->variant == GO_ACQV_8MS)
+                {
+                    /* galileo_pcps_8ms_acquisition_cc.cc:148,166: float(GALILEO_TWO_PI) * doppler / float(fs), all float32 */
+                    const double GALILEO_TWO_PI = 6.283185307179600;
+                    phase_step_rad = (float)GALILEO_TWO_PI * (float)doppler / (float)conf->fs_in;
+                }
+            else
+                /* pcps_tong_acquisition_cc.cc:200: GPS_TWO_PI (double) * doppler / float(fs), rounded once to float32 */
+                phase_step_rad = (float)(GO_GPS_TWO_PI * doppler / (float)conf->fs_in);
+            go_sincos(a->wipeoffs[i], -phase_step_rad, 0.0f, (int)n);
+        }
+    a->fft_code_a = (float*)calloc(2 * (size_t)n, sizeof(float));
+    a->fft_code_b = (float*)calloc(2 * (size_t)n, sizeof(float));
+    a->work = (float*)calloc(2 * (size_t)n, sizeof(float));
+    a->mag = (float*)calloc(n, sizeof(float));
+    a->tong_count = (int32_t)conf->tong_init_val;
+    return a;
+}
+
+void go_acqv_destroy(go_acqv* a)
+{
+    if (!a) return;
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            free(a->wipeoffs[i]);
+            free(a->grid[i]);
+        }
+    free(a->wipeoffs);
+    free(a->grid);
+    free(a->fft_code_a);
+    free(a->fft_code_b);
+    free(a->work);
+    free(a->mag);
+    free(a);
+}
+
+uint32_t go_acqv_num_doppler_bins(const go_acqv* a) { return a->num_bins; }
+float go_acqv_phase_step(const go_acqv* a, uint32_t bin)
+{
+    /* the table's increment is -phase_step_rad: entry 1 is (cos(-s), sin(-s)); tests read the step back through this */
+    const int32_t doppler = -(int32_t)a->c.doppler_max + (int32_t)(a->c.doppler_step * bin);
+    if (a->c.variant == GO_ACQV_8MS) return (float)6.283185307179600 * (float)doppler / (float)a->c.fs_in;
+    return (float)(GO_GPS_TWO_PI * doppler / (float)a->c.fs_in);
+}
+
+static void go_acqv_code_fft_(go_acqv* a, float* dst)
+{
+    const uint32_t n = a->c.fft_size;
+    go_fft_f32(a->work, (int)n, -1);
+    for (uint32_t i = 0; i < n; i++)
+        {
+            dst[2 * i] = a->work[2 * i];
+            dst[2 * i + 1] = -a->work[2 * i + 1];
+        }
+}
+
+/* pcps_tong_acquisition_cc.cc:170-178; galileo_pcps_8ms_acquisition_cc.cc:117-138 (code B: second replica times -1) */
+void go_acqv_set_local_code(go_acqv* a, const float* code_iq)
+{
+    const uint32_t n = a->c.fft_size;
+    memcpy(a->work, code_iq, sizeof(float) * 2 * n);
+    go_acqv_code_fft_(a, a->fft_code_a);
+    if (a->c.variant == GO_ACQV_8MS)
+        {
+            memcpy(a->work, code_iq, sizeof(float) * 2 * n);
+            for (uint32_t i = a->c.samples_per_code; i < 2 * a->c.samples_per_code && i < n; i++)
+                {
+                    /* volk_32fc_s32fc_multiply_32fc by (-1, 0): (x + jy)(-1 + j0) */
+                    const float xr = code_iq[2 * i], xi = code_iq[2 * i + 1];
+                    a->work[2 * i] = xr * -1.0f - xi * 0.0f;
+                    a->work[2 * i + 1] = xr * 0.0f + xi * -1.0f;
+                }
+            go_acqv_code_fft_(a, a->fft_code_b);
+        }
+}
+
+/* set_state(1) of the Tong block (:226-252): new attempt */
+void go_acqv_restart(go_acqv* a)
+{
+    a->dwell_count = 0;
+    a->tong_count = (int32_t)a->c.tong_init_val;
+    for (uint32_t i = 0; i < a->num_bins; i++) memset(a->grid[i], 0, sizeof(float) * a->c.fft_size);
+}
+
+static void go_acqv_correlate_(go_acqv* a, const float* in, uint32_t bin, const float* fft_code)
+{
+    const uint32_t n = a->c.fft_size;
+    const float* w = a->wipeoffs[bin];
+    for (uint32_t i = 0; i < n; i++)
+        {
+            a->work[2 * i] = in[2 * i] * w[2 * i] - in[2 * i + 1] * w[2 * i + 1];
+            a->work[2 * i + 1] = in[2 * i] * w[2 * i + 1] + in[2 * i + 1] * w[2 * i];
+        }
+    go_fft_f32(a->work, (int)n, -1);
+    for (uint32_t i = 0; i < n; i++)
+        {
+            const float xr = a->work[2 * i], xi = a->work[2 * i + 1];
+            const float cr = fft_code[2 * i], ci = fft_code[2 * i + 1];
+            a->work[2 * i] = xr * cr - xi * ci;
+            a->work[2 * i + 1] = xr * ci + xi * cr;
+        }
+    go_fft_f32(a->work, (int)n, +1);
+    for (uint32_t i = 0; i < n; i++) a->mag[i] = a->work[2 * i] * a->work[2 * i] + a->work[2 * i + 1] * a->work[2 * i + 1];
+}
+
+/* one call = one pass through general_work state 1 (one dwell of fft_size gr_complex items).
+ * Tong: pcps_tong_acquisition_cc.cc:290-395.  8 ms: galileo_pcps_8ms_acquisition_cc.cc:225-375. */
+int go_acqv_run(go_acqv* a, const float* in_iq, go_acqv_result* out)
+{
+    const uint32_t n = a->c.fft_size;
+    const float fnf = (float)n * (float)n;
+    float input_power = 0.0f, d_mag = 0.0f;
+    memset(out, 0, sizeof(*out));
+    a->dwell_count++;
+    for (uint32_t i = 0; i < n; i++) a->mag[i] = in_iq[2 * i] * in_iq[2 * i] + in_iq[2 * i + 1] * in_iq[2 * i + 1];
+    for (uint32_t i = 0; i < n; i++) input_power += a->mag[i];
+    input_power /= (float)n;
+    for (uint32_t bin = 0; bin < a->num_bins; bin++)
+        {
+            const int32_t doppler = -(int32_t)a->c.doppler_max + (int32_t)(a->c.doppler_step * bin);
+            uint32_t indext;
+            float magt;
+            if (a->c.variant == GO_ACQV_8MS)
+                {
+                    go_acqv_correlate_(a, in_iq, bin, a->fft_code_a);
+                    const uint32_t ia = go_index_max(a->mag, n);
+                    const float ma = a->mag[ia] / (fnf * fnf);
+                    go_acqv_correlate_(a, in_iq, bin, a->fft_code_b);
+                    const uint32_t ib = go_index_max(a->mag, n);
+                    const float mb = a->mag[ib] / (fnf * fnf);
+                    if (ma >= mb)
+                        {
+                            magt = ma;
+                            indext = ia;
+                        }
+                    else
+                        {
+                            magt = mb;
+                            indext = ib;
+                        }
+                }
+            else
+                {
+                    go_acqv_correlate_(a, in_iq, bin, a->fft_code_a);
+                    const float scale = 1 / (fnf * fnf * input_power);
+                    for (uint32_t i = 0; i < n; i++) a->mag[i] = a->mag[i] * scale;
+                    for (uint32_t i = 0; i < n; i++) a->grid[bin][i] = a->mag[i] + a->grid[bin][i];
+                    indext = go_index_max(a->grid[bin], n);
+                    magt = a->grid[bin][indext];
+                }
+            if (d_mag < magt)
+                {
+                    d_mag = magt;
+                    out->code_phase_index = indext;
+                    out->acq_delay_samples = (double)(indext % a->c.samples_per_code);
+                    out->doppler_hz = doppler;
+                    out->doppler_bin = bin;
+                }
+        }
+    out->mag = d_mag;
+    out->input_power = input_power;
+    if (a->c.variant == GO_ACQV_8MS)
+        {
+            out->test_statistic = d_mag / input_power;
+            if (out->test_statistic > a->c.threshold)
+                out->decision = 1;
+            else if (a->dwell_count == a->c.max_dwells)
+                out->decision = 0;
+            else
+                out->decision = 2;
+        }
+    else
+        {
+            out->test_statistic = d_mag;
+            int state = 1;
+            if (out->test_statistic > a->c.threshold * a->dwell_count)
+                {
+                    a->tong_count++;
+                    if (a->tong_count == (int32_t)a->c.tong_max_val) state = 2;
+                }
+            else
+                {
+                    a->tong_count--;
+                    if (a->tong_count == 0) state = 3;
+                }
+            if (a->dwell_count >= a->c.tong_max_dwells) state = 3;
+            out->decision = state == 2 ? 1 : (state == 3 ? 0 : 2);
+            out->tong_count = a->tong_count;
+        }
+    out->dwell_count = a->dwell_count;
+    return 0;
+}

@@ -118,6 +118,42 @@ int go_acq_run(go_acq* a, const void* samples, uint64_t samp_count, go_acq_resul
 /* kept magnitude grid, bins x effective_fft_size */
 const float* go_acq_grid(const go_acq* a, int bin);
 
+/* ---------------- sibling PCPS blocks: pcps_tong_acquisition_cc, galileo_pcps_8ms_acquisition_cc ---------------- */
+#define GO_ACQV_TONG 0
+#define GO_ACQV_8MS 1
+typedef struct go_acqv_conf
+{
+    int variant;
+    uint32_t fft_size;          /* d_sampled_ms * d_samples_per_ms */
+    uint32_t samples_per_code;
+    uint32_t doppler_max, doppler_step;
+    int64_t fs_in;
+    float threshold;
+    uint32_t max_dwells;                                  /* 8 ms */
+    uint32_t tong_init_val, tong_max_val, tong_max_dwells; /* Tong */
+} go_acqv_conf;
+typedef struct go_acqv_result
+{
+    uint32_t code_phase_index;
+    int32_t doppler_hz;
+    uint32_t doppler_bin;
+    float mag;            /* d_mag: 8 ms: peak / N^4; Tong: accumulated test statistic of the best cell */
+    float input_power;
+    float test_statistic;
+    int decision;         /* 1 positive, 0 negative, 2 keep dwelling */
+    int32_t tong_count;
+    uint32_t dwell_count;
+    double acq_delay_samples;
+} go_acqv_result;
+typedef struct go_acqv go_acqv;
+go_acqv* go_acqv_create(const go_acqv_conf* conf);
+void go_acqv_destroy(go_acqv* a);
+uint32_t go_acqv_num_doppler_bins(const go_acqv* a);
+float go_acqv_phase_step(const go_acqv* a, uint32_t bin);
+void go_acqv_set_local_code(go_acqv* a, const float* code_iq);
+void go_acqv_restart(go_acqv* a);
+int go_acqv_run(go_acqv* a, const float* in_iq, go_acqv_result* out);
+
 #ifdef __cplusplus
 }
 #endif

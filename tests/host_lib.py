@@ -114,8 +114,24 @@ def host():
         L.gbh_pcps_threshold_from_pfa.argtypes = [C.c_float, C.c_uint, C.c_uint, C.c_uint]
         L.gbh_acq_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        L.gbh_acqv_attempt.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int,
+                                       C.POINTER(C.c_double), C.POINTER(C.c_int)]
         _host = L
     return _host
+
+
+def acq_variant_attempt(service, variant, stream_id, code_c64, samp_count, max_runs, sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms,
+                        samples_per_code, threshold, max_dwells=1, tong_init_val=1, tong_max_val=2, tong_max_dwells=20, item_type=0):
+    """B200_Pcps_Tong_Acquisition (variant 0) / B200_Galileo_Pcps_8ms_Acquisition (variant 1): one attempt; returns (event, records)
+    with one record per dwell: event, code_phase_index, Acq_doppler_hz, test_statistic, input_power, tong_count, dwell_count, Acq_delay_samples."""
+    L = host()
+    cfg = (C.c_double * 12)(sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells, tong_init_val,
+                            tong_max_val, tong_max_dwells, item_type)
+    code = np.ascontiguousarray(code_c64, np.complex64).view(np.float32)
+    rec = (C.c_double * (8 * max_runs))()
+    n = C.c_int(0)
+    ev = L.gbh_acqv_attempt(service.h, variant, cfg, stream_id, code, len(code) // 2, samp_count, max_runs, rec, C.byref(n))
+    return ev, np.array(rec[: 8 * n.value]).reshape(n.value, 8)
 
 
 def oracle_loop():

@@ -84,6 +84,16 @@ def oracle():
     L.go_acq_run.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(GoAcqResult)]
     L.go_acq_grid.argtypes = [C.c_void_p, C.c_int]
     L.go_acq_grid.restype = C.POINTER(C.c_float)
+    L.go_acqv_create.argtypes = [C.POINTER(GoAcqvConf)]
+    L.go_acqv_create.restype = C.c_void_p
+    L.go_acqv_destroy.argtypes = [C.c_void_p]
+    L.go_acqv_num_doppler_bins.argtypes = [C.c_void_p]
+    L.go_acqv_num_doppler_bins.restype = C.c_uint32
+    L.go_acqv_phase_step.argtypes = [C.c_void_p, C.c_uint32]
+    L.go_acqv_phase_step.restype = C.c_float
+    L.go_acqv_set_local_code.argtypes = [C.c_void_p, f32p]
+    L.go_acqv_restart.argtypes = [C.c_void_p]
+    L.go_acqv_run.argtypes = [C.c_void_p, f32p, C.POINTER(GoAcqvResult)]
     _oracle = L
     return L
 
@@ -175,6 +185,56 @@ def acq_conf(**kw):
     for k, v in d.items():
         setattr(c, k, v)
     return c
+
+
+class GoAcqvConf(C.Structure):
+    _fields_ = [("variant", C.c_int), ("fft_size", C.c_uint32), ("samples_per_code", C.c_uint32), ("doppler_max", C.c_uint32),
+                ("doppler_step", C.c_uint32), ("fs_in", C.c_int64), ("threshold", C.c_float), ("max_dwells", C.c_uint32),
+                ("tong_init_val", C.c_uint32), ("tong_max_val", C.c_uint32), ("tong_max_dwells", C.c_uint32)]
+
+
+class GoAcqvResult(C.Structure):
+    _fields_ = [("code_phase_index", C.c_uint32), ("doppler_hz", C.c_int32), ("doppler_bin", C.c_uint32), ("mag", C.c_float),
+                ("input_power", C.c_float), ("test_statistic", C.c_float), ("decision", C.c_int), ("tong_count", C.c_int32),
+                ("dwell_count", C.c_uint32), ("acq_delay_samples", C.c_double)]
+
+
+ACQV_TONG, ACQV_8MS = 0, 1
+
+
+class OracleAcqVariant:
+    """pcps_tong_acquisition_cc / galileo_pcps_8ms_acquisition_cc restatement (oracle/gnss_oracle.c go_acqv_*)."""
+
+    def __init__(self, variant, fft_size, samples_per_code, doppler_max, doppler_step, fs_in, threshold, max_dwells=1, tong_init_val=1,
+                 tong_max_val=2, tong_max_dwells=20):
+        self.L = oracle()
+        self.conf = GoAcqvConf(variant, fft_size, samples_per_code, doppler_max, doppler_step, fs_in, threshold, max_dwells, tong_init_val,
+                               tong_max_val, tong_max_dwells)
+        self.h = self.L.go_acqv_create(C.byref(self.conf))
+        self.fft_size = fft_size
+        self.num_bins = self.L.go_acqv_num_doppler_bins(self.h)
+
+    def phase_steps(self):
+        return np.array([self.L.go_acqv_phase_step(self.h, b) for b in range(self.num_bins)], np.float32)
+
+    def set_local_code(self, code_c64):
+        code = np.ascontiguousarray(code_c64, np.complex64).view(np.float32)
+        assert len(code) == 2 * self.fft_size
+        self.L.go_acqv_set_local_code(self.h, code)
+
+    def restart(self):
+        self.L.go_acqv_restart(self.h)
+
+    def run(self, samples_c64):
+        x = np.ascontiguousarray(samples_c64[: self.fft_size], np.complex64).view(np.float32)
+        r = GoAcqvResult()
+        self.L.go_acqv_run(self.h, x, C.byref(r))
+        return r
+
+    def close(self):
+        if self.h:
+            self.L.go_acqv_destroy(self.h)
+            self.h = None
 
 
 class OracleAcq:

@@ -268,3 +268,56 @@ def test_exact_ties_first_maximum_wins(service, n):
     (pairs, _) = run_pair(service, cfg, code, np.zeros(n, np.complex64))
     r, ro = pairs[0]
     assert (r.code_phase_index, r.doppler_bin) == (ro.code_phase_index, ro.doppler_bin) == (0, 0)
+
+
+def test_tong_detector_block_matches_oracle(service, golden_dir):
+    """B200_Pcps_Tong_Acquisition (host mirror of pcps_tong_acquisition_cc on the C ABI: explicit Doppler grid + per-dwell scaled
+    accumulation on the device) against the restated block, dwell by dwell: same cell, same counter walk, statistic within 1e-4."""
+    import gnss_b200 as gb
+    import host_lib as hl
+
+    x = np.fromfile(golden_dir + "/GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat", np.complex64)
+    rng = np.random.default_rng(3)
+    # four 1 ms dwells: the fixture's two, then the same signal again under fresh noise
+    x4 = np.concatenate([x, x + 0.02 * (rng.standard_normal(8000) + 1j * rng.standard_normal(8000)).astype(np.complex64)]).astype(np.complex64)
+    service.push(3, x4, gb.ITEM_32FC, 0)
+    code = synth.golden_array("gps_prn1_4msps_sampled")[:4000]
+    for thr, init, mx, want_event in ((0.3, 1, 4, 1), (1e9, 3, 5, 2)):
+        o = ol.OracleAcqVariant(ol.ACQV_TONG, 4000, 4000, 5000, 250, 4000000, thr, tong_init_val=init, tong_max_val=mx, tong_max_dwells=20)
+        o.set_local_code(code)
+        o.restart()
+        ev, rec = hl.acq_variant_attempt(service, 0, 3, code, 0, 4, sampled_ms=1, doppler_max=5000, doppler_step=250, fs_in=4000000, samples_per_ms=4000,
+                                         samples_per_code=4000, threshold=thr, tong_init_val=init, tong_max_val=mx, tong_max_dwells=20)
+        assert ev == want_event, (ev, rec)
+        for k, row in enumerate(rec):
+            ro = o.run(x4[4000 * k: 4000 * (k + 1)])
+            assert int(row[1]) == ro.code_phase_index and row[2] == float(ro.doppler_hz) and row[7] == ro.acq_delay_samples, (k, row, ro.code_phase_index, ro.doppler_hz)
+            assert close(row[3], ro.test_statistic) and close(row[4], ro.input_power), (k, row[3], ro.test_statistic)
+            assert {0: 2, 1: 1, 2: 0}[int(row[0])] == ro.decision, (k, row[0], ro.decision)
+        assert int(rec[-1][5]) == ro.tong_count and int(rec[-1][6]) == ro.dwell_count == len(rec)
+        o.close()
+
+
+def test_galileo_8ms_block_matches_oracle(service, golden_dir):
+    """B200_Galileo_Pcps_8ms_Acquisition (codes A and B searched in ONE batch over shared forward spectra, 81 inclusive bins with
+    the block's float32 phase-step rule) against the restated galileo_pcps_8ms_acquisition_cc, incl. the case where code B wins."""
+    import gnss_b200 as gb
+    import host_lib as hl
+
+    xg = np.fromfile(golden_dir + "/Galileo_E1_ID_1_Fs_4Msps_8ms.dat", np.complex64)
+    flipped = xg.copy()
+    flipped[16000 + 2920:] *= -1  # data bit transition between the two code periods
+    cg = synth.golden_array("gal_e1b_prn1_4msps_sampled")[:16000]
+    code = np.concatenate([cg, cg])
+    for stream_x, thr, want_event in ((xg, 1e-4, 1), (flipped, 1e-4, 1), (xg, 1e9, 2)):
+        service.push(3, stream_x, gb.ITEM_32FC, 0)
+        o = ol.OracleAcqVariant(ol.ACQV_8MS, 32000, 16000, 10000, 250, 4000000, thr, max_dwells=1)
+        o.set_local_code(code)
+        ro = o.run(stream_x)
+        ev, rec = hl.acq_variant_attempt(service, 1, 3, code, 0, 1, sampled_ms=8, doppler_max=10000, doppler_step=250, fs_in=4000000, samples_per_ms=4000,
+                                         samples_per_code=16000, threshold=thr, max_dwells=1)
+        assert ev == want_event and len(rec) == 1, (ev, rec)
+        row = rec[0]
+        assert int(row[1]) == ro.code_phase_index == 2920 and row[2] == float(ro.doppler_hz) and row[7] == ro.acq_delay_samples, (row, ro.doppler_hz)
+        assert close(row[3], ro.test_statistic) and close(row[4], ro.input_power), (row[3], ro.test_statistic)
+        o.close()

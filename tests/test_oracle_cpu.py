@@ -236,3 +236,39 @@ def test_product_does_not_touch_oracle():
     so = os.path.join(pkg, "libgnss_b200.so")
     out = os.popen("ldd %s 2>/dev/null; nm -D %s | grep -i ' U ' " % (so, so)).read()
     assert "gnss_oracle" not in out and "gnss_ref" not in out
+
+
+def test_acquisition_variants_on_reference_fixtures(golden_dir):
+    """pcps_tong_acquisition_cc / galileo_pcps_8ms_acquisition_cc restatements (go_acqv_*) on the reference's own fixtures:
+    same cell as the fixtures' truth (524 samples / 1680 Hz; 2920 samples / -632 Hz), inclusive bin count, Tong counter walk."""
+    x = np.fromfile(golden_dir + "/GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat", np.complex64)
+    code = synth.golden_array("gps_prn1_4msps_sampled")[:4000]
+    o = ol.OracleAcqVariant(ol.ACQV_TONG, 4000, 4000, 5000, 250, 4000000, 0.3, tong_init_val=1, tong_max_val=3, tong_max_dwells=20)
+    assert o.num_bins == 41  # "doppler <= doppler_max": one more bin than pcps_acquisition's ceil rule
+    o.set_local_code(code)
+    o.restart()
+    r1, r2 = o.run(x[:4000]), o.run(x[4000:8000])
+    assert (r1.code_phase_index, r1.doppler_hz, r1.decision, r1.tong_count) == (524, 1750, 2, 2)
+    assert (r2.code_phase_index, r2.doppler_hz, r2.decision, r2.tong_count) == (524, 1750, 1, 3)
+    assert r2.test_statistic > r1.test_statistic > 0.3  # the statistic accumulates over the dwells
+    o.restart()
+    o.conf.threshold = 1e9
+    o2 = ol.OracleAcqVariant(ol.ACQV_TONG, 4000, 4000, 5000, 250, 4000000, 1e9, tong_init_val=2, tong_max_val=3, tong_max_dwells=20)
+    o2.set_local_code(code)
+    o2.restart()
+    assert [o2.run(x[:4000]).decision, o2.run(x[4000:8000]).decision] == [2, 0]  # counter 2 -> 1 -> 0: negative
+    o.close()
+    o2.close()
+    xg = np.fromfile(golden_dir + "/Galileo_E1_ID_1_Fs_4Msps_8ms.dat", np.complex64)
+    cg = synth.golden_array("gal_e1b_prn1_4msps_sampled")[:16000]
+    o = ol.OracleAcqVariant(ol.ACQV_8MS, 32000, 16000, 10000, 250, 4000000, 1e-4, max_dwells=1)
+    assert o.num_bins == 81
+    o.set_local_code(np.concatenate([cg, cg]))
+    r = o.run(xg)
+    assert r.decision == 1 and r.code_phase_index == 2920 and abs(r.doppler_hz + 632) <= 166 and r.acq_delay_samples == 2920.0
+    # code B (second period inverted) must win when the data bit flips between the two periods
+    flipped = xg.copy()
+    flipped[16000 + 2920:] *= -1
+    rb = o.run(flipped)
+    assert rb.code_phase_index == 2920 and rb.test_statistic > 0.5 * r.test_statistic
+    o.close()
