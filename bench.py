@@ -42,6 +42,8 @@ METRIC = "acq grid cells/s (tracking channel*Msamples/s in 'tracking')"
 
 # one-lane launch pair under ncu (profiles/r01_ncu_acq_inv_dif_*.txt, capture prof_r01f): 21.28 + 2.31 MB (row) + 50.20 + 0.03 MB (col)
 NCU_PAIR_DRAM_BYTES = 73.8e6
+# tracking launch under ncu (profiles/r01_ncu_trk_packed.txt): 35.31 MB read + 0.006 MB written
+NCU_TRK_DRAM_BYTES = 35.3e6
 
 
 def build_stream(seed):
@@ -405,7 +407,9 @@ def run_b200(args, rank, local_rank, world):
                     "d2h_bytes_per_step": len(req_list) * 72, "ms_per_step": tot_e2e_trk_ms / steps,
                     "blocks": E2E_BLOCKS, "note": "samples pushed in %d blocks on the ingest stream; one correlate call, each block's epochs launch when its push has landed" % E2E_BLOCKS},
             "roofline": {"bound": "fp32", "achieved": trk_tflops, "peak": fp32_peak, "unit": "TFLOP/s", "frac": trk_tflops / fp32_peak if fp32_peak else None,
-                         "traffic": None, "kernel": "gb_trk_kernel<16IC,5,data>", "flops_per_channel_sample": flops_per_chs,
+                         "traffic": NCU_TRK_DRAM_BYTES, "traffic_note": "dram__bytes_read+write of the launch under ncu --set full (profiles/r01_ncu_trk_packed.txt): the 32 MB sample stream once + request records; the 32 channels re-read it from L2",
+                         "kernel": "gb_trk_kernel<16IC,5,data,prompt=2>", "flops_per_channel_sample": flops_per_chs,
+                         "fma_pipe_cycles_per_channel_sample": 33, "issue_slots_per_channel_sample": 35.75,
                          "peak_source": "FMA micro-benchmark run in this process (gb200_service_measure_fp32)"},
             "cpu_baseline": cpu_trk,
         },

@@ -245,6 +245,67 @@ private:
 
 // ---- lock detectors ------------------------------------------------------------------------------------------------
 // lock_detectors.cc:68-86 : signal-to-noise-variance estimator, sums in double
+// src/algorithms/tracking/libs/tracking_2nd_DLL_filter.cc:43-108 and tracking_2nd_PLL_filter.cc:42-105: the older second-order
+// loop filters the GLONASS / C_Aid / KF-free trackers use.  All state and coefficients are float32 as there; the
+// double literals in the coefficient expressions promote exactly where the reference's do.
+class Tracking2ndDllFilter
+{
+public:
+    explicit Tracking2ndDllFilter(float pdi_code = 0.001f) : pdi_(pdi_code) {}
+    void set_DLL_BW(float dll_bw_hz)
+    {
+        bw_ = dll_bw_hz;
+        const float Wn = bw_ * 8.0 * zeta_ / (4.0 * zeta_ * zeta_ + 1.0);
+        tau1_ = 1.0f / (Wn * Wn);  // k / (Wn * Wn) with k = 1.0 passed as float
+        tau2_ = 2.0 * zeta_ / Wn;
+    }
+    void set_pdi(float pdi_code) { pdi_ = pdi_code; }
+    void initialize()
+    {
+        old_nco_ = 0.0f;
+        old_error_ = 0.0f;
+    }
+    float get_code_nco(float disc)
+    {
+        const float nco = old_nco_ + (tau2_ / tau1_) * (disc - old_error_) + (disc + old_error_) * (pdi_ / (2.0 * tau1_));
+        old_nco_ = nco;
+        old_error_ = disc;
+        return nco;
+    }
+
+private:
+    float tau1_ = 0.0f, tau2_ = 0.0f, pdi_, bw_ = 0.0f, zeta_ = 0.7, old_error_ = 0.0f, old_nco_ = 0.0f;
+};
+
+class Tracking2ndPllFilter
+{
+public:
+    explicit Tracking2ndPllFilter(float pdi_carr = 0.001f) : pdi_(pdi_carr) {}
+    void set_PLL_BW(float pll_bw_hz)
+    {
+        bw_ = pll_bw_hz;
+        const float Wn = bw_ * 8.0 * zeta_ / (4.0 * zeta_ * zeta_ + 1.0);
+        tau1_ = 0.25f / (Wn * Wn);  // k = 0.25 passed as float
+        tau2_ = 2.0 * zeta_ / Wn;
+    }
+    void set_pdi(float pdi_carr) { pdi_ = pdi_carr; }
+    void initialize()
+    {
+        old_nco_ = 0.0f;
+        old_error_ = 0.0f;
+    }
+    float get_carrier_nco(float disc)
+    {
+        const float nco = old_nco_ + (tau2_ / tau1_) * (disc - old_error_) + (disc + old_error_) * (pdi_ / (2.0 * tau1_));
+        old_nco_ = nco;
+        old_error_ = disc;
+        return nco;
+    }
+
+private:
+    float tau1_ = 0.0f, tau2_ = 0.0f, pdi_, bw_ = 0.0f, zeta_ = 0.7, old_error_ = 0.0f, old_nco_ = 0.0f;
+};
+
 inline float cn0_svn_estimator(const cfloat* prompt, int n, double coh_integration_time_s)
 {
     double psig = 0.0, ptot = 0.0;

@@ -79,3 +79,57 @@ private:
     bool high_dyn_ = false, has_data_ = false;
 };
 }  // namespace gb200
+
+namespace gb200
+{
+// B200_Multicorrelator: the drop-in for Cpu_Multicorrelator (complex local codes, src/algorithms/tracking/libs/
+// cpu_multicorrelator.h:47-70) that the GLONASS L1 / L2 C/A trackers own -- same methods and argument meaning.
+class B200_Multicorrelator
+{
+public:
+    B200_Multicorrelator() = default;
+    ~B200_Multicorrelator() { free(); }
+    B200_Multicorrelator(const B200_Multicorrelator&) = delete;
+    B200_Multicorrelator& operator=(const B200_Multicorrelator&) = delete;
+    // = init (cpu_multicorrelator.cc:51-66)
+    bool init(gb200_service* service, int stream_id, int item_type, int max_signal_length_samples, int n_correlators)
+    {
+        free();
+        s_ = service;
+        stream_ = stream_id;
+        n_ = n_correlators;
+        max_len_ = max_signal_length_samples;
+        gb200_trk_cfg c{};
+        c.n_taps = n_correlators;
+        c.max_code_len = 2 * 10230;
+        c.code_kind = GB200_CODE_CPLX;
+        c.item_type = item_type;
+        return gb200_trk_create(s_, &c, &h_) == GB200_OK;
+    }
+    // = set_local_code_and_taps (:69-79): local_code_in holds code_length_chips complex values
+    bool set_local_code_and_taps(int code_length_chips, const std::complex<float>* local_code_in, const float* shifts_chips, int n_taps)
+    {
+        if (!h_ || n_taps != n_) return false;
+        return gb200_trk_set_local_code_and_taps(h_, local_code_in, code_length_chips, shifts_chips, n_taps) == GB200_OK;
+    }
+    // = set_input_output_vectors (:82-88) + Carrier_wipeoff_multicorrelator_resampler (:99-126)
+    bool correlate(uint64_t first_sample, float rem_carrier_phase_in_rad, float phase_step_rad, float rem_code_phase_chips, float code_phase_step_chips,
+        int signal_length_samples, std::complex<float>* corr_out)
+    {
+        if (!h_ || signal_length_samples > max_len_) return false;
+        return gb200_trk_correlate(h_, stream_, first_sample, rem_carrier_phase_in_rad, phase_step_rad, 0.0f, rem_code_phase_chips, code_phase_step_chips, 0.0f,
+                   signal_length_samples, reinterpret_cast<float*>(corr_out)) == GB200_OK;
+    }
+    bool free()  // (:129-141)
+    {
+        if (h_) gb200_trk_destroy(h_);
+        h_ = nullptr;
+        return true;
+    }
+
+private:
+    gb200_service* s_ = nullptr;
+    gb200_trk* h_ = nullptr;
+    int stream_ = 0, n_ = 0, max_len_ = 0;
+};
+}  // namespace gb200

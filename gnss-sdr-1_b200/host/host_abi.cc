@@ -5,6 +5,7 @@
 
 #include "gb200_acquisition.hpp"
 #include "gb200_acquisition_variants.hpp"
+#include "gb200_glonass_tracking.hpp"
 #include "gb200_host_flat.h"
 #include "gb200_multicorrelator.hpp"
 #include "gb200_tracking.hpp"
@@ -38,6 +39,24 @@ void gbh_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float acq_dop
     f.set_params(fll_bw, pll_bw, order);
     f.initialize(acq_doppler_hz);
     for (int i = 0; i < n; i++) out[i] = f.get_carrier_error(fll[i], pll[i], t);
+}
+
+void gbh_2nd_filter_run(int which, float bw_hz, float pdi_s, const float* disc, float* out, int n)
+{
+    if (which == 0)
+        {
+            Tracking2ndDllFilter f(pdi_s);
+            f.set_DLL_BW(bw_hz);
+            f.initialize();
+            for (int i = 0; i < n; i++) out[i] = f.get_code_nco(disc[i]);
+        }
+    else
+        {
+            Tracking2ndPllFilter f(pdi_s);
+            f.set_PLL_BW(bw_hz);
+            f.initialize();
+            for (int i = 0; i < n; i++) out[i] = f.get_carrier_nco(disc[i]);
+        }
 }
 
 // ---- DLL/PLL tracking channel on the B200 multicorrelator ----
@@ -211,5 +230,49 @@ int gbh_acqv_attempt(gb200_service* service, int variant, const double* cfg, int
         }
     *n_records = n;
     return ev;
+}
+
+// ---- GLONASS L1 C/A DLL/PLL loop (gb200_glonass_tracking.hpp) on the B200 complex-code correlator ----
+// conf = {fs_in, vector_length, pll_bw_hz, dll_bw_hz, early_late_space_chips, band_freq_hz, band_dfreq_hz}
+// epoch = {tracking_sample_counter, prompt_i, prompt_q, carrier_doppler_hz, code_phase_samples, carrier_phase_rads, cn0_db_hz,
+//          abs_e, abs_p, abs_l, valid_symbol + 2 * loss_of_lock, prn_length_samples}
+struct gbh_glo
+{
+    B200_Multicorrelator corr;
+    GlonassL1CaDllPllTracking<B200_Multicorrelator>* loop = nullptr;
+};
+void* gbh_glo_open(gb200_service* service, int stream_id, int item_type, const double* conf)
+{
+    GlonassTrkConf c;
+    gbh_glo_conf(conf, &c);
+    auto* h = new gbh_glo();
+    if (!h->corr.init(service, stream_id, item_type, 2 * (int)c.vector_length, 3))
+        {
+            delete h;
+            return nullptr;
+        }
+    h->loop = new GlonassL1CaDllPllTracking<B200_Multicorrelator>(c, &h->corr);
+    return h;
+}
+int gbh_glo_start(void* hv, const float* code_iq, int freq_channel, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now)
+{
+    auto* h = static_cast<gbh_glo*>(hv);
+    h->loop->set_sample_counter(now);
+    return h->loop->start_tracking(reinterpret_cast<const std::complex<float>*>(code_iq), freq_channel, acq_delay_samples, acq_doppler_hz, acq_samplestamp) ? 0 : -1;
+}
+int gbh_glo_step(void* hv, double* epoch)
+{
+    auto* h = static_cast<gbh_glo*>(hv);
+    GlonassEpoch e;
+    const bool ok = h->loop->step(&e);
+    gbh_glo_fill(e, epoch);
+    return ok ? 0 : -2;
+}
+void gbh_glo_close(void* hv)
+{
+    auto* h = static_cast<gbh_glo*>(hv);
+    if (!h) return;
+    delete h->loop;
+    delete h;
 }
 }

@@ -162,6 +162,25 @@ void gbref_fll_pll_filter_run(float fll_bw, float pll_bw, int order, float acq_d
     for (int i = 0; i < n; i++) out[i] = f.get_carrier_error(fll_disc[i], pll_disc[i], corr_time_s);
 }
 
+// the older second-order filters (GLONASS / C_Aid trackers): which = 0 Tracking_2nd_DLL_filter, 1 Tracking_2nd_PLL_filter
+void gbref_2nd_filter_run(int which, float bw_hz, float pdi_s, const float* disc, float* out, int n)
+{
+    if (which == 0)
+        {
+            Tracking_2nd_DLL_filter f(pdi_s);
+            f.set_DLL_BW(bw_hz);
+            f.initialize();
+            for (int i = 0; i < n; i++) out[i] = f.get_code_nco(disc[i]);
+        }
+    else
+        {
+            Tracking_2nd_PLL_filter f(pdi_s);
+            f.set_PLL_BW(bw_hz);
+            f.initialize();
+            for (int i = 0; i < n; i++) out[i] = f.get_carrier_nco(disc[i]);
+        }
+}
+
 // ---- timed CPU baseline: the shape of cpu_multicorrelator_real_codes_test.cc:133-163, but with the
 //      block's default kernel pair (standard resampler + standard rotator, dll_pll_veml_tracking.cc:419) ----
 double gbref_bench_multicorrelator_real(const float* sig_in_iq, int n_samples, const float* code, int code_len,

@@ -7,6 +7,7 @@ Outputs (tests/golden/):
   trk_golden.npz   multicorrelator known answers: seeded inputs + outputs of the reference's
                    Cpu_Multicorrelator_Real_Codes / Cpu_Multicorrelator with _generic and _u_avx protokernels
   loop_golden.npz  discriminator / loop-filter / lock-detector outputs of the reference's scalar libs
+  loop2_golden.npz Tracking_2nd_DLL_filter / Tracking_2nd_PLL_filter outputs
   trk16_golden.npz Cpu_Multicorrelator_16sc known answers (int16 samples and codes, saturating outputs), seeds only + outputs
   *.dat            the reference's own acquisition fixtures (src/tests/signal_samples), copied verbatim
 """
@@ -138,6 +139,21 @@ def make_loop():
     np.savez_compressed(os.path.join(HERE, "loop_golden.npz"), **out)
 
 
+def make_loop2():
+    """Tracking_2nd_DLL_filter / Tracking_2nd_PLL_filter impulse + noise responses (the GLONASS / C_Aid trackers' filters)."""
+    out = {}
+    rng = np.random.default_rng(77)
+    d = (0.05 * rng.standard_normal(64)).astype(np.float32)
+    d[0] = 0.3
+    out["disc"] = d
+    for which, name in ((0, "dll"), (1, "pll")):
+        for bw in (2.0, 50.0):
+            y = np.zeros(64, np.float32)
+            R.gbref_2nd_filter_run(which, bw, 0.001, d, y, 64)
+            out["%s_bw%g" % (name, bw)] = y
+    np.savez_compressed(os.path.join(HERE, "loop2_golden.npz"), **out)
+
+
 def make_trk16():
     out = {}
     import synth
@@ -158,4 +174,5 @@ if __name__ == "__main__":
     make_trk()
     make_loop()
     make_trk16()
+    make_loop2()
     print("golden fixtures written to", HERE)

@@ -114,6 +114,12 @@ def host():
         L.gbh_pcps_threshold_from_pfa.argtypes = [C.c_float, C.c_uint, C.c_uint, C.c_uint]
         L.gbh_acq_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        L.gbh_2nd_filter_run.argtypes = [C.c_int, C.c_float, C.c_float, f32p, f32p, C.c_int]
+        L.gbh_glo_open.restype = C.c_void_p
+        L.gbh_glo_open.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        L.gbh_glo_start.argtypes = [C.c_void_p, f32p, C.c_int, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        L.gbh_glo_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.gbh_glo_close.argtypes = [C.c_void_p]
         L.gbh_acqv_attempt.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int,
                                        C.POINTER(C.c_double), C.POINTER(C.c_int)]
         _host = L
@@ -143,6 +149,11 @@ def oracle_loop():
         L.hol_start.argtypes = [C.c_void_p, f32p, C.c_void_p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
         L.hol_step.argtypes = [C.c_void_p, C.POINTER(Epoch)]
         L.hol_close.argtypes = [C.c_void_p]
+        L.hol_glo_open.restype = C.c_void_p
+        L.hol_glo_open.argtypes = [f32p, C.c_uint64, C.c_uint64, C.POINTER(C.c_double)]
+        L.hol_glo_start.argtypes = [C.c_void_p, f32p, C.c_int, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        L.hol_glo_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.hol_glo_close.argtypes = [C.c_void_p]
         L.hol_set_channel.argtypes = [C.c_void_p, C.c_uint]
         _hol = L
     return _hol
@@ -192,3 +203,44 @@ def run_b200_channel(service, stream_id, item_type, first_index, conf, code, acq
         out.append(_record(e))
     L.gbh_trk_close(h)
     return out
+
+
+GLO_EPOCH_FIELDS = ("tracking_sample_counter", "prompt_i", "prompt_q", "carrier_doppler_hz", "code_phase_samples", "carrier_phase_rads", "cn0_db_hz",
+                    "abs_e", "abs_p", "abs_l", "flags", "prn_length_samples")
+
+
+def _glo_conf(fs_in, vector_length, pll_bw_hz, dll_bw_hz, early_late_space_chips, band_freq_hz=1.602e9, band_dfreq_hz=0.5625e6):
+    return (C.c_double * 7)(fs_in, vector_length, pll_bw_hz, dll_bw_hz, early_late_space_chips, band_freq_hz, band_dfreq_hz)
+
+
+def _glo_run(step, h, n_steps):
+    out = np.zeros((n_steps, len(GLO_EPOCH_FIELDS)))
+    e = (C.c_double * len(GLO_EPOCH_FIELDS))()
+    for k in range(n_steps):
+        assert step(h, e) == 0, "correlator refused the request at step %d" % k
+        out[k] = e[:]
+    return out
+
+
+def run_oracle_glonass(samples_c64, first_index, code_c64, freq_channel, acq_delay, acq_doppler, acq_stamp, n_steps, **conf):
+    """Glonass L1 C/A loop (gb200_glonass_tracking.hpp) on the oracle's complex-code correlator; rows of GLO_EPOCH_FIELDS."""
+    L = oracle_loop()
+    x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
+    h = L.hol_glo_open(x, len(x) // 2, first_index, _glo_conf(**conf))
+    assert L.hol_glo_start(h, np.ascontiguousarray(code_c64, np.complex64).view(np.float32), freq_channel, acq_delay, acq_doppler, acq_stamp, first_index) == 0
+    try:
+        return _glo_run(L.hol_glo_step, h, n_steps)
+    finally:
+        L.hol_glo_close(h)
+
+
+def run_b200_glonass(service, stream_id, item_type, first_index, code_c64, freq_channel, acq_delay, acq_doppler, acq_stamp, n_steps, **conf):
+    """the same loop on B200_Multicorrelator (complex codes) through the C ABI"""
+    L = host()
+    h = L.gbh_glo_open(service.h, stream_id, item_type, _glo_conf(**conf))
+    assert h
+    assert L.gbh_glo_start(h, np.ascontiguousarray(code_c64, np.complex64).view(np.float32), freq_channel, acq_delay, acq_doppler, acq_stamp, first_index) == 0
+    try:
+        return _glo_run(L.gbh_glo_step, h, n_steps)
+    finally:
+        L.gbh_glo_close(h)

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../gnss-sdr-1_b200/host/gb200_host_flat.h"
+#include "../../gnss-sdr-1_b200/host/gb200_glonass_tracking.hpp"
 #include "../../gnss-sdr-1_b200/host/gb200_tracking.hpp"
 #include "../../oracle/gnss_oracle.h"
 
@@ -89,4 +90,63 @@ int hol_step(void* h, gbh_epoch* out)
 }
 void hol_set_channel(void* h, unsigned channel) { static_cast<Channel*>(h)->loop->set_channel(channel); }
 void hol_close(void* h) { delete static_cast<Channel*>(h); }
+}
+
+// ---- the GLONASS L1 C/A loop on the oracle's complex-code correlator (go_multicorrelator_cplx <- cpu_multicorrelator.cc:99-126) ----
+namespace
+{
+class OracleCplxCorrelator
+{
+public:
+    OracleCplxCorrelator(const float* samples_iq, uint64_t n_samples, uint64_t first_index) : x_(samples_iq), n_(n_samples), first_(first_index) {}
+    bool set_local_code_and_taps(int code_len, const std::complex<float>* code, const float* shifts, int n_taps)
+    {
+        code_.assign(reinterpret_cast<const float*>(code), reinterpret_cast<const float*>(code) + 2 * code_len);
+        shifts_.assign(shifts, shifts + n_taps);
+        return true;
+    }
+    bool correlate(uint64_t first, float rem_carr, float phase_step, float rem_code, float code_step, int n, std::complex<float>* out)
+    {
+        if (first < first_ || first + (uint64_t)n > first_ + n_) return false;
+        go_multicorrelator_cplx(x_ + 2 * (first - first_), n, code_.data(), (int)code_.size() / 2, shifts_.data(), (int)shifts_.size(), rem_carr, phase_step, rem_code,
+            code_step, reinterpret_cast<float*>(out));
+        return true;
+    }
+
+private:
+    const float* x_;
+    uint64_t n_, first_;
+    std::vector<float> code_, shifts_;
+};
+struct GloChannel
+{
+    std::unique_ptr<OracleCplxCorrelator> corr;
+    std::unique_ptr<gb200::GlonassL1CaDllPllTracking<OracleCplxCorrelator>> loop;
+};
+}  // namespace
+
+extern "C" {
+void* hol_glo_open(const float* samples_iq, uint64_t n_samples, uint64_t first_index, const double* conf)
+{
+    gb200::GlonassTrkConf c;
+    gbh_glo_conf(conf, &c);
+    auto* ch = new GloChannel();
+    ch->corr.reset(new OracleCplxCorrelator(samples_iq, n_samples, first_index));
+    ch->loop.reset(new gb200::GlonassL1CaDllPllTracking<OracleCplxCorrelator>(c, ch->corr.get()));
+    return ch;
+}
+int hol_glo_start(void* h, const float* code_iq, int freq_channel, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now)
+{
+    auto* ch = static_cast<GloChannel*>(h);
+    ch->loop->set_sample_counter(now);
+    return ch->loop->start_tracking(reinterpret_cast<const std::complex<float>*>(code_iq), freq_channel, acq_delay_samples, acq_doppler_hz, acq_samplestamp) ? 0 : -1;
+}
+int hol_glo_step(void* h, double* epoch)
+{
+    gb200::GlonassEpoch e;
+    const bool ok = static_cast<GloChannel*>(h)->loop->step(&e);
+    gbh_glo_fill(e, epoch);
+    return ok ? 0 : -2;
+}
+void hol_glo_close(void* h) { delete static_cast<GloChannel*>(h); }
 }

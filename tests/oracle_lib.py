@@ -148,6 +148,8 @@ def ref():
     L.gbref_carrier_lock_detector.argtypes = [f32p, C.c_int]
     L.gbref_carrier_lock_detector.restype = C.c_float
     L.gbref_tracking_loop_filter_run.argtypes = [C.c_float, C.c_float, C.c_int, C.c_int, C.c_float, f32p, f32p, C.c_int]
+    if hasattr(L, "gbref_2nd_filter_run"):
+        L.gbref_2nd_filter_run.argtypes = [C.c_int, C.c_float, C.c_float, f32p, f32p, C.c_int]
     L.gbref_fll_pll_filter_run.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, f32p, f32p, C.c_float, f32p, C.c_int]
     L.gbref_bench_multicorrelator_real.argtypes = [f32p, C.c_int, f32p, C.c_int, f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
     L.gbref_bench_multicorrelator_real.restype = C.c_double

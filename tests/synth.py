@@ -53,7 +53,7 @@ def sampled_code(table, table_rate, fs, n):
 
 def make_iq(fs, n, sats, seed, noise=True):
     """sats: list of dict(kind, prn, cn0_dbhz, doppler_hz, delay_samples, phase=0.0[, pilot_kind][, symbols][, symbol_periods]
-    [, secondary][, doppler_rate_hz_s]).
+    [, secondary][, doppler_rate_hz_s][, carrier_offset_hz]).
     symbols: +-1 array multiplying the data component, one entry per `symbol_periods` code periods (cyclic);
     secondary: '0'/'1' string multiplying the pilot (or, without pilot_kind, the only) component per code period, '0' -> +1;
     doppler_rate_hz_s: linear Doppler drift (carrier phase gets the quadratic term; the code rate follows the mean Doppler).
@@ -85,7 +85,8 @@ def make_iq(fs, n, sats, seed, noise=True):
             sig = (sig - pil) / np.sqrt(2.0)
         elif sec is not None:
             sig = sig * sec
-        ph = 2 * np.pi * s["doppler_hz"] * t + s.get("phase", 0.0)
+        # carrier_offset_hz: a frequency offset that is NOT Doppler (GLONASS FDMA channel k * 562.5 kHz): carrier only, code rate untouched
+        ph = 2 * np.pi * (s["doppler_hz"] + s.get("carrier_offset_hz", 0.0)) * t + s.get("phase", 0.0)
         if "doppler_rate_hz_s" in s:
             ph = ph + np.pi * s["doppler_rate_hz_s"] * t * t
         x += amp * sig * np.exp(1j * ph)

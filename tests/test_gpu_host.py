@@ -207,3 +207,30 @@ def test_acquisition_dump_matfile(service, tmp_path):
     o.close()
     np.testing.assert_allclose(m["acq_grid"].T, want, rtol=2e-4, atol=1e-6 * want.max())
     assert float(m["input_power"][0, 0]) == pytest.approx(r.input_power, rel=1e-5)
+
+
+def test_glonass_l1_loop_on_b200_matches_oracle_loop(service):
+    """C4's fourth constellation: the GLONASS L1 C/A DLL/PLL block mirror (complex-code correlator, FDMA carrier k * 562.5 kHz,
+    second-order filters) closed on the B200 correlator vs the same loop on the oracle correlator, 8-bit samples at 4 Msps."""
+    import gnss_b200 as gb
+    import test_host_cpu as thc
+
+    fs, doppler, delay, k = 4e6, -2210.0, 1533.7, -3
+    x, code = thc.glonass_scene(500, doppler, delay, k, cn0=48.0, seed=20260008)
+    q = synth.quantize(x, "8ic")
+    service.push(2, q, gb.ITEM_8IC, 0)
+    xq = (q[0::2].astype(np.float32) + 1j * q[1::2].astype(np.float32)).astype(np.complex64)
+    kw = dict(fs_in=fs, vector_length=4000, pll_bw_hz=40.0, dll_bw_hz=2.0, early_late_space_chips=0.5)
+    args = dict(code_c64=code, freq_channel=k, acq_delay=delay - 0.5, acq_doppler=doppler + 35.0, acq_stamp=0, n_steps=480)
+    ref = hl.run_oracle_glonass(xq, 0, **args, **kw)
+    got = hl.run_b200_glonass(service, 2, gb.ITEM_8IC, 0, **args, **kw)
+    F = {n: i for i, n in enumerate(hl.GLO_EPOCH_FIELDS)}
+    assert np.array_equal(got[:, F["tracking_sample_counter"]], ref[:, F["tracking_sample_counter"]])
+    assert np.array_equal(got[:, F["flags"]], ref[:, F["flags"]]) and np.all(got[-200:, F["flags"]] == 1)
+    rel = np.abs(got[1:, F["abs_p"]] - ref[1:, F["abs_p"]]) / ref[1:, F["abs_p"]].max()
+    dd = np.abs(got[:, F["carrier_doppler_hz"]] - ref[:, F["carrier_doppler_hz"]])
+    print("GLONASS closed loop: doppler diff max %.3g Hz, prompt magnitude diff max %.3g of peak, final doppler %.1f Hz" % (
+        dd.max(), rel.max(), got[-1, F["carrier_doppler_hz"]]))
+    assert dd.max() < 0.5 and rel.max() < 2e-3
+    assert abs(got[-150:, F["carrier_doppler_hz"]].mean() - doppler) < 3.0
+    assert np.abs(got[:, F["code_phase_samples"]] - ref[:, F["code_phase_samples"]]).max() < 0.01

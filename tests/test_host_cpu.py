@@ -227,3 +227,40 @@ def test_matfile_writer_is_read_back_by_scipy(tmp_path):
     assert m["PRN"].dtype == np.uint32 and m["PRN"].shape == (1, 1) and int(m["PRN"][0, 0]) == 9
     assert m["sample_counter"].dtype == np.uint64 and int(m["sample_counter"][0, 0]) == (1 << 40) + 5
     assert m["d_positive_acq"].dtype == np.int32 and int(m["d_positive_acq"][0, 0]) == 1
+
+
+def glonass_scene(n_ms, doppler, delay, freq_channel, cn0=47.0, fs=4e6, seed=20260007):
+    x = synth.make_iq(fs, int(n_ms * fs / 1000), [dict(kind="glo_l1_ca", prn=1, cn0_dbhz=cn0, doppler_hz=doppler, delay_samples=delay,
+                                                       carrier_offset_hz=562500.0 * freq_channel, phase=0.4)], seed)
+    code = synth.code_table("glo_l1_ca", 1).astype(np.complex64)
+    return x, code
+
+
+def test_glonass_l1_loop_locks_on_oracle_correlator():
+    """GlonassL1CaDllPllTracking (mirror of glonass_l1_ca_dll_pll_tracking_cc: FDMA carrier, complex code, 2nd-order DLL/PLL) on the
+    oracle's Cpu_Multicorrelator restatement: pulls in from a coarse acquisition estimate and stays locked."""
+    fs, doppler, delay, k = 4e6, 1234.0, 777.3, 1
+    x, code = glonass_scene(700, doppler, delay, k)
+    ep = hl.run_oracle_glonass(x, 0, code, k, acq_delay=delay + 0.6, acq_doppler=doppler - 40.0, acq_stamp=0, n_steps=680,
+                               fs_in=fs, vector_length=4000, pll_bw_hz=40.0, dll_bw_hz=2.0, early_late_space_chips=0.5)
+    F = {n: i for i, n in enumerate(hl.GLO_EPOCH_FIELDS)}
+    assert ep[0, F["flags"]] == 0 and ep[0, F["prn_length_samples"]] == round(delay + 0.6 + 4000 - 0)  # pull-in alignment epoch
+    tail = ep[-200:]
+    assert np.all(tail[:, F["flags"]] == 1)  # valid symbols, no loss of lock
+    assert abs(tail[:, F["carrier_doppler_hz"]].mean() - doppler) < 3.0
+    assert 43.0 < tail[:, F["cn0_db_hz"]].mean() < 51.0
+    assert np.all(tail[:, F["abs_p"]] > 1.5 * np.maximum(tail[:, F["abs_e"]], tail[:, F["abs_l"]]) * 0.5)
+    # the block advances by whole code periods (4000 +- 1 samples at 4 Msps)
+    assert set(np.unique(tail[:, F["prn_length_samples"]])) <= {3999.0, 4000.0, 4001.0}
+
+
+def test_second_order_filters_match_reference_golden(golden_dir):
+    """Tracking2ndDllFilter / Tracking2ndPllFilter (gb200_loop_math.hpp) bit-exact against the reference's
+    Tracking_2nd_DLL_filter / Tracking_2nd_PLL_filter (tests/golden/loop2_golden.npz, generated from oracle/_ref)."""
+    g = np.load(golden_dir + "/loop2_golden.npz")
+    L = hl.host()
+    for which, name in ((0, "dll"), (1, "pll")):
+        for bw in (2.0, 50.0):
+            y = np.zeros(64, np.float32)
+            L.gbh_2nd_filter_run(which, bw, 0.001, g["disc"], y, 64)
+            assert np.array_equal(y, g["%s_bw%g" % (name, bw)]), (name, bw)
