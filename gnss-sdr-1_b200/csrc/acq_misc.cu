@@ -178,6 +178,65 @@ __global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, 
     if (threadIdx.x == 0) *second = best.mag;
 }
 
+// galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:466-606, one CTA per Doppler bin (see gb200_acq_iq_combine in the header)
+struct GbIqRows
+{
+    const float* g[4];  // I_A, Q_A, I_B, Q_B grids [bins][row_len] or nullptr
+};
+__global__ void __launch_bounds__(1024) gb_iq_combine_kernel(GbIqRows rows, int row_len, float norm, gb200_acq_iq_bin* out)
+{
+    __shared__ GbPeak s_pk[5];
+    const size_t off = (size_t)blockIdx.x * row_len;
+    const float* r[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) r[k] = rows.g[k] ? rows.g[k] + off : nullptr;
+    auto row_max = [&](const float* a, const float* b, int slot) {  // first maximum of a[i] (+ b[i])
+        GbPeak best;
+        best.mag = -INFINITY;
+        best.idx = 0xffffffffu;
+        best.bin = 0;
+        best.pad_ = 0;
+        for (int i = threadIdx.x; i < row_len; i += blockDim.x)
+            {
+                GbPeak c;
+                c.mag = b ? __fadd_rn(a[i], b[i]) : a[i];
+                c.idx = (unsigned)i;
+                c.bin = 0;
+                c.pad_ = 0;
+                if (peak_before(c, best)) best = c;
+            }
+        best = peak_block_reduce(best);
+        if (threadIdx.x == 0) s_pk[slot] = best;
+        __syncthreads();
+    };
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (r[k]) row_max(r[k], nullptr, k);
+    const float m_ia = __fdiv_rn(s_pk[0].mag, norm);
+    const float m_qa = r[1] ? __fdiv_rn(s_pk[1].mag, norm) : 0.f;
+    const float m_ib = r[2] ? __fdiv_rn(s_pk[2].mag, norm) : 0.f;
+    const float ib_at_qb = (r[2] && r[3]) ? r[2][s_pk[3].idx] : 0.f;
+    const float m_qb = __fdiv_rn(ib_at_qb, norm);
+    const bool i_b = r[2] && !(m_ia >= m_ib);
+    const bool q_b = r[3] && !(m_qa >= m_qb);
+    row_max(i_b ? r[2] : r[0], r[1] ? (q_b ? r[3] : r[1]) : nullptr, 4);
+    if (threadIdx.x == 0)
+        {
+            gb200_acq_iq_bin o;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                {
+                    o.peak[k] = r[k] ? s_pk[k].mag : 0.f;
+                    o.index[k] = r[k] ? s_pk[k].idx : 0u;
+                }
+            o.ib_at_qb = ib_at_qb;
+            o.mag = s_pk[4].mag;
+            o.indext = s_pk[4].idx;
+            o.picked = (i_b ? 1u : 0u) | (q_b ? 2u : 0u);
+            out[blockIdx.x] = o;
+        }
+}
+
 // last dwell's magnitudes of the LAST Doppler bin into d_tmp_buffer (pcps_acquisition.cc:737, dwell > 1)
 __global__ void gb_copy_kernel(float* dst, const float* src, int n)
 {
@@ -219,6 +278,15 @@ cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins
 cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches)
 {
     gb_grid_peaks_kernel<<<n_handles, 1024, 0, st>>>(grids, n_bins, row_len, out);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_len, float norm, gb200_acq_iq_bin* d_out, cudaStream_t st, int* launches)
+{
+    GbIqRows r;
+    for (int k = 0; k < 4; k++) r.g[k] = rows[k];
+    gb_iq_combine_kernel<<<n_bins, 1024, 0, st>>>(r, row_len, norm, d_out);
     if (launches) (*launches)++;
     return cudaGetLastError();
 }

@@ -201,6 +201,7 @@ cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins
 // grid path: scan stored grids -> per handle peak
 cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches);
 // first_vs_second_peak_statistic's second peak with the d_tmp_buffer quirk (pcps_acquisition.cc:633-660)
+cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_len, float norm, gb200_acq_iq_bin* d_out, cudaStream_t st, int* launches);
 cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches);
 cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st, int* launches);
 size_t gb_acq_col_smem(const GbFftPlan& plan);

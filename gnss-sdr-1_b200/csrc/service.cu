@@ -471,7 +471,12 @@ extern "C" int gb200_service_flush_l2(gb200_service* s, size_t bytes)
 // ------------------------------------------------------------------ sample ring
 static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_items, int item_type, uint64_t first, cudaMemcpyKind kind)
 {
-    if (!s || !src || stream_id < 0 || stream_id >= (int)s->rings.size() || item_type < 0 || item_type > 2) return GB200_E_INVALID;
+    if (!s || !src) return GB200_E_INVALID;
+    if (stream_id < 0 || stream_id >= (int)s->rings.size() || item_type < 0 || item_type > 2)
+        {
+            s->set_error("gb200_stream_push: stream_id outside [0, " + std::to_string(s->rings.size()) + ") or unknown item_type");
+            return GB200_E_INVALID;
+        }
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
     GbRing& r = s->rings[stream_id];
@@ -1073,6 +1078,46 @@ extern "C" int gb200_acq_read_grid(gb200_acq* a, float* dst)
             return GB200_E_STATE;
         }
     GB_CUDA(s, cudaMemcpyAsync(dst, a->d_grid, sizeof(float) * a->num_bins * a->eff, cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    return GB200_OK;
+}
+
+extern "C" int gb200_acq_iq_combine(gb200_acq* ia, gb200_acq* qa, gb200_acq* ib, gb200_acq* qb, float norm, gb200_acq_iq_bin* out)
+{
+    if (!ia || !out) return GB200_E_INVALID;
+    gb200_service* s = ia->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    gb200_acq* h[4] = {ia, qa, ib, qb};
+    const float* rows[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (int k = 0; k < 4; k++)
+        {
+            if (!h[k]) continue;
+            if (h[k]->s != s || h[k]->eff != ia->eff || h[k]->num_bins != ia->num_bins)
+                {
+                    s->set_error("gb200_acq_iq_combine: handles differ in service, geometry or Doppler grid");
+                    return GB200_E_INVALID;
+                }
+            if (!h[k]->d_grid || !h[k]->keep_grid)
+                {
+                    s->set_error("gb200_acq_iq_combine: every handle must keep its grid (gb200_acq_keep_grid) and have run a dwell");
+                    return GB200_E_STATE;
+                }
+            rows[k] = h[k]->d_grid;
+        }
+    if (qb && !ib)
+        {
+            s->set_error("gb200_acq_iq_combine: Q_B needs I_B (the block compares magt_QB on the I_B row)");
+            return GB200_E_INVALID;
+        }
+    void* d_out;
+    int rc;
+    const size_t bytes = sizeof(gb200_acq_iq_bin) * ia->num_bins;
+    if ((rc = s->scratch(9, bytes, &d_out))) return rc;
+    int l = 0;
+    GB_CUDA(s, gb_acq_iq_combine(rows, (int)ia->num_bins, (int)ia->eff, norm, (gb200_acq_iq_bin*)d_out, s->stream, &l));
+    s->launches += l;
+    GB_CUDA(s, cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
     return GB200_OK;
 }

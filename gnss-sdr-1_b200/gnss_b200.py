@@ -53,6 +53,12 @@ class AcqResult(C.Structure):
     ]
 
 
+class AcqIqBin(C.Structure):
+    """gb200_acq_iq_bin: one Doppler bin of gb200_acq_iq_combine."""
+    _fields_ = [("peak", C.c_float * 4), ("index", C.c_uint32 * 4), ("ib_at_qb", C.c_float), ("mag", C.c_float),
+                ("indext", C.c_uint32), ("picked", C.c_uint32)]
+
+
 class TrkCfg(C.Structure):
     _fields_ = [("n_taps", C.c_int), ("max_code_len", C.c_int), ("code_kind", C.c_int), ("high_dyn", C.c_int), ("item_type", C.c_int)]
 
@@ -73,7 +79,7 @@ EXPORTS = [
     "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
-    "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid",
+    "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine",
     "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_set_taps", "gb200_trk_correlate",
     "gb200_trk_correlate_batch", "gb200_trk_correlate_16sc", "gb200_trk_correlate_16sc_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
 ]
@@ -127,6 +133,7 @@ def lib():
     L.gb200_acq_collect_batch.argtypes = [C.POINTER(vp), i, C.POINTER(AcqResult)]
     L.gb200_acq_keep_grid.argtypes = [vp, i]
     L.gb200_acq_read_grid.argtypes = [vp, vp]
+    L.gb200_acq_iq_combine.argtypes = [vp, vp, vp, vp, f, C.POINTER(AcqIqBin)]
     L.gb200_trk_create.argtypes = [vp, C.POINTER(TrkCfg), C.POINTER(vp)]
     L.gb200_trk_destroy.argtypes = [vp]
     L.gb200_trk_set_local_code_and_taps.argtypes = [vp, vp, i, vp, i]
@@ -247,11 +254,13 @@ class Acquisition:
 
     def set_doppler(self, doppler_max, doppler_step, freq_offset_hz=0):
         self.s.check(self.s.L.gb200_acq_set_doppler(self.h, doppler_max, doppler_step, freq_offset_hz))
+        self.num_bins = self.s.L.gb200_acq_num_doppler_bins(self.h)
 
     def set_doppler_grid(self, phase_steps_rad):
         """explicit per-bin phase steps (sibling PCPS blocks with their own grid rule)"""
         st = np.ascontiguousarray(phase_steps_rad, np.float32)
         self.s.check(self.s.L.gb200_acq_set_doppler_grid(self.h, len(st), _ptr(st)))
+        self.num_bins = self.s.L.gb200_acq_num_doppler_bins(self.h)
 
     def set_scaled_accumulation(self, enable=True):
         """Tong detector arithmetic: grid += |y|^2 / (N^4 input_power) every dwell"""
@@ -282,6 +291,14 @@ class Acquisition:
         if self.h:
             self.s.L.gb200_acq_destroy(self.h)
             self.h = C.c_void_p()
+
+
+def acq_iq_combine(ia, qa=None, ib=None, qb=None, norm=1.0):
+    """gb200_acq_iq_combine over the grids the handles kept from their last batch; returns the per-bin records."""
+    rec = (AcqIqBin * ia.num_bins)()
+    h = [a.h if a is not None else None for a in (ia, qa, ib, qb)]
+    ia.s.check(ia.s.L.gb200_acq_iq_combine(h[0], h[1], h[2], h[3], norm, rec))
+    return rec
 
 
 def acq_handles(acqs):

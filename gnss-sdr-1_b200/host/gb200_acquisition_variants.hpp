@@ -1,13 +1,16 @@
-// Host mirrors of two sibling PCPS blocks that run the same Doppler loop as pcps_acquisition, on top of
+// Host mirrors of the sibling PCPS blocks that run the same Doppler loop as pcps_acquisition, on top of
 // the C ABI:
 //   B200_Pcps_Tong_Acquisition        pcps_tong_acquisition_cc         (src/algorithms/acquisition/gnuradio_blocks/pcps_tong_acquisition_cc.cc)
 //   B200_Galileo_Pcps_8ms_Acquisition galileo_pcps_8ms_acquisition_cc  (.../galileo_pcps_8ms_acquisition_cc.cc)
-// Both blocks use fft_size = sampled_ms * samples_per_ms with NO zero padding, count their Doppler bins inclusively
+//   B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf  galileo_e5a_noncoherentIQ_acquisition_caf_cc (.../galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc)
+// The blocks use fft_size = sampled_ms * samples_per_ms with NO zero padding, count their Doppler bins inclusively
 // ("doppler <= doppler_max") and build the wipe-off tables with their own phase-step expression, so the bins are handed to
 // the engine as an explicit list (gb200_acq_set_doppler_grid).  The device does the per-bin arithmetic; the counters,
 // thresholds and Gnss_Synchro fields stay here.
 #pragma once
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <complex>
 #include <cstdint>
 #include <vector>
@@ -28,6 +31,8 @@ struct AcqVariantConf
     float threshold = 0.0f;
     uint32_t max_dwells = 1;                                          // 8 ms block
     uint32_t tong_init_val = 1, tong_max_val = 2, tong_max_dwells = 20;  // Tong block
+    bool bit_transition_flag = false, both_signal_components = false;    // E5a block
+    int caf_window_hz = 0, zero_padding = 0;                             // E5a block
     int item_type = GB200_ITEM_32FC;
 };
 
@@ -278,5 +283,214 @@ private:
     int state_ = 0;
     uint32_t bins_ = 0, well_count_ = 0, indext_ = 0, bin_ = 0;
     float mag_ = 0.0f, input_power_ = 0.0f, test_statistics_ = 0.0f;
+};
+// ------------------------------------------------------------------------------------------------ Galileo E5a non-coherent I/Q + CAF
+// galileo_e5a_noncoherentIQ_acquisition_caf_cc: up to four code spectra (I_A, Q_A and -- for more than one code period --
+// the B replicas whose first period is inverted) correlated against the same wiped-off spectra; per bin the stronger of
+// A / B is kept per component, the Q row is added onto the I row (non-coherent combination) and the row maximum taken.
+// The device does all of that per bin (one batch + gb200_acq_iq_combine); the scalar bookkeeping per bin, the CAF filter
+// over the per-bin peak values and the decision stay here.
+namespace detail
+{
+// :685-768.  Integer types as in the block: `d` is int in the first and last segment and unsigned in the middle one, and
+// several distances are converted to unsigned before (or without) abs() -- bins beyond the centre then weigh hugely
+// negative.  That is the reference's arithmetic and is kept.
+inline void caf_filter(const float* vi, const float* vq, float* cv, unsigned int nb, int window_hz, unsigned int doppler_step)
+{
+    const int H = window_hz / (2 * static_cast<int>(doppler_step));
+    const float wf = 0.5 / static_cast<float>(H);
+    auto smooth = [&](const float* v, int lo, int hi, auto weight, float divisor) {
+        float acc = 0;
+        for (int i = lo; i < hi; i++) acc += v[i] * weight(i);
+        acc /= divisor;
+        return acc;
+    };
+    for (int d = 0; d < H; d++)
+        {
+            const float div = 1 + H + d - wf * H * (H + 1) / 2 - wf * d * (d + 1) / 2;
+            cv[d] = smooth(vi, 0, H + d + 1, [&](int i) { return 1 - wf * static_cast<unsigned int>(d - i); }, div);
+            if (vq) cv[d] += smooth(vq, 0, H + d + 1, [&](int i) { return 1 - wf * static_cast<unsigned int>(std::abs(d - i)); }, div);
+        }
+    for (unsigned int d = H; d < nb - H; d++)
+        {
+            const float div = 1 + 2 * H - 2 * wf * H * (H + 1) / 2;
+            auto w = [&](int i) { return 1 - wf * static_cast<unsigned int>(d - i); };
+            cv[d] = smooth(vi, static_cast<int>(d - H), static_cast<int>(d + H + 1), w, div);
+            if (vq) cv[d] += smooth(vq, static_cast<int>(d - H), static_cast<int>(d + H + 1), w, div);
+        }
+    for (int d = nb - H; d < static_cast<int>(nb); d++)
+        {
+            const float div = 1 + H + (nb - d - 1) - wf * H * (H + 1) / 2 - wf * (nb - d - 1) * (nb - d) / 2;
+            auto w = [&](int i) { return 1 - wf * (std::abs(d - i)); };
+            cv[d] = smooth(vi, d - H, static_cast<int>(nb), w, div);
+            if (vq) cv[d] += smooth(vq, d - H, static_cast<int>(nb), w, div);
+        }
+}
+}  // namespace detail
+
+class B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf
+{
+public:
+    B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf(gb200_service* s, const AcqVariantConf& c, int stream_id) : s_(s), c_(c), stream_(stream_id)
+    {
+        // :95-104: Zero_padding forces the block's d_sampled_ms to 1 (no B replicas); d_fft_size keeps sampled_ms
+        eff_sampled_ms_ = c.zero_padding > 0 ? 1u : c.sampled_ms;
+        const gb200_acq_cfg g = detail::variant_cfg(c, false);
+        const bool want[4] = {true, c.both_signal_components, eff_sampled_ms_ > 1, c.both_signal_components && eff_sampled_ms_ > 1};
+        ok_ = true;
+        for (int k = 0; k < 4 && ok_; k++)
+            if (want[k]) ok_ = gb200_acq_create(s_, &g, &h_[k]) == GB200_OK && gb200_acq_keep_grid(h_[k], 1) == GB200_OK;
+        if (ok_) init();
+    }
+    ~B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf()
+    {
+        for (auto* h : h_)
+            if (h) gb200_acq_destroy(h);
+    }
+    B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf(const B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf&) = delete;
+    B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf& operator=(const B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf&) = delete;
+    bool ok() const { return ok_; }
+    void set_gnss_synchro(AcqSynchro* p) { synchro_ = p; }
+    void set_threshold(float t) { c_.threshold = t; }
+    // = init() (:275-331): GALILEO_TWO_PI (double) * doppler / float(fs), rounded once to float32
+    void init()
+    {
+        const double GALILEO_TWO_PI = 6.283185307179600;
+        bins_ = detail::inclusive_bins(c_.doppler_max, c_.doppler_step);
+        std::vector<float> steps(bins_);
+        for (uint32_t i = 0; i < bins_; i++)
+            {
+                const int doppler = -static_cast<int>(c_.doppler_max) + static_cast<int>(c_.doppler_step * i);
+                const float phase_step_rad = GALILEO_TWO_PI * doppler / static_cast<float>(c_.fs_in);
+                steps[i] = phase_step_rad;
+            }
+        for (auto* h : h_)
+            if (h) ok_ = ok_ && gb200_acq_set_doppler_grid(h, bins_, steps.data()) == GB200_OK;
+        caf_.assign(bins_, 0.0f);
+        caf_i_.assign(bins_, 0.0f);
+        caf_q_.assign(bins_, 0.0f);
+        rec_.resize(bins_);
+    }
+    // = set_local_code(codeI, codeQ) (:238-272).  The block builds the B replicas by overwriting the first code period of
+    // the FFT input buffer, which still holds the previous transform's input: the tail of I_B is codeQ's when both
+    // components are used.
+    bool set_local_code(const std::complex<float>* codeI, const std::complex<float>* codeQ, size_t n_items)
+    {
+        std::vector<std::complex<float>> inbuf(codeI, codeI + n_items);
+        bool ok = gb200_acq_set_local_code(h_[0], reinterpret_cast<const float*>(inbuf.data()), n_items) == GB200_OK;
+        if (h_[1])
+            {
+                inbuf.assign(codeQ, codeQ + n_items);
+                ok = ok && gb200_acq_set_local_code(h_[1], reinterpret_cast<const float*>(inbuf.data()), n_items) == GB200_OK;
+            }
+        const size_t spc = std::min(static_cast<size_t>(c_.samples_per_code), n_items);
+        for (int k = 2; k < 4; k++)
+            {
+                if (!h_[k]) continue;
+                const std::complex<float>* src = k == 2 ? codeI : codeQ;
+                for (size_t i = 0; i < spc; i++) inbuf[i] = src[i] * std::complex<float>(-1.0f, 0.0f);
+                ok = ok && gb200_acq_set_local_code(h_[k], reinterpret_cast<const float*>(inbuf.data()), n_items) == GB200_OK;
+            }
+        return ok;
+    }
+    void set_state(int state)
+    {
+        state_ = state;
+        if (state == 1)
+            {
+                // state 0 with d_active (:385-404)
+                well_count_ = 0;
+                test_statistics_ = 0.0f;
+                mag_ = 0.0f;
+                input_power_ = 0.0f;
+            }
+    }
+    void reset() { set_state(1); }
+    uint32_t fft_size() const { return gb200_acq_fft_size(h_[0]); }
+    uint32_t num_doppler_bins() const { return bins_; }
+    float test_statistics() const { return test_statistics_; }
+    float mag() const { return mag_; }
+    float input_power() const { return input_power_; }
+    uint32_t code_phase_index() const { return indext_; }
+    uint32_t doppler_bin() const { return bin_; }
+    int doppler_hz() const { return doppler_hz_; }
+    bool updated() const { return updated_; }
+    uint32_t well_count() const { return well_count_; }
+    const std::vector<float>& caf_vector() const { return caf_; }
+    const std::vector<gb200_acq_iq_bin>& bin_records() const { return rec_; }
+
+    // one dwell = state 2 of general_work (:440-792).  Returns 0 (next dwell), 1 (positive), 2 (negative), -1 (engine error).
+    int run(uint64_t samp_count)
+    {
+        if (state_ != 1) return 0;
+        gb200_acq* list[4];
+        int n = 0;
+        for (auto* h : h_)
+            if (h) list[n++] = h;
+        gb200_acq_result r[4];
+        if (gb200_acq_run_batch(list, n, stream_, samp_count, r) != GB200_OK) return -1;
+        const float fnf = static_cast<float>(fft_size()) * static_cast<float>(fft_size());
+        if (gb200_acq_iq_combine(h_[0], h_[1], h_[2], h_[3], fnf * fnf, rec_.data()) != GB200_OK) return -1;
+        well_count_++;
+        input_power_ = r[0].input_power;
+        mag_ = 0.0f;
+        updated_ = false;
+        for (uint32_t b = 0; b < bins_; b++)
+            {
+                const gb200_acq_iq_bin& q = rec_[b];
+                if (c_.caf_window_hz > 0)
+                    {
+                        caf_i_[b] = q.peak[(q.picked & 1u) ? 2 : 0];
+                        if (h_[1]) caf_q_[b] = q.peak[(q.picked & 2u) ? 3 : 1];
+                    }
+                const float magt = q.mag / (fnf * fnf);
+                if (mag_ < magt)
+                    {
+                        mag_ = magt;
+                        if (test_statistics_ < (mag_ / input_power_) || !c_.bit_transition_flag)
+                            {
+                                indext_ = q.indext;
+                                bin_ = b;
+                                doppler_hz_ = -static_cast<int>(c_.doppler_max) + static_cast<int>(c_.doppler_step * b);
+                                updated_ = true;
+                                test_statistics_ = mag_ / input_power_;
+                                if (synchro_)
+                                    {
+                                        synchro_->Acq_delay_samples = static_cast<double>(indext_ % static_cast<uint32_t>(c_.samples_per_code));
+                                        synchro_->Acq_doppler_hz = static_cast<double>(doppler_hz_);
+                                        synchro_->Acq_samplestamp_samples = r[0].acq_samplestamp;
+                                        synchro_->Acq_doppler_step = c_.doppler_step;
+                                    }
+                            }
+                    }
+            }
+        if (c_.caf_window_hz > 0)
+            {
+                detail::caf_filter(caf_i_.data(), h_[1] ? caf_q_.data() : nullptr, caf_.data(), bins_, c_.caf_window_hz, c_.doppler_step);
+                uint32_t t = 0;  // volk_gnsssdr_32f_index_max_32u: first maximum
+                for (uint32_t i = 1; i < bins_; i++)
+                    if (caf_[i] > caf_[t]) t = i;
+                doppler_hz_ = -static_cast<int>(c_.doppler_max) + static_cast<int>(c_.doppler_step * t);
+                if (synchro_) synchro_->Acq_doppler_hz = static_cast<double>(doppler_hz_);
+            }
+        if (well_count_ != c_.max_dwells) return 0;
+        const bool positive = test_statistics_ > c_.threshold;
+        state_ = 0;
+        if (synchro_) synchro_->Flag_valid_acquisition = positive;
+        return positive ? 1 : 2;
+    }
+
+private:
+    gb200_service* s_;
+    AcqVariantConf c_;
+    gb200_acq* h_[4] = {nullptr, nullptr, nullptr, nullptr};  // I_A, Q_A, I_B, Q_B
+    AcqSynchro* synchro_ = nullptr;
+    int stream_;
+    bool ok_ = false, updated_ = false;
+    int state_ = 0, doppler_hz_ = 0;
+    uint32_t eff_sampled_ms_ = 1, bins_ = 0, well_count_ = 0, indext_ = 0, bin_ = 0;
+    float mag_ = 0.0f, input_power_ = 0.0f, test_statistics_ = 0.0f;
+    std::vector<float> caf_, caf_i_, caf_q_;
+    std::vector<gb200_acq_iq_bin> rec_;
 };
 }  // namespace gb200

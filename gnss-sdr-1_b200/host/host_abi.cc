@@ -232,6 +232,65 @@ int gbh_acqv_attempt(gb200_service* service, int variant, const double* cfg, int
     return ev;
 }
 
+// ---- Galileo E5a non-coherent I/Q acquisition with CAF filter (gb200_acquisition_variants.hpp) ----
+// cfg = {sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells, bit_transition_flag,
+//        both_signal_components, caf_window_hz, zero_padding, item_type}
+// record (10 doubles per dwell) = {event, code_phase_index, Acq_doppler_hz, doppler_bin, test_statistic, input_power, mag, well_count,
+//        Acq_delay_samples, updated}; caf_out (may be null) receives the CAF vector of the last dwell.
+int gbh_e5a_attempt(gb200_service* service, const double* cfg, int stream_id, const float* code_i_iq, const float* code_q_iq, size_t code_items,
+    uint64_t samp_count, int max_runs, double* records, int* n_records, float* caf_out)
+{
+    AcqVariantConf c;
+    c.sampled_ms = (uint32_t)cfg[0];
+    c.doppler_max = (uint32_t)cfg[1];
+    c.doppler_step = (uint32_t)cfg[2];
+    c.fs_in = (int64_t)cfg[3];
+    c.samples_per_ms = (int)cfg[4];
+    c.samples_per_code = (int)cfg[5];
+    c.threshold = (float)cfg[6];
+    c.max_dwells = (uint32_t)cfg[7];
+    c.bit_transition_flag = cfg[8] != 0;
+    c.both_signal_components = cfg[9] != 0;
+    c.caf_window_hz = (int)cfg[10];
+    c.zero_padding = (int)cfg[11];
+    c.item_type = (int)cfg[12];
+    B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf acq(service, c, stream_id);
+    if (!acq.ok()) return -1;
+    AcqSynchro syn;
+    acq.set_gnss_synchro(&syn);
+    if (!acq.set_local_code(reinterpret_cast<const std::complex<float>*>(code_i_iq), reinterpret_cast<const std::complex<float>*>(code_q_iq), code_items)) return -1;
+    acq.reset();
+    int ev = 0, n = 0;
+    uint64_t at = samp_count;
+    for (int k = 0; k < max_runs && ev == 0; k++)
+        {
+            ev = acq.run(at);
+            if (ev < 0) return ev;
+            double* r = records + 10 * n++;
+            r[0] = ev;
+            r[1] = acq.code_phase_index();
+            r[2] = syn.Acq_doppler_hz;
+            r[3] = acq.doppler_bin();
+            r[4] = acq.test_statistics();
+            r[5] = acq.input_power();
+            r[6] = acq.mag();
+            r[7] = acq.well_count();
+            r[8] = syn.Acq_delay_samples;
+            r[9] = acq.updated() ? 1.0 : 0.0;
+            at += acq.fft_size();
+        }
+    if (caf_out)
+        for (size_t i = 0; i < acq.caf_vector().size(); i++) caf_out[i] = acq.caf_vector()[i];
+    *n_records = n;
+    return ev;
+}
+
+// the CAF filter of the E5a block alone (host arithmetic, no device): caf_q may be null
+void gbh_caf_filter(const float* caf_i, const float* caf_q, float* caf_out, unsigned int num_bins, int caf_window_hz, unsigned int doppler_step)
+{
+    gb200::detail::caf_filter(caf_i, caf_q, caf_out, num_bins, caf_window_hz, doppler_step);
+}
+
 // ---- GLONASS L1 C/A DLL/PLL loop (gb200_glonass_tracking.hpp) on the B200 complex-code correlator ----
 // conf = {fs_in, vector_length, pll_bw_hz, dll_bw_hz, early_late_space_chips, band_freq_hz, band_dfreq_hz}
 // epoch = {tracking_sample_counter, prompt_i, prompt_q, carrier_doppler_hz, code_phase_samples, carrier_phase_rads, cn0_db_hz,

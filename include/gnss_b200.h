@@ -170,6 +170,24 @@ int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_result* out
 int gb200_acq_keep_grid(gb200_acq* a, int keep);
 int gb200_acq_read_grid(gb200_acq* a, float* dst);
 
+/* Non-coherent I/Q combination of galileo_e5a_noncoherentIQ_acquisition_caf_cc's Doppler loop body
+ * (galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:466-606), over the grids the handles kept from their last batch
+ * (gb200_acq_keep_grid; all four share one geometry and Doppler grid).  Codes: ia = I_A (required), qa = Q_A, ib = I_B,
+ * qb = Q_B (each may be NULL as in the block: Q only with both_signal_components, B only with sampled_ms > 1).
+ * Per Doppler bin the device finds each row's first maximum, picks A or B per component by magt_xA >= magt_xB after
+ * dividing by `norm` (= fft_normalization_factor^2; magt_QB reads the I_B row at indext_QB, :508), adds the chosen Q row
+ * onto the chosen I row and takes that row's first maximum.  `out` receives num_doppler_bins records. */
+typedef struct gb200_acq_iq_bin
+{
+    float peak[4];     /* d_magnitudeIA[indext_IA], QA, IB, QB (not normalised; 0 when the code is absent) */
+    uint32_t index[4]; /* indext_IA, _QA, _IB, _QB */
+    float ib_at_qb;    /* d_magnitudeIB[indext_QB]: what the block compares as magt_QB */
+    float mag;         /* maximum of the combined row (not normalised) */
+    uint32_t indext;   /* its index */
+    uint32_t picked;   /* bit 0: I component took B; bit 1: Q component took B */
+} gb200_acq_iq_bin;
+int gb200_acq_iq_combine(gb200_acq* ia, gb200_acq* qa, gb200_acq* ib, gb200_acq* qb, float norm, gb200_acq_iq_bin* out);
+
 /* ------------------------------------------------------------------ tracking ------------ */
 #define GB200_MAX_TAPS 8
 #define GB200_CODE_REAL 0 /* Cpu_Multicorrelator_Real_Codes (float codes)        */

@@ -1108,3 +1108,284 @@ int go_acqv_run(go_acqv* a, const float* in_iq, go_acqv_result* out)
     out->dwell_count = a->dwell_count;
     return 0;
 }
+
+/* ======================= galileo_e5a_noncoherent_iq_acquisition_caf_cc =======================
+ * TEST INFRASTRUCTURE.  Block-level parity unpinned (no reference fixture, block needs GNU Radio); see gnss_oracle.h. */
+struct go_e5a
+{
+    go_e5a_conf c;
+    uint32_t fft_size, num_bins, eff_sampled_ms;
+    float** wipeoffs;
+    float* fft_code[4]; /* I_A, Q_A, I_B, Q_B: conj(FFT(.)) */
+    float* mag[4];      /* d_magnitudeIA, QA, IB, QB */
+    float* work;
+    float *caf, *caf_i, *caf_q;
+    uint32_t well_count;
+    float test_statistics; /* survives from dwell to dwell (:389-403 resets it only in state 0) */
+    go_e5a_result last;    /* Gnss_Synchro image */
+};
+
+go_e5a* go_e5a_create(const go_e5a_conf* conf)
+{
+    go_e5a* a = (go_e5a*)calloc(1, sizeof(go_e5a));
+    a->c = *conf;
+    /* :95-104: Zero_padding forces d_sampled_ms to 1 while d_fft_size keeps the constructor's sampled_ms */
+    a->eff_sampled_ms = conf->zero_padding > 0 ? 1u : conf->sampled_ms;
+    a->fft_size = conf->sampled_ms * conf->samples_per_ms;
+    const uint32_t n = a->fft_size;
+    for (int32_t d = -(int32_t)conf->doppler_max; d <= (int32_t)conf->doppler_max; d += (int32_t)conf->doppler_step) a->num_bins++;
+    a->wipeoffs = (float**)calloc(a->num_bins, sizeof(float*));
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            a->wipeoffs[i] = (float*)calloc(2 * (size_t)n, sizeof(float));
+            go_sincos(a->wipeoffs[i], -go_e5a_phase_step(a, i), 0.0f, (int)n);
+        }
+    for (int k = 0; k < 4; k++)
+        {
+            a->fft_code[k] = (float*)calloc(2 * (size_t)n, sizeof(float));
+            a->mag[k] = (float*)calloc(n, sizeof(float));
+        }
+    a->work = (float*)calloc(2 * (size_t)n, sizeof(float));
+    a->caf = (float*)calloc(a->num_bins, sizeof(float));
+    a->caf_i = (float*)calloc(a->num_bins, sizeof(float));
+    a->caf_q = (float*)calloc(a->num_bins, sizeof(float));
+    return a;
+}
+
+void go_e5a_destroy(go_e5a* a)
+{
+    if (!a) return;
+    for (uint32_t i = 0; i < a->num_bins; i++) free(a->wipeoffs[i]);
+    free(a->wipeoffs);
+    for (int k = 0; k < 4; k++)
+        {
+            free(a->fft_code[k]);
+            free(a->mag[k]);
+        }
+    free(a->work);
+    free(a->caf);
+    free(a->caf_i);
+    free(a->caf_q);
+    free(a);
+}
+
+uint32_t go_e5a_num_doppler_bins(const go_e5a* a) { return a->num_bins; }
+const float* go_e5a_caf_vector(const go_e5a* a) { return a->caf; }
+
+/* :314-316: double GALILEO_TWO_PI * int doppler / float(fs) evaluated in double, rounded once to float32 */
+float go_e5a_phase_step(const go_e5a* a, uint32_t bin)
+{
+    const double GALILEO_TWO_PI = 6.283185307179600;
+    const int doppler = -(int)a->c.doppler_max + (int)(a->c.doppler_step * bin);
+    return (float)(GALILEO_TWO_PI * doppler / (float)a->c.fs_in);
+}
+
+static void go_e5a_code_fft_(go_e5a* a, float* dst)
+{
+    const uint32_t n = a->fft_size;
+    go_fft_f32(a->work, (int)n, -1);
+    for (uint32_t i = 0; i < n; i++)
+        {
+            dst[2 * i] = a->work[2 * i];
+            dst[2 * i + 1] = -a->work[2 * i + 1];
+        }
+}
+
+/* :238-272.  The B replicas overwrite only the first samples_per_code items of the FFT input, the rest still holds the
+ * previous transform's INPUT in FFTW (in-buffer untouched by execute): here the previously copied code. */
+void go_e5a_set_local_code(go_e5a* a, const float* code_i, const float* code_q)
+{
+    const uint32_t n = a->fft_size;
+    const int both = a->c.both_signal_components != 0;
+    float* inbuf = (float*)calloc(2 * (size_t)n, sizeof(float)); /* d_fft_if->get_inbuf() */
+    memcpy(inbuf, code_i, sizeof(float) * 2 * n);
+    memcpy(a->work, inbuf, sizeof(float) * 2 * n);
+    go_e5a_code_fft_(a, a->fft_code[0]);
+    if (both)
+        {
+            memcpy(inbuf, code_q, sizeof(float) * 2 * n);
+            memcpy(a->work, inbuf, sizeof(float) * 2 * n);
+            go_e5a_code_fft_(a, a->fft_code[1]);
+        }
+    if (a->eff_sampled_ms > 1)
+        {
+            for (int k = 0; k < (both ? 2 : 1); k++)
+                {
+                    const float* src = k == 0 ? code_i : code_q;
+                    for (uint32_t i = 0; i < a->c.samples_per_code && i < n; i++)
+                        {
+                            const float xr = src[2 * i], xi = src[2 * i + 1];
+                            inbuf[2 * i] = xr * -1.0f - xi * 0.0f;
+                            inbuf[2 * i + 1] = xr * 0.0f + xi * -1.0f;
+                        }
+                    memcpy(a->work, inbuf, sizeof(float) * 2 * n);
+                    go_e5a_code_fft_(a, a->fft_code[2 + k]);
+                }
+        }
+    free(inbuf);
+}
+
+void go_e5a_restart(go_e5a* a)
+{
+    /* state 0 with d_active (:385-404) */
+    a->well_count = 0;
+    a->test_statistics = 0.0f;
+    memset(&a->last, 0, sizeof(a->last));
+}
+
+static void go_e5a_correlate_(go_e5a* a, const float* spectrum, int k)
+{
+    const uint32_t n = a->fft_size;
+    const float* fc = a->fft_code[k];
+    for (uint32_t i = 0; i < n; i++)
+        {
+            const float xr = spectrum[2 * i], xi = spectrum[2 * i + 1];
+            a->work[2 * i] = xr * fc[2 * i] - xi * fc[2 * i + 1];
+            a->work[2 * i + 1] = xr * fc[2 * i + 1] + xi * fc[2 * i];
+        }
+    go_fft_f32(a->work, (int)n, +1);
+    for (uint32_t i = 0; i < n; i++) a->mag[k][i] = a->work[2 * i] * a->work[2 * i] + a->work[2 * i + 1] * a->work[2 * i + 1];
+}
+
+/* CAF filter over the per-bin peak values, :685-768.  Types as in the block: the first and third loops count in int, the
+ * second in unsigned, and the (doppler_index - i) differences are cast to unsigned BEFORE any abs() in the I sums of loops
+ * one and two and in the Q sum of loop two -- bins on the far side of the centre get a huge negative weight there. */
+void go_e5a_caf_filter(const float* ci, const float* cq, float* cv, uint32_t num_bins, int caf_window_hz, uint32_t doppler_step, int both)
+{
+    int CAF_bins_half = caf_window_hz / (2 * (int)doppler_step);
+    float weighting_factor = 0.5 / (float)CAF_bins_half;
+    const unsigned int nb = num_bins;
+    float accum;
+    for (int d = 0; d < CAF_bins_half; d++)
+        {
+            cv[d] = 0;
+            for (int i = 0; i < CAF_bins_half + d + 1; i++) cv[d] += ci[i] * (1 - weighting_factor * (unsigned int)(d - i));
+            cv[d] /= 1 + CAF_bins_half + d - weighting_factor * CAF_bins_half * (CAF_bins_half + 1) / 2 - weighting_factor * d * (d + 1) / 2;
+            if (both)
+                {
+                    accum = 0;
+                    for (int i = 0; i < CAF_bins_half + d + 1; i++) accum += cq[i] * (1 - weighting_factor * (unsigned int)(abs(d - i)));
+                    accum /= 1 + CAF_bins_half + d - weighting_factor * CAF_bins_half * (CAF_bins_half + 1) / 2 - weighting_factor * d * (d + 1) / 2;
+                    cv[d] += accum;
+                }
+        }
+    for (unsigned int d = CAF_bins_half; d < nb - CAF_bins_half; d++)
+        {
+            cv[d] = 0;
+            for (int i = d - CAF_bins_half; i < (int)(d + CAF_bins_half + 1); i++) cv[d] += ci[i] * (1 - weighting_factor * (unsigned int)(d - i));
+            cv[d] /= 1 + 2 * CAF_bins_half - 2 * weighting_factor * CAF_bins_half * (CAF_bins_half + 1) / 2;
+            if (both)
+                {
+                    accum = 0;
+                    for (int i = d - CAF_bins_half; i < (int)(d + CAF_bins_half + 1); i++) accum += cq[i] * (1 - weighting_factor * (unsigned int)(d - i));
+                    accum /= 1 + 2 * CAF_bins_half - 2 * weighting_factor * CAF_bins_half * (CAF_bins_half + 1) / 2;
+                    cv[d] += accum;
+                }
+        }
+    for (int d = nb - CAF_bins_half; d < (int)nb; d++)
+        {
+            cv[d] = 0;
+            for (int i = d - CAF_bins_half; i < (int)nb; i++) cv[d] += ci[i] * (1 - weighting_factor * (abs(d - i)));
+            cv[d] /= 1 + CAF_bins_half + (nb - d - 1) - weighting_factor * CAF_bins_half * (CAF_bins_half + 1) / 2 - weighting_factor * (nb - d - 1) * (nb - d) / 2;
+            if (both)
+                {
+                    accum = 0;
+                    for (int i = d - CAF_bins_half; i < (int)nb; i++) accum += cq[i] * (1 - weighting_factor * (abs(d - i)));
+                    accum /= 1 + CAF_bins_half + (nb - d - 1) - weighting_factor * CAF_bins_half * (CAF_bins_half + 1) / 2 - weighting_factor * (nb - d - 1) * (nb - d) / 2;
+                    cv[d] += accum;
+                }
+        }
+}
+
+/* one dwell = state 2 of general_work (:440-792) on d_fft_size buffered items */
+int go_e5a_run(go_e5a* a, const float* in, go_e5a_result* out)
+{
+    const uint32_t n = a->fft_size;
+    const int both = a->c.both_signal_components != 0;
+    const int ab = a->eff_sampled_ms > 1;
+    const float fnf = (float)n * (float)n;
+    float* spectrum = (float*)malloc(sizeof(float) * 2 * n);
+    float input_power = 0.0f, d_mag = 0.0f;
+    a->well_count++;
+    a->last.updated = 0;
+    for (uint32_t i = 0; i < n; i++) a->mag[0][i] = in[2 * i] * in[2 * i] + in[2 * i + 1] * in[2 * i + 1];
+    for (uint32_t i = 0; i < n; i++) input_power += a->mag[0][i];
+    input_power /= (float)n;
+    for (uint32_t bin = 0; bin < a->num_bins; bin++)
+        {
+            const int doppler = -(int)a->c.doppler_max + (int)(a->c.doppler_step * bin);
+            const float* w = a->wipeoffs[bin];
+            uint32_t idx[4] = {0, 0, 0, 0};
+            float magt[4] = {0.0f, 0.0f, 0.0f, 0.0f}; /* magt_IA, magt_QA, magt_IB, magt_QB */
+            for (uint32_t i = 0; i < n; i++)
+                {
+                    spectrum[2 * i] = in[2 * i] * w[2 * i] - in[2 * i + 1] * w[2 * i + 1];
+                    spectrum[2 * i + 1] = in[2 * i] * w[2 * i + 1] + in[2 * i + 1] * w[2 * i];
+                }
+            go_fft_f32(spectrum, (int)n, -1);
+            go_e5a_correlate_(a, spectrum, 0);
+            idx[0] = go_index_max(a->mag[0], n);
+            magt[0] = a->mag[0][idx[0]] / (fnf * fnf);
+            if (both)
+                {
+                    go_e5a_correlate_(a, spectrum, 1);
+                    idx[1] = go_index_max(a->mag[1], n);
+                    magt[1] = a->mag[1][idx[1]] / (fnf * fnf);
+                }
+            if (ab)
+                {
+                    go_e5a_correlate_(a, spectrum, 2);
+                    idx[2] = go_index_max(a->mag[2], n);
+                    magt[2] = a->mag[2][idx[2]] / (fnf * fnf);
+                    if (both)
+                        {
+                            go_e5a_correlate_(a, spectrum, 3);
+                            idx[3] = go_index_max(a->mag[3], n);
+                            magt[3] = a->mag[2][idx[3]] / (fnf * fnf); /* :508 reads d_magnitudeIB at indext_QB */
+                        }
+                }
+            /* :512-606: pick A or B per component by its peak, add the Q row onto the I row, take the row maximum */
+            const int pi = (ab && !(magt[0] >= magt[2])) ? 2 : 0;
+            const int pq = (ab && !(magt[1] >= magt[3])) ? 3 : 1;
+            if (a->c.caf_window_hz > 0) a->caf_i[bin] = a->mag[pi][idx[pi]];
+            if (both)
+                {
+                    if (a->c.caf_window_hz > 0) a->caf_q[bin] = a->mag[pq][idx[pq]];
+                    for (uint32_t i = 0; i < n; i++) a->mag[pi][i] += a->mag[pq][i];
+                }
+            const uint32_t indext = go_index_max(a->mag[pi], n);
+            const float m = a->mag[pi][indext] / (fnf * fnf);
+            if (d_mag < m)
+                {
+                    d_mag = m;
+                    if (a->test_statistics < (d_mag / input_power) || !a->c.bit_transition_flag)
+                        {
+                            a->last.code_phase_index = indext;
+                            a->last.acq_delay_samples = (double)(indext % a->c.samples_per_code);
+                            a->last.doppler_hz = doppler;
+                            a->last.doppler_bin = bin;
+                            a->last.updated = 1;
+                            a->test_statistics = d_mag / input_power;
+                        }
+                }
+        }
+    free(spectrum);
+    if (a->c.caf_window_hz > 0)
+        {
+            const unsigned int nb = a->num_bins;
+            float* cv = a->caf;
+            go_e5a_caf_filter(a->caf_i, a->caf_q, cv, nb, a->c.caf_window_hz, a->c.doppler_step, both);
+            const uint32_t t = go_index_max(cv, nb);
+            a->last.doppler_hz = -(int)a->c.doppler_max + (int)(a->c.doppler_step * t);
+        }
+    a->last.mag = d_mag;
+    a->last.input_power = input_power;
+    a->last.test_statistic = a->test_statistics;
+    a->last.well_count = a->well_count;
+    if (a->well_count == a->c.max_dwells)
+        a->last.decision = a->test_statistics > a->c.threshold ? 1 : 0;
+    else
+        a->last.decision = 2;
+    *out = a->last;
+    return 0;
+}

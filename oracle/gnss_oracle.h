@@ -154,6 +154,40 @@ void go_acqv_set_local_code(go_acqv* a, const float* code_iq);
 void go_acqv_restart(go_acqv* a);
 int go_acqv_run(go_acqv* a, const float* in_iq, go_acqv_result* out);
 
+/* ---------------- galileo_e5a_noncoherent_iq_acquisition_caf_cc (pilot + data components, A/B code pairs, CAF filter) ----------------
+ * Block-level parity is UNPINNED: the reference holds no fixture for this block and it needs GNU Radio to build; the
+ * arithmetic underneath (wipe-off table, FFT correlation, |.|^2, first-maximum index) is the pinned go_* code above. */
+typedef struct go_e5a_conf
+{
+    uint32_t sampled_ms;        /* constructor argument; d_fft_size = sampled_ms * samples_per_ms */
+    uint32_t samples_per_ms, samples_per_code;
+    uint32_t max_dwells, doppler_max, doppler_step;
+    int64_t fs_in;
+    int bit_transition_flag, both_signal_components, caf_window_hz, zero_padding;
+    float threshold;
+} go_e5a_conf;
+typedef struct go_e5a_result
+{
+    uint32_t code_phase_index;  /* indext of the winning bin (before % samples_per_code) */
+    uint32_t doppler_bin;       /* bin of the winning cell (before the CAF stage) */
+    int32_t doppler_hz;         /* Acq_doppler_hz after the CAF stage */
+    float mag, input_power, test_statistic;
+    int decision;               /* 1 positive, 0 negative, 2 next dwell */
+    uint32_t well_count;
+    double acq_delay_samples;
+    int updated;                /* the dwell rewrote the Gnss_Synchro fields */
+} go_e5a_result;
+typedef struct go_e5a go_e5a;
+go_e5a* go_e5a_create(const go_e5a_conf* conf);
+void go_e5a_destroy(go_e5a* a);
+uint32_t go_e5a_num_doppler_bins(const go_e5a* a);
+float go_e5a_phase_step(const go_e5a* a, uint32_t bin);
+void go_e5a_set_local_code(go_e5a* a, const float* code_i_iq, const float* code_q_iq);
+void go_e5a_restart(go_e5a* a);   /* state 0 -> 1 */
+int go_e5a_run(go_e5a* a, const float* in_iq, go_e5a_result* out);
+void go_e5a_caf_filter(const float* caf_i, const float* caf_q, float* caf_out, uint32_t num_bins, int caf_window_hz, uint32_t doppler_step, int both);
+const float* go_e5a_caf_vector(const go_e5a* a);  /* d_CAF_vector after the last dwell, num_bins floats (caf_window_hz > 0) */
+
 #ifdef __cplusplus
 }
 #endif

@@ -122,8 +122,42 @@ def host():
         L.gbh_glo_close.argtypes = [C.c_void_p]
         L.gbh_acqv_attempt.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int,
                                        C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.gbh_e5a_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, f32p, C.c_size_t, C.c_uint64, C.c_int,
+                                      C.POINTER(C.c_double), C.POINTER(C.c_int), f32p]
+        L.gbh_caf_filter.argtypes = [f32p, C.c_void_p, f32p, C.c_uint, C.c_int, C.c_uint]
         _host = L
     return _host
+
+
+def caf_filter(caf_i, caf_q, caf_window_hz, doppler_step):
+    """detail::caf_filter of gb200_acquisition_variants.hpp (host arithmetic only)."""
+    L = host()
+    vi = np.ascontiguousarray(caf_i, np.float32)
+    vq = None if caf_q is None else np.ascontiguousarray(caf_q, np.float32)
+    out = np.zeros(len(vi), np.float32)
+    L.gbh_caf_filter(vi, None if vq is None else vq.ctypes.data_as(C.c_void_p), out, len(vi), caf_window_hz, doppler_step)
+    return out
+
+
+E5A_RECORD_FIELDS = ("event", "code_phase_index", "doppler_hz", "doppler_bin", "test_statistic", "input_power", "mag", "well_count",
+                     "acq_delay_samples", "updated")
+
+
+def e5a_caf_attempt(service, stream_id, code_i_c64, code_q_c64, samp_count, max_runs, sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms,
+                    samples_per_code, threshold, max_dwells=1, bit_transition_flag=False, both_signal_components=False, caf_window_hz=0,
+                    zero_padding=0, item_type=0):
+    """B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf: one attempt; returns (event, records [dwells][10], CAF vector of the last dwell)."""
+    L = host()
+    cfg = (C.c_double * 13)(sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells,
+                            int(bit_transition_flag), int(both_signal_components), caf_window_hz, zero_padding, item_type)
+    ci = np.ascontiguousarray(code_i_c64, np.complex64).view(np.float32)
+    cq = np.ascontiguousarray(code_q_c64, np.complex64).view(np.float32)
+    bins = len(range(-int(doppler_max), int(doppler_max) + 1, int(doppler_step)))
+    caf = np.zeros(bins, np.float32)
+    rec = (C.c_double * (10 * max_runs))()
+    n = C.c_int(0)
+    ev = L.gbh_e5a_attempt(service.h, cfg, stream_id, ci, cq, len(ci) // 2, samp_count, max_runs, rec, C.byref(n), caf)
+    return ev, np.array(rec[: 10 * n.value]).reshape(n.value, 10), caf
 
 
 def acq_variant_attempt(service, variant, stream_id, code_c64, samp_count, max_runs, sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms,

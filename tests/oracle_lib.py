@@ -94,6 +94,19 @@ def oracle():
     L.go_acqv_set_local_code.argtypes = [C.c_void_p, f32p]
     L.go_acqv_restart.argtypes = [C.c_void_p]
     L.go_acqv_run.argtypes = [C.c_void_p, f32p, C.POINTER(GoAcqvResult)]
+    L.go_e5a_create.argtypes = [C.POINTER(GoE5aConf)]
+    L.go_e5a_create.restype = C.c_void_p
+    L.go_e5a_destroy.argtypes = [C.c_void_p]
+    L.go_e5a_num_doppler_bins.argtypes = [C.c_void_p]
+    L.go_e5a_num_doppler_bins.restype = C.c_uint32
+    L.go_e5a_phase_step.argtypes = [C.c_void_p, C.c_uint32]
+    L.go_e5a_phase_step.restype = C.c_float
+    L.go_e5a_set_local_code.argtypes = [C.c_void_p, f32p, f32p]
+    L.go_e5a_restart.argtypes = [C.c_void_p]
+    L.go_e5a_run.argtypes = [C.c_void_p, f32p, C.POINTER(GoE5aResult)]
+    L.go_e5a_caf_filter.argtypes = [f32p, f32p, f32p, C.c_uint32, C.c_int, C.c_uint32, C.c_int]
+    L.go_e5a_caf_vector.argtypes = [C.c_void_p]
+    L.go_e5a_caf_vector.restype = C.POINTER(C.c_float)
     _oracle = L
     return L
 
@@ -202,6 +215,67 @@ class GoAcqvResult(C.Structure):
 
 
 ACQV_TONG, ACQV_8MS = 0, 1
+
+
+class GoE5aConf(C.Structure):
+    _fields_ = [("sampled_ms", C.c_uint32), ("samples_per_ms", C.c_uint32), ("samples_per_code", C.c_uint32), ("max_dwells", C.c_uint32),
+                ("doppler_max", C.c_uint32), ("doppler_step", C.c_uint32), ("fs_in", C.c_int64), ("bit_transition_flag", C.c_int),
+                ("both_signal_components", C.c_int), ("caf_window_hz", C.c_int), ("zero_padding", C.c_int), ("threshold", C.c_float)]
+
+
+class GoE5aResult(C.Structure):
+    _fields_ = [("code_phase_index", C.c_uint32), ("doppler_bin", C.c_uint32), ("doppler_hz", C.c_int32), ("mag", C.c_float),
+                ("input_power", C.c_float), ("test_statistic", C.c_float), ("decision", C.c_int), ("well_count", C.c_uint32),
+                ("acq_delay_samples", C.c_double), ("updated", C.c_int)]
+
+
+def e5a_caf_filter(caf_i, caf_q, caf_window_hz, doppler_step):
+    vi = np.ascontiguousarray(caf_i, np.float32)
+    vq = np.ascontiguousarray(caf_q if caf_q is not None else np.zeros(len(vi)), np.float32)
+    out = np.zeros(len(vi), np.float32)
+    oracle().go_e5a_caf_filter(vi, vq, out, len(vi), caf_window_hz, doppler_step, int(caf_q is not None))
+    return out
+
+
+class OracleE5aCaf:
+    """galileo_e5a_noncoherentIQ_acquisition_caf_cc restatement (oracle/gnss_oracle.c go_e5a_*)."""
+
+    def __init__(self, sampled_ms, samples_per_ms, samples_per_code, max_dwells, doppler_max, doppler_step, fs_in, threshold,
+                 bit_transition_flag=False, both_signal_components=False, caf_window_hz=0, zero_padding=0):
+        self.L = oracle()
+        self.conf = GoE5aConf(sampled_ms, samples_per_ms, samples_per_code, max_dwells, doppler_max, doppler_step, fs_in,
+                              int(bit_transition_flag), int(both_signal_components), caf_window_hz, zero_padding, threshold)
+        self.h = self.L.go_e5a_create(C.byref(self.conf))
+        self.fft_size = sampled_ms * samples_per_ms
+        self.num_bins = self.L.go_e5a_num_doppler_bins(self.h)
+
+    def phase_steps(self):
+        return np.array([self.L.go_e5a_phase_step(self.h, b) for b in range(self.num_bins)], np.float32)
+
+    def set_local_code(self, code_i_c64, code_q_c64):
+        ci = np.ascontiguousarray(code_i_c64, np.complex64).view(np.float32)
+        cq = np.ascontiguousarray(code_q_c64, np.complex64).view(np.float32)
+        assert len(ci) == 2 * self.fft_size and len(cq) == 2 * self.fft_size
+        self.L.go_e5a_set_local_code(self.h, ci, cq)
+
+    def restart(self):
+        self.L.go_e5a_restart(self.h)
+
+    def run(self, samples_c64):
+        x = np.ascontiguousarray(samples_c64[: self.fft_size], np.complex64).view(np.float32)
+        assert len(x) == 2 * self.fft_size
+        r = GoE5aResult()
+        self.L.go_e5a_run(self.h, x, C.byref(r))
+        return r
+
+    def caf_vector(self):
+        p = self.L.go_e5a_caf_vector(self.h)
+        return np.array([p[i] for i in range(self.num_bins)], np.float32)
+
+    def close(self):
+        if self.h:
+            self.L.go_e5a_destroy(self.h)
+            self.h = None
 
 
 class OracleAcqVariant:

@@ -127,3 +127,30 @@ def trk16_cases():
             args[1] = 0.0
         cases.append(dict(x=x, code=code, shifts=shifts, args=[np.float32(a).item() for a in args]))
     return cases
+
+
+def iq_pilot_scene(fs, n, prn, cn0_dbhz, doppler_hz, delay_samples, seed, data_flip_at=None, pilot_flip_at=None, phase=0.3):
+    """A data component on I and a pilot in quadrature on one carrier, x = A (c_I d + j c_Q s) e^{j(2 pi f t + phi)} / sqrt(2) + w,
+    the shape galileo_e5a_noncoherentIQ_acquisition_caf_cc searches.  The 10230-chip GPS L5 I5/Q5 tables stand in for the
+    E5a-I/E5a-Q primaries (same length and rate; the block itself is code-agnostic).  `data_flip_at` / `pilot_flip_at`:
+    sample index from which the component's sign is inverted (a data-bit / secondary-code transition).  complex64[n]."""
+    rng = np.random.default_rng(seed)
+    w = rng.standard_normal(n) + 1j * rng.standard_normal(n)
+    comp = []
+    for kind, flip_at in (("gps_l5i", data_flip_at), ("gps_l5q", pilot_flip_at)):
+        c = make_iq(fs, n, [dict(kind=kind, prn=prn, cn0_dbhz=cn0_dbhz - 3.0, doppler_hz=doppler_hz, delay_samples=delay_samples, phase=phase)],
+                    seed=0, noise=False).astype(np.complex128)
+        if flip_at is not None:
+            c[int(flip_at):] *= -1.0
+        comp.append(c)
+    return (w + comp[0] + 1j * comp[1]).astype(np.complex64)
+
+
+def iq_pilot_codes(fs, n, prn, samples_per_code=None, zero_pad_from=None):
+    """Local replicas (codeI, codeQ) of iq_pilot_scene, `n` samples; optionally zeroed from `zero_pad_from` on (Zero_padding)."""
+    ci = sampled_code(code_table("gps_l5i", prn), TABLE_RATE["gps_l5i"], fs, n)
+    cq = sampled_code(code_table("gps_l5q", prn), TABLE_RATE["gps_l5q"], fs, n)
+    if zero_pad_from is not None:
+        ci[zero_pad_from:] = 0
+        cq[zero_pad_from:] = 0
+    return ci, cq

@@ -321,3 +321,103 @@ def test_galileo_8ms_block_matches_oracle(service, golden_dir):
         assert int(row[1]) == ro.code_phase_index == 2920 and row[2] == float(ro.doppler_hz) and row[7] == ro.acq_delay_samples, (row, ro.doppler_hz)
         assert close(row[3], ro.test_statistic) and close(row[4], ro.input_power), (row[3], ro.test_statistic)
         o.close()
+
+
+def test_e5a_noncoherent_iq_caf_block_matches_oracle(service):
+    """B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf (up to four code spectra in ONE batch over shared forward spectra, per-bin
+    A/B pick + I+Q row sum + row maximum on the device: gb200_acq_iq_combine) against the restated
+    galileo_e5a_noncoherentIQ_acquisition_caf_cc: indices, bins, events and the Gnss_Synchro fields exactly, statistics to 1e-4,
+    the CAF vector to 1e-4 of its largest magnitude."""
+    import gnss_b200 as gb
+    import host_lib as hl
+
+    fs, spm, delay, dop = 16000000, 16000, 4321, 750.0
+    x1 = synth.iq_pilot_scene(fs, spm, 5, 50.0, dop, delay, seed=11)
+    x2 = synth.iq_pilot_scene(fs, 2 * spm, 5, 50.0, dop, delay, seed=12, data_flip_at=spm + delay, pilot_flip_at=spm + delay)
+    noise = synth.make_iq(fs, spm, [], seed=13)
+    c1 = synth.iq_pilot_codes(fs, spm, 5)
+    c2 = synth.iq_pilot_codes(fs, 2 * spm, 5)
+    c2z = synth.iq_pilot_codes(fs, 2 * spm, 5, zero_pad_from=spm)
+    cases = [
+        # (dwell streams, codes, sampled_ms, kwargs, threshold)
+        ([x1], c1, 1, dict(), 1e-9),
+        ([x1], c1, 1, dict(both_signal_components=True, caf_window_hz=1000), 1e-9),
+        ([x1], c1, 1, dict(both_signal_components=True, caf_window_hz=1000), 1e9),
+        ([x2], c2, 2, dict(caf_window_hz=1500), 1e-9),
+        ([x2], c2, 2, dict(both_signal_components=True, caf_window_hz=1000), 1e-9),
+        ([x2], c2z, 2, dict(both_signal_components=True, zero_padding=1), 1e-9),
+        ([x1, noise], c1, 1, dict(bit_transition_flag=True, both_signal_components=True, max_dwells=2), 1e-9),
+        ([noise, x1], c1, 1, dict(bit_transition_flag=True, max_dwells=2, caf_window_hz=1000), 1e-9),
+    ]
+    for streams, (ci, cq), sms, kw, thr in cases:
+        okw = {k: v for k, v in kw.items() if k != "max_dwells"}
+        o = ol.OracleE5aCaf(sms, spm, spm, kw.get("max_dwells", 1), 2000, 250, fs, thr, **okw)
+        o.set_local_code(ci, cq)
+        o.restart()
+        want = [o.run(x) for x in streams]
+        want_caf = o.caf_vector()
+        service.push(3, np.concatenate(streams), gb.ITEM_32FC, 0)
+        ev, rec, caf = hl.e5a_caf_attempt(service, 3, ci, cq, 0, len(streams), sampled_ms=sms, doppler_max=2000, doppler_step=250, fs_in=fs,
+                                          samples_per_ms=spm, samples_per_code=spm, threshold=thr, **kw)
+        assert len(rec) == len(want), (kw, rec)
+        for row, ro in zip(rec, want):
+            r = dict(zip(hl.E5A_RECORD_FIELDS, row))
+            assert {0: 2, 1: 1, 2: 0}[int(r["event"])] == ro.decision, (kw, r, ro.decision)
+            # with several code periods in the FFT the correlation is periodic in the code length (and a B replica peaks equally
+            # at d and d + samples_per_code): the raw index is decided by rounding, the block itself reports it modulo the code
+            assert int(r["code_phase_index"]) % spm == ro.code_phase_index % spm and int(r["doppler_bin"]) == ro.doppler_bin, (kw, r, ro.code_phase_index, ro.doppler_bin)
+            assert sms > 1 or int(r["code_phase_index"]) == ro.code_phase_index
+            assert r["doppler_hz"] == float(ro.doppler_hz) and r["acq_delay_samples"] == ro.acq_delay_samples, (kw, r, ro.doppler_hz)
+            assert int(r["well_count"]) == ro.well_count and int(r["updated"]) == ro.updated, (kw, r)
+            assert close(r["test_statistic"], ro.test_statistic) and close(r["input_power"], ro.input_power) and close(r["mag"], ro.mag), (kw, r, ro.mag)
+        assert ev == {2: 0, 1: 1, 0: 2}[want[-1].decision]
+        if kw.get("caf_window_hz", 0) > 0:
+            assert np.max(np.abs(caf - want_caf)) <= 1e-4 * np.max(np.abs(want_caf)), (kw, caf, want_caf)
+        o.close()
+    # the first case really found the scene
+    assert want is not None
+
+
+def test_iq_combine_records_and_error_paths(service):
+    """gb200_acq_iq_combine directly: per-bin records equal what the kept grids say (first maxima, A/B pick after the
+    division by norm, the I_B-row read that stands in for magt_QB, maximum of the I+Q row), and it fails loudly (state error
+    with a message) when a handle keeps no grid."""
+    import gnss_b200 as gb
+
+    fs, spm = 16000000, 16000
+    x = synth.iq_pilot_scene(fs, 2 * spm, 9, 48.0, -500.0, 777, seed=21, data_flip_at=spm + 777)
+    ci, cq = synth.iq_pilot_codes(fs, 2 * spm, 9)
+    service.push(3, x, gb.ITEM_32FC, 0)
+    steps = (2 * np.pi * np.arange(-1000, 1001, 250) / fs).astype(np.float32)
+    codes = [ci, cq, np.concatenate([-ci[:spm], cq[spm:]]), np.concatenate([-cq[:spm], cq[spm:]])]
+    hs = []
+    for c in codes:
+        a = gb.Acquisition(service, sampled_ms=2, ms_per_code=2, samples_per_chip=1, doppler_max=1000, doppler_step=250, fs_in=fs,
+                           samples_per_ms=float(spm), samples_per_code=float(spm))
+        a.set_doppler_grid(steps)
+        a.set_local_code(c)
+        hs.append(a)
+    with pytest.raises(gb.Gb200Error) as e:
+        gb.acq_iq_combine(*hs)
+    assert e.value.code == -5 and "grid" in str(e.value)
+    for a in hs:
+        a.keep_grid(True)
+    gb.acq_run_batch(hs, 3, 0)
+    norm = np.float32(2 * spm) ** 4
+    rec = gb.acq_iq_combine(*hs, norm=float(norm))
+    grids = [a.read_grid() for a in hs]
+    for b in range(len(steps)):
+        rows = [g[b] for g in grids]
+        idx = [int(np.argmax(r)) for r in rows]
+        r = rec[b]
+        assert list(r.index) == idx and [r.peak[k] for k in range(4)] == [rows[k][idx[k]] for k in range(4)]
+        assert r.ib_at_qb == rows[2][idx[3]]
+        m = [np.float32(rows[0][idx[0]]) / norm, np.float32(rows[1][idx[1]]) / norm, np.float32(rows[2][idx[2]]) / norm, np.float32(rows[2][idx[3]]) / norm]
+        i_b, q_b = not (m[0] >= m[2]), not (m[1] >= m[3])
+        assert r.picked == int(i_b) + 2 * int(q_b)
+        comb = rows[2 if i_b else 0] + rows[3 if q_b else 1]
+        assert r.indext == int(np.argmax(comb)) and r.mag == comb[r.indext]
+    # the data-bit transition makes the B replica win on I in the signal's bin (-500 Hz -> bin 2)
+    assert rec[2].picked & 1 and rec[2].indext % spm == 777
+    for a in hs:
+        a.close()

@@ -264,3 +264,19 @@ def test_second_order_filters_match_reference_golden(golden_dir):
             y = np.zeros(64, np.float32)
             L.gbh_2nd_filter_run(which, bw, 0.001, g["disc"], y, 64)
             assert np.array_equal(y, g["%s_bw%g" % (name, bw)]), (name, bw)
+
+
+def test_caf_filter_matches_oracle_arithmetic():
+    """detail::caf_filter (host mirror of galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:685-768) against the oracle's
+    restatement, bit for bit: same integer promotions (the unsigned casts that make far-side weights hugely negative),
+    same float32 accumulation order, with and without the Q component."""
+    import oracle_lib as ol
+
+    rng = np.random.default_rng(77)
+    for bins, window, step in ((17, 1000, 250), (41, 3000, 250), (9, 500, 125), (81, 2000, 125)):
+        vi = (rng.random(bins) * 1e9).astype(np.float32)
+        vq = (rng.random(bins) * 1e9).astype(np.float32)
+        for q in (None, vq):
+            got = hl.caf_filter(vi, q, window, step)
+            want = ol.e5a_caf_filter(vi, q, window, step)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (bins, window, step, q is None)

@@ -272,3 +272,58 @@ def test_acquisition_variants_on_reference_fixtures(golden_dir):
     rb = o.run(flipped)
     assert rb.code_phase_index == 2920 and rb.test_statistic > 0.5 * r.test_statistic
     o.close()
+
+
+E5A_FS, E5A_SPM = 16000000, 16000
+
+
+def test_e5a_caf_block_restatement_finds_the_scene():
+    """go_e5a_* (galileo_e5a_noncoherentIQ_acquisition_caf_cc restated; block-level parity unpinned, see oracle/gnss_oracle.h)
+    on a synthetic data+pilot scene: code phase and Doppler bin are found, the B replicas carry a data-bit transition that
+    the A replicas alone lose, and the test statistic survives from dwell to dwell with bit_transition_flag."""
+    delay, dop = 4321, 750.0
+    # one code period, I only
+    x1 = synth.iq_pilot_scene(E5A_FS, E5A_SPM, 5, 50.0, dop, delay, seed=11)
+    ci, cq = synth.iq_pilot_codes(E5A_FS, E5A_SPM, 5)
+    o = ol.OracleE5aCaf(1, E5A_SPM, E5A_SPM, 1, 2000, 250, E5A_FS, 1e-9)
+    assert o.num_bins == 17 and np.isclose(o.phase_steps()[0], -2 * np.pi * 2000 / E5A_FS, rtol=1e-6)
+    o.set_local_code(ci, cq)
+    o.restart()
+    r = o.run(x1)
+    assert r.decision == 1 and r.code_phase_index == delay and r.doppler_hz == 750 and r.doppler_bin == 11 and r.updated == 1
+    single = r.test_statistic
+    o.close()
+    # both components: the non-coherent sum raises the statistic
+    o = ol.OracleE5aCaf(1, E5A_SPM, E5A_SPM, 1, 2000, 250, E5A_FS, 1e-9, both_signal_components=True, caf_window_hz=1000)
+    o.set_local_code(ci, cq)
+    o.restart()
+    r = o.run(x1)
+    assert r.code_phase_index == delay and r.doppler_bin == 11 and r.test_statistic > 1.5 * single
+    o.close()
+    # two code periods with a data-bit transition at the period boundary: A+B replicas hold what zero-padded A loses half of
+    n2 = 2 * E5A_SPM
+    x2 = synth.iq_pilot_scene(E5A_FS, n2, 5, 50.0, dop, delay, seed=12, data_flip_at=E5A_SPM + delay)
+    ci2, cq2 = synth.iq_pilot_codes(E5A_FS, n2, 5)
+    o = ol.OracleE5aCaf(2, E5A_SPM, E5A_SPM, 1, 2000, 250, E5A_FS, 1e-9)
+    o.set_local_code(ci2, cq2)
+    o.restart()
+    r_ab = o.run(x2)
+    o.close()
+    ciz, cqz = synth.iq_pilot_codes(E5A_FS, n2, 5, zero_pad_from=E5A_SPM)
+    o = ol.OracleE5aCaf(2, E5A_SPM, E5A_SPM, 1, 2000, 250, E5A_FS, 1e-9, zero_padding=1)
+    o.set_local_code(ciz, cqz)
+    o.restart()
+    r_zp = o.run(x2)
+    o.close()
+    assert r_ab.code_phase_index % E5A_SPM == delay and r_zp.code_phase_index % E5A_SPM == delay
+    # coherent over 2 * 16000 - 2 * delay samples (circular correlation) against 16000 of the zero-padded replica
+    assert r_ab.test_statistic > 1.8 * r_zp.test_statistic
+    # bit_transition_flag: two dwells, the second (noise only) must not overwrite the first one's result
+    o = ol.OracleE5aCaf(1, E5A_SPM, E5A_SPM, 2, 2000, 250, E5A_FS, 1e-9, bit_transition_flag=True)
+    o.set_local_code(ci, cq)
+    o.restart()
+    ra = o.run(x1)
+    noise = synth.make_iq(E5A_FS, E5A_SPM, [], seed=13)
+    rb = o.run(noise)
+    assert ra.decision == 2 and rb.decision == 1 and rb.updated == 0 and rb.code_phase_index == delay and rb.test_statistic == ra.test_statistic
+    o.close()
