@@ -307,6 +307,70 @@ cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st
 
 
 
+// ---- ingest: acquisition resampler (gnss_flowgraph.cc:423-476: fir_filter_ccf(decimation, low-pass taps)) ----
+// y[k] = sum_j taps[j] x[kD - j].  A CTA produces blockDim.x consecutive outputs: it stages the input span
+// [k0 D - (T-1), (k0 + B - 1) D] once (coalesced, ring wrap and the zero history handled there) de-interleaved by phase
+// (element m -> s[m % D][m / D]), so that in the dot product consecutive threads read consecutive shared-memory words for
+// every tap; the taps are a warp-uniform read.  HBM traffic: 8 B per input item + 8/D B per item written.
+namespace
+{
+__global__ void gb_fir_decimate_kernel(const float2* __restrict__ ring, unsigned long long cap, unsigned long long valid_begin, unsigned long long k_first,
+    unsigned n_out, unsigned D, const float* __restrict__ taps, unsigned T, float2* __restrict__ out)
+{
+    extern __shared__ float2 s_x[];
+    const unsigned B = blockDim.x;
+    const unsigned long long k0 = k_first + (unsigned long long)blockIdx.x * B;
+    const unsigned span = (B - 1) * D + T;            // inputs this CTA touches
+    const unsigned rows = (span + D - 1) / D;         // elements per phase row
+    const long long base = (long long)(k0 * D) - (long long)(T - 1);  // absolute index of span element 0 (may be negative)
+    for (unsigned m = threadIdx.x; m < span; m += B)
+        {
+            const long long a = base + (long long)m;
+            float2 v = make_float2(0.f, 0.f);
+            if (a >= (long long)valid_begin) v = ring[(unsigned long long)a % cap];
+            s_x[(m % D) * rows + m / D] = v;
+        }
+    __syncthreads();
+    const unsigned t = threadIdx.x;
+    if ((unsigned long long)blockIdx.x * B + t >= n_out) return;
+    // output k0 + t reads span elements m = t D + (T - 1) - j
+    float ax = 0.f, ay = 0.f;
+    unsigned m = t * D + (T - 1);
+    unsigned p = m % D, q = m / D;
+    for (unsigned j = 0; j < T; j++)
+        {
+            const float w = __ldg(taps + j);
+            const float2 x = s_x[p * rows + q];
+            ax = fmaf(w, x.x, ax);
+            ay = fmaf(w, x.y, ay);
+            if (p == 0)
+                {
+                    p = D - 1;
+                    q--;
+                }
+            else
+                p--;
+        }
+    out[(unsigned long long)blockIdx.x * B + t] = make_float2(ax, ay);
+}
+}  // namespace
+
+cudaError_t gb_fir_decimate(const float2* ring, unsigned long long cap, unsigned long long valid_begin, unsigned long long k_first, unsigned n_out,
+    unsigned decimation, const float* d_taps, unsigned n_taps, float2* out, cudaStream_t st, int* launches)
+{
+    if (n_out == 0) return cudaSuccess;
+    unsigned B = 256;
+    auto smem = [&](unsigned b) { return sizeof(float2) * (size_t)decimation * (((size_t)(b - 1) * decimation + n_taps + decimation - 1) / decimation); };
+    while (B > 32 && smem(B) > 96 * 1024) B >>= 1;
+    const size_t sm = smem(B);
+    if (sm > 96 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(gb_fir_decimate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    if (e != cudaSuccess) return e;
+    gb_fir_decimate_kernel<<<(n_out + B - 1) / B, B, sm, st>>>(ring, cap, valid_begin, k_first, n_out, decimation, d_taps, n_taps, out);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
 // ---- ingest: conjugate the pushed items in place (inverted_spectrum option of the data-type adapters) ----
 // Replaces conjugate_cc / conjugate_sc / conjugate_ic (src/algorithms/libs/conjugate_{cc,sc,ic}.cc -> volk_32fc_conjugate_32fc,
 // volk_gnsssdr_16ic_conjugate_16ic, volk_gnsssdr_8ic_conjugate_8ic): the imaginary part is negated in the item's own type, so

@@ -201,6 +201,9 @@ cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins
 // grid path: scan stored grids -> per handle peak
 cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches);
 // first_vs_second_peak_statistic's second peak with the d_tmp_buffer quirk (pcps_acquisition.cc:633-660)
+// FIR + decimation of the newest items of a 32fc ring into a linear buffer (gb200_stream_set_decimator)
+cudaError_t gb_fir_decimate(const float2* ring, unsigned long long cap, unsigned long long valid_begin, unsigned long long k_first, unsigned n_out,
+    unsigned decimation, const float* d_taps, unsigned n_taps, float2* out, cudaStream_t st, int* launches);
 cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_len, float norm, gb200_acq_iq_bin* d_out, cudaStream_t st, int* launches);
 cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches);
 cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st, int* launches);

@@ -53,6 +53,18 @@ struct GbRing
     static const int kMarks = 16;
     Mark marks[kMarks];
     uint64_t push_seq = 0;
+    // acquisition resampler hanging off this (source) stream: gb200_stream_set_decimator
+    struct Decimator
+    {
+        bool on = false;
+        int dst = -1;
+        unsigned D = 0, T = 0;
+        float* d_taps = nullptr;
+        float2* d_out = nullptr;     // one push worth of outputs, then copied into the destination ring in stream order
+        size_t out_cap = 0;
+        uint64_t next_k = 0;         // next output index to produce
+        uint64_t valid_begin = 0;    // first source item of the current continuous run (older ones count as zero history)
+    } decim;
     // event of the oldest recorded push that already covers item index `need_end - 1` (nullptr: none recorded)
     const Mark* mark_for(uint64_t need_end) const
     {
@@ -248,7 +260,11 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     cudaStreamSynchronize(s->stream);
     if (s->cb) gb200_trk_batch_destroy(s->cb);
     for (auto& r : s->rings)
-        if (r.d_buf) cudaFree(r.d_buf);
+        {
+            if (r.d_buf) cudaFree(r.d_buf);
+            if (r.decim.d_taps) cudaFree(r.decim.d_taps);
+            if (r.decim.d_out) cudaFree(r.decim.d_out);
+        }
     for (auto& kv : s->plans)
         {
             if (kv.second.d_tw1) cudaFree(kv.second.d_tw1);
@@ -509,6 +525,12 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
             s->set_error("push larger than ring capacity");
             return GB200_E_RANGE;
         }
+    const bool restart = !r.any || first != r.end;
+    if (r.decim.on && (item_type != GB200_ITEM_32FC || n_items + r.decim.T + r.decim.D > r.cap))
+        {
+            s->set_error("gb200_stream_push: the stream's decimator needs GB200_ITEM_32FC items and push + taps + decimation <= ring capacity");
+            return item_type != GB200_ITEM_32FC ? GB200_E_UNSUPPORTED : GB200_E_RANGE;
+        }
     if (r.any && first != r.end)
         {
             // discontinuity: everything held so far is dropped
@@ -553,6 +575,145 @@ static int ring_push(gb200_service* s, int stream_id, const void* src, size_t n_
     r.end = first + n_items;
     r.any = true;
     if (r.end - r.begin > r.cap) r.begin = r.end - r.cap;
+    if (r.decim.on)
+        {
+            // fir_filter_ccf(decimation, taps) of the flowgraph's acquisition resampler, behind the copy on the same stream
+            GbRing::Decimator& d = r.decim;
+            if (restart)
+                {
+                    d.valid_begin = first;
+                    d.next_k = (first + d.D - 1) / d.D;
+                }
+            const uint64_t newest = r.end - 1;
+            if (d.next_k * d.D <= newest)
+                {
+                    const uint64_t k_last = newest / d.D;
+                    const unsigned n_out = (unsigned)(k_last - d.next_k + 1);
+                    int l = 0;
+                    GB_CUDA(s, gb_fir_decimate((const float2*)r.d_buf, r.cap, d.valid_begin, d.next_k, n_out, d.D, d.d_taps, d.T, d.d_out, s->copy_stream, &l));
+                    s->launches += l;
+                    const uint64_t k_first = d.next_k;
+                    d.next_k = k_last + 1;
+                    const int dst = d.dst;
+                    const float2* src_out = d.d_out;
+                    // (r may dangle after this call if the rings vector were resized; it is not: fixed size from creation)
+                    return ring_push(s, dst, src_out, n_out, GB200_ITEM_32FC, k_first, cudaMemcpyDeviceToDevice);
+                }
+        }
+    return GB200_OK;
+}
+
+extern "C" int gb200_stream_set_decimator(gb200_service* s, int src_stream, int dst_stream, uint32_t decimation, const float* taps, uint32_t n_taps)
+{
+    if (!s) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (src_stream < 0 || src_stream >= (int)s->rings.size())
+        {
+            s->set_error("gb200_stream_set_decimator: src_stream out of range");
+            return GB200_E_INVALID;
+        }
+    GbRing::Decimator& d = s->rings[src_stream].decim;
+    GB_CUDA(s, cudaStreamSynchronize(s->copy_stream));
+    if (d.d_taps) cudaFree(d.d_taps);
+    if (d.d_out) cudaFree(d.d_out);
+    d = GbRing::Decimator();
+    if (decimation == 0) return GB200_OK;
+    if (dst_stream < 0 || dst_stream >= (int)s->rings.size() || dst_stream == src_stream || !taps || n_taps == 0 || s->rings[dst_stream].decim.on)
+        {
+            s->set_error("gb200_stream_set_decimator: dst_stream must be another stream of the service without a decimator of its own, taps non-empty");
+            return GB200_E_INVALID;
+        }
+    const size_t span_min = sizeof(float2) * (size_t)decimation * (((size_t)31 * decimation + n_taps + decimation - 1) / decimation);
+    if (span_min > 96 * 1024 || (uint64_t)n_taps + decimation >= s->ring_capacity)
+        {
+            s->set_error("gb200_stream_set_decimator: taps x decimation too large for one CTA's staging buffer (96 KB) or the ring");
+            return GB200_E_UNSUPPORTED;
+        }
+    d.out_cap = (size_t)(s->ring_capacity / decimation) + 2;
+    GB_CUDA(s, cudaMalloc(&d.d_taps, sizeof(float) * n_taps));
+    GB_CUDA(s, cudaMalloc(&d.d_out, sizeof(float2) * d.out_cap));
+    GB_CUDA(s, cudaMemcpy(d.d_taps, taps, sizeof(float) * n_taps, cudaMemcpyHostToDevice));
+    d.D = decimation;
+    d.T = n_taps;
+    d.dst = dst_stream;
+    d.next_k = 0;
+    d.valid_begin = 0;
+    d.on = true;
+    // the next push starts a fresh filter run whatever the stream held before
+    GbRing& r = s->rings[src_stream];
+    if (r.any)
+        {
+            d.valid_begin = r.end;
+            d.next_k = (r.end + d.D - 1) / d.D;
+        }
+    return GB200_OK;
+}
+
+// = gr::filter::firdes::low_pass(gain, fs, fc, tw, WIN_HAMMING) (GNU Radio >= 3.7.3; not in the reference tree): windowed sinc,
+// tap count from the window's 53 dB attenuation, Hamming window gr::fft::window::hamming, taps scaled to DC gain `gain`.
+extern "C" int gb200_firdes_low_pass(double gain, double sampling_freq, double cutoff_freq, double transition_width, float* taps, uint32_t* n_taps)
+{
+    if (!taps || !n_taps || !(sampling_freq > 0.0) || !(cutoff_freq > 0.0) || cutoff_freq > sampling_freq / 2 || !(transition_width > 0.0)) return GB200_E_INVALID;
+    int ntaps = (int)(53.0 * sampling_freq / (22.0 * transition_width));
+    if ((ntaps & 1) == 0) ntaps++;
+    if ((uint32_t)ntaps > *n_taps)
+        {
+            *n_taps = (uint32_t)ntaps;
+            return GB200_E_RANGE;
+        }
+    std::vector<float> w(ntaps);
+    {
+        const float M = static_cast<float>(ntaps - 1);
+        for (int n = 0; n < ntaps; n++) w[n] = 0.54 - 0.46 * cos((2 * M_PI * n) / M);
+    }
+    const int M = (ntaps - 1) / 2;
+    const double fwT0 = 2 * M_PI * cutoff_freq / sampling_freq;
+    for (int n = -M; n <= M; n++)
+        {
+            if (n == 0)
+                taps[n + M] = fwT0 / M_PI * w[n + M];
+            else
+                taps[n + M] = sin(n * fwT0) / (n * M_PI) * w[n + M];
+        }
+    double fmax = taps[0 + M];
+    for (int n = 1; n <= M; n++) fmax += 2 * taps[n + M];
+    gain /= fmax;
+    for (int i = 0; i < ntaps; i++) taps[i] *= gain;
+    *n_taps = (uint32_t)ntaps;
+    return GB200_OK;
+}
+
+extern "C" int gb200_stream_read(gb200_service* s, int stream_id, uint64_t first_sample_index, size_t n_items, void* dst)
+{
+    if (!s || !dst) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (stream_id < 0 || stream_id >= (int)s->rings.size() || !s->rings[stream_id].d_buf)
+        {
+            s->set_error("gb200_stream_read: no such stream");
+            return GB200_E_INVALID;
+        }
+    GbRing& r = s->rings[stream_id];
+    const size_t isz = gb_item_bytes(r.item_type);
+    if (!r.any || first_sample_index < r.begin || first_sample_index + n_items > r.end)
+        {
+            s->set_error("gb200_stream_read: items not held by the ring");
+            return GB200_E_RANGE;
+        }
+    GB_CUDA(s, cudaStreamSynchronize(s->copy_stream));
+    uint64_t idx = first_sample_index;
+    size_t left = n_items;
+    char* p = (char*)dst;
+    while (left)
+        {
+            const uint64_t pos = idx % r.cap;
+            const size_t run = (size_t)std::min<uint64_t>(left, r.cap - pos);
+            GB_CUDA(s, cudaMemcpy(p, (const char*)r.d_buf + pos * isz, run * isz, cudaMemcpyDeviceToHost));
+            p += run * isz;
+            idx += run;
+            left -= run;
+        }
     return GB200_OK;
 }
 

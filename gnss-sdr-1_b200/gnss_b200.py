@@ -76,7 +76,7 @@ EXPORTS = [
     "gb200_service_create", "gb200_service_destroy", "gb200_last_error", "gb200_version", "gb200_service_cuda_stream",
     "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
     "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
-    "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum",
+    "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine",
@@ -115,6 +115,9 @@ def lib():
     L.gb200_service_kernel_timing.argtypes = [vp, i]
     L.gb200_service_kernel_stats.argtypes = [vp, i, C.POINTER(C.c_double), C.POINTER(u64)]
     L.gb200_stream_push.argtypes = [vp, i, vp, C.c_size_t, i, u64]
+    L.gb200_stream_set_decimator.argtypes = [vp, i, i, u32, vp, u32]
+    L.gb200_firdes_low_pass.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, vp, C.POINTER(u32)]
+    L.gb200_stream_read.argtypes = [vp, i, u64, C.c_size_t, vp]
     L.gb200_stream_push_device.argtypes = [vp, i, vp, C.c_size_t, i, u64]
     L.gb200_acq_create.argtypes = [vp, C.POINTER(AcqCfg), C.POINTER(vp)]
     L.gb200_acq_destroy.argtypes = [vp]
@@ -223,6 +226,17 @@ class Service:
         """inverted_spectrum of the data-type adapters: later pushes to this stream are conjugated on the device."""
         self.check(self.L.gb200_stream_set_inverted_spectrum(self.h, stream_id, int(inverted)))
 
+    def set_decimator(self, src_stream, dst_stream, decimation, taps=None):
+        """acquisition resampler (gnss_flowgraph.cc:423-476): later pushes to src_stream also feed the FIR-decimated items to dst_stream"""
+        t = np.ascontiguousarray(taps if taps is not None else [1.0], np.float32)
+        self.check(self.L.gb200_stream_set_decimator(self.h, src_stream, dst_stream, decimation, _ptr(t), len(t)))
+
+    def read(self, stream_id, first_sample_index, n_items, item_type=ITEM_32FC):
+        """items of a stream back on the host, in their wire type"""
+        out = np.zeros(n_items if item_type == ITEM_32FC else 2 * n_items, ITEM_DTYPES[item_type])
+        self.check(self.L.gb200_stream_read(self.h, stream_id, first_sample_index, n_items, _ptr(out)))
+        return out
+
     def push_ptr(self, stream_id, host_ptr, n_items, item_type, first_sample_index):
         self.check(self.L.gb200_stream_push(self.h, stream_id, C.c_void_p(host_ptr), n_items, item_type, first_sample_index))
 
@@ -291,6 +305,21 @@ class Acquisition:
         if self.h:
             self.s.L.gb200_acq_destroy(self.h)
             self.h = C.c_void_p()
+
+
+def firdes_low_pass(gain, sampling_freq, cutoff_freq, transition_width):
+    """gr::filter::firdes::low_pass(.., WIN_HAMMING) as the C ABI restates it (host arithmetic)"""
+    L = lib()
+    n = C.c_uint32(0)
+    one = np.zeros(1, np.float32)
+    rc = L.gb200_firdes_low_pass(gain, sampling_freq, cutoff_freq, transition_width, _ptr(one), C.byref(n))
+    if rc != -4:
+        raise Gb200Error(rc, "gb200_firdes_low_pass")
+    taps = np.zeros(n.value, np.float32)
+    rc = L.gb200_firdes_low_pass(gain, sampling_freq, cutoff_freq, transition_width, _ptr(taps), C.byref(n))
+    if rc:
+        raise Gb200Error(rc, "gb200_firdes_low_pass")
+    return taps
 
 
 def acq_iq_combine(ia, qa=None, ib=None, qb=None, norm=1.0):

@@ -45,6 +45,31 @@ inline float pcps_threshold_from_pfa(float pfa, unsigned doppler_max, unsigned d
     return static_cast<float>(-std::log1p(-val) / lambda);
 }
 
+// Integer decimation of the acquisition resampler (gnss_flowgraph.cc:431-437; the adapters repeat it, e.g.
+// gps_l1_ca_pcps_acquisition.cc:97-104): the largest divisor of fs_in not above fs_in / opt_acq_fs; 1 = no resampler.
+inline uint32_t acq_resampler_decimation(int64_t fs_in, uint32_t opt_acq_fs)
+{
+    if (fs_in <= static_cast<int64_t>(opt_acq_fs)) return 1;
+    uint32_t decimation = static_cast<uint32_t>(fs_in / opt_acq_fs);
+    while (fs_in % decimation > 0) decimation--;
+    return decimation;
+}
+
+// The flowgraph's resampler for one (signal, RF channel): taps = firdes::low_pass(1.0, fs, acq_fs / 2.1, acq_fs / 10, WIN_HAMMING)
+// with acq_fs = fs / decimation (gnss_flowgraph.cc:437-447), attached to the source stream.  Returns the filter latency the
+// flowgraph hands to set_resampler_latency(), (taps.size() - 1) / 2 (:476), or -1.
+inline int attach_acq_resampler(gb200_service* s, int src_stream, int dst_stream, int64_t fs_in, uint32_t decimation)
+{
+    const double acq_fs = static_cast<double>(fs_in) / static_cast<double>(decimation);
+    uint32_t n = 0;
+    std::vector<float> taps(1);
+    if (gb200_firdes_low_pass(1.0, static_cast<double>(fs_in), acq_fs / 2.1, acq_fs / 10, taps.data(), &n) != GB200_E_RANGE) return -1;
+    taps.resize(n);
+    if (gb200_firdes_low_pass(1.0, static_cast<double>(fs_in), acq_fs / 2.1, acq_fs / 10, taps.data(), &n) != GB200_OK) return -1;
+    if (gb200_stream_set_decimator(s, src_stream, dst_stream, decimation, taps.data(), n) != GB200_OK) return -1;
+    return static_cast<int>((taps.size() - 1) / 2);
+}
+
 class B200_Pcps_Acquisition
 {
 public:
@@ -99,6 +124,15 @@ public:
         state_ = state;
         if (state == 1) gb200_acq_reset(h_);
     }
+    // Acq_Conf::use_automatic_resampler / resampler_ratio (the adapter fills them, gps_l1_ca_pcps_acquisition.cc:89-112) and
+    // set_resampler_latency (pcps_acquisition.cc:232-236).  `conf` then describes the RESAMPLED stream (fs_in = resampled_fs,
+    // which is also what update_local_carrier uses, :299-302) and `stream_id` names the decimator's destination stream.
+    void set_automatic_resampler(float resampler_ratio)
+    {
+        use_automatic_resampler_ = true;
+        resampler_ratio_ = resampler_ratio;
+    }
+    void set_resampler_latency(uint32_t latency_samples) { resampler_latency_samples_ = latency_samples; }
     void reset() { set_state(1); }  // ChannelFsm::start_acquisition -> adapter reset() -> set_active(true) (:226-229)
     void stop_acquisition() { state_ = 0; }
     signed int mag() const { return static_cast<signed int>(mag_); }
@@ -122,6 +156,13 @@ public:
                 synchro_->Acq_doppler_hz = r.acq_doppler_hz;
                 synchro_->Acq_samplestamp_samples = r.acq_samplestamp;
                 synchro_->Acq_doppler_step = conf_.doppler_step;
+                if (use_automatic_resampler_)
+                    {
+                        // (:756-762, :814-820) back to the rate the tracking blocks run at
+                        synchro_->Acq_delay_samples = static_cast<double>(std::fmod(static_cast<float>(r.code_phase_index), conf_.samples_per_code)) * resampler_ratio_;
+                        synchro_->Acq_delay_samples -= static_cast<double>(resampler_latency_samples_);
+                        synchro_->Acq_samplestamp_samples = rint(static_cast<double>(r.acq_samplestamp) * resampler_ratio_);
+                    }
             }
         if (r.decision != 3) num_dwells_++;  // d_num_noncoherent_integrations_counter (:711); the step-two pass does not count
         if (r.decision == 1 || r.decision == 0)
@@ -182,6 +223,9 @@ private:
     int stream_;
     unsigned channel_ = 0;
     int state_ = 0;
+    bool use_automatic_resampler_ = false;
+    float resampler_ratio_ = 1.0f;
+    uint32_t resampler_latency_samples_ = 0;
     bool ok_ = false;
     float mag_ = 0.0f, test_statistics_ = 0.0f;
     bool dump_ = false;

@@ -169,6 +169,43 @@ int gbh_acq_search_dump(gb200_service* service, const gb200_acq_cfg* conf, int s
     return ev;
 }
 
+// ---- acquisition resampler (GNSSFlowgraph + the adapters' Acq_Conf fields) ----
+unsigned gbh_acq_resampler_decimation(long long fs_in, unsigned opt_acq_fs) { return acq_resampler_decimation(fs_in, opt_acq_fs); }
+int gbh_attach_acq_resampler(gb200_service* service, int src_stream, int dst_stream, long long fs_in, unsigned decimation)
+{
+    return attach_acq_resampler(service, src_stream, dst_stream, fs_in, decimation);
+}
+// the search of gbh_acq_search on the resampled stream `stream_id` (conf describes that stream), results scaled back as the
+// block does with use_automatic_resampler (pcps_acquisition.cc:756-762)
+int gbh_acq_search_resampled(gb200_service* service, const gb200_acq_cfg* conf, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count,
+    int max_runs, float resampler_ratio, unsigned latency_samples, double* delay_samples, double* doppler_hz, uint64_t* samplestamp, float* test_statistic)
+{
+    B200_Pcps_Acquisition acq(service, *conf, stream_id);
+    if (!acq.ok()) return -1;
+    AcqSynchro syn;
+    acq.set_gnss_synchro(&syn);
+    acq.set_automatic_resampler(resampler_ratio);
+    acq.set_resampler_latency(latency_samples);
+    acq.set_doppler_step(conf->doppler_step);
+    acq.set_threshold(conf->threshold);
+    acq.init();
+    if (!acq.set_local_code(reinterpret_cast<const std::complex<float>*>(code_iq), code_items)) return -1;
+    acq.reset();
+    int ev = 0;
+    uint64_t at = samp_count;
+    for (int k = 0; k < max_runs && ev == 0; k++)
+        {
+            gb200_acq_result r{};
+            ev = acq.run(at, &r);
+            if (ev == 0 && r.decision == 2) at += acq.consumed_samples();
+        }
+    *delay_samples = syn.Acq_delay_samples;
+    *doppler_hz = syn.Acq_doppler_hz;
+    *samplestamp = syn.Acq_samplestamp_samples;
+    *test_statistic = acq.test_statistics();
+    return ev;
+}
+
 // ---- sibling PCPS blocks (gb200_acquisition_variants.hpp): a whole attempt, one record of 8 doubles per dwell ----
 // cfg = {sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells, tong_init_val,
 //        tong_max_val, tong_max_dwells, item_type}; variant 0 = Tong, 1 = Galileo E1 8 ms.

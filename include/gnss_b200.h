@@ -95,6 +95,23 @@ int gb200_stream_set_inverted_spectrum(gb200_service* s, int stream_id, int inve
 int gb200_stream_push_device(gb200_service* s, int stream_id, const void* d_samples, size_t n_items, int item_type,
     uint64_t first_sample_index);
 
+/* Acquisition resampler of GNSSFlowgraph (src/core/receiver/gnss_flowgraph.cc:423-476, GNSS-SDR.use_acquisition_resampler):
+ * a gr::filter::fir_filter_ccf(decimation, taps) between the signal conditioner and the channel's acquisition.  Here it is a
+ * property of the source stream: every later push to `src_stream` (GB200_ITEM_32FC only, as in the adapters, e.g.
+ * gps_l1_ca_pcps_acquisition.cc:90-94) also appends y[k] = sum_j taps[j] * x[k * decimation - j] (x before the stream's
+ * first item is 0, the block's zero history) to `dst_stream` for every k whose newest input has arrived; item k of
+ * `dst_stream` is aligned with item k * decimation of `src_stream`.  The filter runs on the device right behind the copy.
+ * decimation == 0 removes it.  A discontinuity of the source restarts the filter history and the destination stream. */
+int gb200_stream_set_decimator(gb200_service* s, int src_stream, int dst_stream, uint32_t decimation, const float* taps, uint32_t n_taps);
+/* The taps the flowgraph asks GNU Radio for: gr::filter::firdes::low_pass(gain, sampling_freq, cutoff_freq, transition_width,
+ * WIN_HAMMING) -- GNU Radio (>= 3.7.3, CMakeLists.txt:398) is not part of the reference tree; this restates its published
+ * windowed-sinc design (odd tap count (int)(53 * fs / (22 * transition_width)) | 1, Hamming window, DC gain `gain`).
+ * Host arithmetic only.  `*n_taps`: in = capacity of `taps`, out = number of taps (GB200_E_RANGE if it does not fit). */
+int gb200_firdes_low_pass(double gain, double sampling_freq, double cutoff_freq, double transition_width, float* taps, uint32_t* n_taps);
+/* copies items [first_sample_index, first_sample_index + n_items) of a stream back to the host in their wire type
+ * (what a file_sink after the conditioner / resampler would record); GB200_E_RANGE if the ring no longer holds them */
+int gb200_stream_read(gb200_service* s, int stream_id, uint64_t first_sample_index, size_t n_items, void* dst);
+
 /* ------------------------------------------------------------------ acquisition --------- */
 /* = Acq_Conf (src/algorithms/acquisition/libs/acq_conf.h:39-68) + the setters' values */
 typedef struct gb200_acq_cfg

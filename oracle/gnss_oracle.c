@@ -1389,3 +1389,66 @@ int go_e5a_run(go_e5a* a, const float* in, go_e5a_result* out)
     *out = a->last;
     return 0;
 }
+
+
+/* ======================= acquisition resampler -- TEST INFRASTRUCTURE, parity unpinned (GNU Radio absent) ======================= */
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
+static double go_hamming_max_attenuation_(void) { return 53; }
+
+int go_firdes_low_pass(double gain, double sampling_freq, double cutoff_freq, double transition_width, float* taps, int capacity)
+{
+    /* firdes::compute_ntaps: (int)(attenuation * fs / (22 * transition)), made odd */
+    int ntaps = (int)(go_hamming_max_attenuation_() * sampling_freq / (22.0 * transition_width));
+    if ((ntaps & 1) == 0) ntaps++;
+    if (ntaps > capacity) return -ntaps;
+    float* w = (float*)malloc(sizeof(float) * (size_t)ntaps);
+    /* gr::fft::window::hamming: 0.54 - 0.46 cos(2 pi n / (ntaps - 1)), the divisor held in float32 */
+    float Mw = (float)(ntaps - 1);
+    for (int n = 0; n < ntaps; n++) w[n] = (float)(0.54 - 0.46 * cos((2 * M_PI * n) / Mw));
+    int M = (ntaps - 1) / 2;
+    double fwT0 = 2 * M_PI * cutoff_freq / sampling_freq;
+    for (int n = -M; n <= M; n++)
+        {
+            if (n == 0)
+                taps[n + M] = (float)(fwT0 / M_PI * w[n + M]);
+            else
+                taps[n + M] = (float)(sin(n * fwT0) / (n * M_PI) * w[n + M]);
+        }
+    /* unity gain at DC: sum of the (symmetric) taps */
+    double fmax = taps[0 + M];
+    for (int n = 1; n <= M; n++) fmax += 2 * taps[n + M];
+    gain /= fmax;
+    for (int i = 0; i < ntaps; i++) taps[i] = (float)(taps[i] * gain);
+    free(w);
+    return ntaps;
+}
+
+int go_fir_decimate(const float* in, int n_in, const float* taps, int n_taps, int D, float* out)
+{
+    int count = 0;
+    for (long long k = 0; k * D <= (long long)n_in - 1; k++)
+        {
+            float ar = 0.0f, ai = 0.0f;
+            for (int j = 0; j < n_taps; j++)
+                {
+                    const long long m = k * D - j;
+                    if (m < 0) break;
+                    ar += taps[j] * in[2 * m];
+                    ai += taps[j] * in[2 * m + 1];
+                }
+            out[2 * k] = ar;
+            out[2 * k + 1] = ai;
+            count++;
+        }
+    return count;
+}
+
+uint32_t go_acq_resampler_decimation(int64_t fs_in, uint32_t opt_acq_fs)
+{
+    if ((uint64_t)fs_in <= opt_acq_fs) return 1;
+    uint32_t decimation = (uint32_t)(fs_in / opt_acq_fs);
+    while (fs_in % decimation > 0) decimation--;
+    return decimation;
+}

@@ -188,6 +188,16 @@ int go_e5a_run(go_e5a* a, const float* in_iq, go_e5a_result* out);
 void go_e5a_caf_filter(const float* caf_i, const float* caf_q, float* caf_out, uint32_t num_bins, int caf_window_hz, uint32_t doppler_step, int both);
 const float* go_e5a_caf_vector(const go_e5a* a);  /* d_CAF_vector after the last dwell, num_bins floats (caf_window_hz > 0) */
 
+/* ---------------- acquisition resampler of GNSSFlowgraph (gnss_flowgraph.cc:423-476) ----------------
+ * gr::filter::firdes::low_pass(.., WIN_HAMMING) and gr::filter::fir_filter_ccf(decimation, taps) belong to GNU Radio
+ * (>= 3.7.3 per CMakeLists.txt:398), which is NOT in the reference tree: their published algorithms are restated here and
+ * parity for this row is UNPINNED (no reference output to check against). */
+int go_firdes_low_pass(double gain, double sampling_freq, double cutoff_freq, double transition_width, float* taps, int capacity);
+/* y[k] = sum_j taps[j] x[k D - j], x[n < 0] = 0; k = 0 .. (n_in - 1) / D; float32 accumulation in tap order. Returns the count. */
+int go_fir_decimate(const float* in_iq, int n_in, const float* taps, int n_taps, int decimation, float* out_iq);
+/* integer decimation the flowgraph / adapters pick (gnss_flowgraph.cc:431-437, gps_l1_ca_pcps_acquisition.cc:97-104) */
+uint32_t go_acq_resampler_decimation(int64_t fs_in, uint32_t opt_acq_fs);
+
 #ifdef __cplusplus
 }
 #endif

@@ -124,9 +124,33 @@ def host():
                                        C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.gbh_e5a_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, f32p, C.c_size_t, C.c_uint64, C.c_int,
                                       C.POINTER(C.c_double), C.POINTER(C.c_int), f32p]
+        L.gbh_acq_resampler_decimation.restype = C.c_uint
+        L.gbh_acq_resampler_decimation.argtypes = [C.c_longlong, C.c_uint]
+        L.gbh_attach_acq_resampler.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_uint]
+        L.gbh_acq_search_resampled.argtypes = [C.c_void_p, C.c_void_p, C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.c_float, C.c_uint,
+                                               C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_float)]
         L.gbh_caf_filter.argtypes = [f32p, C.c_void_p, f32p, C.c_uint, C.c_int, C.c_uint]
         _host = L
     return _host
+
+
+def acq_resampler_decimation(fs_in, opt_acq_fs):
+    return host().gbh_acq_resampler_decimation(fs_in, opt_acq_fs)
+
+
+def attach_acq_resampler(service, src_stream, dst_stream, fs_in, decimation):
+    """attach_acq_resampler of gb200_acquisition.hpp: the flowgraph's firdes taps + decimator on src_stream; returns the latency."""
+    return host().gbh_attach_acq_resampler(service.h, src_stream, dst_stream, fs_in, decimation)
+
+
+def acq_search_resampled(service, cfg, stream_id, code_c64, samp_count, max_runs, resampler_ratio, latency_samples):
+    """B200_Pcps_Acquisition with use_automatic_resampler: returns (event, Acq_delay_samples, Acq_doppler_hz, Acq_samplestamp_samples, test_statistic)."""
+    L = host()
+    code = np.ascontiguousarray(code_c64, np.complex64).view(np.float32)
+    d, f, st, ts = C.c_double(0), C.c_double(0), C.c_uint64(0), C.c_float(0)
+    ev = L.gbh_acq_search_resampled(service.h, C.byref(cfg), stream_id, code, len(code) // 2, samp_count, max_runs, resampler_ratio, latency_samples,
+                                    C.byref(d), C.byref(f), C.byref(st), C.byref(ts))
+    return ev, d.value, f.value, st.value, ts.value
 
 
 def caf_filter(caf_i, caf_q, caf_window_hz, doppler_step):

@@ -104,6 +104,10 @@ def oracle():
     L.go_e5a_set_local_code.argtypes = [C.c_void_p, f32p, f32p]
     L.go_e5a_restart.argtypes = [C.c_void_p]
     L.go_e5a_run.argtypes = [C.c_void_p, f32p, C.POINTER(GoE5aResult)]
+    L.go_firdes_low_pass.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, f32p, C.c_int]
+    L.go_fir_decimate.argtypes = [f32p, C.c_int, f32p, C.c_int, C.c_int, f32p]
+    L.go_acq_resampler_decimation.argtypes = [C.c_int64, C.c_uint32]
+    L.go_acq_resampler_decimation.restype = C.c_uint32
     L.go_e5a_caf_filter.argtypes = [f32p, f32p, f32p, C.c_uint32, C.c_int, C.c_uint32, C.c_int]
     L.go_e5a_caf_vector.argtypes = [C.c_void_p]
     L.go_e5a_caf_vector.restype = C.POINTER(C.c_float)
@@ -227,6 +231,25 @@ class GoE5aResult(C.Structure):
     _fields_ = [("code_phase_index", C.c_uint32), ("doppler_bin", C.c_uint32), ("doppler_hz", C.c_int32), ("mag", C.c_float),
                 ("input_power", C.c_float), ("test_statistic", C.c_float), ("decision", C.c_int), ("well_count", C.c_uint32),
                 ("acq_delay_samples", C.c_double), ("updated", C.c_int)]
+
+
+def firdes_low_pass(gain, fs, cutoff, transition):
+    """oracle restatement of gr::filter::firdes::low_pass(.., WIN_HAMMING)"""
+    L = oracle()
+    n = -L.go_firdes_low_pass(gain, fs, cutoff, transition, np.zeros(1, np.float32), 0)
+    taps = np.zeros(n, np.float32)
+    assert L.go_firdes_low_pass(gain, fs, cutoff, transition, taps, n) == n
+    return taps
+
+
+def fir_decimate(x_c64, taps, decimation):
+    """oracle restatement of gr::filter::fir_filter_ccf(decimation, taps) over a stream that starts at x[0]"""
+    x = np.ascontiguousarray(x_c64, np.complex64).view(np.float32)
+    t = np.ascontiguousarray(taps, np.float32)
+    n_in = len(x) // 2
+    out = np.zeros(2 * ((n_in - 1) // decimation + 1), np.float32)
+    n = oracle().go_fir_decimate(x, n_in, t, len(t), decimation, out)
+    return out[: 2 * n].view(np.complex64)
 
 
 def e5a_caf_filter(caf_i, caf_q, caf_window_hz, doppler_step):

@@ -234,3 +234,92 @@ def test_glonass_l1_loop_on_b200_matches_oracle_loop(service):
     assert dd.max() < 0.5 and rel.max() < 2e-3
     assert abs(got[-150:, F["carrier_doppler_hz"]].mean() - doppler) < 3.0
     assert np.abs(got[:, F["code_phase_samples"]] - ref[:, F["code_phase_samples"]]).max() < 0.01
+
+
+def test_stream_decimator_matches_oracle_fir(service):
+    """gb200_stream_set_decimator (the flowgraph's fir_filter_ccf(decimation, taps) acquisition resampler, run on the device behind
+    every push): ragged pushes (shorter than the filter, not multiples of the decimation), a discontinuity that restarts the
+    history, ring wrap-around, against the oracle's sequential float32 FIR; tolerance 2e-6 of sum|taps| * max|x|."""
+    import gnss_b200 as gb
+    import oracle_lib as ol
+
+    rng = np.random.default_rng(31)
+    taps = gb.firdes_low_pass(1.0, 4e6, 1e6 / 2.1, 1e5)
+    x = (rng.standard_normal(60000) + 1j * rng.standard_normal(60000)).astype(np.complex64)
+    service.set_decimator(0, 1, 4, taps)
+    at = 0
+    for n in (1000, 37, 3, 4099, 1, 20000, 34860):
+        service.push(0, x[at: at + n], gb.ITEM_32FC, at)
+        at += n
+    assert at == len(x)
+    want = ol.fir_decimate(x, taps, 4)
+    got = service.read(1, 0, len(want))
+    tol = 2e-6 * float(np.abs(taps).sum()) * float(np.abs(x).max())
+    assert np.abs(got - want).max() <= tol, (np.abs(got - want).max(), tol)
+    with pytest.raises(gb.Gb200Error):  # nothing beyond the newest complete output
+        service.read(1, 0, len(want) + 1)
+    # discontinuity: the filter history and the destination stream restart; item k of the destination sits at source item 4k
+    seg = (rng.standard_normal(5000) + 1j * rng.standard_normal(5000)).astype(np.complex64)
+    first = 100003
+    service.push(0, seg, gb.ITEM_32FC, first)
+    z = np.concatenate([np.zeros(3, np.complex64), seg])  # absolute index 100000 onwards, zeros before the segment
+    want = ol.fir_decimate(z, taps, 4)[1:]                # k = 25001 onwards
+    got = service.read(1, 25001, len(want))
+    assert np.abs(got - want).max() <= tol
+    with pytest.raises(gb.Gb200Error):
+        service.read(1, 25000, 1)
+    # other decimation / taps, long enough to wrap the 2^23-item ring
+    service.set_decimator(0, 1, 0)
+    t2 = rng.standard_normal(10).astype(np.float32)
+    service.set_decimator(0, 1, 3, t2)
+    big = (rng.standard_normal(9000000) + 1j * rng.standard_normal(9000000)).astype(np.complex64)
+    first = 3000000
+    for k in range(3):
+        service.push(0, big[k * 3000000:(k + 1) * 3000000], gb.ITEM_32FC, first + k * 3000000)
+    want = ol.fir_decimate(big, t2, 3)  # source starts at a multiple of 3: k0 = 1000000
+    got = service.read(1, 1000000, len(want))
+    assert np.abs(got - want).max() <= 2e-6 * float(np.abs(t2).sum()) * float(np.abs(big).max())
+    service.set_decimator(0, 1, 0)
+    # only gr_complex streams have the resampler (gps_l1_ca_pcps_acquisition.cc:90-94)
+    service.set_decimator(0, 1, 4, taps)
+    with pytest.raises(gb.Gb200Error) as e:
+        service.push(0, np.zeros(64, np.int16), gb.ITEM_16IC, 0)
+    assert e.value.code == -6
+    service.set_decimator(0, 1, 0)
+
+
+def test_acquisition_through_resampler_matches_oracle(service):
+    """GNSS-SDR.use_acquisition_resampler end to end: 16 Msps GPS L1 C/A scene -> attach_acq_resampler (firdes taps, decimation by 4)
+    -> B200_Pcps_Acquisition on the 4 Msps stream with the adapter's resampled Acq_Conf -> Gnss_Synchro scaled back by
+    resampler_ratio and the filter latency (pcps_acquisition.cc:756-762), against the oracle's FIR + pcps_acquisition restatement."""
+    import gnss_b200 as gb
+    import oracle_lib as ol
+
+    fs, dec = 16000000, 4
+    assert hl.acq_resampler_decimation(fs, 4000000) == dec
+    sats = [dict(kind="gps_l1_ca", prn=7, cn0_dbhz=50.0, doppler_hz=1300.0, delay_samples=5003.0)]
+    x = synth.make_iq(fs, 40000, sats, seed=41)
+    latency = hl.attach_acq_resampler(service, 0, 1, fs, dec)
+    taps = ol.firdes_low_pass(1.0, fs, (fs / dec) / 2.1, (fs / dec) / 10)
+    assert latency == (len(taps) - 1) // 2
+    service.push(0, x, gb.ITEM_32FC, 0)
+    xd = ol.fir_decimate(x, taps, dec)
+    rfs = fs // dec
+    code = np.zeros(2 * 4000, np.float32)
+    ol.oracle().go_gps_l1_ca_code_sampled(code, 7, rfs, 0)
+    o = ol.OracleAcq(sampled_ms=1, ms_per_code=1, samples_per_chip=4, doppler_max=5000, doppler_step=250, fs_in=rfs, samples_per_ms=4000.0,
+                     samples_per_code=4000.0, threshold=1e-9)
+    o.set_local_code(code.view(np.complex64))
+    ro = o.run(xd[2000:6000], 6000)  # the block's sample counter stands behind the consumed block
+    cfg = gb.AcqCfg(sampled_ms=1, ms_per_code=1, samples_per_chip=4, max_dwells=1, doppler_max=5000, doppler_step=250, num_doppler_bins_step2=4,
+                    doppler_step2=125.0, fs_in=rfs, samples_per_ms=4000.0, samples_per_code=4000.0, bit_transition_flag=0, use_CFAR_algorithm_flag=1,
+                    make_2_steps=0, item_type=gb.ITEM_32FC, threshold=1e-9, freq_offset_hz=0)
+    ev, delay, dop, stamp, stat = hl.acq_search_resampled(service, cfg, 1, code.view(np.complex64), 2000, 1, float(dec), latency)
+    assert ev == 1 and dop == float(ro.doppler_hz) == 1250.0
+    want_delay = float(np.fmod(np.float32(ro.code_phase_index), np.float32(4000.0))) * dec - latency
+    assert delay == want_delay and stamp == int(np.rint(float(ro.acq_samplestamp) * dec))
+    assert abs(stat - ro.test_statistic) <= 1e-4 * ro.test_statistic
+    # and it is the right answer: the peak sits where the scene put the code (filter delay removed, +-2 resampled samples)
+    assert abs((delay - (5003.0 - 2000 * dec)) % 16000) <= 2 * dec or abs((delay - (5003.0 - 2000 * dec)) % 16000 - 16000) <= 2 * dec
+    service.set_decimator(0, 1, 0)
+    o.close()

@@ -280,3 +280,30 @@ def test_caf_filter_matches_oracle_arithmetic():
             got = hl.caf_filter(vi, q, window, step)
             want = ol.e5a_caf_filter(vi, q, window, step)
             assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (bins, window, step, q is None)
+
+
+def test_acq_resampler_design_matches_oracle_restatement():
+    """The flowgraph's acquisition resampler design (gnss_flowgraph.cc:431-447): the decimation rule and the firdes low-pass taps the
+    C ABI produces against the oracle's restatement (bit for bit; GNU Radio itself is not in the tree, parity unpinned), plus
+    what any correct design must show: odd symmetric taps, unit DC gain, > 45 dB rejection past cutoff + transition."""
+    import gnss_b200 as gb
+    import oracle_lib as ol
+
+    L = ol.oracle()
+    for fs, opt, want in ((4000000, 1000000, 4), (16000000, 1000000, 16), (25000000, 10000000, 2), (30000000, 10000000, 3), (6625000, 2000000, 2),
+                          (12000000, 2000000, 6), (1000000, 1000000, 1), (8000000, 3000000, 2), (7000001, 2000000, 1), (500000, 1000000, 1)):
+        assert hl.acq_resampler_decimation(fs, opt) == L.go_acq_resampler_decimation(fs, opt) == want, (fs, opt)
+        assert fs % want == 0 and want <= max(1, fs // opt)
+    for fs, dec in ((4e6, 4), (16e6, 4), (12e6, 6), (30e6, 3)):
+        acq_fs = fs / dec
+        got = gb.firdes_low_pass(1.0, fs, acq_fs / 2.1, acq_fs / 10)
+        want = ol.firdes_low_pass(1.0, fs, acq_fs / 2.1, acq_fs / 10)
+        assert len(got) == len(want) and len(got) % 2 == 1 and np.array_equal(got.view(np.uint32), want.view(np.uint32))
+        assert len(got) == (int(53 * fs / (22 * acq_fs / 10)) | 1)
+        assert np.array_equal(got, got[::-1]) and abs(float(got.astype(np.float64).sum()) - 1.0) < 1e-6
+        h = np.abs(np.fft.rfft(got.astype(np.float64), 1 << 16))
+        f = np.fft.rfftfreq(1 << 16, 1.0 / fs)
+        assert 20 * np.log10(h[f > acq_fs / 2.1 + acq_fs / 10].max()) < -45.0
+        assert abs(20 * np.log10(h[f < acq_fs / 2.1 - acq_fs / 10].min())) < 0.1
+    # capacity protocol of the C entry point
+    assert len(gb.firdes_low_pass(2.0, 4e6, 4e5, 2e5)) == (int(53 * 4e6 / (22 * 2e5)) | 1)
