@@ -1448,6 +1448,8 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             const int lanes = s->kt.enabled ? 1 : lanes_cfg;
             const size_t l2_budget = l2_total / (size_t)lanes;
             int chunkT = (int)std::max<size_t>(1, l2_budget / (sizeof(float2) * (size_t)N));
+            static const int chunk_override = getenv("GB200_ACQ_CHUNK_T") ? atoi(getenv("GB200_ACQ_CHUNK_T")) : 0;
+            if (chunk_override > 0) chunkT = chunk_override;
             chunkT = std::min(chunkT, T);
             const int tiles = (plan.N2 + plan.inv_tile1 - 1) / plan.inv_tile1;
             void* d_rows[4] = {nullptr, nullptr, nullptr, nullptr};
