@@ -1,5 +1,6 @@
 // Inverse side of the PCPS acquisition search (x conj(code DFT), inverse DFT, |.|^2, arg-max), once per (PRN, Doppler bin).
 #include "acq_dif.cuh"
+#include <algorithm>
 
 namespace
 {
@@ -154,22 +155,27 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
 // ---------------------------------------------------------------------------------------------------------------
 // Fast path: both sub-lengths compile-time (GbDif), in-place DIF tiles, first/last pass fused with global I/O.
 
-// rows: spectra x code spectrum -> inverse DFT over k2 -> x W_N^+(k1 n2) -> rowbuf[t][k1][n2]
-template <int LOGT, int NT, int OCC, class DROW, int N1>
-__global__ void __launch_bounds__(NT, OCC)
-    gb_acq_inv_row_dif(PlanDev pl, GbAcqInvParams p)
+// rows: spectra x code spectrum -> inverse DFT over k2 -> x W_N^+(k1 n2) -> dst[k1][n2] (one transform's row tile r0 .. r0+TILE)
+__device__ __forceinline__ int gb_ld_poll(const int* p);
+
+// `dep` / `need` (fused kernel only): a completion counter that must have reached `need` before this tile may STORE -- the
+// slot of the row-buffer ring it overwrites.  Thread 0 reads it when the tile starts and looks at the value only after the
+// first pass, so the round trip hides behind the tables and the first butterflies.
+template <int LOGT, int NT, class DROW, int N1>
+__device__ __forceinline__ void gb_inv_row_tile(float2* smem, const PlanDev& pl, const GbAcqInvParams& p, int r0, int t, float2* __restrict__ dst_transform,
+    const int* dep = nullptr, int need = 0)
 {
+    int dep_seen = need;
+    if (dep && threadIdx.x == 0) dep_seen = gb_ld_poll(dep);
     constexpr int M = DROW::kM, TILE = 1 << LOGT, N = N1 * M;
     constexpr int RL = DROW::kLastR, NIL = DROW::kLastNI;
     using L = GbTile<LOGT, NT>;
-    extern __shared__ __align__(16) float2 smem[];
     constexpr int IL = 8, IH = (NIL + IL - 1) / IL;  // last-pass item i = IL * ih + il
     float2* buf = smem;
     float2* tw = buf + L::size(M);
     float2* step = tw + M;          // [TILE]      W_N^(k1 NIL): ratio between consecutive outputs of one item
     float2* tlo = step + TILE;      // [TILE][IL]  W_N^(k1 il)
     float2* thi = tlo + TILE * IL;  // [TILE][IH]  W_N^(k1 IL ih)      (all forward sign; k1 = r0 + b)
-    const int r0 = blockIdx.x * TILE;
     const int nb = min(TILE, N1 - r0);
     for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
     for (int q = threadIdx.x; q < TILE * (1 + IL + IH); q += NT)
@@ -185,15 +191,16 @@ __global__ void __launch_bounds__(NT, OCC)
             else
                 thi[b * IH + c - 1 - IL] = w;
         }
-    const int t = p.first_transform + blockIdx.y;
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
     const float2* xs = p.spectra + (size_t)bin * N + (size_t)r0 * M;
     const float2* cs = p.code_fft[handle] + (size_t)r0 * M;
     dif_first<+1, L, true, M, DROW::kFirstR>(buf, pl.tw, [&](int b, int m) {
         return b < nb ? cmul(__ldg(xs + b * M + m), __ldg(cs + b * M + m)) : make_float2(0.f, 0.f);
     });
+    if (dep && threadIdx.x == 0 && dep_seen < need)
+        while (gb_ld_poll(dep) < need) __nanosleep(64);
     __syncthreads();
-    float2* dst = p.rowbuf + (size_t)blockIdx.y * N + (size_t)r0 * M;
+    float2* dst = dst_transform + (size_t)r0 * M;
     DROW::template run_rest<+1, L, true>(buf, tw, [&](int b, int i, const float2* v) {
         if (b >= nb) return;
         float2 w = cmul(tlo[b * IL + (i & (IL - 1))], thi[b * IH + (i / IL)]);  // W_N^(k1 i)
@@ -208,28 +215,47 @@ __global__ void __launch_bounds__(NT, OCC)
     });
 }
 
+template <int LOGT, int NT, int OCC, class DROW, int N1>
+__global__ void __launch_bounds__(NT, OCC)
+    gb_acq_inv_row_dif(PlanDev pl, GbAcqInvParams p)
+{
+    extern __shared__ __align__(16) float2 smem[];
+    constexpr int N = N1 * DROW::kM;
+    gb_inv_row_tile<LOGT, NT, DROW, N1>(smem, pl, p, blockIdx.x << LOGT, p.first_transform + blockIdx.y, p.rowbuf + (size_t)blockIdx.y * N);
+}
+
+// columns of one transform's tile c0 .. c0+TILE: src[k1][n2] -> inverse DFT over k1 -> |y|^2 -> arg-max partial / grid.
 // MODE 0: arg-max over the whole row (keep_offset == 0, keep_len == N: the common single-dwell CFAR search);
 // MODE 1: arg-max over a kept window (bit transition); MODE 2: magnitude grid written / accumulated.
-template <int LOGT, int NT, int OCC, class DCOL, int N2, int MODE>
-__global__ void __launch_bounds__(NT, OCC)
-    gb_acq_inv_col_dif(PlanDev pl, GbAcqInvParams p)
+// COHERENT: the source was written earlier in the SAME launch by other CTAs (fused kernel): ld.global.cg (L2) instead of
+// the read-only path, see gb_ld_poll.
+template <int LOGT, int NT, class DCOL, int N2, int MODE, bool COHERENT>
+__device__ __forceinline__ void gb_inv_col_tile(float2* smem, float* s_mag, unsigned* s_idx, const PlanDev& pl, const GbAcqInvParams& p, int tile, int n_tiles, int t,
+    const float2* __restrict__ src_transform, const int* dep = nullptr, int need = 0)
 {
-    constexpr int M = DCOL::kM, TILE = 1 << LOGT, N = N2 * M;
+    constexpr int M = DCOL::kM, TILE = 1 << LOGT;
     constexpr int RL = DCOL::kLastR, NIL = DCOL::kLastNI;
     using L = GbTile<LOGT, NT>;
-    extern __shared__ __align__(16) float2 smem[];
-    __shared__ float s_mag[NT / 32];
-    __shared__ unsigned s_idx[NT / 32];
     float2* buf = smem;
     float2* tw = buf + L::size(M);
-    const int c0 = blockIdx.x * TILE;
+    const int c0 = tile * TILE;
+    // `dep` / `need` (fused kernel only): the transform's row tiles must all have signalled before its row buffer is read;
+    // the counter is read together with the twiddle table, one round trip for both
+    int dep_seen = need;
+    if (dep && threadIdx.x == 0) dep_seen = gb_ld_poll(dep);
     for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
-    const float2* src = p.rowbuf + (size_t)blockIdx.y * N + c0;
+    if (dep)
+        {
+            if (threadIdx.x == 0 && dep_seen < need)
+                while (gb_ld_poll(dep) < need) __nanosleep(64);
+            __syncthreads();
+        }
+    const float2* src = src_transform + c0;
     dif_first<+1, L, false, M, DCOL::kFirstR>(buf, pl.tw, [&](int b, int m) {
-        return ((N2 % TILE) == 0 || c0 + b < N2) ? __ldg(src + m * N2 + b) : make_float2(0.f, 0.f);
+        if (!((N2 % TILE) == 0 || c0 + b < N2)) return make_float2(0.f, 0.f);
+        return COHERENT ? __ldcg(src + m * N2 + b) : __ldg(src + m * N2 + b);
     });
     __syncthreads();
-    const int t = p.first_transform + blockIdx.y;
     const int handle = t / p.n_bins, bin = t - handle * p.n_bins;
     float* grid = MODE == 2 ? p.grid[handle] + (size_t)bin * p.keep_len : nullptr;
     float* tmp = (MODE == 2 && p.accumulate && p.tmpbuf && p.tmpbuf[handle] && bin == p.n_bins - 1) ? p.tmpbuf[handle] : nullptr;
@@ -286,19 +312,116 @@ __global__ void __launch_bounds__(NT, OCC)
                     s_idx[warp] = best_i;
                 }
             __syncthreads();
-            if (threadIdx.x != 0) return;
-            for (int k = 1; k < NT / 32; k++)
-                if (peak_better(s_mag[k], s_idx[k], best, best_i))
-                    {
-                        best = s_mag[k];
-                        best_i = s_idx[k];
-                    }
-            GbPeak pk;
-            pk.mag = best;
-            pk.idx = best_i;
-            pk.bin = (unsigned)bin;
-            pk.pad_ = 0;
-            p.partial[(size_t)t * gridDim.x + blockIdx.x] = pk;
+            if (threadIdx.x == 0)
+                {
+                    for (int k = 1; k < NT / 32; k++)
+                        if (peak_better(s_mag[k], s_idx[k], best, best_i))
+                            {
+                                best = s_mag[k];
+                                best_i = s_idx[k];
+                            }
+                    GbPeak pk;
+                    pk.mag = best;
+                    pk.idx = best_i;
+                    pk.bin = (unsigned)bin;
+                    pk.pad_ = 0;
+                    p.partial[(size_t)t * n_tiles + tile] = pk;
+                }
+        }
+}
+
+template <int LOGT, int NT, int OCC, class DCOL, int N2, int MODE>
+__global__ void __launch_bounds__(NT, OCC)
+    gb_acq_inv_col_dif(PlanDev pl, GbAcqInvParams p)
+{
+    extern __shared__ __align__(16) float2 smem[];
+    __shared__ float s_mag[NT / 32];
+    __shared__ unsigned s_idx[NT / 32];
+    constexpr int N = N2 * DCOL::kM;
+    gb_inv_col_tile<LOGT, NT, DCOL, N2, MODE, false>(smem, s_mag, s_idx, pl, p, blockIdx.x, gridDim.x, p.first_transform + blockIdx.y, p.rowbuf + (size_t)blockIdx.y * N);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// One persistent launch for the whole inverse side of a dwell (opt-in: GB200_ACQ_FUSED=1; measured 0.483 ms against the
+// two-lane pipeline's ~0.49 ms at C2, profiles/r01_acq_fused_persistent.txt -- parity-tested, not yet faster, kept as the
+// base of the next round's work).  Every launch of the two kernels above pays about one
+// extra wave of fill and drain (profiles/r01_acq_chunk_sweep.txt) and the L2 budget keeps a launch at ~3 waves; here the
+// grid is as many CTAs as fit on the device and never drains: CTAs pull tile tasks from a counter in the order
+//   step s = 0, 1, ...:  the row tiles of transform s, then the column tiles of transform s - lag,
+// a column tile waits until its transform's row tiles have all signalled (release / acquire on a per-transform counter),
+// and a row tile of transform t waits for the column tiles of transform t - ring before it overwrites their slot of the
+// row-buffer ring (which stays L2-resident: ring x N x 8 B).  A task only ever waits for tasks pulled before it, so the
+// queue cannot deadlock whatever part of the grid is resident.
+struct GbFusedCtl
+{
+    unsigned next_task;
+    unsigned pad_[3];
+    // followed by int row_done[T], col_done[T]
+};
+
+// Polling load of a completion counter.  Deliberately NOT ld.acquire.gpu: that compiles to LDG.STRONG.GPU + CCTL.IVALL, and
+// invalidating the SM's whole L1 at the head of every task throws away the twiddle and code-spectrum lines every CTA on the
+// SM keeps hitting.  The only data that needs coherence is the row-buffer ring, and that is read with ld.global.cg (L2, where
+// the producer's MEMBAR.GPU + REDG made it visible before the counter moved); the loads are issued behind the poll's branch
+// and a CTA barrier.
+__device__ __forceinline__ int gb_ld_poll(const int* p)
+{
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void gb_red_release_inc(int* p)
+{
+    asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p) : "memory");
+}
+
+template <int LT1, int LT2, int NT, int OCC, class D1, class D2, int MODE>
+__global__ void __launch_bounds__(NT, OCC)
+    gb_acq_inv_fused(PlanDev plr, PlanDev plc, GbAcqInvParams p, GbFusedCtl* ctl, int lag, int ring)
+{
+    extern __shared__ __align__(16) float2 smem[];
+    __shared__ float s_mag[NT / 32];
+    __shared__ unsigned s_idx[NT / 32];
+    __shared__ unsigned s_task;
+    constexpr int N = D1::kM * D2::kM;
+    constexpr int TR = (D1::kM + (1 << LT2) - 1) >> LT2;  // row tiles per transform (rows of length N2, N1 of them)
+    constexpr int TC = (D2::kM + (1 << LT1) - 1) >> LT1;  // column tiles per transform
+    const int T = p.n_transforms;
+    int* row_done = (int*)(ctl + 1);
+    int* col_done = row_done + T;
+    const unsigned total = (unsigned)(T + lag) * (unsigned)(TR + TC);
+    unsigned pulled = 0;  // thread 0: the task id pulled one task ahead, so the atomic's round trip hides behind a tile
+    if (threadIdx.x == 0) pulled = atomicAdd(&ctl->next_task, 1u);
+    for (;;)
+        {
+            __syncthreads();  // everyone is done with s_task and with the tile of the previous task
+            if (threadIdx.x == 0)
+                {
+                    s_task = pulled;
+                    if (pulled < total) pulled = atomicAdd(&ctl->next_task, 1u);
+                }
+            __syncthreads();
+            const unsigned u = s_task;
+            if (u >= total) break;
+            const int step = (int)(u / (unsigned)(TR + TC)), v = (int)(u - (unsigned)step * (unsigned)(TR + TC));
+            if (v < TR)
+                {
+                    const int t = step;
+                    if (t >= T) continue;
+                    gb_inv_row_tile<LT2, NT, D2, D1::kM>(smem, plr, p, v << LT2, p.first_transform + t, p.rowbuf + (size_t)(t % ring) * N,
+                        t >= ring ? col_done + t - ring : nullptr, TC);
+                    __syncthreads();
+                    if (threadIdx.x == 0) gb_red_release_inc(row_done + t);
+                }
+            else
+                {
+                    const int t = step - lag;
+                    if (t < 0 || t >= T) continue;
+                    gb_inv_col_tile<LT1, NT, D1, D2::kM, MODE, true>(smem, s_mag, s_idx, plc, p, v - TR, TC, p.first_transform + t, p.rowbuf + (size_t)(t % ring) * N,
+                        row_done + t, TR);
+                    __syncthreads();
+                    if (threadIdx.x == 0) gb_red_release_inc(col_done + t);
+                }
         }
 }
 
@@ -389,6 +512,44 @@ bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2)
         *tile1 = 1 << decltype(c1)::LOGT;
         *tile2 = 1 << decltype(c2)::LOGT;
     });
+}
+
+size_t gb_acq_fused_ctl_bytes(int n_transforms) { return sizeof(GbFusedCtl) + 2 * sizeof(int) * (size_t)n_transforms; }
+
+// The whole inverse side of a dwell in one persistent launch (p covers ALL transforms; p.rowbuf holds `ring` transforms).
+// cudaErrorNotSupported: no such kernel for this plan / mode -- the caller falls back to gb_acq_inverse per chunk.
+cudaError_t gb_acq_inverse_fused(const GbFftPlan& plan, const GbAcqInvParams& p, void* d_ctl, int lag, int ring, int sm_count, cudaStream_t st, int* launches, void* kt)
+{
+    if (!plan.inv_fast || p.grid || !(p.keep_offset == 0 && p.keep_len == plan.N)) return cudaErrorNotSupported;
+    cudaError_t e = cudaErrorNotSupported;
+    const PlanDev pdr = make_plan_dev(plan, false), pdc = make_plan_dev(plan, true);
+    gb_with_dif_pair(plan.N1, plan.N2, plan.inv_variant, [&](auto d1, auto d2, auto c1, auto c2) {
+        using D1 = decltype(d1);
+        using D2 = decltype(d2);
+        using C1 = decltype(c1);
+        using C2 = decltype(c2);
+        if constexpr (C1::NT == C2::NT)
+            {
+                constexpr int LT1 = C1::LOGT, LT2 = C2::LOGT, NT = C1::NT, OCC = C1::OCC < C2::OCC ? C1::OCC : C2::OCC;
+                auto k = gb_acq_inv_fused<LT1, LT2, NT, OCC, D1, D2, 0>;
+                const size_t smr = (GbTile<LT2, NT>::size(D2::kM) + D2::kM + (1 << LT2) * (1 + 8 + (D2::kLastNI + 7) / 8)) * sizeof(float2);
+                const size_t smc = (GbTile<LT1, NT>::size(D1::kM) + D1::kM) * sizeof(float2);
+                const size_t sm = smr > smc ? smr : smc;
+                if ((e = set_smem(k, sm)) != cudaSuccess) return;
+                int per_sm = 0;
+                if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, NT, sm)) != cudaSuccess) return;
+                constexpr int TR = (D1::kM + (1 << LT2) - 1) >> LT2, TC = (D2::kM + (1 << LT1) - 1) >> LT1;
+                const long long tasks = (long long)(p.n_transforms + lag) * (TR + TC);
+                const int grid = (int)std::min<long long>(tasks, (long long)std::max(1, per_sm) * sm_count);
+                if ((e = cudaMemsetAsync(d_ctl, 0, gb_acq_fused_ctl_bytes(p.n_transforms), st)) != cudaSuccess) return;
+                if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_INV_ROW);
+                k<<<grid, NT, sm, st>>>(pdr, pdc, p, (GbFusedCtl*)d_ctl, lag, ring);
+                if (kt) gb_kt_end(kt);
+                e = cudaGetLastError();
+                if (e == cudaSuccess && launches) (*launches)++;
+            }
+    });
+    return e;
 }
 
 cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt)

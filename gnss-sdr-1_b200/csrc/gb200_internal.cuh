@@ -192,6 +192,8 @@ void gb_kt_begin(void* ctx, int kernel_class);
 void gb_kt_end(void* ctx);
 cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt);
 cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt);
+size_t gb_acq_fused_ctl_bytes(int n_transforms);
+cudaError_t gb_acq_inverse_fused(const GbFftPlan& plan, const GbAcqInvParams& p, void* d_ctl, int lag, int ring, int sm_count, cudaStream_t st, int* launches, void* kt);
 bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2);
 bool gb_acq_preferred_split(int N, int avoid_n1, int* n1, int* n2);  // a split of N that has the fast inverse kernels  // true when the pair has the fast inverse kernels
 cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches);

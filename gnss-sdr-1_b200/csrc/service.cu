@@ -135,8 +135,8 @@ struct gb200_service
     std::string error = "no error";
     std::recursive_mutex mu;
     // scratch pools (grown on demand, reused)
-    void* d_scratch[16] = {};
-    size_t scratch_bytes[16] = {};
+    void* d_scratch[20] = {};
+    size_t scratch_bytes[20] = {};
     void* h16 = nullptr;  // pinned staging of the int16 correlator (work items in, results out)
     size_t h16_bytes = 0;
     void* h_pinned = nullptr;
@@ -272,7 +272,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
             if (kv.second.d_twN) cudaFree(kv.second.d_twN);
             if (kv.second.d_twNhi) cudaFree(kv.second.d_twNhi);
         }
-    for (int i = 0; i < 16; i++)
+    for (int i = 0; i < 20; i++)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
     if (s->h16) cudaFreeHost(s->h16);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
@@ -1460,7 +1460,42 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             for (int k = 1; k < lanes; k++)
                 if ((rc = s->scratch(row_slots[k], sizeof(float2) * (size_t)N * chunkT, &d_rows[k]))) return rc;
             if ((rc = s->scratch(3, sizeof(GbPeak) * (size_t)T * tiles, &d_part))) return rc;
-            const bool fork = lanes > 1 && T > chunkT;
+            // Opt-in (GB200_ACQ_FUSED=1): one persistent launch for the whole inverse side when there is a kernel for this plan
+            // and mode (plain arg-max search); otherwise, and by default, chunks of transforms on the lanes below.
+            static const int fused_cfg = getenv("GB200_ACQ_FUSED") ? atoi(getenv("GB200_ACQ_FUSED")) : 0;
+            static const int fused_lag = getenv("GB200_ACQ_FUSED_LAG") ? std::max(1, atoi(getenv("GB200_ACQ_FUSED_LAG"))) : 80;
+            static const int fused_ring = getenv("GB200_ACQ_FUSED_RING") ? std::max(2, atoi(getenv("GB200_ACQ_FUSED_RING"))) : 176;
+            bool fused_done = false;
+            if (fused_cfg && !g.grid)
+                {
+                    const int ring = std::max(2, std::min(fused_ring, T));
+                    const int lag = std::min(fused_lag, ring - 1);
+                    void *d_ring, *d_ctl;
+                    if ((rc = s->scratch(17, sizeof(float2) * (size_t)N * ring, &d_ring))) return rc;
+                    if ((rc = s->scratch(16, std::max<size_t>(gb_acq_fused_ctl_bytes(T), 16), &d_ctl))) return rc;
+                    GbAcqInvParams ip;
+                    ip.spectra = (const float2*)d_spec;
+                    ip.code_fft = (const float2* const*)((char*)d_up + g.off_code);
+                    ip.rowbuf = (float2*)d_ring;
+                    ip.n_bins = bins;
+                    ip.first_transform = 0;
+                    ip.n_transforms = T;
+                    ip.keep_offset = a0->c.bit_transition_flag ? N / 2 : 0;
+                    ip.keep_len = (int)a0->eff;
+                    ip.grid = nullptr;
+                    ip.accumulate = 0;
+                    ip.partial = (GbPeak*)d_part;
+                    ip.tmpbuf = nullptr;
+                    ip.scale = nullptr;
+                    cudaError_t fe = gb_acq_inverse_fused(plan, ip, d_ctl, lag, ring, s->sm_count, s->stream, &l, s);
+                    if (fe == cudaSuccess)
+                        fused_done = true;
+                    else if (fe != cudaErrorNotSupported)
+                        GB_CUDA(s, fe);
+                    else
+                        (void)cudaGetLastError();
+                }
+            const bool fork = !fused_done && lanes > 1 && T > chunkT;
             cudaStream_t lane_stream[4] = {s->stream, s->stream2, s->stream34[0], s->stream34[1]};
             cudaEvent_t lane_join[4] = {nullptr, s->ev_join, s->ev_join34[0], s->ev_join34[1]};
             if (fork)
@@ -1469,7 +1504,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     for (int k = 1; k < lanes; k++) GB_CUDA(s, cudaStreamWaitEvent(lane_stream[k], s->ev_fork, 0));
                 }
             int lane = 0;
-            for (int t0 = 0; t0 < T; t0 += chunkT, lane = (lane + 1) % lanes)
+            for (int t0 = fused_done ? T : 0; t0 < T; t0 += chunkT, lane = (lane + 1) % lanes)
                 {
                     const int ln = fork ? lane : 0;
                     GbAcqInvParams ip;

@@ -4,6 +4,8 @@ Bar: code_phase_index, doppler bin / Hz and decision EQUAL to the
 the float32-DFT oracle and the float64-DFT oracle agree (all inputs here carry a signal or are checked for
 that); test_statistic, input_power, peak_mag within 1e-4 relative.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -421,3 +423,19 @@ def test_iq_combine_records_and_error_paths(service):
     assert rec[2].picked & 1 and rec[2].indext % spm == 777
     for a in hs:
         a.close()
+
+
+def test_fused_persistent_inverse_matches_default_path():
+    """GB200_ACQ_FUSED=1 (one persistent launch with a device-side tile queue instead of two kernels per chunk) is read once per
+    process, so a child process runs the batch-search parity tests of this file under it; they compare with the oracle exactly
+    as the default path does."""
+    import subprocess
+    import sys as _sys
+
+    env = dict(os.environ, GB200_ACQ_FUSED="1", GB200_ACQ_FUSED_LAG="3", GB200_ACQ_FUSED_RING="5")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([_sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_acquisition.py"), "-m", "gpu", "-x", "-q", "-k",
+                        "not fused and (fixture or batch or fast_inverse or ties or odd_lengths or zero_padded or bin_range)"], env=env, capture_output=True, text=True,
+                       timeout=240)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
