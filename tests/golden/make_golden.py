@@ -166,7 +166,7 @@ def make_trk16():
 
 
 if __name__ == "__main__":
-    for f in ("GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat", "Galileo_E1_ID_1_Fs_4Msps_8ms.dat"):
+    for f in ("GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat", "Galileo_E1_ID_1_Fs_4Msps_8ms.dat", "GSoC_CTTC_capture_2012_07_26_4Msps_4ms.dat"):
         src = os.path.join("/root/reference/src/tests/signal_samples", f)
         if os.path.exists(src):
             shutil.copyfile(src, os.path.join(HERE, f))
