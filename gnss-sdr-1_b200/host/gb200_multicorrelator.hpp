@@ -4,6 +4,7 @@
 // service's device ring and a correlation names them by absolute sample index.
 #pragma once
 #include <complex>
+#include <vector>
 #include <cstdint>
 
 #include "../../include/gnss_b200.h"
@@ -87,6 +88,7 @@ namespace gb200
 class B200_Multicorrelator
 {
 public:
+    using out_t = std::complex<float>;
     B200_Multicorrelator() = default;
     ~B200_Multicorrelator() { free(); }
     B200_Multicorrelator(const B200_Multicorrelator&) = delete;
@@ -121,6 +123,70 @@ public:
                    signal_length_samples, reinterpret_cast<float*>(corr_out)) == GB200_OK;
     }
     bool free()  // (:129-141)
+    {
+        if (h_) gb200_trk_destroy(h_);
+        h_ = nullptr;
+        return true;
+    }
+
+private:
+    gb200_service* s_ = nullptr;
+    gb200_trk* h_ = nullptr;
+    int stream_ = 0, n_ = 0, max_len_ = 0;
+};
+
+// = Cpu_Multicorrelator_16sc (src/algorithms/tracking/libs/cpu_multicorrelator_16sc.h:47-72): lv_16sc_t samples (a
+// GB200_ITEM_16IC stream), lv_16sc_t local code, lv_16sc_t outputs -- bit-exact against the reference's generic kernels.
+class B200_Multicorrelator_16sc
+{
+public:
+    using out_t = std::complex<int16_t>;
+    B200_Multicorrelator_16sc() = default;
+    ~B200_Multicorrelator_16sc() { free(); }
+    B200_Multicorrelator_16sc(const B200_Multicorrelator_16sc&) = delete;
+    B200_Multicorrelator_16sc& operator=(const B200_Multicorrelator_16sc&) = delete;
+    // = init (cpu_multicorrelator_16sc.cc:49-66)
+    bool init(gb200_service* service, int stream_id, int max_signal_length_samples, int n_correlators)
+    {
+        free();
+        s_ = service;
+        stream_ = stream_id;
+        n_ = n_correlators;
+        max_len_ = max_signal_length_samples;
+        gb200_trk_cfg c{};
+        c.n_taps = n_correlators;
+        c.max_code_len = 2 * 10230;
+        c.code_kind = GB200_CODE_16SC;
+        c.item_type = GB200_ITEM_16IC;
+        return gb200_trk_create(s_, &c, &h_) == GB200_OK;
+    }
+    // The trackers hand over a gr_complex code and convert it first (volk_gnsssdr_32fc_convert_16ic, e.g.
+    // gps_l1_ca_dll_pll_c_aid_tracking_sc.cc:252-255): clamp to the int16 range, round to nearest even (rintf)
+    bool set_local_code_and_taps(int code_length_chips, const std::complex<float>* local_code_in, const float* shifts_chips, int n_taps)
+    {
+        if (!h_ || n_taps != n_) return false;
+        std::vector<int16_t> c16(2 * static_cast<size_t>(code_length_chips));
+        const float* f = reinterpret_cast<const float*>(local_code_in);
+        for (size_t i = 0; i < c16.size(); i++)
+            {
+                float aux = f[i];
+                if (aux > 32767.0f)
+                    aux = 32767.0f;
+                else if (aux < -32768.0f)
+                    aux = -32768.0f;
+                c16[i] = static_cast<int16_t>(rintf(aux));
+            }
+        return gb200_trk_set_local_code_and_taps(h_, c16.data(), code_length_chips, shifts_chips, n_taps) == GB200_OK;
+    }
+    // = set_input_output_vectors + Carrier_wipeoff_multicorrelator_resampler (:78-105)
+    bool correlate(uint64_t first_sample, float rem_carrier_phase_in_rad, float phase_step_rad, float rem_code_phase_chips, float code_phase_step_chips,
+        int signal_length_samples, out_t* corr_out)
+    {
+        if (!h_ || signal_length_samples > max_len_) return false;
+        return gb200_trk_correlate_16sc(h_, stream_, first_sample, rem_carrier_phase_in_rad, phase_step_rad, rem_code_phase_chips, code_phase_step_chips,
+                   signal_length_samples, reinterpret_cast<int16_t*>(corr_out)) == GB200_OK;
+    }
+    bool free()
     {
         if (h_) gb200_trk_destroy(h_);
         h_ = nullptr;

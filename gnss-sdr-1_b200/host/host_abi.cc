@@ -5,6 +5,7 @@
 
 #include "gb200_acquisition.hpp"
 #include "gb200_acquisition_variants.hpp"
+#include "gb200_c_aid_tracking.hpp"
 #include "gb200_glonass_tracking.hpp"
 #include "gb200_host_flat.h"
 #include "gb200_multicorrelator.hpp"
@@ -369,6 +370,72 @@ void gbh_glo_close(void* hv)
     auto* h = static_cast<gbh_glo*>(hv);
     if (!h) return;
     delete h->loop;
+    delete h;
+}
+
+// ---- carrier-aided GPS L1 C/A trackers (gb200_c_aid_tracking.hpp): variant 0 = _cc on B200_Multicorrelator (32fc stream),
+//      variant 1 = _sc on B200_Multicorrelator_16sc (16ic stream) ----
+struct gbh_caid
+{
+    int variant = 0;
+    B200_Multicorrelator corr_cc;
+    B200_Multicorrelator_16sc corr_sc;
+    GpsL1CaDllPllCAidTracking<B200_Multicorrelator>* loop_cc = nullptr;
+    GpsL1CaDllPllCAidTracking<B200_Multicorrelator_16sc>* loop_sc = nullptr;
+};
+void* gbh_caid_open(gb200_service* service, int stream_id, int variant, const double* conf)
+{
+    CAidTrkConf c;
+    gbh_caid_conf(conf, &c);
+    auto* h = new gbh_caid();
+    h->variant = variant;
+    const bool ok = variant == 1 ? h->corr_sc.init(service, stream_id, 2 * (int)c.vector_length, 3)
+                                 : h->corr_cc.init(service, stream_id, GB200_ITEM_32FC, 2 * (int)c.vector_length, 3);
+    if (!ok)
+        {
+            delete h;
+            return nullptr;
+        }
+    if (variant == 1)
+        h->loop_sc = new GpsL1CaDllPllCAidTracking<B200_Multicorrelator_16sc>(c, &h->corr_sc);
+    else
+        h->loop_cc = new GpsL1CaDllPllCAidTracking<B200_Multicorrelator>(c, &h->corr_cc);
+    return h;
+}
+int gbh_caid_start(void* hv, const float* code_iq, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now)
+{
+    auto* h = static_cast<gbh_caid*>(hv);
+    const auto* code = reinterpret_cast<const std::complex<float>*>(code_iq);
+    if (h->variant == 1)
+        {
+            h->loop_sc->set_sample_counter(now);
+            return h->loop_sc->start_tracking(code, acq_delay_samples, acq_doppler_hz, acq_samplestamp) ? 0 : -1;
+        }
+    h->loop_cc->set_sample_counter(now);
+    return h->loop_cc->start_tracking(code, acq_delay_samples, acq_doppler_hz, acq_samplestamp) ? 0 : -1;
+}
+void gbh_caid_set_preamble(void* hv, double preamble_timestamp_s)
+{
+    auto* h = static_cast<gbh_caid*>(hv);
+    if (h->variant == 1)
+        h->loop_sc->set_preamble_timestamp(preamble_timestamp_s);
+    else
+        h->loop_cc->set_preamble_timestamp(preamble_timestamp_s);
+}
+int gbh_caid_step(void* hv, double* epoch)
+{
+    auto* h = static_cast<gbh_caid*>(hv);
+    CAidEpoch e;
+    const bool ok = h->variant == 1 ? h->loop_sc->step(&e) : h->loop_cc->step(&e);
+    gbh_caid_fill(e, epoch);
+    return ok ? 0 : -2;
+}
+void gbh_caid_close(void* hv)
+{
+    auto* h = static_cast<gbh_caid*>(hv);
+    if (!h) return;
+    delete h->loop_cc;
+    delete h->loop_sc;
     delete h;
 }
 }

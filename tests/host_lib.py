@@ -124,6 +124,12 @@ def host():
                                        C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.gbh_e5a_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, f32p, C.c_size_t, C.c_uint64, C.c_int,
                                       C.POINTER(C.c_double), C.POINTER(C.c_int), f32p]
+        L.gbh_caid_open.restype = C.c_void_p
+        L.gbh_caid_open.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        L.gbh_caid_start.argtypes = [C.c_void_p, f32p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        L.gbh_caid_set_preamble.argtypes = [C.c_void_p, C.c_double]
+        L.gbh_caid_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.gbh_caid_close.argtypes = [C.c_void_p]
         L.gbh_acq_resampler_decimation.restype = C.c_uint
         L.gbh_acq_resampler_decimation.argtypes = [C.c_longlong, C.c_uint]
         L.gbh_attach_acq_resampler.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_uint]
@@ -212,6 +218,12 @@ def oracle_loop():
         L.hol_glo_start.argtypes = [C.c_void_p, f32p, C.c_int, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
         L.hol_glo_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.hol_glo_close.argtypes = [C.c_void_p]
+        L.hol_caid_open.restype = C.c_void_p
+        L.hol_caid_open.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
+        L.hol_caid_start.argtypes = [C.c_void_p, f32p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        L.hol_caid_set_preamble.argtypes = [C.c_void_p, C.c_double]
+        L.hol_caid_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.hol_caid_close.argtypes = [C.c_void_p]
         L.hol_set_channel.argtypes = [C.c_void_p, C.c_uint]
         _hol = L
     return _hol
@@ -302,3 +314,47 @@ def run_b200_glonass(service, stream_id, item_type, first_index, code_c64, freq_
         return _glo_run(L.gbh_glo_step, h, n_steps)
     finally:
         L.gbh_glo_close(h)
+
+
+CAID_EPOCH_FIELDS = ("tracking_sample_counter", "prompt_i", "prompt_q", "carrier_doppler_hz", "code_phase_samples", "carrier_phase_rads", "cn0_db_hz",
+                     "abs_e", "abs_p", "abs_l", "flags", "correlation_length_samples", "correlation_length_ms")
+
+
+def _caid_conf(fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz=20.0, dll_bw_narrow_hz=2.0, early_late_space_chips=0.5, extend_correlation_ms=1):
+    return (C.c_double * 8)(fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms)
+
+
+def _caid_run(step, set_preamble, h, n_steps, preamble):
+    out = np.zeros((n_steps, len(CAID_EPOCH_FIELDS)))
+    e = (C.c_double * len(CAID_EPOCH_FIELDS))()
+    for k in range(n_steps):
+        if preamble is not None and k == preamble[0]:
+            set_preamble(h, preamble[1])
+        assert step(h, e) == 0, "correlator refused the request at step %d" % k
+        out[k] = e[:]
+    return out
+
+
+def run_oracle_caid(samples, variant, first_index, code_c64, acq_delay, acq_doppler, acq_stamp, n_steps, preamble=None, **conf):
+    """Carrier-aided GPS L1 C/A loop (gb200_c_aid_tracking.hpp) on the oracle's correlators: variant 0 = _cc (complex64 samples),
+    variant 1 = _sc (interleaved int16 samples).  preamble = (step index, preamble_timestamp_s) starts extended integration."""
+    L = oracle_loop()
+    x = np.ascontiguousarray(samples, np.int16) if variant == 1 else np.ascontiguousarray(samples, np.complex64).view(np.float32)
+    h = L.hol_caid_open(x.ctypes.data_as(C.c_void_p), len(x) // 2, first_index, variant, _caid_conf(**conf))
+    assert L.hol_caid_start(h, np.ascontiguousarray(code_c64, np.complex64).view(np.float32), acq_delay, acq_doppler, acq_stamp, first_index) == 0
+    try:
+        return _caid_run(L.hol_caid_step, L.hol_caid_set_preamble, h, n_steps, preamble)
+    finally:
+        L.hol_caid_close(h)
+
+
+def run_b200_caid(service, stream_id, variant, first_index, code_c64, acq_delay, acq_doppler, acq_stamp, n_steps, preamble=None, **conf):
+    """the same loop on B200_Multicorrelator (variant 0, 32fc stream) / B200_Multicorrelator_16sc (variant 1, 16ic stream) through the C ABI"""
+    L = host()
+    h = L.gbh_caid_open(service.h, stream_id, variant, _caid_conf(**conf))
+    assert h
+    assert L.gbh_caid_start(h, np.ascontiguousarray(code_c64, np.complex64).view(np.float32), acq_delay, acq_doppler, acq_stamp, first_index) == 0
+    try:
+        return _caid_run(L.gbh_caid_step, L.gbh_caid_set_preamble, h, n_steps, preamble)
+    finally:
+        L.gbh_caid_close(h)

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../gnss-sdr-1_b200/host/gb200_host_flat.h"
+#include "../../gnss-sdr-1_b200/host/gb200_c_aid_tracking.hpp"
 #include "../../gnss-sdr-1_b200/host/gb200_glonass_tracking.hpp"
 #include "../../gnss-sdr-1_b200/host/gb200_tracking.hpp"
 #include "../../oracle/gnss_oracle.h"
@@ -98,6 +99,7 @@ namespace
 class OracleCplxCorrelator
 {
 public:
+    using out_t = std::complex<float>;
     OracleCplxCorrelator(const float* samples_iq, uint64_t n_samples, uint64_t first_index) : x_(samples_iq), n_(n_samples), first_(first_index) {}
     bool set_local_code_and_taps(int code_len, const std::complex<float>* code, const float* shifts, int n_taps)
     {
@@ -149,4 +151,102 @@ int hol_glo_step(void* h, double* epoch)
     return ok ? 0 : -2;
 }
 void hol_glo_close(void* h) { delete static_cast<GloChannel*>(h); }
+}
+
+// ---- the carrier-aided GPS L1 C/A loops on the oracle's correlators: _cc on go_multicorrelator_cplx, _sc on go_multicorrelator_16sc ----
+namespace
+{
+class Oracle16scCorrelator
+{
+public:
+    using out_t = std::complex<int16_t>;
+    Oracle16scCorrelator(const int16_t* samples_iq, uint64_t n_samples, uint64_t first_index) : x_(samples_iq), n_(n_samples), first_(first_index) {}
+    // volk_gnsssdr_32fc_convert_16ic.h (generic): clamp, rintf
+    bool set_local_code_and_taps(int code_len, const std::complex<float>* code, const float* shifts, int n_taps)
+    {
+        const float* f = reinterpret_cast<const float*>(code);
+        code_.resize(2 * (size_t)code_len);
+        for (size_t i = 0; i < code_.size(); i++)
+            {
+                float aux = f[i];
+                if (aux > 32767.0f) aux = 32767.0f;
+                if (aux < -32768.0f) aux = -32768.0f;
+                code_[i] = (int16_t)rintf(aux);
+            }
+        shifts_.assign(shifts, shifts + n_taps);
+        return true;
+    }
+    bool correlate(uint64_t first, float rem_carr, float phase_step, float rem_code, float code_step, int n, out_t* out)
+    {
+        if (first < first_ || first + (uint64_t)n > first_ + n_) return false;
+        go_multicorrelator_16sc(x_ + 2 * (first - first_), n, code_.data(), (int)code_.size() / 2, shifts_.data(), (int)shifts_.size(), rem_carr, phase_step, rem_code,
+            code_step, reinterpret_cast<int16_t*>(out));
+        return true;
+    }
+
+private:
+    const int16_t* x_;
+    uint64_t n_, first_;
+    std::vector<int16_t> code_;
+    std::vector<float> shifts_;
+};
+struct CAidChannel
+{
+    int variant = 0;
+    std::unique_ptr<OracleCplxCorrelator> corr_cc;
+    std::unique_ptr<Oracle16scCorrelator> corr_sc;
+    std::unique_ptr<gb200::GpsL1CaDllPllCAidTracking<OracleCplxCorrelator>> loop_cc;
+    std::unique_ptr<gb200::GpsL1CaDllPllCAidTracking<Oracle16scCorrelator>> loop_sc;
+};
+}  // namespace
+
+extern "C" {
+// samples: float IQ pairs (variant 0) or int16 IQ pairs (variant 1)
+void* hol_caid_open(const void* samples_iq, uint64_t n_samples, uint64_t first_index, int variant, const double* conf)
+{
+    gb200::CAidTrkConf c;
+    gbh_caid_conf(conf, &c);
+    auto* ch = new CAidChannel();
+    ch->variant = variant;
+    if (variant == 1)
+        {
+            ch->corr_sc.reset(new Oracle16scCorrelator(static_cast<const int16_t*>(samples_iq), n_samples, first_index));
+            ch->loop_sc.reset(new gb200::GpsL1CaDllPllCAidTracking<Oracle16scCorrelator>(c, ch->corr_sc.get()));
+        }
+    else
+        {
+            ch->corr_cc.reset(new OracleCplxCorrelator(static_cast<const float*>(samples_iq), n_samples, first_index));
+            ch->loop_cc.reset(new gb200::GpsL1CaDllPllCAidTracking<OracleCplxCorrelator>(c, ch->corr_cc.get()));
+        }
+    return ch;
+}
+int hol_caid_start(void* h, const float* code_iq, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t now)
+{
+    auto* ch = static_cast<CAidChannel*>(h);
+    const auto* code = reinterpret_cast<const std::complex<float>*>(code_iq);
+    if (ch->variant == 1)
+        {
+            ch->loop_sc->set_sample_counter(now);
+            return ch->loop_sc->start_tracking(code, acq_delay_samples, acq_doppler_hz, acq_samplestamp) ? 0 : -1;
+        }
+    ch->loop_cc->set_sample_counter(now);
+    return ch->loop_cc->start_tracking(code, acq_delay_samples, acq_doppler_hz, acq_samplestamp) ? 0 : -1;
+}
+void hol_caid_set_preamble(void* h, double preamble_timestamp_s)
+{
+    auto* ch = static_cast<CAidChannel*>(h);
+    if (ch->variant == 1)
+        ch->loop_sc->set_preamble_timestamp(preamble_timestamp_s);
+    else
+        ch->loop_cc->set_preamble_timestamp(preamble_timestamp_s);
+}
+int hol_caid_step(void* h, double* epoch)
+{
+    auto* ch = static_cast<CAidChannel*>(h);
+    gb200::CAidEpoch e;
+    const bool ok = ch->variant == 1 ? ch->loop_sc->step(&e) : ch->loop_cc->step(&e);
+    gbh_caid_fill(e, epoch);
+    return ok ? 0 : -2;
+}
+void hol_caid_close(void* h) { delete static_cast<CAidChannel*>(h); }
 }

@@ -323,3 +323,40 @@ def test_acquisition_through_resampler_matches_oracle(service):
     assert abs((delay - (5003.0 - 2000 * dec)) % 16000) <= 2 * dec or abs((delay - (5003.0 - 2000 * dec)) % 16000 - 16000) <= 2 * dec
     service.set_decimator(0, 1, 0)
     o.close()
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_c_aid_loops_on_b200_match_oracle_loops(service, variant):
+    """The carrier-aided GPS L1 C/A trackers (gps_l1_ca_dll_pll_c_aid_tracking_cc on the complex-code correlator, _sc on the int16
+    correlator) closed on the B200 through the C ABI vs the same loop on the oracle correlators, incl. the switch to 5 ms
+    extended integration.  The int16 correlator is bit-exact, so the whole _sc loop is: every field of every epoch equal."""
+    import gnss_b200 as gb
+    import test_host_cpu as thc
+
+    fs, doppler, delay = 4e6, 3100.0, 2750.6
+    x, code = thc.caid_scene(700, doppler, delay, seed=20260012)
+    conf = dict(fs_in=fs, vector_length=4000, pll_bw_hz=35.0, dll_bw_hz=2.0, pll_bw_narrow_hz=15.0, dll_bw_narrow_hz=1.5, early_late_space_chips=0.5,
+                extend_correlation_ms=5)
+    args = dict(code_c64=code, acq_delay=delay - 0.6, acq_doppler=doppler - 50.0, acq_stamp=0, n_steps=650, preamble=(400, 0.0))
+    F = {n: i for i, n in enumerate(hl.CAID_EPOCH_FIELDS)}
+    if variant == 1:
+        q = np.ascontiguousarray(np.rint(np.stack([x.real, x.imag], -1) * 4.0).astype(np.int16).reshape(-1))
+        service.push(2, q, gb.ITEM_16IC, 0)
+        ref = hl.run_oracle_caid(q, 1, 0, **args, **conf)
+        got = hl.run_b200_caid(service, 2, 1, 0, **args, **conf)
+        assert np.array_equal(got, ref)
+    else:
+        service.push(2, x, gb.ITEM_32FC, 0)
+        ref = hl.run_oracle_caid(x, 0, 0, **args, **conf)
+        got = hl.run_b200_caid(service, 2, 0, 0, **args, **conf)
+        assert np.array_equal(got[:, F["tracking_sample_counter"]], ref[:, F["tracking_sample_counter"]])
+        assert np.array_equal(got[:, F["flags"]], ref[:, F["flags"]])
+        rel = np.abs(got[1:, F["abs_p"]] - ref[1:, F["abs_p"]]) / ref[1:, F["abs_p"]].max()
+        dd = np.abs(got[:, F["carrier_doppler_hz"]] - ref[:, F["carrier_doppler_hz"]])
+        print("c_aid _cc closed loop: doppler diff max %.3g Hz, prompt magnitude diff max %.3g of peak" % (dd.max(), rel.max()))
+        assert dd.max() < 0.5 and rel.max() < 2e-3
+        assert np.abs(got[:, F["code_phase_samples"]] - ref[:, F["code_phase_samples"]]).max() < 0.01
+    lock = got[250:400]
+    assert np.all(lock[:, F["flags"]] == 1) and abs(lock[:, F["carrier_doppler_hz"]].mean() - doppler) < 4.0
+    ext = got[450:]
+    assert np.all(ext[ext[:, F["flags"]] == 1, F["correlation_length_ms"]] == 5) and 0.18 < (ext[:, F["flags"]] == 1).mean() < 0.22

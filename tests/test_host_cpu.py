@@ -307,3 +307,43 @@ def test_acq_resampler_design_matches_oracle_restatement():
         assert abs(20 * np.log10(h[f < acq_fs / 2.1 - acq_fs / 10].min())) < 0.1
     # capacity protocol of the C entry point
     assert len(gb.firdes_low_pass(2.0, 4e6, 4e5, 2e5)) == (int(53 * 4e6 / (22 * 2e5)) | 1)
+
+
+def caid_scene(n_ms, doppler, delay, cn0=48.0, fs=4e6, prn=9, seed=20260011):
+    x = synth.make_iq(fs, int(n_ms * fs / 1000), [dict(kind="gps_l1_ca", prn=prn, cn0_dbhz=cn0, doppler_hz=doppler, delay_samples=delay, phase=0.7)], seed)
+    return x, synth.code_table("gps_l1_ca", prn).astype(np.complex64)
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_c_aid_loop_locks_on_oracle_correlator(variant):
+    """GpsL1CaDllPllCAidTracking (mirror of gps_l1_ca_dll_pll_c_aid_tracking_cc / _sc: FLL-assisted PLL filter with the FLL input at 0,
+    2nd-order DLL, block length from the code NCO) on the oracle's Cpu_Multicorrelator / Cpu_Multicorrelator_16sc restatements:
+    pull-in from a coarse estimate, lock, CN0; then extended integration once a preamble time is known (valid symbols every
+    `extend_correlation_ms` blocks, NCOs free-running in between, lock kept)."""
+    fs, doppler, delay = 4e6, -2222.0, 1500.4
+    x, code = caid_scene(900, doppler, delay)
+    # _sc: the int16 correlator accumulates in saturating int16 and the extended correlator adds prompts in int16, so the
+    # front end has to deliver few-bit samples: noise sigma = 4 LSB keeps 5 coherent prompts (5 * 4000 * 0.18 * 4) inside +-32767
+    samples = np.ascontiguousarray(np.rint(np.stack([x.real, x.imag], -1) * 4.0).astype(np.int16).reshape(-1)) if variant == 1 else x
+    F = {n: i for i, n in enumerate(hl.CAID_EPOCH_FIELDS)}
+    conf = dict(fs_in=fs, vector_length=4000, pll_bw_hz=35.0, dll_bw_hz=2.0, pll_bw_narrow_hz=15.0, dll_bw_narrow_hz=1.5, early_late_space_chips=0.5,
+                extend_correlation_ms=5)
+    ep = hl.run_oracle_caid(samples, variant, 0, code, acq_delay=delay + 0.7, acq_doppler=doppler + 60.0, acq_stamp=0, n_steps=850,
+                            preamble=(500, 0.0), **conf)
+    assert ep[0, F["flags"]] == 0 and ep[0, F["correlation_length_samples"]] == round(delay + 0.7 + 4000)  # pull-in alignment epoch
+    lock = ep[300:500]
+    assert np.all(lock[:, F["flags"]] == 1) and np.all(lock[:, F["correlation_length_ms"]] == 1)
+    assert abs(lock[:, F["carrier_doppler_hz"]].mean() - doppler) < 4.0
+    assert 44.0 < lock[:, F["cn0_db_hz"]].mean() < 52.0
+    assert np.all(lock[:, F["abs_p"]] > 1.2 * np.maximum(lock[:, F["abs_e"]], lock[:, F["abs_l"]]))
+    assert set(np.unique(lock[:, F["correlation_length_samples"]])) <= {3999.0, 4000.0, 4001.0}
+    # extended integration: one valid symbol per 5 blocks with a 5x coherent prompt, Doppler still right
+    ext = ep[600:]
+    valid = ext[:, F["flags"]] == 1
+    assert 0.18 < valid.mean() < 0.22 and np.all(ext[valid, F["correlation_length_ms"]] == 5)
+    assert np.median(ext[valid, F["abs_p"]]) > 4.0 * np.median(lock[:, F["abs_p"]])
+    assert abs(ext[valid, F["carrier_doppler_hz"]].mean() - doppler) < 4.0
+    assert not np.any(ep[:, F["flags"]] >= 2)  # never lost lock
+    if variant == 1:
+        # the _sc correlator's outputs are integers
+        assert np.all(ep[:, F["prompt_i"]] == np.round(ep[:, F["prompt_i"]]))
