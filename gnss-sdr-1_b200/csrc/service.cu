@@ -130,6 +130,22 @@ struct gb200_service
     int live_trk = 0;       // float-correlator handles alive
     int prev_batch_n = 1;   // callers served by the previous coalesced launch: the collector waits for that many (adaptive)
     uint64_t coalesced_batches = 0, coalesced_requests = 0;
+    // the same for concurrent gb200_acq_run callers (the channels' acquisitions over one sample block become
+    // ONE gb200_acq_run_batch, so the Doppler-wiped forward spectra are computed once for all of them)
+    struct AcqPending
+    {
+        gb200_acq* a;
+        int stream_id;
+        uint64_t first;
+        gb200_acq_result* out;
+        int rc;
+        bool done;
+    };
+    std::mutex aqmu;
+    std::condition_variable aqcv;
+    std::vector<AcqPending*> acq_queue;
+    bool acq_collecting = false;
+    uint64_t acq_coalesced_batches = 0, acq_coalesced_requests = 0;
     gb200_trk_batch* cb = nullptr;  // arena of gb200_trk_correlate_batch (grow-only)
     int cb_n = 0, cb_chunks = 0;
     std::string error = "no error";
@@ -1743,8 +1759,76 @@ extern "C" int gb200_acq_run_batch(gb200_acq* const* list, int n, int stream_id,
 
 extern "C" int gb200_acq_run(gb200_acq* a, int stream_id, uint64_t first_sample_index, gb200_acq_result* out)
 {
-    gb200_acq* l[1] = {a};
-    return gb200_acq_run_batch(l, 1, stream_id, first_sample_index, out);
+    if (!a || !out) return GB200_E_INVALID;
+    gb200_service* s = a->s;
+    if (s->batch_window_us == 0)
+        {
+            gb200_acq* l[1] = {a};
+            return gb200_acq_run_batch(l, 1, stream_id, first_sample_index, out);
+        }
+    // ---- coalescing: every channel's acquisition thread queues its search; the first one in collects for batch_window_us,
+    // then runs ONE batch per (stream, first sample) group and hands each caller its own result ----
+    gb200_service::AcqPending me{a, stream_id, first_sample_index, out, GB200_OK, false};
+    std::unique_lock<std::mutex> lk(s->aqmu);
+    s->acq_queue.push_back(&me);
+    if (s->acq_collecting)
+        {
+            s->aqcv.wait(lk, [&] { return me.done; });
+            return me.rc;
+        }
+    s->acq_collecting = true;
+    s->aqcv.wait_for(lk, std::chrono::microseconds(s->batch_window_us), [] { return false; });
+    std::vector<gb200_service::AcqPending*> batch;
+    batch.swap(s->acq_queue);
+    s->acq_collecting = false;  // the next arrival collects the next batch while this one runs (the service mutex serialises the GPU work)
+    lk.unlock();
+    std::vector<bool> taken(batch.size(), false);
+    uint64_t groups = 0;
+    for (size_t i = 0; i < batch.size(); i++)
+        {
+            if (taken[i]) continue;
+            std::vector<size_t> members;
+            for (size_t k = i; k < batch.size(); k++)
+                if (!taken[k] && batch[k]->stream_id == batch[i]->stream_id && batch[k]->first == batch[i]->first)
+                    {
+                        taken[k] = true;
+                        members.push_back(k);
+                    }
+            std::vector<gb200_acq*> list(members.size());
+            std::vector<gb200_acq_result> res(members.size());
+            for (size_t k = 0; k < members.size(); k++) list[k] = batch[members[k]]->a;
+            const int rc = gb200_acq_run_batch(list.data(), (int)list.size(), batch[i]->stream_id, batch[i]->first, res.data());
+            if (rc != GB200_OK && members.size() > 1)
+                {
+                    // one bad request must not fail the others: redo one by one
+                    for (size_t k = 0; k < members.size(); k++)
+                        batch[members[k]]->rc = gb200_acq_run_batch(&list[k], 1, batch[i]->stream_id, batch[i]->first, batch[members[k]]->out);
+                }
+            else
+                for (size_t k = 0; k < members.size(); k++)
+                    {
+                        batch[members[k]]->rc = rc;
+                        if (rc == GB200_OK) *batch[members[k]]->out = res[k];
+                    }
+            groups++;
+        }
+    lk.lock();
+    s->acq_coalesced_batches += groups;
+    s->acq_coalesced_requests += batch.size();
+    for (auto* b : batch) b->done = true;
+    const int my_rc = me.rc;
+    lk.unlock();
+    s->aqcv.notify_all();
+    return my_rc;
+}
+
+extern "C" int gb200_service_acq_coalescing_stats(gb200_service* s, uint64_t* batches, uint64_t* requests)
+{
+    if (!s) return GB200_E_INVALID;
+    std::lock_guard<std::mutex> lk(s->aqmu);
+    if (batches) *batches = s->acq_coalesced_batches;
+    if (requests) *requests = s->acq_coalesced_requests;
+    return GB200_OK;
 }
 
 // ------------------------------------------------------------------ tracking

@@ -75,7 +75,7 @@ class TrkReq(C.Structure):
 EXPORTS = [
     "gb200_service_create", "gb200_service_destroy", "gb200_last_error", "gb200_version", "gb200_service_cuda_stream",
     "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
-    "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
+    "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_acq_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
     "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
@@ -111,6 +111,7 @@ def lib():
     L.gb200_service_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.gb200_service_flush_l2.argtypes = [vp, C.c_size_t]
     L.gb200_service_coalescing_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.gb200_service_acq_coalescing_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.gb200_service_measure_fp32.argtypes = [vp, C.POINTER(C.c_double)]
     L.gb200_service_kernel_timing.argtypes = [vp, i]
     L.gb200_service_kernel_stats.argtypes = [vp, i, C.POINTER(C.c_double), C.POINTER(u64)]
@@ -175,6 +176,11 @@ class Service:
     def coalescing_stats(self):
         b, r = C.c_uint64(), C.c_uint64()
         self.check(self.L.gb200_service_coalescing_stats(self.h, C.byref(b), C.byref(r)))
+        return b.value, r.value
+
+    def acq_coalescing_stats(self):
+        b, r = C.c_uint64(), C.c_uint64()
+        self.check(self.L.gb200_service_acq_coalescing_stats(self.h, C.byref(b), C.byref(r)))
         return b.value, r.value
 
     def close(self):

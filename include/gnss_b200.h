@@ -79,6 +79,10 @@ int gb200_service_measure_fp32(gb200_service* s, double* tflops);
 int gb200_service_flush_l2(gb200_service* s, size_t bytes);
 /* how many coalesced launches served how many gb200_trk_correlate calls so far (batch_window_us > 0) */
 int gb200_service_coalescing_stats(gb200_service* s, uint64_t* batches, uint64_t* requests);
+/* the same for gb200_acq_run: with batch_window_us > 0 concurrent callers (each Channel's acquisition thread,
+ * pcps_acquisition.cc:1020-1043; what GNSSFlowgraph::priorize_satellites / ChannelFsm start together, gnss_flowgraph.cc:1494-1546)
+ * that name the same stream and first sample are run as ONE gb200_acq_run_batch, results identical to lone calls */
+int gb200_service_acq_coalescing_stats(gb200_service* s, uint64_t* batches, uint64_t* requests);
 
 /* Hand a block of the conditioned sample stream to the device ONCE for all channels.  Replaces each
  * block's own read of input_items[0] (pcps_acquisition.cc:995-1034 state 1 buffering;

@@ -479,3 +479,54 @@ def test_real_capture_all_gps_prns(service, golden_dir):
         a.close()
     o32.close()
     o64.close()
+
+
+def test_service_coalesces_concurrent_acquisition_threads():
+    """one thread per channel calling the blocking gb200_acq_run on the same sample block (what ChannelFsm starts
+    together): with batch_window_us > 0 the service runs them as ONE gb200_acq_run_batch (forward spectra shared), every caller
+    gets exactly the result of a lone call, and far fewer kernels are launched."""
+    import threading
+
+    import gnss_b200 as gb
+
+    prns, x = c1_signal(8000)
+    cfg = dict(doppler_max=5000, doppler_step=250, threshold=0.008, samples_per_chip=4)
+
+    def run(window):
+        svc = gb.Service(ring_capacity=1 << 20, ring_slack=1 << 16, batch_window_us=window)
+        try:
+            svc.push(0, x, gb.ITEM_32FC, 0)
+            acqs = []
+            for p in prns + [30, 31]:
+                a = gb.Acquisition(svc, **cfg)
+                a.set_local_code(gps_local_code(p))
+                acqs.append(a)
+            res = [None] * len(acqs)
+            l0 = svc.launch_count()
+
+            def worker(k):
+                res[k] = acqs[k].run(0, 1000)
+
+            th = [threading.Thread(target=worker, args=(k,)) for k in range(len(acqs))]
+            for t in th:
+                t.start()
+            for t in th:
+                t.join()
+            launches = svc.launch_count() - l0
+            stats = svc.acq_coalescing_stats()
+            for a in acqs:
+                a.close()
+            return res, launches, stats
+        finally:
+            svc.close()
+
+    alone, launches_alone, stats0 = run(0)
+    assert stats0 == (0, 0)
+    together, launches_together, (batches, requests) = run(20000)
+    assert requests == len(alone) and batches < requests
+    for ra, rt in zip(alone, together):
+        for f in ("code_phase_index", "doppler_hz", "doppler_bin", "peak_mag", "input_power", "test_statistic", "decision", "acq_delay_samples",
+                  "acq_samplestamp"):
+            assert getattr(ra, f) == getattr(rt, f), f
+    assert launches_together * 2 < launches_alone, (launches_together, launches_alone)
+    assert sum(r.decision == 1 for r in together) == 8
