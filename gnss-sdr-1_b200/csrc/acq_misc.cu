@@ -140,9 +140,9 @@ __global__ void __launch_bounds__(1024) gb_grid_peaks_kernel(float* const* grids
 //   memcpy(d_tmp_buffer, row, d_fft_size BYTES)  -> only the first N/4 floats are refreshed (quirk 1)
 //   zero [idx - spc, idx + spc) with the one-sided wrap of :637-644 (quirk 2), do-while semantics
 //   second peak = first maximum of d_tmp_buffer[0..N)
-__global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, int row_len, float* tmp, int N, int idx, int spc, float* second)
+__global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, int row_len, float* tmp, int N, int idx, int spc, float* second, int ncopy_all)
 {
-    const int ncopy = min(N / 4, row_len);
+    const int ncopy = ncopy_all ? min(N, row_len) : min(N / 4, row_len);
     for (int i = threadIdx.x; i < ncopy; i += blockDim.x) tmp[i] = row[i];
     __syncthreads();
     int ex1 = idx - spc, ex2 = idx + spc;
@@ -293,7 +293,75 @@ cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_le
 
 cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches)
 {
-    gb_second_peak_kernel<<<1, 1024, 0, st>>>(grid_row, N, tmp_buffer, N, idx, samples_per_chip, d_second);
+    gb_second_peak_kernel<<<1, 1024, 0, st>>>(grid_row, N, tmp_buffer, N, idx, samples_per_chip, d_second, 0);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+// pcps_acquisition_fine_doppler_cc.cc:296-322: the exclusion is applied to the whole row (here: to a copy of it)
+cudaError_t gb_acq_second_peak_row(const float* grid_row, float* tmp_row, int N, int idx, int half_width, float* d_second, cudaStream_t st, int* launches)
+{
+    gb_second_peak_kernel<<<1, 1024, 0, st>>>(grid_row, N, tmp_row, N, idx, half_width, d_second, 1);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+namespace
+{
+// volk_32fc_x2_multiply_32fc of the buffered samples with the code replica (pcps_acquisition_fine_doppler_cc.cc:430)
+template <int ITEM>
+__global__ void gb_code_wipe_kernel(const void* __restrict__ samples, const float2* __restrict__ rep, int n, float2* __restrict__ out)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        {
+            const float2 x = gb_load_item<ITEM>(samples, i);
+            const float2 c = rep[i];
+            out[i] = make_float2(__fsub_rn(__fmul_rn(x.x, c.x), __fmul_rn(x.y, c.y)), __fadd_rn(__fmul_rn(x.x, c.y), __fmul_rn(x.y, c.x)));
+        }
+}
+
+// first maximum of |X[k]|^2 in natural frequency order; X is stored [k1][k2] with k = k1 + N1 * k2 (four-step output order)
+__global__ void __launch_bounds__(1024) gb_spectrum_peak_kernel(const float2* __restrict__ X, int N1, int N2, GbPeak* out)
+{
+    GbPeak best;
+    best.mag = -INFINITY;
+    best.idx = 0xffffffffu;
+    best.bin = 0;
+    best.pad_ = 0;
+    const int N = N1 * N2;
+    for (int pos = threadIdx.x; pos < N; pos += blockDim.x)
+        {
+            const int k1 = pos / N2, k2 = pos - k1 * N2;
+            const float2 v = X[pos];
+            GbPeak c;
+            c.mag = __fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y));
+            c.idx = (unsigned)(k1 + N1 * k2);
+            c.bin = 0;
+            c.pad_ = 0;
+            if (peak_before(c, best)) best = c;
+        }
+    best = peak_block_reduce(best);
+    if (threadIdx.x == 0) *out = best;
+}
+}  // namespace
+
+cudaError_t gb_acq_code_wipe(const void* samples, int item_type, const float2* replica, int n, float2* out, cudaStream_t st, int* launches)
+{
+    const int blocks = std::min((n + 255) / 256, 148 * 8);
+    switch (item_type)
+        {
+        case GB200_ITEM_32FC: gb_code_wipe_kernel<GB200_ITEM_32FC><<<blocks, 256, 0, st>>>(samples, replica, n, out); break;
+        case GB200_ITEM_16IC: gb_code_wipe_kernel<GB200_ITEM_16IC><<<blocks, 256, 0, st>>>(samples, replica, n, out); break;
+        case GB200_ITEM_8IC: gb_code_wipe_kernel<GB200_ITEM_8IC><<<blocks, 256, 0, st>>>(samples, replica, n, out); break;
+        default: return cudaErrorInvalidValue;
+        }
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_spectrum_peak(const float2* spectrum, int N1, int N2, GbPeak* d_out, cudaStream_t st, int* launches)
+{
+    gb_spectrum_peak_kernel<<<1, 1024, 0, st>>>(spectrum, N1, N2, d_out);
     if (launches) (*launches)++;
     return cudaGetLastError();
 }

@@ -207,6 +207,10 @@ cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, in
 cudaError_t gb_fir_decimate(const float2* ring, unsigned long long cap, unsigned long long valid_begin, unsigned long long k_first, unsigned n_out,
     unsigned decimation, const float* d_taps, unsigned n_taps, float2* out, cudaStream_t st, int* launches);
 cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_len, float norm, gb200_acq_iq_bin* d_out, cudaStream_t st, int* launches);
+// fine-Doppler block helpers (acq_misc.cu)
+cudaError_t gb_acq_second_peak_row(const float* grid_row, float* tmp_row, int N, int idx, int half_width, float* d_second, cudaStream_t st, int* launches);
+cudaError_t gb_acq_code_wipe(const void* samples, int item_type, const float2* replica, int n, float2* out, cudaStream_t st, int* launches);
+cudaError_t gb_acq_spectrum_peak(const float2* spectrum, int N1, int N2, GbPeak* d_out, cudaStream_t st, int* launches);
 cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches);
 cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st, int* launches);
 size_t gb_acq_col_smem(const GbFftPlan& plan);

@@ -942,7 +942,7 @@ struct gb200_acq
 
     // sibling blocks served through the same Doppler loop
     std::vector<float> custom_steps;  // gb200_acq_set_doppler_grid: phase step per bin replaces the doppler_max/doppler_step rule
-    bool scaled_accum = false;        // gb200_acq_set_scaled_accumulation: Tong detector, grid += mag / (N^4 input_power) every dwell
+    int scaled_accum = 0;             // gb200_acq_set_scaled_accumulation: 1 = Tong detector, grid += mag / (N^4 input_power) every dwell; 2 = plain grid += mag
 
     bool need_grid() const { return keep_grid || !use_cfar || c.max_dwells > 1 || scaled_accum; }
 };
@@ -1210,7 +1210,7 @@ extern "C" int gb200_acq_set_scaled_accumulation(gb200_acq* a, int enable)
             a->s->set_error("gb200_acq_set_scaled_accumulation: not combined with bit_transition_flag / make_2_steps");
             return GB200_E_INVALID;
         }
-    a->scaled_accum = enable != 0;
+    a->scaled_accum = enable == 2 ? 2 : (enable != 0 ? 1 : 0);
     return acq_alloc_grid(a);
 }
 
@@ -1296,6 +1296,81 @@ extern "C" int gb200_acq_iq_combine(gb200_acq* ia, gb200_acq* qa, gb200_acq* ib,
     s->launches += l;
     GB_CUDA(s, cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    return GB200_OK;
+}
+
+// pcps_acquisition_fine_doppler_cc::compute_CAF (:296-322): second peak of one kept grid row with the +-half_width exclusion
+// around `idx` (same wrap rule and do-while as pcps_acquisition's, but on the whole row)
+extern "C" int gb200_acq_second_peak(gb200_acq* a, uint32_t bin, uint32_t idx, uint32_t half_width, float* second_peak)
+{
+    if (!a || !second_peak) return GB200_E_INVALID;
+    gb200_service* s = a->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (!a->d_grid || bin >= a->num_bins || idx >= a->eff)
+        {
+            s->set_error("gb200_acq_second_peak: handle keeps no grid, or bin / index out of range");
+            return GB200_E_STATE;
+        }
+    void* d_tmp;
+    int rc;
+    if ((rc = s->scratch(18, sizeof(float) * (a->eff + 4), &d_tmp))) return rc;
+    int l = 0;
+    float* d_second = (float*)d_tmp + a->eff;
+    GB_CUDA(s, gb_acq_second_peak_row(a->d_grid + (size_t)bin * a->eff, (float*)d_tmp, (int)a->eff, (int)idx, (int)half_width, d_second, s->stream, &l));
+    s->launches += l;
+    GB_CUDA(s, cudaMemcpyAsync(second_peak, d_second, sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    return GB200_OK;
+}
+
+// pcps_acquisition_fine_doppler_cc::estimate_Doppler (:400-441): items x replica, zero-padded to fft_len, forward FFT, |.|^2,
+// first maximum in natural frequency order
+extern "C" int gb200_acq_wiped_spectrum_peak(gb200_service* s, int stream_id, uint64_t first_sample_index, const float* replica_iq, uint32_t n_items,
+    uint32_t fft_len, uint32_t* peak_index, float* peak_mag)
+{
+    if (!s || !replica_iq || !peak_index || !peak_mag || n_items == 0 || fft_len < n_items) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    cudaSetDevice(s->device);
+    if (stream_id < 0 || stream_id >= (int)s->rings.size() || !s->rings[stream_id].d_buf)
+        {
+            s->set_error("gb200_acq_wiped_spectrum_peak: no such stream");
+            return GB200_E_INVALID;
+        }
+    const int item_type = s->rings[stream_id].item_type;
+    const GbFftPlan* plan;
+    int rc = get_plan(s, (int)fft_len, &plan);
+    if (rc) return rc;
+    if ((rc = rings_acquire(s))) return rc;
+    const void* win;
+    if ((rc = ring_window(s, stream_id, first_sample_index, n_items, item_type, &win))) return rc;
+    void *d_rp, *d_col, *d_spec, *d_pk;
+    if ((rc = s->scratch(18, sizeof(float2) * 2 * (size_t)n_items, &d_rp))) return rc;
+    if ((rc = s->scratch(19, sizeof(float2) * (size_t)fft_len, &d_col))) return rc;
+    if ((rc = s->scratch(1, sizeof(float2) * (size_t)fft_len, &d_spec))) return rc;
+    if ((rc = s->scratch(9, sizeof(GbPeak), &d_pk))) return rc;
+    float2* d_rep = (float2*)d_rp;
+    float2* d_prod = d_rep + n_items;
+    GB_CUDA(s, cudaMemcpyAsync(d_rep, replica_iq, sizeof(float2) * n_items, cudaMemcpyHostToDevice, s->stream));
+    int l = 0;
+    GB_CUDA(s, gb_acq_code_wipe(win, item_type, d_rep, (int)n_items, d_prod, s->stream, &l));
+    GbAcqFwdParams p;
+    p.samples = d_prod;
+    p.consumed = (int)n_items;
+    p.item_type = GB200_ITEM_32FC;
+    p.segs = nullptr;
+    p.seg_offsets = nullptr;
+    p.colbuf = (float2*)d_col;
+    p.spectra = (float2*)d_spec;
+    GB_CUDA(s, gb_acq_forward(*plan, p, 1, false, s->stream, &l, nullptr));
+    GB_CUDA(s, gb_acq_spectrum_peak((const float2*)d_spec, plan->N1, plan->N2, (GbPeak*)d_pk, s->stream, &l));
+    s->launches += l;
+    GbPeak pk;
+    GB_CUDA(s, cudaMemcpyAsync(&pk, d_pk, sizeof(GbPeak), cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaStreamSynchronize(s->stream));
+    { int rc0 = rings_release(s); if (rc0) return rc0; }
+    *peak_index = pk.idx;
+    *peak_mag = pk.mag;
     return GB200_OK;
 }
 
@@ -1536,7 +1611,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     ip.accumulate = (g.grid && a0->dwell_counter >= 1) ? 1 : 0;  // this is dwell number dwell_counter+1
                     ip.partial = (GbPeak*)d_part;
                     ip.tmpbuf = (g.grid && !a0->use_cfar && !a0->scaled_accum) ? (float* const*)((char*)d_up + g.off_tmp) : nullptr;
-                    ip.scale = (g.grid && a0->scaled_accum) ? d_power + 1 : nullptr;
+                    ip.scale = (g.grid && a0->scaled_accum == 1) ? d_power + 1 : nullptr;
                     GB_CUDA(s, gb_acq_inverse(plan, ip, lane_stream[ln], &l, s));
                 }
             if (fork)

@@ -3,6 +3,7 @@
 //   B200_Pcps_Tong_Acquisition        pcps_tong_acquisition_cc         (src/algorithms/acquisition/gnuradio_blocks/pcps_tong_acquisition_cc.cc)
 //   B200_Galileo_Pcps_8ms_Acquisition galileo_pcps_8ms_acquisition_cc  (.../galileo_pcps_8ms_acquisition_cc.cc)
 //   B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf  galileo_e5a_noncoherentIQ_acquisition_caf_cc (.../galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc)
+//   B200_Pcps_Acquisition_Fine_Doppler  pcps_acquisition_fine_doppler_cc (.../pcps_acquisition_fine_doppler_cc.cc)
 // The blocks use fft_size = sampled_ms * samples_per_ms with NO zero padding, count their Doppler bins inclusively
 // ("doppler <= doppler_max") and build the wipe-off tables with their own phase-step expression, so the bins are handed to
 // the engine as an explicit list (gb200_acq_set_doppler_grid).  The device does the per-bin arithmetic; the counters,
@@ -492,5 +493,143 @@ private:
     float mag_ = 0.0f, input_power_ = 0.0f, test_statistics_ = 0.0f;
     std::vector<float> caf_, caf_i_, caf_q_;
     std::vector<gb200_acq_iq_bin> rec_;
+};
+// ------------------------------------------------------------------------------------------------ fine Doppler
+// pcps_acquisition_fine_doppler_cc: the grid is the plain sum of |.|^2 over max_dwells dwells, the statistic is the ratio of its
+// maximum to the second peak of the same Doppler row (one chip either side excluded), and a positive acquisition refines the
+// Doppler with an 8x zero-padded FFT of 10 ms of code-wiped samples.  The grid, both peak searches, the wipe-off and the long
+// FFT run on the device; the state sequence, the replica (incl. the block's off-by-one std::rotate) and the bin-to-Hz table
+// arithmetic stay here.
+class B200_Pcps_Acquisition_Fine_Doppler
+{
+public:
+    B200_Pcps_Acquisition_Fine_Doppler(gb200_service* s, const AcqVariantConf& c, int stream_id) : s_(s), c_(c), stream_(stream_id)
+    {
+        AcqVariantConf one = c;
+        one.sampled_ms = 1;  // d_fft_size = d_samples_per_ms (:64-66)
+        const gb200_acq_cfg g = detail::variant_cfg(one, true);
+        ok_ = gb200_acq_create(s_, &g, &h_) == GB200_OK && gb200_acq_set_scaled_accumulation(h_, 2) == GB200_OK;
+        if (ok_) set_doppler_step(c_.doppler_step);
+    }
+    ~B200_Pcps_Acquisition_Fine_Doppler()
+    {
+        if (h_) gb200_acq_destroy(h_);
+    }
+    B200_Pcps_Acquisition_Fine_Doppler(const B200_Pcps_Acquisition_Fine_Doppler&) = delete;
+    B200_Pcps_Acquisition_Fine_Doppler& operator=(const B200_Pcps_Acquisition_Fine_Doppler&) = delete;
+    bool ok() const { return ok_; }
+    void set_gnss_synchro(AcqSynchro* p) { synchro_ = p; }
+    void set_threshold(float t) { c_.threshold = t; }
+    // = set_doppler_step + update_carrier_wipeoff (:146-160, :246-261): floor(|2 doppler_max| / step) points from -doppler_max,
+    // phase step float(GPS_TWO_PI) * doppler / float(fs) in float32
+    void set_doppler_step(unsigned int doppler_step)
+    {
+        const double GPS_TWO_PI = 6.283185307179586;
+        c_.doppler_step = doppler_step;
+        num_doppler_points_ = floor(std::abs(2 * static_cast<int>(c_.doppler_max)) / c_.doppler_step);
+        std::vector<float> steps(num_doppler_points_);
+        for (int i = 0; i < num_doppler_points_; i++)
+            {
+                const int doppler_hz = c_.doppler_step * i - static_cast<int>(c_.doppler_max);
+                steps[i] = static_cast<float>(GPS_TWO_PI) * doppler_hz / static_cast<float>(c_.fs_in);
+            }
+        ok_ = ok_ && num_doppler_points_ > 0 && gb200_acq_set_doppler_grid(h_, num_doppler_points_, steps.data()) == GB200_OK;
+    }
+    // = set_local_code (:190-195); the copy is what estimate_Doppler regenerates with gps_l1_ca_code_gen_complex_sampled (:415)
+    bool set_local_code(const std::complex<float>* code, size_t n_items)
+    {
+        code_.assign(code, code + std::min<size_t>(n_items, fft_size()));
+        return gb200_acq_set_local_code(h_, reinterpret_cast<const float*>(code), n_items) == GB200_OK;
+    }
+    void set_state(int state)
+    {
+        state_ = state;
+        if (state == 1) gb200_acq_reset(h_);  // reset_grid (:232-243)
+    }
+    void reset() { set_state(1); }
+    uint32_t fft_size() const { return gb200_acq_fft_size(h_); }
+    int num_doppler_points() const { return num_doppler_points_; }
+    float test_statistics() const { return test_statistics_; }
+    float first_peak() const { return first_peak_; }
+    float second_peak() const { return second_peak_; }
+    uint32_t index_time() const { return index_time_; }
+    uint32_t index_doppler() const { return index_doppler_; }
+    uint32_t fine_index() const { return fine_index_; }
+    bool fine_accepted() const { return fine_accepted_; }
+
+    // states 1..5 of general_work (:520-650) for an attempt whose first item is `samp_count`; the stream must hold
+    // max(max_dwells, 10) * fft_size items from there.  Returns 1 (positive), 2 (negative), -1 (engine error).
+    int run(uint64_t samp_count)
+    {
+        if (state_ != 1) return 0;
+        const uint32_t N = fft_size();
+        gb200_acq_result r{};
+        for (uint32_t d = 0; d < c_.max_dwells; d++)  // S1: compute_and_accumulate_grid
+            if (gb200_acq_run(h_, stream_, samp_count + static_cast<uint64_t>(d) * N, &r) != GB200_OK) return -1;
+        // S2: compute_CAF (:266-326)
+        first_peak_ = r.peak_mag;
+        index_time_ = r.code_phase_index;
+        index_doppler_ = r.doppler_bin;
+        const double GPS_L1_CA_CHIP_PERIOD = 9.7752e-07;
+        const uint32_t samplesPerChip = ceil(GPS_L1_CA_CHIP_PERIOD * static_cast<float>(c_.fs_in));
+        if (gb200_acq_second_peak(h_, index_doppler_, index_time_, samplesPerChip, &second_peak_) != GB200_OK) return -1;
+        test_statistics_ = first_peak_ / second_peak_;
+        double acq_doppler_hz = static_cast<double>(static_cast<int>(index_doppler_ * c_.doppler_step) - static_cast<int>(c_.doppler_max));
+        const double acq_delay_samples = static_cast<double>(index_time_);
+        fine_accepted_ = false;
+        fine_index_ = 0;
+        const bool positive = test_statistics_ > c_.threshold;
+        if (positive)
+            {
+                // S3: estimate_Doppler (:400-479)
+                const int zero_padding_factor = 8, prn_replicas = 10;
+                const int signal_samples = prn_replicas * static_cast<int>(N);
+                const int fft_size_extended = signal_samples * zero_padding_factor;
+                std::vector<std::complex<float>> code_replica(signal_samples);
+                std::copy(code_.begin(), code_.end(), code_replica.begin());
+                const int shift_index = static_cast<int>(acq_delay_samples);
+                if (shift_index != 0) std::rotate(code_replica.begin(), code_replica.begin() + (N - shift_index), code_replica.begin() + N - 1);
+                for (int n = 0; n < prn_replicas - 1; n++) std::copy(code_replica.begin(), code_replica.begin() + N, code_replica.begin() + (n + 1) * N);
+                float peak = 0.0f;
+                if (gb200_acq_wiped_spectrum_peak(s_, stream_, samp_count, reinterpret_cast<const float*>(code_replica.data()), signal_samples, fft_size_extended,
+                        &fine_index_, &peak) != GB200_OK)
+                    return -1;
+                // fftFreqBins[tmp_index_freq] (:443-459)
+                const int k = static_cast<int>(fine_index_);
+                float bin_hz;
+                if (k < fft_size_extended / 2)
+                    bin_hz = ((static_cast<float>(c_.fs_in) / 2.0) * static_cast<float>(k)) / (static_cast<float>(fft_size_extended) / 2.0);
+                else
+                    bin_hz = ((-static_cast<float>(c_.fs_in) / 2.0) * static_cast<float>(fft_size_extended / 2 - (k - fft_size_extended / 2))) /
+                             (static_cast<float>(fft_size_extended) / 2.0);
+                if (std::abs(bin_hz - acq_doppler_hz) < 1000)
+                    {
+                        acq_doppler_hz = static_cast<double>(bin_hz);
+                        fine_accepted_ = true;
+                    }
+            }
+        if (synchro_)
+            {
+                synchro_->Acq_delay_samples = acq_delay_samples;
+                synchro_->Acq_doppler_hz = acq_doppler_hz;
+                synchro_->Acq_samplestamp_samples = r.acq_samplestamp;
+                synchro_->Acq_doppler_step = c_.doppler_step;
+                synchro_->Flag_valid_acquisition = positive;
+            }
+        state_ = 0;
+        return positive ? 1 : 2;
+    }
+
+private:
+    gb200_service* s_;
+    AcqVariantConf c_;
+    gb200_acq* h_ = nullptr;
+    AcqSynchro* synchro_ = nullptr;
+    int stream_;
+    bool ok_ = false, fine_accepted_ = false;
+    int state_ = 0, num_doppler_points_ = 0;
+    uint32_t index_time_ = 0, index_doppler_ = 0, fine_index_ = 0;
+    float first_peak_ = 0.0f, second_peak_ = 0.0f, test_statistics_ = 0.0f;
+    std::vector<std::complex<float>> code_;
 };
 }  // namespace gb200

@@ -270,6 +270,41 @@ int gbh_acqv_attempt(gb200_service* service, int variant, const double* cfg, int
     return ev;
 }
 
+// ---- pcps_acquisition_fine_doppler_cc mirror: one attempt ----
+// cfg = {samples_per_ms, max_dwells, doppler_max, doppler_step, fs_in, threshold, item_type}
+// out = {event, index_time, index_doppler, first_peak, second_peak, test_statistic, Acq_delay_samples, Acq_doppler_hz, fine_index, fine_accepted}
+int gbh_fd_attempt(gb200_service* service, const double* cfg, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count, double* out)
+{
+    AcqVariantConf c;
+    c.samples_per_ms = (int)cfg[0];
+    c.samples_per_code = (int)cfg[0];
+    c.max_dwells = (uint32_t)cfg[1];
+    c.doppler_max = (uint32_t)cfg[2];
+    c.doppler_step = (uint32_t)cfg[3];
+    c.fs_in = (int64_t)cfg[4];
+    c.threshold = (float)cfg[5];
+    c.item_type = (int)cfg[6];
+    B200_Pcps_Acquisition_Fine_Doppler acq(service, c, stream_id);
+    if (!acq.ok()) return -1;
+    AcqSynchro syn;
+    acq.set_gnss_synchro(&syn);
+    if (!acq.set_local_code(reinterpret_cast<const std::complex<float>*>(code_iq), code_items)) return -1;
+    acq.reset();
+    const int ev = acq.run(samp_count);
+    if (ev < 0) return ev;
+    out[0] = ev;
+    out[1] = acq.index_time();
+    out[2] = acq.index_doppler();
+    out[3] = acq.first_peak();
+    out[4] = acq.second_peak();
+    out[5] = acq.test_statistics();
+    out[6] = syn.Acq_delay_samples;
+    out[7] = syn.Acq_doppler_hz;
+    out[8] = acq.fine_index();
+    out[9] = acq.fine_accepted() ? 1.0 : 0.0;
+    return ev;
+}
+
 // ---- Galileo E5a non-coherent I/Q acquisition with CAF filter (gb200_acquisition_variants.hpp) ----
 // cfg = {sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells, bit_transition_flag,
 //        both_signal_components, caf_window_hz, zero_padding, item_type}

@@ -174,7 +174,7 @@ int gb200_acq_set_doppler_grid(gb200_acq* a, uint32_t n_bins, const float* phase
 /* Tong detector arithmetic (pcps_tong_acquisition_cc.cc:330-350): every dwell adds |y|^2 / (N^4 * input_power_of_that_dwell) to
  * the kept grid; gb200_acq_result::peak_mag / test_statistic are the accumulated maximum, decision is always 2 (the
  * caller owns the Tong counter) and gb200_acq_reset starts a new attempt (= set_state(1), :226-252). */
-int gb200_acq_set_scaled_accumulation(gb200_acq* a, int enable);
+int gb200_acq_set_scaled_accumulation(gb200_acq* a, int enable); /* 0 off, 1 scaled (Tong), 2 unscaled sum (fine-Doppler block) */
 /* = reset()/set_state(1): clears dwell counter, step-two state and the magnitude grid */
 int gb200_acq_reset(gb200_acq* a);
 /* = acquisition_core (pcps_acquisition.cc:668-930) for one dwell over d_consumed_samples items of
@@ -208,6 +208,18 @@ typedef struct gb200_acq_iq_bin
     uint32_t picked;   /* bit 0: I component took B; bit 1: Q component took B */
 } gb200_acq_iq_bin;
 int gb200_acq_iq_combine(gb200_acq* ia, gb200_acq* qa, gb200_acq* ib, gb200_acq* qb, float norm, gb200_acq_iq_bin* out);
+
+/* The two device steps pcps_acquisition_fine_doppler_cc adds to the Doppler loop
+ * (src/algorithms/acquisition/gnuradio_blocks/pcps_acquisition_fine_doppler_cc.cc).  Its coarse stage is the plain sum of
+ * |.|^2 over max_dwells dwells (compute_and_accumulate_grid, :343-372): gb200_acq_set_scaled_accumulation(a, 2).
+ * gb200_acq_second_peak = the tail of compute_CAF (:296-322): the maximum of kept grid row `bin` after zeroing
+ * [idx - half_width, idx + half_width) with the block's one-sided wrap and do-while.
+ * gb200_acq_wiped_spectrum_peak = estimate_Doppler's steps 2-4 (:429-441): items [first, first + n_items) of the stream
+ * times `replica_iq` (n_items gr_complex: the caller's 10-period code replica, :412-428), zero-padded to fft_len, forward
+ * FFT, |.|^2, first maximum -> its index (natural frequency order) and value. */
+int gb200_acq_second_peak(gb200_acq* a, uint32_t bin, uint32_t idx, uint32_t half_width, float* second_peak);
+int gb200_acq_wiped_spectrum_peak(gb200_service* s, int stream_id, uint64_t first_sample_index, const float* replica_iq, uint32_t n_items,
+    uint32_t fft_len, uint32_t* peak_index, float* peak_mag);
 
 /* ------------------------------------------------------------------ tracking ------------ */
 #define GB200_MAX_TAPS 8

@@ -1452,3 +1452,192 @@ uint32_t go_acq_resampler_decimation(int64_t fs_in, uint32_t opt_acq_fs)
     while (fs_in % decimation > 0) decimation--;
     return decimation;
 }
+
+
+/* ======================= pcps_acquisition_fine_doppler_cc -- TEST INFRASTRUCTURE, block-level parity unpinned ======================= */
+struct go_fd
+{
+    go_fd_conf c;
+    uint32_t n;
+    int num_points;
+    float** wipeoffs;
+    float** grid;
+    float* fft_code;
+    float* work;
+};
+
+go_fd* go_fd_create(const go_fd_conf* conf)
+{
+    go_fd* a = (go_fd*)calloc(1, sizeof(go_fd));
+    a->c = *conf;
+    a->n = conf->samples_per_ms;
+    /* set_doppler_step (:146-160): floor(|2 doppler_max| / step) points, the last one below +doppler_max */
+    a->num_points = (int)floor(abs(2 * (int)conf->doppler_max) / conf->doppler_step);
+    a->wipeoffs = (float**)calloc((size_t)a->num_points, sizeof(float*));
+    a->grid = (float**)calloc((size_t)a->num_points, sizeof(float*));
+    for (int i = 0; i < a->num_points; i++)
+        {
+            a->wipeoffs[i] = (float*)calloc(2 * (size_t)a->n, sizeof(float));
+            a->grid[i] = (float*)calloc(a->n, sizeof(float));
+            go_sincos(a->wipeoffs[i], -go_fd_phase_step(a, i), 0.0f, (int)a->n);
+        }
+    a->fft_code = (float*)calloc(2 * (size_t)a->n, sizeof(float));
+    a->work = (float*)calloc(2 * (size_t)a->n, sizeof(float));
+    return a;
+}
+
+void go_fd_destroy(go_fd* a)
+{
+    if (!a) return;
+    for (int i = 0; i < a->num_points; i++)
+        {
+            free(a->wipeoffs[i]);
+            free(a->grid[i]);
+        }
+    free(a->wipeoffs);
+    free(a->grid);
+    free(a->fft_code);
+    free(a->work);
+    free(a);
+}
+
+int go_fd_num_doppler_points(const go_fd* a) { return a->num_points; }
+
+/* update_carrier_wipeoff (:246-261): float(GPS_TWO_PI) * int doppler / float(fs), all float32 */
+float go_fd_phase_step(const go_fd* a, int bin)
+{
+    const int doppler_hz = (int)a->c.doppler_step * bin - (int)a->c.doppler_max;
+    return (float)GO_GPS_TWO_PI * doppler_hz / (float)a->c.fs_in;
+}
+
+void go_fd_set_local_code(go_fd* a, const float* code_iq)
+{
+    memcpy(a->work, code_iq, sizeof(float) * 2 * a->n);
+    go_fft_f32(a->work, (int)a->n, -1);
+    for (uint32_t i = 0; i < a->n; i++)
+        {
+            a->fft_code[2 * i] = a->work[2 * i];
+            a->fft_code[2 * i + 1] = -a->work[2 * i + 1];
+        }
+}
+
+void go_fd_replica(const float* code, uint32_t n, int shift_index, float* rep)
+{
+    memcpy(rep, code, sizeof(float) * 2 * n);
+    if (shift_index != 0)
+        {
+            /* std::rotate(first, first + (n - shift), first + n - 1): the LAST element stays where it is (:419-423) */
+            const uint32_t m = n - 1, k = (n - (uint32_t)shift_index) % (m ? m : 1);
+            float* tmp = (float*)malloc(sizeof(float) * 2 * m);
+            for (uint32_t i = 0; i < m; i++)
+                {
+                    tmp[2 * i] = rep[2 * ((i + k) % m)];
+                    tmp[2 * i + 1] = rep[2 * ((i + k) % m) + 1];
+                }
+            memcpy(rep, tmp, sizeof(float) * 2 * m);
+            free(tmp);
+        }
+    for (int r = 1; r < 10; r++) memcpy(rep + 2 * (size_t)r * n, rep, sizeof(float) * 2 * n);
+}
+
+int go_fd_attempt(go_fd* a, const float* in, const float* code_1ms, go_fd_result* out)
+{
+    const uint32_t n = a->n;
+    memset(out, 0, sizeof(*out));
+    for (int i = 0; i < a->num_points; i++) memset(a->grid[i], 0, sizeof(float) * n); /* reset_grid */
+    /* state 1, max_dwells times: compute_and_accumulate_grid (:343-372) */
+    for (uint32_t d = 0; d < a->c.max_dwells; d++)
+        {
+            const float* x = in + 2 * (size_t)d * n;
+            for (int b = 0; b < a->num_points; b++)
+                {
+                    const float* w = a->wipeoffs[b];
+                    for (uint32_t i = 0; i < n; i++)
+                        {
+                            a->work[2 * i] = x[2 * i] * w[2 * i] - x[2 * i + 1] * w[2 * i + 1];
+                            a->work[2 * i + 1] = x[2 * i] * w[2 * i + 1] + x[2 * i + 1] * w[2 * i];
+                        }
+                    go_fft_f32(a->work, (int)n, -1);
+                    for (uint32_t i = 0; i < n; i++)
+                        {
+                            const float xr = a->work[2 * i], xi = a->work[2 * i + 1];
+                            const float cr = a->fft_code[2 * i], ci = a->fft_code[2 * i + 1];
+                            a->work[2 * i] = xr * cr - xi * ci;
+                            a->work[2 * i + 1] = xr * ci + xi * cr;
+                        }
+                    go_fft_f32(a->work, (int)n, +1);
+                    for (uint32_t i = 0; i < n; i++)
+                        a->grid[b][i] = a->grid[b][i] + (a->work[2 * i] * a->work[2 * i] + a->work[2 * i + 1] * a->work[2 * i + 1]);
+                }
+        }
+    /* state 2: compute_CAF (:266-326) */
+    float firstPeak = 0.0f;
+    int index_doppler = 0;
+    uint32_t index_time = 0;
+    for (int i = 0; i < a->num_points; i++)
+        {
+            const uint32_t t = go_index_max(a->grid[i], n);
+            if (a->grid[i][t] > firstPeak)
+                {
+                    firstPeak = a->grid[i][t];
+                    index_doppler = i;
+                    index_time = t;
+                }
+        }
+    const double GPS_L1_CA_CHIP_PERIOD = 9.7752e-07;
+    const uint32_t samplesPerChip = (uint32_t)ceil(GPS_L1_CA_CHIP_PERIOD * (float)a->c.fs_in);
+    int32_t ex1 = (int32_t)(index_time - samplesPerChip), ex2 = (int32_t)(index_time + samplesPerChip);
+    if (ex1 < 0)
+        ex1 = (int32_t)n + ex1;
+    else if (ex2 >= (int32_t)n)
+        ex2 = ex2 - (int32_t)n;
+    int32_t idx = ex1;
+    do
+        {
+            a->grid[index_doppler][idx] = 0.0f;
+            idx++;
+            if (idx == (int32_t)n) idx = 0;
+        }
+    while (idx != ex2);
+    const uint32_t t2 = go_index_max(a->grid[index_doppler], n);
+    const float secondPeak = a->grid[index_doppler][t2];
+    out->index_time = index_time;
+    out->index_doppler = (uint32_t)index_doppler;
+    out->first_peak = firstPeak;
+    out->second_peak = secondPeak;
+    out->test_statistic = firstPeak / secondPeak;
+    out->acq_delay_samples = (double)index_time;
+    out->acq_doppler_hz = (double)(index_doppler * (int)a->c.doppler_step - (int)a->c.doppler_max);
+    out->positive = out->test_statistic > a->c.threshold;
+    if (!out->positive) return 0;
+    /* state 3: estimate_Doppler (:400-479) over the first 10 ms of the attempt */
+    const int signal_samples = 10 * (int)n, ext = signal_samples * 8;
+    float* rep = (float*)malloc(sizeof(float) * 2 * (size_t)signal_samples);
+    float* buf = (float*)calloc(2 * (size_t)ext, sizeof(float));
+    go_fd_replica(code_1ms, n, (int)out->acq_delay_samples, rep);
+    for (int i = 0; i < signal_samples; i++)
+        {
+            buf[2 * i] = in[2 * i] * rep[2 * i] - in[2 * i + 1] * rep[2 * i + 1];
+            buf[2 * i + 1] = in[2 * i] * rep[2 * i + 1] + in[2 * i + 1] * rep[2 * i];
+        }
+    go_fft_f32(buf, ext, -1);
+    float* mag = (float*)malloc(sizeof(float) * (size_t)ext);
+    for (int i = 0; i < ext; i++) mag[i] = buf[2 * i] * buf[2 * i] + buf[2 * i + 1] * buf[2 * i + 1];
+    const uint32_t k = go_index_max(mag, (uint32_t)ext);
+    /* fftFreqBins (:443-459): k < ext/2 -> +, then ext/2 .. 1 counted down with a minus sign */
+    float f;
+    if ((int)k < ext / 2)
+        f = (((float)a->c.fs_in / 2.0) * (float)k) / ((float)ext / 2.0);
+    else
+        f = ((-(float)a->c.fs_in / 2.0) * (float)(ext / 2 - ((int)k - ext / 2))) / ((float)ext / 2.0);
+    out->fine_index = k;
+    if (fabs(f - out->acq_doppler_hz) < 1000)
+        {
+            out->acq_doppler_hz = (double)f;
+            out->fine_accepted = 1;
+        }
+    free(rep);
+    free(buf);
+    free(mag);
+    return 0;
+}

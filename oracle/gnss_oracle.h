@@ -198,6 +198,36 @@ int go_fir_decimate(const float* in_iq, int n_in, const float* taps, int n_taps,
 /* integer decimation the flowgraph / adapters pick (gnss_flowgraph.cc:431-437, gps_l1_ca_pcps_acquisition.cc:97-104) */
 uint32_t go_acq_resampler_decimation(int64_t fs_in, uint32_t opt_acq_fs);
 
+/* ---------------- pcps_acquisition_fine_doppler_cc (grid accumulated over dwells, first/second-peak ratio, zero-padded FFT Doppler refinement) ----------------
+ * Block-level parity UNPINNED (no reference fixture; the block needs GNU Radio); the arithmetic underneath is the pinned go_* code. */
+typedef struct go_fd_conf
+{
+    uint32_t samples_per_ms; /* d_fft_size */
+    uint32_t max_dwells, doppler_max, doppler_step;
+    int64_t fs_in;
+    float threshold;
+} go_fd_conf;
+typedef struct go_fd_result
+{
+    uint32_t index_time, index_doppler;
+    float first_peak, second_peak, test_statistic;
+    int positive;             /* d_test_statistics > d_threshold */
+    double acq_delay_samples, acq_doppler_hz; /* after estimate_Doppler when positive */
+    uint32_t fine_index;      /* tmp_index_freq of the zero-padded FFT (positive only) */
+    int fine_accepted;        /* |fftFreqBins[idx] - coarse| < 1000 */
+} go_fd_result;
+typedef struct go_fd go_fd;
+go_fd* go_fd_create(const go_fd_conf* conf);
+void go_fd_destroy(go_fd* a);
+int go_fd_num_doppler_points(const go_fd* a);
+float go_fd_phase_step(const go_fd* a, int bin);
+void go_fd_set_local_code(go_fd* a, const float* code_iq);
+/* one whole attempt: `in_iq` holds max(max_dwells, 10) * samples_per_ms items from the attempt's first sample; code_1ms_iq is
+ * what gps_l1_ca_code_gen_complex_sampled(.., PRN, fs, 0) returns (the block regenerates it inside estimate_Doppler) */
+int go_fd_attempt(go_fd* a, const float* in_iq, const float* code_1ms_iq, go_fd_result* out);
+/* the replica estimate_Doppler builds (:412-428): 10 * samples_per_ms items, incl. its off-by-one std::rotate */
+void go_fd_replica(const float* code_1ms_iq, uint32_t fft_size, int shift_index, float* replica_iq);
+
 #ifdef __cplusplus
 }
 #endif

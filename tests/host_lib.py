@@ -124,6 +124,7 @@ def host():
                                        C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.gbh_e5a_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, f32p, C.c_size_t, C.c_uint64, C.c_int,
                                       C.POINTER(C.c_double), C.POINTER(C.c_int), f32p]
+        L.gbh_fd_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, C.c_size_t, C.c_uint64, C.POINTER(C.c_double)]
         L.gbh_caid_open.restype = C.c_void_p
         L.gbh_caid_open.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.gbh_caid_start.argtypes = [C.c_void_p, f32p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
@@ -358,3 +359,17 @@ def run_b200_caid(service, stream_id, variant, first_index, code_c64, acq_delay,
         return _caid_run(L.gbh_caid_step, L.gbh_caid_set_preamble, h, n_steps, preamble)
     finally:
         L.gbh_caid_close(h)
+
+
+FD_FIELDS = ("event", "index_time", "index_doppler", "first_peak", "second_peak", "test_statistic", "acq_delay_samples", "acq_doppler_hz", "fine_index",
+             "fine_accepted")
+
+
+def fine_doppler_attempt(service, stream_id, code_1ms_c64, samp_count, samples_per_ms, max_dwells, doppler_max, doppler_step, fs_in, threshold, item_type=0):
+    """B200_Pcps_Acquisition_Fine_Doppler: one attempt; returns (event, dict of FD_FIELDS)."""
+    L = host()
+    cfg = (C.c_double * 7)(samples_per_ms, max_dwells, doppler_max, doppler_step, fs_in, threshold, item_type)
+    code = np.ascontiguousarray(code_1ms_c64, np.complex64).view(np.float32)
+    out = (C.c_double * len(FD_FIELDS))()
+    ev = L.gbh_fd_attempt(service.h, cfg, stream_id, code, len(code) // 2, samp_count, out)
+    return ev, dict(zip(FD_FIELDS, out[:]))

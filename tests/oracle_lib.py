@@ -104,6 +104,15 @@ def oracle():
     L.go_e5a_set_local_code.argtypes = [C.c_void_p, f32p, f32p]
     L.go_e5a_restart.argtypes = [C.c_void_p]
     L.go_e5a_run.argtypes = [C.c_void_p, f32p, C.POINTER(GoE5aResult)]
+    L.go_fd_create.argtypes = [C.POINTER(GoFdConf)]
+    L.go_fd_create.restype = C.c_void_p
+    L.go_fd_destroy.argtypes = [C.c_void_p]
+    L.go_fd_num_doppler_points.argtypes = [C.c_void_p]
+    L.go_fd_phase_step.argtypes = [C.c_void_p, C.c_int]
+    L.go_fd_phase_step.restype = C.c_float
+    L.go_fd_set_local_code.argtypes = [C.c_void_p, f32p]
+    L.go_fd_attempt.argtypes = [C.c_void_p, f32p, f32p, C.POINTER(GoFdResult)]
+    L.go_fd_replica.argtypes = [f32p, C.c_uint32, C.c_int, f32p]
     L.go_firdes_low_pass.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, f32p, C.c_int]
     L.go_fir_decimate.argtypes = [f32p, C.c_int, f32p, C.c_int, C.c_int, f32p]
     L.go_acq_resampler_decimation.argtypes = [C.c_int64, C.c_uint32]
@@ -219,6 +228,54 @@ class GoAcqvResult(C.Structure):
 
 
 ACQV_TONG, ACQV_8MS = 0, 1
+
+
+class GoFdConf(C.Structure):
+    _fields_ = [("samples_per_ms", C.c_uint32), ("max_dwells", C.c_uint32), ("doppler_max", C.c_uint32), ("doppler_step", C.c_uint32),
+                ("fs_in", C.c_int64), ("threshold", C.c_float)]
+
+
+class GoFdResult(C.Structure):
+    _fields_ = [("index_time", C.c_uint32), ("index_doppler", C.c_uint32), ("first_peak", C.c_float), ("second_peak", C.c_float),
+                ("test_statistic", C.c_float), ("positive", C.c_int), ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double),
+                ("fine_index", C.c_uint32), ("fine_accepted", C.c_int)]
+
+
+class OracleFineDoppler:
+    """pcps_acquisition_fine_doppler_cc restatement (oracle/gnss_oracle.c go_fd_*): one attempt per call."""
+
+    def __init__(self, samples_per_ms, max_dwells, doppler_max, doppler_step, fs_in, threshold):
+        self.L = oracle()
+        self.conf = GoFdConf(samples_per_ms, max_dwells, doppler_max, doppler_step, fs_in, threshold)
+        self.h = self.L.go_fd_create(C.byref(self.conf))
+        self.n = samples_per_ms
+        self.num_points = self.L.go_fd_num_doppler_points(self.h)
+
+    def phase_steps(self):
+        return np.array([self.L.go_fd_phase_step(self.h, b) for b in range(self.num_points)], np.float32)
+
+    def attempt(self, samples_c64, code_1ms_c64):
+        code = np.ascontiguousarray(code_1ms_c64, np.complex64).view(np.float32)
+        assert len(code) == 2 * self.n
+        x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
+        assert len(x) >= 2 * self.n * max(10, self.conf.max_dwells)
+        self.L.go_fd_set_local_code(self.h, code)
+        r = GoFdResult()
+        self.L.go_fd_attempt(self.h, x, code, C.byref(r))
+        return r
+
+    def close(self):
+        if self.h:
+            self.L.go_fd_destroy(self.h)
+            self.h = None
+
+
+def fd_replica(code_1ms_c64, shift_index):
+    code = np.ascontiguousarray(code_1ms_c64, np.complex64).view(np.float32)
+    n = len(code) // 2
+    out = np.zeros(20 * n, np.float32)
+    oracle().go_fd_replica(code, n, shift_index, out)
+    return out.view(np.complex64)
 
 
 class GoE5aConf(C.Structure):

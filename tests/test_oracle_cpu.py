@@ -327,3 +327,27 @@ def test_e5a_caf_block_restatement_finds_the_scene():
     rb = o.run(noise)
     assert ra.decision == 2 and rb.decision == 1 and rb.updated == 0 and rb.code_phase_index == delay and rb.test_statistic == ra.test_statistic
     o.close()
+
+
+def test_fine_doppler_block_restatement_refines_the_doppler():
+    """go_fd_* (pcps_acquisition_fine_doppler_cc restated; block-level parity unpinned): two accumulated dwells find the cell on a
+    500 Hz grid, the first/second-peak ratio separates signal from noise, and the zero-padded FFT over 10 ms moves the Doppler to
+    within one 12.5 Hz bin of the truth; the replica reproduces the block's std::rotate that leaves the last chip sample in place."""
+    fs, n, delay, dop = 4000000, 4000, 1234, 1730.0
+    x = synth.make_iq(fs, 10 * n, [dict(kind="gps_l1_ca", prn=5, cn0_dbhz=50.0, doppler_hz=dop, delay_samples=delay)], seed=31)
+    code = np.zeros(2 * n, np.float32)
+    ol.oracle().go_gps_l1_ca_code_sampled(code, 5, fs, 0)
+    code = code.view(np.complex64)
+    o = ol.OracleFineDoppler(n, 2, 5000, 500, fs, 2.5)
+    assert o.num_points == 20 and np.isclose(o.phase_steps()[0], -2 * np.pi * 5000 / fs, rtol=1e-6)
+    r = o.attempt(x, code)
+    assert r.positive == 1 and abs(int(r.index_time) - delay) <= 1 and r.index_doppler in (13, 14) and r.test_statistic > 5.0
+    assert r.fine_accepted == 1 and abs(r.acq_doppler_hz - dop) <= 12.5 and r.acq_delay_samples == r.index_time
+    assert r.fine_index == int(round(r.acq_doppler_hz / (fs / (80.0 * n))))
+    noise = synth.make_iq(fs, 10 * n, [], seed=32)
+    rn = o.attempt(noise, code)
+    assert rn.positive == 0 and rn.test_statistic < 2.0 and rn.fine_accepted == 0
+    o.close()
+    rep = ol.fd_replica(code, 7)
+    want = np.concatenate([np.roll(code[:-1], 7 - 1)[: n - 1] if False else np.concatenate([code[n - 7:n - 1], code[:n - 7]]), code[-1:]])
+    assert np.array_equal(rep[:n], want) and np.array_equal(rep[n:2 * n], rep[:n]) and np.array_equal(rep[9 * n:], rep[:n])
