@@ -1,5 +1,8 @@
 // Small acquisition kernels: conjugate, input power, peak reductions, second-peak statistic.
 #include "acq_fft.cuh"
+#include <cstring>
+#include <mutex>
+#include <string>
 
 namespace
 {
@@ -468,4 +471,65 @@ cudaError_t gb_conj_items(void* d_items, size_t n_items, int item_type, cudaStre
     else
         gb_conj_kernel<signed char><<<blocks, threads, 0, st>>>((signed char*)d_items, n_items);
     return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// gb200_second_peak_noalloc: the second-peak search of gb_acq_second_peak_row for callers that must not allocate (CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The row copy the kernel works on lives in a file-scope device array instead of service scratch:
+// GB200_NOALLOC_MAX_ROW floats (1 MiB) held by every GPU that loads the library until exit.  Every call shares it and it keeps
+// the last call's contents; the kernel overwrites elements [0, n) before it reads them, so nothing has to be cleared, but two
+// calls that overlap on the GPU (different streams, no ordering between them) race on it.
+static __device__ __align__(256) float gb_noalloc_row[GB200_NOALLOC_MAX_ROW];
+
+namespace
+{
+// device address of gb_noalloc_row per device ordinal: in host code the array's name is only a host-side stand-in
+float* g_noalloc_ptr[64] = {};
+std::mutex g_noalloc_mu;
+
+int noalloc_fail(char* err, size_t cap, int code, const std::string& msg)
+{
+    if (err && cap > 0)
+        {
+            strncpy(err, msg.c_str(), cap - 1);
+            err[cap - 1] = 0;
+        }
+    return code;
+}
+}  // namespace
+
+extern "C" int gb200_second_peak_noalloc(const float* d_row, uint32_t n, uint32_t idx, uint32_t half_width, float* d_second, void* cuda_stream, char* err,
+    size_t err_cap)
+{
+    if (!d_row || !d_second) return noalloc_fail(err, err_cap, GB200_E_INVALID, "gb200_second_peak_noalloc: d_row and d_second must be device pointers");
+    if (n > (uint32_t)GB200_NOALLOC_MAX_ROW)
+        return noalloc_fail(err, err_cap, GB200_E_RANGE,
+            "gb200_second_peak_noalloc: row of " + std::to_string(n) + " floats exceeds GB200_NOALLOC_MAX_ROW = " + std::to_string(GB200_NOALLOC_MAX_ROW) +
+                " (the fixed device scratch of this entry point; use gb200_acq_second_peak for longer rows)");
+    if (n == 0 || idx >= n || half_width >= n)
+        return noalloc_fail(err, err_cap, GB200_E_INVALID, "gb200_second_peak_noalloc: need 0 < n, idx < n, half_width < n");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64)
+        return noalloc_fail(err, err_cap, GB200_E_NO_DEVICE, std::string("gb200_second_peak_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[dev])
+            {
+                // once per device, with that device current
+                e = cudaGetSymbolAddress((void**)&g_noalloc_ptr[dev], gb_noalloc_row);
+                if (e != cudaSuccess)
+                    {
+                        g_noalloc_ptr[dev] = nullptr;
+                        return noalloc_fail(err, err_cap, GB200_E_CUDA, std::string("gb200_second_peak_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+                    }
+            }
+        scratch = g_noalloc_ptr[dev];
+    }
+    gb_second_peak_kernel<<<1, 1024, 0, (cudaStream_t)cuda_stream>>>(d_row, (int)n, scratch, (int)n, (int)idx, (int)half_width, d_second, 1);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return noalloc_fail(err, err_cap, GB200_E_CUDA, std::string("gb200_second_peak_noalloc: launch: ") + cudaGetErrorString(e));
+    return GB200_OK;
 }

@@ -79,7 +79,7 @@ EXPORTS = [
     "gb200_service_measure_fp32", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
-    "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine", "gb200_acq_second_peak", "gb200_acq_wiped_spectrum_peak",
+    "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine", "gb200_acq_second_peak", "gb200_acq_wiped_spectrum_peak", "gb200_second_peak_noalloc",
     "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_set_taps", "gb200_trk_correlate",
     "gb200_trk_correlate_batch", "gb200_trk_correlate_16sc", "gb200_trk_correlate_16sc_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
 ]
@@ -139,6 +139,7 @@ def lib():
     L.gb200_acq_read_grid.argtypes = [vp, vp]
     L.gb200_acq_iq_combine.argtypes = [vp, vp, vp, vp, f, C.POINTER(AcqIqBin)]
     L.gb200_acq_second_peak.argtypes = [vp, u32, u32, u32, C.POINTER(C.c_float)]
+    L.gb200_second_peak_noalloc.argtypes = [vp, u32, u32, u32, vp, vp, C.c_char_p, C.c_size_t]
     L.gb200_acq_wiped_spectrum_peak.argtypes = [vp, i, u64, vp, u32, u32, C.POINTER(u32), C.POINTER(C.c_float)]
     L.gb200_trk_create.argtypes = [vp, C.POINTER(TrkCfg), C.POINTER(vp)]
     L.gb200_trk_destroy.argtypes = [vp]

@@ -221,6 +221,19 @@ int gb200_acq_second_peak(gb200_acq* a, uint32_t bin, uint32_t idx, uint32_t hal
 int gb200_acq_wiped_spectrum_peak(gb200_service* s, int stream_id, uint64_t first_sample_index, const float* replica_iq, uint32_t n_items,
     uint32_t fft_len, uint32_t* peak_index, float* peak_mag);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same second-peak search as
+ * gb200_acq_second_peak, on a row the CALLER holds in device memory: *d_second (device pointer) = maximum of d_row[0..n) after
+ * zeroing [idx - half_width, idx + half_width) with the block's one-sided wrap and do-while.  Allocates nothing (no
+ * cudaMalloc / cudaFree / service, no synchronisation): the launch is issued on `cuda_stream` (a cudaStream_t, may be 0) of the
+ * CURRENT device and the working copy of the row lives in a fixed device array of GB200_NOALLOC_MAX_ROW floats (1 MiB per GPU
+ * that loads the library, held until exit).  n > GB200_NOALLOC_MAX_ROW -> GB200_E_RANGE.  All calls share that array, which
+ * keeps the last call's contents (every element read is overwritten first, nothing needs clearing): calls that overlap on the
+ * GPU race -- order them on one stream or with events.  `err` (may be NULL) receives the message of a failed call. */
+#define GB200_NOALLOC_MAX_ROW 262144
+int gb200_second_peak_noalloc(const float* d_row, uint32_t n, uint32_t idx, uint32_t half_width, float* d_second, void* cuda_stream, char* err,
+    size_t err_cap);
+
 /* ------------------------------------------------------------------ tracking ------------ */
 #define GB200_MAX_TAPS 8
 #define GB200_CODE_REAL 0 /* Cpu_Multicorrelator_Real_Codes (float codes)        */
