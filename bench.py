@@ -31,6 +31,7 @@ N_FFT = 32_000          # 4 ms at 8 Msps
 N_PRN = 32
 DOPPLER_MAX, DOPPLER_STEP = 5000, 125
 N_BINS = 80
+ACQ_THRESHOLD = 7e-4     # CFAR statistic: noise-only maxima of the 2.56 M-cell grid reach ~6e-4, a 40 dB-Hz E1B reaches 9e-4
 N_CH = 32
 N_EPOCH = 248
 EPOCH = 32_000
@@ -46,18 +47,20 @@ NCU_PAIR_DRAM_BYTES = 73.8e6
 NCU_TRK_DRAM_BYTES = 35.3e6
 
 
-def build_stream(seed):
-    """Synthetic C2 stream: 10 E1 satellites (B - C), CN0 44..35 dB-Hz, int16 at 2^10 LSB per sigma."""
+def build_stream(seed, items=None):
+    """Synthetic C2 stream: 10 E1 satellites (B - C), CN0 44..35 dB-Hz, int16 at 2^10 LSB per sigma.
+    `items` < STREAM_ITEMS returns the identical prefix (noise is drawn in 1 M-item blocks)."""
     import synth
 
     sats = [dict(kind="gal_e1b_sinboc", pilot_kind="gal_e1c_sinboc", prn=1 + 3 * k, cn0_dbhz=44 - k, doppler_hz=-4500 + 1000 * k,
                  delay_samples=1000 + 2917 * k) for k in range(10)]
     rng = np.random.default_rng(seed)
     # noise in float32 blocks (8 M complex samples); signals added block-wise to bound memory
-    out = np.empty(2 * STREAM_ITEMS, np.int16)
+    total = STREAM_ITEMS if items is None else -(-int(items) // 1_000_000) * 1_000_000
+    out = np.empty(2 * total, np.int16)
     blk = 1_000_000
-    for b0 in range(0, STREAM_ITEMS, blk):
-        n = min(blk, STREAM_ITEMS - b0)
+    for b0 in range(0, total, blk):
+        n = min(blk, total - b0)
         x = (rng.standard_normal(n, np.float32) + 1j * rng.standard_normal(n, np.float32)).astype(np.complex64)
         t = (b0 + np.arange(n, dtype=np.float64)) / FS
         for s in sats:
@@ -258,7 +261,7 @@ def run_b200(args, rank, local_rank, world):
     acqs = []
     for p in range(N_PRN):
         a = gb.Acquisition(svc, sampled_ms=4, ms_per_code=4, samples_per_chip=8, doppler_max=DOPPLER_MAX, doppler_step=DOPPLER_STEP,
-                           fs_in=FS, samples_per_ms=8000.0, samples_per_code=float(N_FFT), threshold=2.5e-4, item_type=gb.ITEM_16IC)
+                           fs_in=FS, samples_per_ms=8000.0, samples_per_code=float(N_FFT), threshold=ACQ_THRESHOLD, item_type=gb.ITEM_16IC)
         a.set_local_code(np.roll(codes[p], 131 * rank))
         acqs.append(a)
     handles = gb.acq_handles(acqs)
