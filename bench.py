@@ -253,6 +253,7 @@ def run_b200(args, rank, local_rank, world):
     host_ptr = host_stream.data_ptr()
 
     svc = gb.Service(device=dev, ring_capacity=1 << 24, ring_slack=1 << 20)
+    tuned = svc.tune_from_env()  # GB200_TUNE (profiling sweeps only; recorded in the line when set)
     fp32_peak = svc.measure_fp32_tflops()
     hbm_peak, peak_src = measured_peaks()
 

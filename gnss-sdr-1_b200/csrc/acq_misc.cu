@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(1024) gb_grid_peaks_kernel(float* const* grids
 //   memcpy(d_tmp_buffer, row, d_fft_size BYTES)  -> only the first N/4 floats are refreshed (quirk 1)
 //   zero [idx - spc, idx + spc) with the one-sided wrap of :637-644 (quirk 2), do-while semantics
 //   second peak = first maximum of d_tmp_buffer[0..N)
-__global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, int row_len, float* tmp, int N, int idx, int spc, float* second, int ncopy_all)
+__device__ __forceinline__ void second_peak_body(const float* row, int row_len, float* tmp, int N, int idx, int spc, float* second, int ncopy_all)
 {
     const int ncopy = ncopy_all ? min(N, row_len) : min(N / 4, row_len);
     for (int i = threadIdx.x; i < ncopy; i += blockDim.x) tmp[i] = row[i];
@@ -179,6 +179,19 @@ __global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, 
         }
     best = peak_block_reduce(best);
     if (threadIdx.x == 0) *second = best.mag;
+}
+
+__global__ void __launch_bounds__(1024) gb_second_peak_kernel(const float* row, int row_len, float* tmp, int N, int idx, int spc, float* second, int ncopy_all)
+{
+    second_peak_body(row, row_len, tmp, N, idx, spc, second, ncopy_all);
+}
+
+// the same for every handle of a batch group, one CTA each: the winning (bin, index) comes from the peak record the grid scan
+// left on the device, so nothing crosses to the host between the scan and the second-peak search
+__global__ void __launch_bounds__(1024) gb_second_peak_batch_kernel(float* const* grids, float* const* tmps, const GbPeak* peaks, int row_len, int N, int spc, float* seconds)
+{
+    const GbPeak pk = peaks[blockIdx.x];
+    second_peak_body(grids[blockIdx.x] + (size_t)pk.bin * row_len, N, tmps[blockIdx.x], N, (int)pk.idx, spc, seconds + blockIdx.x, 0);
 }
 
 // galileo_e5a_noncoherent_iq_acquisition_caf_cc.cc:466-606, one CTA per Doppler bin (see gb200_acq_iq_combine in the header)
@@ -297,6 +310,14 @@ cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_le
 cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches)
 {
     gb_second_peak_kernel<<<1, 1024, 0, st>>>(grid_row, N, tmp_buffer, N, idx, samples_per_chip, d_second, 0);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+
+cudaError_t gb_acq_second_peak_batch(float* const* grids, float* const* tmps, const GbPeak* d_peaks, int n_handles, int row_len, int N, int samples_per_chip,
+    float* d_seconds, cudaStream_t st, int* launches)
+{
+    gb_second_peak_batch_kernel<<<n_handles, 1024, 0, st>>>(grids, tmps, d_peaks, row_len, N, samples_per_chip, d_seconds);
     if (launches) (*launches)++;
     return cudaGetLastError();
 }
@@ -511,8 +532,9 @@ extern "C" int gb200_second_peak_noalloc(const float* d_row, uint32_t n, uint32_
         return noalloc_fail(err, err_cap, GB200_E_INVALID, "gb200_second_peak_noalloc: need 0 < n, idx < n, half_width < n");
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess || dev < 0 || dev >= 64)
-        return noalloc_fail(err, err_cap, GB200_E_NO_DEVICE, std::string("gb200_second_peak_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+    if (e != cudaSuccess) return noalloc_fail(err, err_cap, GB200_E_NO_DEVICE, std::string("gb200_second_peak_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64)
+        return noalloc_fail(err, err_cap, GB200_E_UNSUPPORTED, "gb200_second_peak_noalloc: device ordinal " + std::to_string(dev) + " outside the 64 this entry point keeps an address for");
     float* scratch = nullptr;
     {
         std::lock_guard<std::mutex> lk(g_noalloc_mu);

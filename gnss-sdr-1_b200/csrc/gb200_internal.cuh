@@ -211,6 +211,8 @@ cudaError_t gb_acq_iq_combine(const float* const rows[4], int n_bins, int row_le
 cudaError_t gb_acq_second_peak_row(const float* grid_row, float* tmp_row, int N, int idx, int half_width, float* d_second, cudaStream_t st, int* launches);
 cudaError_t gb_acq_code_wipe(const void* samples, int item_type, const float2* replica, int n, float2* out, cudaStream_t st, int* launches);
 cudaError_t gb_acq_spectrum_peak(const float2* spectrum, int N1, int N2, GbPeak* d_out, cudaStream_t st, int* launches);
+cudaError_t gb_acq_second_peak_batch(float* const* grids, float* const* tmps, const GbPeak* d_peaks, int n_handles, int row_len, int N, int samples_per_chip,
+    float* d_seconds, cudaStream_t st, int* launches);
 cudaError_t gb_acq_second_peak(const float* grid_row, float* tmp_buffer, int N, int idx, int samples_per_chip, float* d_second, cudaStream_t st, int* launches);
 cudaError_t gb_acq_copy_f32(float* dst, const float* src, int n, cudaStream_t st, int* launches);
 size_t gb_acq_col_smem(const GbFftPlan& plan);

@@ -95,6 +95,46 @@ struct GbKernelTiming
     uint64_t count[GB200_KCLASS_COUNT] = {0};
 };
 
+// ---- batched acquisition: launch -> collect hand-over (one per service) ----
+struct AcqGroup
+{
+    std::vector<int> members;  // indices into the caller's list
+    std::vector<float> steps;
+    bool grid = false;
+    int mode_key = 0;          // grid-keeping handles share a group only when they run the same column-kernel mode
+    size_t off_segs = 0, off_segoff = 0, off_code = 0, off_grid = 0, off_tmp = 0;  // byte offsets in the upload arena
+    size_t off_power = 0, off_peaks = 0, off_second = 0;                          // byte offsets in the result arena
+};
+struct AcqBatchCtx
+{
+    std::vector<AcqGroup> groups;
+    bool active = false;
+    // results land in a pinned buffer of the batch's own (not the service's shared staging area, which
+    // gb200_acq_set_local_code reuses between launch and collect)
+    char* h_res = nullptr;
+    size_t h_res_bytes = 0;
+    size_t res_bytes = 0;
+    // signature of the launched batch: when the next launch has the same one the group tables on the device are reused
+    std::vector<uint64_t> sig;
+    size_t up_bytes = 0;
+};
+
+// Tuning switches of the acquisition inverse side (gb200_service_set_tuning); 0 = the default of each
+struct GbTuning
+{
+    int lanes = 2;        // streams the inverse chunks alternate on
+    int l2_mb = 48;       // row-buffer budget across the lanes
+    int chunk_t = 0;      // transforms per chunk (0: from l2_mb)
+    int fused = 0;        // one persistent launch for the inverse side
+    int fused_lag = 80, fused_ring = 176;
+    int split_n1 = 0;     // force N1 of the four-step split
+    int variant = 0;      // alternative kernel instantiation of a split
+    int generic = 0;      // run-time parametrised kernels only
+    int host_threads = 8; // request staging threads of long tracking batches
+    int trk_chunk_max = 32768;
+    int trace = 0;
+};
+
 struct gb200_service
 {
     int device = 0;
@@ -162,6 +202,8 @@ struct gb200_service
     GbKernelTiming kt;
     void* d_flush = nullptr;
     size_t flush_bytes = 0;
+    AcqBatchCtx acq_ctx;
+    GbTuning tune;
 
     void set_error(const std::string& e)
     {
@@ -292,6 +334,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
         if (s->d_scratch[i]) cudaFree(s->d_scratch[i]);
     if (s->h16) cudaFreeHost(s->h16);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    if (s->acq_ctx.h_res) cudaFreeHost(s->acq_ctx.h_res);
     if (s->d_flush) cudaFree(s->d_flush);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -497,6 +540,42 @@ extern "C" int gb200_service_flush_l2(gb200_service* s, size_t bytes)
             s->flush_bytes = bytes;
         }
     GB_CUDA(s, cudaMemsetAsync(s->d_flush, 0x5a, bytes, s->stream));
+    return GB200_OK;
+}
+
+// Tuning switches (profiling / experiments; every default is the measured best).  Keys: "acq_lanes" (1..4), "acq_l2_mb",
+// "acq_chunk_t", "acq_fused", "acq_fused_lag", "acq_fused_ring", "host_threads", "trk_chunk_max", "trace"; and, only before the
+// first acquisition handle of a given FFT length exists (they shape the cached plan): "acq_split_n1", "acq_variant", "acq_generic".
+extern "C" int gb200_service_set_tuning(gb200_service* s, const char* key, int value)
+{
+    if (!s || !key) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    const std::string k(key);
+    GbTuning& t = s->tune;
+    if (k == "acq_lanes") t.lanes = value;
+    else if (k == "acq_l2_mb") t.l2_mb = value;
+    else if (k == "acq_chunk_t") t.chunk_t = value;
+    else if (k == "acq_fused") t.fused = value;
+    else if (k == "acq_fused_lag") t.fused_lag = value;
+    else if (k == "acq_fused_ring") t.fused_ring = value;
+    else if (k == "host_threads") t.host_threads = value;
+    else if (k == "trk_chunk_max") t.trk_chunk_max = value;
+    else if (k == "trace") t.trace = value;
+    else if (k == "acq_split_n1" || k == "acq_variant" || k == "acq_generic")
+        {
+            if (!s->plans.empty())
+                {
+                    s->set_error("gb200_service_set_tuning: " + k + " must be set before the first acquisition handle is created");
+                    return GB200_E_STATE;
+                }
+            (k == "acq_split_n1" ? t.split_n1 : (k == "acq_variant" ? t.variant : t.generic)) = value;
+        }
+    else
+        {
+            s->set_error("gb200_service_set_tuning: unknown key " + k);
+            return GB200_E_INVALID;
+        }
+    s->acq_ctx.sig.clear();
     return GB200_OK;
 }
 
@@ -746,6 +825,20 @@ extern "C" int gb200_stream_push(gb200_service* s, int stream_id, const void* sa
     return ring_push(s, stream_id, samples, n_items, item_type, first_sample_index, cudaMemcpyHostToDevice);
 }
 
+extern "C" int gb200_stream_wait(gb200_service* s, int stream_id)
+{
+    if (!s || stream_id < 0 || stream_id >= (int)s->rings.size()) return GB200_E_INVALID;
+    cudaEvent_t ev;
+    {
+        std::lock_guard<std::recursive_mutex> lk(s->mu);
+        ev = s->rings[stream_id].ev_pushed;
+    }
+    if (!ev) return GB200_OK;  // nothing pushed yet
+    cudaSetDevice(s->device);
+    GB_CUDA(s, cudaEventSynchronize(ev));
+    return GB200_OK;
+}
+
 extern "C" int gb200_stream_push_device(gb200_service* s, int stream_id, const void* d_samples, size_t n_items, int item_type, uint64_t first_sample_index)
 {
     return ring_push(s, stream_id, d_samples, n_items, item_type, first_sample_index, cudaMemcpyDeviceToDevice);
@@ -831,16 +924,14 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
             best1 = n1;
         }
     {
-        // prefer a split with compile-time inverse kernels (GB200_ACQ_SPLIT=<n1> steers away from it, tuning only)
-        const char* force = getenv("GB200_ACQ_GENERIC");
-        const char* split = getenv("GB200_ACQ_SPLIT");
+        // prefer a split with compile-time inverse kernels (tuning key "acq_split_n1" steers away from it)
         int p1 = 0, p2 = 0, r[GB200_MAX_RADIX_PASSES], nr;
-        if (!(force && force[0] == '1'))
+        if (!s->tune.generic)
             {
                 bool ok = false;
-                if (split && atoi(split) > 0 && N % atoi(split) == 0)
+                if (s->tune.split_n1 > 0 && N % s->tune.split_n1 == 0)
                     {
-                        p1 = atoi(split);
+                        p1 = s->tune.split_n1;
                         p2 = N / p1;
                         ok = true;
                     }
@@ -865,13 +956,11 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
     e.plan.tile2 = pick_tile(e.plan.N2);
     e.plan.inv_tile1 = e.plan.tile1;
     {
-        // compile-time specialised inverse kernels for the common (N1, N2) pairs; GB200_ACQ_GENERIC=1 forces the general path
+        // compile-time specialised inverse kernels for the common (N1, N2) pairs; tuning key "acq_generic" forces the general path
         int t1 = 0, t2 = 0;
-        const char* force = getenv("GB200_ACQ_GENERIC");
-        const char* var = getenv("GB200_ACQ_VARIANT");
-        int variant = var ? atoi(var) : 0;
+        int variant = s->tune.variant;
         if (!gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, variant, &t1, &t2)) variant = 0;
-        if (!(force && force[0] == '1') && gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, variant, &t1, &t2))
+        if (!s->tune.generic && gb_acq_inverse_tiles(e.plan.N1, e.plan.N2, variant, &t1, &t2))
             {
                 e.plan.inv_fast = 1;
                 e.plan.inv_variant = variant;
@@ -939,6 +1028,7 @@ struct gb200_acq
     uint64_t pending_first = 0;
     int pending_group = -1, pending_slot = -1;
     bool pending = false;
+    uint64_t cfg_epoch = 0;  // bumped by every setter that changes grouping, tables or device pointers (batch signature)
 
     // sibling blocks served through the same Doppler loop
     std::vector<float> custom_steps;  // gb200_acq_set_doppler_grid: phase step per bin replaces the doppler_max/doppler_step rule
@@ -1106,6 +1196,7 @@ extern "C" int gb200_acq_destroy(gb200_acq* a)
     std::lock_guard<std::recursive_mutex> lk(a->s->mu);
     cudaSetDevice(a->s->device);
     cudaStreamSynchronize(a->s->stream);
+    a->s->acq_ctx.sig.clear();  // a later handle may reuse this address
     if (a->d_code_fft) cudaFree(a->d_code_fft);
     if (a->d_grid) cudaFree(a->d_grid);
     if (a->d_tmp) cudaFree(a->d_tmp);
@@ -1181,6 +1272,7 @@ extern "C" int gb200_acq_set_doppler(gb200_acq* a, uint32_t doppler_max, uint32_
     a->c.doppler_max = doppler_max;
     a->c.doppler_step = doppler_step;
     a->c.freq_offset_hz = freq_offset_hz;
+    a->cfg_epoch++;
     acq_derive(a);
     return acq_alloc_grid(a);
 }
@@ -1197,6 +1289,7 @@ extern "C" int gb200_acq_set_doppler_grid(gb200_acq* a, uint32_t n_bins, const f
         }
     a->custom_steps.assign(phase_step_rad, phase_step_rad + n_bins);
     a->num_bins = n_bins;
+    a->cfg_epoch++;
     return acq_alloc_grid(a);
 }
 
@@ -1211,6 +1304,7 @@ extern "C" int gb200_acq_set_scaled_accumulation(gb200_acq* a, int enable)
             return GB200_E_INVALID;
         }
     a->scaled_accum = enable == 2 ? 2 : (enable != 0 ? 1 : 0);
+    a->cfg_epoch++;
     return acq_alloc_grid(a);
 }
 
@@ -1227,6 +1321,7 @@ extern "C" int gb200_acq_keep_grid(gb200_acq* a, int keep)
     std::lock_guard<std::recursive_mutex> lk(a->s->mu);
     cudaSetDevice(a->s->device);
     a->keep_grid = keep != 0;
+    a->cfg_epoch++;
     return acq_alloc_grid(a);
 }
 
@@ -1377,28 +1472,15 @@ extern "C" int gb200_acq_wiped_spectrum_peak(gb200_service* s, int stream_id, ui
 // ---- batched acquisition: launch (asynchronous) / collect ----
 namespace
 {
-struct AcqGroup
-{
-    std::vector<int> members;  // indices into the caller's list
-    std::vector<float> steps;
-    bool grid = false;
-    size_t off_segs = 0, off_segoff = 0, off_code = 0, off_grid = 0, off_tmp = 0;  // byte offsets in the upload arena
-    size_t off_power = 0, off_peaks = 0;                            // byte offsets in the result arena
-};
-struct AcqBatchCtx
-{
-    std::vector<AcqGroup> groups;
-    std::vector<char> h_results;
-    bool active = false;
-};
-AcqBatchCtx g_unused_ctx;
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 }  // namespace
 
-static std::map<gb200_service*, AcqBatchCtx>& acq_ctx_map()
+// what decides which column-kernel mode a grid-keeping handle runs in: handles may share a group (one forward side, one launch
+// sequence) only when these agree
+static int acq_mode_key(const gb200_acq* a)
 {
-    static std::map<gb200_service*, AcqBatchCtx> m;
-    return m;
+    if (!a->need_grid()) return 0;
+    return 1 | (a->use_cfar ? 2 : 0) | (a->scaled_accum << 2) | (a->dwell_counter >= 1 ? 16 : 0) | ((int)a->c.samples_per_chip << 8);
 }
 
 extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index)
@@ -1407,7 +1489,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
     gb200_service* s = list[0]->s;
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
-    AcqBatchCtx& ctx = acq_ctx_map()[s];
+    AcqBatchCtx& ctx = s->acq_ctx;
     if (ctx.active)
         {
             s->set_error("gb200_acq_launch_batch: previous batch not collected");
@@ -1425,82 +1507,117 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                 if (list[j] == list[i]) return GB200_E_INVALID;
         }
     { int rc0 = rings_acquire(s); if (rc0) return rc0; }
-    // group handles that can share the wiped-off forward spectra
-    ctx.groups.clear();
-    std::vector<float> steps;
+    // Signature of the batch: the handles, what their Doppler grids / modes were last set to, and the state bits that pick a
+    // kernel mode.  A launch with the signature of the previous one (the steady state: the same channels searching block after
+    // block) reuses the group tables already on the device: no host rebuild, no upload, no wait for the stream.
+    std::vector<uint64_t> sig;
+    sig.reserve(3 * (size_t)n + 1);
+    sig.push_back((uint64_t)n);
     for (int i = 0; i < n; i++)
         {
-            gb200_acq* a = list[i];
-            acq_bin_steps(a, steps);
-            bool placed = false;
-            if (!a->need_grid())
-                for (auto& g : ctx.groups)
-                    {
-                        gb200_acq* b = list[g.members[0]];
-                        if (!g.grid && b->fft_size == a->fft_size && b->consumed == a->consumed && b->c.item_type == a->c.item_type &&
-                            b->c.bit_transition_flag == a->c.bit_transition_flag && g.steps == steps)
-                            {
-                                g.members.push_back(i);
-                                placed = true;
-                                break;
-                            }
-                    }
-            if (!placed)
-                {
-                    AcqGroup g;
-                    g.members.push_back(i);
-                    g.steps = steps;
-                    g.grid = a->need_grid();
-                    ctx.groups.push_back(g);
-                }
+            sig.push_back((uint64_t)(uintptr_t)list[i]);
+            sig.push_back((list[i]->cfg_epoch << 8) | (uint64_t)(list[i]->step_two ? 1 : 0) | ((uint64_t)(acq_mode_key(list[i]) & 0x7f) << 1));
+            uint32_t center_bits = 0;  // the step-two grid is centred on the coarse estimate (:383-390)
+            if (list[i]->step_two) memcpy(&center_bits, &list[i]->doppler_center_step_two, sizeof center_bits);
+            sig.push_back(center_bits);
         }
-    // arenas
-    size_t up = 0, res = 0;
-    for (auto& g : ctx.groups)
-        {
-            gb200_acq* a0 = list[g.members[0]];
-            if (a0->seg_steps != g.steps || a0->seg_offs.empty())
-                {
-                    acq_all_segments(g.steps, a0->fft_size, a0->segs, a0->seg_offs);
-                    a0->seg_steps = g.steps;
-                }
-            g.off_segs = up;
-            up = align_up(up + a0->segs.size() * sizeof(GbWipeSeg), 16);
-            g.off_segoff = up;
-            up = align_up(up + a0->seg_offs.size() * sizeof(int), 16);
-            g.off_code = up;
-            up = align_up(up + g.members.size() * sizeof(void*), 16);
-            g.off_grid = up;
-            up = align_up(up + g.members.size() * sizeof(void*), 16);
-            g.off_tmp = up;
-            up = align_up(up + g.members.size() * sizeof(void*), 16);
-            g.off_power = res;
-            res = align_up(res + 2 * sizeof(float), 16);  // input power, Tong scale
-            g.off_peaks = res;
-            res = align_up(res + g.members.size() * sizeof(GbPeak), 16);
-        }
-    void *h_up, *d_up, *d_res;
+    const bool reuse = !ctx.sig.empty() && sig == ctx.sig;
+    void *h_up = nullptr, *d_up, *d_res;
     int rc;
-    if ((rc = s->pinned(up + res, &h_up))) return rc;
-    GB_CUDA(s, cudaStreamSynchronize(s->stream));
-    if ((rc = s->scratch(4, up, &d_up))) return rc;
-    if ((rc = s->scratch(5, res, &d_res))) return rc;
-    for (auto& g : ctx.groups)
+    if (!reuse)
         {
-            {
-                gb200_acq* a0 = list[g.members[0]];
-                memcpy((char*)h_up + g.off_segs, a0->segs.data(), a0->segs.size() * sizeof(GbWipeSeg));
-                memcpy((char*)h_up + g.off_segoff, a0->seg_offs.data(), a0->seg_offs.size() * sizeof(int));
-            }
-            for (size_t k = 0; k < g.members.size(); k++)
+            ctx.sig.clear();
+            // group handles that can share the wiped-off forward spectra
+            ctx.groups.clear();
+            std::vector<float> steps;
+            for (int i = 0; i < n; i++)
                 {
-                    gb200_acq* a = list[g.members[k]];
-                    ((const float2**)((char*)h_up + g.off_code))[k] = a->d_code_fft;
-                    ((float**)((char*)h_up + g.off_grid))[k] = g.grid ? a->d_grid : nullptr;
-                    ((float**)((char*)h_up + g.off_tmp))[k] = a->d_tmp;
+                    gb200_acq* a = list[i];
+                    acq_bin_steps(a, steps);
+                    const int key = acq_mode_key(a);
+                    bool placed = false;
+                    for (auto& g : ctx.groups)
+                        {
+                            gb200_acq* b = list[g.members[0]];
+                            if (g.mode_key == key && b->fft_size == a->fft_size && b->consumed == a->consumed && b->c.item_type == a->c.item_type &&
+                                b->c.bit_transition_flag == a->c.bit_transition_flag && g.steps == steps)
+                                {
+                                    g.members.push_back(i);
+                                    placed = true;
+                                    break;
+                                }
+                        }
+                    if (!placed)
+                        {
+                            AcqGroup g;
+                            g.members.push_back(i);
+                            g.steps = steps;
+                            g.grid = a->need_grid();
+                            g.mode_key = key;
+                            ctx.groups.push_back(g);
+                        }
                 }
+            // arenas
+            size_t up = 0, res = 0;
+            for (auto& g : ctx.groups)
+                {
+                    gb200_acq* a0 = list[g.members[0]];
+                    if (a0->seg_steps != g.steps || a0->seg_offs.empty())
+                        {
+                            acq_all_segments(g.steps, a0->fft_size, a0->segs, a0->seg_offs);
+                            a0->seg_steps = g.steps;
+                        }
+                    g.off_segs = up;
+                    up = align_up(up + a0->segs.size() * sizeof(GbWipeSeg), 16);
+                    g.off_segoff = up;
+                    up = align_up(up + a0->seg_offs.size() * sizeof(int), 16);
+                    g.off_code = up;
+                    up = align_up(up + g.members.size() * sizeof(void*), 16);
+                    g.off_grid = up;
+                    up = align_up(up + g.members.size() * sizeof(void*), 16);
+                    g.off_tmp = up;
+                    up = align_up(up + g.members.size() * sizeof(void*), 16);
+                    g.off_power = res;
+                    res = align_up(res + 2 * sizeof(float), 16);  // input power, Tong scale
+                    g.off_peaks = res;
+                    res = align_up(res + g.members.size() * sizeof(GbPeak), 16);
+                    g.off_second = res;
+                    res = align_up(res + g.members.size() * sizeof(float), 16);
+                }
+            if ((rc = s->pinned(up, &h_up))) return rc;
+            GB_CUDA(s, cudaStreamSynchronize(s->stream));  // the staging buffer / the device tables may still be in use
+            if (res > ctx.h_res_bytes)
+                {
+                    if (ctx.h_res) cudaFreeHost(ctx.h_res);
+                    ctx.h_res = nullptr;
+                    ctx.h_res_bytes = 0;
+                    GB_CUDA(s, cudaMallocHost((void**)&ctx.h_res, 2 * res));
+                    ctx.h_res_bytes = 2 * res;
+                }
+            ctx.res_bytes = res;
+            ctx.up_bytes = up;
         }
-    GB_CUDA(s, cudaMemcpyAsync(d_up, h_up, up, cudaMemcpyHostToDevice, s->stream));
+    if ((rc = s->scratch(4, ctx.up_bytes, &d_up))) return rc;
+    if ((rc = s->scratch(5, ctx.res_bytes, &d_res))) return rc;
+    if (!reuse)
+        {
+            for (auto& g : ctx.groups)
+                {
+                    {
+                        gb200_acq* a0 = list[g.members[0]];
+                        memcpy((char*)h_up + g.off_segs, a0->segs.data(), a0->segs.size() * sizeof(GbWipeSeg));
+                        memcpy((char*)h_up + g.off_segoff, a0->seg_offs.data(), a0->seg_offs.size() * sizeof(int));
+                    }
+                    for (size_t k = 0; k < g.members.size(); k++)
+                        {
+                            gb200_acq* a = list[g.members[k]];
+                            ((const float2**)((char*)h_up + g.off_code))[k] = a->d_code_fft;
+                            ((float**)((char*)h_up + g.off_grid))[k] = g.grid ? a->d_grid : nullptr;
+                            ((float**)((char*)h_up + g.off_tmp))[k] = a->d_tmp;
+                        }
+                }
+            GB_CUDA(s, cudaMemcpyAsync(d_up, h_up, ctx.up_bytes, cudaMemcpyHostToDevice, s->stream));
+        }
 
     int l = 0;
     for (auto& g : ctx.groups)
@@ -1528,19 +1645,24 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag || list[m]->scaled_accum;
             float* d_power = (float*)((char*)d_res + g.off_power);
             if (want_power)
-                GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, N, d_power, (g.grid && !a0->use_cfar) ? a0->d_tmp : nullptr, s->stream, &l));
+                {
+                    const bool image = g.grid && !a0->use_cfar;  // the |x|^2 image the block leaves in d_tmp_buffer
+                    GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, N, d_power, image ? a0->d_tmp : nullptr, s->stream, &l));
+                    if (image)
+                        for (size_t k = 1; k < g.members.size(); k++)
+                            GB_CUDA(s, cudaMemcpyAsync(list[g.members[k]]->d_tmp, a0->d_tmp, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));
+                }
             // inverse side in L2-sized chunks of transforms
             const int T = bins * (int)g.members.size();
             // Two lanes: chunk c runs on stream (c & 1) with its own row buffer, so one lane's column kernel overlaps the
             // other lane's row kernel and each kernel's ragged last wave is filled by the other lane.  Both row buffers
             // together stay within the L2 budget.  With per-launch event timing on, everything stays on one stream.
-            static const int lanes_cfg = getenv("GB200_ACQ_ONE_LANE") ? 1 : (getenv("GB200_ACQ_LANES") ? std::max(1, std::min(4, atoi(getenv("GB200_ACQ_LANES")))) : 2);
-            static const size_t l2_total = (size_t)(getenv("GB200_ACQ_L2_MB") ? std::max(4, atoi(getenv("GB200_ACQ_L2_MB"))) : 48) << 20;
+            const int lanes_cfg = std::max(1, std::min(4, s->tune.lanes));
+            const size_t l2_total = (size_t)std::max(4, s->tune.l2_mb) << 20;
             const int lanes = s->kt.enabled ? 1 : lanes_cfg;
             const size_t l2_budget = l2_total / (size_t)lanes;
             int chunkT = (int)std::max<size_t>(1, l2_budget / (sizeof(float2) * (size_t)N));
-            static const int chunk_override = getenv("GB200_ACQ_CHUNK_T") ? atoi(getenv("GB200_ACQ_CHUNK_T")) : 0;
-            if (chunk_override > 0) chunkT = chunk_override;
+            if (s->tune.chunk_t > 0) chunkT = s->tune.chunk_t;
             chunkT = std::min(chunkT, T);
             const int tiles = (plan.N2 + plan.inv_tile1 - 1) / plan.inv_tile1;
             void* d_rows[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -1551,11 +1673,9 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             for (int k = 1; k < lanes; k++)
                 if ((rc = s->scratch(row_slots[k], sizeof(float2) * (size_t)N * chunkT, &d_rows[k]))) return rc;
             if ((rc = s->scratch(3, sizeof(GbPeak) * (size_t)T * tiles, &d_part))) return rc;
-            // Opt-in (GB200_ACQ_FUSED=1): one persistent launch for the whole inverse side when there is a kernel for this plan
+            // Opt-in (tuning key "acq_fused"): one persistent launch for the whole inverse side when there is a kernel for this plan
             // and mode (plain arg-max search); otherwise, and by default, chunks of transforms on the lanes below.
-            static const int fused_cfg = getenv("GB200_ACQ_FUSED") ? atoi(getenv("GB200_ACQ_FUSED")) : 0;
-            static const int fused_lag = getenv("GB200_ACQ_FUSED_LAG") ? std::max(1, atoi(getenv("GB200_ACQ_FUSED_LAG"))) : 80;
-            static const int fused_ring = getenv("GB200_ACQ_FUSED_RING") ? std::max(2, atoi(getenv("GB200_ACQ_FUSED_RING"))) : 176;
+            const int fused_cfg = s->tune.fused, fused_lag = std::max(1, s->tune.fused_lag), fused_ring = std::max(2, s->tune.fused_ring);
             bool fused_done = false;
             if (fused_cfg && !g.grid)
                 {
@@ -1622,14 +1742,20 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     }
             GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
             if (g.grid)
-                GB_CUDA(s, gb_acq_grid_peaks((float* const*)((char*)d_up + g.off_grid), (int)g.members.size(), bins, (int)a0->eff, d_peaks, s->stream, &l));
+                {
+                    GB_CUDA(s, gb_acq_grid_peaks((float* const*)((char*)d_up + g.off_grid), (int)g.members.size(), bins, (int)a0->eff, d_peaks, s->stream, &l));
+                    // first/second-peak statistic (:633-660): the second peak of every member's winning row, one CTA each, in this
+                    // launch phase -- the results ride back with the peaks
+                    if (!a0->use_cfar && !a0->scaled_accum)
+                        GB_CUDA(s, gb_acq_second_peak_batch((float* const*)((char*)d_up + g.off_grid), (float* const*)((char*)d_up + g.off_tmp), d_peaks,
+                                       (int)g.members.size(), (int)a0->eff, N, (int)a0->c.samples_per_chip, (float*)((char*)d_res + g.off_second), s->stream, &l));
+                }
             else
                 GB_CUDA(s, gb_acq_reduce_peaks((const GbPeak*)d_part, (int)g.members.size(), bins, tiles, d_peaks, s->stream, &l));
         }
     s->launches += l;
     { int rc0 = rings_release(s); if (rc0) return rc0; }
-    ctx.h_results.resize(res);
-    GB_CUDA(s, cudaMemcpyAsync((char*)h_up + up, d_res, res, cudaMemcpyDeviceToHost, s->stream));
+    GB_CUDA(s, cudaMemcpyAsync(ctx.h_res, d_res, ctx.res_bytes, cudaMemcpyDeviceToHost, s->stream));
     for (int i = 0; i < n; i++)
         {
             list[i]->pending = true;
@@ -1642,9 +1768,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                 list[ctx.groups[gi].members[k]]->pending_slot = (int)k;
             }
     ctx.active = true;
-    // remember where the results will land
-    ctx.h_results.assign(sizeof(void*) + sizeof(size_t), 0);
-    *(void**)ctx.h_results.data() = (char*)h_up + up;
+    ctx.sig.swap(sig);
     return GB200_OK;
 }
 
@@ -1726,14 +1850,14 @@ extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_
     gb200_service* s = list[0]->s;
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
-    AcqBatchCtx& ctx = acq_ctx_map()[s];
+    AcqBatchCtx& ctx = s->acq_ctx;
     if (!ctx.active)
         {
             s->set_error("gb200_acq_collect_batch: nothing launched");
             return GB200_E_STATE;
         }
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
-    const char* h_res = *(char**)ctx.h_results.data();
+    const char* h_res = ctx.h_res;
     int rc = GB200_OK;
     for (int i = 0; i < n; i++)
         {
@@ -1783,23 +1907,8 @@ extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_
             else
                 {
                     r.input_power = a->c.bit_transition_flag ? power : 0.0f;
-                    // second peak on the winning row (:633-660); one more tiny launch + 4-byte read
-                    float* d_second;
-                    void* scratch;
-                    if ((rc = s->scratch(6, 16, &scratch))) break;
-                    d_second = (float*)scratch;
-                    int l = 0;
-                    cudaError_t e = gb_acq_second_peak(a->d_grid + (size_t)pk.bin * a->eff, a->d_tmp, (int)a->fft_size, (int)pk.idx, (int)a->c.samples_per_chip, d_second, s->stream, &l);
-                    s->launches += l;
-                    float second = 0.f;
-                    if (e == cudaSuccess) e = cudaMemcpyAsync(&second, d_second, sizeof(float), cudaMemcpyDeviceToHost, s->stream);
-                    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
-                    if (e != cudaSuccess)
-                        {
-                            s->set_error(std::string("second peak: ") + cudaGetErrorString(e));
-                            rc = GB200_E_CUDA;
-                            break;
-                        }
+                    // second peak of the winning row (:633-660), found on the device in the launch phase
+                    const float second = ((const float*)(h_res + g.off_second))[a->pending_slot];
                     stat = pk.mag / second;
                 }
             r.test_statistic = stat;
@@ -1827,6 +1936,9 @@ extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_
 
 extern "C" int gb200_acq_run_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index, gb200_acq_result* out)
 {
+    if (!list || n <= 0 || !list[0]) return GB200_E_INVALID;
+    // ONE critical section for launch + collect: another channel's thread (or a set_local_code) cannot get between the two
+    std::lock_guard<std::recursive_mutex> lk(list[0]->s->mu);
     int rc = gb200_acq_launch_batch(list, n, stream_id, first_sample_index);
     if (rc) return rc;
     return gb200_acq_collect_batch(list, n, out);
@@ -1875,7 +1987,8 @@ extern "C" int gb200_acq_run(gb200_acq* a, int stream_id, uint64_t first_sample_
             const int rc = gb200_acq_run_batch(list.data(), (int)list.size(), batch[i]->stream_id, batch[i]->first, res.data());
             if (rc != GB200_OK && members.size() > 1)
                 {
-                    // one bad request must not fail the others: redo one by one
+                    // one bad request must not fail the others: redo one by one.  The batch failed in its launch phase (collect has
+                    // no failing step once the results are back), so no handle's dwell state has advanced yet.
                     for (size_t k = 0; k < members.size(); k++)
                         batch[members[k]]->rc = gb200_acq_run_batch(&list[k], 1, batch[i]->stream_id, batch[i]->first, batch[members[k]]->out);
                 }
@@ -2085,7 +2198,7 @@ extern "C" int gb200_trk_set_local_code_and_taps(gb200_trk* t, const void* code,
     const size_t w = t->c.code_kind == GB200_CODE_CPLX ? 2 : 1;
     GB_CUDA(s, cudaMemcpyAsync(t->d_code, code, sizeof(float) * w * code_len, cudaMemcpyHostToDevice, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));  // `code` is caller memory: do not keep reading it
-    if (t->has_data && code_len != t->code_len) t->has_data = false;  // a data table of another length cannot ride along
+    if (t->has_data && (code_len != t->code_len || t->prompt_tap >= n_taps)) t->has_data = false;  // a data table of another length, or one whose prompt tap no longer exists, cannot ride along
     t->code_len = code_len;
     t->n_taps = n_taps;
     for (int i = 0; i < GB200_MAX_TAPS; i++) t->shifts[i] = i < n_taps ? shifts[i] : 0.f;
@@ -2218,16 +2331,8 @@ static bool trk_same_group(const TrkGroup& a, const TrkGroup& b)
 }
 
 // (re)build the work array of a batch from requests; buffers must already be sized for b->n requests
-// host threads that fill a long batch of request records (GB200_HOST_THREADS, default 8)
-[[maybe_unused]] static int gb_host_threads()
-{
-    static const int n = [] {
-        const char* e = getenv("GB200_HOST_THREADS");
-        const int v = e ? atoi(e) : 8;
-        return v < 1 ? 1 : (v > 64 ? 64 : v);
-    }();
-    return n;
-}
+// host threads that fill a long batch of request records (tuning key "host_threads", default 8)
+[[maybe_unused]] static int gb_host_threads(const gb200_service* s) { return std::max(1, std::min(64, s->tune.host_threads)); }
 
 static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
 {
@@ -2235,13 +2340,13 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
     const int n = b->n;
     // bucket requests by kernel variant, keeping request order inside a bucket
     b->groups.clear();
-    static const bool trace = getenv("GB200_TRACE") != nullptr;
+    const bool trace = s->tune.trace != 0;
     const auto ts0 = std::chrono::steady_clock::now();
     std::vector<int> gid(n);
     std::vector<TrkGroup> keys(n);
     for (int i = 0; i < n; i++)
         if (!reqs[i].trk) return GB200_E_INVALID;
-#pragma omp parallel for schedule(static) num_threads(gb_host_threads()) if (n >= 1024)
+#pragma omp parallel for schedule(static) num_threads(gb_host_threads(s)) if (n >= 1024)
     for (int i = 0; i < n; i++)
         {
             TrkGroup& k = keys[i];
@@ -2312,7 +2417,7 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
         // the per-request NCO constants go through host libm in float32 and float64 (~0.1 us each): a long batch is filled
         // by a few host threads
         int first_rc = GB200_OK;
-#pragma omp parallel for schedule(static) num_threads(gb_host_threads()) if (n >= 1024)
+#pragma omp parallel for schedule(static) num_threads(gb_host_threads(s)) if (n >= 1024)
         for (int i = 0; i < n; i++)
             {
                 const int rc = trk_fill_work(s, reqs[i], i, &b->h_work[slot_of[i]]);
@@ -2353,7 +2458,7 @@ static int trk_batch_stage(gb200_trk_batch* b, const gb200_trk_req* reqs)
     auto win_for = [&](int c) { return ((int)ceil((double)(std::min(c, max_n) + 1023) * chips_per_sample + spread) + 8 + 1) & ~1; };
     long long ctas = 0;
     b->chunk = 1024;
-    static const int chunk_cap = getenv("GB200_TRK_CHUNK_MAX") ? atoi(getenv("GB200_TRK_CHUNK_MAX")) : 32768;  // tuning only
+    const int chunk_cap = s->tune.trk_chunk_max;  // tuning only
     for (int c : {32768, 16384, 8192, 4096, 2048, 1024})
         {
             if (c > chunk_cap && c > 1024) continue;
@@ -2495,7 +2600,7 @@ extern "C" int gb200_trk_correlate_batch(gb200_service* s, int n, const gb200_tr
         }
     gb200_trk_batch* b = s->cb;
     b->n = n;
-    static const bool trace = getenv("GB200_TRACE") != nullptr;  // host wall-clock phases of one call, to stderr
+    const bool trace = s->tune.trace != 0;  // host wall-clock phases of one call, to stderr
     const auto t0 = std::chrono::steady_clock::now();
     int rc = trk_batch_stage(b, reqs);
     if (rc) return rc;

@@ -24,5 +24,6 @@ def service():
     import gnss_b200 as gb
 
     s = gb.Service(device=0, ring_capacity=1 << 23, ring_slack=1 << 21)
+    s.tune_from_env()  # GB200_TUNE="key=value,...": lets a child pytest run the same tests under a tuning switch
     yield s
     s.close()

@@ -426,13 +426,13 @@ def test_iq_combine_records_and_error_paths(service):
 
 
 def test_fused_persistent_inverse_matches_default_path():
-    """GB200_ACQ_FUSED=1 (one persistent launch with a device-side tile queue instead of two kernels per chunk) is read once per
-    process, so a child process runs the batch-search parity tests of this file under it; they compare with the oracle exactly
-    as the default path does."""
+    """Tuning key acq_fused=1 (one persistent launch with a device-side tile queue instead of two kernels per chunk): a child
+    process whose session service is steered by GB200_TUNE (tests/conftest.py -> gb200_service_set_tuning) runs the batch-search
+    parity tests of this file under it; they compare with the oracle exactly as the default path does."""
     import subprocess
     import sys as _sys
 
-    env = dict(os.environ, GB200_ACQ_FUSED="1", GB200_ACQ_FUSED_LAG="3", GB200_ACQ_FUSED_RING="5")
+    env = dict(os.environ, GB200_TUNE="acq_fused=1,acq_fused_lag=3,acq_fused_ring=5")
     here = os.path.dirname(os.path.abspath(__file__))
     r = subprocess.run([_sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_acquisition.py"), "-m", "gpu", "-x", "-q", "-k",
                         "not fused and (fixture or batch or fast_inverse or ties or odd_lengths or zero_padded or bin_range)"], env=env, capture_output=True, text=True,
@@ -530,3 +530,87 @@ def test_service_coalesces_concurrent_acquisition_threads():
             assert getattr(ra, f) == getattr(rt, f), f
     assert launches_together * 2 < launches_alone, (launches_together, launches_alone)
     assert sum(r.decision == 1 for r in together) == 8
+
+
+def test_set_local_code_between_launch_and_collect(service):
+    """The split launch / collect API keeps its results in a buffer of the batch's own: another channel's set_local_code (which
+    reuses the service's staging area and waits for the stream) between the two calls must not disturb them."""
+    import gnss_b200 as gb
+
+    prns, x = c1_signal(8000, seed=314)
+    service.push(2, x, gb.ITEM_32FC, 0)
+    cfg = dict(doppler_max=5000, doppler_step=250, threshold=0.008, samples_per_chip=4)
+    acqs = []
+    for p in prns[:4]:
+        a = gb.Acquisition(service, **cfg)
+        a.set_local_code(gps_local_code(p))
+        acqs.append(a)
+    want = gb.acq_run_batch(acqs, 2, 100)
+    other = gb.Acquisition(service, sampled_ms=4, ms_per_code=4, samples_per_ms=8000.0, samples_per_code=32000.0, fs_in=8000000, **cfg)
+    handles = gb.acq_handles(acqs)
+    gb.acq_launch_batch(acqs, handles, 2, 100)
+    other.set_local_code(np.ones(32000, np.complex64))  # a larger staging request than the batch's: the old code reallocated here
+    got = gb.acq_collect_batch(acqs, handles)
+    for r, w in zip(got, want):
+        assert (r.code_phase_index, r.doppler_bin, r.decision, r.peak_mag, r.test_statistic) == (w.code_phase_index, w.doppler_bin, w.decision, w.peak_mag, w.test_statistic)
+    # a second launch of the same batch reuses the group tables on the device (same signature) and gives the same answer
+    got2 = gb.acq_run_batch(acqs, 2, 100)
+    for r, w in zip(got2, want):
+        assert (r.code_phase_index, r.doppler_bin, r.decision, r.peak_mag) == (w.code_phase_index, w.doppler_bin, w.decision, w.peak_mag)
+    # ... and after a Doppler-grid change of one member the tables are rebuilt
+    acqs[1].set_doppler(2500, 250)
+    got3 = gb.acq_run_batch(acqs, 2, 100)
+    assert acqs[1].num_bins == 20 and got3[0].peak_mag == want[0].peak_mag and got3[1].doppler_bin < 20
+    for a in acqs + [other]:
+        a.close()
+
+
+def test_two_threads_run_acquisitions_concurrently(service):
+    """Two channel threads calling gb200_acq_run in a loop with no batching window: launch + collect of one call is one critical
+    section, so neither ever sees the other's batch ('previous batch not collected') and both get their own results."""
+    import threading
+
+    import gnss_b200 as gb
+
+    prns, x = c1_signal(8000, seed=2718)
+    service.push(2, x, gb.ITEM_32FC, 0)
+    cfg = dict(doppler_max=5000, doppler_step=250, threshold=0.008, samples_per_chip=4)
+    acqs = []
+    for p in (prns[0], prns[5]):
+        a = gb.Acquisition(service, **cfg)
+        a.set_local_code(gps_local_code(p))
+        acqs.append(a)
+    want = [a.run(2, 0) for a in acqs]
+    errors = []
+
+    def loop(k):
+        try:
+            for _ in range(40):
+                r = acqs[k].run(2, 0)
+                assert (r.code_phase_index, r.doppler_bin, r.peak_mag) == (want[k].code_phase_index, want[k].doppler_bin, want[k].peak_mag)
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    th = [threading.Thread(target=loop, args=(k,)) for k in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errors, errors[:3]
+    for a in acqs:
+        a.close()
+
+
+def test_tuning_keys_and_stream_wait(service):
+    import gnss_b200 as gb
+
+    with pytest.raises(gb.Gb200Error):
+        service.set_tuning("no_such_key", 1)
+    with pytest.raises(gb.Gb200Error):
+        service.set_tuning("acq_variant", 1)  # plans exist by now: must be set before the first acquisition handle
+    service.set_tuning("acq_lanes", 1)
+    service.set_tuning("acq_lanes", 2)
+    x = np.zeros(1000, np.complex64)
+    service.push(3, x, gb.ITEM_32FC, 0)
+    service.wait_pushes(3)
+    assert np.array_equal(service.read(3, 0, 1000), x)

@@ -315,3 +315,31 @@ def test_service_coalesces_concurrent_channel_threads():
             break
     assert launches_together <= launches_alone // 3, (launches_together, launches_alone)
     assert np.array_equal(alone, together)
+
+
+def test_tap_count_change_drops_a_stale_data_tap(service):
+    """set_local_code_and_taps with fewer taps than the attached data code's prompt tap: the data tap is dropped (its prompt tap no
+    longer exists) instead of reading a tap that is not there; re-attaching with a valid prompt tap brings it back."""
+    import gnss_b200 as gb
+
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal(9000) + 1j * rng.standard_normal(9000)).astype(np.complex64)
+    service.push(0, x, gb.ITEM_32FC, 0)
+    e1c = synth.code_table("gal_e1c_sinboc", 7)
+    e1b = synth.code_table("gal_e1b_sinboc", 7)
+    m = gb.Multicorrelator(service, 5, 8184)
+    m.set_local_code_and_taps(e1c, [-1.2, -0.3, 0.0, 0.3, 1.2])
+    m.set_data_code(e1b, 4)
+    assert m.n_out == 6
+    m.set_local_code_and_taps(e1c, [-0.3, 0.0, 0.3])
+    args = (0.4, 0.01, 0.3, 8184 / 32000)
+    got = m.correlate(0, 100, *args, 8000)
+    want = ol.multicorrelator_real("oracle", x[100:8100], e1c, np.asarray([-0.3, 0.0, 0.3], np.float32), *args)
+    assert len(got) == 3 and np.abs(got - want).max() < TOL * np.abs(want).max()
+    m.set_data_code(e1b, 1)
+    got = m.correlate(0, 100, *args, 8000)
+    wd = ol.multicorrelator_real("oracle", x[100:8100], e1b, np.asarray([0.0], np.float32), *args)
+    assert len(got) == 4 and abs(got[3] - wd[0]) < TOL * max(np.abs(want).max(), abs(wd[0]))
+    with pytest.raises(gb.Gb200Error):
+        m.set_data_code(e1b, 3)
+    m.close()
