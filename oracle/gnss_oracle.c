@@ -725,7 +725,20 @@ int go_acq_run(go_acq* a, const void* samples, uint64_t samp_count, go_acq_resul
     if (a->use_cfar || a->c.bit_transition_flag) /* :703-709 */
         {
             for (uint32_t i = 0; i < n; i++) a->tmp_buffer[i] = in[2 * i] * in[2 * i] + in[2 * i + 1] * in[2 * i + 1];
-            for (uint32_t i = 0; i < n; i++) input_power += a->tmp_buffer[i];
+            if (a->c.accumulator_lanes > 1)
+                {
+                    /* VOLK volk_32f_accumulator_s32f a_avx / u_avx: one vector accumulator of `lanes` floats over the whole
+                     * multiples of `lanes`, lanes added in order, then the remaining points one by one */
+                    const uint32_t lanes = (uint32_t)a->c.accumulator_lanes, whole = n / lanes;
+                    float acc[16] = {0};
+                    for (uint32_t k = 0; k < whole; k++)
+                        for (uint32_t l = 0; l < lanes && l < 16; l++) acc[l] += a->tmp_buffer[k * lanes + l];
+                    input_power = acc[0];
+                    for (uint32_t l = 1; l < lanes && l < 16; l++) input_power += acc[l];
+                    for (uint32_t i = whole * lanes; i < n; i++) input_power += a->tmp_buffer[i];
+                }
+            else
+                for (uint32_t i = 0; i < n; i++) input_power += a->tmp_buffer[i];
             input_power /= (float)n;
         }
 

@@ -90,6 +90,9 @@ typedef struct go_acq_conf
     int fft_f64;            /* arbiter: run the DFTs in float64 */
     int analytic_wipeoff;   /* arbiter: exact phase instead of float32-accumulated table */
     int keep_grid;          /* tests: snapshot the magnitude grid before the end-of-attempt reset (:919-928) */
+    int accumulator_lanes;  /* volk_32f_accumulator_s32f (upstream VOLK, not in the tree) behind d_input_power: 0 / 1 = its _generic
+                             * protokernel (one sequential float32 sum), 8 = its a_avx / u_avx protokernels (eight interleaved
+                             * partial sums added in lane order, then the tail) -- what VOLK dispatches on an x86 host */
 } go_acq_conf;
 
 typedef struct go_acq_result

@@ -29,7 +29,7 @@ class GoAcqConf(C.Structure):
         ("samples_per_ms", C.c_float), ("samples_per_code", C.c_float), ("bit_transition_flag", C.c_int),
         ("use_CFAR_algorithm_flag", C.c_int), ("make_2_steps", C.c_int), ("cshort", C.c_int),
         ("threshold", C.c_float), ("freq_offset_hz", C.c_int64), ("fft_f64", C.c_int),
-        ("analytic_wipeoff", C.c_int), ("keep_grid", C.c_int),
+        ("analytic_wipeoff", C.c_int), ("keep_grid", C.c_int), ("accumulator_lanes", C.c_int),
     ]
 
 
@@ -208,7 +208,7 @@ def acq_conf(**kw):
     d = dict(sampled_ms=1, ms_per_code=1, samples_per_chip=4, max_dwells=1, doppler_max=5000, doppler_step=250,
              num_doppler_bins_step2=4, doppler_step2=125.0, fs_in=4000000, samples_per_ms=4000.0,
              samples_per_code=4000.0, bit_transition_flag=0, use_CFAR_algorithm_flag=1, make_2_steps=0,
-             cshort=0, threshold=0.0, freq_offset_hz=0, fft_f64=0, analytic_wipeoff=0, keep_grid=0)
+             cshort=0, threshold=0.0, freq_offset_hz=0, fft_f64=0, analytic_wipeoff=0, keep_grid=0, accumulator_lanes=0)
     d.update(kw)
     for k, v in d.items():
         setattr(c, k, v)

@@ -27,14 +27,14 @@ def tup(r):
     return (r.code_phase_index, r.doppler_bin, r.doppler_hz, r.decision)
 
 
-def oracle_batch(cfg, codes, host_block, samp_count, cshort, arbiter=True):
+def oracle_batch(cfg, codes, host_block, samp_count, cshort, arbiter=True, accumulator_lanes=0):
     """One oracle object per code, float32 DFT (the statement of the reference) and float64 DFT (the conditioning arbiter),
     run on a thread pool (ctypes releases the GIL; every oracle object owns its buffers)."""
 
     def one(code):
         out = []
         for f64 in ((0, 1) if arbiter else (0,)):
-            o = ol.OracleAcq(cshort=int(cshort), fft_f64=f64, **cfg)
+            o = ol.OracleAcq(cshort=int(cshort), fft_f64=f64, accumulator_lanes=accumulator_lanes, **cfg)
             o.set_local_code(code)
             r = o.run(host_block, samp_count)
             out.append((tup(r), r.test_statistic, r.peak_mag, r.input_power, r.acq_delay_samples, r.acq_doppler_hz, r.acq_samplestamp))
@@ -148,7 +148,11 @@ def test_c3_l5_e5a_batch_non_cfar(service):
 def test_c4_ibyte_acquisition(service, what):
     """C4: 20 Msps interleaved int8 input (GB200_ITEM_8IC: the reference converts cbyte to gr_complex in front of the block,
     gps_l1_ca_pcps_acquisition.cc:292-299, i.e. an exact int8 -> float conversion), GPS L1 C/A at N = 20000 and Galileo E1 at
-    N = 80000 (4 ms).  The oracle gets the same items converted to float32."""
+    N = 80000 (4 ms).  The oracle gets the same items converted to float32.
+    d_input_power: upstream VOLK's volk_32f_accumulator_s32f sums in float32, and on 8-bit items (|x|^2 are small integers) its
+    _generic protokernel -- ONE sequential sum, which passes 2^25 here -- ends 4.2e-4 below the exact sum at N = 80000, while its
+    a_avx / u_avx protokernels (eight interleaved partial sums, what VOLK dispatches on any x86 host) stay exact.  The two
+    statements of the reference differ by more than the 1e-4 budget; the engine's tree sum is held to the AVX one here."""
     fs = 20_000_000
     if what == "gps_20000":
         n, kind, rate = 20000, "gps_l1_ca", 1.023e6
@@ -168,7 +172,7 @@ def test_c4_ibyte_acquisition(service, what):
     res, consumed, fft = run_batch(service, cfg, codes, q, "8ic", 64, off)
     assert (consumed, fft) == (n, n)
     host = q[2 * off: 2 * (off + n)].astype(np.float32).view(np.complex64)
-    ora = oracle_batch(cfg, codes, host, 64 + off + n, cshort=False)
+    ora = oracle_batch(cfg, codes, host, 64 + off + n, cshort=False, accumulator_lanes=8)
     compare(res, ora, set(range(len(prns))), "C4 " + what)
     for s, r in zip(sats, res):
         assert r.decision == 1 and abs(int(r.code_phase_index) - (s["delay_samples"] - off) % n) <= 1, (s, tup(r))
@@ -192,7 +196,7 @@ def test_c4_beidou_b1i_ms_per_code_zero(service):
     res, consumed, fft = run_batch(service, cfg, codes, q, "8ic", 0, 0)
     assert (consumed, fft) == (20000, 40000)
     host = q[: 2 * n].astype(np.float32).view(np.complex64)
-    ora = oracle_batch(cfg, codes, host, n, cshort=False)
+    ora = oracle_batch(cfg, codes, host, n, cshort=False, accumulator_lanes=8)
     compare(res, ora, {0, 1, 2}, "B1I")
     for s, r in zip(sats, res):
         assert r.decision == 1 and abs(int(r.acq_delay_samples) - s["delay_samples"] % n) <= 1, (s, tup(r), r.acq_delay_samples)
