@@ -176,6 +176,12 @@ public:
     }
 
     void stop_tracking() { state_ = 0; }
+    // the "telemetry_to_trk" message port (dll_pll_veml_tracking.cc:516-536): int 1 = telemetry fault in this channel, the
+    // decoder asks for a re-acquisition by forcing the loss-of-lock condition at the next lock test
+    void telemetry_to_trk(int tlm_event)
+    {
+        if (tlm_event == 1) carrier_lock_fail_counter_ = 10000;
+    }
     int state() const { return state_; }
     uint64_t sample_counter() const { return sample_counter_; }
     double current_correlation_time_s() const { return current_correlation_time_s_; }

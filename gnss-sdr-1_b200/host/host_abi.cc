@@ -85,6 +85,10 @@ void gbh_trk_set_channel(gbh_trk* h, unsigned channel)
 {
     if (h) h->loop->set_channel(channel);
 }
+void gbh_trk_telemetry(gbh_trk* h, int tlm_event)
+{
+    if (h) h->loop->telemetry_to_trk(tlm_event);
+}
 int gbh_trk_start(gbh_trk* h, const float* code, const float* data_code, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp,
     uint64_t sample_counter_now)
 {

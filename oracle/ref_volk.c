@@ -126,3 +126,68 @@ void gbref_16ic_convert_32fc(float* out_iq, const int16_t* in_iq, unsigned n)
 {
     volk_gnsssdr_16ic_convert_32fc_generic((lv_32fc_t*)out_iq, (const lv_16sc_t*)in_iq, n);
 }
+
+/* ---- dispatcher names pcps_acquisition.cc calls: the reference's own _generic protokernels ---- */
+void volk_gnsssdr_s32f_sincos_32fc(lv_32fc_t* out, const float phase_inc, float* phase, unsigned int num_points)
+{
+    volk_gnsssdr_s32f_sincos_32fc_generic(out, phase_inc, phase, num_points);
+}
+void volk_gnsssdr_32f_index_max_32u(uint32_t* target, const float* src0, uint32_t num_points)
+{
+    volk_gnsssdr_32f_index_max_32u_generic(target, src0, num_points);
+}
+void volk_gnsssdr_16ic_convert_32fc(lv_32fc_t* outputVector, const lv_16sc_t* inputVector, unsigned int num_points)
+{
+    volk_gnsssdr_16ic_convert_32fc_generic(outputVector, inputVector, num_points);
+}
+
+/* ---- upstream VOLK (not in the reference tree): published _generic protokernels, see shim/volk/volk.h ---- */
+int gb_volk_accumulator_lanes = 0;
+void volk_32fc_x2_multiply_32fc(lv_32fc_t* c, const lv_32fc_t* a, const lv_32fc_t* b, unsigned int n)
+{
+    const float* pa = (const float*)a;
+    const float* pb = (const float*)b;
+    float* pc = (float*)c;
+    for (unsigned int i = 0; i < n; i++)
+        {
+            const float ar = pa[2 * i], ai = pa[2 * i + 1], br = pb[2 * i], bi = pb[2 * i + 1];
+            pc[2 * i] = ar * br - ai * bi;
+            pc[2 * i + 1] = ar * bi + ai * br;
+        }
+}
+void volk_32fc_conjugate_32fc(lv_32fc_t* c, const lv_32fc_t* a, unsigned int n)
+{
+    const float* pa = (const float*)a;
+    float* pc = (float*)c;
+    for (unsigned int i = 0; i < n; i++)
+        {
+            pc[2 * i] = pa[2 * i];
+            pc[2 * i + 1] = -pa[2 * i + 1];
+        }
+}
+void volk_32fc_magnitude_squared_32f(float* m, const lv_32fc_t* a, unsigned int n)
+{
+    const float* pa = (const float*)a;
+    for (unsigned int i = 0; i < n; i++) m[i] = pa[2 * i] * pa[2 * i] + pa[2 * i + 1] * pa[2 * i + 1];
+}
+void volk_32f_accumulator_s32f(float* result, const float* in, unsigned int n)
+{
+    float r = 0.0f;
+    if (gb_volk_accumulator_lanes > 1)
+        {
+            const unsigned int lanes = gb_volk_accumulator_lanes > 16 ? 16 : (unsigned int)gb_volk_accumulator_lanes, whole = n / lanes;
+            float acc[16] = {0};
+            for (unsigned int k = 0; k < whole; k++)
+                for (unsigned int l = 0; l < lanes; l++) acc[l] += in[k * lanes + l];
+            r = acc[0];
+            for (unsigned int l = 1; l < lanes; l++) r += acc[l];
+            for (unsigned int i = whole * lanes; i < n; i++) r += in[i];
+        }
+    else
+        for (unsigned int i = 0; i < n; i++) r += in[i];
+    *result = r;
+}
+void volk_32f_x2_add_32f(float* c, const float* a, const float* b, unsigned int n)
+{
+    for (unsigned int i = 0; i < n; i++) c[i] = a[i] + b[i];
+}

@@ -40,7 +40,12 @@ size_t volk_gnsssdr_get_alignment(void) { return 64; }
 void* volk_gnsssdr_malloc(size_t size, size_t alignment)
 {
     size_t a = alignment < 64 ? 64 : alignment;
-    return aligned_alloc(a, (size + a - 1) / a * a);
+    // Zero-filled, like the fresh pages a large first allocation gets from the kernel: pcps_acquisition reads d_tmp_buffer beyond
+    // the part it has written in first_vs_second_peak_statistic (memcpy of d_fft_size BYTES, :647), so with recycled heap memory
+    // the reference's result there is undefined; zeros are the defined behaviour the restatement and the engine reproduce.
+    void* p = aligned_alloc(a, (size + a - 1) / a * a);
+    if (p) memset(p, 0, (size + a - 1) / a * a);
+    return p;
 }
 void volk_gnsssdr_free(void* p) { free(p); }
 

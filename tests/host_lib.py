@@ -226,6 +226,7 @@ def oracle_loop():
         L.hol_caid_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.hol_caid_close.argtypes = [C.c_void_p]
         L.hol_set_channel.argtypes = [C.c_void_p, C.c_uint]
+        L.hol_telemetry.argtypes = [C.c_void_p, C.c_int]
         _hol = L
     return _hol
 
@@ -240,7 +241,9 @@ def _record(e):
     return d
 
 
-def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None, channel=None):
+def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_doppler, acq_stamp, n_steps, data_code=None, channel=None,
+                       telemetry_fault_at=None):
+    """telemetry_fault_at: step index before which the telemetry_to_trk fault message (int 1) is delivered"""
     L = oracle_loop()
     x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
     h = L.hol_open(x, len(x) // 2, first_index, C.byref(conf))
@@ -250,7 +253,9 @@ def run_oracle_channel(samples_c64, first_index, conf, code, acq_delay, acq_dopp
     dc = np.ascontiguousarray(data_code, np.float32) if data_code is not None else None
     assert L.hol_start(h, code, dc.ctypes.data_as(C.c_void_p) if dc is not None else None, acq_delay, acq_doppler, acq_stamp, first_index) == 0
     out, e = [], Epoch()
-    for _ in range(n_steps):
+    for k in range(n_steps):
+        if telemetry_fault_at is not None and k == telemetry_fault_at:
+            L.hol_telemetry(h, 1)
         if L.hol_step(h, C.byref(e)) != 0:
             break
         out.append(_record(e))

@@ -90,6 +90,7 @@ int hol_step(void* h, gbh_epoch* out)
     return ok ? 0 : -2;
 }
 void hol_set_channel(void* h, unsigned channel) { static_cast<Channel*>(h)->loop->set_channel(channel); }
+void hol_telemetry(void* h, int tlm_event) { static_cast<Channel*>(h)->loop->telemetry_to_trk(tlm_event); }
 void hol_close(void* h) { delete static_cast<Channel*>(h); }
 }
 

@@ -436,3 +436,192 @@ class OracleAcq:
             self.close()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------- the reference's GNU Radio blocks themselves (oracle/ref_blocks.cc)
+class GbRefAcqConf(C.Structure):
+    _fields_ = [("sampled_ms", C.c_uint32), ("ms_per_code", C.c_uint32), ("samples_per_chip", C.c_uint32), ("max_dwells", C.c_uint32),
+                ("doppler_max", C.c_uint32), ("doppler_step", C.c_uint32), ("num_doppler_bins_step2", C.c_uint32), ("doppler_step2", C.c_float),
+                ("fs_in", C.c_int64), ("samples_per_ms", C.c_float), ("samples_per_code", C.c_float), ("bit_transition_flag", C.c_int),
+                ("use_CFAR_algorithm_flag", C.c_int), ("make_2_steps", C.c_int), ("cshort", C.c_int), ("threshold", C.c_float),
+                ("system", C.c_char), ("signal", C.c_char * 3), ("prn", C.c_uint32), ("use_fsm", C.c_int)]
+
+
+class GbRefAcqState(C.Structure):
+    _fields_ = [("state", C.c_int32), ("active", C.c_int32), ("step_two", C.c_int32), ("positive_acq", C.c_int32), ("dwell_counter", C.c_uint32),
+                ("fft_size", C.c_uint32), ("consumed_samples", C.c_uint32), ("num_doppler_bins", C.c_uint32), ("threshold", C.c_float), ("mag", C.c_float),
+                ("input_power", C.c_float), ("test_statistics", C.c_float), ("doppler_center_step_two", C.c_float), ("sample_counter", C.c_uint64),
+                ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("acq_doppler_step", C.c_uint32),
+                ("fsm_valid_acquisitions", C.c_int32), ("old_freq", C.c_int64)]
+
+
+class GbRefTrkConf(C.Structure):
+    _fields_ = [("fs_in", C.c_double), ("vector_length", C.c_uint32), ("system", C.c_char), ("signal", C.c_char * 3), ("pll_filter_order", C.c_int),
+                ("dll_filter_order", C.c_int), ("fll_filter_order", C.c_int), ("enable_fll_pull_in", C.c_int), ("enable_fll_steady_state", C.c_int),
+                ("pull_in_time_s", C.c_uint32), ("fll_bw_hz", C.c_float), ("pll_bw_hz", C.c_float), ("dll_bw_hz", C.c_float), ("pll_bw_narrow_hz", C.c_float),
+                ("dll_bw_narrow_hz", C.c_float), ("early_late_space_chips", C.c_float), ("very_early_late_space_chips", C.c_float),
+                ("early_late_space_narrow_chips", C.c_float), ("very_early_late_space_narrow_chips", C.c_float), ("extend_correlation_symbols", C.c_int32),
+                ("high_dyn", C.c_int), ("smoother_length", C.c_uint32), ("cn0_samples", C.c_int32), ("cn0_min", C.c_int32), ("max_lock_fail", C.c_int32),
+                ("carrier_lock_th", C.c_double), ("track_pilot", C.c_int), ("dump", C.c_int), ("dump_filename", C.c_char * 256)]
+
+
+class GbRefTrkEpoch(C.Structure):
+    _fields_ = [("tracking_sample_counter", C.c_uint64), ("first_sample", C.c_uint64), ("n_samples", C.c_int32), ("state_after", C.c_int32),
+                ("prompt_i", C.c_double), ("prompt_q", C.c_double), ("carrier_phase_rads", C.c_double), ("carrier_doppler_hz", C.c_double),
+                ("code_phase_samples", C.c_double), ("cn0_db_hz", C.c_double), ("code_freq_chips", C.c_double), ("rem_code_phase_chips", C.c_double),
+                ("acc_carrier_phase_rad", C.c_double), ("carrier_lock_test", C.c_double), ("rem_carr_phase_rad", C.c_float), ("correlation_length_ms", C.c_int32),
+                ("cloop", C.c_int32), ("pull_in_transitory", C.c_int32), ("current_symbol", C.c_int32), ("lock_fail_counter", C.c_int32),
+                ("corr", C.c_float * 10), ("p_accu", C.c_float * 2)]
+
+
+def ref_blocks():
+    """oracle/_ref with the block harness bound, or None (no oracle/_ref, or one built before the blocks were added)."""
+    L = ref()
+    if L is None or not hasattr(L, "gbref_acq_block_create"):
+        return None
+    if getattr(L, "_blocks_bound", False):
+        return L
+    L.gbref_acq_block_create.argtypes = [C.POINTER(GbRefAcqConf)]
+    L.gbref_acq_block_create.restype = C.c_void_p
+    L.gbref_acq_block_destroy.argtypes = [C.c_void_p]
+    L.gbref_acq_block_set_local_code.argtypes = [C.c_void_p, f32p]
+    L.gbref_acq_block_set_state.argtypes = [C.c_void_p, C.c_int]
+    L.gbref_acq_block_set_active.argtypes = [C.c_void_p, C.c_int]
+    L.gbref_acq_block_set_threshold.argtypes = [C.c_void_p, C.c_float]
+    L.gbref_acq_block_set_sample_counter.argtypes = [C.c_void_p, C.c_uint64]
+    L.gbref_set_accumulator_lanes.argtypes = [C.c_int]
+    L.gbref_acq_block_work.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+    L.gbref_acq_block_get_state.argtypes = [C.c_void_p, C.POINTER(GbRefAcqState)]
+    L.gbref_acq_block_grid_row.argtypes = [C.c_void_p, C.c_uint32]
+    L.gbref_acq_block_grid_row.restype = C.POINTER(C.c_float)
+    L.gbref_trk_block_create.argtypes = [C.POINTER(GbRefTrkConf)]
+    L.gbref_trk_block_create.restype = C.c_void_p
+    L.gbref_trk_block_destroy.argtypes = [C.c_void_p]
+    L.gbref_trk_block_start.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+    L.gbref_trk_block_stop.argtypes = [C.c_void_p]
+    L.gbref_trk_block_telemetry_fault.argtypes = [C.c_void_p]
+    L.gbref_trk_block_state.argtypes = [C.c_void_p]
+    L.gbref_trk_block_position.argtypes = [C.c_void_p]
+    L.gbref_trk_block_position.restype = C.c_longlong
+    L.gbref_trk_block_run.argtypes = [C.c_void_p, f32p, C.c_longlong, C.POINTER(GbRefTrkEpoch), C.c_int, i32p, C.c_int, C.POINTER(C.c_int)]
+    L.gbref_read_tracking_dump.argtypes = [C.c_char_p, f64p, C.c_longlong]
+    L.gbref_read_tracking_dump.restype = C.c_longlong
+    L._blocks_bound = True
+    return L
+
+
+DUMP_READER_FIELDS = ("abs_VE", "abs_E", "abs_P", "abs_L", "abs_VL", "prompt_I", "prompt_Q", "PRN_start_sample_count", "acc_carrier_phase_rad",
+                      "carrier_doppler_hz", "carrier_doppler_rate_hz_s", "code_freq_chips", "code_freq_rate_chips", "carr_error_hz", "carr_error_filt_hz",
+                      "code_error_chips", "code_error_filt_chips", "CN0_SNV_dB_Hz", "carrier_lock_test", "aux1", "aux2")
+
+
+def read_tracking_dump(path, max_epochs=100000):
+    """A tracking .dat dump read by the reference's own Tracking_Dump_Reader; returns (num_epochs, array [n, 21])."""
+    L = ref_blocks()
+    out = np.zeros((max_epochs, 21), np.float64)
+    n = L.gbref_read_tracking_dump(str(path).encode(), out.reshape(-1), max_epochs)
+    return n, out[: max(0, min(n, max_epochs))]
+
+
+class RefAcqBlock:
+    """The reference's pcps_acquisition block (compiled from /root/reference), driven dwell by dwell.
+    Keyword arguments as OracleAcq / gb.Acquisition, plus system / signal / prn (GLONASS FDMA: signal '1G' and a PRN whose
+    GLONASS_PRN channel number gives the offset) and use_fsm."""
+
+    def __init__(self, system=b"G", signal=b"1C", prn=1, use_fsm=0, **kw):
+        self.L = ref_blocks()
+        d = dict(sampled_ms=1, ms_per_code=1, samples_per_chip=4, max_dwells=1, doppler_max=5000, doppler_step=250, num_doppler_bins_step2=4,
+                 doppler_step2=125.0, fs_in=4000000, samples_per_ms=4000.0, samples_per_code=4000.0, bit_transition_flag=0,
+                 use_CFAR_algorithm_flag=1, make_2_steps=0, cshort=0, threshold=0.0)
+        d.update(kw)
+        self.cshort = d["cshort"]
+        self.conf = GbRefAcqConf(system=system, signal=signal, prn=prn, use_fsm=use_fsm, **d)
+        self.h = self.L.gbref_acq_block_create(C.byref(self.conf))
+        st = self.state()
+        self.fft_size, self.consumed, self.num_bins = st.fft_size, st.consumed_samples, st.num_doppler_bins
+
+    def state(self):
+        s = GbRefAcqState()
+        self.L.gbref_acq_block_get_state(self.h, C.byref(s))
+        return s
+
+    def set_local_code(self, code_c64):
+        need = self.fft_size // 2 if self.conf.bit_transition_flag else self.consumed
+        code = np.ascontiguousarray(code_c64, np.complex64)
+        assert len(code) >= need
+        self.L.gbref_acq_block_set_local_code(self.h, code.view(np.float32).copy())
+
+    def reset(self):
+        """AcquisitionInterface::reset() of the adapters = set_active(true)"""
+        self.L.gbref_acq_block_set_active(self.h, 1)
+
+    def start(self, sample_counter=0):
+        """what the unit tests / ChannelFsm::start_acquisition do before the first dwell: set_state(1) (reset() = set_active(true))"""
+        self.L.gbref_acq_block_set_sample_counter(self.h, sample_counter)
+        self.L.gbref_acq_block_set_state(self.h, 1)
+
+    def dwell(self, samples):
+        """Feeds general_work() from `samples` (complex64, or interleaved int16 when cshort) until acquisition_core has run once;
+        returns (GbRefAcqState, event) with event 1 positive / 2 negative / 0 none (more dwells or step two armed)."""
+        buf = np.ascontiguousarray(samples, np.int16 if self.cshort else np.complex64)
+        isz = 4 if self.cshort else 8
+        n_items = buf.nbytes // isz
+        pos, ev = 0, C.c_int(0)
+        before = self.state()
+        for _ in range(64):
+            st0 = self.state()
+            if not st0.active and not st0.step_two:
+                raise RuntimeError("block is in standby: call start() (set_state(1)) or reset() first")
+            # (standby with step two armed: general_work re-centres the fine grid and re-activates the block by itself, :978-985)
+            was_state = st0.state
+            used = self.L.gbref_acq_block_work(self.h, C.c_void_p(buf.ctypes.data + pos * isz), n_items - pos, C.byref(ev))
+            pos += used
+            if was_state == 2:
+                return self.state(), ev.value
+        raise RuntimeError("acquisition_core did not run (state %d -> %d)" % (before.state, self.state().state))
+
+    def grid(self):
+        eff = self.fft_size // 2 if self.conf.bit_transition_flag else self.fft_size
+        return np.stack([np.ctypeslib.as_array(self.L.gbref_acq_block_grid_row(self.h, b), shape=(self.fft_size,))[:eff].copy() for b in range(self.num_bins)])
+
+    def close(self):
+        if self.h:
+            self.L.gbref_acq_block_destroy(self.h)
+            self.h = None
+
+
+class RefTrkBlock:
+    """The reference's dll_pll_veml_tracking block (compiled from /root/reference)."""
+
+    def __init__(self, **kw):
+        self.L = ref_blocks()
+        d = dict(fs_in=4e6, vector_length=4000, system=b"G", signal=b"1C", pll_filter_order=3, dll_filter_order=2, fll_filter_order=1,
+                 enable_fll_pull_in=0, enable_fll_steady_state=0, pull_in_time_s=2, fll_bw_hz=35.0, pll_bw_hz=50.0, dll_bw_hz=2.0, pll_bw_narrow_hz=20.0,
+                 dll_bw_narrow_hz=2.0, early_late_space_chips=0.5, very_early_late_space_chips=0.5, early_late_space_narrow_chips=0.5,
+                 very_early_late_space_narrow_chips=0.5, extend_correlation_symbols=1, high_dyn=0, smoother_length=10, cn0_samples=20, cn0_min=25,
+                 max_lock_fail=50, carrier_lock_th=0.85, track_pilot=0, dump=0, dump_filename=b"")
+        d.update(kw)
+        self.conf = GbRefTrkConf(**d)
+        self.h = self.L.gbref_trk_block_create(C.byref(self.conf))
+
+    def start(self, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index=0):
+        self.L.gbref_trk_block_start(self.h, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index)
+
+    def run(self, samples_c64, max_epochs):
+        x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
+        out = (GbRefTrkEpoch * max_epochs)()
+        ev = np.zeros(64, np.int32)
+        nev = C.c_int(0)
+        n = self.L.gbref_trk_block_run(self.h, x, len(x) // 2, out, max_epochs, ev, 64, C.byref(nev))
+        return [out[i] for i in range(n)], list(ev[: nev.value])
+
+    def state(self):
+        return self.L.gbref_trk_block_state(self.h)
+
+    def telemetry_fault(self):
+        self.L.gbref_trk_block_telemetry_fault(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.gbref_trk_block_destroy(self.h)
+            self.h = None
