@@ -360,3 +360,78 @@ def test_c_aid_loops_on_b200_match_oracle_loops(service, variant):
     assert np.all(lock[:, F["flags"]] == 1) and abs(lock[:, F["carrier_doppler_hz"]].mean() - doppler) < 4.0
     ext = got[450:]
     assert np.all(ext[ext[:, F["flags"]] == 1, F["correlation_length_ms"]] == 5) and 0.18 < (ext[:, F["flags"]] == 1).mean() < 0.22
+
+
+def test_c1_b200_loop_against_the_reference_tracking_block(service):
+    """The same comparison with the reference's OWN block on the other side: dll_pll_veml_tracking.cc compiled from /root/reference
+    (oracle/_ref, driven by oracle/ref_blocks.cc) against the mirror loop on the B200 correlator, C1 scene, 900 epochs: identical
+    sample counters / block lengths while the NCO states coincide, correlator taps within 2e-4 of the largest tap, Doppler / code
+    position / CN0 / carrier phase trajectories together."""
+    import gnss_b200 as gb
+    import oracle_lib as ol
+    import test_ref_blocks_cpu as trb
+
+    if ol.ref_blocks() is None:
+        pytest.skip("oracle/_ref (the compiled reference) not built")
+    sats, x = c1_scene(1000)
+    service.push(1, x, gb.ITEM_32FC, 0)
+    s = sats[2]
+    code = synth.code_table("gps_l1_ca", s["prn"])
+    acq_delay, acq_doppler = float(s["delay_samples"]) - 0.2, s["doppler_hz"] - 30.0
+    got = hl.run_b200_channel(service, 1, gb.ITEM_32FC, 0, conf=hl.gps_l1_conf(prn=s["prn"]), code=code, acq_delay=acq_delay, acq_doppler=acq_doppler, acq_stamp=0,
+                              n_steps=900)
+    with trb.quiet():
+        b = ol.RefTrkBlock(pll_bw_hz=50.0, dll_bw_hz=2.0, pll_filter_order=3, dll_filter_order=2, early_late_space_chips=0.5, cn0_min=30, carrier_lock_th=0.80)
+        b.start(s["prn"], acq_delay, acq_doppler, 0, 0)
+        er, ev = b.run(x, 900)
+        b.close()
+    gv = [e for e in got if e["valid"]]
+    assert ev == [] and not any(e["loss_of_lock"] for e in got) and len(gv) >= 890 and len(er) >= len(gv)
+    for g, r in list(zip(gv, er))[:40]:
+        assert g["tracking_sample_counter"] == r.tracking_sample_counter and g["current_prn_length_samples"] == r.n_samples
+        taps = np.array(r.corr[:6], np.float32).view(np.complex64)
+        assert np.abs(g["taps"][:3] - taps).max() <= 2e-4 * np.abs(taps).max()
+    n = len(gv)
+    d_dop = np.abs(np.array([e["carrier_doppler_hz"] for e in gv]) - np.array([e.carrier_doppler_hz for e in er[:n]]))
+    d_pos = np.abs(np.array([e["tracking_sample_counter"] + e["code_phase_samples"] for e in gv]) - np.array([e.tracking_sample_counter + e.code_phase_samples for e in er[:n]]))
+    d_cn0 = np.abs(np.array([e["cn0_db_hz"] for e in gv]) - np.array([e.cn0_db_hz for e in er[:n]]))
+    d_ph = np.abs(np.array([e["carrier_phase_rads"] for e in gv]) - np.array([e.carrier_phase_rads for e in er[:n]]))
+    print("vs reference block: doppler max %.3g Hz, position max %.3g samples, cn0 max %.3g dB, phase max %.3g rad" % (d_dop.max(), d_pos.max(), d_cn0.max(), d_ph.max()))
+    assert d_dop.max() < 2.0 and np.percentile(d_dop, 95) < 0.5 and d_pos.max() < 0.05 and d_cn0.max() < 0.2 and d_ph.max() < 0.1
+    assert abs(np.mean([e["carrier_doppler_hz"] for e in gv[-200:]]) - s["doppler_hz"]) < 3.0
+
+
+def test_acquisition_against_the_reference_block(service):
+    """C1 batch against pcps_acquisition.cc itself (oracle/_ref): 8 present PRNs + 1 absent, gr_complex and cshort input."""
+    import gnss_b200 as gb
+    import oracle_lib as ol
+
+    if ol.ref_blocks() is None:
+        pytest.skip("oracle/_ref (the compiled reference) not built")
+    sats, x = c1_scene(3, cn0=58.0)
+    for item, it in (("32fc", gb.ITEM_32FC), ("16ic", gb.ITEM_16IC)):
+        host = x if item == "32fc" else synth.quantize(x, "16ic")
+        service.push(2, host, it, 777)
+        cfg = dict(doppler_max=5000, doppler_step=250, threshold=0.008, samples_per_chip=4)
+        acqs, codes = [], []
+        for p in PRNS + [31]:
+            c = np.zeros(8000, np.float32)
+            ol.oracle().go_gps_l1_ca_code_sampled(c, p, 4000000, 0)
+            codes.append(c.view(np.complex64))
+            a = gb.Acquisition(service, item_type=it, **cfg)
+            a.set_local_code(codes[-1])
+            acqs.append(a)
+        res = gb.acq_run_batch(acqs, 2, 777 + 500)
+        for k, (a, r) in enumerate(zip(acqs, res)):
+            b = ol.RefAcqBlock(cshort=int(item == "16ic"), prn=(PRNS + [31])[k], **cfg)
+            b.set_local_code(codes[k])
+            b.start(777 + 500)
+            seg = host[500:4500] if item == "32fc" else host[1000:9000]
+            st, ev = b.dwell(seg)
+            assert {1: 1, 0: 2}[r.decision] == ev, (item, k, r.decision, ev)
+            assert abs(r.input_power - st.input_power) <= 1e-4 * st.input_power
+            if k < 8:
+                assert (r.acq_delay_samples, r.acq_doppler_hz, r.acq_samplestamp) == (st.acq_delay_samples, st.acq_doppler_hz, st.acq_samplestamp_samples), (item, k)
+                assert abs(r.test_statistic - st.test_statistics) <= 1e-4 * st.test_statistics and ev == 1
+            b.close()
+            a.close()
