@@ -1934,6 +1934,25 @@ extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_
     return rc;
 }
 
+// = AcquisitionInterface::stop_acquisition() for a search that is in flight: the launched batch is abandoned -- nothing is
+// waited for, no result is read, no handle's dwell / step-two state advances (the kernels still run to completion on the stream)
+extern "C" int gb200_acq_discard_batch(gb200_acq* const* list, int n)
+{
+    if (!list || n <= 0 || !list[0]) return GB200_E_INVALID;
+    gb200_service* s = list[0]->s;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    AcqBatchCtx& ctx = s->acq_ctx;
+    if (!ctx.active)
+        {
+            s->set_error("gb200_acq_discard_batch: nothing launched");
+            return GB200_E_STATE;
+        }
+    for (int i = 0; i < n; i++)
+        if (list[i]) list[i]->pending = false;
+    ctx.active = false;
+    return GB200_OK;
+}
+
 extern "C" int gb200_acq_run_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index, gb200_acq_result* out)
 {
     if (!list || n <= 0 || !list[0]) return GB200_E_INVALID;

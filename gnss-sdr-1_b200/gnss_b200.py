@@ -79,7 +79,7 @@ EXPORTS = [
     "gb200_service_measure_fp32", "gb200_service_set_tuning", "gb200_stream_wait", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
-    "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine", "gb200_acq_second_peak", "gb200_acq_wiped_spectrum_peak", "gb200_second_peak_noalloc",
+    "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_discard_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine", "gb200_acq_second_peak", "gb200_acq_wiped_spectrum_peak", "gb200_second_peak_noalloc",
     "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_set_taps", "gb200_trk_correlate",
     "gb200_trk_correlate_batch", "gb200_trk_correlate_16sc", "gb200_trk_correlate_16sc_batch", "gb200_trk_batch_create", "gb200_trk_batch_launch", "gb200_trk_batch_fetch", "gb200_trk_batch_destroy",
 ]
@@ -137,6 +137,7 @@ def lib():
     L.gb200_acq_run_batch.argtypes = [C.POINTER(vp), i, i, u64, C.POINTER(AcqResult)]
     L.gb200_acq_launch_batch.argtypes = [C.POINTER(vp), i, i, u64]
     L.gb200_acq_collect_batch.argtypes = [C.POINTER(vp), i, C.POINTER(AcqResult)]
+    L.gb200_acq_discard_batch.argtypes = [C.POINTER(vp), i]
     L.gb200_acq_keep_grid.argtypes = [vp, i]
     L.gb200_acq_read_grid.argtypes = [vp, vp]
     L.gb200_acq_iq_combine.argtypes = [vp, vp, vp, vp, f, C.POINTER(AcqIqBin)]
@@ -370,6 +371,12 @@ def acq_run_batch(acqs, stream_id, first_sample_index):
 def acq_launch_batch(acqs, handles, stream_id, first_sample_index):
     s = acqs[0].s
     s.check(s.L.gb200_acq_launch_batch(handles, len(acqs), stream_id, first_sample_index))
+
+
+def acq_discard_batch(acqs, handles):
+    """stop_acquisition() for a launched batch: abandon it without waiting"""
+    s = acqs[0].s
+    s.check(s.L.gb200_acq_discard_batch(handles, len(acqs)))
 
 
 def acq_collect_batch(acqs, handles):

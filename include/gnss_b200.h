@@ -205,6 +205,10 @@ GB200_API int gb200_acq_run_batch(gb200_acq* const* list, int n, int stream_id, 
 /* split form of run_batch: launch is asynchronous on the service stream, collect blocks */
 GB200_API int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_id, uint64_t first_sample_index);
 GB200_API int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_result* out);
+/* = AcquisitionInterface::stop_acquisition() (acquisition_interface.h:71) for a launched batch: abandon it.  Nothing is waited for,
+ * no result is read and no handle's dwell / step-two state advances; the next gb200_acq_launch_batch may follow at once (its
+ * kernels queue behind the abandoned ones on the service stream). */
+GB200_API int gb200_acq_discard_batch(gb200_acq* const* list, int n);
 /* magnitude grid of the last dwell, num_bins x effective_fft_size floats (dump=true, pcps_acquisition.cc:741-744).
  * Only valid when the handle keeps a grid: max_dwells > 1, use_CFAR_algorithm_flag == 0, or after gb200_acq_keep_grid(a, 1). */
 GB200_API int gb200_acq_keep_grid(gb200_acq* a, int keep);

@@ -12,8 +12,9 @@ import scipy.fft as sfft
 
 
 class AcqPort:
-    def __init__(self, fs, n_fft, consumed, doppler_max, doppler_step, workers=-1):
+    def __init__(self, fs, n_fft, consumed, doppler_max, doppler_step, workers=-1, group=4):
         self.fs, self.n, self.consumed = fs, n_fft, consumed
+        self.group = group
         self.workers = workers
         self.num_bins = int(np.ceil(2 * doppler_max / doppler_step))
         dopp = -doppler_max + doppler_step * np.arange(self.num_bins)
@@ -36,16 +37,22 @@ class AcqPort:
         x[: self.consumed] = samples_c64[: self.consumed]
         power = np.float32(np.sum(x.real * x.real + x.imag * x.imag, dtype=np.float32) / np.float32(self.n))
         out = []
+        nf = np.float32(self.n) * np.float32(self.n)
         for cf in code_ffts:
-            wiped = x[None, :] * self.wipe                      # volk_32fc_x2_multiply_32fc per bin (:717)
-            spec = sfft.fft(wiped, axis=1, workers=self.workers)  # d_fft_if->execute() (:721)
-            spec *= cf[None, :]                                  # (:724)
-            y = sfft.ifft(spec, axis=1, workers=self.workers, norm="forward")  # un-normalised backward (:727)
-            mag = y.real * y.real + y.imag * y.imag             # (:733)
-            idx = np.argmax(mag, axis=1)                        # volk_gnsssdr_32f_index_max_32u per bin (:576)
-            peak = mag[np.arange(self.num_bins), idx]
-            b = int(np.argmax(peak))                            # first bin wins ties (strict >)
-            nf = np.float32(self.n) * np.float32(self.n)
-            stat = np.float32(peak[b]) / (nf * nf) / power
-            out.append((int(idx[b]), int(self.doppler[b]), float(stat)))
+            # the Doppler loop in cache-sized groups of bins (same arithmetic per bin; a whole-grid pass would stream 20 MB arrays
+            # through DRAM five times): the first maximum over bins in ascending order wins, strict '>' (:576-583)
+            best_mag, best_bin, best_idx = np.float32(0), 0, 0
+            for b0 in range(0, self.num_bins, self.group):
+                wiped = x[None, :] * self.wipe[b0: b0 + self.group]      # volk_32fc_x2_multiply_32fc per bin (:717)
+                spec = sfft.fft(wiped, axis=1, workers=self.workers, overwrite_x=True)  # d_fft_if->execute() (:721)
+                spec *= cf[None, :]                                      # (:724)
+                y = sfft.ifft(spec, axis=1, workers=self.workers, norm="forward", overwrite_x=True)  # un-normalised backward (:727)
+                mag = y.real * y.real + y.imag * y.imag                 # (:733)
+                idx = np.argmax(mag, axis=1)                            # volk_gnsssdr_32f_index_max_32u per bin (:576)
+                peak = mag[np.arange(mag.shape[0]), idx]
+                k = int(np.argmax(peak))
+                if peak[k] > best_mag:
+                    best_mag, best_bin, best_idx = peak[k], b0 + k, int(idx[k])
+            stat = np.float32(best_mag) / (nf * nf) / power
+            out.append((best_idx, int(self.doppler[best_bin]), float(stat)))
         return out

@@ -557,6 +557,15 @@ def test_set_local_code_between_launch_and_collect(service):
     got2 = gb.acq_run_batch(acqs, 2, 100)
     for r, w in zip(got2, want):
         assert (r.code_phase_index, r.doppler_bin, r.decision, r.peak_mag) == (w.code_phase_index, w.doppler_bin, w.decision, w.peak_mag)
+    # stop_acquisition(): launches abandoned without a wait leave no trace in the handles' state; a collected one after them is right
+    for _ in range(3):
+        gb.acq_launch_batch(acqs, handles, 2, 100)
+        gb.acq_discard_batch(acqs, handles)
+    with pytest.raises(gb.Gb200Error):
+        gb.acq_discard_batch(acqs, handles)
+    got2 = gb.acq_run_batch(acqs, 2, 100)
+    for r, w in zip(got2, want):
+        assert (r.code_phase_index, r.doppler_bin, r.decision, r.peak_mag) == (w.code_phase_index, w.doppler_bin, w.decision, w.peak_mag)
     # ... and after a Doppler-grid change of one member the tables are rebuilt
     acqs[1].set_doppler(2500, 250)
     got3 = gb.acq_run_batch(acqs, 2, 100)
