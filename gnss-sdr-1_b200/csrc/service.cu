@@ -825,6 +825,25 @@ extern "C" int gb200_stream_push(gb200_service* s, int stream_id, const void* sa
     return ring_push(s, stream_id, samples, n_items, item_type, first_sample_index, cudaMemcpyHostToDevice);
 }
 
+// Several blocks of one flowgraph are fed the SAME conditioned stream by the scheduler (every channel's acquisition and tracking
+// block hangs off the signal conditioner's output): each hands over what it was given, the first to arrive copies it to the
+// device, the others find their items already in the ring.
+extern "C" int gb200_stream_push_shared(gb200_service* s, int stream_id, const void* samples, size_t n_items, int item_type, uint64_t first_sample_index)
+{
+    if (!s || !samples) return GB200_E_INVALID;
+    if (stream_id < 0 || stream_id >= (int)s->rings.size() || item_type < 0 || item_type > 2) return GB200_E_INVALID;
+    std::lock_guard<std::recursive_mutex> lk(s->mu);
+    const GbRing& r = s->rings[stream_id];
+    if (r.any && r.item_type == item_type && first_sample_index <= r.end)
+        {
+            const uint64_t end = first_sample_index + n_items;
+            if (end <= r.end) return GB200_OK;  // all of it is there already (or older than what the ring still holds)
+            const uint64_t skip = r.end - first_sample_index;
+            return ring_push(s, stream_id, (const char*)samples + skip * gb_item_bytes(item_type), (size_t)(n_items - skip), item_type, r.end, cudaMemcpyHostToDevice);
+        }
+    return ring_push(s, stream_id, samples, n_items, item_type, first_sample_index, cudaMemcpyHostToDevice);
+}
+
 extern "C" int gb200_stream_wait(gb200_service* s, int stream_id)
 {
     if (!s || stream_id < 0 || stream_id >= (int)s->rings.size()) return GB200_E_INVALID;

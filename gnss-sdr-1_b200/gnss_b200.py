@@ -76,7 +76,7 @@ EXPORTS = [
     "gb200_service_create", "gb200_service_destroy", "gb200_last_error", "gb200_version", "gb200_service_cuda_stream",
     "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
     "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_acq_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
-    "gb200_service_measure_fp32", "gb200_service_set_tuning", "gb200_stream_wait", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
+    "gb200_service_measure_fp32", "gb200_service_set_tuning", "gb200_stream_wait", "gb200_stream_push_shared", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
     "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_discard_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine", "gb200_acq_second_peak", "gb200_acq_wiped_spectrum_peak", "gb200_second_peak_noalloc",
@@ -118,6 +118,7 @@ def lib():
     L.gb200_stream_push.argtypes = [vp, i, vp, C.c_size_t, i, u64]
     L.gb200_service_set_tuning.argtypes = [vp, C.c_char_p, i]
     L.gb200_stream_wait.argtypes = [vp, i]
+    L.gb200_stream_push_shared.argtypes = [vp, i, vp, C.c_size_t, i, u64]
     L.gb200_stream_set_decimator.argtypes = [vp, i, i, u32, vp, u32]
     L.gb200_firdes_low_pass.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, vp, C.POINTER(u32)]
     L.gb200_stream_read.argtypes = [vp, i, u64, C.c_size_t, vp]
@@ -190,6 +191,12 @@ class Service:
             k, v = kv.split("=")
             self.set_tuning(k.strip(), int(v))
         return spec
+
+    def push_shared(self, stream_id, samples, item_type, first_sample_index):
+        """one of several producers of the same stream: only items beyond the ring's newest are copied"""
+        a = np.ascontiguousarray(samples, ITEM_DTYPES[item_type])
+        n_items = a.size if item_type == ITEM_32FC else a.size // 2
+        self.check(self.L.gb200_stream_push_shared(self.h, stream_id, _ptr(a), n_items, item_type, first_sample_index))
 
     def wait_pushes(self, stream_id):
         self.check(self.L.gb200_stream_wait(self.h, stream_id))

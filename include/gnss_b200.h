@@ -108,6 +108,12 @@ GB200_API int gb200_service_set_tuning(gb200_service* s, const char* key, int va
  * (a GNU Radio block that hands over its input buffer calls gb200_stream_wait before consume_each()). */
 GB200_API int gb200_stream_push(gb200_service* s, int stream_id, const void* samples, size_t n_items, int item_type,
     uint64_t first_sample_index);
+/* The same for SEVERAL producers of one stream: in a GNU Radio flowgraph every channel's acquisition and tracking block is fed the
+ * same conditioned stream (channel.cc:127-186 connects them all to the conditioner's output) and each hands over the items its
+ * general_work() was given; items already in the ring are skipped, only the part beyond its newest item is copied.  A block that
+ * lags more than the ring capacity behind finds its items gone (the later correlate / run call reports GB200_E_RANGE). */
+GB200_API int gb200_stream_push_shared(gb200_service* s, int stream_id, const void* samples, size_t n_items, int item_type,
+    uint64_t first_sample_index);
 /* blocks until every push issued so far to `stream_id` has landed in the device ring (the caller's buffers are free again) */
 GB200_API int gb200_stream_wait(gb200_service* s, int stream_id);
 /* `inverted_spectrum` of the data-type adapters (ishort_to_complex.cc:49-59, ibyte_to_complex.cc:49-59: a conjugate_cc /
