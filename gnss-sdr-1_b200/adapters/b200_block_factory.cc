@@ -1,0 +1,33 @@
+#include "b200_block_factory.h"
+#include "galileo_e1_dll_pll_veml_tracking_b200.h"
+#include "galileo_e1_pcps_ambiguous_acquisition_b200.h"
+#include "gps_l1_ca_dll_pll_tracking_b200.h"
+#include "gps_l1_ca_pcps_acquisition_b200.h"
+
+std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const std::shared_ptr<ConfigurationInterface>& configuration, const std::string& role,
+    const std::string& implementation, unsigned int in_streams, unsigned int out_streams)
+{
+    if (implementation == "GPS_L1_CA_PCPS_Acquisition_B200")
+        return std::unique_ptr<AcquisitionInterface>(new GpsL1CaPcpsAcquisitionB200(configuration.get(), role, in_streams, out_streams));
+    if (implementation == "Galileo_E1_PCPS_Ambiguous_Acquisition_B200")
+        return std::unique_ptr<AcquisitionInterface>(new GalileoE1PcpsAmbiguousAcquisitionB200(configuration.get(), role, in_streams, out_streams));
+    return nullptr;
+}
+
+std::unique_ptr<TrackingInterface> GetB200TrkBlock(const std::shared_ptr<ConfigurationInterface>& configuration, const std::string& role,
+    const std::string& implementation, unsigned int in_streams, unsigned int out_streams)
+{
+    if (implementation == "GPS_L1_CA_DLL_PLL_Tracking_B200")
+        return std::unique_ptr<TrackingInterface>(new GpsL1CaDllPllTrackingB200(configuration.get(), role, in_streams, out_streams));
+    if (implementation == "Galileo_E1_DLL_PLL_VEML_Tracking_B200")
+        return std::unique_ptr<TrackingInterface>(new GalileoE1DllPllVemlTrackingB200(configuration.get(), role, in_streams, out_streams));
+    return nullptr;
+}
+
+std::unique_ptr<GNSSBlockInterface> GetB200Block(const std::shared_ptr<ConfigurationInterface>& configuration, const std::string& role,
+    const std::string& implementation, unsigned int in_streams, unsigned int out_streams)
+{
+    if (auto a = GetB200AcqBlock(configuration, role, implementation, in_streams, out_streams)) return a;
+    if (auto t = GetB200TrkBlock(configuration, role, implementation, in_streams, out_streams)) return t;
+    return nullptr;
+}

@@ -3,11 +3,18 @@
 #ifndef GB_ORACLE_SHIM_CHANNEL_FSM_H
 #define GB_ORACLE_SHIM_CHANNEL_FSM_H
 #include <cstdint>
+#include <functional>
 #include <memory>
 class ChannelFsm
 {
 public:
     int valid_acquisitions = 0;
-    bool Event_valid_acquisition() { valid_acquisitions++; return true; }
+    std::function<void()> on_valid_acquisition;  // harness hook: what ChannelFsm::Event_valid_acquisition does next (start_tracking)
+    bool Event_valid_acquisition()
+    {
+        valid_acquisitions++;
+        if (on_valid_acquisition) on_valid_acquisition();
+        return true;
+    }
 };
 #endif

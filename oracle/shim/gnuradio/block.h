@@ -24,7 +24,14 @@ auto bind(F&& f, A&&... a) -> decltype(std::bind(std::forward<F>(f), std::forwar
 using std::placeholders::_1;
 namespace gr
 {
-class block
+class basic_block
+{
+public:
+    virtual ~basic_block() {}
+};
+typedef std::shared_ptr<basic_block> basic_block_sptr;
+
+class block : public basic_block
 {
 public:
     block(const std::string& name, io_signature::sptr in, io_signature::sptr out) : d_name(name), d_in(in), d_out(out) {}
