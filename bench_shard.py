@@ -70,23 +70,35 @@ def run(args, rank, local_rank, world):
     handles = gb.acq_handles(acqs) if acqs else None
     acq_cells = 32 * 40 * n_gps + 36 * 80 * n_e1
 
+    phases, phase_log = {}, {}
+
+    def mark(name, t0):
+        phases[name] = phases.get(name, 0.0) + (time.perf_counter() - t0) * 1e3
+        return time.perf_counter()
+
     def acq_step():
+        t = time.perf_counter()
         if backend_inited:
             dist.broadcast(d_block, src=0)
         torch.cuda.current_stream().synchronize()
+        t = mark("acq_broadcast", t)
         svc.push_device_ptr(0, d_block.data_ptr(), n_e1 + 1000, gb.ITEM_32FC, 0)
         recs = []
         if acqs:
             res = gb.acq_run_batch(acqs, 0, 0)
+            t = mark("acq_push_and_search", t)
             for u, r in zip(acq_unit, res):
                 recs.append(shard.acq_record(u, units[u], r.code_phase_index, r.doppler_bin, r.doppler_hz, r.peak_mag, r.input_power))
+        t = mark("acq_records", t)
         if backend_inited:
-            allrecs = shard.gather_records(recs, dist, dst=0)
+            allrecs = shard.gather_records(recs, dist, dst=0, capacity=-(-len(units) // world))
         else:
             allrecs = recs
+        t = mark("acq_gather", t)
         merged = None
         if rank == 0:
-            merged = shard.merge_acq_records(allrecs, len(prn_list), 1)  # statistic is recomputed per system below
+            merged = shard.merge_acq_winners(allrecs)  # one winner per PRN with the reference's tie-break
+        mark("acq_merge", t)
         return merged
 
     # ------------------------------------------------------------------ tracking: C4, 1024 channels
@@ -123,27 +135,33 @@ def run(args, rank, local_rank, world):
                           float(np.float32(0.3 + 1e-3 * e)), float(cs), 0.0, epoch))
     reqs = gb.make_reqs(items) if items else None
     per_ch_epochs = [step_items // kinds[c % 4][3] for c in my_ch]
+    pack_ch = np.concatenate([np.full(ne, j) for j, ne in enumerate(per_ch_epochs)]) if my_ch else np.zeros(0, int)
+    pack_ep = np.concatenate([np.arange(ne) for ne in per_ch_epochs]) if my_ch else np.zeros(0, int)
     trk_chs = n_ch // 4 * (3 * 40 * 20000 + 10 * 80000)
 
     def trk_step():
+        t = time.perf_counter()
         if backend_inited:
             dist.broadcast(d_bytes, src=0)
         torch.cuda.current_stream().synchronize()
+        t = mark("trk_broadcast", t)
         svc.push_device_ptr(1, d_bytes.data_ptr(), step_items + 100_000, gb.ITEM_8IC, 0)
         local = np.zeros((len(my_ch), max_epochs, gb.OUT_STRIDE), np.complex64)
         if reqs is not None:
             out = gb.correlate_batch(svc, reqs)
-            k = 0
-            for j, ne in enumerate(per_ch_epochs):
-                local[j, :ne] = out[k: k + ne]
-                k += ne
+            t = mark("trk_push_and_correlate", t)
+            local[pack_ch, pack_ep] = out  # request order -> [channel, epoch] (index arrays built once)
+        t = mark("trk_pack", t)
         if backend_inited:
-            return shard.gather_channel_outputs(my_ch, local, n_ch, dist, dst=0)
+            r = shard.gather_channel_outputs(my_ch, local, n_ch, dist, dst=0)
+            mark("trk_gather", t)
+            return r
         return local
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
             fn()
+        phases.clear()
         if backend_inited:
             dist.barrier()
         torch.cuda.synchronize()
@@ -156,6 +174,7 @@ def run(args, rank, local_rank, world):
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         if backend_inited:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        phase_log.update({k: v / steps for k, v in phases.items()})
         return float(ms.item()) / steps, last
 
     sampler = bench.ClockSampler(local_rank) if rank == 0 else None
@@ -173,11 +192,11 @@ def run(args, rank, local_rank, world):
         found = {}
         for s in sats:
             slot = (s["prn"] - 1) if s["kind"] == "gps_l1_ca" else 32 + s["prn"] - 1
-            m = merged[slot]
+            hit = merged[merged["prn_slot"] == slot]
             n = n_gps if s["kind"] == "gps_l1_ca" else n_e1
-            ok = m is not None and abs(int(m["code_phase_index"]) - s["delay_samples"] % n) <= 1 and abs(int(m["doppler_hz"]) - s["doppler_hz"]) <= 250
+            ok = len(hit) == 1 and abs(int(hit[0]["code_phase_index"]) - s["delay_samples"] % n) <= 1 and abs(int(hit[0]["doppler_hz"]) - s["doppler_hz"]) <= 250
             found["%s%d" % ("G" if s["kind"] == "gps_l1_ca" else "E", s["prn"])] = bool(ok)
-        assert all(m is not None for m in merged), "a PRN's record is missing from the gather"
+        assert len(merged) == len(prn_list), "a PRN's record is missing from the gather"
         assert full.shape == (n_ch, max_epochs, gb.OUT_STRIDE) and np.isfinite(full).all() and np.abs(full[:, 0, 1]).min() > 0
         line = {
             "metric": "acq grid cells/s (tracking channel*Msamples/s in 'tracking_value'), ONE fixed job sharded over the GPUs",
@@ -188,6 +207,7 @@ def run(args, rank, local_rank, world):
                        "in_timed_region": "NCCL broadcast of the sample block, device push, own share through the C ABI, NCCL all-gather of records / outputs, merge on rank 0",
                        "acq_ms_per_step": acq_ms, "trk_ms_per_step": trk_ms, "units_per_rank": len(mine), "channels_per_rank": len(my_ch)},
             "tracking_value": trk_chs / (trk_ms * 1e-3) / 1e6, "tracking_unit": "channel*Msamples/s",
+            "host_phases_ms_per_step_rank0": phase_log,
             "acq_found": found, "clocks": sampler.summary(t0, t1),
         }
         print(json.dumps(line))

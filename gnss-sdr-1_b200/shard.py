@@ -72,53 +72,75 @@ def acq_record(unit_index, unit, code_phase_index, local_bin, local_doppler_hz, 
     return r
 
 
+def merge_acq_winners(records):
+    """The winning record of every PRN slot present in `records` (structured array, sorted by prn_slot): one lexsort with the
+    reference's ordering key (magnitude desc, Doppler bin asc, code-phase index asc), no per-record Python work."""
+    arr = np.asarray(records, dtype=ACQ_RECORD) if not isinstance(records, np.ndarray) else records
+    if arr.size == 0:
+        return arr
+    order = np.lexsort((arr["code_phase_index"], arr["doppler_bin"], -arr["peak_mag"], arr["prn_slot"]))
+    srt = arr[order]
+    first = np.ones(len(srt), bool)
+    first[1:] = srt["prn_slot"][1:] != srt["prn_slot"][:-1]
+    return srt[first]
+
+
 def merge_acq_records(records, n_prn, fft_size, threshold=None):
     """Per PRN: the winning record over its units with the reference's tie-break, and the CFAR statistic
     max / N^4 / input_power in float32 like max_to_input_power_statistic (pcps_acquisition.cc:594)."""
-    out = []
-    for p in range(n_prn):
-        mine = [r for r in records if int(r["prn_slot"]) == p]
-        if not mine:
-            out.append(None)
+    out = [None] * n_prn
+    if len(records) == 0:
+        return out
+    arr = np.asarray(records, dtype=ACQ_RECORD) if not isinstance(records, np.ndarray) else records
+    # one sort with the ordering key (PRN, magnitude desc, Doppler bin asc, code-phase index asc); the first row of every PRN wins
+    order = np.lexsort((arr["code_phase_index"], arr["doppler_bin"], -arr["peak_mag"], arr["prn_slot"]))
+    srt = arr[order]
+    first = np.ones(len(srt), bool)
+    first[1:] = srt["prn_slot"][1:] != srt["prn_slot"][:-1]
+    nf = np.float32(fft_size) * np.float32(fft_size)
+    for best in srt[first]:
+        p = int(best["prn_slot"])
+        if p < 0 or p >= n_prn:
             continue
-        best = min(mine, key=lambda r: (-float(r["peak_mag"]), int(r["doppler_bin"]), int(r["code_phase_index"])))
-        nf = np.float32(fft_size) * np.float32(fft_size)
         stat = np.float32(best["peak_mag"]) / (nf * nf) / np.float32(best["input_power"]) if best["input_power"] > 0 else np.float32(0)
         d = {k: best[k].item() for k in ACQ_RECORD.names}
         d["test_statistic"] = float(stat)
         if threshold is not None:
             d["decision"] = int(stat > np.float32(threshold))
-        out.append(d)
+        out[p] = d
     return out
 
 
-def gather_records(local_records, dist, dst=0):
-    """Gather variable-length lists of fixed-size records on `dst` (None elsewhere) with tensor collectives only."""
+def gather_records(local_records, dist, dst=0, capacity=None):
+    """Gather lists of fixed-size records on `dst` (None elsewhere) with tensor collectives only.  `capacity` = the largest number
+    of records any rank can hold (known from the unit list: ceil(n_units / world)); with it the gather is ONE all_gather of
+    capacity + 1 records per rank (the first slot carries the count), without it the counts are exchanged first."""
     import torch
 
     world, rank = dist.get_world_size(), dist.get_rank()
     dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
     arr = np.array(local_records, dtype=ACQ_RECORD) if len(local_records) else np.zeros(0, ACQ_RECORD)
-    n = torch.tensor([arr.size], dtype=torch.int64, device=dev)
-    counts = [torch.zeros_like(n) for _ in range(world)]
-    dist.all_gather(counts, n)
-    cap = max(int(c.item()) for c in counts)
-    buf = torch.zeros(max(cap, 1) * ACQ_RECORD.itemsize, dtype=torch.uint8, device=dev)
-    raw = torch.from_numpy(arr.view(np.uint8).copy())
-    buf[: raw.numel()] = raw.to(dev)
-    bufs = [torch.zeros_like(buf) for _ in range(world)]
-    dist.all_gather(bufs, buf)
+    if capacity is None:
+        n = torch.tensor([arr.size], dtype=torch.int64, device=dev)
+        counts = [torch.zeros_like(n) for _ in range(world)]
+        dist.all_gather(counts, n)
+        capacity = max(int(c.item()) for c in counts)
+    assert arr.size <= capacity
+    host = np.zeros(capacity + 1, ACQ_RECORD)
+    host[0]["unit"] = arr.size
+    host[1: 1 + arr.size] = arr
+    buf = torch.from_numpy(host.view(np.uint8)).to(dev)
+    allbuf = torch.empty(world * buf.numel(), dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(allbuf, buf)
     if rank != dst:
         return None
-    out = []
-    for c, b in zip(counts, bufs):
-        k = int(c.item())
-        out.extend(np.frombuffer(b.cpu().numpy().tobytes()[: k * ACQ_RECORD.itemsize], dtype=ACQ_RECORD))
-    return out
+    full = np.frombuffer(allbuf.cpu().numpy().tobytes(), dtype=ACQ_RECORD).reshape(world, capacity + 1)
+    return np.concatenate([full[r, 1: 1 + int(full[r, 0]["unit"])] for r in range(world)])
 
 
 def gather_channel_outputs(local_channels, local_outputs, n_channels, dist, dst=0):
-    """Tracking: rank-local correlator outputs [n_local, epochs, taps] (complex64) -> [n_channels, epochs, taps] on `dst`."""
+    """Tracking: rank-local correlator outputs [n_local, epochs, taps] (complex64) -> [n_channels, epochs, taps] on `dst`
+    (one all_gather_into_tensor of equal-sized, zero-padded shares)."""
     import torch
 
     world, rank = dist.get_world_size(), dist.get_rank()
@@ -128,15 +150,16 @@ def gather_channel_outputs(local_channels, local_outputs, n_channels, dist, dst=
     shape = (per,) + tuple(local_outputs.shape[1:])
     pad = np.zeros(shape, np.complex64)
     pad[: len(local_channels)] = local_outputs
-    t = torch.from_numpy(pad.view(np.float32)).to(dev)
-    bufs = [torch.zeros_like(t) for _ in range(world)]
-    dist.all_gather(bufs, t)
+    t = torch.from_numpy(pad.view(np.float32)).to(dev, non_blocking=True)
+    allt = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=dev)
+    dist.all_gather_into_tensor(allt, t)
     if rank != dst:
         return None
+    host = allt.cpu().numpy().view(np.complex64)
     full = np.zeros((n_channels,) + tuple(local_outputs.shape[1:]), np.complex64)
-    for r, b in enumerate(bufs):
+    for r in range(world):
         chans = partition(n_channels, r, world)
-        full[chans] = b.cpu().numpy().view(np.complex64)[: len(chans)]
+        full[chans] = host[r, : len(chans)]
     return full
 
 
