@@ -150,12 +150,12 @@ def gather_channel_outputs(local_channels, local_outputs, n_channels, dist, dst=
     shape = (per,) + tuple(local_outputs.shape[1:])
     pad = np.zeros(shape, np.complex64)
     pad[: len(local_channels)] = local_outputs
-    t = torch.from_numpy(pad.view(np.float32)).to(dev, non_blocking=True)
-    allt = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=dev)
+    t = torch.from_numpy(pad.view(np.float32).reshape(-1)).to(dev, non_blocking=True)
+    allt = torch.empty(world * t.numel(), dtype=t.dtype, device=dev)
     dist.all_gather_into_tensor(allt, t)
     if rank != dst:
         return None
-    host = allt.cpu().numpy().view(np.complex64)
+    host = allt.cpu().numpy().view(np.complex64).reshape((world,) + shape)
     full = np.zeros((n_channels,) + tuple(local_outputs.shape[1:]), np.complex64)
     for r in range(world):
         chans = partition(n_channels, r, world)
