@@ -191,3 +191,26 @@ void volk_32f_x2_add_32f(float* c, const float* a, const float* b, unsigned int 
 {
     for (unsigned int i = 0; i < n; i++) c[i] = a[i] + b[i];
 }
+
+void volk_32f_s32f_multiply_32f(float* c, const float* a, const float scalar, unsigned int n)
+{
+    for (unsigned int i = 0; i < n; i++) c[i] = a[i] * scalar;
+}
+void volk_32fc_s32fc_multiply_32fc(lv_32fc_t* c, const lv_32fc_t* a, const lv_32fc_t scalar, unsigned int n)
+{
+    const float* pa = (const float*)a;
+    float* pc = (float*)c;
+    const float sr = crealf(scalar), si = cimagf(scalar);
+    for (unsigned int i = 0; i < n; i++)
+        {
+            const float ar = pa[2 * i], ai = pa[2 * i + 1];
+            pc[2 * i] = ar * sr - ai * si;
+            pc[2 * i + 1] = ar * si + ai * sr;
+        }
+}
+/* volk_gnsssdr_32fc_convert_16ic (gps_l1_ca_dll_pll_c_aid_tracking_sc.cc:252-255): the reference's _generic protokernel */
+#include <volk_gnsssdr_32fc_convert_16ic.h>
+void volk_gnsssdr_32fc_convert_16ic(lv_16sc_t* outputVector, const lv_32fc_t* inputVector, unsigned int num_points)
+{
+    volk_gnsssdr_32fc_convert_16ic_generic(outputVector, inputVector, num_points);
+}

@@ -1,0 +1,1 @@
+#include <gnuradio/thread/thread.h>

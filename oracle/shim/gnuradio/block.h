@@ -6,6 +6,10 @@
 #define GB_ORACLE_SHIM_GR_BLOCK_H
 #include <functional>
 #include <boost/shared_ptr.hpp>
+#include <deque>
+#include <fstream>
+#include <gnuradio/gr_complex.h>
+#include <iostream>
 #include <gnuradio/io_signature.h>
 #include <gnuradio/thread/thread.h>
 #include <gnuradio/types.h>

@@ -17,6 +17,7 @@ struct pmt_base
 {
     std::string sym;
     long lval = 0;
+    double dval = 0.0;
     boost::any a;
 };
 typedef std::shared_ptr<pmt_base> pmt_t;
@@ -33,6 +34,13 @@ inline pmt_t from_long(long v)
     return p;
 }
 inline long to_long(const pmt_t& p) { return p->lval; }
+inline pmt_t from_double(double v)
+{
+    pmt_t p(new pmt_base);
+    p->dval = v;
+    return p;
+}
+inline double to_double(const pmt_t& p) { return p->dval; }
 inline pmt_t make_any(const boost::any& a)
 {
     pmt_t p(new pmt_base);

@@ -15,6 +15,11 @@ void volk_32fc_conjugate_32fc(lv_32fc_t* c, const lv_32fc_t* a, unsigned int n);
 void volk_32fc_magnitude_squared_32f(float* m, const lv_32fc_t* a, unsigned int n);
 void volk_32f_accumulator_s32f(float* result, const float* in, unsigned int n);
 void volk_32f_x2_add_32f(float* c, const float* a, const float* b, unsigned int n);
+/* used by the sibling acquisition blocks (Tong, 8 ms, E5a CAF, fine Doppler, QuickSync) */
+void volk_32f_s32f_multiply_32f(float* c, const float* a, const float scalar, unsigned int n);
+void volk_32fc_s32fc_multiply_32fc(lv_32fc_t* c, const lv_32fc_t* a, const lv_32fc_t scalar, unsigned int n);
+#define volk_32f_accumulator_s32f_a volk_32f_accumulator_s32f
+#define volk_32f_s32f_multiply_32f_a volk_32f_s32f_multiply_32f
 #ifdef __cplusplus
 }
 #endif

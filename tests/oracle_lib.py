@@ -625,3 +625,80 @@ class RefTrkBlock:
         if self.h:
             self.L.gbref_trk_block_destroy(self.h)
             self.h = None
+
+
+# ---------------------------------------------------------------- the reference's sibling blocks (oracle/ref_blocks2.cc)
+class GbRefAcqvCall(C.Structure):
+    _fields_ = [("state_before", C.c_int32), ("state_after", C.c_int32), ("consumed", C.c_int32), ("event", C.c_int32), ("test_statistics", C.c_float),
+                ("input_power", C.c_float), ("mag", C.c_float), ("count", C.c_uint32), ("tong_count", C.c_uint32), ("acq_delay_samples", C.c_double),
+                ("acq_doppler_hz", C.c_double), ("acq_samplestamp_samples", C.c_uint64), ("sample_counter", C.c_uint64), ("acq_doppler_step", C.c_uint32),
+                ("active", C.c_int32)]
+
+
+REF_TONG, REF_8MS, REF_E5A, REF_QUICKSYNC = 0, 1, 2, 3
+
+
+def ref_blocks2():
+    L = ref_blocks()
+    if L is None or not hasattr(L, "gbref_acqv_create"):
+        return None
+    if getattr(L, "_blocks2_bound", False):
+        return L
+    L.gbref_acqv_create.argtypes = [C.c_int, f64p, C.c_char, C.c_char_p]
+    L.gbref_acqv_create.restype = C.c_void_p
+    L.gbref_acqv_destroy.argtypes = [C.c_void_p]
+    L.gbref_acqv_vector_items.argtypes = [C.c_void_p]
+    L.gbref_acqv_vector_items.restype = C.c_uint32
+    L.gbref_acqv_init.argtypes = [C.c_void_p]
+    L.gbref_acqv_set_local_code.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gbref_acqv_set_state.argtypes = [C.c_void_p, C.c_int]
+    L.gbref_acqv_set_active.argtypes = [C.c_void_p, C.c_int]
+    L.gbref_acqv_work.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(GbRefAcqvCall)]
+    L.gbref_acqv_caf_vector.argtypes = [C.c_void_p, f32p, C.c_int]
+    L.gbref_set_flags.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double]
+    L._blocks2_bound = True
+    return L
+
+
+class RefAcqVariantBlock:
+    """pcps_tong_acquisition_cc / galileo_pcps_8ms_acquisition_cc / galileo_e5a_noncoherentIQ_acquisition_caf_cc /
+    pcps_quicksync_acquisition_cc compiled from /root/reference, one general_work() call at a time."""
+
+    def __init__(self, variant, sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells=1, tong_init_val=1,
+                 tong_max_val=2, tong_max_dwells=20, bit_transition_flag=0, both_signal_components=0, caf_window_hz=0, zero_padding=0, folding_factor=2, prn=1,
+                 system=b"G", signal=b"1C"):
+        self.L = ref_blocks2()
+        cfg = np.array([sampled_ms, max_dwells, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, tong_init_val, tong_max_val,
+                        tong_max_dwells, bit_transition_flag, both_signal_components, caf_window_hz, zero_padding, folding_factor, prn], np.float64)
+        self.h = self.L.gbref_acqv_create(variant, cfg, system, signal)
+        self.vector_items = self.L.gbref_acqv_vector_items(self.h)
+        self.L.gbref_acqv_init(self.h)
+        self._keep = []
+
+    def set_local_code(self, code_c64, code_q_c64=None):
+        c = np.ascontiguousarray(code_c64, np.complex64).copy()
+        q = np.ascontiguousarray(code_q_c64, np.complex64).copy() if code_q_c64 is not None else None
+        self._keep = [c, q]
+        self.L.gbref_acqv_set_local_code(self.h, c.ctypes.data_as(C.c_void_p), q.ctypes.data_as(C.c_void_p) if q is not None else None)
+
+    def set_state(self, state):
+        self.L.gbref_acqv_set_state(self.h, state)
+
+    def set_active(self, active=True):
+        self.L.gbref_acqv_set_active(self.h, int(active))
+
+    def work(self, items_c64, n_in):
+        x = np.ascontiguousarray(items_c64, np.complex64)
+        r = GbRefAcqvCall()
+        self.L.gbref_acqv_work(self.h, x.ctypes.data_as(C.c_void_p), n_in, C.byref(r))
+        return r
+
+    def caf_vector(self, n):
+        out = np.zeros(n, np.float32)
+        k = self.L.gbref_acqv_caf_vector(self.h, out, n)
+        return out[:k]
+
+    def close(self):
+        if self.h:
+            self.L.gbref_acqv_destroy(self.h)
+            self.h = None

@@ -1,0 +1,127 @@
+"""The reference's SIBLING acquisition blocks themselves as the oracle of their restatements (CPU only).
+
+pcps_tong_acquisition_cc, galileo_pcps_8ms_acquisition_cc and galileo_e5a_noncoherentIQ_acquisition_caf_cc are compiled unmodified
+from /root/reference into oracle/_ref (oracle/ref_blocks2.cc drives them).  The restatements oracle/gnss_oracle.c go_acqv_* / go_e5a_*
+-- the checkers of the GPU tests of B200_Pcps_Tong_Acquisition, B200_Galileo_Pcps_8ms_Acquisition and
+B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf -- are held to the blocks dwell by dwell: statistic, input power, delay, Doppler,
+counters and events EQUAL (same DFT, same float32 arithmetic).  This turns "block-level parity unpinned" into pinned for them."""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import synth
+
+pytestmark = pytest.mark.skipif(ol.ref_blocks2() is None, reason="oracle/_ref (the compiled reference) not built")
+
+
+def drive(block, x, vector_items, max_calls=200):
+    """general_work() calls over `x` until an event is published; returns the calls that ran a dwell and the event"""
+    pos, dwells = 0, []
+    for _ in range(max_calls):
+        n_avail = (len(x) - pos) // vector_items if vector_items > 1 else len(x) - pos
+        r = block.work(x[pos:] if pos < len(x) else x[:1], max(0, n_avail))
+        pos += r.consumed * (vector_items if vector_items > 1 else 1)
+        dwells.append(r)
+        if r.event:
+            return dwells, r.event
+    return dwells, 0
+
+
+def test_tong_block_equals_restatement(golden_dir):
+    x = np.fromfile(golden_dir + "/GPS_L1_CA_ID_1_Fs_4Msps_2ms.dat", np.complex64)
+    rng = np.random.default_rng(3)
+    x4 = np.concatenate([x, x + 0.02 * (rng.standard_normal(8000) + 1j * rng.standard_normal(8000)).astype(np.complex64), x]).astype(np.complex64)
+    code = synth.golden_array("gps_prn1_4msps_sampled")[:4000]
+    for thr, init, mx, want_event in ((0.3, 1, 4, 1), (1e9, 3, 5, 2), (0.3, 2, 3, 1)):
+        b = ol.RefAcqVariantBlock(ol.REF_TONG, 1, 5000, 250, 4000000, 4000, 4000, thr, tong_init_val=init, tong_max_val=mx, tong_max_dwells=20)
+        b.set_local_code(code)
+        b.set_state(1)
+        o = ol.OracleAcqVariant(ol.ACQV_TONG, 4000, 4000, 5000, 250, 4000000, thr, tong_init_val=init, tong_max_val=mx, tong_max_dwells=20)
+        o.set_local_code(code)
+        o.restart()
+        calls, ev = drive(b, x4, 4000)
+        assert ev == want_event
+        k = 0
+        for r in calls:
+            if r.state_before != 1:
+                continue
+            ro = o.run(x4[4000 * k: 4000 * (k + 1)])
+            k += 1
+            assert (r.test_statistics, r.input_power, r.acq_delay_samples, r.acq_doppler_hz, r.tong_count, r.count) == \
+                (ro.test_statistic, ro.input_power, ro.acq_delay_samples, float(ro.doppler_hz), ro.tong_count, ro.dwell_count), (thr, k)
+            assert {2: 1, 3: 0}.get(r.state_after, 2) == ro.decision
+        assert k >= 1
+        b.close()
+        o.close()
+
+
+def test_galileo_8ms_block_equals_restatement(golden_dir):
+    xg = np.fromfile(golden_dir + "/Galileo_E1_ID_1_Fs_4Msps_8ms.dat", np.complex64)
+    flipped = xg.copy()
+    flipped[16000 + 2920:] *= -1  # data bit transition between the two code periods: code B wins
+    cg = synth.golden_array("gal_e1b_prn1_4msps_sampled")[:16000]
+    code = np.concatenate([cg, cg])
+    for stream_x, thr, want_event in ((xg, 1e-4, 1), (flipped, 1e-4, 1), (xg, 1e9, 2)):
+        b = ol.RefAcqVariantBlock(ol.REF_8MS, 8, 10000, 250, 4000000, 4000, 16000, thr, max_dwells=1, system=b"E", signal=b"1B")
+        b.set_local_code(code)
+        b.set_state(1)
+        o = ol.OracleAcqVariant(ol.ACQV_8MS, 32000, 16000, 10000, 250, 4000000, thr, max_dwells=1)
+        o.set_local_code(code)
+        calls, ev = drive(b, np.concatenate([stream_x, stream_x]), 32000)
+        ro = o.run(stream_x)
+        assert ev == want_event == {1: 1, 0: 2}[ro.decision]
+        r = [c for c in calls if c.state_before == 1][0]
+        assert (r.test_statistics, r.input_power, r.acq_delay_samples, r.acq_doppler_hz) == (ro.test_statistic, ro.input_power, ro.acq_delay_samples, float(ro.doppler_hz))
+        assert r.acq_delay_samples == 2920.0
+        b.close()
+        o.close()
+
+
+E5A_FS, E5A_SPM = 16000000, 16000
+
+
+@pytest.mark.parametrize("what", ["i_only", "i_and_q_caf", "two_periods_ab", "zero_padding", "bit_transition_two_dwells", "negative"])
+def test_e5a_noncoherent_iq_caf_block_equals_restatement(what):
+    delay, dop = 4321, 750.0
+    kw = dict(bit_transition_flag=False, both_signal_components=False, caf_window_hz=0, zero_padding=0)
+    sampled_ms, max_dwells, thr, n_dwells = 1, 1, 1e-9, 1
+    x = synth.iq_pilot_scene(E5A_FS, E5A_SPM, 5, 50.0, dop, delay, seed=11)
+    ci, cq = synth.iq_pilot_codes(E5A_FS, E5A_SPM, 5)
+    if what == "i_and_q_caf":
+        kw.update(both_signal_components=True, caf_window_hz=1000)
+    elif what in ("two_periods_ab", "zero_padding"):
+        sampled_ms = 2
+        x = synth.iq_pilot_scene(E5A_FS, 2 * E5A_SPM, 5, 50.0, dop, delay, seed=12, data_flip_at=E5A_SPM + delay)
+        ci, cq = synth.iq_pilot_codes(E5A_FS, 2 * E5A_SPM, 5, zero_pad_from=E5A_SPM if what == "zero_padding" else None)
+        if what == "zero_padding":
+            kw.update(zero_padding=1)
+    elif what == "bit_transition_two_dwells":
+        kw.update(bit_transition_flag=True)
+        max_dwells, n_dwells = 2, 2
+        rng = np.random.default_rng(5)
+        x = np.concatenate([x, (rng.standard_normal(E5A_SPM) + 1j * rng.standard_normal(E5A_SPM)).astype(np.complex64)])
+    elif what == "negative":
+        thr = 1e9
+    n = sampled_ms * E5A_SPM
+    b = ol.RefAcqVariantBlock(ol.REF_E5A, sampled_ms, 2000, 250, E5A_FS, E5A_SPM, E5A_SPM, thr, max_dwells=max_dwells, system=b"E", signal=b"5X",
+                              bit_transition_flag=int(kw["bit_transition_flag"]), both_signal_components=int(kw["both_signal_components"]),
+                              caf_window_hz=kw["caf_window_hz"], zero_padding=kw["zero_padding"])
+    b.set_local_code(ci, cq)
+    b.set_state(1)
+    o = ol.OracleE5aCaf(sampled_ms, E5A_SPM, E5A_SPM, max_dwells, 2000, 250, E5A_FS, thr, **kw)
+    o.set_local_code(ci, cq)
+    o.restart()
+    calls, ev = drive(b, np.concatenate([x, x[:n]]), 1)
+    cores = [c for c in calls if c.state_before == 2]
+    assert len(cores) == n_dwells
+    for k, r in enumerate(cores):
+        ro = o.run(x[k * n: (k + 1) * n])
+        assert (r.test_statistics, r.input_power, r.acq_delay_samples, r.acq_doppler_hz, r.count) == \
+            (ro.test_statistic, ro.input_power, ro.acq_delay_samples, float(ro.doppler_hz), ro.well_count), (what, k)
+    assert ev == {1: 1, 0: 2}[ro.decision]
+    if kw["caf_window_hz"]:
+        np.testing.assert_array_equal(b.caf_vector(o.num_bins), o.caf_vector())
+    if what != "negative":
+        assert ev == 1 and cores[0].acq_delay_samples % E5A_SPM == delay
+    b.close()
+    o.close()
