@@ -16,6 +16,7 @@
 //   bool correlate(uint64_t first_sample, float rem_carr_rad, float phase_step_rad, float rem_code_chips, float code_step_chips,
 //                  int n_samples, out_t* out);
 #pragma once
+#include <type_traits>
 #include <cmath>
 #include <complex>
 #include <cstdint>
@@ -51,6 +52,8 @@ class GpsL1CaDllPllCAidTracking
 {
 public:
     using out_t = typename Correlator::out_t;
+    // complex-float correlator outputs = the _cc block, int16 outputs = the _sc block
+    static constexpr bool kRetunesDllPdi = std::is_same<out_t, std::complex<float>>::value;
     GpsL1CaDllPllCAidTracking(const CAidTrkConf& c, Correlator* corr) : c_(c), corr_(corr)
     {
         // ctor (gps_l1_ca_dll_pll_c_aid_tracking_sc.cc:110-197)
@@ -182,6 +185,9 @@ public:
                                         preamble_synchronized_ = true;
                                     }
                                 CURRENT_INTEGRATION_TIME_S = static_cast<double>(c_.extend_correlation_ms) * kCodePeriodS;
+                                // the _cc block also retunes the DLL filter's integration time here (gps_l1_ca_dll_pll_c_aid_tracking_cc.cc:669);
+                                // the _sc block does not (gps_l1_ca_dll_pll_c_aid_tracking_sc.cc:666-668) -- found by running both reference blocks
+                                if (kRetunesDllPdi) code_loop_filter_.set_pdi(static_cast<float>(CURRENT_INTEGRATION_TIME_S));
                                 enable_dll_pll = true;
                             }
                         else if (preamble_synchronized_ == true)
@@ -205,6 +211,7 @@ public:
                         else
                             {
                                 CURRENT_INTEGRATION_TIME_S = static_cast<double>(correlation_length_samples_) / static_cast<double>(c_.fs_in);
+                                if (kRetunesDllPdi) code_loop_filter_.set_pdi(static_cast<float>(CURRENT_INTEGRATION_TIME_S));  // (_cc.cc:706)
                                 enable_dll_pll = true;
                             }
                     }

@@ -230,4 +230,118 @@ int gbref_acqv_caf_vector(void* hv, float* dst, int cap)
     return n;
 }
 
+// ------------------------------------------------------------------------------------------------ sibling trackers
+// kind 0: glonass_l1_ca_dll_pll_tracking_cc (gr_complex), 1: gps_l1_ca_dll_pll_c_aid_tracking_cc (gr_complex),
+// 2: gps_l1_ca_dll_pll_c_aid_tracking_sc (lv_16sc_t)
+struct GbRefTrk2
+{
+    int kind = 0;
+    glonass_l1_ca_dll_pll_tracking_cc_sptr glo;
+    gps_l1_ca_dll_pll_c_aid_tracking_cc_sptr cc;
+    gps_l1_ca_dll_pll_c_aid_tracking_sc_sptr sc;
+    gr::block* blk = nullptr;
+    Gnss_Synchro sync;
+    long long pos = 0;
+    uint32_t vector_length = 0;
+};
+
+// conf: fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms
+void* gbref_trk2_create(int kind, const double* c)
+{
+    GbRefTrk2* h = new GbRefTrk2();
+    h->kind = kind;
+    h->vector_length = (uint32_t)c[1];
+    if (kind == 0)
+        {
+            h->glo = glonass_l1_ca_dll_pll_make_tracking_cc((int64_t)c[0], (uint32_t)c[1], false, "", (float)c[2], (float)c[3], (float)c[6]);
+            h->blk = h->glo.get();
+        }
+    else if (kind == 1)
+        {
+            h->cc = gps_l1_ca_dll_pll_c_aid_make_tracking_cc((int64_t)c[0], (uint32_t)c[1], false, "", (float)c[2], (float)c[3], (float)c[4], (float)c[5], (int32_t)c[7], (float)c[6]);
+            h->blk = h->cc.get();
+        }
+    else
+        {
+            h->sc = gps_l1_ca_dll_pll_c_aid_make_tracking_sc((int64_t)c[0], (uint32_t)c[1], false, "", (float)c[2], (float)c[3], (float)c[4], (float)c[5], (int32_t)c[7], (float)c[6]);
+            h->blk = h->sc.get();
+        }
+    h->sync = Gnss_Synchro();
+    return h;
+}
+void gbref_trk2_destroy(void* hv) { delete (GbRefTrk2*)hv; }
+
+void gbref_trk2_start(void* hv, uint32_t prn, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint64_t first_item_index)
+{
+    GbRefTrk2* h = (GbRefTrk2*)hv;
+    h->sync.System = h->kind == 0 ? 'R' : 'G';
+    std::memcpy(h->sync.Signal, h->kind == 0 ? "1G" : "1C", 3);
+    h->sync.PRN = prn;
+    h->sync.Acq_delay_samples = acq_delay_samples;
+    h->sync.Acq_doppler_hz = acq_doppler_hz;
+    h->sync.Acq_samplestamp_samples = acq_samplestamp;
+    h->pos = 0;
+#define GB_START(B)                          \
+    B->set_channel(0);                       \
+    B->set_gnss_synchro(&h->sync);           \
+    B->d_sample_counter = first_item_index;  \
+    B->start_tracking();
+    if (h->glo) { GB_START(h->glo) }
+    if (h->cc) { GB_START(h->cc) }
+    if (h->sc) { GB_START(h->sc) }
+#undef GB_START
+}
+
+// the "preamble_timestamp_s" message of the telemetry decoder (c_aid trackers: starts the extended integration)
+void gbref_trk2_preamble(void* hv, double preamble_timestamp_s)
+{
+    GbRefTrk2* h = (GbRefTrk2*)hv;
+    h->blk->gb_post("preamble_timestamp_s", pmt::from_double(preamble_timestamp_s));
+}
+
+// n_calls general_work() calls (or until fewer than 2 * vector_length items remain); one row of 13 doubles per call:
+// tracking_sample_counter, prompt_i, prompt_q, carrier_doppler_hz, code_phase_samples, carrier_phase_rads, cn0_db_hz, abs_e, abs_p, abs_l,
+// flags (1 valid symbol, 2 loss of lock event), items consumed, correlation_length_ms
+int gbref_trk2_run(void* hv, const void* samples, long long n_items, int n_calls, double* rows)
+{
+    GbRefTrk2* h = (GbRefTrk2*)hv;
+    const size_t isz = h->kind == 2 ? sizeof(lv_16sc_t) : sizeof(gr_complex);
+    int k = 0;
+    for (; k < n_calls && n_items - h->pos >= 2LL * h->vector_length; k++)
+        {
+            gr_vector_int ninput(1, (int)std::min<long long>(n_items - h->pos, 1LL << 30));
+            gr_vector_const_void_star in(1, static_cast<const char*>(samples) + isz * h->pos);
+            Gnss_Synchro item = Gnss_Synchro();
+            gr_vector_void_star outv(1, &item);
+            h->blk->gb_consumed = 0;
+            h->blk->gb_events.clear();
+            const int produced = h->blk->general_work(1, ninput, in, outv);
+            h->pos += h->blk->gb_consumed;
+            double* r = rows + 13 * k;
+            std::fill(r, r + 13, 0.0);
+            if (produced == 1)
+                {
+                    r[0] = (double)item.Tracking_sample_counter;
+                    r[1] = item.Prompt_I;
+                    r[2] = item.Prompt_Q;
+                    r[3] = item.Carrier_Doppler_hz;
+                    r[4] = item.Code_phase_samples;
+                    r[5] = item.Carrier_phase_rads;
+                    r[6] = item.CN0_dB_hz;
+                    r[10] = item.Flag_valid_symbol_output ? 1.0 : 0.0;
+                    r[12] = item.correlation_length_ms;
+                }
+            if (h->glo)
+                for (int t = 0; t < 3; t++) r[7 + t] = std::abs(h->glo->d_correlator_outs[t]);
+            if (h->cc)
+                for (int t = 0; t < 3; t++) r[7 + t] = std::abs(h->cc->d_correlator_outs[t]);
+            if (h->sc)
+                for (int t = 0; t < 3; t++) r[7 + t] = std::abs(std::complex<float>(h->sc->d_correlator_outs_16sc[t].real(), h->sc->d_correlator_outs_16sc[t].imag()));
+            for (long ev : h->blk->gb_events)
+                if (ev == 3) r[10] += 2.0;
+            r[11] = (double)h->blk->gb_consumed;
+        }
+    return k;
+}
+
 }  // extern "C"

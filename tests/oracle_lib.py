@@ -702,3 +702,43 @@ class RefAcqVariantBlock:
         if self.h:
             self.L.gbref_acqv_destroy(self.h)
             self.h = None
+
+
+TRK2_FIELDS = ("tracking_sample_counter", "prompt_i", "prompt_q", "carrier_doppler_hz", "code_phase_samples", "carrier_phase_rads", "cn0_db_hz",
+               "abs_e", "abs_p", "abs_l", "flags", "consumed", "correlation_length_ms")
+REF_TRK_GLONASS, REF_TRK_CAID_CC, REF_TRK_CAID_SC = 0, 1, 2
+
+
+class RefSiblingTracker:
+    """glonass_l1_ca_dll_pll_tracking_cc / gps_l1_ca_dll_pll_c_aid_tracking_cc / _sc compiled from /root/reference."""
+
+    def __init__(self, kind, fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz=20.0, dll_bw_narrow_hz=2.0, early_late_space_chips=0.5,
+                 extend_correlation_ms=1):
+        self.L = ref_blocks2()
+        self.L.gbref_trk2_create.argtypes = [C.c_int, f64p]
+        self.L.gbref_trk2_create.restype = C.c_void_p
+        self.L.gbref_trk2_destroy.argtypes = [C.c_void_p]
+        self.L.gbref_trk2_start.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
+        self.L.gbref_trk2_preamble.argtypes = [C.c_void_p, C.c_double]
+        self.L.gbref_trk2_run.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, f64p]
+        self.kind = kind
+        conf = np.array([fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms], np.float64)
+        self.h = self.L.gbref_trk2_create(kind, conf)
+
+    def start(self, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index=0):
+        self.L.gbref_trk2_start(self.h, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index)
+
+    def preamble(self, timestamp_s):
+        self.L.gbref_trk2_preamble(self.h, timestamp_s)
+
+    def run(self, samples, n_calls):
+        x = np.ascontiguousarray(samples, np.int16 if self.kind == REF_TRK_CAID_SC else np.complex64)
+        n_items = x.size // 2 if self.kind == REF_TRK_CAID_SC else x.size
+        rows = np.zeros((n_calls, 13), np.float64)
+        n = self.L.gbref_trk2_run(self.h, x.ctypes.data_as(C.c_void_p), n_items, n_calls, rows.reshape(-1))
+        return rows[:n]
+
+    def close(self):
+        if self.h:
+            self.L.gbref_trk2_destroy(self.h)
+            self.h = None

@@ -125,3 +125,69 @@ def test_e5a_noncoherent_iq_caf_block_equals_restatement(what):
         assert ev == 1 and cores[0].acq_delay_samples % E5A_SPM == delay
     b.close()
     o.close()
+
+
+# ------------------------------------------------------------------------------------------------ sibling trackers
+def _same_rows(mirror, ref, len_field, F, what):
+    import host_lib as hl  # noqa: F401
+
+    n = min(len(mirror), len(ref))
+    assert n > 0
+    for i in range(n):
+        a, r = mirror[i], ref[i]
+        assert a[F[len_field]] == r[11], (what, i, "block length", a[F[len_field]], r[11])
+        assert (int(a[F["flags"]]) & 1) == (int(r[10]) & 1), (what, i, "valid flag")
+        if int(r[10]) & 1:
+            for j in range(10):
+                assert a[j] == r[j], (what, i, j, a[j], r[j])
+    return n
+
+
+def test_glonass_l1_tracker_mirror_equals_the_block():
+    """GlonassL1CaDllPllTracking (host/gb200_glonass_tracking.hpp, on the oracle's complex-code correlator) against
+    glonass_l1_ca_dll_pll_tracking_cc itself: FDMA channel +1 (PRN 1), 680 general_work calls, every field of every valid epoch and
+    every block length equal."""
+    import host_lib as hl
+    import test_host_cpu as thc
+    from test_ref_blocks_cpu import quiet
+
+    fs, doppler, delay, k = 4e6, 1234.0, 777.3, 1
+    x, code = thc.glonass_scene(700, doppler, delay, k)
+    ep = hl.run_oracle_glonass(x, 0, code, k, acq_delay=delay + 0.6, acq_doppler=doppler - 40.0, acq_stamp=0, n_steps=680, fs_in=fs, vector_length=4000,
+                               pll_bw_hz=40.0, dll_bw_hz=2.0, early_late_space_chips=0.5)
+    with quiet():
+        b = ol.RefSiblingTracker(ol.REF_TRK_GLONASS, fs, 4000, 40.0, 2.0, early_late_space_chips=0.5)
+        b.start(1, delay + 0.6, doppler - 40.0, 0, 0)
+        rr = b.run(x, 680)
+        b.close()
+    F = {n: i for i, n in enumerate(hl.GLO_EPOCH_FIELDS)}
+    assert _same_rows(ep, rr, "prn_length_samples", F, "glonass") == 680 and (rr[:, 10].astype(int) & 1).sum() > 600
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_c_aid_tracker_mirrors_equal_the_blocks(variant):
+    """GpsL1CaDllPllCAidTracking against gps_l1_ca_dll_pll_c_aid_tracking_cc (variant 0) / _sc (variant 1, int16 correlator and
+    int16 extended-integration history): pull-in, 1 ms tracking, the preamble message after 500 blocks, then 5 ms extended
+    integration -- 850 calls, all equal.  (This comparison found that only the _cc block retunes the DLL filter's integration
+    time when it extends the correlation; the mirror had followed the _sc block for both.)"""
+    import host_lib as hl
+    import test_host_cpu as thc
+    from test_ref_blocks_cpu import quiet
+
+    fs, doppler, delay = 4e6, -2222.0, 1500.4
+    x, code = thc.caid_scene(900, doppler, delay)
+    samples = np.ascontiguousarray(np.rint(np.stack([x.real, x.imag], -1) * 4.0).astype(np.int16).reshape(-1)) if variant == 1 else x
+    conf = dict(fs_in=fs, vector_length=4000, pll_bw_hz=35.0, dll_bw_hz=2.0, pll_bw_narrow_hz=15.0, dll_bw_narrow_hz=1.5, early_late_space_chips=0.5,
+                extend_correlation_ms=5)
+    ep = hl.run_oracle_caid(samples, variant, 0, code, acq_delay=delay + 0.7, acq_doppler=doppler + 60.0, acq_stamp=0, n_steps=850, preamble=(500, 0.0), **conf)
+    with quiet():
+        b = ol.RefSiblingTracker(ol.REF_TRK_CAID_CC + variant, fs, 4000, 35.0, 2.0, 15.0, 1.5, 0.5, 5)
+        b.start(9, delay + 0.7, doppler + 60.0, 0, 0)
+        rr = np.concatenate([b.run(samples, 500), (b.preamble(0.0), b.run(samples, 350))[1]])
+        b.close()
+    F = {n: i for i, n in enumerate(hl.CAID_EPOCH_FIELDS)}
+    assert _same_rows(ep, rr, "correlation_length_samples", F, "c_aid %d" % variant) == 850
+    valid = (rr[:, 10].astype(int) & 1) == 1
+    assert valid[:500].sum() > 480 and 60 < valid[500:].sum() < 80 and np.all(rr[500:][valid[500:], 12] == 5)
+    for i in np.nonzero(valid)[0]:
+        assert ep[i, F["correlation_length_ms"]] == rr[i, 12]
