@@ -64,7 +64,14 @@ public:
         return gb200_trk_correlate(h_, stream_, first_sample, rem_carrier_phase_in_rad, phase_step_rad, phase_rate_step_rad, rem_code_phase_chips,
                    code_phase_step_chips, code_phase_rate_step_chips, signal_length_samples, reinterpret_cast<float*>(corr_out)) == GB200_OK;
     }
-    bool free()  // (:155-170)
+    // = the six-argument overload (:155-170): code resampler as configured, plain rotator (no carrier rate term)
+    bool correlate(uint64_t first_sample, float rem_carrier_phase_in_rad, float phase_step_rad, float rem_code_phase_chips, float code_phase_step_chips,
+        float code_phase_rate_step_chips, int signal_length_samples, std::complex<float>* corr_out)
+    {
+        return correlate(first_sample, rem_carrier_phase_in_rad, phase_step_rad, 0.0f, rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips,
+            signal_length_samples, corr_out);
+    }
+    bool free()  // (:173-190)
     {
         if (h_) gb200_trk_destroy(h_);
         h_ = nullptr;

@@ -7,6 +7,7 @@
 #include "gb200_acquisition_variants.hpp"
 #include "gb200_c_aid_tracking.hpp"
 #include "gb200_glonass_tracking.hpp"
+#include "gb200_kf_tracking.hpp"
 #include "gb200_host_flat.h"
 #include "gb200_multicorrelator.hpp"
 #include "gb200_tracking.hpp"
@@ -475,6 +476,48 @@ void gbh_caid_close(void* hv)
     if (!h) return;
     delete h->loop_cc;
     delete h->loop_sc;
+    delete h;
+}
+
+// ---- Kalman GPS L1 C/A tracker (gb200_kf_tracking.hpp) on the real-code B200 correlator, any item type of the stream ----
+struct gbh_kf
+{
+    B200_Multicorrelator_Real_Codes corr;
+    GpsL1CaKfTracking<B200_Multicorrelator_Real_Codes>* loop = nullptr;
+};
+void* gbh_kf_open(gb200_service* service, int stream_id, int item_type, const double* conf)
+{
+    KfTrkConf c;
+    gbh_kf_conf(conf, &c);
+    auto* h = new gbh_kf();
+    h->corr.set_high_dynamics_resampler(true);  // the reference correlator's constructor default, which the block keeps
+    if (!h->corr.init(service, stream_id, item_type, 2 * (int)c.vector_length, 3))
+        {
+            delete h;
+            return nullptr;
+        }
+    h->loop = new GpsL1CaKfTracking<B200_Multicorrelator_Real_Codes>(c, &h->corr);
+    return h;
+}
+int gbh_kf_start(void* hv, const float* code, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint32_t acq_doppler_step, uint64_t now)
+{
+    auto* h = static_cast<gbh_kf*>(hv);
+    h->loop->set_sample_counter(now);
+    return h->loop->start_tracking(code, acq_delay_samples, acq_doppler_hz, acq_samplestamp, acq_doppler_step) ? 0 : -1;
+}
+int gbh_kf_step(void* hv, double* epoch)
+{
+    auto* h = static_cast<gbh_kf*>(hv);
+    KfEpoch e;
+    const bool ok = h->loop->step(&e);
+    gbh_kf_fill(e, epoch);
+    return ok ? 0 : -2;
+}
+void gbh_kf_close(void* hv)
+{
+    auto* h = static_cast<gbh_kf*>(hv);
+    if (!h) return;
+    delete h->loop;
     delete h;
 }
 }

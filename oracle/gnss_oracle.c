@@ -190,7 +190,14 @@ void go_multicorrelator_real(const float* in_iq, int n, const float* code, int c
     float* codes = (float*)malloc(sizeof(float) * (size_t)n_taps * (size_t)n);
     float phase[2] = {cosf(rem_carr_phase_rad), -sinf(rem_carr_phase_rad)}; /* :140-141 */
     /* std::exp(lv_32fc_t(0.0, -step)) == std::polar(expf(0), -step) == (cosf(-step), sinf(-step)) */
-    if (high_dyn)
+    if (high_dyn == 2)
+        {
+            /* the six-argument overload (:155-170) with d_use_high_dynamics_resampler left at its constructor default (true, :49):
+             * high-dynamics code resampler, PLAIN rotator -- what gps_l1_ca_kf_tracking_cc runs */
+            go_resampler_real_hd(codes, code, rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips, shifts, code_len, n_taps, n);
+            go_rotator_dot_prod_real(corr_out_iq, in_iq, cosf(-phase_step_rad), sinf(-phase_step_rad), phase, codes, n_taps, n);
+        }
+    else if (high_dyn)
         {
             go_resampler_real_hd(codes, code, rem_code_phase_chips, code_phase_step_chips, code_phase_rate_step_chips, shifts, code_len, n_taps, n);
             go_rotator_dot_prod_real_hd(corr_out_iq, in_iq, cosf(-phase_step_rad), sinf(-phase_step_rad),

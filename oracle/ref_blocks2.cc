@@ -39,6 +39,7 @@
 #include "glonass_l1_ca_dll_pll_tracking_cc.h"
 #include "gps_l1_ca_dll_pll_c_aid_tracking_cc.h"
 #include "gps_l1_ca_dll_pll_c_aid_tracking_sc.h"
+#include "gps_l1_ca_kf_tracking_cc.h"
 #include "pcps_acquisition_fine_doppler_cc.h"
 #include "pcps_quicksync_acquisition_cc.h"
 #include "pcps_tong_acquisition_cc.h"
@@ -232,20 +233,22 @@ int gbref_acqv_caf_vector(void* hv, float* dst, int cap)
 
 // ------------------------------------------------------------------------------------------------ sibling trackers
 // kind 0: glonass_l1_ca_dll_pll_tracking_cc (gr_complex), 1: gps_l1_ca_dll_pll_c_aid_tracking_cc (gr_complex),
-// 2: gps_l1_ca_dll_pll_c_aid_tracking_sc (lv_16sc_t)
+// 2: gps_l1_ca_dll_pll_c_aid_tracking_sc (lv_16sc_t), 3: gps_l1_ca_kf_tracking_cc (gr_complex; Armadillo stand-in, see shim/armadillo)
 struct GbRefTrk2
 {
     int kind = 0;
     glonass_l1_ca_dll_pll_tracking_cc_sptr glo;
     gps_l1_ca_dll_pll_c_aid_tracking_cc_sptr cc;
     gps_l1_ca_dll_pll_c_aid_tracking_sc_sptr sc;
+    gps_l1_ca_kf_tracking_cc_sptr kf;
     gr::block* blk = nullptr;
     Gnss_Synchro sync;
     long long pos = 0;
     uint32_t vector_length = 0;
 };
 
-// conf: fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms
+// conf: fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms,
+//       (kind 3 only) order, bce_run, bce_ptrans, bce_strans, bce_nu, bce_kappa
 void* gbref_trk2_create(int kind, const double* c)
 {
     GbRefTrk2* h = new GbRefTrk2();
@@ -260,6 +263,12 @@ void* gbref_trk2_create(int kind, const double* c)
         {
             h->cc = gps_l1_ca_dll_pll_c_aid_make_tracking_cc((int64_t)c[0], (uint32_t)c[1], false, "", (float)c[2], (float)c[3], (float)c[4], (float)c[5], (int32_t)c[7], (float)c[6]);
             h->blk = h->cc.get();
+        }
+    else if (kind == 3)
+        {
+            h->kf = gps_l1_ca_kf_make_tracking_cc((uint32_t)c[8], 0, (int64_t)c[0], (uint32_t)c[1], false, "", (float)c[3], (float)c[6], c[9] != 0.0, (uint32_t)c[10],
+                (uint32_t)c[11], (int32_t)c[12], (int32_t)c[13]);
+            h->blk = h->kf.get();
         }
     else
         {
@@ -289,8 +298,12 @@ void gbref_trk2_start(void* hv, uint32_t prn, double acq_delay_samples, double a
     if (h->glo) { GB_START(h->glo) }
     if (h->cc) { GB_START(h->cc) }
     if (h->sc) { GB_START(h->sc) }
+    if (h->kf) { GB_START(h->kf) }
 #undef GB_START
 }
+
+// Acq_doppler_step of the acquisition result (the Kalman tracker sizes its initial Doppler variance from it); before gbref_trk2_start
+void gbref_trk2_set_doppler_step(void* hv, uint32_t step) { ((GbRefTrk2*)hv)->sync.Acq_doppler_step = step; }
 
 // the "preamble_timestamp_s" message of the telemetry decoder (c_aid trackers: starts the extended integration)
 void gbref_trk2_preamble(void* hv, double preamble_timestamp_s)
@@ -335,6 +348,8 @@ int gbref_trk2_run(void* hv, const void* samples, long long n_items, int n_calls
                 for (int t = 0; t < 3; t++) r[7 + t] = std::abs(h->glo->d_correlator_outs[t]);
             if (h->cc)
                 for (int t = 0; t < 3; t++) r[7 + t] = std::abs(h->cc->d_correlator_outs[t]);
+            if (h->kf)
+                for (int t = 0; t < 3; t++) r[7 + t] = std::abs(h->kf->d_correlator_outs[t]);
             if (h->sc)
                 for (int t = 0; t < 3; t++) r[7 + t] = std::abs(std::complex<float>(h->sc->d_correlator_outs_16sc[t].real(), h->sc->d_correlator_outs_16sc[t].imag()));
             for (long ev : h->blk->gb_events)

@@ -120,6 +120,11 @@ def host():
         L.gbh_glo_start.argtypes = [C.c_void_p, f32p, C.c_int, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
         L.gbh_glo_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.gbh_glo_close.argtypes = [C.c_void_p]
+        L.gbh_kf_open.restype = C.c_void_p
+        L.gbh_kf_open.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        L.gbh_kf_start.argtypes = [C.c_void_p, f32p, C.c_double, C.c_double, C.c_uint64, C.c_uint32, C.c_uint64]
+        L.gbh_kf_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.gbh_kf_close.argtypes = [C.c_void_p]
         L.gbh_acqv_attempt.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int,
                                        C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.gbh_e5a_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, f32p, C.c_size_t, C.c_uint64, C.c_int,
@@ -219,6 +224,11 @@ def oracle_loop():
         L.hol_glo_start.argtypes = [C.c_void_p, f32p, C.c_int, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
         L.hol_glo_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.hol_glo_close.argtypes = [C.c_void_p]
+        L.hol_kf_open.restype = C.c_void_p
+        L.hol_kf_open.argtypes = [f32p, C.c_uint64, C.c_uint64, C.POINTER(C.c_double)]
+        L.hol_kf_start.argtypes = [C.c_void_p, f32p, C.c_double, C.c_double, C.c_uint64, C.c_uint32, C.c_uint64]
+        L.hol_kf_step.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.hol_kf_close.argtypes = [C.c_void_p]
         L.hol_caid_open.restype = C.c_void_p
         L.hol_caid_open.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
         L.hol_caid_start.argtypes = [C.c_void_p, f32p, C.c_double, C.c_double, C.c_uint64, C.c_uint64]
@@ -320,6 +330,48 @@ def run_b200_glonass(service, stream_id, item_type, first_index, code_c64, freq_
         return _glo_run(L.gbh_glo_step, h, n_steps)
     finally:
         L.gbh_glo_close(h)
+
+
+KF_EPOCH_FIELDS = GLO_EPOCH_FIELDS + ("carrier_dopplerrate_hz2", "carr_phase_sigma2", "rem_carr_phase_rad")
+
+
+def _kf_conf(fs_in, vector_length, dll_bw_hz, order=2, early_late_space_chips=0.5, bce_run=False, bce_ptrans=0, bce_strans=0, bce_nu=0, bce_kappa=0,
+             cn0_samples=20, cn0_min=25, max_lock_fail=50, carrier_lock_th=0.85):
+    return (C.c_double * 14)(order, fs_in, vector_length, dll_bw_hz, early_late_space_chips, 1.0 if bce_run else 0.0, bce_ptrans, bce_strans, bce_nu, bce_kappa,
+                             cn0_samples, cn0_min, max_lock_fail, carrier_lock_th)
+
+
+def _kf_run(step, h, n_steps):
+    out = np.zeros((n_steps, len(KF_EPOCH_FIELDS)))
+    e = (C.c_double * len(KF_EPOCH_FIELDS))()
+    for k in range(n_steps):
+        assert step(h, e) == 0, "correlator refused the request at step %d" % k
+        out[k] = e[:]
+    return out
+
+
+def run_oracle_kf(samples_c64, first_index, code_f32, acq_delay, acq_doppler, acq_stamp, acq_doppler_step, n_steps, **conf):
+    """Kalman GPS L1 C/A loop (gb200_kf_tracking.hpp) on the oracle's real-code correlator; rows of KF_EPOCH_FIELDS."""
+    L = oracle_loop()
+    x = np.ascontiguousarray(samples_c64, np.complex64).view(np.float32)
+    h = L.hol_kf_open(x, len(x) // 2, first_index, _kf_conf(**conf))
+    assert L.hol_kf_start(h, np.ascontiguousarray(code_f32, np.float32), acq_delay, acq_doppler, acq_stamp, acq_doppler_step, first_index) == 0
+    try:
+        return _kf_run(L.hol_kf_step, h, n_steps)
+    finally:
+        L.hol_kf_close(h)
+
+
+def run_b200_kf(service, stream_id, item_type, first_index, code_f32, acq_delay, acq_doppler, acq_stamp, acq_doppler_step, n_steps, **conf):
+    """the same loop on B200_Multicorrelator_Real_Codes through the C ABI"""
+    L = host()
+    h = L.gbh_kf_open(service.h, stream_id, item_type, _kf_conf(**conf))
+    assert h
+    assert L.gbh_kf_start(h, np.ascontiguousarray(code_f32, np.float32), acq_delay, acq_doppler, acq_stamp, acq_doppler_step, first_index) == 0
+    try:
+        return _kf_run(L.gbh_kf_step, h, n_steps)
+    finally:
+        L.gbh_kf_close(h)
 
 
 CAID_EPOCH_FIELDS = ("tracking_sample_counter", "prompt_i", "prompt_q", "carrier_doppler_hz", "code_phase_samples", "carrier_phase_rads", "cn0_db_hz",

@@ -10,6 +10,7 @@
 #include "../../gnss-sdr-1_b200/host/gb200_host_flat.h"
 #include "../../gnss-sdr-1_b200/host/gb200_c_aid_tracking.hpp"
 #include "../../gnss-sdr-1_b200/host/gb200_glonass_tracking.hpp"
+#include "../../gnss-sdr-1_b200/host/gb200_kf_tracking.hpp"
 #include "../../gnss-sdr-1_b200/host/gb200_tracking.hpp"
 #include "../../oracle/gnss_oracle.h"
 
@@ -50,6 +51,15 @@ public:
                 go_multicorrelator_real(x, n, data_.data(), (int)data_.size(), &s0, 1, rem_carr, phase_step, phase_rate, rem_code, code_step, code_rate, high_dyn_ ? 1 : 0,
                     reinterpret_cast<float*>(out + shifts_.size()));
             }
+        return true;
+    }
+
+    // the six-argument overload (cpu_multicorrelator_real_codes.cc:155-170): code resampler as configured, plain rotator
+    bool correlate(uint64_t first, float rem_carr, float phase_step, float rem_code, float code_step, float code_rate, int n, std::complex<float>* out)
+    {
+        if (first < first_ || first + (uint64_t)n > first_ + n_) return false;
+        go_multicorrelator_real(x_ + 2 * (first - first_), n, code_.data(), (int)code_.size(), shifts_.data(), (int)shifts_.size(), rem_carr, phase_step, 0.0f, rem_code,
+            code_step, code_rate, high_dyn_ ? 2 : 0, reinterpret_cast<float*>(out));
         return true;
     }
 
@@ -250,4 +260,39 @@ int hol_caid_step(void* h, double* epoch)
     return ok ? 0 : -2;
 }
 void hol_caid_close(void* h) { delete static_cast<CAidChannel*>(h); }
+}
+
+// ---- the Kalman GPS L1 C/A loop (gb200_kf_tracking.hpp) on the oracle's real-code correlator ----
+namespace
+{
+struct KfChannel
+{
+    std::unique_ptr<OracleCorrelator> corr;
+    std::unique_ptr<gb200::GpsL1CaKfTracking<OracleCorrelator>> loop;
+};
+}  // namespace
+extern "C" {
+void* hol_kf_open(const float* samples_iq, uint64_t n_samples, uint64_t first_index, const double* conf)
+{
+    gb200::KfTrkConf c;
+    gbh_kf_conf(conf, &c);
+    auto* ch = new KfChannel();
+    ch->corr.reset(new OracleCorrelator(samples_iq, n_samples, first_index, true));  // the constructor default of the reference class
+    ch->loop.reset(new gb200::GpsL1CaKfTracking<OracleCorrelator>(c, ch->corr.get()));
+    return ch;
+}
+int hol_kf_start(void* h, const float* code, double acq_delay_samples, double acq_doppler_hz, uint64_t acq_samplestamp, uint32_t acq_doppler_step, uint64_t now)
+{
+    auto* ch = static_cast<KfChannel*>(h);
+    ch->loop->set_sample_counter(now);
+    return ch->loop->start_tracking(code, acq_delay_samples, acq_doppler_hz, acq_samplestamp, acq_doppler_step) ? 0 : -1;
+}
+int hol_kf_step(void* h, double* epoch)
+{
+    gb200::KfEpoch e;
+    const bool ok = static_cast<KfChannel*>(h)->loop->step(&e);
+    gbh_kf_fill(e, epoch);
+    return ok ? 0 : -2;
+}
+void hol_kf_close(void* h) { delete static_cast<KfChannel*>(h); }
 }

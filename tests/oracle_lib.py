@@ -706,14 +706,14 @@ class RefAcqVariantBlock:
 
 TRK2_FIELDS = ("tracking_sample_counter", "prompt_i", "prompt_q", "carrier_doppler_hz", "code_phase_samples", "carrier_phase_rads", "cn0_db_hz",
                "abs_e", "abs_p", "abs_l", "flags", "consumed", "correlation_length_ms")
-REF_TRK_GLONASS, REF_TRK_CAID_CC, REF_TRK_CAID_SC = 0, 1, 2
+REF_TRK_GLONASS, REF_TRK_CAID_CC, REF_TRK_CAID_SC, REF_TRK_KF = 0, 1, 2, 3
 
 
 class RefSiblingTracker:
     """glonass_l1_ca_dll_pll_tracking_cc / gps_l1_ca_dll_pll_c_aid_tracking_cc / _sc compiled from /root/reference."""
 
     def __init__(self, kind, fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz=20.0, dll_bw_narrow_hz=2.0, early_late_space_chips=0.5,
-                 extend_correlation_ms=1):
+                 extend_correlation_ms=1, order=2, bce_run=False, bce_ptrans=0, bce_strans=0, bce_nu=0, bce_kappa=0):
         self.L = ref_blocks2()
         self.L.gbref_trk2_create.argtypes = [C.c_int, f64p]
         self.L.gbref_trk2_create.restype = C.c_void_p
@@ -722,10 +722,13 @@ class RefSiblingTracker:
         self.L.gbref_trk2_preamble.argtypes = [C.c_void_p, C.c_double]
         self.L.gbref_trk2_run.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, f64p]
         self.kind = kind
-        conf = np.array([fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms], np.float64)
+        self.L.gbref_trk2_set_doppler_step.argtypes = [C.c_void_p, C.c_uint32]
+        conf = np.array([fs_in, vector_length, pll_bw_hz, dll_bw_hz, pll_bw_narrow_hz, dll_bw_narrow_hz, early_late_space_chips, extend_correlation_ms,
+                         order, 1.0 if bce_run else 0.0, bce_ptrans, bce_strans, bce_nu, bce_kappa], np.float64)
         self.h = self.L.gbref_trk2_create(kind, conf)
 
-    def start(self, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index=0):
+    def start(self, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index=0, acq_doppler_step=0):
+        self.L.gbref_trk2_set_doppler_step(self.h, acq_doppler_step)
         self.L.gbref_trk2_start(self.h, prn, acq_delay_samples, acq_doppler_hz, acq_samplestamp, first_item_index)
 
     def preamble(self, timestamp_s):

@@ -435,3 +435,40 @@ def test_acquisition_against_the_reference_block(service):
                 assert abs(r.test_statistic - st.test_statistics) <= 1e-4 * st.test_statistics and ev == 1
             b.close()
             a.close()
+
+
+@pytest.mark.parametrize("order", [2, 3])
+def test_kf_loop_on_b200_matches_oracle_loop_and_the_reference_block(service, order):
+    """gps_l1_ca_kf_tracking_cc: the Kalman carrier loop mirror (host/gb200_kf_tracking.hpp) closed on the B200
+    real-code correlator -- configured like the reference object the block owns: high-dynamics code resampler, plain rotator --
+    vs the same loop on the oracle correlator AND vs the reference block itself (oracle/_ref).  Block boundaries and flags equal;
+    Doppler within 0.5 Hz, prompts within 2e-3 of the peak, code phase within 0.01 samples over 600 epochs."""
+    import gnss_b200 as gb
+    import oracle_lib as ol
+    import test_host_cpu as thc
+    from test_ref_blocks_cpu import quiet
+
+    fs, doppler, delay = 4e6, -2650.0, 912.3
+    x, code = thc.caid_scene(640, doppler, delay, cn0=47.0, prn=23, seed=20260033)
+    service.push(2, x, gb.ITEM_32FC, 0)
+    kw = dict(fs_in=fs, vector_length=4000, dll_bw_hz=2.0, early_late_space_chips=0.5, order=order)
+    args = dict(code_f32=code.real, acq_delay=delay + 0.4, acq_doppler=doppler + 45.0, acq_stamp=0, acq_doppler_step=250, n_steps=600)
+    ref = hl.run_oracle_kf(x, 0, **args, **kw)
+    got = hl.run_b200_kf(service, 2, gb.ITEM_32FC, 0, **args, **kw)
+    with quiet():
+        b = ol.RefSiblingTracker(ol.REF_TRK_KF, fs, 4000, 0.0, 2.0, early_late_space_chips=0.5, order=order)
+        b.start(23, delay + 0.4, doppler + 45.0, 0, 0, acq_doppler_step=250)
+        blk = b.run(x, 600)
+        b.close()
+    F = {n: i for i, n in enumerate(hl.KF_EPOCH_FIELDS)}
+    assert len(blk) == 600 and np.array_equal(ref[1:, :10], blk[1:, :10])  # mirror on the oracle correlator == block (also a CPU test)
+    assert np.array_equal(got[:, F["prn_length_samples"]], blk[:, 11])
+    assert np.array_equal(got[:, F["tracking_sample_counter"]], ref[:, F["tracking_sample_counter"]])
+    assert np.array_equal(got[:, F["flags"]], ref[:, F["flags"]]) and np.all(got[-300:, F["flags"]] == 1)
+    rel = np.abs(got[1:, F["abs_p"]] - blk[1:, 8]) / blk[1:, 8].max()
+    dd = np.abs(got[:, F["carrier_doppler_hz"]] - blk[:, 3])
+    print("KF order %d closed loop vs the block: doppler diff max %.3g Hz, prompt magnitude diff max %.3g of peak, final doppler %.1f Hz" % (
+        order, dd[1:].max(), rel.max(), got[-1, F["carrier_doppler_hz"]]))
+    assert dd[1:].max() < 0.5 and rel.max() < 2e-3
+    assert abs(got[-200:, F["carrier_doppler_hz"]].mean() - doppler) < 3.0
+    assert np.abs(got[1:, F["code_phase_samples"]] - blk[1:, 4]).max() < 0.01

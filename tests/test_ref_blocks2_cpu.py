@@ -191,3 +191,34 @@ def test_c_aid_tracker_mirrors_equal_the_blocks(variant):
     assert valid[:500].sum() > 480 and 60 < valid[500:].sum() < 80 and np.all(rr[500:][valid[500:], 12] == 5)
     for i in np.nonzero(valid)[0]:
         assert ep[i, F["correlation_length_ms"]] == rr[i, 12]
+
+
+@pytest.mark.parametrize("order,bce", [(2, False), (3, False), (2, True)])
+def test_kf_tracker_mirror_equals_the_block(order, bce):
+    """GpsL1CaKfTracking (host/gb200_kf_tracking.hpp, on the oracle's real-code correlator) against gps_l1_ca_kf_tracking_cc itself
+    (compiled with the Armadillo stand-in of oracle/shim/armadillo, so the pin is on the block's own statement order, not on
+    Armadillo's BLAS): 2-state and 3-state filters, and the 2-state filter with the Bayesian covariance estimator switched on after
+    100 + 50 epochs -- pull-in epoch, 700 general_work calls, every field of every valid epoch and every block length equal."""
+    import host_lib as hl
+    import test_host_cpu as thc
+    from test_ref_blocks_cpu import quiet
+
+    fs, doppler, delay = 4e6, 1777.0, 2100.6
+    x, code = thc.caid_scene(720, doppler, delay, cn0=47.0, prn=17, seed=20260031)
+    kw = dict(order=order, bce_run=bce, bce_ptrans=100, bce_strans=50, bce_nu=10, bce_kappa=10)
+    ep = hl.run_oracle_kf(x, 0, code.real, acq_delay=delay + 0.5, acq_doppler=doppler - 30.0, acq_stamp=0, acq_doppler_step=250, n_steps=700, fs_in=fs,
+                          vector_length=4000, dll_bw_hz=2.0, early_late_space_chips=0.5, **kw)
+    with quiet():
+        b = ol.RefSiblingTracker(ol.REF_TRK_KF, fs, 4000, 0.0, 2.0, early_late_space_chips=0.5, **kw)
+        b.start(17, delay + 0.5, doppler - 30.0, 0, 0, acq_doppler_step=250)
+        rr = b.run(x, 700)
+        b.close()
+    F = {n: i for i, n in enumerate(hl.KF_EPOCH_FIELDS)}
+    assert _same_rows(ep, rr, "prn_length_samples", F, "kf order %d bce %d" % (order, bce)) == 700
+    lock = ep[400:]
+    assert np.all(lock[:, F["flags"]] == 1) and abs(lock[:, F["carrier_doppler_hz"]].mean() - doppler) < 5.0
+    assert 43.0 < lock[:, F["cn0_db_hz"]].mean() < 51.0
+    if bce:  # the estimator replaced the CN0-derived measurement variance
+        assert not np.array_equal(ep[300:, F["carr_phase_sigma2"]], hl.run_oracle_kf(
+            x, 0, code.real, acq_delay=delay + 0.5, acq_doppler=doppler - 30.0, acq_stamp=0, acq_doppler_step=250, n_steps=700, fs_in=fs, vector_length=4000,
+            dll_bw_hz=2.0, early_late_space_chips=0.5, order=order)[300:, F["carr_phase_sigma2"]])
