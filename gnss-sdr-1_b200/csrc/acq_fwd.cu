@@ -37,27 +37,33 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
             const int n2 = c0 + b;
             const int n = N2 * n1 + n2;
             float2 x = make_float2(0.f, 0.f);
-            if (n2 < N2 && n < p.consumed)
+            // fold == 1: one wiped sample.  QuickSync (fold > 1): the wiped samples n, n + N, n + 2N, ... added in that order onto a
+            // zeroed buffer in float32, as the block's std::transform(std::plus) passes do
+            for (int f = 0; f < p.fold; f++)
                 {
-                    x = gb_load_item<ITEM>(p.samples, (size_t)n);
+                    const int m = n + f * pl.N;
+                    if (!(n2 < N2 && m < p.consumed)) break;
+                    float2 v = gb_load_item<ITEM>(p.samples, (size_t)m);
                     if (wipeoff)
                         {
-                            // last segment with n_start <= n (binary search; a bin has ~10 segments)
+                            // last segment with n_start <= m (binary search; a bin has ~10 segments)
                             int lo = 0, hi = nseg - 1;
                             while (lo < hi)
                                 {
                                     const int mid = (lo + hi + 1) >> 1;
-                                    if (__ldg(&segs[mid].n_start) <= n)
+                                    if (__ldg(&segs[mid].n_start) <= m)
                                         lo = mid;
                                     else
                                         hi = mid - 1;
                                 }
                             const GbWipeSeg sg = segs[lo];
-                            const float ph = (float)fma((double)(n - sg.n_start), (double)sg.inc_eff, (double)sg.ph_start);  // exact
+                            const float ph = (float)fma((double)(m - sg.n_start), (double)sg.inc_eff, (double)sg.ph_start);  // exact
                             float s, c;
                             sincosf(ph, &s, &c);
-                            x = cmul(x, make_float2(c, s));
+                            v = cmul(v, make_float2(c, s));
                         }
+                    x.x = __fadd_rn(x.x, v.x);
+                    x.y = __fadd_rn(x.y, v.y);
                 }
             bufA[n1 * PITCH + b] = x;
         }

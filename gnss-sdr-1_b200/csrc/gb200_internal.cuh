@@ -168,6 +168,7 @@ struct GbAcqFwdParams
     const int* seg_offsets;       // [bins + 1] offsets into segs
     float2* colbuf;        // [bins][N1][N2] scratch after the column stage
     float2* spectra;       // [bins][N1][N2] forward spectra, [k1][k2] layout
+    int fold = 1;          // QuickSync: the wiped block is folded `fold` times onto the N-point FFT input (pcps_quicksync_acquisition_cc.cc:391-398)
 };
 
 struct GbAcqInvParams

@@ -1052,6 +1052,7 @@ struct gb200_acq
 
     // sibling blocks served through the same Doppler loop
     std::vector<float> custom_steps;  // gb200_acq_set_doppler_grid: phase step per bin replaces the doppler_max/doppler_step rule
+    uint32_t fold = 1;                // gb200_acq_create_folded: QuickSync, consumed = fold * fft_size
     int scaled_accum = 0;             // gb200_acq_set_scaled_accumulation: 1 = Tong detector, grid += mag / (N^4 input_power) every dwell; 2 = plain grid += mag
 
     bool need_grid() const { return keep_grid || !use_cfar || c.max_dwells > 1 || scaled_accum; }
@@ -1166,9 +1167,11 @@ static int acq_alloc_grid(gb200_acq* a)
     return GB200_OK;
 }
 
-extern "C" int gb200_acq_create(gb200_service* s, const gb200_acq_cfg* cfg, gb200_acq** out)
+extern "C" int gb200_acq_create(gb200_service* s, const gb200_acq_cfg* cfg, gb200_acq** out) { return gb200_acq_create_folded(s, cfg, 1, out); }
+
+extern "C" int gb200_acq_create_folded(gb200_service* s, const gb200_acq_cfg* cfg, uint32_t fold, gb200_acq** out)
 {
-    if (!s || !cfg || !out) return GB200_E_INVALID;
+    if (!s || !cfg || !out || fold == 0) return GB200_E_INVALID;
     std::lock_guard<std::recursive_mutex> lk(s->mu);
     cudaSetDevice(s->device);
     *out = nullptr;
@@ -1181,6 +1184,19 @@ extern "C" int gb200_acq_create(gb200_service* s, const gb200_acq_cfg* cfg, gb20
     a->s = s;
     a->c = *cfg;
     acq_derive(a);
+    if (fold > 1)
+        {
+            // pcps_quicksync_acquisition_cc.cc:94-95: d_fft_size = samples_per_code / folding_factor, fed by folding_factor^2 segments
+            if (cfg->bit_transition_flag || cfg->make_2_steps || cfg->sampled_ms != cfg->ms_per_code || a->consumed % fold != 0)
+                {
+                    s->set_error("gb200_acq_create_folded: needs sampled_ms == ms_per_code, no bit transition / two steps, and consumed samples divisible by fold");
+                    delete a;
+                    return GB200_E_INVALID;
+                }
+            a->fold = fold;
+            a->fft_size = a->consumed / fold;
+            a->eff = a->fft_size;
+        }
     if (a->consumed == 0 || a->num_bins == 0 || (uint64_t)a->consumed > s->ring_slack)
         {
             s->set_error("gb200_acq_create: consumed samples is 0 or exceeds the ring slack");
@@ -1241,6 +1257,11 @@ extern "C" int gb200_acq_set_local_code(gb200_acq* a, const float* code_iq, size
         {
             offset = N / 2;
             count = N / 2;
+        }
+    else if (a->fold > 1)
+        {
+            offset = 0;
+            count = N;  // the caller's folded code (pcps_quicksync_acquisition_cc.cc:186-196)
         }
     else if (a->c.sampled_ms == a->c.ms_per_code)
         {
@@ -1559,7 +1580,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     for (auto& g : ctx.groups)
                         {
                             gb200_acq* b = list[g.members[0]];
-                            if (g.mode_key == key && b->fft_size == a->fft_size && b->consumed == a->consumed && b->c.item_type == a->c.item_type &&
+                            if (g.mode_key == key && b->fft_size == a->fft_size && b->consumed == a->consumed && b->fold == a->fold && b->c.item_type == a->c.item_type &&
                                 b->c.bit_transition_flag == a->c.bit_transition_flag && g.steps == steps)
                                 {
                                     g.members.push_back(i);
@@ -1584,7 +1605,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     gb200_acq* a0 = list[g.members[0]];
                     if (a0->seg_steps != g.steps || a0->seg_offs.empty())
                         {
-                            acq_all_segments(g.steps, a0->fft_size, a0->segs, a0->seg_offs);
+                            acq_all_segments(g.steps, std::max(a0->fft_size, a0->fold > 1 ? a0->consumed : 0u), a0->segs, a0->seg_offs);
                             a0->seg_steps = g.steps;
                         }
                     g.off_segs = up;
@@ -1659,6 +1680,7 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             fp.seg_offsets = (const int*)((char*)d_up + g.off_segoff);
             fp.colbuf = (float2*)d_col;
             fp.spectra = (float2*)d_spec;
+            fp.fold = (int)a0->fold;
             GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l, s));
             // input power (CFAR or bit transition, pcps_acquisition.cc:703-709)
             bool want_power = false;
@@ -1667,7 +1689,8 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             if (want_power)
                 {
                     const bool image = g.grid && !a0->use_cfar;  // the |x|^2 image the block leaves in d_tmp_buffer
-                    GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, N, d_power, image ? a0->d_tmp : nullptr, s->stream, &l));
+                    // folded handles: the power is the mean over all consumed items (pcps_quicksync_acquisition_cc.cc:363-365)
+                    GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, a0->fold > 1 ? (int)a0->consumed : N, d_power, image ? a0->d_tmp : nullptr, s->stream, &l));
                     if (image)
                         for (size_t k = 1; k < g.members.size(); k++)
                             GB_CUDA(s, cudaMemcpyAsync(list[g.members[k]]->d_tmp, a0->d_tmp, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));

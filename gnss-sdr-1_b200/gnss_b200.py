@@ -77,7 +77,7 @@ EXPORTS = [
     "gb200_service_synchronize", "gb200_service_launch_count", "gb200_service_timer_start", "gb200_service_timer_stop",
     "gb200_service_flush_l2", "gb200_service_coalescing_stats", "gb200_service_acq_coalescing_stats", "gb200_service_kernel_timing", "gb200_service_kernel_stats",
     "gb200_service_measure_fp32", "gb200_service_set_tuning", "gb200_stream_wait", "gb200_stream_push_shared", "gb200_stream_push", "gb200_stream_push_device", "gb200_stream_set_inverted_spectrum", "gb200_stream_set_decimator", "gb200_firdes_low_pass", "gb200_stream_read",
-    "gb200_acq_create", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
+    "gb200_acq_create", "gb200_acq_create_folded", "gb200_acq_destroy", "gb200_acq_fft_size", "gb200_acq_consumed_samples", "gb200_acq_num_doppler_bins",
     "gb200_acq_set_local_code", "gb200_acq_set_doppler", "gb200_acq_set_doppler_grid", "gb200_acq_set_scaled_accumulation", "gb200_acq_set_threshold", "gb200_acq_reset", "gb200_acq_run",
     "gb200_acq_run_batch", "gb200_acq_launch_batch", "gb200_acq_collect_batch", "gb200_acq_discard_batch", "gb200_acq_keep_grid", "gb200_acq_read_grid", "gb200_acq_iq_combine", "gb200_acq_second_peak", "gb200_acq_wiped_spectrum_peak", "gb200_second_peak_noalloc",
     "gb200_trk_create", "gb200_trk_destroy", "gb200_trk_set_local_code_and_taps", "gb200_trk_set_data_code", "gb200_trk_set_taps", "gb200_trk_correlate",
@@ -124,6 +124,7 @@ def lib():
     L.gb200_stream_read.argtypes = [vp, i, u64, C.c_size_t, vp]
     L.gb200_stream_push_device.argtypes = [vp, i, vp, C.c_size_t, i, u64]
     L.gb200_acq_create.argtypes = [vp, C.POINTER(AcqCfg), C.POINTER(vp)]
+    L.gb200_acq_create_folded.argtypes = [vp, C.POINTER(AcqCfg), C.c_uint32, C.POINTER(vp)]
     L.gb200_acq_destroy.argtypes = [vp]
     for fn in (L.gb200_acq_fft_size, L.gb200_acq_consumed_samples, L.gb200_acq_num_doppler_bins):
         fn.argtypes = [vp]
@@ -281,7 +282,7 @@ class Service:
 class Acquisition:
     """gb200_acq: one pcps_acquisition block instance (one channel / PRN)."""
 
-    def __init__(self, service, **kw):
+    def __init__(self, service, fold=1, **kw):
         self.s = service
         d = dict(sampled_ms=1, ms_per_code=1, samples_per_chip=4, max_dwells=1, doppler_max=5000, doppler_step=250,
                  num_doppler_bins_step2=4, doppler_step2=125.0, fs_in=4000000, samples_per_ms=4000.0, samples_per_code=4000.0,
@@ -290,7 +291,8 @@ class Acquisition:
         d.update(kw)
         self.cfg = AcqCfg(**d)
         self.h = C.c_void_p()
-        service.check(service.L.gb200_acq_create(service.h, C.byref(self.cfg), C.byref(self.h)))
+        # fold > 1: QuickSync geometry (the wiped block folded `fold` times onto consumed / fold FFT points)
+        service.check(service.L.gb200_acq_create_folded(service.h, C.byref(self.cfg), fold, C.byref(self.h)))
         L = service.L
         self.fft_size = L.gb200_acq_fft_size(self.h)
         self.consumed = L.gb200_acq_consumed_samples(self.h)

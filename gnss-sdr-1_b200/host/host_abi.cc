@@ -8,6 +8,7 @@
 #include "gb200_c_aid_tracking.hpp"
 #include "gb200_glonass_tracking.hpp"
 #include "gb200_kf_tracking.hpp"
+#include "gb200_quicksync.hpp"
 #include "gb200_host_flat.h"
 #include "gb200_multicorrelator.hpp"
 #include "gb200_tracking.hpp"
@@ -270,6 +271,55 @@ int gbh_acqv_attempt(gb200_service* service, int variant, const double* cfg, int
         {
             B200_Galileo_Pcps_8ms_Acquisition acq(service, c, stream_id);
             ev = drive(acq);
+        }
+    *n_records = n;
+    return ev;
+}
+
+// ---- pcps_quicksync_acquisition_cc mirror (gb200_quicksync.hpp): a whole attempt, one record of 10 doubles per dwell ----
+// cfg = {folding_factor, sampled_ms, max_dwells, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, bit_transition_flag, threshold}
+// record = {event, folded_index, Acq_doppler_hz, test_statistic, input_power, mag, well_count, Acq_delay_samples, Acq_samplestamp, best |corr|^2}
+int gbh_qs_attempt(gb200_service* service, const double* cfg, int stream_id, const float* code_iq, size_t code_items, uint64_t samp_count, int max_runs,
+    double* records, int* n_records)
+{
+    QuickSyncConf c;
+    c.folding_factor = (uint32_t)cfg[0];
+    c.sampled_ms = (uint32_t)cfg[1];
+    c.max_dwells = (uint32_t)cfg[2];
+    c.doppler_max = (uint32_t)cfg[3];
+    c.doppler_step = (uint32_t)cfg[4];
+    c.fs_in = (int64_t)cfg[5];
+    c.samples_per_ms = (int32_t)cfg[6];
+    c.samples_per_code = (int32_t)cfg[7];
+    c.bit_transition_flag = cfg[8] != 0.0;
+    c.threshold = (float)cfg[9];
+    B200_Pcps_QuickSync_Acquisition acq(service, c, stream_id);
+    *n_records = 0;
+    if (!acq.ok()) return -1;
+    AcqSynchro syn;
+    acq.set_gnss_synchro(&syn);
+    if (!acq.set_local_code(reinterpret_cast<const std::complex<float>*>(code_iq), code_items)) return -1;
+    acq.reset();
+    int ev = 0, n = 0;
+    uint64_t at = samp_count;
+    for (int k = 0; k < max_runs && ev == 0; k++)
+        {
+            ev = acq.run(at);
+            if (ev < 0) return ev;
+            double* r = records + 10 * n++;
+            r[0] = ev;
+            r[1] = acq.folded_index();
+            r[2] = syn.Acq_doppler_hz;
+            r[3] = acq.test_statistics();
+            r[4] = acq.input_power();
+            r[5] = acq.mag();
+            r[6] = acq.well_count();
+            r[7] = syn.Acq_delay_samples;
+            r[8] = (double)syn.Acq_samplestamp_samples;
+            float best = 0.0f;
+            for (float v : acq.corr_output()) best = v > best ? v : best;
+            r[9] = best;
+            at += acq.vector_items();
         }
     *n_records = n;
     return ev;

@@ -180,6 +180,15 @@ typedef struct gb200_acq_result
 
 /* = pcps_acquisition ctor + init() (pcps_acquisition.cc:63-195, 313-370) */
 GB200_API int gb200_acq_create(gb200_service* s, const gb200_acq_cfg* cfg, gb200_acq** out);
+/* = pcps_quicksync_acquisition_cc's geometry (src/algorithms/acquisition/gnuradio_blocks/pcps_quicksync_acquisition_cc.cc:94-95,
+ * 380-398): a dwell still reads d_consumed_samples = sampled_ms * samples_per_ms items, but every Doppler bin's wiped block is
+ * FOLDED `fold` times (fold = folding_factor^2: segment i is added onto segment 0 in float32, i ascending) onto an FFT of
+ * consumed / fold points; gb200_acq_fft_size() returns that length, gb200_acq_set_local_code() takes the caller's folded code
+ * (fft_size items, :186-196) and the input power is the mean over all consumed items (:363-365).  gb200_acq_result::peak_mag /
+ * code_phase_index / doppler_bin are the folded search's maximum (first maximum in bin, then index order); the block's
+ * time-domain disambiguation among the folding_factor candidate delays (:436-470) is the caller's (host/gb200_quicksync.hpp).
+ * fold == 1 is gb200_acq_create.  Needs sampled_ms == ms_per_code, no bit_transition_flag / make_2_steps in `cfg`. */
+GB200_API int gb200_acq_create_folded(gb200_service* s, const gb200_acq_cfg* cfg, uint32_t fold, gb200_acq** out);
 GB200_API int gb200_acq_destroy(gb200_acq* a);
 GB200_API uint32_t gb200_acq_fft_size(const gb200_acq* a);         /* d_fft_size */
 GB200_API uint32_t gb200_acq_consumed_samples(const gb200_acq* a); /* d_consumed_samples */

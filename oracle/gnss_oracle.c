@@ -1474,7 +1474,8 @@ uint32_t go_acq_resampler_decimation(int64_t fs_in, uint32_t opt_acq_fs)
 }
 
 
-/* ======================= pcps_acquisition_fine_doppler_cc -- TEST INFRASTRUCTURE, block-level parity unpinned ======================= */
+/* ======================= pcps_acquisition_fine_doppler_cc -- TEST INFRASTRUCTURE; pinned to the block itself by
+ * tests/test_ref_blocks2_cpu.py::test_fine_doppler_block_equals_restatement ======================= */
 struct go_fd
 {
     go_fd_conf c;
@@ -1659,5 +1660,188 @@ int go_fd_attempt(go_fd* a, const float* in, const float* code_1ms, go_fd_result
     free(rep);
     free(buf);
     free(mag);
+    return 0;
+}
+
+/* ======================= pcps_quicksync_acquisition_cc -- TEST INFRASTRUCTURE =======================
+ * src/algorithms/acquisition/gnuradio_blocks/pcps_quicksync_acquisition_cc.cc.  fft_size = samples_per_code / folding_factor
+ * (:95); a dwell uses samples_per_code * folding_factor items, wiped off and folded folding_factor^2 times (:391-398).
+ * The block's complex_acumulator[100] is an UNINITIALISED stack array it adds onto (:439-462); this restatement starts it at 0. */
+struct go_qs
+{
+    go_qs_conf c;
+    uint32_t fft_size, num_bins, used;
+    float** wipeoffs;
+    float *fft_codes, *code, *work, *in_temp, *mag;
+    uint32_t well_count;
+    float d_mag, test_statistics;
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp;
+};
+
+go_qs* go_qs_create(const go_qs_conf* conf)
+{
+    go_qs* a = (go_qs*)calloc(1, sizeof(go_qs));
+    a->c = *conf;
+    if (a->c.doppler_step == 0) a->c.doppler_step = 250; /* init() :214-217 */
+    a->fft_size = (uint32_t)conf->samples_per_code / conf->folding_factor;
+    a->used = (uint32_t)conf->samples_per_code * conf->folding_factor;
+    for (int32_t d = -(int32_t)a->c.doppler_max; d <= (int32_t)a->c.doppler_max; d += (int32_t)a->c.doppler_step) a->num_bins++;
+    a->wipeoffs = (float**)calloc(a->num_bins, sizeof(float*));
+    for (uint32_t i = 0; i < a->num_bins; i++)
+        {
+            a->wipeoffs[i] = (float*)calloc(2 * (size_t)a->used, sizeof(float));
+            go_sincos(a->wipeoffs[i], -go_qs_phase_step(a, i), 0.0f, (int)a->used);
+        }
+    a->fft_codes = (float*)calloc(2 * (size_t)a->fft_size, sizeof(float));
+    a->code = (float*)calloc(2 * (size_t)conf->samples_per_code, sizeof(float));
+    a->work = (float*)calloc(2 * (size_t)a->fft_size, sizeof(float));
+    a->in_temp = (float*)calloc(2 * (size_t)a->used, sizeof(float));
+    a->mag = (float*)calloc(a->fft_size, sizeof(float));
+    return a;
+}
+
+void go_qs_destroy(go_qs* a)
+{
+    if (!a) return;
+    for (uint32_t i = 0; i < a->num_bins; i++) free(a->wipeoffs[i]);
+    free(a->wipeoffs);
+    free(a->fft_codes);
+    free(a->code);
+    free(a->work);
+    free(a->in_temp);
+    free(a->mag);
+    free(a);
+}
+
+uint32_t go_qs_fft_size(const go_qs* a) { return a->fft_size; }
+uint32_t go_qs_num_doppler_bins(const go_qs* a) { return a->num_bins; }
+/* :236-237: float phase_step_rad = GPS_TWO_PI * doppler / static_cast<float>(d_fs_in) -- double product rounded once */
+float go_qs_phase_step(const go_qs* a, uint32_t bin)
+{
+    const int32_t doppler = -(int32_t)a->c.doppler_max + (int32_t)(a->c.doppler_step * bin);
+    return (float)(GO_GPS_TWO_PI * doppler / (float)a->c.fs_in);
+}
+
+/* set_local_code (:177-200): keep the unfolded code, fold folding_factor segments onto a zeroed buffer, FFT, conjugate */
+void go_qs_set_local_code(go_qs* a, const float* code_iq, float* folded_iq)
+{
+    const uint32_t n = a->fft_size;
+    memcpy(a->code, code_iq, sizeof(float) * 2 * (size_t)a->c.samples_per_code);
+    memset(a->work, 0, sizeof(float) * 2 * n);
+    for (uint32_t i = 0; i < a->c.folding_factor; i++)
+        for (uint32_t k = 0; k < 2 * n; k++) a->work[k] = code_iq[2 * (size_t)i * n + k] + a->work[k]; /* std::plus(code, inbuf) */
+    if (folded_iq) memcpy(folded_iq, a->work, sizeof(float) * 2 * n);
+    go_fft_f32(a->work, (int)n, -1);
+    for (uint32_t i = 0; i < n; i++)
+        {
+            a->fft_codes[2 * i] = a->work[2 * i];
+            a->fft_codes[2 * i + 1] = -a->work[2 * i + 1];
+        }
+}
+
+void go_qs_restart(go_qs* a)
+{
+    /* state 0 with d_active (:296-310) / set_state(1) (:255-266) */
+    a->acq_delay_samples = 0.0;
+    a->acq_doppler_hz = 0.0;
+    a->acq_samplestamp = 0;
+    a->well_count = 0;
+    a->d_mag = 0.0f;
+    a->test_statistics = 0.0f;
+}
+
+/* state 1 (:318-532) */
+int go_qs_run(go_qs* a, const float* in_iq, uint64_t sample_counter_after, go_qs_result* out)
+{
+    const uint32_t n = a->fft_size, F = a->c.folding_factor, spc = (uint32_t)a->c.samples_per_code, used = a->used;
+    const float fnf = (float)n * (float)n;
+    float input_power = 0.0f;
+    memset(out, 0, sizeof(*out));
+    a->d_mag = 0.0f;            /* :343-346: d_mag and d_test_statistics restart EVERY dwell */
+    a->test_statistics = 0.0f;
+    a->well_count++;
+    for (uint32_t i = 0; i < used; i++) input_power += in_iq[2 * i] * in_iq[2 * i] + in_iq[2 * i + 1] * in_iq[2 * i + 1];
+    input_power /= (float)used;
+    for (uint32_t bin = 0; bin < a->num_bins; bin++)
+        {
+            const int32_t doppler = -(int32_t)a->c.doppler_max + (int32_t)(a->c.doppler_step * bin);
+            const float* w = a->wipeoffs[bin];
+            for (uint32_t i = 0; i < used; i++)
+                {
+                    a->in_temp[2 * i] = in_iq[2 * i] * w[2 * i] - in_iq[2 * i + 1] * w[2 * i + 1];
+                    a->in_temp[2 * i + 1] = in_iq[2 * i] * w[2 * i + 1] + in_iq[2 * i + 1] * w[2 * i];
+                }
+            memset(a->work, 0, sizeof(float) * 2 * n);
+            for (uint32_t i = 0; i < F * F; i++)
+                for (uint32_t k = 0; k < 2 * n; k++) a->work[k] = a->in_temp[2 * (size_t)i * n + k] + a->work[k];
+            go_fft_f32(a->work, (int)n, -1);
+            for (uint32_t i = 0; i < n; i++)
+                {
+                    const float xr = a->work[2 * i], xi = a->work[2 * i + 1];
+                    const float cr = a->fft_codes[2 * i], ci = a->fft_codes[2 * i + 1];
+                    a->work[2 * i] = xr * cr - xi * ci;
+                    a->work[2 * i + 1] = xr * ci + xi * cr;
+                }
+            go_fft_f32(a->work, (int)n, +1);
+            for (uint32_t i = 0; i < n; i++) a->mag[i] = a->work[2 * i] * a->work[2 * i] + a->work[2 * i + 1] * a->work[2 * i + 1];
+            const uint32_t indext = go_index_max(a->mag, n);
+            const float magt = a->mag[indext] / (fnf * fnf);
+            if (a->d_mag < magt)
+                {
+                    a->d_mag = magt;
+                    if (a->test_statistics < (a->d_mag / input_power) || !a->c.bit_transition_flag)
+                        {
+                            const uint32_t folded = indext % spc;
+                            float best = 0.0f;
+                            uint32_t best_i = 0;
+                            for (uint32_t i = 0; i < F; i++)
+                                {
+                                    const uint32_t delay = folded + i * n;
+                                    float ar = 0.0f, ai = 0.0f; /* the block's accumulator is uninitialised stack memory */
+                                    for (uint32_t j = 0; j < spc; j++)
+                                        {
+                                            const float xr = a->in_temp[2 * (size_t)(delay + j)], xi = a->in_temp[2 * (size_t)(delay + j) + 1];
+                                            const float cr = a->code[2 * j], ci = a->code[2 * j + 1];
+                                            ar += xr * cr - xi * ci;
+                                            ai += xr * ci + xi * cr;
+                                        }
+                                    const float m = ar * ar + ai * ai;
+                                    if (i < 16) out->corr_output[i] = m;
+                                    if (i == 0 || m > best) /* volk_gnsssdr_32f_index_max_32u: first maximum */
+                                        {
+                                            best = m;
+                                            best_i = i;
+                                        }
+                                }
+                            a->acq_delay_samples = (double)(folded + best_i * n);
+                            a->acq_doppler_hz = (double)doppler;
+                            a->acq_samplestamp = sample_counter_after;
+                            a->test_statistics = a->d_mag / input_power;
+                            out->improved = 1;
+                            out->folded_index = indext;
+                            out->doppler_bin = bin;
+                            out->best_candidate = best_i;
+                        }
+                }
+        }
+    int state = 1;
+    if (!a->c.bit_transition_flag)
+        {
+            if (a->test_statistics > a->c.threshold)
+                state = 2;
+            else if (a->well_count == a->c.max_dwells)
+                state = 3;
+        }
+    else if (a->well_count == a->c.max_dwells)
+        state = a->test_statistics > a->c.threshold ? 2 : 3;
+    out->well_count = a->well_count;
+    out->mag = a->d_mag;
+    out->input_power = input_power;
+    out->test_statistic = a->test_statistics;
+    out->state = state;
+    out->acq_delay_samples = a->acq_delay_samples;
+    out->acq_doppler_hz = a->acq_doppler_hz;
+    out->acq_samplestamp = a->acq_samplestamp;
     return 0;
 }

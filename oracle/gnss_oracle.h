@@ -231,6 +231,38 @@ int go_fd_attempt(go_fd* a, const float* in_iq, const float* code_1ms_iq, go_fd_
 /* the replica estimate_Doppler builds (:412-428): 10 * samples_per_ms items, incl. its off-by-one std::rotate */
 void go_fd_replica(const float* code_1ms_iq, uint32_t fft_size, int shift_index, float* replica_iq);
 
+/* ---- pcps_quicksync_acquisition_cc: folded FFT search + time-domain disambiguation ---- */
+typedef struct go_qs_conf
+{
+    uint32_t folding_factor, sampled_ms, max_dwells, doppler_max, doppler_step;
+    int64_t fs_in;
+    int32_t samples_per_ms, samples_per_code;
+    int bit_transition_flag;
+    float threshold;
+} go_qs_conf;
+typedef struct go_qs_result
+{
+    uint32_t well_count, folded_index, doppler_bin, best_candidate; /* of the last improvement in this dwell (0 if none) */
+    int improved;                /* the dwell rewrote the Gnss_Synchro fields */
+    float mag, input_power, test_statistic;
+    int state;                   /* 1 more dwells, 2 positive, 3 negative (d_state after the dwell) */
+    double acq_delay_samples, acq_doppler_hz;
+    uint64_t acq_samplestamp;
+    float corr_output[16];       /* d_corr_output_f of the last improvement */
+} go_qs_result;
+typedef struct go_qs go_qs;
+go_qs* go_qs_create(const go_qs_conf* conf);
+void go_qs_destroy(go_qs* a);
+uint32_t go_qs_fft_size(const go_qs* a);
+uint32_t go_qs_num_doppler_bins(const go_qs* a);
+float go_qs_phase_step(const go_qs* a, uint32_t bin);
+/* code_iq: samples_per_code items (the block copies that many, :181); folded_iq (may be NULL) receives the fft_size folded items */
+void go_qs_set_local_code(go_qs* a, const float* code_iq, float* folded_iq);
+void go_qs_restart(go_qs* a); /* set_state(1) / state 0 with d_active */
+/* one pass through state 1: in_iq = one input vector (sampled_ms * samples_per_ms items, of which samples_per_code *
+ * folding_factor are used); sample_counter_after = d_sample_counter after the += at :349 */
+int go_qs_run(go_qs* a, const float* in_iq, uint64_t sample_counter_after, go_qs_result* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,7 +80,8 @@ struct GbRefAcqvCall
 
 struct GbRefAcqv
 {
-    int variant = 0;  // 0 Tong, 1 Galileo 8 ms, 2 E5a non-coherent I/Q CAF, 3 QuickSync
+    int variant = 0;  // 0 Tong, 1 Galileo 8 ms, 2 E5a non-coherent I/Q CAF, 3 QuickSync, 4 fine Doppler
+    pcps_acquisition_fine_doppler_cc_sptr fd;
     pcps_tong_acquisition_cc_sptr tong;
     galileo_pcps_8ms_acquisition_cc_sptr g8;
     galileo_e5a_noncoherentIQ_acquisition_caf_cc_sptr e5a;
@@ -128,6 +129,28 @@ void* gbref_acqv_create(int variant, const double* cfg, char system, const char*
             GB_SETUP(h->e5a)
             h->vector_items = 1;  // this block takes a plain gr_complex stream and buffers it itself
             break;
+        case 4:
+            {
+                // the adapter's Acq_Conf (gps_l1_ca_pcps_acquisition_fine_doppler.cc:52-80): doppler_max, sampled_ms, max_dwells, samples_per_ms
+                Acq_Conf ac = Acq_Conf();
+                ac.fs_in = fs_in;
+                ac.samples_per_chip = 1;
+                ac.doppler_max = doppler_max;
+                ac.sampled_ms = sampled_ms;
+                ac.max_dwells = max_dwells;
+                ac.samples_per_ms = (float)samples_per_ms;
+                ac.dump = false;
+                ac.blocking_on_standby = false;
+                h->fd = pcps_make_acquisition_fine_doppler_cc(ac);
+                h->fd->set_channel(0);
+                h->fd->set_gnss_synchro(&h->sync);
+                h->fd->set_threshold((float)cfg[7]);
+                h->fd->set_doppler_max(doppler_max);
+                h->fd->set_doppler_step(doppler_step);
+                h->blk = h->fd.get();
+                h->vector_items = 1;  // plain gr_complex stream
+                break;
+            }
         default:
             h->qs = pcps_quicksync_make_acquisition_cc((uint32_t)cfg[15], sampled_ms, max_dwells, doppler_max, fs_in, samples_per_ms, samples_per_code, cfg[11] != 0, false, "");
             GB_SETUP(h->qs)
@@ -148,6 +171,7 @@ void gbref_acqv_init(void* hv)
     if (h->g8) h->g8->init();
     if (h->e5a) h->e5a->init();
     if (h->qs) h->qs->init();
+    if (h->fd) h->fd->init();
 }
 
 void gbref_acqv_set_local_code(void* hv, float* code_iq, float* code_q_iq)
@@ -158,6 +182,7 @@ void gbref_acqv_set_local_code(void* hv, float* code_iq, float* code_q_iq)
     if (h->g8) h->g8->set_local_code(c);
     if (h->e5a) h->e5a->set_local_code(c, reinterpret_cast<std::complex<float>*>(code_q_iq));
     if (h->qs) h->qs->set_local_code(c);
+    if (h->fd) h->fd->set_local_code(c);
 }
 
 void gbref_acqv_set_state(void* hv, int state)
@@ -167,6 +192,7 @@ void gbref_acqv_set_state(void* hv, int state)
     if (h->g8) h->g8->set_state(state);
     if (h->e5a) h->e5a->set_state(state);
     if (h->qs) h->qs->set_state(state);
+    if (h->fd) h->fd->set_state(state);
 }
 
 void gbref_acqv_set_active(void* hv, int active)
@@ -176,6 +202,7 @@ void gbref_acqv_set_active(void* hv, int active)
     if (h->g8) h->g8->set_active(active != 0);
     if (h->e5a) h->e5a->set_active(active != 0);
     if (h->qs) h->qs->set_active(active != 0);
+    if (h->fd) h->fd->set_active(active != 0);
 }
 
 // one general_work() on `n_in` input items (vectors for Tong / 8 ms / QuickSync, gr_complex items for the E5a block)
@@ -189,13 +216,14 @@ void gbref_acqv_work(void* hv, const float* items_iq, int n_in, GbRefAcqvCall* o
     if (h->g8) out->state_before = h->g8->d_state;
     if (h->e5a) out->state_before = h->e5a->d_state;
     if (h->qs) out->state_before = h->qs->d_state;
+    if (h->fd) out->state_before = h->fd->d_state;
 #undef GB_STATE
     gr_vector_int ninput(1, n_in);
     gr_vector_const_void_star in(1, items_iq);
     gr_vector_void_star outv;
     h->blk->gb_consumed = 0;
     h->blk->gb_events.clear();
-    h->blk->general_work(0, ninput, in, outv);
+    h->blk->general_work(h->fd ? n_in : 0, ninput, in, outv);  // the fine-Doppler block reads its input count from noutput_items
     out->consumed = (int32_t)h->blk->gb_consumed;
     out->event = h->blk->gb_events.empty() ? 0 : (int32_t)h->blk->gb_events.back();
 #define GB_COPY(B, CNT)                                \
@@ -214,6 +242,14 @@ void gbref_acqv_work(void* hv, const float* items_iq, int n_in, GbRefAcqvCall* o
     if (h->g8) { GB_COPY(h->g8, d_well_count) }
     if (h->e5a) { GB_COPY(h->e5a, d_well_count) }
     if (h->qs) { GB_COPY(h->qs, d_well_count) }
+    if (h->fd)
+        {
+            out->state_after = h->fd->d_state;
+            out->test_statistics = h->fd->d_test_statistics;
+            out->count = (uint32_t)h->fd->d_well_count;
+            out->sample_counter = h->fd->d_sample_counter;
+            out->active = h->fd->d_active;
+        }
 #undef GB_COPY
     out->acq_delay_samples = h->sync.Acq_delay_samples;
     out->acq_doppler_hz = h->sync.Acq_doppler_hz;

@@ -210,6 +210,20 @@ def acq_variant_attempt(service, variant, stream_id, code_c64, samp_count, max_r
     return ev, np.array(rec[: 8 * n.value]).reshape(n.value, 8)
 
 
+def quicksync_attempt(service, stream_id, code_c64, samp_count, max_runs, folding_factor, sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms,
+                      samples_per_code, threshold, max_dwells=1, bit_transition_flag=0):
+    """B200_Pcps_QuickSync_Acquisition: one attempt; returns (event, records) with one record per dwell: event, folded_index, Acq_doppler_hz,
+    test_statistic, input_power, mag, well_count, Acq_delay_samples, Acq_samplestamp, best |corr|^2."""
+    L = host()
+    L.gbh_qs_attempt.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, f32p, C.c_size_t, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    cfg = (C.c_double * 10)(folding_factor, sampled_ms, max_dwells, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, bit_transition_flag, threshold)
+    code = np.ascontiguousarray(code_c64, np.complex64).view(np.float32)
+    rec = (C.c_double * (10 * max_runs))()
+    n = C.c_int(0)
+    ev = L.gbh_qs_attempt(service.h, cfg, stream_id, code, len(code) // 2, samp_count, max_runs, rec, C.byref(n))
+    return ev, np.array(rec[: 10 * n.value]).reshape(n.value, 10)
+
+
 def oracle_loop():
     global _hol
     if _hol is None:

@@ -393,6 +393,70 @@ class OracleAcqVariant:
             self.h = None
 
 
+class GoQsConf(C.Structure):
+    _fields_ = [("folding_factor", C.c_uint32), ("sampled_ms", C.c_uint32), ("max_dwells", C.c_uint32), ("doppler_max", C.c_uint32),
+                ("doppler_step", C.c_uint32), ("fs_in", C.c_int64), ("samples_per_ms", C.c_int32), ("samples_per_code", C.c_int32),
+                ("bit_transition_flag", C.c_int), ("threshold", C.c_float)]
+
+
+class GoQsResult(C.Structure):
+    _fields_ = [("well_count", C.c_uint32), ("folded_index", C.c_uint32), ("doppler_bin", C.c_uint32), ("best_candidate", C.c_uint32),
+                ("improved", C.c_int), ("mag", C.c_float), ("input_power", C.c_float), ("test_statistic", C.c_float), ("state", C.c_int),
+                ("acq_delay_samples", C.c_double), ("acq_doppler_hz", C.c_double), ("acq_samplestamp", C.c_uint64), ("corr_output", C.c_float * 16)]
+
+
+class OracleQuickSync:
+    """pcps_quicksync_acquisition_cc restatement (oracle/gnss_oracle.c go_qs_*)."""
+
+    def __init__(self, folding_factor, sampled_ms, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, threshold, max_dwells=1,
+                 bit_transition_flag=0):
+        self.L = oracle()
+        L = self.L
+        L.go_qs_create.argtypes = [C.POINTER(GoQsConf)]
+        L.go_qs_create.restype = C.c_void_p
+        L.go_qs_destroy.argtypes = [C.c_void_p]
+        L.go_qs_fft_size.argtypes = [C.c_void_p]
+        L.go_qs_fft_size.restype = C.c_uint32
+        L.go_qs_num_doppler_bins.argtypes = [C.c_void_p]
+        L.go_qs_num_doppler_bins.restype = C.c_uint32
+        L.go_qs_phase_step.argtypes = [C.c_void_p, C.c_uint32]
+        L.go_qs_phase_step.restype = C.c_float
+        L.go_qs_set_local_code.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.go_qs_restart.argtypes = [C.c_void_p]
+        L.go_qs_run.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(GoQsResult)]
+        self.conf = GoQsConf(folding_factor, sampled_ms, max_dwells, doppler_max, doppler_step, fs_in, samples_per_ms, samples_per_code, bit_transition_flag, threshold)
+        self.h = L.go_qs_create(C.byref(self.conf))
+        self.fft_size = L.go_qs_fft_size(self.h)
+        self.num_bins = L.go_qs_num_doppler_bins(self.h)
+        self.vector_items = sampled_ms * samples_per_ms
+        self.samples_per_code = samples_per_code
+
+    def phase_steps(self):
+        return np.array([self.L.go_qs_phase_step(self.h, b) for b in range(self.num_bins)], np.float32)
+
+    def set_local_code(self, code_c64):
+        code = np.ascontiguousarray(code_c64, np.complex64)
+        assert len(code) >= self.samples_per_code
+        folded = np.zeros(self.fft_size, np.complex64)
+        self.L.go_qs_set_local_code(self.h, code.ctypes.data_as(C.c_void_p), folded.ctypes.data_as(C.c_void_p))
+        return folded
+
+    def restart(self):
+        self.L.go_qs_restart(self.h)
+
+    def run(self, vector_c64, sample_counter_after):
+        x = np.ascontiguousarray(vector_c64[: self.vector_items], np.complex64)
+        assert len(x) == self.vector_items
+        r = GoQsResult()
+        self.L.go_qs_run(self.h, x.ctypes.data_as(C.c_void_p), sample_counter_after, C.byref(r))
+        return r
+
+    def close(self):
+        if self.h:
+            self.L.go_qs_destroy(self.h)
+            self.h = None
+
+
 class OracleAcq:
     """pcps_acquisition restatement as an object (oracle/gnss_oracle.c go_acq_*)."""
 
@@ -635,7 +699,7 @@ class GbRefAcqvCall(C.Structure):
                 ("active", C.c_int32)]
 
 
-REF_TONG, REF_8MS, REF_E5A, REF_QUICKSYNC = 0, 1, 2, 3
+REF_TONG, REF_8MS, REF_E5A, REF_QUICKSYNC, REF_FINE_DOPPLER = 0, 1, 2, 3, 4
 
 
 def ref_blocks2():

@@ -442,7 +442,7 @@ def test_kf_loop_on_b200_matches_oracle_loop_and_the_reference_block(service, or
     """gps_l1_ca_kf_tracking_cc: the Kalman carrier loop mirror (host/gb200_kf_tracking.hpp) closed on the B200
     real-code correlator -- configured like the reference object the block owns: high-dynamics code resampler, plain rotator --
     vs the same loop on the oracle correlator AND vs the reference block itself (oracle/_ref).  Block boundaries and flags equal;
-    Doppler within 0.5 Hz, prompts within 2e-3 of the peak, code phase within 0.01 samples over 600 epochs."""
+    Doppler within 0.01 Hz, prompts within 1e-4 of the peak in the median, code phase within 1e-3 samples over 600 epochs."""
     import gnss_b200 as gb
     import oracle_lib as ol
     import test_host_cpu as thc
@@ -469,6 +469,9 @@ def test_kf_loop_on_b200_matches_oracle_loop_and_the_reference_block(service, or
     dd = np.abs(got[:, F["carrier_doppler_hz"]] - blk[:, 3])
     print("KF order %d closed loop vs the block: doppler diff max %.3g Hz, prompt magnitude diff max %.3g of peak, final doppler %.1f Hz" % (
         order, dd[1:].max(), rel.max(), got[-1, F["carrier_doppler_hz"]]))
-    assert dd[1:].max() < 0.5 and rel.max() < 2e-3
+    # the two closed loops drift apart by ~1e-6 samples of code phase, so now and then ONE sample of one epoch falls on the other side
+    # of a chip boundary and moves that epoch's prompt by up to 2 |x| (measured: one epoch of 600 at 3.2e-3 of the peak, all others
+    # below 5e-5; the same correlate call with the block's own arguments agrees to 2e-5): median tight, maximum = one flipped chip
+    assert dd[1:].max() < 0.01 and np.median(rel) < 1e-4 and rel.max() < 1.5e-2
     assert abs(got[-200:, F["carrier_doppler_hz"]].mean() - doppler) < 3.0
-    assert np.abs(got[1:, F["code_phase_samples"]] - blk[1:, 4]).max() < 0.01
+    assert np.abs(got[1:, F["code_phase_samples"]] - blk[1:, 4]).max() < 1e-3

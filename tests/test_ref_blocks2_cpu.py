@@ -1,10 +1,12 @@
-"""The reference's SIBLING acquisition blocks themselves as the oracle of their restatements (CPU only).
+"""The reference's SIBLING blocks themselves as the oracle of their restatements and mirrors (CPU only).
 
-pcps_tong_acquisition_cc, galileo_pcps_8ms_acquisition_cc and galileo_e5a_noncoherentIQ_acquisition_caf_cc are compiled unmodified
-from /root/reference into oracle/_ref (oracle/ref_blocks2.cc drives them).  The restatements oracle/gnss_oracle.c go_acqv_* / go_e5a_*
--- the checkers of the GPU tests of B200_Pcps_Tong_Acquisition, B200_Galileo_Pcps_8ms_Acquisition and
-B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf -- are held to the blocks dwell by dwell: statistic, input power, delay, Doppler,
-counters and events EQUAL (same DFT, same float32 arithmetic).  This turns "block-level parity unpinned" into pinned for them."""
+pcps_tong_acquisition_cc, galileo_pcps_8ms_acquisition_cc, galileo_e5a_noncoherentIQ_acquisition_caf_cc, pcps_quicksync_acquisition_cc,
+pcps_acquisition_fine_doppler_cc, glonass_l1_ca_dll_pll_tracking_cc, gps_l1_ca_dll_pll_c_aid_tracking_cc / _sc and
+gps_l1_ca_kf_tracking_cc are compiled unmodified from /root/reference into oracle/_ref (oracle/ref_blocks2.cc drives them).
+The restatements oracle/gnss_oracle.c go_acqv_* / go_e5a_* / go_qs_* / go_fd_* -- the checkers of the GPU tests of the B200_* acquisition
+mirrors -- are held to the blocks dwell by dwell: statistic, input power, delay, Doppler, counters and events EQUAL (same DFT, same
+float32 arithmetic); the tracker mirrors (host/gb200_*_tracking.hpp on the oracle's correlators) are held to the blocks epoch by
+epoch.  This turns "block-level parity unpinned" into pinned for all of them."""
 import numpy as np
 import pytest
 
@@ -222,3 +224,93 @@ def test_kf_tracker_mirror_equals_the_block(order, bce):
         assert not np.array_equal(ep[300:, F["carr_phase_sigma2"]], hl.run_oracle_kf(
             x, 0, code.real, acq_delay=delay + 0.5, acq_doppler=doppler - 30.0, acq_stamp=0, acq_doppler_step=250, n_steps=700, fs_in=fs, vector_length=4000,
             dll_bw_hz=2.0, early_late_space_chips=0.5, order=order)[300:, F["carr_phase_sigma2"]])
+
+
+# ------------------------------------------------------------------------------------------------ QuickSync
+def _qs_scene(fs, spc, n_vectors, vec, delay, doppler, cn0, seed, prn=7):
+    x = synth.make_iq(fs, n_vectors * vec, [dict(kind="gps_l1_ca", prn=prn, cn0_dbhz=cn0, doppler_hz=doppler, delay_samples=delay, phase=0.3)], seed)
+    code1 = synth.sampled_code(synth.code_table("gps_l1_ca", prn), 1.023e6, fs, spc).astype(np.complex64)
+    return x, code1
+
+
+@pytest.mark.parametrize("what,folding,cn0,thr,max_dwells,bit_transition", [
+    ("positive F=2", 2, 50.0, 0.05, 1, 0),
+    ("positive F=4", 4, 52.0, 0.05, 1, 0),
+    ("negative two dwells", 2, 0.0, 1e9, 2, 0),
+    ("bit transition rule", 2, 50.0, 0.05, 2, 1),
+])
+def test_quicksync_block_equals_restatement(what, folding, cn0, thr, max_dwells, bit_transition):
+    """pcps_quicksync_acquisition_cc itself against go_qs_*: folded search (folding_factor^2 segments onto samples_per_code /
+    folding_factor points), input power over the used items, normalised maximum, the time-domain choice among the folding_factor
+    candidate delays, well counter, sample stamp, state and event -- all EQUAL, dwell by dwell.  (The block adds its time-domain
+    sums onto an uninitialised stack array; compiled here that memory is zero when the block reaches it, which is what the
+    restatement assumes.)"""
+    from test_ref_blocks_cpu import quiet
+
+    fs, spc = 4_000_000, 4000
+    sampled_ms = folding * 2  # adapter rule: a multiple of folding_factor (gps_l1_ca_pcps_quicksync_acquisition.cc:74-90)
+    vec = sampled_ms * 4000
+    delay, doppler = 2345, 1250.0
+    x, code1 = _qs_scene(fs, spc, max_dwells + 2, vec, delay, doppler, cn0, 20260041 + folding)
+    with quiet():
+        b = ol.RefAcqVariantBlock(ol.REF_QUICKSYNC, sampled_ms, 5000, 250, fs, 4000, spc, thr, max_dwells=max_dwells, bit_transition_flag=bit_transition,
+                                  folding_factor=folding, prn=7)
+        code = np.tile(code1, sampled_ms // folding)  # the adapter's code_ (:243-247); the block copies samples_per_code items of it
+        b.set_local_code(code)
+        b.set_state(1)
+        calls, ev = drive(b, x, vec)
+    o = ol.OracleQuickSync(folding, sampled_ms, 5000, 250, fs, 4000, spc, thr, max_dwells=max_dwells, bit_transition_flag=bit_transition)
+    o.set_local_code(code)
+    o.restart()
+    k = 0
+    for r in calls:
+        if r.state_before != 1:
+            continue
+        ro = o.run(x[k * vec: (k + 1) * vec], (k + 1) * vec)
+        k += 1
+        assert (r.test_statistics, r.input_power, r.mag, r.count, r.acq_delay_samples, r.acq_doppler_hz, r.acq_samplestamp_samples, r.state_after) == \
+            (ro.test_statistic, ro.input_power, ro.mag, ro.well_count, ro.acq_delay_samples, ro.acq_doppler_hz, ro.acq_samplestamp, ro.state), (what, k)
+    assert k == (max_dwells if ("negative" in what or bit_transition) else 1)
+    assert ev == (2 if "negative" in what else 1)
+    if "negative" not in what:
+        assert ro.acq_delay_samples == delay and ro.acq_doppler_hz == doppler
+    b.close()
+    o.close()
+
+
+# ------------------------------------------------------------------------------------------------ fine Doppler
+@pytest.mark.parametrize("dop,delay,cn0,dwells,thr", [(1730.0, 1234, 50.0, 2, 2.5), (-3120.0, 3999, 47.0, 3, 2.5), (400.0, 0, 50.0, 1, 2.5), (0.0, 100, -100.0, 2, 2.5)])
+def test_fine_doppler_block_equals_restatement(dop, delay, cn0, dwells, thr):
+    """pcps_acquisition_fine_doppler_cc itself against go_fd_*: the un-normalised grid summed over max_dwells dwells, compute_CAF's
+    first / second peak ratio, the 10 ms buffer, estimate_Doppler's replica (with its off-by-one std::rotate), the 8x zero-padded
+    FFT's maximum, the bin-to-Hz table and the 1 kHz acceptance test -- statistic, delay, refined Doppler, sample stamp and event
+    EQUAL (same scenes as tests/test_gpu_zz_fine_doppler.py, which holds the B200 mirror to go_fd_*)."""
+    from test_ref_blocks_cpu import quiet
+
+    fs, n = 4000000, 4000
+    sats = [dict(kind="gps_l1_ca", prn=5, cn0_dbhz=cn0, doppler_hz=dop, delay_samples=delay)] if cn0 > 0 else []
+    x = synth.make_iq(fs, 12 * n, sats, seed=int(abs(dop)) + 7)
+    code = np.zeros(2 * n, np.float32)
+    ol.oracle().go_gps_l1_ca_code_sampled(code, 5, fs, 0)
+    code = code.view(np.complex64)
+    o = ol.OracleFineDoppler(n, dwells, 5000, 500, fs, thr)
+    ro = o.attempt(x, code)
+    o.close()
+    with quiet():
+        b = ol.RefAcqVariantBlock(ol.REF_FINE_DOPPLER, 1, 5000, 500, fs, n, n, thr, max_dwells=dwells, prn=5)
+        b.set_local_code(code)
+        b.set_state(1)
+        pos, ev, stat = 0, 0, None
+        for _ in range(60):
+            r = b.work(x[pos:], min(len(x) - pos, n))
+            pos += r.consumed
+            if r.state_before == 2:
+                stat = r.test_statistics
+            if r.event:
+                ev = r.event
+                break
+        b.close()
+    assert ev == (1 if ro.positive else 2) and stat == ro.test_statistic, (ev, stat, ro.test_statistic)
+    if ro.positive:
+        assert (r.acq_delay_samples, r.acq_doppler_hz) == (ro.acq_delay_samples, ro.acq_doppler_hz), (r.acq_delay_samples, r.acq_doppler_hz, ro.acq_doppler_hz)
+        assert abs((r.acq_delay_samples - delay + n // 2) % n - n // 2) <= 1 and abs(r.acq_doppler_hz - dop) < 15.0 and ro.fine_accepted
