@@ -373,14 +373,14 @@ def config_results(svc, gb, steps):
     out = {}
     rng = np.random.default_rng(7)
 
-    def acq_case(fs, n, kind, rate, prns, step, item, sampled_ms, spc, spms, cfar, scene_sats):
+    def acq_case(fs, n, kind, rate, prns, step, item, sampled_ms, spc, spms, cfar, scene_sats, cfar_threshold=1e-3):
         x = synth.make_iq(fs, n + 64, scene_sats, 1234)
         host = x if item == gb.ITEM_32FC else synth.quantize(x, "16ic")
         svc.push(2, host, item, 0)
         acqs = []
         for p in prns:
             a = gb.Acquisition(svc, sampled_ms=sampled_ms, ms_per_code=sampled_ms, samples_per_chip=spc, doppler_max=5000, doppler_step=step, fs_in=fs,
-                               samples_per_ms=spms, samples_per_code=float(n), threshold=1e-3 if cfar else 2.0, use_CFAR_algorithm_flag=int(cfar), item_type=item)
+                               samples_per_ms=spms, samples_per_code=float(n), threshold=cfar_threshold if cfar else 2.0, use_CFAR_algorithm_flag=int(cfar), item_type=item)
             a.set_local_code(synth.sampled_code(synth.code_table(kind, p), rate, fs, n))
             acqs.append(a)
         h = gb.acq_handles(acqs)
@@ -448,7 +448,8 @@ def config_results(svc, gb, steps):
                  "tracking": trk_case(25e6, 12, 320, 25000, "gps_l5q", "gps_l5i", np.array([-0.5, 0.0, 0.5], np.float32), gb.ITEM_32FC, 10230.0, 1176.45e6)}
     e1 = [dict(kind="gal_e1b_sinboc", pilot_kind="gal_e1c_sinboc", prn=p, cn0_dbhz=50 - 2 * k, doppler_hz=-3300 + 2900 * k, delay_samples=12345 + 61111 * k) for k, p in enumerate([2, 12, 25])]
     out["C5"] = {"workload": "cold start at 50 Msps gr_complex: Galileo E1 acquisition 8 PRN x 80 bins x 200000 (of the 36-PRN search; --mode shard runs all 68 PRNs); tracking 8 E1 pilot channels x 40 epochs x 200000 samples, 5 taps + data-prompt tap",
-                 "acquisition": acq_case(50_000_000, 200000, "gal_e1b_sinboc", 2 * 1.023e6, [2, 12, 25, 1, 3, 4, 5, 6], 125, gb.ITEM_32FC, 4, 49, 50000.0, True, e1),
+                 "acquisition": acq_case(50_000_000, 200000, "gal_e1b_sinboc", 2 * 1.023e6, [2, 12, 25, 1, 3, 4, 5, 6], 125, gb.ITEM_32FC, 4, 49, 50000.0, True, e1,
+                                         cfar_threshold=2e-4),  # E1B alone carries half the power: statistic ~ CN0 / (2 fs) = 1e-3 at 50 dBHz; noise-only maximum ~ ln(cells) / N = 8e-5
                  "tracking": trk_case(50e6, 8, 40, 200000, "gal_e1c_sinboc", "gal_e1b_sinboc", TAPS, gb.ITEM_32FC, 8184.0, 1575.42e6)}
     return out
 
