@@ -6,6 +6,7 @@
 #ifndef GNSS_SDR_B200_PCPS_ACQUISITION_H
 #define GNSS_SDR_B200_PCPS_ACQUISITION_H
 
+#include "GLONASS_L1_L2_CA.h"  // DFRQ1_GLO, DFRQ2_GLO, GLONASS_PRN
 #include "acq_conf.h"
 #include "channel_fsm.h"
 #include "gnss_synchro.h"
@@ -16,6 +17,7 @@
 #include <cmath>
 #include <complex>
 #include <cstdint>
+#include <cstring>
 #include <memory>
 
 class b200_pcps_acquisition;
@@ -53,11 +55,20 @@ public:
         d_gnss_synchro->Acq_samplestamp_samples = 0ULL;
         d_mag = 0.0;
         d_input_power = 0.0;
-        gb200_acq_set_doppler(h_, acq_parameters.doppler_max, d_doppler_step, freq_offset_hz_);
+        gb200_acq_set_doppler(h_, acq_parameters.doppler_max, d_doppler_step, freq_offset_hz_ + fdma_offset_hz_);
     }
     void set_local_code(std::complex<float>* code)  // (:239-274); `code` as the adapter built it (d_consumed_samples items, or N/2 with bit transition)
     {
         gr::thread::scoped_lock lock(d_setlock);
+        // FDMA (:242-248, is_fdma :277-293): the satellite's channel offset is added to every Doppler bin of the wipe-off grid
+        int64_t fdma = 0;
+        if (d_gnss_synchro && std::strcmp(d_gnss_synchro->Signal, "1G") == 0 && GLONASS_PRN.count(d_gnss_synchro->PRN)) fdma = DFRQ1_GLO * GLONASS_PRN.at(d_gnss_synchro->PRN);
+        if (d_gnss_synchro && std::strcmp(d_gnss_synchro->Signal, "2G") == 0 && GLONASS_PRN.count(d_gnss_synchro->PRN)) fdma = DFRQ2_GLO * GLONASS_PRN.at(d_gnss_synchro->PRN);
+        if (fdma != fdma_offset_hz_)
+            {
+                fdma_offset_hz_ = fdma;
+                gb200_acq_set_doppler(h_, acq_parameters.doppler_max, d_doppler_step, freq_offset_hz_ + fdma_offset_hz_);
+            }
         const size_t n = acq_parameters.bit_transition_flag ? gb200_acq_fft_size(h_) / 2 : gb200_acq_consumed_samples(h_);
         gb200_acq_set_local_code(h_, reinterpret_cast<const float*>(code), n);
     }
@@ -271,6 +282,7 @@ private:
     gb200_acq* h_ = nullptr;
     int stream_, item_type_;
     int64_t freq_offset_hz_;
+    int64_t fdma_offset_hz_ = 0;  // GLONASS channel offset of the satellite being searched (set_local_code)
     Acq_Conf acq_parameters;
     bool d_active = false, d_step_two = false;
     int32_t d_state = 0;

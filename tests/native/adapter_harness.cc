@@ -64,18 +64,18 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                     std::unique_ptr<Chan> c(new Chan());
                     std::unique_ptr<AcquisitionInterface> a = GetB200AcqBlock(config, acq_role, acq_impl, 1, 0);
                     std::unique_ptr<TrackingInterface> t = GetB200TrkBlock(config, trk_role, trk_impl, 1, 1);
-                    if (!a || !t) return -1;
+                    if (!a || (!t && !trk_impl.empty())) return -1;  // no Tracking_XX.implementation in the conf: acquisition only
                     c->acq = std::move(a);  // Channel keeps them as shared_ptr (channel.cc:45-52)
                     c->trk = std::move(t);
                     c->fsm = std::make_shared<ChannelFsm>();
                     // ---- Channel::Channel (channel.cc:60-104)
                     c->acq->set_channel(k);
                     c->acq->set_channel_fsm(c->fsm);
-                    c->trk->set_channel(k);
+                    if (c->trk) c->trk->set_channel(k);
                     c->syn = Gnss_Synchro();
                     c->syn.Channel_ID = k;
                     c->acq->set_gnss_synchro(&c->syn);
-                    c->trk->set_gnss_synchro(&c->syn);
+                    if (c->trk) c->trk->set_gnss_synchro(&c->syn);
                     uint32_t doppler_step = config->property("Acquisition_" + sig + std::to_string(k) + ".doppler_step", 0);
                     if (doppler_step == 0) doppler_step = config->property("Acquisition_" + sig + ".doppler_step", 500);
                     c->acq->set_doppler_step(doppler_step);
@@ -85,11 +85,11 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                     c->acq->init();
                     // ---- GNSSFlowgraph::connect: the blocks the channel exposes
                     c->acq_blk = dynamic_cast<gr::block*>(c->acq->get_left_block().get());
-                    c->trk_blk = dynamic_cast<gr::block*>(c->trk->get_left_block().get());
-                    if (!c->acq_blk || !c->trk_blk) return -2;
+                    c->trk_blk = c->trk ? dynamic_cast<gr::block*>(c->trk->get_left_block().get()) : nullptr;
+                    if (!c->acq_blk || (c->trk && !c->trk_blk)) return -2;
                     gr::top_block_sptr top = gr::make_top_block("harness");
                     c->acq->connect(top);
-                    c->trk->connect(top);
+                    if (c->trk) c->trk->connect(top);
                     // ---- Channel::set_signal (:208-226)
                     c->syn.System = system_signal[0];
                     std::memcpy(c->syn.Signal, sig.c_str(), 3);
@@ -105,8 +105,8 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                                 cp->first_acq_doppler = cp->syn.Acq_doppler_hz;
                                 cp->first_acq_stamp = cp->syn.Acq_samplestamp_samples;
                             }
-                        cp->trk->start_tracking();
-                        cp->tracking = true;
+                        if (cp->trk) cp->trk->start_tracking();
+                        cp->tracking = cp->trk != nullptr;
                     };
                     // ---- ChannelFsm::start_acquisition -> acq_->reset() (:203-206)
                     c->acq->reset();
@@ -121,9 +121,13 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
     const size_t isz = ch[0]->acq->item_size();
     const char* base = static_cast<const char*>(samples);
     // ---- scheduler: round robin; a block is offered at most chunk_items items per call from its own read position
+    // (a block may need a call that consumes nothing to change state -- pcps_acquisition moves from buffering to the search that way --
+    // so the loop ends only after a few rounds in which nobody consumed anything)
     bool progress = true;
-    while (progress)
+    int idle_rounds = 0;
+    while (idle_rounds < 4)
         {
+            idle_rounds = progress ? 0 : idle_rounds + 1;
             progress = false;
             for (auto& c : ch)
                 {
@@ -146,6 +150,7 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                                         progress = true;
                                     }
                         }
+                    if (!c->trk_blk) continue;
                     // tracking block: forecast() asks for 2 * vector_length items
                     gr_vector_int need(1, 0);
                     c->trk_blk->forecast(1, need);
@@ -194,7 +199,7 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                 }
             o[8] = c.loss_of_lock;
             o[11] = (double)c.acq->item_size();
-            o[12] = (double)c.trk->item_size();
+            o[12] = c.trk ? (double)c.trk->item_size() : 0.0;
         }
     ch.clear();
     B200Service::shutdown();

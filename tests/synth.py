@@ -65,8 +65,9 @@ def make_iq(fs, n, sats, seed, noise=True):
         x = np.zeros(n, np.complex128)
     t = np.arange(n, dtype=np.float64) / fs
     for s in sats:
-        tab = code_table(s["kind"], s["prn"]).astype(np.float64)
-        rate = TABLE_RATE[s["kind"]] * (1.0 + s["doppler_hz"] / CARRIER_HZ[s["kind"]])
+        # "table" (+ "table_rate", "carrier_hz"): a caller-supplied +-1 code table instead of a named one (signals without a golden table)
+        tab = np.asarray(s["table"], np.float64) if "table" in s else code_table(s["kind"], s["prn"]).astype(np.float64)
+        rate = (s["table_rate"] if "table" in s else TABLE_RATE[s["kind"]]) * (1.0 + s["doppler_hz"] / (s["carrier_hz"] if "table" in s else CARRIER_HZ[s["kind"]]))
         tau = s["delay_samples"] / fs
         pos = np.floor((t - tau) * rate).astype(np.int64)
         idx = pos % len(tab)

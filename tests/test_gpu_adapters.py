@@ -100,3 +100,128 @@ Tracking_1B.pll_filter_order=2
     bad.write_text(conf.read_text().replace("Galileo_E1_PCPS_Ambiguous_Acquisition_B200", "Galileo_E1_PCPS_Ambiguous_Acquisition"))
     rc, _, _ = run_receiver(str(bad), q, n, prns, b"E1B")
     assert rc == -1
+
+
+# ------------------------------------------------------------------------------------------------ table-driven adapters (b200_signal_adapters.*)
+def _conf(tmp_path, name, text):
+    p = tmp_path / name
+    p.write_text("[GNSS-SDR]\nGNSS-SDR.b200_batch_window_us=0\n" + text)
+    return str(p)
+
+
+def _check(out, sats, prns, n_code, dstep, min_epochs, dopp_tol=4.0, cn0_tol=None):
+    """cn0_tol None: only "above the lock detector's floor".  On signals with a secondary code the reference block's own CN0 estimate
+    sits 10-17 dB under the scene's (tests/test_ref_blocks_cpu.py::test_other_signals_mirror_equals_the_tracking_block holds the
+    mirror to the block there), so it is not compared with the truth."""
+    for k, s in enumerate(sats):
+        o = out[k]
+        want = (s["delay_samples"] - (o[4] - n_code)) % n_code
+        assert o[0] >= 1 and min(abs(o[2] - want), n_code - abs(o[2] - want)) <= 1.0, (k, o, want)
+        assert abs(o[3] - s["doppler_hz"]) <= dstep, (k, o[3])
+        if min_epochs:
+            assert o[8] == 0 and o[5] > min_epochs, (k, o)
+            assert abs(o[6] - s["doppler_hz"]) < dopp_tol, (k, o[6], s["doppler_hz"])
+            assert (abs(o[7] - s["cn0_dbhz"]) < cn0_tol) if cn0_tol else (o[7] > 25.0), (k, o[7])
+
+
+def test_gps_l5_adapters_from_the_signal_table(tmp_path):
+    """GPS_L5i_PCPS_Acquisition_B200 + GPS_L5_DLL_PLL_Tracking_B200 (BASELINE C3's signal) made by name through the factory: the L5i
+    adapter's keys and derivations (floor code length, samples_per_code from the period, per-channel pfa lookup) and the L5 tracker's
+    defaults; L5I data component with its 10-bit Neuman-Hofman code, 25 Msps gr_complex (C3's rate: 2.4 samples per chip, so the
+    one-sample ambiguity of the acquisition is inside the DLL's pull-in range), 0.3 s."""
+    conf = _conf(tmp_path, "l5.conf", """GNSS-SDR.internal_fs_sps=25000000
+Acquisition_L5.implementation=GPS_L5i_PCPS_Acquisition_B200
+Acquisition_L5.threshold=0.002
+Acquisition_L5.doppler_max=5000
+Acquisition_L5.doppler_step=250
+Tracking_L5.implementation=GPS_L5_DLL_PLL_Tracking_B200
+Tracking_L5.pll_bw_hz=30.0
+Tracking_L5.dll_bw_hz=2.0
+""")
+    prns = [3, 24]
+    sats = [dict(kind="gps_l5i", prn=p, cn0_dbhz=50 - 2 * k, doppler_hz=1520.0 - 2730.0 * k, delay_samples=2345 + 5001 * k, secondary="0000110101") for k, p in enumerate(prns)]
+    fs, n = 25e6, 7_500_000
+    x = synth.make_iq(fs, n, sats, 20260061)
+    rc, out, names = run_receiver(conf, x, n, prns, b"GL5", chunk=50000)
+    assert rc == 0 and names == "GPS_L5i_PCPS_Acquisition_B200 GPS_L5_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 25000, 250.0, 180)
+
+
+def test_galileo_e5a_adapters_from_the_signal_table(tmp_path):
+    """Galileo_E5a_Pcps_Acquisition_B200 + Galileo_E5a_DLL_PLL_Tracking_B200: the E5a adapter's own rules (sampled_ms fixed at 1,
+    first/second-peak statistic by default, code length recomputed with round(), "5I" replica) and the E5a tracker defaults
+    (PLL 20 Hz / DLL 20 Hz); E5a-I primary code from the reference generator (oracle/_ref) with the 20-bit secondary code."""
+    import oracle_lib as ol
+
+    R = ol.ref()
+    if R is None:
+        pytest.skip("oracle/_ref not built")
+    conf = _conf(tmp_path, "e5a.conf", """GNSS-SDR.internal_fs_sps=25000000
+Acquisition_5X.implementation=Galileo_E5a_Pcps_Acquisition_B200
+Acquisition_5X.threshold=2.5
+Acquisition_5X.doppler_max=5000
+Acquisition_5X.doppler_step=250
+Tracking_5X.implementation=Galileo_E5a_DLL_PLL_Tracking_B200
+Tracking_5X.dll_bw_hz=5.0
+""")
+    prns = [11, 30]
+    sats = []
+    for k, p in enumerate(prns):
+        c = np.zeros(2 * 10230, np.float32)
+        R.gbref_galileo_e5a_code_primary(c, p, b"5I")
+        sats.append(dict(kind="e5a_i", prn=p, table=c[0::2], table_rate=10.23e6, carrier_hz=1176.45e6, cn0_dbhz=51 - 2 * k, doppler_hz=-2243.0 + 3490.0 * k,  # within 7 Hz of a bin: a Costas loop on the 20-bit secondary code false-locks 25 Hz off otherwise
+                        
+                         delay_samples=777 + 6007 * k, secondary="10000100001011101001"))
+    fs, n = 25e6, 7_500_000
+    x = synth.make_iq(fs, n, sats, 20260062)
+    rc, out, names = run_receiver(conf, x, n, prns, b"E5X", chunk=50000)
+    assert rc == 0 and names == "Galileo_E5a_Pcps_Acquisition_B200 Galileo_E5a_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 25000, 250.0, 180)
+
+
+def test_beidou_b1i_adapters_from_the_signal_table(tmp_path):
+    """BEIDOU_B1I_PCPS_Acquisition_B200 + BEIDOU_B1I_DLL_PLL_Tracking_B200 (BASELINE C4's third constellation): the older adapter
+    layout (round() code length, samples_per_ms = samples_per_code = code length, Acq_Conf::ms_per_code left at its default), cbyte
+    items kept packed on the device; MEO satellites with the 20-bit Neuman-Hofman code."""
+    conf = _conf(tmp_path, "b1i.conf", """GNSS-SDR.internal_fs_sps=8000000
+Acquisition_B1.implementation=BEIDOU_B1I_PCPS_Acquisition_B200
+Acquisition_B1.item_type=cbyte
+Acquisition_B1.threshold=0.003
+Acquisition_B1.doppler_max=5000
+Acquisition_B1.doppler_step=250
+Tracking_B1.implementation=BEIDOU_B1I_DLL_PLL_Tracking_B200
+Tracking_B1.item_type=cbyte
+Tracking_B1.pll_bw_hz=30.0
+""")
+    prns = [8, 14]
+    sats = [dict(kind="bds_b1i", prn=p, cn0_dbhz=51 - 2 * k, doppler_hz=2480.0 - 3210.0 * k, delay_samples=1234 + 377 * k, secondary="00000100110101001110") for k, p in enumerate(prns)]
+    # (small code delays on purpose: with Acq_Conf::ms_per_code left at 0 the block zero-pads to twice the length and correlates linearly,
+    # so a satellite whose code starts late in the block overlaps the replica only partly -- the reference adapter's own sensitivity loss)
+    fs, n = 8e6, 4_000_000
+    x = synth.make_iq(fs, n, sats, 20260063)
+    q = synth.quantize(x, "8ic")
+    rc, out, names = run_receiver(conf, q, n, prns, b"CB1", chunk=16000)
+    assert rc == 0 and names == "BEIDOU_B1I_PCPS_Acquisition_B200 BEIDOU_B1I_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 8000, 250.0, 300)
+    assert out[0][11] == 2 and out[0][12] == 2  # item_size() of cbyte
+
+
+def test_glonass_l1_acquisition_adapter_adds_the_fdma_offset(tmp_path):
+    """GLONASS_L1_CA_PCPS_Acquisition_B200 (no Tracking_1G line: acquisition only): every satellite is searched on its own FDMA
+    channel -- the block reads Gnss_Synchro::Signal == "1G" and the slot's channel number (GLONASS_PRN) in set_local_code and adds
+    k * 562.5 kHz to every Doppler bin, as pcps_acquisition::is_fdma does."""
+    conf = _conf(tmp_path, "glo.conf", """GNSS-SDR.internal_fs_sps=8000000
+Acquisition_1G.implementation=GLONASS_L1_CA_PCPS_Acquisition_B200
+Acquisition_1G.threshold=0.003
+Acquisition_1G.doppler_max=5000
+Acquisition_1G.doppler_step=250
+""")
+    prns = [1, 2, 3]          # GLONASS_PRN: slots 1, 2, 3 -> channels 1, -4, 5
+    chans = [1, -4, 5]
+    sats = [dict(kind="glo_l1_ca", prn=1, cn0_dbhz=50 - k, doppler_hz=-1730.0 + 1500.0 * k, carrier_offset_hz=562500.0 * ch, delay_samples=431 + 2003 * k)
+            for k, ch in enumerate(chans)]
+    fs, n = 8e6, 400_000
+    x = synth.make_iq(fs, n, sats, 20260064)
+    rc, out, names = run_receiver(conf, x, n, prns, b"R1G", chunk=16000)
+    assert rc == 0 and names.strip() == "GLONASS_L1_CA_PCPS_Acquisition_B200", (rc, names)
+    _check(out, sats, prns, 8000, 250.0, 0)

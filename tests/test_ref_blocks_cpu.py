@@ -372,3 +372,53 @@ def test_loss_of_lock_and_telemetry_fault():
     assert len(lost) == 1 and 200 <= lost[0] <= 221
     assert_epochs_equal(ep[: lost[0]], er + er2, 199)
     assert len([e for e in ep[: lost[0]] if e["valid"]]) == len(er) + len(er2)
+
+
+@pytest.mark.parametrize("what", ["gps_l5i", "beidou_b1i", "galileo_e5a_i"])
+def test_other_signals_mirror_equals_the_tracking_block(what):
+    """The signals behind the table-driven adapters (gnss-sdr-1_b200/adapters/b200_signal_adapters.*): GPS L5 (data component, 10-bit
+    Neuman-Hofman code: secondary-code lock, then the state 3 / 4 cycle over the 10 symbols of a bit), BeiDou B1I (20-bit NH code) and
+    Galileo E5a-I (no secondary-code lock on the data component) with their adapters' default loop settings -- every epoch of the
+    mirror equal to the block's.  (The block's own CN0 estimate on these 50 dB-Hz scenes is 33-40 dB-Hz once it sums prompts over a
+    bit; the adapter tests on the GPU therefore do not compare CN0 with the scene's for these signals.)"""
+    if what == "gps_l5i":
+        fs, vlen, prn, sec = 12e6, 12000, 3, "0000110101"
+        code = synth.code_table("gps_l5i", prn)
+        sat = dict(kind="gps_l5i", prn=prn)
+        sig = dict(signal_carrier_freq=1176.45e6, code_chip_rate=10.23e6, code_length_chips=10230, secondary=1, symbols_per_bit=10, secondary_code=sec)
+        loop = dict(pll_bw_hz=50.0, dll_bw_hz=2.0, pll_bw_narrow_hz=2.0, dll_bw_narrow_hz=0.25, early_late_space_chips=0.5, early_late_space_narrow_chips=0.15,
+                    carrier_lock_th=0.75)
+        blk = dict(system=b"G", signal=b"L5")
+    elif what == "beidou_b1i":
+        fs, vlen, prn, sec = 8e6, 8000, 8, "00000100110101001110"
+        code = synth.code_table("bds_b1i", prn)
+        sat = dict(kind="bds_b1i", prn=prn)
+        sig = dict(signal_carrier_freq=1561.098e6, code_chip_rate=2.046e6, code_length_chips=2046, secondary=1, symbols_per_bit=20, secondary_code=sec)
+        loop = dict(pll_bw_hz=50.0, dll_bw_hz=2.0, pll_bw_narrow_hz=20.0, dll_bw_narrow_hz=2.0, early_late_space_chips=0.5, early_late_space_narrow_chips=0.5,
+                    carrier_lock_th=0.85)
+        blk = dict(system=b"C", signal=b"B1")
+    else:
+        R = ol.ref()
+        fs, vlen, prn, sec = 12e6, 12000, 11, "10000100001011101001"
+        c = np.zeros(2 * 10230, np.float32)
+        R.gbref_galileo_e5a_code_primary(c, prn, b"5I")
+        code = np.ascontiguousarray(c[0::2])
+        sat = dict(kind="e5a_i", prn=prn, table=code, table_rate=10.23e6, carrier_hz=1176.45e6)
+        sig = dict(signal_carrier_freq=1176.45e6, code_chip_rate=10.23e6, code_length_chips=10230, secondary=0, symbols_per_bit=20, secondary_code="")
+        loop = dict(pll_bw_hz=20.0, dll_bw_hz=20.0, pll_bw_narrow_hz=5.0, dll_bw_narrow_hz=2.0, early_late_space_chips=0.5, early_late_space_narrow_chips=0.15,
+                    carrier_lock_th=0.85)
+        blk = dict(system=b"E", signal=b"5X")
+    doppler, delay, n_ep = 1520.0, 2345, 260
+    x = synth.make_iq(fs, int((n_ep + 12) * vlen), [dict(cn0_dbhz=50.0, doppler_hz=doppler, delay_samples=delay, secondary=sec, **sat)], 20260071)
+    conf = hl.gps_l1_conf(fs_in=fs, vector_length=vlen, very_early_late_space_chips=0.0, very_early_late_space_narrow_chips=0.0, cn0_min=25.0, prn=prn,
+                          preamble_symbols=[], **sig, **loop)
+    ep = hl.run_oracle_channel(x, 0, conf, code, acq_delay=delay + 0.6, acq_doppler=doppler - 15.0, acq_stamp=0, n_steps=n_ep)
+    with quiet():
+        b = ol.RefTrkBlock(fs_in=fs, vector_length=vlen, very_early_late_space_chips=0.0, very_early_late_space_narrow_chips=0.0, cn0_min=25, **blk, **loop)
+        b.start(prn, delay + 0.6, doppler - 15.0, 0, 0)
+        er, ev = b.run(x, n_ep)
+        b.close()
+    assert ev == [] and assert_epochs_equal(ep, er, n_ep - 10) >= n_ep - 10
+    assert abs(np.mean([e.carrier_doppler_hz for e in er[-60:]]) - doppler) < 6.0
+    if what != "galileo_e5a_i":
+        assert {e.state_after for e in er} >= {2, 3} or {e.state_after for e in er} >= {2, 4}  # secondary-code lock was reached
