@@ -1,4 +1,5 @@
 #include "b200_block_factory.h"
+#include "b200_sibling_tracking_adapters.h"
 #include "b200_signal_adapters.h"
 #include "galileo_e1_dll_pll_veml_tracking_b200.h"
 #include "galileo_e1_pcps_ambiguous_acquisition_b200.h"
@@ -26,7 +27,7 @@ std::unique_ptr<TrackingInterface> GetB200TrkBlock(const std::shared_ptr<Configu
         return std::unique_ptr<TrackingInterface>(new GalileoE1DllPllVemlTrackingB200(configuration.get(), role, in_streams, out_streams));
     if (const B200TrkTraits* t = b200_trk_traits(implementation))  // GPS L5, Galileo E5a, BeiDou B1I
         return std::unique_ptr<TrackingInterface>(new B200DllPllTrackingAdapter(configuration.get(), role, in_streams, out_streams, *t));
-    return nullptr;
+    return GetB200SiblingTrkBlock(configuration.get(), role, implementation, in_streams, out_streams);  // GLONASS L1 C/A, carrier-aided and Kalman GPS L1 C/A trackers
 }
 
 std::unique_ptr<GNSSBlockInterface> GetB200Block(const std::shared_ptr<ConfigurationInterface>& configuration, const std::string& role,

@@ -154,7 +154,10 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                     // tracking block: forecast() asks for 2 * vector_length items
                     gr_vector_int need(1, 0);
                     c->trk_blk->forecast(1, need);
-                    if (n_items - c->trk_pos >= need[0])
+                    // A standby tracking block runs at full throttle in its own GNU Radio thread and stays at the head of the stream; here it
+                    // is called until it has caught up with its channel's acquisition block, so that start_tracking() never finds the
+                    // tracker's sample counter behind the acquisition stamp (gps_l1_ca_kf_tracking_cc subtracts the two as uint64_t).
+                    while (n_items - c->trk_pos >= need[0])
                         {
                             gr_vector_int ninput(1, (int)std::min<long long>(std::max(chunk_items, need[0]), n_items - c->trk_pos));
                             gr_vector_const_void_star in(1, base + isz * c->trk_pos);
@@ -173,6 +176,7 @@ int b200_adapter_receiver(const char* conf_path, const void* samples, long long 
                                         c->tracking = false;
                                         c->acq->reset();  // Event_failed_tracking_standby -> the flowgraph restarts the acquisition
                                     }
+                            if (c->tracking || c->trk_blk->gb_consumed == 0 || c->trk_pos >= c->acq_pos) break;
                         }
                 }
         }

@@ -225,3 +225,59 @@ Acquisition_1G.doppler_step=250
     rc, out, names = run_receiver(conf, x, n, prns, b"R1G", chunk=16000)
     assert rc == 0 and names.strip() == "GLONASS_L1_CA_PCPS_Acquisition_B200", (rc, names)
     _check(out, sats, prns, 8000, 250.0, 0)
+
+
+# ------------------------------------------------------------------------------------------------ the older per-signal trackers (b200_sibling_tracking*)
+@pytest.mark.parametrize("impl,item", [("GPS_L1_CA_KF_Tracking_B200", "gr_complex"), ("GPS_L1_CA_DLL_PLL_C_Aid_Tracking_B200", "gr_complex"),
+                                       ("GPS_L1_CA_DLL_PLL_C_Aid_Tracking_B200", "cshort")])
+def test_gps_l1_sibling_tracker_adapters(tmp_path, impl, item):
+    """GPS_L1_CA_KF_Tracking_B200 and GPS_L1_CA_DLL_PLL_C_Aid_Tracking_B200 (gr_complex -> the _cc loop, cshort -> the _sc loop on the
+    int16 correlator, as the reference adapter chooses) behind the GPS L1 acquisition adapter: made by name, configured by the
+    reference adapters' keys, one Gnss_Synchro per general_work, locked on the scene's Doppler."""
+    conf = _conf(tmp_path, "sib.conf", """GNSS-SDR.internal_fs_sps=4000000
+Acquisition_1C.implementation=GPS_L1_CA_PCPS_Acquisition_B200
+Acquisition_1C.item_type=%s
+Acquisition_1C.threshold=0.008
+Acquisition_1C.doppler_max=5000
+Acquisition_1C.doppler_step=250
+Tracking_1C.implementation=%s
+Tracking_1C.item_type=%s
+Tracking_1C.pll_bw_hz=35.0
+Tracking_1C.dll_bw_hz=2.0
+Tracking_1C.order=2
+""" % (item, impl, item))
+    prns = [5, 20]
+    sats = [dict(kind="gps_l1_ca", prn=p, cn0_dbhz=49 - k, doppler_hz=-1490.0 + 2755.0 * k, delay_samples=911 + 1501 * k) for k, p in enumerate(prns)]
+    fs, n = 4e6, 3_200_000  # 0.8 s
+    x = synth.make_iq(fs, n, sats, 20260081)
+    samples = x if item == "gr_complex" else np.ascontiguousarray(np.rint(np.stack([x.real, x.imag], -1) * 4.0).astype(np.int16).reshape(-1))
+    rc, out, names = run_receiver(conf, samples, n, prns, b"G1C")
+    assert rc == 0 and names == "GPS_L1_CA_PCPS_Acquisition_B200 " + impl, (rc, names)
+    # the Kalman tracker has no frequency pull-in aid: its Doppler state closes in over seconds, not within this 0.8 s stream
+    _check(out, sats, prns, 4000, 250.0, 500, dopp_tol=12.0 if "KF" in impl else 5.0, cn0_tol=6.0)
+    assert out[0][12] == (8 if item == "gr_complex" else 4)
+
+
+def test_glonass_l1_acquisition_and_tracking_adapters(tmp_path):
+    """GLONASS_L1_CA_PCPS_Acquisition_B200 + GLONASS_L1_CA_DLL_PLL_Tracking_B200 on three FDMA channels: the tracker takes the slot's
+    channel number from GLONASS_PRN and tracks carrier = Doppler + k * 562.5 kHz with the complex-code correlator."""
+    conf = _conf(tmp_path, "glo2.conf", """GNSS-SDR.internal_fs_sps=8000000
+Acquisition_1G.implementation=GLONASS_L1_CA_PCPS_Acquisition_B200
+Acquisition_1G.threshold=0.003
+Acquisition_1G.doppler_max=5000
+Acquisition_1G.doppler_step=250
+Tracking_1G.implementation=GLONASS_L1_CA_DLL_PLL_Tracking_B200
+Tracking_1G.pll_bw_hz=40.0
+Tracking_1G.dll_bw_hz=2.0
+""")
+    # slots 1, 11, 12 -> channels 1, 0, -1.  (On the far channels the reference's float32-accumulated wipe-off phase -- 2 rad per sample at
+    # k = -4 -- drifts enough to move the peak one 250 Hz bin; the engine reproduces that, tests/test_gpu_configs.py, and a tracker
+    # started 230 Hz off does not pull in, there or here.)
+    prns, chans = [1, 11, 12], [1, 0, -1]
+    sats = [dict(kind="glo_l1_ca", prn=1, cn0_dbhz=50 - k, doppler_hz=-1730.0 + 1500.0 * k, carrier_offset_hz=562500.0 * ch, delay_samples=431 + 2003 * k)
+            for k, ch in enumerate(chans)]
+    fs, n = 8e6, 4_000_000  # 0.5 s
+    x = synth.make_iq(fs, n, sats, 20260082)
+    rc, out, names = run_receiver(conf, x, n, prns, b"R1G", chunk=16000)
+    assert rc == 0 and names == "GLONASS_L1_CA_PCPS_Acquisition_B200 GLONASS_L1_CA_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 8000, 250.0, 300, dopp_tol=5.0, cn0_tol=6.0)
