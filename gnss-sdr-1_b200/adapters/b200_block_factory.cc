@@ -1,4 +1,5 @@
 #include "b200_block_factory.h"
+#include "b200_sibling_acquisition_adapters.h"
 #include "b200_sibling_tracking_adapters.h"
 #include "b200_signal_adapters.h"
 #include "galileo_e1_dll_pll_veml_tracking_b200.h"
@@ -15,7 +16,7 @@ std::unique_ptr<AcquisitionInterface> GetB200AcqBlock(const std::shared_ptr<Conf
         return std::unique_ptr<AcquisitionInterface>(new GalileoE1PcpsAmbiguousAcquisitionB200(configuration.get(), role, in_streams, out_streams));
     if (const B200AcqTraits* t = b200_acq_traits(implementation))  // GPS L5i, Galileo E5a, BeiDou B1I, GLONASS L1 C/A: one class, a table row each
         return std::unique_ptr<AcquisitionInterface>(new B200PcpsAcquisitionAdapter(configuration.get(), role, in_streams, out_streams, *t));
-    return nullptr;
+    return GetB200SiblingAcqBlock(configuration.get(), role, implementation, in_streams, out_streams);  // GPS L1 C/A Tong, QuickSync, fine-Doppler acquisitions
 }
 
 std::unique_ptr<TrackingInterface> GetB200TrkBlock(const std::shared_ptr<ConfigurationInterface>& configuration, const std::string& role,

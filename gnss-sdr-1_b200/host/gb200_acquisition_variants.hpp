@@ -535,6 +535,12 @@ public:
             }
         ok_ = ok_ && num_doppler_points_ > 0 && gb200_acq_set_doppler_grid(h_, num_doppler_points_, steps.data()) == GB200_OK;
     }
+    void set_doppler_max(unsigned int doppler_max)  // (:210-217 of the header: stored; the grid follows at the next set_doppler_step)
+    {
+        c_.doppler_max = doppler_max;
+        if (c_.doppler_step > 0) set_doppler_step(c_.doppler_step);
+    }
+    void init() {}  // (:208-219): only clears the Gnss_Synchro fields, which the caller owns here
     // = set_local_code (:190-195); the copy is what estimate_Doppler regenerates with gps_l1_ca_code_gen_complex_sampled (:415)
     bool set_local_code(const std::complex<float>* code, size_t n_items)
     {

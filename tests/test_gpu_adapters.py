@@ -281,3 +281,29 @@ Tracking_1G.dll_bw_hz=2.0
     rc, out, names = run_receiver(conf, x, n, prns, b"R1G", chunk=16000)
     assert rc == 0 and names == "GLONASS_L1_CA_PCPS_Acquisition_B200 GLONASS_L1_CA_DLL_PLL_Tracking_B200", (rc, names)
     _check(out, sats, prns, 8000, 250.0, 300, dopp_tol=5.0, cn0_tol=6.0)
+
+
+@pytest.mark.parametrize("impl,keys", [
+    ("GPS_L1_CA_PCPS_Tong_Acquisition_B200", "Acquisition_1C.threshold=0.008\nAcquisition_1C.tong_init_val=1\nAcquisition_1C.tong_max_val=2\n"),
+    ("GPS_L1_CA_PCPS_QuickSync_Acquisition_B200", "Acquisition_1C.threshold=0.1\nAcquisition_1C.folding_factor=2\nAcquisition_1C.coherent_integration_time_ms=4\n"),
+    ("GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200", "Acquisition_1C.threshold=2.5\nAcquisition_1C.max_dwells=2\n"),
+])
+def test_gps_l1_sibling_acquisition_adapters(tmp_path, impl, keys):
+    """The sibling GPS L1 C/A acquisition blocks as adapters made by name (Tong detector, QuickSync, fine Doppler), each handing over to
+    the GPS L1 DLL/PLL tracking adapter through the channel's Gnss_Synchro: right delay, Doppler within a bin (the fine-Doppler one
+    within 20 Hz), tracking locked for the rest of the stream."""
+    conf = _conf(tmp_path, "sibacq.conf", """GNSS-SDR.internal_fs_sps=4000000
+Acquisition_1C.implementation=%s
+Acquisition_1C.doppler_max=5000
+Acquisition_1C.doppler_step=250
+%sTracking_1C.implementation=GPS_L1_CA_DLL_PLL_Tracking_B200
+Tracking_1C.pll_bw_hz=35.0
+Tracking_1C.dll_bw_hz=2.0
+""" % (impl, keys))
+    prns = [5, 20]
+    sats = [dict(kind="gps_l1_ca", prn=p, cn0_dbhz=50 - k, doppler_hz=-1490.0 + 2755.0 * k, delay_samples=911 + 1501 * k) for k, p in enumerate(prns)]
+    fs, n = 4e6, 3_200_000  # 0.8 s
+    x = synth.make_iq(fs, n, sats, 20260083)
+    rc, out, names = run_receiver(conf, x, n, prns, b"G1C", chunk=65536)
+    assert rc == 0 and names == impl + " GPS_L1_CA_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 4000, 20.0 if "Fine" in impl else 250.0, 500, dopp_tol=5.0, cn0_tol=6.0)
