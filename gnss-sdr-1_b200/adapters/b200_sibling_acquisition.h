@@ -1,5 +1,6 @@
 // b200_sibling_acquisition<Policy>: ONE GNU Radio block template for the sibling PCPS acquisition blocks of the reference (each its
-// own gr::block there): pcps_tong_acquisition_cc, pcps_quicksync_acquisition_cc, pcps_acquisition_fine_doppler_cc.  The searches are
+// own gr::block there): pcps_tong_acquisition_cc, pcps_quicksync_acquisition_cc, pcps_acquisition_fine_doppler_cc,
+// galileo_pcps_8ms_acquisition_cc, galileo_e5a_noncoherentIQ_acquisition_caf_cc.  The searches are
 // the host mirrors of gnss-sdr-1_b200/host/ (each pinned to its block) on the shared B200 service; a Policy names the
 // mirror, its configuration and how many items one pass through the block's search state reads and consumes.  What the blocks
 // share is here: standby consumes whatever arrives, an active block waits for one whole search window, runs it, copies the result
@@ -30,6 +31,7 @@ struct B200TongPolicy
     static const char* name() { return "b200_pcps_tong_acquisition"; }
     static uint32_t window_items(const Conf& c) { return c.sampled_ms * static_cast<uint32_t>(c.samples_per_ms); }  // one dwell = one vector
     static uint32_t code_items(const Conf& c) { return window_items(c); }
+    static bool set_code(Mirror& m, const std::complex<float>* code, const std::complex<float>*, const Conf& c) { return m.set_local_code(code, code_items(c)); }
 };
 struct B200FineDopplerPolicy
 {
@@ -39,6 +41,25 @@ struct B200FineDopplerPolicy
     // one run() is the whole attempt: max_dwells grid dwells, then the 10 ms the fine estimate reads (pcps_acquisition_fine_doppler_cc.cc:543-578)
     static uint32_t window_items(const Conf& c) { return std::max<uint32_t>(c.max_dwells, 10u) * static_cast<uint32_t>(c.samples_per_ms); }
     static uint32_t code_items(const Conf& c) { return static_cast<uint32_t>(c.samples_per_ms); }
+    static bool set_code(Mirror& m, const std::complex<float>* code, const std::complex<float>*, const Conf& c) { return m.set_local_code(code, code_items(c)); }
+};
+struct B200Galileo8msPolicy
+{
+    using Conf = gb200::AcqVariantConf;
+    using Mirror = gb200::B200_Galileo_Pcps_8ms_Acquisition;
+    static const char* name() { return "b200_galileo_pcps_8ms_acquisition"; }
+    static uint32_t window_items(const Conf& c) { return c.sampled_ms * static_cast<uint32_t>(c.samples_per_ms); }
+    static uint32_t code_items(const Conf& c) { return window_items(c); }
+    static bool set_code(Mirror& m, const std::complex<float>* code, const std::complex<float>*, const Conf& c) { return m.set_local_code(code, code_items(c)); }
+};
+struct B200E5aCafPolicy
+{
+    using Conf = gb200::AcqVariantConf;
+    using Mirror = gb200::B200_Galileo_E5a_NoncoherentIQ_Acquisition_Caf;
+    static const char* name() { return "b200_galileo_e5a_noncoherent_iq_acquisition_caf"; }
+    static uint32_t window_items(const Conf& c) { return c.sampled_ms * static_cast<uint32_t>(c.samples_per_ms); }  // d_fft_size (:76)
+    static uint32_t code_items(const Conf& c) { return window_items(c); }
+    static bool set_code(Mirror& m, const std::complex<float>* codeI, const std::complex<float>* codeQ, const Conf& c) { return m.set_local_code(codeI, codeQ ? codeQ : codeI, code_items(c)); }
 };
 struct B200QuickSyncPolicy
 {
@@ -47,6 +68,7 @@ struct B200QuickSyncPolicy
     static const char* name() { return "b200_pcps_quicksync_acquisition"; }
     static uint32_t window_items(const Conf& c) { return c.sampled_ms * static_cast<uint32_t>(c.samples_per_ms); }
     static uint32_t code_items(const Conf& c) { return static_cast<uint32_t>(c.samples_per_code); }
+    static bool set_code(Mirror& m, const std::complex<float>* code, const std::complex<float>*, const Conf& c) { return m.set_local_code(code, code_items(c)); }
 };
 
 template <class Policy>
@@ -92,10 +114,10 @@ public:
             }
         mirror_->init();
     }
-    void set_local_code(std::complex<float>* code)
+    void set_local_code(std::complex<float>* code, std::complex<float>* code_q = nullptr)  // code_q: the E5a block's second replica
     {
         gr::thread::scoped_lock lock(d_setlock);
-        mirror_->set_local_code(code, Policy::code_items(conf_));
+        Policy::set_code(*mirror_, code, code_q, conf_);
     }
     void set_active(bool active)
     {

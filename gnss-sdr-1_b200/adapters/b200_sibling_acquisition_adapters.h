@@ -1,7 +1,9 @@
-// *_B200 adapters of the sibling GPS L1 C/A acquisition blocks, AcquisitionInterface implementations made by name:
+// *_B200 adapters of the sibling acquisition blocks, AcquisitionInterface implementations made by name:
 //   GPS_L1_CA_PCPS_Tong_Acquisition_B200           replaces GPS_L1_CA_PCPS_Tong_Acquisition           (gps_l1_ca_pcps_tong_acquisition.cc)
 //   GPS_L1_CA_PCPS_QuickSync_Acquisition_B200      replaces GPS_L1_CA_PCPS_QuickSync_Acquisition      (gps_l1_ca_pcps_quicksync_acquisition.cc)
 //   GPS_L1_CA_PCPS_Acquisition_Fine_Doppler_B200   replaces GPS_L1_CA_PCPS_Acquisition_Fine_Doppler   (gps_l1_ca_pcps_acquisition_fine_doppler.cc)
+//   Galileo_E1_PCPS_8ms_Ambiguous_Acquisition_B200 replaces Galileo_E1_PCPS_8ms_Ambiguous_Acquisition (galileo_e1_pcps_8ms_ambiguous_acquisition.cc)
+//   Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200 replaces Galileo_E5a_Noncoherent_IQ_Acquisition_CAF (galileo_e5a_noncoherent_iq_acquisition_caf.cc)
 // Same keys and defaults; gr_complex streams only, as in the reference adapters.
 #ifndef GNSS_SDR_B200_SIBLING_ACQUISITION_ADAPTERS_H
 #define GNSS_SDR_B200_SIBLING_ACQUISITION_ADAPTERS_H
@@ -22,7 +24,8 @@ public:
     // pfa_mode 0: no pfa key (fine Doppler); 1: role + channel + ".pfa" then role + ".pfa", cells = vector_length * inclusive bins (Tong);
     // 2: role + ".pfa", cells = (code_length / folding_factor) * inclusive bins (QuickSync)
     B200SiblingAcquisitionAdapter(ConfigurationInterface* configuration, const std::string& role, unsigned int in_streams, unsigned int out_streams,
-        const std::string& implementation, const typename Policy::Conf& conf, unsigned int code_length, unsigned int num_codes, int pfa_mode, unsigned int pfa_cells_per_bin);
+        const std::string& implementation, const typename Policy::Conf& conf, unsigned int code_length, unsigned int num_codes, int pfa_mode, unsigned int pfa_cells_per_bin,
+        int code_kind = 0, int zero_padding = 0);
     inline std::string role() override { return role_; }
     inline std::string implementation() override { return implementation_; }
     inline size_t item_size() override { return sizeof(std::complex<float>); }
@@ -74,6 +77,9 @@ private:
     int64_t fs_in_;
     unsigned int code_length_, num_codes_, channel_ = 0, doppler_max_, doppler_step_ = 0, pfa_cells_per_bin_;
     int pfa_mode_;
+    int code_kind_ = 0;  // 0: GPS L1 C/A generator, 1: galileo_e1_code_gen_complex_sampled, 2: Galileo E5a I (+ Q) replicas
+    int zero_padding_ = 0;
+    std::vector<std::complex<float>> code_q_;
     std::vector<std::complex<float>> code_;
     std::string role_, implementation_;
 };

@@ -202,6 +202,16 @@ public:
     bool ok() const { return ok_; }
     void set_gnss_synchro(AcqSynchro* p) { synchro_ = p; }
     void set_threshold(float t) { c_.threshold = t; }
+    void set_doppler_max(uint32_t v)
+    {
+        c_.doppler_max = v;
+        init();
+    }
+    void set_doppler_step(uint32_t v)
+    {
+        c_.doppler_step = v;
+        init();
+    }
     // = init() (galileo_pcps_8ms_acquisition_cc.cc:140-172): float(GALILEO_TWO_PI) * doppler / float(fs), all in float32
     void init()
     {
@@ -353,6 +363,16 @@ public:
     bool ok() const { return ok_; }
     void set_gnss_synchro(AcqSynchro* p) { synchro_ = p; }
     void set_threshold(float t) { c_.threshold = t; }
+    void set_doppler_max(uint32_t v)
+    {
+        c_.doppler_max = v;
+        init();
+    }
+    void set_doppler_step(uint32_t v)
+    {
+        c_.doppler_step = v;
+        init();
+    }
     // = init() (:275-331): GALILEO_TWO_PI (double) * doppler / float(fs), rounded once to float32
     void init()
     {

@@ -307,3 +307,71 @@ Tracking_1C.dll_bw_hz=2.0
     rc, out, names = run_receiver(conf, x, n, prns, b"G1C", chunk=65536)
     assert rc == 0 and names == impl + " GPS_L1_CA_DLL_PLL_Tracking_B200", (rc, names)
     _check(out, sats, prns, 4000, 20.0 if "Fine" in impl else 250.0, 500, dopp_tol=5.0, cn0_tol=6.0)
+
+
+def test_galileo_e1_8ms_acquisition_adapter(tmp_path):
+    """Galileo_E1_PCPS_8ms_Ambiguous_Acquisition_B200 (8 ms dwell, codes A and B searched in one batch, coherent_integration_time_ms a
+    multiple of 4) handing over to the Galileo E1 VEML tracking adapter."""
+    conf = _conf(tmp_path, "e1_8ms.conf", """GNSS-SDR.internal_fs_sps=4000000
+Acquisition_1B.implementation=Galileo_E1_PCPS_8ms_Ambiguous_Acquisition_B200
+Acquisition_1B.coherent_integration_time_ms=8
+Acquisition_1B.threshold=0.002
+Acquisition_1B.doppler_max=5000
+Acquisition_1B.doppler_step=125
+Tracking_1B.implementation=Galileo_E1_DLL_PLL_VEML_Tracking_B200
+Tracking_1B.track_pilot=true
+Tracking_1B.pll_bw_hz=15.0
+Tracking_1B.dll_bw_hz=2.0
+Tracking_1B.pll_filter_order=2
+""")
+    prns = [11, 19]
+    sats = [dict(kind="gal_e1b_sinboc", pilot_kind="gal_e1c_sinboc", prn=p, cn0_dbhz=50 - 2 * k, doppler_hz=1270.0 - 2875.0 * k, delay_samples=9123 + 3001 * k,
+                 secondary="0011100000001010110110010") for k, p in enumerate(prns)]
+    fs, n = 4e6, 2_800_000  # 0.7 s
+    x = synth.make_iq(fs, n, sats, 20260084)
+    rc, out, names = run_receiver(conf, x, n, prns, b"E1B", chunk=65536)
+    assert rc == 0 and names == "Galileo_E1_PCPS_8ms_Ambiguous_Acquisition_B200 Galileo_E1_DLL_PLL_VEML_Tracking_B200", (rc, names)
+    for k, s in enumerate(sats):
+        o = out[k]
+        want = (s["delay_samples"] - (o[4] - 32000)) % 16000
+        assert o[0] >= 1 and min(abs(o[2] - want), 16000 - abs(o[2] - want)) <= 1.0 and abs(o[3] - s["doppler_hz"]) <= 125.0, (k, o, want)
+        assert o[8] == 0 and o[5] > 120 and abs(o[6] - s["doppler_hz"]) < 3.0, (k, o)
+
+
+def test_galileo_e5a_noncoherent_iq_caf_acquisition_adapter(tmp_path):
+    """Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200 (I and Q replicas, non-coherent combination on the device, CAF window) in front of
+    the Galileo E5a tracking adapter; E5a-I + E5a-Q in quadrature from the reference generator (oracle/_ref)."""
+    import oracle_lib as ol
+
+    R = ol.ref()
+    if R is None:
+        pytest.skip("oracle/_ref not built")
+    conf = _conf(tmp_path, "e5a_caf.conf", """GNSS-SDR.internal_fs_sps=25000000
+Channel.signal=5X
+Acquisition_5X.implementation=Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200
+Acquisition_5X.threshold=0.001
+Acquisition_5X.doppler_max=5000
+Acquisition_5X.doppler_step=250
+Acquisition_5X.CAF_window_hz=0
+Acquisition_5X.max_dwells=1
+Tracking_5X.implementation=Galileo_E5a_DLL_PLL_Tracking_B200
+Tracking_5X.dll_bw_hz=5.0
+""")
+    prns = [11, 30]
+    fs, n = 25e6, 7_500_000
+    x = None
+    sats = []
+    for k, p in enumerate(prns):
+        ci = np.zeros(2 * 10230, np.float32)
+        cq = np.zeros(2 * 10230, np.float32)
+        R.gbref_galileo_e5a_code_primary(ci, p, b"5I")
+        R.gbref_galileo_e5a_code_primary(cq, p, b"5Q")
+        base = dict(prn=p, table_rate=10.23e6, carrier_hz=1176.45e6, cn0_dbhz=48 - 2 * k, doppler_hz=-2243.0 + 3490.0 * k, delay_samples=777 + 6007 * k)
+        s_i = dict(kind="e5a_i", table=ci[0::2], secondary="10000100001011101001", phase=0.0, **base)
+        s_q = dict(kind="e5a_q", table=cq[1::2], phase=np.pi / 2, **base)  # the pilot rides on the quadrature carrier
+        part = synth.make_iq(fs, n, [s_i, s_q], 20260085 + k, noise=(k == 0))
+        x = part if x is None else x + part
+        sats.append(dict(cn0_dbhz=51 - 2 * k, **{kk: base[kk] for kk in ("doppler_hz", "delay_samples")}))
+    rc, out, names = run_receiver(conf, np.ascontiguousarray(x, np.complex64), n, prns, b"E5X", chunk=50000)
+    assert rc == 0 and names == "Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200 Galileo_E5a_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 25000, 250.0, 180)
