@@ -195,6 +195,7 @@ private:
         : gr::block("b200_pcps_acquisition", gr::io_signature::make(1, 1, conf_.it_size), gr::io_signature::make(0, 0, conf_.it_size)),
           s_(service), stream_(stream_id), item_type_(item_type), freq_offset_hz_(freq_offset_hz), acq_parameters(conf_)
     {
+        if (acq_parameters.bit_transition_flag) acq_parameters.max_dwells = 1;  // (:113-117): the block's own copy, as pcps_acquisition's constructor leaves it
         this->message_port_register_out(pmt::mp("events"));
         gb200_acq_cfg c{};
         c.sampled_ms = conf_.sampled_ms;

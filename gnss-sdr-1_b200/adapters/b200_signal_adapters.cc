@@ -41,27 +41,28 @@ void gen_glo_l1(std::complex<float>* dst, const Gnss_Synchro&, int64_t fs, const
 
 // columns: implementation, replaces, code rate, code length, period ms, resampler target, default fs, default CFAR, reads sampled_ms,
 //          modern layout, final round(), sets ms_per_code, samples_per_code = length, blocking_on_standby key, dump_channel key,
-//          per-channel pfa, loop-counted bins, default dump file name, generator
+//          samples_per_chip in the older layout, per-channel pfa, loop-counted bins, default dump file name, generator
 const B200AcqTraits kAcq[] = {
     {"GPS_L5i_PCPS_Acquisition_B200", "GPS_L5i_PCPS_Acquisition", GPS_L5I_CODE_RATE_HZ, GPS_L5I_CODE_LENGTH_CHIPS, GPS_L5I_PERIOD * 1000.0, GPS_L5_OPT_ACQ_FS_HZ,
-        2048000, true, true, true, false, true, false, true, true, true, true, "./acquisition.mat", gen_l5i},
+        2048000, true, true, true, false, true, false, true, true, 0.0, true, true, "./acquisition.mat", gen_l5i},
     {"Galileo_E5a_Pcps_Acquisition_B200", "Galileo_E5a_Pcps_Acquisition", GALILEO_E5A_CODE_CHIP_RATE_HZ, GALILEO_E5A_CODE_LENGTH_CHIPS, GALILEO_E5A_CODE_PERIOD_MS,
-        GALILEO_E5A_OPT_ACQ_FS_HZ, 32000000, false, false, true, true, true, false, true, true, true, true, "./acquisition.mat", gen_e5a},
+        GALILEO_E5A_OPT_ACQ_FS_HZ, 32000000, false, false, true, true, true, false, true, true, 0.0, true, true, "./acquisition.mat", gen_e5a},
     {"BEIDOU_B1I_PCPS_Acquisition_B200", "BEIDOU_B1I_PCPS_Acquisition", BEIDOU_B1I_CODE_RATE_HZ, BEIDOU_B1I_CODE_LENGTH_CHIPS, 1.0, 0.0, 2048000, true, true, false,
-        false, false, true, false, false, false, false, "./data/acquisition.dat", gen_b1i},
+        false, false, true, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b1i},
     {"GLONASS_L1_CA_PCPS_Acquisition_B200", "GLONASS_L1_CA_PCPS_Acquisition", GLONASS_L1_CA_CODE_RATE_HZ, GLONASS_L1_CA_CODE_LENGTH_CHIPS,
-        GLONASS_L1_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, true, false, true, true, false, false, "./data/acquisition.dat", gen_glo_l1},
+        GLONASS_L1_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, true, false, true, true, GLONASS_L1_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l1},
 };
 
 // columns: implementation, replaces, name in warnings, system, signal, code rate, code length, pll_bw, dll_bw, pll_bw_narrow, dll_bw_narrow,
-//          early_late_space, early_late_space_narrow, cn0_min, carrier_lock_th, default fs, has pilot, data-component clamp
+//          early_late_space, early_late_space_narrow, cn0_min, carrier_lock_th, default fs, reads dump_mat / high_dyn / smoother_length, has pilot,
+//          data-component clamp
 const B200TrkTraits kTrk[] = {
     {"GPS_L5_DLL_PLL_Tracking_B200", "GPS_L5_DLL_PLL_Tracking", "GPS L5", 'G', "L5", GPS_L5I_CODE_RATE_HZ, GPS_L5I_CODE_LENGTH_CHIPS, 50.0, 2.0, 2.0, 0.25, 0.5, 0.15,
-        25, 0.75, 2048000, true, GPS_L5I_NH_CODE_LENGTH},  // gps_l5_dll_pll_tracking.cc:78-178
+        25, 0.75, 2048000, true, true, GPS_L5I_NH_CODE_LENGTH},  // gps_l5_dll_pll_tracking.cc:78-178
     {"Galileo_E5a_DLL_PLL_Tracking_B200", "Galileo_E5a_DLL_PLL_Tracking", "Galileo E5a", 'E', "5X", GALILEO_E5A_CODE_CHIP_RATE_HZ, GALILEO_E5A_CODE_LENGTH_CHIPS, 20.0,
-        20.0, 5.0, 2.0, 0.5, 0.15, 25, 0.85, 12000000, true, GALILEO_E5A_I_SECONDARY_CODE_LENGTH},  // galileo_e5a_dll_pll_tracking.cc:72-172
+        20.0, 5.0, 2.0, 0.5, 0.15, 25, 0.85, 12000000, true, true, GALILEO_E5A_I_SECONDARY_CODE_LENGTH},  // galileo_e5a_dll_pll_tracking.cc:72-172
     {"BEIDOU_B1I_DLL_PLL_Tracking_B200", "BEIDOU_B1I_DLL_PLL_Tracking", "BEIDOU B1I", 'C', "B1", BEIDOU_B1I_CODE_RATE_HZ, BEIDOU_B1I_CODE_LENGTH_CHIPS, 50.0, 2.0, 20.0,
-        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, 20},  // beidou_b1i_dll_pll_tracking.cc:60-160
+        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, 20},  // beidou_b1i_dll_pll_tracking.cc:60-160
 };
 }  // namespace
 
@@ -157,6 +158,8 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
             code_length_ = static_cast<unsigned int>(std::round(static_cast<double>(fs_in_) / code_period_hz));
             vector_length_ = code_length_ * acq_parameters_.sampled_ms;
             if (acq_parameters_.bit_transition_flag) vector_length_ *= 2;
+            if (t_.old_layout_chip_period_s > 0.0)
+                acq_parameters_.samples_per_chip = static_cast<unsigned int>(ceil(t_.old_layout_chip_period_s * static_cast<float>(acq_parameters_.fs_in)));
             if (t_.samples_per_code_is_length)
                 {
                     acq_parameters_.samples_per_ms = code_length_;
@@ -262,15 +265,18 @@ B200DllPllTrackingAdapter::B200DllPllTrackingAdapter(ConfigurationInterface* con
     trk_param.dump = configuration->property(role + ".dump", false);
     std::string default_dump_filename = "./track_ch";
     trk_param.dump_filename = configuration->property(role + ".dump_filename", default_dump_filename);
-    trk_param.dump_mat = configuration->property(role + ".dump_mat", true);
-    trk_param.high_dyn = configuration->property(role + ".high_dyn", false);
-    if (configuration->property(role + ".smoother_length", 10) < 1)
+    if (t_.reads_modern_keys)
         {
-            trk_param.smoother_length = 1;
-            std::cout << "WARNING: " << t_.what << ". smoother_length must be bigger than 0. It has been set to 1" << std::endl;
+            trk_param.dump_mat = configuration->property(role + ".dump_mat", true);
+            trk_param.high_dyn = configuration->property(role + ".high_dyn", false);
+            if (configuration->property(role + ".smoother_length", 10) < 1)
+                {
+                    trk_param.smoother_length = 1;
+                    std::cout << "WARNING: " << t_.what << ". smoother_length must be bigger than 0. It has been set to 1" << std::endl;
+                }
+            else
+                trk_param.smoother_length = configuration->property(role + ".smoother_length", 10);
         }
-    else
-        trk_param.smoother_length = configuration->property(role + ".smoother_length", 10);
     trk_param.pll_bw_hz = configuration->property(role + ".pll_bw_hz", t_.pll_bw_hz);
     trk_param.dll_bw_hz = configuration->property(role + ".dll_bw_hz", t_.dll_bw_hz);
     trk_param.pll_bw_narrow_hz = configuration->property(role + ".pll_bw_narrow_hz", t_.pll_bw_narrow_hz);

@@ -54,6 +54,8 @@ struct B200AcqTraits
     bool sets_ms_per_code;            // BeiDou B1I never assigns Acq_Conf::ms_per_code (stays at the struct's default)
     bool samples_per_code_is_length;  // BeiDou B1I: samples_per_code = code_length_ (:106)
     bool has_blocking_on_standby, has_dump_channel;
+    double old_layout_chip_period_s;  // older layout only: samples_per_chip = ceil(chip period * float(fs)) with the adapter's own chip-period constant
+                                      // (glonass_l1_ca_pcps_acquisition.cc:64, GLONASS_L1_CA_CHIP_PERIOD); 0: never assigned (BeiDou B1I)
     bool per_channel_pfa;             // role + channel + ".pfa" first (L5i, E5a)
     bool inclusive_loop_bins;         // calculate_threshold counts the bins with the for loop; else (2 max + step) / step
     const char* default_dump_filename;
@@ -130,6 +132,7 @@ struct B200TrkTraits
     int cn0_min;
     double carrier_lock_th;
     int default_fs;
+    bool reads_modern_keys;    // dump_mat, high_dyn, smoother_length are keys (beidou_b1i_dll_pll_tracking.cc reads none of them: Dll_Pll_Conf defaults)
     bool has_pilot;            // false: track_pilot is forced off with a warning and extend_correlation_symbols is clamped to [1, max_extend]
     int max_extend_data;       // clamp of extend_correlation_symbols when the data component is tracked
 };
