@@ -8,11 +8,15 @@
 #define GNSS_SDR_B200_DLL_PLL_VEML_TRACKING_H
 
 #include "Beidou_B1I.h"
+#include "Beidou_B3I.h"
+#include "GPS_L2C.h"
 #include "GPS_L1_CA.h"
 #include "GPS_L5.h"
 #include "Galileo_E1.h"
 #include "Galileo_E5a.h"
 #include "beidou_b1i_signal_processing.h"
+#include "beidou_b3i_signal_processing.h"
+#include "gps_l2c_signal.h"
 #include "dll_pll_conf.h"
 #include "galileo_e1_signal_processing.h"
 #include "galileo_e5_signal_processing.h"
@@ -73,6 +77,8 @@ public:
         bool have_data = false;
         if (trk_parameters.system == 'G' && sig == "1C")
             gps_l1_ca_code_gen_float(code.data(), syn.PRN, 0);
+        else if (trk_parameters.system == 'G' && sig == "2S")
+            gps_l2c_m_code_gen_float(code.data(), syn.PRN);  // (:586-589)
         else if (trk_parameters.system == 'G' && sig == "L5")
             {
                 if (trk_parameters.track_pilot)
@@ -121,6 +127,21 @@ public:
                 if (syn.PRN > 0 && syn.PRN < 6)
                     {
                         // GEO satellites (:630-667): no secondary code, D2 preamble of 11 bits x 2 symbols
+                        c.symbols_per_bit = 2;
+                        c.secondary = false;
+                        c.secondary_code.clear();
+                        c.preamble_symbols.clear();
+                        const int bits[11] = {1, 1, 1, 0, 0, 0, 1, 0, 0, 1, 0};
+                        for (int b : bits)
+                            for (int j = 0; j < 2; j++) c.preamble_symbols.push_back(b ? 1 : -1);
+                    }
+            }
+        else if (trk_parameters.system == 'C' && sig == "B3")
+            {
+                beidou_b3i_code_gen_float(code.data(), syn.PRN, 0);
+                if (syn.PRN > 0 && syn.PRN < 6)
+                    {
+                        // GEO satellites (:668-705): no secondary code, D2 preamble of 11 bits x 2 symbols
                         c.symbols_per_bit = 2;
                         c.secondary = false;
                         c.secondary_code.clear();
@@ -268,6 +289,17 @@ private:
                 for (uint16_t b : preambles_bits)
                     for (uint32_t j = 0; j < GPS_CA_TELEMETRY_SYMBOLS_PER_BIT; j++) c.preamble_symbols.push_back(b == 1 ? 1 : -1);
             }
+        else if (p.system == 'G' && sig == "2S")
+            {
+                // (:155-168): 20 ms code, no pilot, no secondary code
+                c.signal_carrier_freq = GPS_L2_FREQ_HZ;
+                c.code_period = GPS_L2_M_PERIOD;
+                c.code_chip_rate = GPS_L2_M_CODE_RATE_HZ;
+                c.code_length_chips = static_cast<int>(GPS_L2_M_CODE_LENGTH_CHIPS);
+                c.symbols_per_bit = GPS_L2_SAMPLES_PER_SYMBOL;
+                c.correlation_length_ms = 20;
+                c.track_pilot = false;
+            }
         else if (p.system == 'G' && sig == "L5")
             {
                 c.signal_carrier_freq = GPS_L5_FREQ_HZ;
@@ -315,6 +347,17 @@ private:
                 c.secondary = true;
                 c.track_pilot = false;
                 c.secondary_code = BEIDOU_B1I_SECONDARY_CODE_STR;
+            }
+        else if (p.system == 'C' && sig == "B3")
+            {
+                c.signal_carrier_freq = BEIDOU_B3I_FREQ_HZ;
+                c.code_period = BEIDOU_B3I_CODE_PERIOD;
+                c.code_chip_rate = BEIDOU_B3I_CODE_RATE_HZ;
+                c.code_length_chips = static_cast<int>(BEIDOU_B3I_CODE_LENGTH_CHIPS);
+                c.symbols_per_bit = BEIDOU_B3I_TELEMETRY_SYMBOLS_PER_BIT;
+                c.secondary = true;
+                c.track_pilot = false;
+                c.secondary_code = BEIDOU_B3I_SECONDARY_CODE_STR;
             }
     }
 

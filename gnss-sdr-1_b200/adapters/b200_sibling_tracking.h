@@ -1,6 +1,6 @@
 // b200_sibling_tracking<Policy>: ONE GNU Radio block template for the older per-signal trackers of the reference, each of which
 // is its own gr::block there:
-//   glonass_l1_ca_dll_pll_tracking_cc        (src/algorithms/tracking/gnuradio_blocks/glonass_l1_ca_dll_pll_tracking_cc.cc)
+//   glonass_l1_ca_dll_pll_tracking_cc, glonass_l2_ca_dll_pll_tracking_cc (src/algorithms/tracking/gnuradio_blocks/glonass_l{1,2}_ca_dll_pll_tracking_cc.cc)
 //   gps_l1_ca_dll_pll_c_aid_tracking_cc / _sc (.../gps_l1_ca_dll_pll_c_aid_tracking_cc.cc, _sc.cc)
 //   gps_l1_ca_kf_tracking_cc                 (.../gps_l1_ca_kf_tracking_cc.cc)
 // The loops are the host mirrors of gnss-sdr-1_b200/host/ (each pinned to its block) on the B200 correlators; a
@@ -13,6 +13,7 @@
 #include "GLONASS_L1_L2_CA.h"
 #include "GPS_L1_CA.h"
 #include "glonass_l1_signal_processing.h"
+#include "glonass_l2_signal_processing.h"
 #include "gnss_synchro.h"
 #include "gps_sdr_signal_processing.h"
 #include "host/gb200_c_aid_tracking.hpp"
@@ -50,6 +51,19 @@ struct B200GlonassL1Policy
     static void preamble(Loop&, double) {}
     static int consumed(const Epoch& e) { return e.prn_length_samples; }
     static int length_ms(const Epoch&) { return 1; }
+};
+
+struct B200GlonassL2Policy : B200GlonassL1Policy
+{
+    // glonass_l2_ca_dll_pll_tracking_cc.cc: the same loop with the L2 band constants (GlonassTrkConf::band_freq_hz / band_dfreq_hz) and generator
+    static const char* name() { return "b200_glonass_l2_ca_dll_pll_tracking"; }
+    static bool start(Loop& l, const Gnss_Synchro& syn)
+    {
+        std::vector<std::complex<float>> code(static_cast<size_t>(GLONASS_L2_CA_CODE_LENGTH_CHIPS));
+        glonass_l2_ca_code_gen_complex(code.data(), 0);
+        const int k = GLONASS_PRN.count(syn.PRN) ? GLONASS_PRN.at(syn.PRN) : 0;
+        return l.start_tracking(code.data(), k, syn.Acq_delay_samples, syn.Acq_doppler_hz, syn.Acq_samplestamp_samples);
+    }
 };
 
 template <class CorrT>

@@ -20,7 +20,8 @@ B200SiblingTrackingAdapter<Policy>::B200SiblingTrackingAdapter(ConfigurationInte
 std::unique_ptr<TrackingInterface> GetB200SiblingTrkBlock(ConfigurationInterface* configuration, const std::string& role, const std::string& implementation,
     unsigned int in_streams, unsigned int out_streams)
 {
-    const bool glo = implementation == "GLONASS_L1_CA_DLL_PLL_Tracking_B200", caid = implementation == "GPS_L1_CA_DLL_PLL_C_Aid_Tracking_B200",
+    const bool glo2 = implementation == "GLONASS_L2_CA_DLL_PLL_Tracking_B200";
+    const bool glo = implementation == "GLONASS_L1_CA_DLL_PLL_Tracking_B200" || glo2, caid = implementation == "GPS_L1_CA_DLL_PLL_C_Aid_Tracking_B200",
                kf = implementation == "GPS_L1_CA_KF_Tracking_B200";
     if (!glo && !caid && !kf) return nullptr;
     std::string default_item_type = "gr_complex";
@@ -37,6 +38,13 @@ std::unique_ptr<TrackingInterface> GetB200SiblingTrkBlock(ConfigurationInterface
             c.dll_bw_hz = configuration->property(role + ".dll_bw_hz", 2.0);
             c.early_late_space_chips = configuration->property(role + ".early_late_space_chips", 0.5);
             c.vector_length = std::round(fs_in / (GLONASS_L1_CA_CODE_RATE_HZ / GLONASS_L1_CA_CODE_LENGTH_CHIPS));
+            if (glo2)
+                {
+                    // glonass_l2_ca_dll_pll_tracking.cc: the same keys and defaults; the block uses the L2 band (GLONASS_L1_L2_CA.h:84-85)
+                    c.band_freq_hz = GLONASS_L2_CA_FREQ_HZ;
+                    c.band_dfreq_hz = GLONASS_L2_CA_DFREQ_HZ;
+                    return std::unique_ptr<TrackingInterface>(new B200SiblingTrackingAdapter<B200GlonassL2Policy>(configuration, role, in_streams, out_streams, implementation, c, wire));
+                }
             auto* a = new B200SiblingTrackingAdapter<B200GlonassL1Policy>(configuration, role, in_streams, out_streams, implementation, c, wire);
             return std::unique_ptr<TrackingInterface>(a);
         }

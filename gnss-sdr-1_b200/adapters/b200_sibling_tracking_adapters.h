@@ -1,5 +1,6 @@
 // *_B200 adapters of the older per-signal trackers, TrackingInterface implementations made by name:
 //   GLONASS_L1_CA_DLL_PLL_Tracking_B200         replaces GLONASS_L1_CA_DLL_PLL_Tracking        (glonass_l1_ca_dll_pll_tracking.cc)
+//   GLONASS_L2_CA_DLL_PLL_Tracking_B200         replaces GLONASS_L2_CA_DLL_PLL_Tracking        (glonass_l2_ca_dll_pll_tracking.cc)
 //   GPS_L1_CA_DLL_PLL_C_Aid_Tracking_B200       replaces GPS_L1_CA_DLL_PLL_C_Aid_Tracking      (gps_l1_ca_dll_pll_c_aid_tracking.cc; item_type
 //                                                gr_complex -> the _cc loop, cshort -> the _sc loop on the int16 correlator, as there)
 //   GPS_L1_CA_KF_Tracking_B200                  replaces GPS_L1_CA_KF_Tracking                 (gps_l1_ca_kf_tracking.cc)

@@ -3,11 +3,16 @@
 // The gflags overrides (FLAGS_doppler_max, FLAGS_pll_bw_hz, ...) are the receiver's command line and stay with the reference's main().
 #include "b200_signal_adapters.h"
 #include "Beidou_B1I.h"
+#include "Beidou_B3I.h"
+#include "GPS_L2C.h"
 #include "GLONASS_L1_L2_CA.h"
 #include "GPS_L5.h"
 #include "Galileo_E5a.h"
 #include "b200_service_singleton.h"
 #include "beidou_b1i_signal_processing.h"
+#include "beidou_b3i_signal_processing.h"
+#include "glonass_l2_signal_processing.h"
+#include "gps_l2c_signal.h"
 #include "configuration_interface.h"
 #include "galileo_e5_signal_processing.h"
 #include "glonass_l1_signal_processing.h"
@@ -39,30 +44,53 @@ void gen_glo_l1(std::complex<float>* dst, const Gnss_Synchro&, int64_t fs, const
     glonass_l1_ca_code_gen_complex_sampled(dst, static_cast<int32_t>(fs), 0);  // glonass_l1_ca_pcps_acquisition.cc:211 (one code for all satellites)
 }
 
+void gen_l2m(std::complex<float>* dst, const Gnss_Synchro& syn, int64_t fs, const B200AcqFlags&)
+{
+    gps_l2c_m_code_gen_complex_sampled(dst, syn.PRN, static_cast<int32_t>(fs));  // gps_l2_m_pcps_acquisition.cc:240-252
+}
+void gen_b3i(std::complex<float>* dst, const Gnss_Synchro& syn, int64_t fs, const B200AcqFlags&)
+{
+    beidou_b3i_code_gen_complex_sampled(dst, syn.PRN, static_cast<int32_t>(fs), 0);  // beidou_b3i_pcps_acquisition.cc:206
+}
+void gen_glo_l2(std::complex<float>* dst, const Gnss_Synchro&, int64_t fs, const B200AcqFlags&)
+{
+    glonass_l2_ca_code_gen_complex_sampled(dst, static_cast<int32_t>(fs), 0);  // glonass_l2_ca_pcps_acquisition.cc:210
+}
+
 // columns: implementation, replaces, code rate, code length, period ms, resampler target, default fs, default CFAR, reads sampled_ms,
-//          modern layout, final round(), sets ms_per_code, samples_per_code = length, blocking_on_standby key, dump_channel key,
+//          modern layout, final round(), ms_per_code, samples_per_code = length, blocking_on_standby key, dump_channel key,
 //          samples_per_chip in the older layout, per-channel pfa, loop-counted bins, default dump file name, generator
 const B200AcqTraits kAcq[] = {
     {"GPS_L5i_PCPS_Acquisition_B200", "GPS_L5i_PCPS_Acquisition", GPS_L5I_CODE_RATE_HZ, GPS_L5I_CODE_LENGTH_CHIPS, GPS_L5I_PERIOD * 1000.0, GPS_L5_OPT_ACQ_FS_HZ,
-        2048000, true, true, true, false, true, false, true, true, 0.0, true, true, "./acquisition.mat", gen_l5i},
+        2048000, true, true, true, false, 1, false, true, true, 0.0, true, true, "./acquisition.mat", gen_l5i},
+    {"GPS_L2_M_PCPS_Acquisition_B200", "GPS_L2_M_PCPS_Acquisition", GPS_L2_M_CODE_RATE_HZ, GPS_L2_M_CODE_LENGTH_CHIPS, GPS_L2_M_PERIOD * 1000.0, GPS_L2C_OPT_ACQ_FS_HZ,
+        2048000, true, true, true, false, 20, false, true, true, 0.0, true, true, "./acquisition.mat", gen_l2m},
     {"Galileo_E5a_Pcps_Acquisition_B200", "Galileo_E5a_Pcps_Acquisition", GALILEO_E5A_CODE_CHIP_RATE_HZ, GALILEO_E5A_CODE_LENGTH_CHIPS, GALILEO_E5A_CODE_PERIOD_MS,
-        GALILEO_E5A_OPT_ACQ_FS_HZ, 32000000, false, false, true, true, true, false, true, true, 0.0, true, true, "./acquisition.mat", gen_e5a},
+        GALILEO_E5A_OPT_ACQ_FS_HZ, 32000000, false, false, true, true, 1, false, true, true, 0.0, true, true, "./acquisition.mat", gen_e5a},
     {"BEIDOU_B1I_PCPS_Acquisition_B200", "BEIDOU_B1I_PCPS_Acquisition", BEIDOU_B1I_CODE_RATE_HZ, BEIDOU_B1I_CODE_LENGTH_CHIPS, 1.0, 0.0, 2048000, true, true, false,
-        false, false, true, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b1i},
+        false, 0, true, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b1i},
+    {"BEIDOU_B3I_PCPS_Acquisition_B200", "BEIDOU_B3I_PCPS_Acquisition", BEIDOU_B3I_CODE_RATE_HZ, BEIDOU_B3I_CODE_LENGTH_CHIPS, 1.0, 0.0, 2048000, true, true, false,
+        false, 0, true, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b3i},
     {"GLONASS_L1_CA_PCPS_Acquisition_B200", "GLONASS_L1_CA_PCPS_Acquisition", GLONASS_L1_CA_CODE_RATE_HZ, GLONASS_L1_CA_CODE_LENGTH_CHIPS,
-        GLONASS_L1_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, true, false, true, true, GLONASS_L1_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l1},
+        GLONASS_L1_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, 1, false, true, true, GLONASS_L1_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l1},
+    {"GLONASS_L2_CA_PCPS_Acquisition_B200", "GLONASS_L2_CA_PCPS_Acquisition", GLONASS_L2_CA_CODE_RATE_HZ, GLONASS_L2_CA_CODE_LENGTH_CHIPS,
+        GLONASS_L2_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, 1, false, true, true, GLONASS_L2_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l2},
 };
 
 // columns: implementation, replaces, name in warnings, system, signal, code rate, code length, pll_bw, dll_bw, pll_bw_narrow, dll_bw_narrow,
-//          early_late_space, early_late_space_narrow, cn0_min, carrier_lock_th, default fs, reads dump_mat / high_dyn / smoother_length, has pilot,
+//          early_late_space, early_late_space_narrow, cn0_min, carrier_lock_th, default fs, reads dump_mat, reads high_dyn + smoother_length, reads the narrow keys, extend mode, has pilot,
 //          data-component clamp
 const B200TrkTraits kTrk[] = {
     {"GPS_L5_DLL_PLL_Tracking_B200", "GPS_L5_DLL_PLL_Tracking", "GPS L5", 'G', "L5", GPS_L5I_CODE_RATE_HZ, GPS_L5I_CODE_LENGTH_CHIPS, 50.0, 2.0, 2.0, 0.25, 0.5, 0.15,
-        25, 0.75, 2048000, true, true, GPS_L5I_NH_CODE_LENGTH},  // gps_l5_dll_pll_tracking.cc:78-178
+        25, 0.75, 2048000, true, true, true, 0, true, GPS_L5I_NH_CODE_LENGTH},  // gps_l5_dll_pll_tracking.cc:78-178
+    {"GPS_L2_M_DLL_PLL_Tracking_B200", "GPS_L2_M_DLL_PLL_Tracking", "GPS L2", 'G', "2S", GPS_L2_M_CODE_RATE_HZ, GPS_L2_M_CODE_LENGTH_CHIPS, 2.0, 0.75, 0.0, 0.0, 0.5, 0.0,
+        25, 0.85, 2048000, true, false, false, 2, false, 1},  // gps_l2_m_dll_pll_tracking.cc:56-150 (narrow values assigned 0.0, not read)
     {"Galileo_E5a_DLL_PLL_Tracking_B200", "Galileo_E5a_DLL_PLL_Tracking", "Galileo E5a", 'E', "5X", GALILEO_E5A_CODE_CHIP_RATE_HZ, GALILEO_E5A_CODE_LENGTH_CHIPS, 20.0,
-        20.0, 5.0, 2.0, 0.5, 0.15, 25, 0.85, 12000000, true, true, GALILEO_E5A_I_SECONDARY_CODE_LENGTH},  // galileo_e5a_dll_pll_tracking.cc:72-172
+        20.0, 5.0, 2.0, 0.5, 0.15, 25, 0.85, 12000000, true, true, true, 0, true, GALILEO_E5A_I_SECONDARY_CODE_LENGTH},  // galileo_e5a_dll_pll_tracking.cc:72-172
     {"BEIDOU_B1I_DLL_PLL_Tracking_B200", "BEIDOU_B1I_DLL_PLL_Tracking", "BEIDOU B1I", 'C', "B1", BEIDOU_B1I_CODE_RATE_HZ, BEIDOU_B1I_CODE_LENGTH_CHIPS, 50.0, 2.0, 20.0,
-        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, 20},  // beidou_b1i_dll_pll_tracking.cc:60-160
+        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, true, 1, false, 20},  // beidou_b1i_dll_pll_tracking.cc:60-160
+    {"BEIDOU_B3I_DLL_PLL_Tracking_B200", "BEIDOU_B3I_DLL_PLL_Tracking", "BEIDOU B3I", 'C', "B3", BEIDOU_B3I_CODE_RATE_HZ, BEIDOU_B3I_CODE_LENGTH_CHIPS, 50.0, 2.0, 20.0,
+        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, true, 1, false, 20},  // beidou_b3i_dll_pll_tracking.cc:58-158
 };
 }  // namespace
 
@@ -100,13 +128,18 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
     acq_parameters_.blocking = configuration_->property(role + ".blocking", true);
     doppler_max_ = configuration_->property(role + ".doppler_max", 5000);
     acq_parameters_.doppler_max = doppler_max_;
-    acq_parameters_.sampled_ms = t_.reads_sampled_ms ? configuration_->property(role + ".coherent_integration_time_ms", 1) : 1;
+    acq_parameters_.sampled_ms = t_.reads_sampled_ms ? configuration_->property(role + ".coherent_integration_time_ms", std::max(1, t_.ms_per_code)) : 1;
+    if (t_.ms_per_code > 1 && (acq_parameters_.sampled_ms % t_.ms_per_code) != 0)
+        {
+            LOG(WARNING) << "Parameter coherent_integration_time_ms should be a multiple of " << t_.ms_per_code << ". Setting it to " << t_.ms_per_code;
+            acq_parameters_.sampled_ms = t_.ms_per_code;
+        }
     acq_parameters_.bit_transition_flag = configuration_->property(role + ".bit_transition_flag", false);
     acq_parameters_.use_CFAR_algorithm_flag = configuration_->property(role + ".use_CFAR_algorithm", t_.default_cfar);
     acq_parameters_.max_dwells = configuration_->property(role + ".max_dwells", 1);
     acq_parameters_.dump_filename = configuration_->property(role + ".dump_filename", default_dump_filename);
-    if (t_.sets_ms_per_code) acq_parameters_.ms_per_code = 1;
-    num_codes_ = acq_parameters_.sampled_ms;
+    if (t_.ms_per_code > 0) acq_parameters_.ms_per_code = t_.ms_per_code;
+    num_codes_ = acq_parameters_.sampled_ms / std::max(1, t_.ms_per_code);
     acq_parameters_.num_doppler_bins_step2 = configuration_->property(role + ".second_nbins", 4);
     acq_parameters_.doppler_step2 = configuration_->property(role + ".second_doppler_step", 125.0);
     acq_parameters_.make_2_steps = configuration_->property(role + ".make_two_steps", false);
@@ -265,9 +298,9 @@ B200DllPllTrackingAdapter::B200DllPllTrackingAdapter(ConfigurationInterface* con
     trk_param.dump = configuration->property(role + ".dump", false);
     std::string default_dump_filename = "./track_ch";
     trk_param.dump_filename = configuration->property(role + ".dump_filename", default_dump_filename);
-    if (t_.reads_modern_keys)
+    if (t_.reads_dump_mat) trk_param.dump_mat = configuration->property(role + ".dump_mat", true);
+    if (t_.reads_high_dyn)
         {
-            trk_param.dump_mat = configuration->property(role + ".dump_mat", true);
             trk_param.high_dyn = configuration->property(role + ".high_dyn", false);
             if (configuration->property(role + ".smoother_length", 10) < 1)
                 {
@@ -279,8 +312,16 @@ B200DllPllTrackingAdapter::B200DllPllTrackingAdapter(ConfigurationInterface* con
         }
     trk_param.pll_bw_hz = configuration->property(role + ".pll_bw_hz", t_.pll_bw_hz);
     trk_param.dll_bw_hz = configuration->property(role + ".dll_bw_hz", t_.dll_bw_hz);
-    trk_param.pll_bw_narrow_hz = configuration->property(role + ".pll_bw_narrow_hz", t_.pll_bw_narrow_hz);
-    trk_param.dll_bw_narrow_hz = configuration->property(role + ".dll_bw_narrow_hz", t_.dll_bw_narrow_hz);
+    if (t_.reads_narrow)
+        {
+            trk_param.pll_bw_narrow_hz = configuration->property(role + ".pll_bw_narrow_hz", t_.pll_bw_narrow_hz);
+            trk_param.dll_bw_narrow_hz = configuration->property(role + ".dll_bw_narrow_hz", t_.dll_bw_narrow_hz);
+        }
+    else
+        {
+            trk_param.pll_bw_narrow_hz = t_.pll_bw_narrow_hz;  // assigned, not read (gps_l2_m_dll_pll_tracking.cc:139-140: 0.0)
+            trk_param.dll_bw_narrow_hz = t_.dll_bw_narrow_hz;
+        }
     trk_param.early_late_space_chips = configuration->property(role + ".early_late_space_chips", t_.early_late_space_chips);
     int dll_filter_order = configuration->property(role + ".dll_filter_order", 2);
     if (dll_filter_order < 1)
@@ -313,14 +354,22 @@ B200DllPllTrackingAdapter::B200DllPllTrackingAdapter(ConfigurationInterface* con
     trk_param.pull_in_time_s = configuration->property(role + ".pull_in_time_s", 2.0);
     trk_param.vector_length = std::round(static_cast<double>(fs_in) / (t_.code_rate_hz / t_.code_length_chips));
     int extend_correlation_symbols = configuration->property(role + ".extend_correlation_symbols", 1);
-    trk_param.early_late_space_narrow_chips = configuration->property(role + ".early_late_space_narrow_chips", t_.early_late_space_narrow_chips);
+    trk_param.early_late_space_narrow_chips =
+        t_.reads_narrow ? configuration->property(role + ".early_late_space_narrow_chips", t_.early_late_space_narrow_chips) : t_.early_late_space_narrow_chips;  // (:79: 0.0)
     bool track_pilot = configuration->property(role + ".track_pilot", false);
-    if (extend_correlation_symbols < 1)
+    if (t_.extend_mode == 2)
+        {
+            // gps_l2_m_dll_pll_tracking.cc:113-118
+            if (extend_correlation_symbols != 1)
+                std::cout << "WARNING: Extended coherent integration is not allowed in " << t_.what << ". Coherent integration has been set to one code period (1 symbol)" << std::endl;
+            extend_correlation_symbols = 1;
+        }
+    else if (extend_correlation_symbols < 1)
         {
             extend_correlation_symbols = 1;
             std::cout << "WARNING: " << t_.what << ". extend_correlation_symbols must be bigger than 0. Coherent integration has been set to 1 symbol (1 ms)" << std::endl;
         }
-    else if ((!t_.has_pilot or !track_pilot) and extend_correlation_symbols > t_.max_extend_data)
+    else if ((t_.extend_mode == 1 or !track_pilot) and extend_correlation_symbols > t_.max_extend_data)
         {
             // gps_l5_dll_pll_tracking.cc:143-147 / galileo_e5a_dll_pll_tracking.cc:137-141 (data component only); beidou_b1i_dll_pll_tracking.cc:114-118 (always)
             extend_correlation_symbols = t_.max_extend_data;

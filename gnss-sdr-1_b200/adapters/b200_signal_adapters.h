@@ -15,6 +15,8 @@
 //   GPS_L5_DLL_PLL_Tracking_B200             GPS_L5_DLL_PLL_Tracking         gps_l5_dll_pll_tracking.cc
 //   Galileo_E5a_DLL_PLL_Tracking_B200        Galileo_E5a_DLL_PLL_Tracking    galileo_e5a_dll_pll_tracking.cc
 //   BEIDOU_B1I_DLL_PLL_Tracking_B200         BEIDOU_B1I_DLL_PLL_Tracking     beidou_b1i_dll_pll_tracking.cc
+//   GPS_L2_M_PCPS_Acquisition_B200, BEIDOU_B3I_PCPS_Acquisition_B200, GLONASS_L2_CA_PCPS_Acquisition_B200, GPS_L2_M_DLL_PLL_Tracking_B200,
+//   BEIDOU_B3I_DLL_PLL_Tracking_B200         (gps_l2_m_*, beidou_b3i_*, glonass_l2_ca_pcps_acquisition.cc)
 #ifndef GNSS_SDR_B200_SIGNAL_ADAPTERS_H
 #define GNSS_SDR_B200_SIGNAL_ADAPTERS_H
 
@@ -51,7 +53,8 @@ struct B200AcqTraits
     bool modern;                      // floor() code length + float samples_per_ms + dump_channel / blocking_on_standby keys; else the older
                                       // layout: round() code length, samples_per_ms = code_length, no resampler keys
     bool final_round_code_length;     // E5a recomputes code_length_ from fs_in with round() after the resampler branch (:123)
-    bool sets_ms_per_code;            // BeiDou B1I never assigns Acq_Conf::ms_per_code (stays at the struct's default)
+    int ms_per_code;                  // Acq_Conf::ms_per_code; 0: never assigned (BeiDou B1I / B3I: the struct's default stays).  > 1 (GPS L2C M: 20): it is also
+                                      // the default of coherent_integration_time_ms, which must be a multiple of it (gps_l2_m_pcps_acquisition.cc:81-87)
     bool samples_per_code_is_length;  // BeiDou B1I: samples_per_code = code_length_ (:106)
     bool has_blocking_on_standby, has_dump_channel;
     double old_layout_chip_period_s;  // older layout only: samples_per_chip = ceil(chip period * float(fs)) with the adapter's own chip-period constant
@@ -132,7 +135,11 @@ struct B200TrkTraits
     int cn0_min;
     double carrier_lock_th;
     int default_fs;
-    bool reads_modern_keys;    // dump_mat, high_dyn, smoother_length are keys (beidou_b1i_dll_pll_tracking.cc reads none of them: Dll_Pll_Conf defaults)
+    bool reads_dump_mat;       // .dump_mat is a key (the BeiDou adapters do not read it)
+    bool reads_high_dyn;       // .high_dyn and .smoother_length are keys (GPS L5, Galileo E5a; not GPS L2C, BeiDou)
+    bool reads_narrow;         // .pll_bw_narrow_hz, .dll_bw_narrow_hz, .early_late_space_narrow_chips are keys (not GPS L2C)
+    int extend_mode;           // extend_correlation_symbols: 0 clamp to max_extend_data only when the data component is tracked (L5, E5a); 1 clamp to
+                               // [1, max_extend_data] always (BeiDou); 2 forced to 1 with a warning (GPS L2C)
     bool has_pilot;            // false: track_pilot is forced off with a warning and extend_correlation_symbols is clamped to [1, max_extend]
     int max_extend_data;       // clamp of extend_correlation_symbols when the data component is tracked
 };

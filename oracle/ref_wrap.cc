@@ -13,6 +13,7 @@
 #include "cpu_multicorrelator_16sc.h"
 #include "cpu_multicorrelator_real_codes.h"
 #include "beidou_b1i_signal_processing.h"
+#include "beidou_b3i_signal_processing.h"
 #include "galileo_e1_signal_processing.h"
 #include "galileo_e5_signal_processing.h"
 #include "glonass_l1_signal_processing.h"
@@ -136,6 +137,7 @@ void gbref_galileo_e5a_code_sampled(float* dest_iq, const char* sig, unsigned pr
     galileo_e5_a_code_gen_complex_sampled(reinterpret_cast<std::complex<float>*>(dest_iq), s, prn, fs, chip_shift);
 }
 void gbref_beidou_b1i_code_float(float* dest, int prn, unsigned chip_shift) { beidou_b1i_code_gen_float(dest, prn, chip_shift); }
+void gbref_beidou_b3i_code_float(float* dest, int prn, unsigned chip_shift) { beidou_b3i_code_gen_float(dest, prn, chip_shift); }
 void gbref_beidou_b1i_code_sampled(float* dest_iq, unsigned prn, int fs, unsigned chip_shift) { beidou_b1i_code_gen_complex_sampled(reinterpret_cast<std::complex<float>*>(dest_iq), prn, fs, chip_shift); }
 void gbref_glonass_l1_ca_code(float* dest_iq, unsigned chip_shift) { glonass_l1_ca_code_gen_complex(reinterpret_cast<std::complex<float>*>(dest_iq), chip_shift); }
 void gbref_glonass_l1_ca_code_sampled(float* dest_iq, int fs, unsigned chip_shift) { glonass_l1_ca_code_gen_complex_sampled(reinterpret_cast<std::complex<float>*>(dest_iq), fs, chip_shift); }

@@ -4,6 +4,7 @@
 #include <ostream>
 struct gb_null_stream { template <class T> gb_null_stream& operator<<(const T&) { return *this; }
                         gb_null_stream& operator<<(std::ostream& (*)(std::ostream&)) { return *this; } };
+namespace google { class LogMessage {}; }  /* some reference files say `using google::LogMessage;` */
 #define LOG(x) gb_null_stream()
 #define DLOG(x) gb_null_stream()
 #endif

@@ -30,6 +30,8 @@
 #include "b200_signal_adapters.h"
 #include "beidou_b1i_dll_pll_tracking.h"
 #include "beidou_b1i_pcps_acquisition.h"
+#include "beidou_b3i_dll_pll_tracking.h"
+#include "beidou_b3i_pcps_acquisition.h"
 #include "file_configuration.h"
 #include "galileo_e1_dll_pll_veml_tracking.h"
 #include "galileo_e1_dll_pll_veml_tracking_b200.h"
@@ -38,10 +40,13 @@
 #include "galileo_e5a_dll_pll_tracking.h"
 #include "galileo_e5a_pcps_acquisition.h"
 #include "glonass_l1_ca_pcps_acquisition.h"
+#include "glonass_l2_ca_pcps_acquisition.h"
 #include "gps_l1_ca_dll_pll_tracking.h"
 #include "gps_l1_ca_dll_pll_tracking_b200.h"
 #include "gps_l1_ca_pcps_acquisition.h"
 #include "gps_l1_ca_pcps_acquisition_b200.h"
+#include "gps_l2_m_dll_pll_tracking.h"
+#include "gps_l2_m_pcps_acquisition.h"
 #include "gps_l5_dll_pll_tracking.h"
 #include "gps_l5i_pcps_acquisition.h"
 #undef private
@@ -153,6 +158,9 @@ int b200_adapter_conf_compare(const char* conf_path, int kind, const char* role_
                     if (ref_impl == "Galileo_E5a_Pcps_Acquisition") n_ref = ref_acq<GalileoE5aPcpsAcquisition>(config.get(), role, &syn, doppler_step, threshold, out_ref);
                     if (ref_impl == "BEIDOU_B1I_PCPS_Acquisition") n_ref = ref_acq<BeidouB1iPcpsAcquisition>(config.get(), role, &syn, doppler_step, threshold, out_ref);
                     if (ref_impl == "GLONASS_L1_CA_PCPS_Acquisition") n_ref = ref_acq<GlonassL1CaPcpsAcquisition>(config.get(), role, &syn, doppler_step, threshold, out_ref);
+                    if (ref_impl == "GLONASS_L2_CA_PCPS_Acquisition") n_ref = ref_acq<GlonassL2CaPcpsAcquisition>(config.get(), role, &syn, doppler_step, threshold, out_ref);
+                    if (ref_impl == "BEIDOU_B3I_PCPS_Acquisition") n_ref = ref_acq<BeidouB3iPcpsAcquisition>(config.get(), role, &syn, doppler_step, threshold, out_ref);
+                    if (ref_impl == "GPS_L2_M_PCPS_Acquisition") n_ref = ref_acq<GpsL2MPcpsAcquisition>(config.get(), role, &syn, doppler_step, threshold, out_ref);
                     if (getenv("GB_CC_TRACE")) fprintf(stderr, "cc: reference adapter done (%d values)\n", n_ref);
                     std::unique_ptr<AcquisitionInterface> b = GetB200AcqBlock(config, role, b200_impl, 1, 0);
                     if (getenv("GB_CC_TRACE")) fprintf(stderr, "cc: b200 adapter made %p\n", (void*)b.get());
@@ -174,6 +182,8 @@ int b200_adapter_conf_compare(const char* conf_path, int kind, const char* role_
                     if (ref_impl == "GPS_L5_DLL_PLL_Tracking") n_ref = ref_trk<GpsL5DllPllTracking>(config.get(), role, out_ref);
                     if (ref_impl == "Galileo_E5a_DLL_PLL_Tracking") n_ref = ref_trk<GalileoE5aDllPllTracking>(config.get(), role, out_ref);
                     if (ref_impl == "BEIDOU_B1I_DLL_PLL_Tracking") n_ref = ref_trk<BeidouB1iDllPllTracking>(config.get(), role, out_ref);
+                    if (ref_impl == "BEIDOU_B3I_DLL_PLL_Tracking") n_ref = ref_trk<BeidouB3iDllPllTracking>(config.get(), role, out_ref);
+                    if (ref_impl == "GPS_L2_M_DLL_PLL_Tracking") n_ref = ref_trk<GpsL2MDllPllTracking>(config.get(), role, out_ref);
                     std::unique_ptr<TrackingInterface> b = GetB200TrkBlock(config, role, b200_impl, 1, 1);
                     if (!b) return -2;
                     if (auto* g = dynamic_cast<GpsL1CaDllPllTrackingB200*>(b.get())) n_b = flatten(g->tracking_->trk_parameters, g->item_size(), out_b200);

@@ -27,10 +27,12 @@ TRK_FIELDS = ("fs_in", "vector_length", "dump", "dump_mat", "pll_bw_hz", "dll_bw
 ACQ = [  # (role, reference implementation)
     ("Acquisition_1C", "GPS_L1_CA_PCPS_Acquisition"), ("Acquisition_1B", "Galileo_E1_PCPS_Ambiguous_Acquisition"), ("Acquisition_L5", "GPS_L5i_PCPS_Acquisition"),
     ("Acquisition_5X", "Galileo_E5a_Pcps_Acquisition"), ("Acquisition_B1", "BEIDOU_B1I_PCPS_Acquisition"), ("Acquisition_1G", "GLONASS_L1_CA_PCPS_Acquisition"),
+    ("Acquisition_2S", "GPS_L2_M_PCPS_Acquisition"), ("Acquisition_B3", "BEIDOU_B3I_PCPS_Acquisition"), ("Acquisition_2G", "GLONASS_L2_CA_PCPS_Acquisition"),
 ]
 TRK = [
     ("Tracking_1C", "GPS_L1_CA_DLL_PLL_Tracking"), ("Tracking_1B", "Galileo_E1_DLL_PLL_VEML_Tracking"), ("Tracking_L5", "GPS_L5_DLL_PLL_Tracking"),
-    ("Tracking_5X", "Galileo_E5a_DLL_PLL_Tracking"), ("Tracking_B1", "BEIDOU_B1I_DLL_PLL_Tracking"),
+    ("Tracking_5X", "Galileo_E5a_DLL_PLL_Tracking"), ("Tracking_B1", "BEIDOU_B1I_DLL_PLL_Tracking"), ("Tracking_2S", "GPS_L2_M_DLL_PLL_Tracking"),
+    ("Tracking_B3", "BEIDOU_B3I_DLL_PLL_Tracking"),
 ]
 ACQ_VARIANTS = {
     "defaults": "",
@@ -73,8 +75,10 @@ def compare(tmp_path, kind, role, ref_impl, body, fs):
 @pytest.mark.parametrize("role,ref_impl", ACQ)
 def test_acquisition_adapter_derives_the_reference_adapters_acq_conf(tmp_path, role, ref_impl, variant):
     fs = {"resampler": 20_000_000, "odd rate": 6_625_000}.get(variant, 8_000_000)
-    if ref_impl.startswith(("Galileo_E5a", "GPS_L5")) and fs < 12_000_000:
+    if ref_impl.startswith(("Galileo_E5a", "GPS_L5", "BEIDOU_B3I")) and fs < 12_000_000:
         fs = 25_000_000
+    if ref_impl.startswith("GPS_L2_M"):
+        fs = min(fs, 4_000_000)  # 20 ms of code per dwell: keep the reference block's wipe-off tables small
     ref, got = compare(tmp_path, 0, role, ref_impl, ACQ_VARIANTS[variant], fs)
     assert len(ref) == len(ACQ_FIELDS)
     for name, r, g in zip(ACQ_FIELDS, ref, got):
@@ -86,7 +90,7 @@ def test_acquisition_adapter_derives_the_reference_adapters_acq_conf(tmp_path, r
 @pytest.mark.parametrize("variant", list(TRK_VARIANTS))
 @pytest.mark.parametrize("role,ref_impl", TRK)
 def test_tracking_adapter_derives_the_reference_adapters_dll_pll_conf(tmp_path, role, ref_impl, variant):
-    fs = 25_000_000 if ref_impl.startswith(("Galileo_E5a", "GPS_L5")) else 8_000_000
+    fs = 25_000_000 if ref_impl.startswith(("Galileo_E5a", "GPS_L5", "BEIDOU_B3I")) else 8_000_000
     ref, got = compare(tmp_path, 1, role, ref_impl, TRK_VARIANTS[variant], fs)
     assert len(ref) == len(TRK_FIELDS)
     for name, r, g in zip(TRK_FIELDS, ref, got):

@@ -375,3 +375,80 @@ Tracking_5X.dll_bw_hz=5.0
     rc, out, names = run_receiver(conf, np.ascontiguousarray(x, np.complex64), n, prns, b"E5X", chunk=50000)
     assert rc == 0 and names == "Galileo_E5a_Noncoherent_IQ_Acquisition_CAF_B200 Galileo_E5a_DLL_PLL_Tracking_B200", (rc, names)
     _check(out, sats, prns, 25000, 250.0, 180)
+
+
+def _ref_table(fn_name, prn, length, *extra):
+    import oracle_lib as ol
+
+    R = ol.ref()
+    if R is None:
+        pytest.skip("oracle/_ref not built")
+    fn = getattr(R, fn_name)
+    fn.argtypes = [np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")] + [C.c_int if fn_name.startswith("gbref_beidou") else C.c_uint] + [C.c_uint] * len(extra)
+    fn.restype = None
+    c = np.zeros(length, np.float32)
+    fn(c, prn, *extra)
+    return c
+
+
+def test_gps_l2c_adapters_from_the_signal_table(tmp_path):
+    """GPS_L2_M_PCPS_Acquisition_B200 + GPS_L2_M_DLL_PLL_Tracking_B200: 20 ms code (ms_per_code = 20 is also the default dwell), 80000-point
+    search at 4 Msps, 20 ms tracking epochs without secondary code; L2 CM code from the reference generator (oracle/_ref)."""
+    conf = _conf(tmp_path, "l2c.conf", """GNSS-SDR.internal_fs_sps=4000000
+Acquisition_2S.implementation=GPS_L2_M_PCPS_Acquisition_B200
+Acquisition_2S.threshold=0.0008
+Acquisition_2S.doppler_max=2000
+Acquisition_2S.doppler_step=25
+Tracking_2S.implementation=GPS_L2_M_DLL_PLL_Tracking_B200
+Tracking_2S.pll_bw_hz=4.0
+Tracking_2S.dll_bw_hz=0.75
+""")
+    prns = [7, 15]
+    sats = [dict(kind="l2cm", prn=p, table=_ref_table("gbref_gps_l2c_m_code_float", p, 10230), table_rate=0.5115e6, carrier_hz=1227.6e6, cn0_dbhz=44 - 2 * k,
+                 doppler_hz=-1004.0 + 1530.0 * k, delay_samples=31234 + 20011 * k) for k, p in enumerate(prns)]  # within 4 Hz of a 25 Hz bin: a 20 ms PLL pulls in +-12 Hz
+    fs, n = 4e6, 6_000_000  # 1.5 s
+    x = synth.make_iq(fs, n, sats, 20260091)
+    rc, out, names = run_receiver(conf, x, n, prns, b"G2S", chunk=160000)
+    assert rc == 0 and names == "GPS_L2_M_PCPS_Acquisition_B200 GPS_L2_M_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 80000, 25.0, 40, dopp_tol=3.0)
+
+
+def test_beidou_b3i_adapters_from_the_signal_table(tmp_path):
+    """BEIDOU_B3I_PCPS_Acquisition_B200 + BEIDOU_B3I_DLL_PLL_Tracking_B200 at 25 Msps (10.23 Mcps code, 20-bit Neuman-Hofman code)."""
+    conf = _conf(tmp_path, "b3i.conf", """GNSS-SDR.internal_fs_sps=25000000
+Acquisition_B3.implementation=BEIDOU_B3I_PCPS_Acquisition_B200
+Acquisition_B3.threshold=0.0012
+Acquisition_B3.doppler_max=5000
+Acquisition_B3.doppler_step=250
+Tracking_B3.implementation=BEIDOU_B3I_DLL_PLL_Tracking_B200
+Tracking_B3.pll_bw_hz=30.0
+""")
+    prns = [8, 14]
+    sats = [dict(kind="b3i", prn=p, table=_ref_table("gbref_beidou_b3i_code_float", p, 10230, 0), table_rate=10.23e6, carrier_hz=1268.52e6, cn0_dbhz=54 - 2 * k,
+                 doppler_hz=2480.0 - 3210.0 * k, delay_samples=1234 + 977 * k, secondary="00000100110101001110") for k, p in enumerate(prns)]
+    fs, n = 25e6, 7_500_000
+    x = synth.make_iq(fs, n, sats, 20260092)
+    rc, out, names = run_receiver(conf, x, n, prns, b"CB3", chunk=50000)
+    assert rc == 0 and names == "BEIDOU_B3I_PCPS_Acquisition_B200 BEIDOU_B3I_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 25000, 250.0, 180)
+
+
+def test_glonass_l2_acquisition_and_tracking_adapters(tmp_path):
+    """GLONASS_L2_CA_PCPS_Acquisition_B200 + GLONASS_L2_CA_DLL_PLL_Tracking_B200: signal "2G", channel spacing 437.5 kHz (DFRQ2_GLO)."""
+    conf = _conf(tmp_path, "glo_l2.conf", """GNSS-SDR.internal_fs_sps=8000000
+Acquisition_2G.implementation=GLONASS_L2_CA_PCPS_Acquisition_B200
+Acquisition_2G.threshold=0.003
+Acquisition_2G.doppler_max=5000
+Acquisition_2G.doppler_step=250
+Tracking_2G.implementation=GLONASS_L2_CA_DLL_PLL_Tracking_B200
+Tracking_2G.pll_bw_hz=40.0
+Tracking_2G.dll_bw_hz=2.0
+""")
+    prns, chans = [1, 11, 12], [1, 0, -1]
+    sats = [dict(kind="glo_l1_ca", prn=1, cn0_dbhz=50 - k, doppler_hz=-1730.0 + 1500.0 * k, carrier_offset_hz=437500.0 * ch, delay_samples=431 + 2003 * k)
+            for k, ch in enumerate(chans)]  # the L2 C/A code is the L1 C/A code
+    fs, n = 8e6, 4_000_000
+    x = synth.make_iq(fs, n, sats, 20260093)
+    rc, out, names = run_receiver(conf, x, n, prns, b"R2G", chunk=16000)
+    assert rc == 0 and names == "GLONASS_L2_CA_PCPS_Acquisition_B200 GLONASS_L2_CA_DLL_PLL_Tracking_B200", (rc, names)
+    _check(out, sats, prns, 8000, 250.0, 300, dopp_tol=5.0, cn0_tol=6.0)
