@@ -4,7 +4,11 @@
 #include "b200_signal_adapters.h"
 #include "Beidou_B1I.h"
 #include "Beidou_B3I.h"
+#include "GPS_L1_CA.h"
 #include "GPS_L2C.h"
+#include "Galileo_E1.h"
+#include "galileo_e1_signal_processing.h"
+#include "gps_sdr_signal_processing.h"
 #include "GLONASS_L1_L2_CA.h"
 #include "GPS_L5.h"
 #include "Galileo_E5a.h"
@@ -25,6 +29,18 @@
 // ------------------------------------------------------------------------------------------------ the signal tables
 namespace
 {
+void gen_l1ca(std::complex<float>* dst, const Gnss_Synchro& syn, int64_t fs, const B200AcqFlags&)
+{
+    gps_l1_ca_code_gen_complex_sampled(dst, syn.PRN, static_cast<int32_t>(fs), 0);  // gps_l1_ca_pcps_acquisition.cc:227-247
+}
+void gen_e1(std::complex<float>* dst, const Gnss_Synchro& syn, int64_t fs, const B200AcqFlags& f)
+{
+    // galileo_e1_pcps_ambiguous_acquisition.cc:240-282: the pilot replica on request, else the channel's own signal ("1B")
+    char signal_[3];
+    std::memcpy(signal_, f.acquire_pilot ? "1C" : syn.Signal, 3);
+    signal_[2] = 0;
+    galileo_e1_code_gen_complex_sampled(dst, signal_, f.cboc, syn.PRN, static_cast<int32_t>(fs), 0, false);
+}
 void gen_l5i(std::complex<float>* dst, const Gnss_Synchro& syn, int64_t fs, const B200AcqFlags&)
 {
     gps_l5i_code_gen_complex_sampled(dst, syn.PRN, static_cast<int32_t>(fs));  // gps_l5i_pcps_acquisition.cc:237-252
@@ -59,38 +75,47 @@ void gen_glo_l2(std::complex<float>* dst, const Gnss_Synchro&, int64_t fs, const
 
 // columns: implementation, replaces, code rate, code length, period ms, resampler target, default fs, default CFAR, reads sampled_ms,
 //          modern layout, final round(), ms_per_code, samples_per_code = length, blocking_on_standby key, dump_channel key,
-//          samples_per_chip in the older layout, per-channel pfa, loop-counted bins, default dump file name, generator
+//          chip period of the modern samples_per_chip (0: 1 / rate), vector length from the requested ms, resampled_fs left 0, samples_per_chip in the older layout,
+//          per-channel pfa, loop-counted bins, default dump file name, generator
 const B200AcqTraits kAcq[] = {
+    {"GPS_L1_CA_PCPS_Acquisition_B200", "GPS_L1_CA_PCPS_Acquisition", GPS_L1_CA_CODE_RATE_HZ, GPS_L1_CA_CODE_LENGTH_CHIPS, GPS_L1_CA_CODE_PERIOD * 1000.0, GPS_L1_CA_OPT_ACQ_FS_HZ,
+        2048000, true, true, true, false, 1, false, true, true, GPS_L1_CA_CHIP_PERIOD, false, false, 0.0, false, true, "./acquisition.mat", gen_l1ca},
+    {"Galileo_E1_PCPS_Ambiguous_Acquisition_B200", "Galileo_E1_PCPS_Ambiguous_Acquisition", GALILEO_E1_CODE_CHIP_RATE_HZ, GALILEO_E1_B_CODE_LENGTH_CHIPS,
+        GALILEO_E1_CODE_PERIOD_MS, GALILEO_E1_OPT_ACQ_FS_HZ, 4000000, true, true, true, false, 4, false, true, true, 0.0, true, true, 0.0, true, true, "./acquisition.mat", gen_e1},
     {"GPS_L5i_PCPS_Acquisition_B200", "GPS_L5i_PCPS_Acquisition", GPS_L5I_CODE_RATE_HZ, GPS_L5I_CODE_LENGTH_CHIPS, GPS_L5I_PERIOD * 1000.0, GPS_L5_OPT_ACQ_FS_HZ,
-        2048000, true, true, true, false, 1, false, true, true, 0.0, true, true, "./acquisition.mat", gen_l5i},
+        2048000, true, true, true, false, 1, false, true, true, 0.0, false, false, 0.0, true, true, "./acquisition.mat", gen_l5i},
     {"GPS_L2_M_PCPS_Acquisition_B200", "GPS_L2_M_PCPS_Acquisition", GPS_L2_M_CODE_RATE_HZ, GPS_L2_M_CODE_LENGTH_CHIPS, GPS_L2_M_PERIOD * 1000.0, GPS_L2C_OPT_ACQ_FS_HZ,
-        2048000, true, true, true, false, 20, false, true, true, 0.0, true, true, "./acquisition.mat", gen_l2m},
+        2048000, true, true, true, false, 20, false, true, true, 0.0, false, false, 0.0, true, true, "./acquisition.mat", gen_l2m},
     {"Galileo_E5a_Pcps_Acquisition_B200", "Galileo_E5a_Pcps_Acquisition", GALILEO_E5A_CODE_CHIP_RATE_HZ, GALILEO_E5A_CODE_LENGTH_CHIPS, GALILEO_E5A_CODE_PERIOD_MS,
-        GALILEO_E5A_OPT_ACQ_FS_HZ, 32000000, false, false, true, true, 1, false, true, true, 0.0, true, true, "./acquisition.mat", gen_e5a},
+        GALILEO_E5A_OPT_ACQ_FS_HZ, 32000000, false, false, true, true, 1, false, true, true, 0.0, false, false, 0.0, true, true, "./acquisition.mat", gen_e5a},
     {"BEIDOU_B1I_PCPS_Acquisition_B200", "BEIDOU_B1I_PCPS_Acquisition", BEIDOU_B1I_CODE_RATE_HZ, BEIDOU_B1I_CODE_LENGTH_CHIPS, 1.0, 0.0, 2048000, true, true, false,
-        false, 0, true, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b1i},
+        false, 0, true, false, false, 0.0, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b1i},
     {"BEIDOU_B3I_PCPS_Acquisition_B200", "BEIDOU_B3I_PCPS_Acquisition", BEIDOU_B3I_CODE_RATE_HZ, BEIDOU_B3I_CODE_LENGTH_CHIPS, 1.0, 0.0, 2048000, true, true, false,
-        false, 0, true, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b3i},
+        false, 0, true, false, false, 0.0, false, false, 0.0, false, false, "./data/acquisition.dat", gen_b3i},
     {"GLONASS_L1_CA_PCPS_Acquisition_B200", "GLONASS_L1_CA_PCPS_Acquisition", GLONASS_L1_CA_CODE_RATE_HZ, GLONASS_L1_CA_CODE_LENGTH_CHIPS,
-        GLONASS_L1_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, 1, false, true, true, GLONASS_L1_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l1},
+        GLONASS_L1_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, 1, false, true, true, 0.0, false, false, GLONASS_L1_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l1},
     {"GLONASS_L2_CA_PCPS_Acquisition_B200", "GLONASS_L2_CA_PCPS_Acquisition", GLONASS_L2_CA_CODE_RATE_HZ, GLONASS_L2_CA_CODE_LENGTH_CHIPS,
-        GLONASS_L2_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, 1, false, true, true, GLONASS_L2_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l2},
+        GLONASS_L2_CA_CODE_PERIOD * 1000.0, 0.0, 2048000, true, true, false, false, 1, false, true, true, 0.0, false, false, GLONASS_L2_CA_CHIP_PERIOD, false, false, "./data/acquisition.dat", gen_glo_l2},
 };
 
 // columns: implementation, replaces, name in warnings, system, signal, code rate, code length, pll_bw, dll_bw, pll_bw_narrow, dll_bw_narrow,
-//          early_late_space, early_late_space_narrow, cn0_min, carrier_lock_th, default fs, reads dump_mat, reads high_dyn + smoother_length, reads the narrow keys, extend mode, has pilot,
+//          early_late_space, early_late_space_narrow, cn0_min, carrier_lock_th, default fs, reads dump_mat, reads high_dyn + smoother_length, reads the narrow keys, very_early_late_space defaults (wide, narrow; -1: assigned 0), extend mode, has pilot,
 //          data-component clamp
 const B200TrkTraits kTrk[] = {
+    {"GPS_L1_CA_DLL_PLL_Tracking_B200", "GPS_L1_CA_DLL_PLL_Tracking", "GPS L1 C/A", 'G', "1C", GPS_L1_CA_CODE_RATE_HZ, GPS_L1_CA_CODE_LENGTH_CHIPS, 50.0, 2.0, 20.0, 2.0, 0.5,
+        0.5, 30, 0.80, 2048000, true, true, true, -1.0, -1.0, 1, false, 20},  // gps_l1_ca_dll_pll_tracking.cc:55-191
+    {"Galileo_E1_DLL_PLL_VEML_Tracking_B200", "Galileo_E1_DLL_PLL_VEML_Tracking", "Galileo E1", 'E', "1B", GALILEO_E1_CODE_CHIP_RATE_HZ, GALILEO_E1_B_CODE_LENGTH_CHIPS, 5.0,
+        0.5, 2.0, 0.25, 0.15, 0.15, 25, 0.85, 2048000, true, true, true, 0.6, 0.6, 0, true, 1},  // galileo_e1_dll_pll_veml_tracking.cc:55-190
     {"GPS_L5_DLL_PLL_Tracking_B200", "GPS_L5_DLL_PLL_Tracking", "GPS L5", 'G', "L5", GPS_L5I_CODE_RATE_HZ, GPS_L5I_CODE_LENGTH_CHIPS, 50.0, 2.0, 2.0, 0.25, 0.5, 0.15,
-        25, 0.75, 2048000, true, true, true, 0, true, GPS_L5I_NH_CODE_LENGTH},  // gps_l5_dll_pll_tracking.cc:78-178
+        25, 0.75, 2048000, true, true, true, -1.0, -1.0, 0, true, GPS_L5I_NH_CODE_LENGTH},  // gps_l5_dll_pll_tracking.cc:78-178
     {"GPS_L2_M_DLL_PLL_Tracking_B200", "GPS_L2_M_DLL_PLL_Tracking", "GPS L2", 'G', "2S", GPS_L2_M_CODE_RATE_HZ, GPS_L2_M_CODE_LENGTH_CHIPS, 2.0, 0.75, 0.0, 0.0, 0.5, 0.0,
-        25, 0.85, 2048000, true, false, false, 2, false, 1},  // gps_l2_m_dll_pll_tracking.cc:56-150 (narrow values assigned 0.0, not read)
+        25, 0.85, 2048000, true, false, false, -1.0, -1.0, 2, false, 1},  // gps_l2_m_dll_pll_tracking.cc:56-150 (narrow values assigned 0.0, not read)
     {"Galileo_E5a_DLL_PLL_Tracking_B200", "Galileo_E5a_DLL_PLL_Tracking", "Galileo E5a", 'E', "5X", GALILEO_E5A_CODE_CHIP_RATE_HZ, GALILEO_E5A_CODE_LENGTH_CHIPS, 20.0,
-        20.0, 5.0, 2.0, 0.5, 0.15, 25, 0.85, 12000000, true, true, true, 0, true, GALILEO_E5A_I_SECONDARY_CODE_LENGTH},  // galileo_e5a_dll_pll_tracking.cc:72-172
+        20.0, 5.0, 2.0, 0.5, 0.15, 25, 0.85, 12000000, true, true, true, -1.0, -1.0, 0, true, GALILEO_E5A_I_SECONDARY_CODE_LENGTH},  // galileo_e5a_dll_pll_tracking.cc:72-172
     {"BEIDOU_B1I_DLL_PLL_Tracking_B200", "BEIDOU_B1I_DLL_PLL_Tracking", "BEIDOU B1I", 'C', "B1", BEIDOU_B1I_CODE_RATE_HZ, BEIDOU_B1I_CODE_LENGTH_CHIPS, 50.0, 2.0, 20.0,
-        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, true, 1, false, 20},  // beidou_b1i_dll_pll_tracking.cc:60-160
+        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, true, -1.0, -1.0, 1, false, 20},  // beidou_b1i_dll_pll_tracking.cc:60-160
     {"BEIDOU_B3I_DLL_PLL_Tracking_B200", "BEIDOU_B3I_DLL_PLL_Tracking", "BEIDOU B3I", 'C', "B3", BEIDOU_B3I_CODE_RATE_HZ, BEIDOU_B3I_CODE_LENGTH_CHIPS, 50.0, 2.0, 20.0,
-        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, true, 1, false, 20},  // beidou_b3i_dll_pll_tracking.cc:58-158
+        2.0, 0.5, 0.5, 25, 0.85, 2048000, false, false, true, -1.0, -1.0, 1, false, 20},  // beidou_b3i_dll_pll_tracking.cc:58-158
 };
 }  // namespace
 
@@ -129,6 +154,7 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
     doppler_max_ = configuration_->property(role + ".doppler_max", 5000);
     acq_parameters_.doppler_max = doppler_max_;
     acq_parameters_.sampled_ms = t_.reads_sampled_ms ? configuration_->property(role + ".coherent_integration_time_ms", std::max(1, t_.ms_per_code)) : 1;
+    requested_ms_ = acq_parameters_.sampled_ms;
     if (t_.ms_per_code > 1 && (acq_parameters_.sampled_ms % t_.ms_per_code) != 0)
         {
             LOG(WARNING) << "Parameter coherent_integration_time_ms should be a multiple of " << t_.ms_per_code << ". Setting it to " << t_.ms_per_code;
@@ -139,7 +165,7 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
     acq_parameters_.max_dwells = configuration_->property(role + ".max_dwells", 1);
     acq_parameters_.dump_filename = configuration_->property(role + ".dump_filename", default_dump_filename);
     if (t_.ms_per_code > 0) acq_parameters_.ms_per_code = t_.ms_per_code;
-    num_codes_ = acq_parameters_.sampled_ms / std::max(1, t_.ms_per_code);
+    num_codes_ = (t_.vector_from_requested_ms ? requested_ms_ : acq_parameters_.sampled_ms) / std::max(1, t_.ms_per_code);
     acq_parameters_.num_doppler_bins_step2 = configuration_->property(role + ".second_nbins", 4);
     acq_parameters_.doppler_step2 = configuration_->property(role + ".second_doppler_step", 125.0);
     acq_parameters_.make_2_steps = configuration_->property(role + ".make_two_steps", false);
@@ -147,7 +173,8 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
     const double code_period_hz = t_.code_rate_hz / t_.code_length_chips;
     if (t_.modern)
         {
-            // gps_l5i_pcps_acquisition.cc:100-135 / galileo_e5a_pcps_acquisition.cc:88-124
+            // gps_l5i_pcps_acquisition.cc:100-135 / galileo_e5a_pcps_acquisition.cc:88-124 / gps_l1_ca_pcps_acquisition.cc:88-123
+            const double chip_period = t_.modern_chip_period_s > 0.0 ? t_.modern_chip_period_s : (1.0 / t_.code_rate_hz);  // GPS L1: the constant GPS_L1_CA_CHIP_PERIOD
             acq_parameters_.use_automatic_resampler = t_.opt_acq_fs_hz > 0.0 && configuration_->property("GNSS-SDR.use_acquisition_resampler", false);
             if (acq_parameters_.use_automatic_resampler == true and item_type_ != "gr_complex")
                 {
@@ -166,14 +193,14 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
                         }
                     code_length_ = static_cast<unsigned int>(std::floor(static_cast<double>(acq_parameters_.resampled_fs) / code_period_hz));
                     acq_parameters_.samples_per_ms = static_cast<float>(acq_parameters_.resampled_fs) * 0.001;
-                    acq_parameters_.samples_per_chip = static_cast<unsigned int>(ceil((1.0 / t_.code_rate_hz) * static_cast<float>(acq_parameters_.resampled_fs)));
+                    acq_parameters_.samples_per_chip = static_cast<unsigned int>(ceil(chip_period * static_cast<float>(acq_parameters_.resampled_fs)));
                 }
             else
                 {
-                    acq_parameters_.resampled_fs = fs_in_;
+                    if (!t_.leaves_resampled_fs_zero) acq_parameters_.resampled_fs = fs_in_;
                     code_length_ = static_cast<unsigned int>(std::floor(static_cast<double>(fs_in_) / code_period_hz));
                     acq_parameters_.samples_per_ms = static_cast<float>(fs_in_) * 0.001;
-                    acq_parameters_.samples_per_chip = static_cast<unsigned int>(ceil((1.0 / t_.code_rate_hz) * static_cast<float>(acq_parameters_.fs_in)));
+                    acq_parameters_.samples_per_chip = static_cast<unsigned int>(ceil(chip_period * static_cast<float>(acq_parameters_.fs_in)));
                 }
             acq_parameters_.samples_per_code = acq_parameters_.samples_per_ms * static_cast<float>(t_.code_period_ms);
             if (t_.final_round_code_length)
@@ -183,7 +210,8 @@ B200PcpsAcquisitionAdapter::B200PcpsAcquisitionAdapter(ConfigurationInterface* c
                     vector_length_ = code_length_ * acq_parameters_.sampled_ms;
                 }
             else
-                vector_length_ = std::floor(acq_parameters_.sampled_ms * acq_parameters_.samples_per_ms) * (acq_parameters_.bit_transition_flag ? 2 : 1);
+                vector_length_ = std::floor((t_.vector_from_requested_ms ? requested_ms_ : acq_parameters_.sampled_ms) * acq_parameters_.samples_per_ms) *
+                                 (acq_parameters_.bit_transition_flag ? 2 : 1);
         }
     else
         {
@@ -254,6 +282,7 @@ void B200PcpsAcquisitionAdapter::set_local_code()
 {
     // one code period at the acquisition's sample rate, repeated sampled_ms times (e.g. gps_l5i_pcps_acquisition.cc:237-252)
     std::vector<std::complex<float>> code(code_length_);
+    flags_.cboc = configuration_->property("Acquisition" + std::to_string(channel_) + ".cboc", false);  // galileo_e1_pcps_ambiguous_acquisition.cc:242 (sic: no underscore, no signal)
     t_.gen(code.data(), *gnss_synchro_, acq_parameters_.use_automatic_resampler ? acq_parameters_.resampled_fs : fs_in_, flags_);
     for (unsigned int i = 0; i < num_codes_; i++) std::memcpy(&code_[static_cast<size_t>(i) * code_length_], code.data(), sizeof(std::complex<float>) * code_length_);
     acquisition_->set_local_code(code_.data());
@@ -385,8 +414,10 @@ B200DllPllTrackingAdapter::B200DllPllTrackingAdapter(ConfigurationInterface* con
         std::cout << "WARNING: " << t_.what << ". PLL or DLL narrow tracking bandwidth is higher than wide tracking one" << std::endl;
     trk_param.extend_correlation_symbols = extend_correlation_symbols;
     trk_param.track_pilot = track_pilot;
-    trk_param.very_early_late_space_chips = 0.0;
-    trk_param.very_early_late_space_narrow_chips = 0.0;
+    // VEML spacings: keys of the Galileo E1 adapter only (:137-141); every other adapter assigns 0
+    trk_param.very_early_late_space_chips = t_.very_early_late_space_chips < 0.0 ? 0.0 : configuration->property(role + ".very_early_late_space_chips", t_.very_early_late_space_chips);
+    trk_param.very_early_late_space_narrow_chips =
+        t_.very_early_late_space_narrow_chips < 0.0 ? 0.0 : configuration->property(role + ".very_early_late_space_narrow_chips", t_.very_early_late_space_narrow_chips);
     trk_param.system = t_.system;
     std::memcpy(trk_param.signal, t_.signal, 3);
     trk_param.cn0_samples = configuration->property(role + ".cn0_samples", 20);

@@ -1,4 +1,4 @@
-// Table-driven *_B200 adapters for the signals beyond GPS L1 C/A and Galileo E1.
+// Table-driven *_B200 adapters: every signal whose reference adapter wraps pcps_acquisition or dll_pll_veml_tracking.
 //
 // The reference has one adapter file per signal (src/algorithms/acquisition/adapters/*_pcps_acquisition.cc,
 // src/algorithms/tracking/adapters/*_dll_pll_tracking.cc), all wrapping the same two GNU Radio blocks (pcps_acquisition,
@@ -8,10 +8,14 @@
 // defaults, same derived Acq_Conf / Dll_Pll_Conf; the blocks behind them are b200_pcps_acquisition / b200_dll_pll_veml_tracking.
 //
 //   implementation name                      replaces                        reference adapter
+//   GPS_L1_CA_PCPS_Acquisition_B200          GPS_L1_CA_PCPS_Acquisition      gps_l1_ca_pcps_acquisition.cc
+//   Galileo_E1_PCPS_Ambiguous_Acquisition_B200  Galileo_E1_PCPS_Ambiguous_Acquisition  galileo_e1_pcps_ambiguous_acquisition.cc
 //   GPS_L5i_PCPS_Acquisition_B200            GPS_L5i_PCPS_Acquisition        gps_l5i_pcps_acquisition.cc
 //   Galileo_E5a_Pcps_Acquisition_B200        Galileo_E5a_Pcps_Acquisition    galileo_e5a_pcps_acquisition.cc
 //   BEIDOU_B1I_PCPS_Acquisition_B200         BEIDOU_B1I_PCPS_Acquisition     beidou_b1i_pcps_acquisition.cc
 //   GLONASS_L1_CA_PCPS_Acquisition_B200      GLONASS_L1_CA_PCPS_Acquisition  glonass_l1_ca_pcps_acquisition.cc
+//   GPS_L1_CA_DLL_PLL_Tracking_B200          GPS_L1_CA_DLL_PLL_Tracking      gps_l1_ca_dll_pll_tracking.cc
+//   Galileo_E1_DLL_PLL_VEML_Tracking_B200    Galileo_E1_DLL_PLL_VEML_Tracking  galileo_e1_dll_pll_veml_tracking.cc
 //   GPS_L5_DLL_PLL_Tracking_B200             GPS_L5_DLL_PLL_Tracking         gps_l5_dll_pll_tracking.cc
 //   Galileo_E5a_DLL_PLL_Tracking_B200        Galileo_E5a_DLL_PLL_Tracking    galileo_e5a_dll_pll_tracking.cc
 //   BEIDOU_B1I_DLL_PLL_Tracking_B200         BEIDOU_B1I_DLL_PLL_Tracking     beidou_b1i_dll_pll_tracking.cc
@@ -36,7 +40,8 @@ class ConfigurationInterface;
 
 struct B200AcqFlags
 {
-    bool acquire_pilot = false, acquire_iq = false;  // Galileo E5a only
+    bool acquire_pilot = false, acquire_iq = false;  // Galileo E1 (pilot) and E5a (pilot / both)
+    bool cboc = false;                               // Galileo E1: "Acquisition" + channel + ".cboc", read when the code is made
 };
 
 // what distinguishes one *_pcps_acquisition.cc adapter from another
@@ -57,6 +62,10 @@ struct B200AcqTraits
                                       // the default of coherent_integration_time_ms, which must be a multiple of it (gps_l2_m_pcps_acquisition.cc:81-87)
     bool samples_per_code_is_length;  // BeiDou B1I: samples_per_code = code_length_ (:106)
     bool has_blocking_on_standby, has_dump_channel;
+    double modern_chip_period_s;      // modern layout: samples_per_chip = ceil(chip period * float(fs)); 0: the adapter writes (1.0 / code rate) instead of a constant
+    bool vector_from_requested_ms;    // Galileo E1: vector_length_ and the number of code copies use the coherent_integration_time_ms AS READ, even when
+                                      // Acq_Conf::sampled_ms was reset to 4 because it is not a multiple of 4 (galileo_e1_pcps_ambiguous_acquisition.cc:68-75, :123)
+    bool leaves_resampled_fs_zero;    // Galileo E1: without the resampler Acq_Conf::resampled_fs is never assigned (the other modern adapters set it to fs_in)
     double old_layout_chip_period_s;  // older layout only: samples_per_chip = ceil(chip period * float(fs)) with the adapter's own chip-period constant
                                       // (glonass_l1_ca_pcps_acquisition.cc:64, GLONASS_L1_CA_CHIP_PERIOD); 0: never assigned (BeiDou B1I)
     bool per_channel_pfa;             // role + channel + ".pfa" first (L5i, E5a)
@@ -108,7 +117,7 @@ private:
     B200AcqFlags flags_;
     size_t item_size_ = 0;
     std::string item_type_;
-    unsigned int vector_length_ = 0, code_length_ = 0, num_codes_ = 1;
+    unsigned int vector_length_ = 0, code_length_ = 0, num_codes_ = 1, requested_ms_ = 1;
     unsigned int channel_ = 0;
     std::shared_ptr<ChannelFsm> channel_fsm_;
     float threshold_ = 0.0f;
@@ -138,6 +147,7 @@ struct B200TrkTraits
     bool reads_dump_mat;       // .dump_mat is a key (the BeiDou adapters do not read it)
     bool reads_high_dyn;       // .high_dyn and .smoother_length are keys (GPS L5, Galileo E5a; not GPS L2C, BeiDou)
     bool reads_narrow;         // .pll_bw_narrow_hz, .dll_bw_narrow_hz, .early_late_space_narrow_chips are keys (not GPS L2C)
+    double very_early_late_space_chips, very_early_late_space_narrow_chips;  // defaults of the two VEML keys; < 0: the adapter assigns 0 and reads no key
     int extend_mode;           // extend_correlation_symbols: 0 clamp to max_extend_data only when the data component is tracked (L5, E5a); 1 clamp to
                                // [1, max_extend_data] always (BeiDou); 2 forced to 1 with a warning (GPS L2C)
     bool has_pilot;            // false: track_pilot is forced off with a warning and extend_correlation_symbols is clamped to [1, max_extend]

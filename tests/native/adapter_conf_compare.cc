@@ -34,17 +34,13 @@
 #include "beidou_b3i_pcps_acquisition.h"
 #include "file_configuration.h"
 #include "galileo_e1_dll_pll_veml_tracking.h"
-#include "galileo_e1_dll_pll_veml_tracking_b200.h"
 #include "galileo_e1_pcps_ambiguous_acquisition.h"
-#include "galileo_e1_pcps_ambiguous_acquisition_b200.h"
 #include "galileo_e5a_dll_pll_tracking.h"
 #include "galileo_e5a_pcps_acquisition.h"
 #include "glonass_l1_ca_pcps_acquisition.h"
 #include "glonass_l2_ca_pcps_acquisition.h"
 #include "gps_l1_ca_dll_pll_tracking.h"
-#include "gps_l1_ca_dll_pll_tracking_b200.h"
 #include "gps_l1_ca_pcps_acquisition.h"
-#include "gps_l1_ca_pcps_acquisition_b200.h"
 #include "gps_l2_m_dll_pll_tracking.h"
 #include "gps_l2_m_pcps_acquisition.h"
 #include "gps_l5_dll_pll_tracking.h"
@@ -171,8 +167,6 @@ int b200_adapter_conf_compare(const char* conf_path, int kind, const char* role_
                     b->set_threshold(threshold);
                     b->init();
                     if (getenv("GB_CC_TRACE")) fprintf(stderr, "cc: b200 adapter set up\n");
-                    if (auto* g = dynamic_cast<GpsL1CaPcpsAcquisitionB200*>(b.get())) n_b = flatten(g->acquisition_->acq_parameters, g->threshold_, g->item_size(), out_b200);
-                    if (auto* g = dynamic_cast<GalileoE1PcpsAmbiguousAcquisitionB200*>(b.get())) n_b = flatten(g->acquisition_->acq_parameters, g->threshold_, g->item_size(), out_b200);
                     if (auto* g = dynamic_cast<B200PcpsAcquisitionAdapter*>(b.get())) n_b = flatten(g->acquisition_->acq_parameters, g->threshold_, g->item_size(), out_b200);
                 }
             else
@@ -186,8 +180,6 @@ int b200_adapter_conf_compare(const char* conf_path, int kind, const char* role_
                     if (ref_impl == "GPS_L2_M_DLL_PLL_Tracking") n_ref = ref_trk<GpsL2MDllPllTracking>(config.get(), role, out_ref);
                     std::unique_ptr<TrackingInterface> b = GetB200TrkBlock(config, role, b200_impl, 1, 1);
                     if (!b) return -2;
-                    if (auto* g = dynamic_cast<GpsL1CaDllPllTrackingB200*>(b.get())) n_b = flatten(g->tracking_->trk_parameters, g->item_size(), out_b200);
-                    if (auto* g = dynamic_cast<GalileoE1DllPllVemlTrackingB200*>(b.get())) n_b = flatten(g->tracking_->trk_parameters, g->item_size(), out_b200);
                     if (auto* g = dynamic_cast<B200DllPllTrackingAdapter*>(b.get())) n_b = flatten(g->tracking_->trk_parameters, g->item_size(), out_b200);
                 }
         }

@@ -12,11 +12,7 @@
 #include "b200_service_singleton.h"
 #include "channel_fsm.h"
 #include "file_configuration.h"
-#include "galileo_e1_dll_pll_veml_tracking_b200.h"
-#include "galileo_e1_pcps_ambiguous_acquisition_b200.h"
 #include "gnss_synchro.h"
-#include "gps_l1_ca_dll_pll_tracking_b200.h"
-#include "gps_l1_ca_pcps_acquisition_b200.h"
 #include <algorithm>
 #include <cstring>
 #include <memory>
