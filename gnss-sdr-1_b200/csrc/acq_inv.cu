@@ -107,16 +107,16 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
                 {
                     if (p.scale) mag = __fmul_rn(mag, __ldg(p.scale));  // volk_32f_s32f_multiply_32f
                     float* g = grid + (size_t)bin * p.keep_len + n;
-                    *g = p.accumulate ? __fadd_rn(*g, mag) : mag;
                     if (p.accumulate && p.tmpbuf && p.tmpbuf[handle] && bin == p.n_bins - 1) p.tmpbuf[handle][n] = mag;
+                    if (p.accumulate) mag = __fadd_rn(*g, mag);
+                    *g = mag;  // the search below runs over the stored (accumulated) grid, :577-600
                 }
-            else if (peak_better(mag, (unsigned)n, best, best_i))
+            if (peak_better(mag, (unsigned)n, best, best_i))
                 {
                     best = mag;
                     best_i = (unsigned)n;
                 }
         }
-    if (grid) return;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
         {
@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(NT, OCC)
 
 // columns of one transform's tile c0 .. c0+TILE: src[k1][n2] -> inverse DFT over k1 -> |y|^2 -> arg-max partial / grid.
 // MODE 0: arg-max over the whole row (keep_offset == 0, keep_len == N: the common single-dwell CFAR search);
-// MODE 1: arg-max over a kept window (bit transition); MODE 2: magnitude grid written / accumulated.
+// MODE 1: arg-max over a kept window (bit transition); MODE 2: magnitude grid written / accumulated, arg-max over the stored values.
 // COHERENT: the source was written earlier in the SAME launch by other CTAs (fused kernel): ld.global.cg (L2) instead of
 // the read-only path, see gb_ld_poll.
 template <int LOGT, int NT, class DCOL, int N2, int MODE, bool COHERENT>
@@ -277,22 +277,22 @@ __device__ __forceinline__ void gb_inv_col_tile(float2* smem, float* s_mag, unsi
                 if (MODE == 2)
                     {
                         if (p.scale) mag = __fmul_rn(mag, __ldg(p.scale));  // volk_32f_s32f_multiply_32f
-                        grid[n] = p.accumulate ? __fadd_rn(grid[n], mag) : mag;
                         if (tmp) tmp[n] = mag;
+                        if (p.accumulate) mag = __fadd_rn(grid[n], mag);
+                        grid[n] = mag;  // the search runs over the stored (accumulated) grid, :577-600
                     }
-                else if (mag > ibest)
+                if (mag > ibest)
                     {
                         ibest = mag;
                         ibest_i = (unsigned)n;
                     }
             }
-        if (MODE != 2 && peak_better(ibest, ibest_i, best, best_i))
+        if (peak_better(ibest, ibest_i, best, best_i))
             {
                 best = ibest;
                 best_i = ibest_i;
             }
     });
-    if constexpr (MODE != 2)
         {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1)

@@ -21,16 +21,31 @@ __global__ void __launch_bounds__(1024) gb_input_power_kernel(const void* sample
 {
     __shared__ float s[32];
     float acc = 0.f;
-    for (int n = threadIdx.x; n < N; n += blockDim.x)
+    // eight loads in flight per thread; the additions stay in ascending-n order, so the sum is that of the plain strided loop
+    for (int n0 = threadIdx.x; n0 < N; n0 += 8 * blockDim.x)
         {
-            float m = 0.f;
-            if (n < consumed)
+            float m[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++)
                 {
-                    const float2 x = gb_load_item<ITEM>(samples, (size_t)n);
-                    m = __fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y));
+                    const int n = n0 + u * blockDim.x;
+                    m[u] = 0.f;
+                    if (n < consumed && n < N)
+                        {
+                            const float2 x = gb_load_item<ITEM>(samples, (size_t)n);
+                            m[u] = __fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y));
+                        }
                 }
-            if (tmp) tmp[n] = m;
-            acc += m;
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                {
+                    const int n = n0 + u * blockDim.x;
+                    if (n < N)
+                        {
+                            if (tmp) tmp[n] = m[u];
+                            acc += m[u];
+                        }
+                }
         }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
@@ -97,38 +112,6 @@ __global__ void __launch_bounds__(256) gb_reduce_peaks_kernel(const GbPeak* part
     if (threadIdx.x == 0)
         {
             // the reference starts from grid_maximum = 0 with strict '>': an all-zero grid reports bin 0, index 0
-            if (!(best.mag > 0.f))
-                {
-                    best.mag = 0.f;
-                    best.idx = 0;
-                    best.bin = 0;
-                }
-            out[blockIdx.x] = best;
-        }
-}
-
-// one CTA per handle: scan its stored magnitude grid [bins][row_len]
-__global__ void __launch_bounds__(1024) gb_grid_peaks_kernel(float* const* grids, int n_bins, int row_len, GbPeak* out)
-{
-    const float* g = grids[blockIdx.x];
-    GbPeak best;
-    best.mag = -1.f;
-    best.idx = 0xffffffffu;
-    best.bin = 0xffffffffu;
-    best.pad_ = 0;
-    const size_t total = (size_t)n_bins * row_len;
-    for (size_t i = threadIdx.x; i < total; i += blockDim.x)
-        {
-            GbPeak c;
-            c.mag = g[i];
-            c.bin = (unsigned)(i / row_len);
-            c.idx = (unsigned)(i - (size_t)c.bin * row_len);
-            c.pad_ = 0;
-            if (peak_before(c, best)) best = c;
-        }
-    best = peak_block_reduce(best);
-    if (threadIdx.x == 0)
-        {
             if (!(best.mag > 0.f))
                 {
                     best.mag = 0.f;
@@ -287,13 +270,6 @@ cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type,
 cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins, int tiles, GbPeak* out, cudaStream_t st, int* launches)
 {
     gb_reduce_peaks_kernel<<<n_handles, 256, 0, st>>>(partial, n_bins, tiles, out);
-    if (launches) (*launches)++;
-    return cudaGetLastError();
-}
-
-cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches)
-{
-    gb_grid_peaks_kernel<<<n_handles, 1024, 0, st>>>(grids, n_bins, row_len, out);
     if (launches) (*launches)++;
     return cudaGetLastError();
 }

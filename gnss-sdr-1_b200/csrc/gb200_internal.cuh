@@ -199,10 +199,8 @@ bool gb_acq_inverse_tiles(int N1, int N2, int variant, int* tile1, int* tile2);
 bool gb_acq_preferred_split(int N, int avoid_n1, int* n1, int* n2);  // a split of N that has the fast inverse kernels  // true when the pair has the fast inverse kernels
 cudaError_t gb_acq_conj(float2* data, size_t n, cudaStream_t st, int* launches);
 cudaError_t gb_acq_input_power(const void* samples, int consumed, int item_type, int N, float* d_power, float* d_mag2_tmp, cudaStream_t st, int* launches);
-// grid-free path: reduce per-CTA maxima -> per handle peak
+// reduce per-CTA maxima (all modes; over the stored grid where one is kept) -> per handle peak
 cudaError_t gb_acq_reduce_peaks(const GbPeak* partial, int n_handles, int n_bins, int tiles, GbPeak* out, cudaStream_t st, int* launches);
-// grid path: scan stored grids -> per handle peak
-cudaError_t gb_acq_grid_peaks(float* const* grids, int n_handles, int n_bins, int row_len, GbPeak* out, cudaStream_t st, int* launches);
 // first_vs_second_peak_statistic's second peak with the d_tmp_buffer quirk (pcps_acquisition.cc:633-660)
 // FIR + decimation of the newest items of a 32fc ring into a linear buffer (gb200_stream_set_decimator)
 cudaError_t gb_fir_decimate(const float2* ring, unsigned long long cap, unsigned long long valid_begin, unsigned long long k_first, unsigned n_out,

@@ -144,6 +144,7 @@ struct gb200_service
     cudaStream_t stream34[2] = {nullptr, nullptr};  // optional third / fourth lane (GB200_ACQ_LANES)
     cudaEvent_t ev_join34[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_power_fork = nullptr;  // the input-power reduction runs on stream2 beside the forward transforms
     // Ingest runs on its own stream so that the H2D copy of block k+1 overlaps the kernels working on block k.  Ordering:
     // a consumer launch waits for the newest push of every ring (ev_pushed); a push waits for the newest consumer launch
     // (ev_consumed) before it may overwrite ring memory.
@@ -296,6 +297,7 @@ extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service*
         cudaEventCreateWithFlags(&s->ev_join34[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_consumed, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_power_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming) != cudaSuccess)
         {
             g_global_error = "cudaStreamCreate failed";
@@ -340,6 +342,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+    if (s->ev_power_fork) cudaEventDestroy(s->ev_power_fork);
     if (s->ev_join) cudaEventDestroy(s->ev_join);
     if (s->stream2) cudaStreamDestroy(s->stream2);
     for (int k = 0; k < 2; k++)
@@ -1033,6 +1036,9 @@ struct gb200_acq
     float2* d_code_fft = nullptr;
     bool code_set = false;
     float* d_grid = nullptr;  // [max(num_bins, bins_step2)][eff]
+    // End of an attempt (pcps_acquisition.cc:912-929) zeroes the grid.  The next first dwell overwrites every row it searches, so the
+    // zeroing is only owed to whoever looks at the grid before that: it is recorded here and done by grid_settle() on demand.
+    bool grid_zero_pending = false;
     size_t grid_rows = 0;
     float* d_tmp = nullptr;   // d_tmp_buffer image, fft_size floats (non-CFAR statistic only)
     // block state (pcps_acquisition members)
@@ -1366,6 +1372,13 @@ extern "C" int gb200_acq_keep_grid(gb200_acq* a, int keep)
     return acq_alloc_grid(a);
 }
 
+static cudaError_t grid_settle(gb200_acq* a)
+{
+    if (!a->grid_zero_pending || !a->d_grid) return cudaSuccess;
+    a->grid_zero_pending = false;
+    return cudaMemsetAsync(a->d_grid, 0, sizeof(float) * a->grid_rows * a->eff, a->s->stream);
+}
+
 extern "C" int gb200_acq_reset(gb200_acq* a)
 {
     if (!a) return GB200_E_INVALID;
@@ -1375,6 +1388,7 @@ extern "C" int gb200_acq_reset(gb200_acq* a)
     a->dwell_counter = 0;
     a->step_two = false;
     a->positive_acq = 0;
+    a->grid_zero_pending = false;
     if (a->d_grid) GB_CUDA(s, cudaMemsetAsync(a->d_grid, 0, sizeof(float) * a->grid_rows * a->eff, s->stream));
     return GB200_OK;
 }
@@ -1390,6 +1404,7 @@ extern "C" int gb200_acq_read_grid(gb200_acq* a, float* dst)
             s->set_error("gb200_acq_read_grid: handle keeps no grid (see gb200_acq_keep_grid)");
             return GB200_E_STATE;
         }
+    GB_CUDA(s, grid_settle(a));
     GB_CUDA(s, cudaMemcpyAsync(dst, a->d_grid, sizeof(float) * a->num_bins * a->eff, cudaMemcpyDeviceToHost, s->stream));
     GB_CUDA(s, cudaStreamSynchronize(s->stream));
     return GB200_OK;
@@ -1416,6 +1431,7 @@ extern "C" int gb200_acq_iq_combine(gb200_acq* ia, gb200_acq* qa, gb200_acq* ib,
                     s->set_error("gb200_acq_iq_combine: every handle must keep its grid (gb200_acq_keep_grid) and have run a dwell");
                     return GB200_E_STATE;
                 }
+            GB_CUDA(s, grid_settle(h[k]));
             rows[k] = h[k]->d_grid;
         }
     if (qb && !ib)
@@ -1448,6 +1464,7 @@ extern "C" int gb200_acq_second_peak(gb200_acq* a, uint32_t bin, uint32_t idx, u
             s->set_error("gb200_acq_second_peak: handle keeps no grid, or bin / index out of range");
             return GB200_E_STATE;
         }
+    GB_CUDA(s, grid_settle(a));
     void* d_tmp;
     int rc;
     if ((rc = s->scratch(18, sizeof(float) * (a->eff + 4), &d_tmp))) return rc;
@@ -1672,6 +1689,22 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             void *d_col, *d_spec;
             if ((rc = s->scratch(0, sizeof(float2) * (size_t)N * bins, &d_col))) return rc;
             if ((rc = s->scratch(1, sizeof(float2) * (size_t)N * bins, &d_spec))) return rc;
+            // input power (CFAR or bit transition, pcps_acquisition.cc:703-709).  It needs only the samples, and only the final
+            // statistic needs it: unless it also leaves the |x|^2 image the inverse kernels read, it runs on stream2 beside the
+            // forward transforms and is joined before the peak reduction.
+            bool want_power = false;
+            for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag || list[m]->scaled_accum;
+            float* d_power = (float*)((char*)d_res + g.off_power);
+            const bool image = g.grid && !a0->use_cfar;  // the |x|^2 image the block leaves in d_tmp_buffer
+            const bool power_aside = want_power && !image && !a0->scaled_accum && !s->kt.enabled;  // (the Tong scale feeds the inverse kernels)
+            // folded handles: the power is the mean over all consumed items (pcps_quicksync_acquisition_cc.cc:363-365)
+            const int power_n = a0->fold > 1 ? (int)a0->consumed : (int)a0->fft_size;
+            if (power_aside)
+                {
+                    GB_CUDA(s, cudaEventRecord(s->ev_power_fork, s->stream));
+                    GB_CUDA(s, cudaStreamWaitEvent(s->stream2, s->ev_power_fork, 0));
+                    GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, power_n, d_power, nullptr, s->stream2, &l));
+                }
             GbAcqFwdParams fp;
             fp.samples = win;
             fp.consumed = (int)a0->consumed;
@@ -1682,19 +1715,25 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             fp.spectra = (float2*)d_spec;
             fp.fold = (int)a0->fold;
             GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l, s));
-            // input power (CFAR or bit transition, pcps_acquisition.cc:703-709)
-            bool want_power = false;
-            for (int m : g.members) want_power = want_power || list[m]->use_cfar || list[m]->c.bit_transition_flag || list[m]->scaled_accum;
-            float* d_power = (float*)((char*)d_res + g.off_power);
-            if (want_power)
+            if (want_power && !power_aside)
                 {
-                    const bool image = g.grid && !a0->use_cfar;  // the |x|^2 image the block leaves in d_tmp_buffer
-                    // folded handles: the power is the mean over all consumed items (pcps_quicksync_acquisition_cc.cc:363-365)
-                    GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, a0->fold > 1 ? (int)a0->consumed : N, d_power, image ? a0->d_tmp : nullptr, s->stream, &l));
+                    GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, power_n, d_power, image ? a0->d_tmp : nullptr, s->stream, &l));
                     if (image)
                         for (size_t k = 1; k < g.members.size(); k++)
                             GB_CUDA(s, cudaMemcpyAsync(list[g.members[k]]->d_tmp, a0->d_tmp, sizeof(float) * N, cudaMemcpyDeviceToDevice, s->stream));
                 }
+            // a grid whose end-of-attempt zeroing is still owed: a first dwell overwrites all the rows it searches, anything else
+            // (accumulation, rows beyond this search) gets the zeroing now
+            if (g.grid)
+                for (int m : g.members)
+                    {
+                        gb200_acq* a = list[m];
+                        if (!a->grid_zero_pending) continue;
+                        if (a->dwell_counter >= 1 || a->grid_rows > (size_t)bins)
+                            GB_CUDA(s, grid_settle(a));
+                        else
+                            a->grid_zero_pending = false;
+                    }
             // inverse side in L2-sized chunks of transforms
             const int T = bins * (int)g.members.size();
             // Two lanes: chunk c runs on stream (c & 1) with its own row buffer, so one lane's column kernel overlaps the
@@ -1783,18 +1822,19 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                         GB_CUDA(s, cudaEventRecord(lane_join[k], lane_stream[k]));
                         GB_CUDA(s, cudaStreamWaitEvent(s->stream, lane_join[k], 0));
                     }
-            GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
-            if (g.grid)
+            else if (power_aside)
                 {
-                    GB_CUDA(s, gb_acq_grid_peaks((float* const*)((char*)d_up + g.off_grid), (int)g.members.size(), bins, (int)a0->eff, d_peaks, s->stream, &l));
-                    // first/second-peak statistic (:633-660): the second peak of every member's winning row, one CTA each, in this
-                    // launch phase -- the results ride back with the peaks
-                    if (!a0->use_cfar && !a0->scaled_accum)
-                        GB_CUDA(s, gb_acq_second_peak_batch((float* const*)((char*)d_up + g.off_grid), (float* const*)((char*)d_up + g.off_tmp), d_peaks,
-                                       (int)g.members.size(), (int)a0->eff, N, (int)a0->c.samples_per_chip, (float*)((char*)d_res + g.off_second), s->stream, &l));
+                    GB_CUDA(s, cudaEventRecord(s->ev_join, s->stream2));
+                    GB_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_join, 0));
                 }
-            else
-                GB_CUDA(s, gb_acq_reduce_peaks((const GbPeak*)d_part, (int)g.members.size(), bins, tiles, d_peaks, s->stream, &l));
+            GbPeak* d_peaks = (GbPeak*)((char*)d_res + g.off_peaks);
+            // every mode leaves per-tile maxima in d_part (over the stored grid where one is kept)
+            GB_CUDA(s, gb_acq_reduce_peaks((const GbPeak*)d_part, (int)g.members.size(), bins, tiles, d_peaks, s->stream, &l));
+            // first/second-peak statistic (:633-660): the second peak of every member's winning row, one CTA each, in this
+            // launch phase -- the results ride back with the peaks
+            if (g.grid && !a0->use_cfar && !a0->scaled_accum)
+                GB_CUDA(s, gb_acq_second_peak_batch((float* const*)((char*)d_up + g.off_grid), (float* const*)((char*)d_up + g.off_tmp), d_peaks,
+                               (int)g.members.size(), (int)a0->eff, N, (int)a0->c.samples_per_chip, (float*)((char*)d_res + g.off_second), s->stream, &l));
         }
     s->launches += l;
     { int rc0 = rings_release(s); if (rc0) return rc0; }
@@ -1964,11 +2004,7 @@ extern "C" int gb200_acq_collect_batch(gb200_acq* const* list, int n, gb200_acq_
                 {
                     a->dwell_counter = 0;
                     a->positive_acq = 0;
-                    if (a->d_grid && !a->keep_grid)
-                        {
-                            cudaError_t e = cudaMemsetAsync(a->d_grid, 0, sizeof(float) * a->grid_rows * a->eff, s->stream);
-                            if (e != cudaSuccess) rc = GB200_E_CUDA;
-                        }
+                    if (a->d_grid && !a->keep_grid) a->grid_zero_pending = true;
                 }
             a->pending = false;
             out[i] = r;
