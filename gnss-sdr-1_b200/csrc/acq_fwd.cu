@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     for (int i = threadIdx.x; i < M; i += blockDim.x) tw[i] = __ldg(pl.tw + i);
     const int c0 = blockIdx.x * TILE;
     fill_twA(twA, M, c0, pl);
-    const int bin = blockIdx.y;
+    const int bin = p.first_bin + blockIdx.y;
     const GbWipeSeg* segs = nullptr;
     int nseg = 0;
     if (wipeoff)
@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
             nseg = __ldg(p.seg_offsets + bin + 1) - o0;
             segs = p.segs + o0;
         }
+    int lo = 0;
     for (int idx = threadIdx.x; idx < (M << LOGT); idx += blockDim.x)
         {
             const int n1 = idx >> LOGT;
@@ -46,16 +47,10 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
                     float2 v = gb_load_item<ITEM>(p.samples, (size_t)m);
                     if (wipeoff)
                         {
-                            // last segment with n_start <= m (binary search; a bin has ~10 segments)
-                            int lo = 0, hi = nseg - 1;
-                            while (lo < hi)
-                                {
-                                    const int mid = (lo + hi + 1) >> 1;
-                                    if (__ldg(&segs[mid].n_start) <= m)
-                                        lo = mid;
-                                    else
-                                        hi = mid - 1;
-                                }
+                            // last segment with n_start <= m.  A thread's samples come in increasing m (3200 apart at fold == 1), a bin
+                            // has ~10 segments: walking from the previous sample's segment is one comparison almost always
+                            while (lo + 1 < nseg && __ldg(&segs[lo + 1].n_start) <= m) lo++;
+                            while (lo > 0 && __ldg(&segs[lo].n_start) > m) lo--;
                             const GbWipeSeg sg = segs[lo];
                             const float ph = (float)fma((double)(m - sg.n_start), (double)sg.inc_eff, (double)sg.ph_start);  // exact
                             float s, c;
@@ -98,7 +93,7 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     for (int i = threadIdx.x; i < M; i += blockDim.x) tw[i] = __ldg(pl.tw + i);
     const int r0 = blockIdx.x * TILE;
     const int nb = min(TILE, N1 - r0);
-    const float2* src = p.colbuf + (size_t)blockIdx.y * pl.N + (size_t)r0 * M;
+    const float2* src = p.colbuf + (size_t)(p.first_bin + blockIdx.y) * pl.N + (size_t)r0 * M;
     const int db = (int)blockDim.x / M, dm = (int)blockDim.x % M;
     {
         int b = threadIdx.x / M, m = threadIdx.x - b * M;
@@ -116,7 +111,7 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
     }
     __syncthreads();
     float2* res = FFT::template run<-1, LOGT>(bufA, bufB, pl, tw);
-    float2* dst = p.spectra + (size_t)blockIdx.y * pl.N + (size_t)r0 * M;
+    float2* dst = p.spectra + (size_t)(p.first_bin + blockIdx.y) * pl.N + (size_t)r0 * M;
     {
         int b = threadIdx.x / M, m = threadIdx.x - b * M;
         for (int idx = threadIdx.x; idx < M * nb; idx += blockDim.x)
@@ -139,6 +134,13 @@ __global__ void __launch_bounds__(GB200_ACQ_THREADS)
 cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt)
 {
     cudaError_t e;
+    // the compile-time DIF tiles where the split has them (acq_inv.cu); the run-time parametrised kernels below otherwise
+    if (plan.inv_fast && !plan.fwd_generic)
+        {
+            e = gb_acq_forward_dif(plan, p, n_bins, wipeoff, st, launches, kt);
+            if (e != cudaErrorNotSupported) return e;
+            (void)cudaGetLastError();
+        }
     {
         const PlanDev pd = make_plan_dev(plan, true);
         const size_t sm = gb_acq_col_smem(plan);

@@ -141,6 +141,7 @@ struct GbFftPlan
     int inv_fast;   // 1: (N1, N2) has the compile-time in-place DIF inverse kernels (acq_dif.cuh)
     int inv_variant;  // which instantiation of the pair (GB200_ACQ_VARIANT, tuning only)
     int inv_tile1;  // columns per CTA of the inverse column kernel actually launched (sizes the per-CTA peak array)
+    int fwd_generic;  // 1: forward side on the run-time parametrised kernels even where the DIF tiles exist (tuning key "acq_fwd_generic")
     const float2* tw1;  // device: W_N1^i, i < N1 (forward sign)
     const float2* tw2;  // device: W_N2^i, i < N2
     const float2* twN;  // device: W_N^i, i < max(256, 16 * max(N1, N2)): the per-column part of the four-step twiddle
@@ -168,6 +169,7 @@ struct GbAcqFwdParams
     const int* seg_offsets;       // [bins + 1] offsets into segs
     float2* colbuf;        // [bins][N1][N2] scratch after the column stage
     float2* spectra;       // [bins][N1][N2] forward spectra, [k1][k2] layout
+    int first_bin = 0;     // this launch transforms bins first_bin .. first_bin + n_bins - 1 (the forward side runs in bin groups)
     int fold = 1;          // QuickSync: the wiped block is folded `fold` times onto the N-point FFT input (pcps_quicksync_acquisition_cc.cc:391-398)
 };
 
@@ -177,21 +179,40 @@ struct GbAcqInvParams
     const float2* const* code_fft;  // per handle: conj(FFT(code)) in [k1][k2] layout
     float2* rowbuf;                 // [transforms in chunk][N1][N2]
     int n_bins;
-    int first_transform;            // chunk offset; transform t = handle * n_bins + bin
+    int first_transform;            // chunk offset; transform t = handle * n_bins + bin, or bin * n_handles + handle when n_handles > 0
+    int n_handles = 0;              // > 0: bin-major transform order (chunks then need only the first bins' spectra: gb_acq_unit)
     int n_transforms;               // in this chunk
     int keep_offset;                // first kept output index (N/2 with bit_transition, else 0)
     int keep_len;                   // effective_fft_size
     float* const* grid;             // per handle: [bins][keep_len] magnitude grid or nullptr
     int accumulate;                 // dwell > 1: grid += mag
-    GbPeak* partial;                // [transform][tiles] per-CTA maxima (only when grid == nullptr)
+    GbPeak* partial;                // [handle][bin][tiles] per-CTA maxima (over the stored values where a grid is kept)
     float* const* tmpbuf;           // per handle d_tmp_buffer image or nullptr: receives the last bin's magnitudes when accumulating (:737)
     const float* scale;             // device scalar or nullptr: magnitudes are multiplied by it before they enter the grid (Tong detector)
 };
+
+#ifdef __CUDACC__
+// transform number -> (handle, bin) in either order
+__device__ __forceinline__ void gb_acq_unit(const GbAcqInvParams& p, int t, int& handle, int& bin)
+{
+    if (p.n_handles > 0)
+        {
+            bin = t / p.n_handles;
+            handle = t - bin * p.n_handles;
+        }
+    else
+        {
+            handle = t / p.n_bins;
+            bin = t - handle * p.n_bins;
+        }
+}
+#endif
 
 // per-kernel-class CUDA-event timing hooks (service.cu); `ctx` may be nullptr
 void gb_kt_begin(void* ctx, int kernel_class);
 void gb_kt_end(void* ctx);
 cudaError_t gb_acq_forward(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt);
+cudaError_t gb_acq_forward_dif(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt);  // acq_inv.cu
 cudaError_t gb_acq_inverse(const GbFftPlan& plan, const GbAcqInvParams& p, cudaStream_t st, int* launches, void* kt);
 size_t gb_acq_fused_ctl_bytes(int n_transforms);
 cudaError_t gb_acq_inverse_fused(const GbFftPlan& plan, const GbAcqInvParams& p, void* d_ctl, int lag, int ring, int sm_count, cudaStream_t st, int* launches, void* kt);

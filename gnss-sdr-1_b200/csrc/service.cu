@@ -128,9 +128,11 @@ struct GbTuning
     int chunk_t = 0;      // transforms per chunk (0: from l2_mb)
     int fused = 0;        // one persistent launch for the inverse side
     int fused_lag = 80, fused_ring = 176;
+    int fwd_groups = 4;   // bin groups of the forward side; > 1: bin-major transform order, inverse chunks start after the first group
     int split_n1 = 0;     // force N1 of the four-step split
     int variant = 0;      // alternative kernel instantiation of a split
     int generic = 0;      // run-time parametrised kernels only
+    int fwd_generic = 0;  // run-time parametrised kernels on the forward side only
     int host_threads = 8; // request staging threads of long tracking batches
     int trk_chunk_max = 32768;
     int trace = 0;
@@ -144,6 +146,7 @@ struct gb200_service
     cudaStream_t stream34[2] = {nullptr, nullptr};  // optional third / fourth lane (GB200_ACQ_LANES)
     cudaEvent_t ev_join34[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fwd[8] = {};  // one per forward bin group (recorded on the forward stream, stream34[0])
     cudaEvent_t ev_power_fork = nullptr;  // the input-power reduction runs on stream2 beside the forward transforms
     // Ingest runs on its own stream so that the H2D copy of block k+1 overlaps the kernels working on block k.  Ordering:
     // a consumer launch waits for the newest push of every ring (ev_pushed); a push waits for the newest consumer launch
@@ -298,6 +301,7 @@ extern "C" int gb200_service_create(const gb200_service_cfg* cfg, gb200_service*
         cudaEventCreateWithFlags(&s->ev_consumed, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&s->ev_power_fork, cudaEventDisableTiming) != cudaSuccess ||
+        ![&] { for (auto& e : s->ev_fwd) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return false; return true; }() ||
         cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming) != cudaSuccess)
         {
             g_global_error = "cudaStreamCreate failed";
@@ -343,6 +347,7 @@ extern "C" int gb200_service_destroy(gb200_service* s)
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->ev_power_fork) cudaEventDestroy(s->ev_power_fork);
+    for (auto& e : s->ev_fwd) if (e) cudaEventDestroy(e);
     if (s->ev_join) cudaEventDestroy(s->ev_join);
     if (s->stream2) cudaStreamDestroy(s->stream2);
     for (int k = 0; k < 2; k++)
@@ -548,8 +553,8 @@ extern "C" int gb200_service_flush_l2(gb200_service* s, size_t bytes)
 }
 
 // Tuning switches (profiling / experiments; every default is the measured best).  Keys: "acq_lanes" (1..4), "acq_l2_mb",
-// "acq_chunk_t", "acq_fused", "acq_fused_lag", "acq_fused_ring", "host_threads", "trk_chunk_max", "trace"; and, only before the
-// first acquisition handle of a given FFT length exists (they shape the cached plan): "acq_split_n1", "acq_variant", "acq_generic".
+// "acq_chunk_t", "acq_fused", "acq_fused_lag", "acq_fused_ring", "acq_fwd_groups" (1..8), "host_threads", "trk_chunk_max", "trace"; and, only before the
+// first acquisition handle of a given FFT length exists (they shape the cached plan): "acq_split_n1", "acq_variant", "acq_generic", "acq_fwd_generic".
 extern "C" int gb200_service_set_tuning(gb200_service* s, const char* key, int value)
 {
     if (!s || !key) return GB200_E_INVALID;
@@ -562,17 +567,18 @@ extern "C" int gb200_service_set_tuning(gb200_service* s, const char* key, int v
     else if (k == "acq_fused") t.fused = value;
     else if (k == "acq_fused_lag") t.fused_lag = value;
     else if (k == "acq_fused_ring") t.fused_ring = value;
+    else if (k == "acq_fwd_groups") t.fwd_groups = value;
     else if (k == "host_threads") t.host_threads = value;
     else if (k == "trk_chunk_max") t.trk_chunk_max = value;
     else if (k == "trace") t.trace = value;
-    else if (k == "acq_split_n1" || k == "acq_variant" || k == "acq_generic")
+    else if (k == "acq_split_n1" || k == "acq_variant" || k == "acq_generic" || k == "acq_fwd_generic")
         {
             if (!s->plans.empty())
                 {
                     s->set_error("gb200_service_set_tuning: " + k + " must be set before the first acquisition handle is created");
                     return GB200_E_STATE;
                 }
-            (k == "acq_split_n1" ? t.split_n1 : (k == "acq_variant" ? t.variant : t.generic)) = value;
+            (k == "acq_split_n1" ? t.split_n1 : (k == "acq_variant" ? t.variant : (k == "acq_generic" ? t.generic : t.fwd_generic))) = value;
         }
     else
         {
@@ -989,6 +995,7 @@ static int get_plan(gb200_service* s, int N, const GbFftPlan** out)
                 e.plan.inv_variant = variant;
                 e.plan.inv_tile1 = t1;
             }
+        e.plan.fwd_generic = s->tune.fwd_generic ? 1 : 0;
     }
     for (int which = 0; which < 4; which++)
         {
@@ -1705,16 +1712,6 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     GB_CUDA(s, cudaStreamWaitEvent(s->stream2, s->ev_power_fork, 0));
                     GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, power_n, d_power, nullptr, s->stream2, &l));
                 }
-            GbAcqFwdParams fp;
-            fp.samples = win;
-            fp.consumed = (int)a0->consumed;
-            fp.item_type = a0->c.item_type;
-            fp.segs = (const GbWipeSeg*)((char*)d_up + g.off_segs);
-            fp.seg_offsets = (const int*)((char*)d_up + g.off_segoff);
-            fp.colbuf = (float2*)d_col;
-            fp.spectra = (float2*)d_spec;
-            fp.fold = (int)a0->fold;
-            GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l, s));
             if (want_power && !power_aside)
                 {
                     GB_CUDA(s, gb_acq_input_power(win, (int)a0->consumed, a0->c.item_type, power_n, d_power, image ? a0->d_tmp : nullptr, s->stream, &l));
@@ -1758,6 +1755,38 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             // Opt-in (tuning key "acq_fused"): one persistent launch for the whole inverse side when there is a kernel for this plan
             // and mode (plain arg-max search); otherwise, and by default, chunks of transforms on the lanes below.
             const int fused_cfg = s->tune.fused, fused_lag = std::max(1, s->tune.fused_lag), fused_ring = std::max(2, s->tune.fused_ring);
+            GbAcqFwdParams fp;
+            fp.samples = win;
+            fp.consumed = (int)a0->consumed;
+            fp.item_type = a0->c.item_type;
+            fp.segs = (const GbWipeSeg*)((char*)d_up + g.off_segs);
+            fp.seg_offsets = (const int*)((char*)d_up + g.off_segoff);
+            fp.colbuf = (float2*)d_col;
+            fp.spectra = (float2*)d_spec;
+            fp.fold = (int)a0->fold;
+            // Forward side.  Default: in `fwd_groups` groups of bins on its own stream, the transforms numbered bin-major, so that the
+            // first inverse chunks (which then need only the first bins' spectra) start when the first group is done and the later
+            // groups -- launches too small to fill the GPU -- run beside them.  One launch pair on the main stream otherwise.
+            const int H = (int)g.members.size();
+            int fwd_groups = std::max(1, std::min(std::min(8, bins), s->tune.fwd_groups));
+            if (s->kt.enabled || fused_cfg || lanes_cfg > 2 || T <= chunkT) fwd_groups = 1;
+            const bool bin_major = fwd_groups > 1;
+            const int gbins = (bins + fwd_groups - 1) / fwd_groups;
+            if (bin_major) fwd_groups = (bins + gbins - 1) / gbins;
+            if (!bin_major)
+                GB_CUDA(s, gb_acq_forward(plan, fp, bins, true, s->stream, &l, s));
+            else
+                {
+                    cudaStream_t fs = s->stream34[0];
+                    GB_CUDA(s, cudaEventRecord(s->ev_fork, s->stream));
+                    GB_CUDA(s, cudaStreamWaitEvent(fs, s->ev_fork, 0));
+                    for (int gi = 0; gi < fwd_groups; gi++)
+                        {
+                            fp.first_bin = gi * gbins;
+                            GB_CUDA(s, gb_acq_forward(plan, fp, std::min(gbins, bins - fp.first_bin), true, fs, &l, s));
+                            GB_CUDA(s, cudaEventRecord(s->ev_fwd[gi], fs));
+                        }
+                }
             bool fused_done = false;
             if (fused_cfg && !g.grid)
                 {
@@ -1797,16 +1826,28 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
                     for (int k = 1; k < lanes; k++) GB_CUDA(s, cudaStreamWaitEvent(lane_stream[k], s->ev_fork, 0));
                 }
             int lane = 0;
+            int lane_seen[4] = {-1, -1, -1, -1};
             for (int t0 = fused_done ? T : 0; t0 < T; t0 += chunkT, lane = (lane + 1) % lanes)
                 {
                     const int ln = fork ? lane : 0;
+                    const int nT = std::min(chunkT, T - t0);
+                    if (bin_major)
+                        {
+                            const int need = std::min(fwd_groups - 1, ((t0 + nT - 1) / H) / gbins);  // last forward group this chunk reads
+                            if (need > lane_seen[ln])
+                                {
+                                    GB_CUDA(s, cudaStreamWaitEvent(lane_stream[ln], s->ev_fwd[need], 0));
+                                    lane_seen[ln] = need;
+                                }
+                        }
                     GbAcqInvParams ip;
                     ip.spectra = (const float2*)d_spec;
                     ip.code_fft = (const float2* const*)((char*)d_up + g.off_code);
                     ip.rowbuf = (float2*)d_rows[ln];
                     ip.n_bins = bins;
                     ip.first_transform = t0;
-                    ip.n_transforms = std::min(chunkT, T - t0);
+                    ip.n_transforms = nT;
+                    ip.n_handles = bin_major ? H : 0;
                     ip.keep_offset = a0->c.bit_transition_flag ? N / 2 : 0;
                     ip.keep_len = (int)a0->eff;
                     ip.grid = g.grid ? (float* const*)((char*)d_up + g.off_grid) : nullptr;
