@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(NT, OCC)
 {
     extern __shared__ __align__(16) float2 smem[];
     constexpr int M = DCOL::kM, TILE = 1 << LOGT, N = M * N2;
-    constexpr int RL = DCOL::kLastR, NIL = DCOL::kLastNI, S0 = M / DCOL::kFirstR;
+    constexpr int RL = DCOL::kLastR, NIL = DCOL::kLastNI;
     using L = GbTile<LOGT, NT>;
     constexpr int IL = 8, IH = (NIL + IL - 1) / IL;  // last-pass item i = IL * ih + il
     float2* buf = smem;
@@ -387,36 +387,55 @@ __global__ void __launch_bounds__(NT, OCC)
             nseg = __ldg(p.seg_offsets + bin + 1) - o0;
             segs = p.segs + o0;
         }
-    int lo = 0;
-    dif_first<-1, L, false, M, DCOL::kFirstR>(buf, pl.tw, [&](int b, int m1) {
-        const int n2 = c0 + b;
-        float2 x = make_float2(0.f, 0.f);
-        if ((N2 % TILE) != 0 && n2 >= N2) return x;
-        const int n = N2 * m1 + n2;
-        if (m1 < S0) lo = 0;  // first leg of a work item: the legs that follow come in increasing n
-        // fold == 1: one wiped sample.  QuickSync (fold > 1): the wiped samples n, n + N, n + 2N, ... added in that order onto a
-        // zeroed buffer in float32, as the block's std::transform(std::plus) passes do
-        for (int f = 0; f < p.fold; f++)
+    // Stage the wiped tile in shared memory first, every thread with all its loads in flight at once: legs fetched one by one
+    // inside the first butterfly pass (each behind the previous leg's segment walk and sincos) leave the kernel waiting on
+    // global-memory latency 16 times in a row.  The first pass then runs in place like a middle pass.
+    {
+        constexpr int TOTAL = M * TILE, ITERS = (TOTAL + NT - 1) / NT;
+        float2 raw[ITERS];
+#pragma unroll
+        for (int it = 0; it < ITERS; it++)
             {
-                const int m = n + f * N;
-                if (m >= p.consumed) break;
-                float2 v = gb_load_item<ITEM>(p.samples, (size_t)m);
-                if (wipeoff)
-                    {
-                        // last segment with n_start <= m: walked from the previous leg's segment (a bin has ~10 segments)
-                        while (lo + 1 < nseg && __ldg(&segs[lo + 1].n_start) <= m) lo++;
-                        while (lo > 0 && __ldg(&segs[lo].n_start) > m) lo--;
-                        const GbWipeSeg sg = segs[lo];
-                        const float ph = (float)fma((double)(m - sg.n_start), (double)sg.inc_eff, (double)sg.ph_start);  // exact
-                        float sn, cs;
-                        sincosf(ph, &sn, &cs);
-                        v = cmul(v, make_float2(cs, sn));
-                    }
-                x.x = __fadd_rn(x.x, v.x);
-                x.y = __fadd_rn(x.y, v.y);
+                const int idx = it * NT + (int)threadIdx.x;
+                const int b = idx & (TILE - 1), m1 = idx >> LOGT, n2 = c0 + b, n = N2 * m1 + n2;
+                raw[it] = make_float2(0.f, 0.f);
+                if (idx < TOTAL && ((N2 % TILE) == 0 || n2 < N2) && n < p.consumed) raw[it] = gb_load_item<ITEM>(p.samples, (size_t)n);
             }
-        return x;
-    });
+        int lo = 0;
+#pragma unroll
+        for (int it = 0; it < ITERS; it++)
+            {
+                const int idx = it * NT + (int)threadIdx.x;
+                const int b = idx & (TILE - 1), m1 = idx >> LOGT, n2 = c0 + b, n = N2 * m1 + n2;
+                if (idx >= TOTAL) break;
+                float2 x = make_float2(0.f, 0.f);
+                const bool inside = ((N2 % TILE) == 0 || n2 < N2);
+                // fold == 1: one wiped sample.  QuickSync (fold > 1): the wiped samples n, n + N, n + 2N, ... added in that order
+                // onto a zeroed buffer in float32, as the block's std::transform(std::plus) passes do
+                for (int f = 0; inside && f < p.fold; f++)
+                    {
+                        const int m = n + f * N;
+                        if (m >= p.consumed) break;
+                        float2 v = f == 0 ? raw[it] : gb_load_item<ITEM>(p.samples, (size_t)m);
+                        if (wipeoff)
+                            {
+                                // last segment with n_start <= m: a thread's samples come in increasing n, a bin has ~10 segments
+                                while (lo + 1 < nseg && __ldg(&segs[lo + 1].n_start) <= m) lo++;
+                                while (lo > 0 && __ldg(&segs[lo].n_start) > m) lo--;
+                                const GbWipeSeg sg = segs[lo];
+                                const float ph = (float)fma((double)(m - sg.n_start), (double)sg.inc_eff, (double)sg.ph_start);  // exact
+                                float sn, cs;
+                                sincosf(ph, &sn, &cs);
+                                v = cmul(v, make_float2(cs, sn));
+                            }
+                        x.x = __fadd_rn(x.x, v.x);
+                        x.y = __fadd_rn(x.y, v.y);
+                    }
+                buf[b + m1 * L::MS] = x;
+            }
+    }
+    __syncthreads();
+    dif_mid<-1, L, M, M, DCOL::kFirstR>(buf, tw);
     __syncthreads();
     float2* dst = p.colbuf + (size_t)bin * N;
     DCOL::template run_rest<-1, L, false>(buf, tw, [&](int b, int i, const float2* v) {

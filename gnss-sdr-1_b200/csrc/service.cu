@@ -128,7 +128,8 @@ struct GbTuning
     int chunk_t = 0;      // transforms per chunk (0: from l2_mb)
     int fused = 0;        // one persistent launch for the inverse side
     int fused_lag = 80, fused_ring = 176;
-    int fwd_groups = 4;   // bin groups of the forward side; > 1: bin-major transform order, inverse chunks start after the first group
+    int fwd_groups = 1;   // bin groups of the forward side; > 1: bin-major transform order, inverse chunks start after the first group
+                          // (measured: no gain at C2 / C5, a loss on small batches -- profiles/r02_acq_fwd_sweep.txt)
     int split_n1 = 0;     // force N1 of the four-step split
     int variant = 0;      // alternative kernel instantiation of a split
     int generic = 0;      // run-time parametrised kernels only
@@ -1764,9 +1765,10 @@ extern "C" int gb200_acq_launch_batch(gb200_acq* const* list, int n, int stream_
             fp.colbuf = (float2*)d_col;
             fp.spectra = (float2*)d_spec;
             fp.fold = (int)a0->fold;
-            // Forward side.  Default: in `fwd_groups` groups of bins on its own stream, the transforms numbered bin-major, so that the
-            // first inverse chunks (which then need only the first bins' spectra) start when the first group is done and the later
-            // groups -- launches too small to fill the GPU -- run beside them.  One launch pair on the main stream otherwise.
+            // Forward side: one launch pair on the main stream.  Tuning key "acq_fwd_groups" > 1: in that many groups of bins on its own
+            // stream, the transforms numbered bin-major, so that the first inverse chunks (which then need only the first bins'
+            // spectra) start when the first group is done and the later groups run beside them -- the step is bound by the sum of
+            // the kernels' work, not by the forward side's latency, so this buys nothing measurable and stays off.
             const int H = (int)g.members.size();
             int fwd_groups = std::max(1, std::min(std::min(8, bins), s->tune.fwd_groups));
             if (s->kt.enabled || fused_cfg || lanes_cfg > 2 || T <= chunkT) fwd_groups = 1;

@@ -446,6 +446,24 @@ def test_fused_persistent_inverse_matches_default_path():
     assert " passed" in r.stdout
 
 
+@pytest.mark.parametrize("tune", ["acq_fwd_groups=4,acq_chunk_t=3", "acq_fwd_generic=1"])
+def test_forward_side_options_match_default_path(tune):
+    """Tuning keys of the forward side, each in a child process steered by GB200_TUNE running this file's batch-search parity tests
+    against the oracle: acq_fwd_groups > 1 (forward transforms in bin groups on their own stream, transforms numbered bin-major,
+    inverse chunks waiting only for the groups they read; acq_chunk_t=3 forces several chunks on the small test grids) and
+    acq_fwd_generic=1 (the run-time parametrised forward kernels where the compile-time DIF tiles would be used)."""
+    import subprocess
+    import sys as _sys
+
+    env = dict(os.environ, GB200_TUNE=tune)
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([_sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_acquisition.py"), "-m", "gpu", "-x", "-q", "-k",
+                        "not fused and not forward_side and (fixture or batch or fast_inverse or ties or odd_lengths or zero_padded or bin_range or multi_dwell)"], env=env,
+                       capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
+
+
 def test_real_capture_all_gps_prns(service, golden_dir):
     """The reference's real-signal fixture (src/tests/signal_samples/GSoC_CTTC_capture_2012_07_26_4Msps_4ms.dat: USRP1 roof capture;
     GPS PRN 29 and 25 stand out near +9.75 / +9 kHz, the front end's clock offset included): all 32 GPS PRNs searched in one
