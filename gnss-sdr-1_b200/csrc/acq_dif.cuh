@@ -101,8 +101,14 @@ __device__ __forceinline__ void bflyx(float2* v)
 // With an odd element stride both access directions are bank-conflict free for 8-byte words: lanes along b (stride 1)
 // and lanes along m (stride MS = 1 mod 16).  Work items (i, b) are mapped to threads either b-fastest (column kernels: a
 // global row of TILE consecutive columns per instruction) or i-fastest (row kernels' first and last pass: consecutive
-// elements of one contiguous sub-transform per instruction; i is padded to a multiple of 16 so a half-warp never
-// straddles two sub-transforms).
+// elements of one contiguous sub-transform per instruction; i is padded to a multiple of GB_IFAST_PAD so a quarter-warp
+// never straddles two sub-transforms).
+// i-fastest maps pad the item count of one sub-transform to a multiple of this.  16 (a half-warp never straddles two
+// sub-transforms) leaves 8 of 48 last-pass lanes idle at M = 200; 8 measured 2.4 % faster at C2, 1 % at C3, 0.8 % slower at C5;
+// 4 and 1 (no padding) lose to shared-memory conflicts (profiles/r02_acq_fwd_sweep.txt)
+#ifndef GB_IFAST_PAD
+#define GB_IFAST_PAD 8
+#endif
 template <int LOGT, int NT_>
 struct GbTile
 {
@@ -113,7 +119,7 @@ struct GbTile
     template <int NI, bool IFAST>
     struct Map
     {
-        static constexpr int NIP = IFAST ? ((NI + 15) & ~15) : NI;
+        static constexpr int NIP = IFAST ? ((NI + GB_IFAST_PAD - 1) / GB_IFAST_PAD * GB_IFAST_PAD) : NI;
         static constexpr int TOTAL = NIP * TILE;
         static constexpr bool kExact = (NIP == NI) && (TOTAL % NT_) == 0;
         static __device__ __forceinline__ bool split(int idx, int& i, int& b)
