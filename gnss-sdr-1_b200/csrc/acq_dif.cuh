@@ -86,13 +86,78 @@ __device__ __forceinline__ void bfly10(float2* v)
         }
 }
 
+// radix 25 = 5 x 5: x[5a+b] -> X[k1 + 5 k2]
+template <int SIGN>
+__device__ __forceinline__ void bfly25(float2* v)
+{
+    // W_25^m, m = b k1: (cos, sin)(2 pi m / 25)
+    constexpr float C[17] = {1.f, 0.96858316112863107605f, 0.87630668004386358394f, 0.72896862742141155245f, 0.53582679497899654564f, 0.f,
+        0.06279051952931352654f, 0.f, -0.42577929156507271502f, -0.63742398974868974548f, 0.f, 0.f, -0.99211470131447776488f, 0.f, 0.f, 0.f,
+        -0.63742398974868952344f};
+    constexpr float S[17] = {0.f, 0.24868988716485479484f, 0.48175367410171532345f, 0.68454710592868861507f, 0.84432792550201507531f, 0.f,
+        0.99802672842827155897f, 0.f, 0.90482705246601946580f, 0.77051324277578925326f, 0.f, 0.f, 0.12533323356430453588f, 0.f, 0.f, 0.f,
+        -0.77051324277578936428f};
+#pragma unroll
+    for (int b = 0; b < 5; b++)
+        {
+            float2 u[5] = {v[b], v[5 + b], v[10 + b], v[15 + b], v[20 + b]};
+            bfly5<SIGN>(u);  // over a; u[k1]
+#pragma unroll
+            for (int k1 = 0; k1 < 5; k1++) v[5 * k1 + b] = (b == 0 || k1 == 0) ? u[k1] : cmul_const<SIGN>(u[k1], C[b * k1], S[b * k1]);  // t[k1][b]
+        }
+    float2 t[5][5];
+#pragma unroll
+    for (int k1 = 0; k1 < 5; k1++)
+        {
+#pragma unroll
+            for (int b = 0; b < 5; b++) t[k1][b] = v[5 * k1 + b];
+            bfly5<SIGN>(t[k1]);  // over b; t[k1][k2]
+        }
+#pragma unroll
+    for (int k1 = 0; k1 < 5; k1++)
+#pragma unroll
+        for (int k2 = 0; k2 < 5; k2++) v[k1 + 5 * k2] = t[k1][k2];
+}
+
+// radix 20 = 4 x 5: x[5a+b] (a < 4, b < 5) -> X[k1 + 4 k2]
+template <int SIGN>
+__device__ __forceinline__ void bfly20(float2* v)
+{
+    // W_20^m, m = b k1: (cos, sin)(2 pi m / 20)
+    constexpr float C[13] = {1.f, 0.95105651629515353118f, 0.80901699437494745126f, 0.58778525229247313710f, 0.30901699437494745126f, 0.f,
+        -0.30901699437494734024f, 0.f, -0.80901699437494734024f, -0.95105651629515353118f, 0.f, 0.f, -0.80901699437494756229f};
+    constexpr float S[13] = {0.f, 0.30901699437494739575f, 0.58778525229247313710f, 0.80901699437494745126f, 0.95105651629515353118f, 0.f,
+        0.95105651629515364220f, 0.f, 0.58778525229247324813f, 0.30901699437494750677f, 0.f, 0.f, -0.58778525229247302608f};
+    float2 t[4][5];
+#pragma unroll
+    for (int b = 0; b < 5; b++)
+        {
+            float2 u[4] = {v[b], v[5 + b], v[10 + b], v[15 + b]};
+            bfly4<SIGN>(u);  // over a; u[k1]
+#pragma unroll
+            for (int k1 = 0; k1 < 4; k1++) t[k1][b] = (b == 0 || k1 == 0) ? u[k1] : cmul_const<SIGN>(u[k1], C[b * k1], S[b * k1]);
+        }
+#pragma unroll
+    for (int k1 = 0; k1 < 4; k1++)
+        {
+            bfly5<SIGN>(t[k1]);  // over b; t[k1][k2]
+#pragma unroll
+            for (int k2 = 0; k2 < 5; k2++) v[k1 + 4 * k2] = t[k1][k2];
+        }
+}
+
 template <int SIGN, int R>
 __device__ __forceinline__ void bflyx(float2* v)
 {
+    static_assert(R == 2 || R == 3 || R == 4 || R == 5 || R == 8 || R == 10 || R == 16 || R == 20 || R == 25, "no butterfly for this radix");
     if (R == 10)
         bfly10<SIGN>(v);
     else if (R == 16)
         bfly16<SIGN>(v);
+    else if (R == 20)
+        bfly20<SIGN>(v);
+    else if (R == 25)
+        bfly25<SIGN>(v);
     else
         bfly<SIGN, R>(v);
 }

@@ -11,6 +11,9 @@ import gnss_b200 as gb  # noqa: E402
 
 # ACQ_SWEEP_CFG=C2 (default) | C3 | C5: FFT length, handles, item type, Doppler span, CFAR flag of the BASELINE config
 CFG = {"C2": (32000, 32, "16ic", 10000, 8000000, 4, 1), "C3": (25000, 12, "32fc", 5000, 25000000, 1, 0), "C5": (200000, 8, "32fc", 10000, 50000000, 4, 1)}[os.environ.get("ACQ_SWEEP_CFG", "C2")]
+if os.environ.get("ACQ_SWEEP_N"):  # any other FFT length: 8 handles, 1 ms at N ksps, +-5 kHz / 250 Hz, CFAR, gr_complex
+    n_ = int(os.environ["ACQ_SWEEP_N"])
+    CFG = (n_, 8, "32fc", 5000, n_ * 1000, 1, 1)
 N, PRNS = CFG[0], CFG[1]
 
 
