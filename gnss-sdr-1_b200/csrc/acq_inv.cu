@@ -1,5 +1,6 @@
 // Inverse side of the PCPS acquisition search (x conj(code DFT), inverse DFT, |.|^2, arg-max), once per (PRN, Doppler bin).
 #include "acq_dif.cuh"
+#include "acq_pairs.cuh"
 #include <algorithm>
 
 namespace
@@ -346,141 +347,6 @@ __global__ void __launch_bounds__(NT, OCC)
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Forward side on the same in-place DIF tiles (the sample block's spectrum once per Doppler bin, and the local code's).
-//
-// columns: x[N2 n1 + n2] x wipe-off -> DFT over n1 -> x W_N^(n2 k1) -> colbuf[k1][n2]   (tile of columns c0 .. c0+TILE)
-template <int ITEM, int LOGT, int NT, int OCC, class DCOL, int N2>
-__global__ void __launch_bounds__(NT, OCC)
-    gb_acq_fwd_col_dif(PlanDev pl, GbAcqFwdParams p, int wipeoff)
-{
-    extern __shared__ __align__(16) float2 smem[];
-    constexpr int M = DCOL::kM, TILE = 1 << LOGT, N = M * N2;
-    constexpr int RL = DCOL::kLastR, NIL = DCOL::kLastNI;
-    using L = GbTile<LOGT, NT>;
-    constexpr int IL = 8, IH = (NIL + IL - 1) / IL;  // last-pass item i = IL * ih + il
-    float2* buf = smem;
-    float2* tw = buf + L::size(M);
-    float2* step = tw + M;          // [TILE]      W_N^(n2 NIL): ratio between consecutive outputs of one item
-    float2* tlo = step + TILE;      // [TILE][IL]  W_N^(n2 il)
-    float2* thi = tlo + TILE * IL;  // [TILE][IH]  W_N^(n2 IL ih)      (n2 = c0 + b)
-    const int c0 = blockIdx.x << LOGT;
-    const int bin = p.first_bin + blockIdx.y;
-    for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
-    for (int q = threadIdx.x; q < TILE * (1 + IL + IH); q += NT)
-        {
-            const int b = q / (1 + IL + IH), c = q - b * (1 + IL + IH);
-            const unsigned n2 = (unsigned)(c0 + b);
-            const unsigned e = (c == 0 ? n2 * (unsigned)NIL : (c <= IL ? n2 * (unsigned)(c - 1) : n2 * (unsigned)(IL * (c - 1 - IL)))) % (unsigned)N;
-            const float2 w = cmul(__ldg(pl.twN + (e & 255u)), __ldg(pl.twNhi + (e >> 8)));
-            if (c == 0)
-                step[b] = w;
-            else if (c <= IL)
-                tlo[b * IL + c - 1] = w;
-            else
-                thi[b * IH + c - 1 - IL] = w;
-        }
-    const GbWipeSeg* segs = nullptr;
-    int nseg = 0;
-    if (wipeoff)
-        {
-            const int o0 = __ldg(p.seg_offsets + bin);
-            nseg = __ldg(p.seg_offsets + bin + 1) - o0;
-            segs = p.segs + o0;
-        }
-    // Stage the wiped tile in shared memory first, every thread with all its loads in flight at once: legs fetched one by one
-    // inside the first butterfly pass (each behind the previous leg's segment walk and sincos) leave the kernel waiting on
-    // global-memory latency 16 times in a row.  The first pass then runs in place like a middle pass.
-    {
-        constexpr int TOTAL = M * TILE, ITERS = (TOTAL + NT - 1) / NT;
-        float2 raw[ITERS];
-#pragma unroll
-        for (int it = 0; it < ITERS; it++)
-            {
-                const int idx = it * NT + (int)threadIdx.x;
-                const int b = idx & (TILE - 1), m1 = idx >> LOGT, n2 = c0 + b, n = N2 * m1 + n2;
-                raw[it] = make_float2(0.f, 0.f);
-                if (idx < TOTAL && ((N2 % TILE) == 0 || n2 < N2) && n < p.consumed) raw[it] = gb_load_item<ITEM>(p.samples, (size_t)n);
-            }
-        int lo = 0;
-#pragma unroll
-        for (int it = 0; it < ITERS; it++)
-            {
-                const int idx = it * NT + (int)threadIdx.x;
-                const int b = idx & (TILE - 1), m1 = idx >> LOGT, n2 = c0 + b, n = N2 * m1 + n2;
-                if (idx >= TOTAL) break;
-                float2 x = make_float2(0.f, 0.f);
-                const bool inside = ((N2 % TILE) == 0 || n2 < N2);
-                // fold == 1: one wiped sample.  QuickSync (fold > 1): the wiped samples n, n + N, n + 2N, ... added in that order
-                // onto a zeroed buffer in float32, as the block's std::transform(std::plus) passes do
-                for (int f = 0; inside && f < p.fold; f++)
-                    {
-                        const int m = n + f * N;
-                        if (m >= p.consumed) break;
-                        float2 v = f == 0 ? raw[it] : gb_load_item<ITEM>(p.samples, (size_t)m);
-                        if (wipeoff)
-                            {
-                                // last segment with n_start <= m: a thread's samples come in increasing n, a bin has ~10 segments
-                                while (lo + 1 < nseg && __ldg(&segs[lo + 1].n_start) <= m) lo++;
-                                while (lo > 0 && __ldg(&segs[lo].n_start) > m) lo--;
-                                const GbWipeSeg sg = segs[lo];
-                                const float ph = (float)fma((double)(m - sg.n_start), (double)sg.inc_eff, (double)sg.ph_start);  // exact
-                                float sn, cs;
-                                sincosf(ph, &sn, &cs);
-                                v = cmul(v, make_float2(cs, sn));
-                            }
-                        x.x = __fadd_rn(x.x, v.x);
-                        x.y = __fadd_rn(x.y, v.y);
-                    }
-                buf[b + m1 * L::MS] = x;
-            }
-    }
-    __syncthreads();
-    dif_mid<-1, L, M, M, DCOL::kFirstR>(buf, tw);
-    __syncthreads();
-    float2* dst = p.colbuf + (size_t)bin * N;
-    DCOL::template run_rest<-1, L, false>(buf, tw, [&](int b, int i, const float2* v) {
-        const int n2 = c0 + b;
-        if ((N2 % TILE) != 0 && n2 >= N2) return;
-        float2 w = cmul(tlo[b * IL + (i & (IL - 1))], thi[b * IH + (i / IL)]);  // W_N^(n2 i)
-        const float2 ws = step[b];
-        float2* d = dst + (size_t)i * N2 + n2;
-#pragma unroll
-        for (int r = 0; r < RL; r++)
-            {
-                d[(size_t)r * NIL * N2] = cmul(v[r], w);
-                if (r + 1 < RL) w = cmul(w, ws);
-            }
-    });
-}
-
-// rows: colbuf[k1][n2] -> DFT over n2 -> spectra[k1][k2]   (tile of rows r0 .. r0+TILE)
-template <int LOGT, int NT, int OCC, class DROW, int N1>
-__global__ void __launch_bounds__(NT, OCC)
-    gb_acq_fwd_row_dif(PlanDev pl, GbAcqFwdParams p)
-{
-    extern __shared__ __align__(16) float2 smem[];
-    constexpr int M = DROW::kM, TILE = 1 << LOGT, N = N1 * M;
-    constexpr int RL = DROW::kLastR, NIL = DROW::kLastNI;
-    using L = GbTile<LOGT, NT>;
-    float2* buf = smem;
-    float2* tw = buf + L::size(M);
-    const int r0 = blockIdx.x << LOGT;
-    const int nb = min(TILE, N1 - r0);
-    const size_t off = (size_t)(p.first_bin + blockIdx.y) * N + (size_t)r0 * M;
-    for (int i = threadIdx.x; i < M; i += NT) tw[i] = __ldg(pl.tw + i);
-    const float2* src = p.colbuf + off;
-    dif_first<-1, L, true, M, DROW::kFirstR>(buf, pl.tw, [&](int b, int m) { return b < nb ? __ldg(src + b * M + m) : make_float2(0.f, 0.f); });
-    __syncthreads();
-    float2* dst = p.spectra + off;
-    DROW::template run_rest<-1, L, true>(buf, tw, [&](int b, int i, const float2* v) {
-        if (b >= nb) return;
-        float2* d = dst + b * M + i;
-#pragma unroll
-        for (int r = 0; r < RL; r++) d[r * NIL] = v[r];
-    });
-}
-
-// ---------------------------------------------------------------------------------------------------------------
 // One persistent launch for the whole inverse side of a dwell (opt-in: GB200_ACQ_FUSED=1; measured 0.483 ms against the
 // two-lane pipeline's ~0.49 ms at C2, profiles/r01_acq_fused_persistent.txt -- parity-tested, not yet faster, kept as the
 // base of the next round's work).  Every launch of the two kernels above pays about one
@@ -564,87 +430,6 @@ __global__ void __launch_bounds__(NT, OCC)
         }
 }
 
-// The (N1, N2) pairs with a fast path.  f(GbDif<N1...>{}, GbDif<N2...>{}, column-kernel config, row-kernel config);
-// a config is GbCfg<LOGT, NT, OCC>: tile (columns / rows per CTA) = 2^LOGT, threads per CTA, CTAs per SM the register
-// allocation is bounded for.  `variant` selects among alternative instantiations of one pair (tuning; 0 = default).
-template <int LOGT_, int NT_, int OCC_>
-struct GbCfg
-{
-    static constexpr int LOGT = LOGT_, NT = NT_, OCC = OCC_;
-};
-
-template <class F>
-bool gb_with_dif_pair(int N1, int N2, int variant, F&& f)
-{
-#define GB_C ,
-#define GB_DIF_PAIR(n1, n2, var, D1, D2, C1, C2)      \
-    if (N1 == n1 && N2 == n2 && variant == var)       \
-        {                                             \
-            f(D1{}, D2{}, C1{}, C2{});                \
-            return true;                              \
-        }
-    using D50 = GbDif<50, 10, 5>;
-    using D80 = GbDif<80, 16, 5>;
-    using D100 = GbDif<100, 10, 10>;
-    using D125 = GbDif<125, 5, 5, 5>;
-    using D128 = GbDif<128, 16, 8>;
-    using D160 = GbDif<160, 16, 10>;
-    using D160c = GbDif<160, 10, 16>;
-    using D200 = GbDif<200, 8, 5, 5>;
-    using D200c = GbDif<200, 5, 8, 5>;
-    using D250 = GbDif<250, 10, 5, 5>;
-    using D256 = GbDif<256, 16, 16>;
-    using D125c = GbDif<125, 5, 25>;
-    using D200e = GbDif<200, 8, 25>;
-    using D200f = GbDif<200, 10, 20>;
-    using D250e = GbDif<250, 10, 25>;
-    using D320e = GbDif<320, 16, 20>;
-    using D400e = GbDif<400, 16, 25>;
-    using D400f = GbDif<400, 20, 20>;
-    using D500e = GbDif<500, 20, 25>;
-    using D320 = GbDif<320, 8, 8, 5>;
-    using D400 = GbDif<400, 16, 5, 5>;
-    using D500 = GbDif<500, 10, 10, 5>;
-    using S128 = GbCfg<4, 128, 8>;
-    using S256 = GbCfg<4, 256, 4>;
-    using E256 = GbCfg<3, 256, 4>;
-    using S256o5 = GbCfg<4, 256, 5>;
-    using S256o3 = GbCfg<4, 256, 3>;
-    using E128 = GbCfg<3, 128, 8>;
-    using T256 = GbCfg<5, 256, 4>;
-    // Default (variant 0) of every pair: as few passes as the butterflies allow -- each pass is a shared-memory round trip, a
-    // barrier and a table of twiddles; two passes with a radix-20 / 25 last butterfly in registers beat three passes by
-    // 9 .. 24 % per step (profiles/r02_acq_fwd_sweep.txt).  The exception is the 125-point COLUMN transform: with 8 columns
-    // per CTA a 25 x 5 or 5 x 25 split leaves most threads without a first- or last-pass item.
-    GB_DIF_PAIR(50, 80, 0, D50, D80, S128, S128)       // 4000   GPS L1 C/A 1 ms @ 4 Msps
-    GB_DIF_PAIR(80, 100, 0, D80, D100, S128, S128)     // 8000
-    GB_DIF_PAIR(125, 128, 0, D125, D128, S256, S256)   // 16000
-    GB_DIF_PAIR(125, 160, 0, D125, D160, S256, S256)   // 20000
-    GB_DIF_PAIR(125, 200, 0, D125, D200e, E256, S256)  // 25000  GPS L5 / Galileo E5a 1 ms @ 25 Msps: rows 8 x 25
-    GB_DIF_PAIR(125, 200, 1, D125, D200, E256, S256)   // rows 8 x 5 x 5 (1.7 % slower at C3)
-    GB_DIF_PAIR(125, 200, 2, D125c, D200e, E256, S256) // columns 5 x 25 (30 % slower; 25 x 5: 14 % slower)
-    GB_DIF_PAIR(125, 256, 0, D125, D256, S256, S256)   // 32000, alternative split (tuning key acq_split_n1=125): 2 KB rows, 128 B aligned, but the 16x16 row passes conflict in shared memory
-    GB_DIF_PAIR(125, 256, 1, D125, D256, S256o5, S256)
-    GB_DIF_PAIR(160, 200, 0, D160c, D200e, S256, S256)  // 32000  Galileo E1 4 ms @ 8 Msps: columns 10 x 16, rows 8 x 25
-    GB_DIF_PAIR(160, 200, 1, D160, D200, S256, S256)    // columns 16 x 10, rows 8 x 5 x 5: the default until the last session of round 2 (11 % slower at C2)
-    GB_DIF_PAIR(160, 200, 2, D160c, D200, S256, S256)   // rows 8 x 5 x 5 (9.5 % slower)
-    GB_DIF_PAIR(160, 200, 3, D160c, D200e, S256, T256)  // row tiles of 32 rows (15 % slower)
-    GB_DIF_PAIR(160, 200, 4, D160c, D200f, S256, S256)  // rows 10 x 20 (19 % slower)
-    GB_DIF_PAIR(160, 200, 5, D160c, D200c, S256, S256)  // rows 5 x 8 x 5
-    GB_DIF_PAIR(160, 200, 6, D160c, D200e, S256, S256o3)
-    GB_DIF_PAIR(160, 200, 7, D160, D200, E128, E128)
-    GB_DIF_PAIR(200, 200, 0, D200e, D200e, E256, S256) // 40000
-    GB_DIF_PAIR(200, 200, 1, D200, D200, E256, S256)   // 8 x 5 x 5 both ways (15 % slower)
-    GB_DIF_PAIR(200, 250, 0, D200e, D250e, E256, E256) // 50000
-    GB_DIF_PAIR(200, 250, 1, D200, D250, E256, E256)   // three passes both ways (13.5 % slower)
-    GB_DIF_PAIR(250, 320, 0, D250e, D320e, E256, E256) // 80000: 10 x 25, 16 x 20
-    GB_DIF_PAIR(250, 320, 1, D250, D320, E256, E256)   // three passes both ways (18 % slower)
-    GB_DIF_PAIR(400, 500, 0, D400e, D500e, E256, E256) // 200000: columns 16 x 25, rows 20 x 25
-    GB_DIF_PAIR(400, 500, 1, D400, D500, E256, E256)   // 16 x 5 x 5, 10 x 10 x 5: the default until the last session of round 2 (24 % slower at C5)
-    GB_DIF_PAIR(400, 500, 2, D400f, D500e, E256, E256) // columns 20 x 20: as fast as 16 x 25
-#undef GB_DIF_PAIR
-    return false;
-}
 }  // namespace
 
 // (N1, N2) splits with a fast path, in order of preference for a given N = N1 * N2
@@ -703,53 +488,6 @@ cudaError_t gb_acq_inverse_fused(const GbFftPlan& plan, const GbAcqInvParams& p,
                 e = cudaGetLastError();
                 if (e == cudaSuccess && launches) (*launches)++;
             }
-    });
-    return e;
-}
-
-// Forward side on the DIF tiles; cudaErrorNotSupported when the plan has no such pair (the caller then runs the run-time
-// parametrised kernels of acq_fwd.cu)
-cudaError_t gb_acq_forward_dif(const GbFftPlan& plan, const GbAcqFwdParams& p, int n_bins, bool wipeoff, cudaStream_t st, int* launches, void* kt)
-{
-    if (!plan.inv_fast) return cudaErrorNotSupported;
-    cudaError_t e = cudaErrorNotSupported;
-    const PlanDev pdr = make_plan_dev(plan, false), pdc = make_plan_dev(plan, true);
-    gb_with_dif_pair(plan.N1, plan.N2, plan.inv_variant, [&](auto d1, auto d2, auto c1, auto c2) {
-        using D1 = decltype(d1);
-        using D2 = decltype(d2);
-        using C1 = decltype(c1);
-        using C2 = decltype(c2);
-        constexpr int LT1 = C1::LOGT, LT2 = C2::LOGT, NT1 = C1::NT, NT2 = C2::NT;
-        constexpr int T1 = 1 << LT1, T2 = 1 << LT2;
-        {
-            auto k = p.item_type == GB200_ITEM_32FC ? gb_acq_fwd_col_dif<GB200_ITEM_32FC, LT1, NT1, C1::OCC, D1, D2::kM>
-                                                    : (p.item_type == GB200_ITEM_16IC ? gb_acq_fwd_col_dif<GB200_ITEM_16IC, LT1, NT1, C1::OCC, D1, D2::kM>
-                                                                                      : gb_acq_fwd_col_dif<GB200_ITEM_8IC, LT1, NT1, C1::OCC, D1, D2::kM>);
-            if (p.item_type != GB200_ITEM_32FC && p.item_type != GB200_ITEM_16IC && p.item_type != GB200_ITEM_8IC)
-                {
-                    e = cudaErrorInvalidValue;
-                    return;
-                }
-            const size_t sm = (GbTile<LT1, NT1>::size(D1::kM) + D1::kM + T1 * (1 + 8 + (D1::kLastNI + 7) / 8)) * sizeof(float2);
-            if ((e = set_smem(k, sm)) != cudaSuccess) return;
-            const dim3 grid((D2::kM + T1 - 1) / T1, n_bins);
-            if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_FWD_COL);
-            k<<<grid, NT1, sm, st>>>(pdc, p, wipeoff ? 1 : 0);
-            if (kt) gb_kt_end(kt);
-            if ((e = cudaGetLastError()) != cudaSuccess) return;
-            if (launches) (*launches)++;
-        }
-        {
-            auto k = gb_acq_fwd_row_dif<LT2, NT2, C2::OCC, D2, D1::kM>;
-            const size_t sm = (GbTile<LT2, NT2>::size(D2::kM) + D2::kM) * sizeof(float2);
-            if ((e = set_smem(k, sm)) != cudaSuccess) return;
-            const dim3 grid((D1::kM + T2 - 1) / T2, n_bins);
-            if (kt) gb_kt_begin(kt, GB200_KCLASS_ACQ_FWD_ROW);
-            k<<<grid, NT2, sm, st>>>(pdr, p);
-            if (kt) gb_kt_end(kt);
-            if ((e = cudaGetLastError()) != cudaSuccess) return;
-            if (launches) (*launches)++;
-        }
     });
     return e;
 }
