@@ -174,6 +174,9 @@ __device__ __forceinline__ void bflyx(float2* v)
 #ifndef GB_IFAST_PAD
 #define GB_IFAST_PAD 8
 #endif
+#ifndef GB_IFAST_BPERM
+#define GB_IFAST_BPERM 1
+#endif
 template <int LOGT, int NT_>
 struct GbTile
 {
@@ -193,6 +196,9 @@ struct GbTile
                 {
                     b = (int)((unsigned)idx / (unsigned)NIP);
                     i = idx - b * NIP;
+                    // 8 items per sub-transform: a half-warp holds two sub-transforms.  With the odd pitch, neighbours b, b + 1 collide
+                    // in one bank pair (items 7 and 0); b and b + TILE/2 never do -- pair those (any bijection of b is valid here)
+                    if (GB_IFAST_BPERM && NIP == 8 && TILE == 16) b = ((b & 1) << 3) | (b >> 1);
                     return (kExact || idx < TOTAL) && (NIP == NI || i < NI);
                 }
             b = idx & (TILE - 1);
