@@ -92,9 +92,11 @@ GB200_API int gb200_service_acq_coalescing_stats(gb200_service* s, uint64_t* bat
 
 /* Tuning switches for profiling and experiments (every default is the measured best); no counterpart in the reference.
  * Keys: "acq_lanes" (1..4 streams the inverse chunks alternate on), "acq_l2_mb" (row-buffer budget), "acq_chunk_t" (transforms
- * per chunk), "acq_fused" (one persistent launch for the inverse side), "acq_fused_lag", "acq_fused_ring", "host_threads",
- * "trk_chunk_max", "trace"; and, only before the first acquisition handle exists (they shape the cached FFT plans),
- * "acq_split_n1", "acq_variant", "acq_generic".  Unknown key -> GB200_E_INVALID. */
+ * per chunk), "acq_fused" (one persistent launch for the inverse side), "acq_fused_lag", "acq_fused_ring", "acq_fwd_groups"
+ * (1..8: forward transforms in bin groups on their own stream, bin-major inverse chunks), "host_threads", "trk_chunk_max",
+ * "trace"; and, only before the first acquisition handle exists (they shape the cached FFT plans), "acq_split_n1",
+ * "acq_variant" (alternative radix orders of a split), "acq_generic", "acq_fwd_generic" (run-time parametrised kernels on both
+ * sides / on the forward side only).  Unknown key -> GB200_E_INVALID. */
 GB200_API int gb200_service_set_tuning(gb200_service* s, const char* key, int value);
 
 /* Hand a block of the conditioned sample stream to the device ONCE for all channels.  Replaces each
