@@ -278,7 +278,8 @@ __device__ __forceinline__ void gb_inv_col_tile(float2* smem, float* s_mag, unsi
             {
                 const int n = nbase + r * (NIL * N2);
                 if (MODE != 0 && (n < 0 || n >= p.keep_len)) continue;
-                float mag = __fadd_rn(__fmul_rn(v[r].x, v[r].x), __fmul_rn(v[r].y, v[r].y));  // volk_32fc_magnitude_squared_32f
+                const float2 sq = upk2(mul2x(pk2(v[r]), pk2(v[r])));  // both squares in one packed multiply (each lane rounds like __fmul_rn)
+                float mag = __fadd_rn(sq.x, sq.y);                    // volk_32fc_magnitude_squared_32f
                 if (MODE == 2)
                     {
                         if (p.scale) mag = __fmul_rn(mag, __ldg(p.scale));  // volk_32f_s32f_multiply_32f
