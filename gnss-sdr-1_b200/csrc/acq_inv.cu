@@ -273,6 +273,7 @@ __device__ __forceinline__ void gb_inv_col_tile(float2* smem, float* s_mag, unsi
         const int nbase = N2 * i + c0 + b - (MODE == 0 ? 0 : p.keep_offset);
         float ibest = -1.0f;
         unsigned ibest_i = 0xffffffffu;
+        int ibest_r = 0;  // MODE 0: the winner's leg; its index is formed once, after the loop
 #pragma unroll
         for (int r = 0; r < RL; r++)
             {
@@ -290,9 +291,13 @@ __device__ __forceinline__ void gb_inv_col_tile(float2* smem, float* s_mag, unsi
                 if (mag > ibest)
                     {
                         ibest = mag;
-                        ibest_i = (unsigned)n;
+                        if (MODE == 0)
+                            ibest_r = r;
+                        else
+                            ibest_i = (unsigned)n;
                     }
             }
+        if (MODE == 0) ibest_i = (unsigned)(nbase + ibest_r * (NIL * N2));  // every leg is inside the row: ibest >= 0 > -1 always wins once
         if (peak_better(ibest, ibest_i, best, best_i))
             {
                 best = ibest;
