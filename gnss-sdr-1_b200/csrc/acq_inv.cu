@@ -305,17 +305,13 @@ __device__ __forceinline__ void gb_inv_col_tile(float2* smem, float* s_mag, unsi
             }
     });
         {
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1)
-                {
-                    const float om = __shfl_down_sync(0xffffffffu, best, o);
-                    const unsigned oi = __shfl_down_sync(0xffffffffu, best_i, o);
-                    if (peak_better(om, oi, best, best_i))
-                        {
-                            best = om;
-                            best_i = oi;
-                        }
-                }
+            // warp stage with two REDUX instructions instead of five shuffle rounds: magnitudes are >= +0 (or the -1 of "no
+            // output"; never NaN -- a NaN never wins a '>'), so their bit patterns order like unsigned integers; the first
+            // maximum is then the smallest index among the lanes that hold the winning pattern
+            const unsigned key = best >= 0.f ? __float_as_uint(best) + 1u : 0u;
+            const unsigned wkey = __reduce_max_sync(0xffffffffu, key);
+            best_i = __reduce_min_sync(0xffffffffu, key == wkey ? best_i : 0xffffffffu);
+            best = wkey ? __uint_as_float(wkey - 1u) : -1.0f;
             const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
             if (lane == 0)
                 {
