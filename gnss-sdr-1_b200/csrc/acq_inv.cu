@@ -199,14 +199,15 @@ __device__ __forceinline__ void gb_inv_row_tile(float2* smem, const PlanDev& pl,
     const float2* xs = p.spectra + (size_t)bin * N + (size_t)r0 * M;
     const float2* cs = p.code_fft[handle] + (size_t)r0 * M;
     dif_first<+1, L, true, M, DROW::kFirstR>(buf, pl.tw, [&](int b, int m) {
-        return b < nb ? cmul(__ldg(xs + b * M + m), __ldg(cs + b * M + m)) : make_float2(0.f, 0.f);
+        if ((N1 % TILE) != 0 && b >= nb) return make_float2(0.f, 0.f);  // (tiles are whole when TILE divides N1: no guard compiled)
+        return cmul(__ldg(xs + b * M + m), __ldg(cs + b * M + m));
     });
     if (dep && threadIdx.x == 0 && dep_seen < need)
         while (gb_ld_poll(dep) < need) __nanosleep(64);
     __syncthreads();
     float2* dst = dst_transform + (size_t)r0 * M;
     DROW::template run_rest<+1, L, true>(buf, tw, [&](int b, int i, const float2* v) {
-        if (b >= nb) return;
+        if ((N1 % TILE) != 0 && b >= nb) return;
         float2 w = cmul(tlo[b * IL + (i & (IL - 1))], thi[b * IH + (i / IL)]);  // W_N^(k1 i)
         const float2 ws = step[b];
         float2* d = dst + b * M + i;
