@@ -446,12 +446,13 @@ def test_fused_persistent_inverse_matches_default_path():
     assert " passed" in r.stdout
 
 
-@pytest.mark.parametrize("tune", ["acq_fwd_groups=4,acq_chunk_t=3", "acq_fwd_generic=1"])
+@pytest.mark.parametrize("tune", ["acq_fwd_groups=4,acq_chunk_t=3", "acq_fwd_generic=1", "acq_variant=1"])
 def test_forward_side_options_match_default_path(tune):
     """Tuning keys of the forward side, each in a child process steered by GB200_TUNE running this file's batch-search parity tests
     against the oracle: acq_fwd_groups > 1 (forward transforms in bin groups on their own stream, transforms numbered bin-major,
     inverse chunks waiting only for the groups they read; acq_chunk_t=3 forces several chunks on the small test grids) and
-    acq_fwd_generic=1 (the run-time parametrised forward kernels where the compile-time DIF tiles would be used)."""
+    acq_fwd_generic=1 (the run-time parametrised forward kernels where the compile-time DIF tiles would be used); acq_variant=1
+    (the three-pass radix orders that were the defaults before the radix-20 / 25 butterflies, still selectable)."""
     import subprocess
     import sys as _sys
 
